@@ -1,0 +1,110 @@
+// TEST INFRASTRUCTURE ONLY (oracle/): C entry points over the reference's OWN classes, compiled
+// from the sources where they lie under /root/reference (see ../Makefile) into oracle/_ref/.
+// Nothing here is on the product path; tests and bench.py's cpu_baseline / --impl reference legs
+// load it through ctypes as the checker / the timed CPU arm.
+//
+// Reference code exercised (unmodified): gm_graph (apps/output_cpp/gm_graph/src/gm_graph.cc),
+// load/store_binary (src/gm_graph_binary_loader.cc:42-252), generators (src/graph_gen.cc:58-287),
+// gm_bfs_template (inc/gm_bfs_template.h:14-754).  pagerank()/hop_dist() are the restated generated
+// procedures in this directory (gm_comp is not buildable here).
+#include <stdio.h>
+#include <string.h>
+#include <sys/time.h>
+#include <vector>
+#include "gm.h"
+#include "graph_gen.h"
+#include "pagerank.h"
+#include "hop_dist.h"
+
+static double now_ms() {
+    struct timeval t;
+    gettimeofday(&t, NULL);
+    return t.tv_sec * 1000.0 + t.tv_usec * 0.001;
+}
+
+// gm_bfs_template<short, multithread, no navigator, forward edges, no save_child>: the shape the
+// code generator emits for a plain InBFS (src/backend_cpp/gm_cpp_gen_bfs.cc:88-221, level_t = short :90).
+class level_recorder_bfs : public gm_bfs_template<short, true, false, false, false> {
+  public:
+    level_recorder_bfs(gm_graph& g, short* out) : gm_bfs_template<short, true, false, false, false>(g), lev(out), levels(0) {}
+    int levels;
+  protected:
+    virtual void visit_fw(node_t t) { lev[t] = get_curr_level(); }
+    virtual void visit_rv(node_t) {}
+    virtual bool check_navigator(node_t, edge_t) { return true; }
+    virtual void do_end_of_level_fw() { levels++; }
+  private:
+    short* lev;
+};
+
+extern "C" {
+
+void ref_set_threads(int n) {
+    gm_rt_initialize();
+    gm_rt_set_num_threads(n);
+}
+int ref_get_threads(void) { return gm_rt_get_num_threads(); }
+
+// after external creation the reference's load path runs do_semi_sort() then make_reverse_edges()
+// (gm_graph_binary_loader.cc:190-197); mirror that so a generated graph equals a stored+loaded one.
+static void* finish(gm_graph* g) {
+    g->do_semi_sort();
+    g->make_reverse_edges();
+    return g;
+}
+
+void* ref_graph_uniform(int32_t N, int32_t M, long seed, int use_xorshift) {
+    return finish(create_uniform_random_graph(N, M, seed, use_xorshift != 0));
+}
+void* ref_graph_rmat(int32_t N, int32_t M, long seed, double a, double b, double c, int permute) {
+    return finish(create_RMAT_graph(N, M, seed, a, b, c, permute != 0));
+}
+void* ref_graph_from_csr(int32_t N, int32_t M, const int32_t* begin, const int32_t* node_idx) {
+    gm_graph* g = new gm_graph();
+    g->prepare_external_creation(N, M);
+    memcpy(g->begin, begin, sizeof(int32_t) * ((size_t)N + 1));
+    memcpy(g->node_idx, node_idx, sizeof(int32_t) * (size_t)M);
+    return finish(g);
+}
+void* ref_graph_load(const char* path) {
+    gm_graph* g = new gm_graph();
+    if (!g->load_binary((char*)path)) { delete g; return NULL; }
+    return g;
+}
+int ref_graph_store(void* h, const char* path) { return ((gm_graph*)h)->store_binary((char*)path) ? 1 : 0; }
+void ref_graph_free(void* h) { delete (gm_graph*)h; }
+int32_t ref_graph_num_nodes(void* h) { return ((gm_graph*)h)->num_nodes(); }
+int32_t ref_graph_num_edges(void* h) { return ((gm_graph*)h)->num_edges(); }
+const int32_t* ref_graph_begin(void* h) { return ((gm_graph*)h)->begin; }
+const int32_t* ref_graph_node_idx(void* h) { return ((gm_graph*)h)->node_idx; }
+const int32_t* ref_graph_r_begin(void* h) { return ((gm_graph*)h)->r_begin; }
+const int32_t* ref_graph_r_node_idx(void* h) { return ((gm_graph*)h)->r_node_idx; }
+const int32_t* ref_graph_e_rev2idx(void* h) { return ((gm_graph*)h)->e_rev2idx; }
+const int32_t* ref_graph_e_idx2idx(void* h) { return ((gm_graph*)h)->e_idx2idx; }
+
+// returns elapsed ms of the procedure call (what common_main.h:198-201 prints as "running time=")
+double ref_pagerank(void* h, double e, double d, int32_t max_iter, double* rank) {
+    double t0 = now_ms();
+    pagerank(*(gm_graph*)h, e, d, max_iter, rank);
+    return now_ms() - t0;
+}
+double ref_hop_dist(void* h, int32_t root, int32_t* dist) {
+    node_t r = root;
+    double t0 = now_ms();
+    hop_dist(*(gm_graph*)h, dist, r);
+    return now_ms() - t0;
+}
+// levels[t] = BFS level of t from root, -2 (the template's __INVALID_LEVEL, gm_bfs_template.h:725) if unreached.
+double ref_bfs_levels(void* h, int32_t root, int16_t* levels, int32_t* n_levels) {
+    gm_graph& G = *(gm_graph*)h;
+    for (node_t i = 0; i < G.num_nodes(); i++) levels[i] = -2;
+    double t0 = now_ms();
+    level_recorder_bfs bfs(G, levels);
+    bfs.prepare(root, gm_rt_get_num_threads());
+    bfs.do_bfs_forward();
+    double t = now_ms() - t0;
+    if (n_levels) *n_levels = bfs.levels;
+    return t;
+}
+
+}  // extern "C"
