@@ -1,0 +1,299 @@
+"""ctypes binding of include/gm_cuda.h.  No compute happens in Python and there is no fallback:
+if libgm_cuda.so is missing, or no CUDA device is usable, calls raise."""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def lib_path():
+    return os.path.join(_HERE, "lib", "libgm_cuda.so")
+
+
+class GmcError(RuntimeError):
+    pass
+
+
+class PagerankInfo(C.Structure):
+    _fields_ = [("iterations", C.c_int32), ("diff", C.c_double), ("kernel_ms", C.c_float), ("launches", C.c_int32)]
+
+
+class BfsInfo(C.Structure):
+    _fields_ = [("levels", C.c_int32), ("reached", C.c_int32), ("edges_traversed", C.c_int64),
+                ("kernel_ms", C.c_float), ("launches", C.c_int32), ("bottom_up_levels", C.c_int32)]
+
+
+ARR = dict(begin=0, node_idx=1, r_begin=2, r_node_idx=3, e_rev2idx=4, e_idx2idx=5)
+_vp = C.c_void_p
+_i32 = C.c_int32
+
+# name -> (restype, argtypes); every symbol include/gm_cuda.h declares
+SIGNATURES = {
+    "gmc_last_error": (C.c_char_p, []),
+    "gmc_version": (C.c_int, []),
+    "gmc_device_count": (C.c_int, [C.POINTER(C.c_int)]),
+    "gmc_init": (C.c_int, [C.c_int]),
+    "gmc_device_info": (C.c_int, [C.POINTER(C.c_int), C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
+    "gmc_sync": (C.c_int, [_vp]),
+    "gmc_malloc": (C.c_int, [C.POINTER(_vp), C.c_size_t]),
+    "gmc_free": (C.c_int, [_vp]),
+    "gmc_h2d": (C.c_int, [_vp, _vp, C.c_size_t, _vp]),
+    "gmc_d2h": (C.c_int, [_vp, _vp, C.c_size_t, _vp]),
+    "gmc_host_register": (C.c_int, [_vp, C.c_size_t]),
+    "gmc_host_unregister": (C.c_int, [_vp]),
+    "gmc_graph_create": (C.c_int, [C.POINTER(_vp), _i32, _i32]),
+    "gmc_graph_destroy": (C.c_int, [_vp]),
+    "gmc_graph_num_nodes": (C.c_int, [_vp, C.POINTER(_i32)]),
+    "gmc_graph_num_edges": (C.c_int, [_vp, C.POINTER(_i32)]),
+    "gmc_graph_upload": (C.c_int, [_vp, _vp, _vp, _vp]),
+    "gmc_graph_upload_reverse": (C.c_int, [_vp, _vp, _vp, _vp]),
+    "gmc_graph_semi_sort": (C.c_int, [_vp, C.c_int, _vp]),
+    "gmc_graph_make_reverse": (C.c_int, [_vp, C.c_int, _vp]),
+    "gmc_graph_has_reverse": (C.c_int, [_vp, C.POINTER(C.c_int)]),
+    "gmc_graph_download": (C.c_int, [_vp, C.c_int, _vp, C.c_size_t, _vp]),
+    "gmc_graph_device_ptr": (C.c_int, [_vp, C.c_int, C.POINTER(_vp)]),
+    "gmc_graph_generate_uniform": (C.c_int, [C.POINTER(_vp), _i32, _i32, C.c_uint64]),
+    "gmc_graph_generate_rmat": (C.c_int, [C.POINTER(_vp), _i32, _i32, C.c_uint64, C.c_double, C.c_double, C.c_double, C.c_int]),
+    "gmc_file_read_header": (C.c_int, [C.c_char_p, C.POINTER(_i32), C.POINTER(_i32)]),
+    "gmc_file_read": (C.c_int, [C.c_char_p, _vp, _vp]),
+    "gmc_file_write": (C.c_int, [C.c_char_p, _i32, _i32, _vp, _vp]),
+    "gmc_pagerank": (C.c_int, [_vp, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo)]),
+    "gmc_pagerank_dev": (C.c_int, [_vp, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo), _vp]),
+    "gmc_pr_shard_create": (C.c_int, [C.POINTER(_vp), _i32, _i32, _i32, _vp, _vp, _vp]),
+    "gmc_pr_shard_destroy": (C.c_int, [_vp]),
+    "gmc_pr_shard_set_peers": (C.c_int, [_vp, C.c_int, _vp, _vp]),
+    "gmc_pr_shard_init": (C.c_int, [_vp, _vp, _vp, _vp]),
+    "gmc_pr_shard_sweep": (C.c_int, [_vp, C.c_double, _vp, _vp, _vp, _vp, _vp, C.c_int, _vp]),
+    "gmc_pr_shard_launches_per_sweep": (C.c_int, [_vp, C.POINTER(_i32)]),
+    "gmc_hop_dist": (C.c_int, [_vp, _i32, _vp, C.POINTER(BfsInfo)]),
+    "gmc_hop_dist_dev": (C.c_int, [_vp, _i32, _vp, C.POINTER(BfsInfo), _vp]),
+    "gmc_bfs_levels": (C.c_int, [_vp, _i32, C.c_int, _vp, _vp, _vp, _i32, C.POINTER(BfsInfo)]),
+    "gmc_bfs_level_order": (C.c_int, [_vp, _vp, _vp, _i32]),
+}
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        assert a.flags["C_CONTIGUOUS"]
+        return a.ctypes.data_as(_vp)
+    return _vp(int(a))
+
+
+def _i32arr(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+class GmCuda:
+    """Loaded libgm_cuda.so.  Constructing it does not touch the GPU; `init()` does."""
+
+    def __init__(self, path=None):
+        path = path or lib_path()
+        if not os.path.exists(path):
+            raise GmcError(f"{path} not found: build it with `make -C green-marl_b200` "
+                           f"(or __graft_entry__.build()); there is no CPU fallback")
+        self.path = path
+        self.L = C.CDLL(path)
+        for name, (res, args) in SIGNATURES.items():
+            f = getattr(self.L, name)     # AttributeError if a declared symbol is missing
+            f.restype = res
+            f.argtypes = args
+
+    def check(self, rc):
+        if rc != 0:
+            raise GmcError(f"gmc status {rc}: {self.L.gmc_last_error().decode(errors='replace')}")
+
+    def init(self, device=0):
+        self.check(self.L.gmc_init(device))
+
+    def device_count(self):
+        n = C.c_int()
+        self.check(self.L.gmc_device_count(C.byref(n)))
+        return n.value
+
+    def device_info(self):
+        sm = C.c_int(); tot = C.c_size_t(); free = C.c_size_t()
+        self.check(self.L.gmc_device_info(C.byref(sm), C.byref(tot), C.byref(free)))
+        return sm.value, tot.value, free.value
+
+    # ---- graphs --------------------------------------------------------------------------
+    def graph_from_csr(self, begin, node_idx, semi_sort=False, make_reverse=True, want_maps=False):
+        begin = _i32arr(begin); node_idx = _i32arr(node_idx)
+        h = _vp()
+        self.check(self.L.gmc_graph_create(C.byref(h), len(begin) - 1, len(node_idx)))
+        g = Graph(self, h)
+        self.check(self.L.gmc_graph_upload(h, _ptr(begin), _ptr(node_idx), None))
+        if semi_sort:
+            self.check(self.L.gmc_graph_semi_sort(h, int(want_maps), None))
+        if make_reverse:
+            self.check(self.L.gmc_graph_make_reverse(h, int(want_maps), None))
+        return g
+
+    def generate_rmat(self, n, m, seed=1997, a=0.57, b=0.19, c=0.19, permute=True):
+        h = _vp()
+        self.check(self.L.gmc_graph_generate_rmat(C.byref(h), n, m, seed, a, b, c, int(permute)))
+        return Graph(self, h)
+
+    def generate_uniform(self, n, m, seed=1997):
+        h = _vp()
+        self.check(self.L.gmc_graph_generate_uniform(C.byref(h), n, m, seed))
+        return Graph(self, h)
+
+    # ---- files ---------------------------------------------------------------------------
+    def file_read(self, path):
+        n = _i32(); m = _i32()
+        self.check(self.L.gmc_file_read_header(path.encode(), C.byref(n), C.byref(m)))
+        begin = np.zeros(n.value + 1, np.int32); idx = np.zeros(max(m.value, 1), np.int32)
+        self.check(self.L.gmc_file_read(path.encode(), _ptr(begin), _ptr(idx)))
+        return begin, idx[:m.value]
+
+    def file_write(self, path, begin, node_idx):
+        begin = _i32arr(begin); node_idx = _i32arr(node_idx)
+        self.check(self.L.gmc_file_write(path.encode(), len(begin) - 1, len(node_idx), _ptr(begin), _ptr(node_idx)))
+
+    # ---- raw memory ----------------------------------------------------------------------
+    def malloc(self, nbytes):
+        p = _vp()
+        self.check(self.L.gmc_malloc(C.byref(p), nbytes))
+        return p.value
+
+    def free(self, p):
+        self.check(self.L.gmc_free(_vp(p)))
+
+    def h2d(self, dev, host, stream=None):
+        self.check(self.L.gmc_h2d(_vp(dev), _ptr(host), host.nbytes, _vp(stream) if stream else None))
+
+    def d2h(self, host, dev, stream=None):
+        self.check(self.L.gmc_d2h(_ptr(host), _vp(dev), host.nbytes, _vp(stream) if stream else None))
+
+    def sync(self, stream=None):
+        self.check(self.L.gmc_sync(_vp(stream) if stream else None))
+
+
+class Graph:
+    """Device-resident CSR (gmc_graph)."""
+
+    def __init__(self, lib, handle):
+        self.lib = lib
+        self.h = handle
+
+    def close(self):
+        if self.h:
+            self.lib.L.gmc_graph_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def num_nodes(self):
+        n = _i32(); self.lib.check(self.lib.L.gmc_graph_num_nodes(self.h, C.byref(n))); return n.value
+
+    @property
+    def num_edges(self):
+        m = _i32(); self.lib.check(self.lib.L.gmc_graph_num_edges(self.h, C.byref(m))); return m.value
+
+    def array(self, name):
+        n, m = self.num_nodes, self.num_edges
+        ln = n + 1 if name in ("begin", "r_begin") else m
+        out = np.zeros(max(ln, 1), np.int32)
+        self.lib.check(self.lib.L.gmc_graph_download(self.h, ARR[name], _ptr(out), ln, None))
+        return out[:ln]
+
+    def device_ptr(self, name):
+        p = _vp()
+        self.lib.check(self.lib.L.gmc_graph_device_ptr(self.h, ARR[name], C.byref(p)))
+        return p.value
+
+    def semi_sort(self, want_idx2idx=False):
+        self.lib.check(self.lib.L.gmc_graph_semi_sort(self.h, int(want_idx2idx), None))
+
+    def make_reverse(self, want_rev2idx=False):
+        self.lib.check(self.lib.L.gmc_graph_make_reverse(self.h, int(want_rev2idx), None))
+
+    def upload_reverse(self, r_begin, r_node_idx):
+        r_begin = _i32arr(r_begin); r_node_idx = _i32arr(r_node_idx)
+        self.lib.check(self.lib.L.gmc_graph_upload_reverse(self.h, _ptr(r_begin), _ptr(r_node_idx), None))
+
+    def pagerank(self, e=1e-30, d=0.85, max_iter=20):
+        rank = np.zeros(max(self.num_nodes, 1), np.float64)
+        info = PagerankInfo()
+        self.lib.check(self.lib.L.gmc_pagerank(self.h, e, d, max_iter, _ptr(rank), C.byref(info)))
+        return rank[:self.num_nodes], info
+
+    def pagerank_dev(self, rank_dev_ptr, e=1e-30, d=0.85, max_iter=20, stream=None):
+        info = PagerankInfo()
+        self.lib.check(self.lib.L.gmc_pagerank_dev(self.h, e, d, max_iter, _vp(rank_dev_ptr), C.byref(info),
+                                                   _vp(stream) if stream else None))
+        return info
+
+    def hop_dist(self, root=0):
+        dist = np.zeros(max(self.num_nodes, 1), np.int32)
+        info = BfsInfo()
+        self.lib.check(self.lib.L.gmc_hop_dist(self.h, root, _ptr(dist), C.byref(info)))
+        return dist[:self.num_nodes], info
+
+    def hop_dist_dev(self, dist_dev_ptr, root=0, stream=None):
+        info = BfsInfo()
+        self.lib.check(self.lib.L.gmc_hop_dist_dev(self.h, root, _vp(dist_dev_ptr), C.byref(info),
+                                                   _vp(stream) if stream else None))
+        return info
+
+    def bfs_levels(self, root=0, use_reverse_edge=False, cap=256):
+        lev = np.zeros(max(self.num_nodes, 1), np.int16)
+        trace = np.full(cap, -1, np.int32); cnt = np.zeros(cap, np.int32)
+        info = BfsInfo()
+        self.lib.check(self.lib.L.gmc_bfs_levels(self.h, root, int(use_reverse_edge), _ptr(lev), _ptr(trace), _ptr(cnt), cap, C.byref(info)))
+        k = min(info.levels, cap)
+        return lev[:self.num_nodes], info, trace[:k], cnt[:k]
+
+    def bfs_level_order(self, n_levels):
+        order = np.zeros(max(self.num_nodes, 1), np.int32)
+        lb = np.zeros(n_levels + 1, np.int32)
+        self.lib.check(self.lib.L.gmc_bfs_level_order(self.h, _ptr(order), _ptr(lb), n_levels + 1))
+        return order[:lb[-1]], lb
+
+
+class PrShard:
+    """Destination-range shard of the PageRank sweep (multi-GPU building block)."""
+
+    def __init__(self, lib, n_global, lo, hi, r_begin_slice, r_node_idx_slice, outdeg_slice):
+        self.lib = lib
+        self.lo, self.hi, self.n_global = lo, hi, n_global
+        rb = _i32arr(r_begin_slice); ri = _i32arr(r_node_idx_slice); od = _i32arr(outdeg_slice)
+        h = _vp()
+        lib.check(lib.L.gmc_pr_shard_create(C.byref(h), n_global, lo, hi, _ptr(rb), _ptr(ri) if len(ri) else None, _ptr(od)))
+        self.h = h
+
+    def close(self):
+        if self.h:
+            self.lib.L.gmc_pr_shard_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_peers(self, even_ptrs, odd_ptrs):
+        n = len(even_ptrs)
+        ev = (C.c_void_p * n)(*even_ptrs); od = (C.c_void_p * n)(*odd_ptrs)
+        self.lib.check(self.lib.L.gmc_pr_shard_set_peers(self.h, n, C.cast(ev, _vp), C.cast(od, _vp)))
+
+    def init(self, contrib_full_ptr, rank_slice_ptr, stream=None):
+        self.lib.check(self.lib.L.gmc_pr_shard_init(self.h, _vp(contrib_full_ptr), _vp(rank_slice_ptr), _vp(stream) if stream else None))
+
+    def sweep(self, d, contrib_in, contrib_out, rank_in, rank_out, diff_part=None, parity=0, stream=None):
+        self.lib.check(self.lib.L.gmc_pr_shard_sweep(self.h, d, _vp(contrib_in), _vp(contrib_out), _vp(rank_in), _vp(rank_out),
+                                                     _vp(diff_part) if diff_part else None, parity, _vp(stream) if stream else None))
+
+    def launches_per_sweep(self):
+        n = _i32()
+        self.lib.check(self.lib.L.gmc_pr_shard_launches_per_sweep(self.h, C.byref(n)))
+        return n.value

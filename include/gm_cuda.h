@@ -1,0 +1,154 @@
+/* gm_cuda.h -- the thin extern "C" boundary of libgm_cuda (B200 / sm_100a).
+ *
+ * Everything the C++ facade (the headers under include/gm/: gm_graph, shl_array, gm_bfs_template, the "generated"
+ * pagerank()/hop_dist()) and the Python harness need from the device goes through these entry points:
+ * plain pointers and sizes, no C++ or torch types.  Ids are the reference's default build,
+ * node_t = edge_t = int32_t (reference setup.mk:55-56; apps/output_cpp/gm_graph/inc/gm_graph_typedef.h:8-20).
+ * Citations are relative to the reference tree (/root/reference).
+ *
+ * Conventions: every function returns GMC_OK (0) or a negative gmc_status; gmc_last_error() gives the
+ * text (thread-local).  `stream` arguments are a cudaStream_t passed as void* (NULL = default stream).
+ * There is NO CPU fallback: without a usable CUDA device every compute entry fails with GMC_ERR_CUDA.
+ */
+#ifndef GM_CUDA_H
+#define GM_CUDA_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    GMC_OK = 0,
+    GMC_ERR_CUDA = -1,      /* a CUDA runtime call failed / no device */
+    GMC_ERR_ARG = -2,       /* bad argument (NULL, negative size, root out of range ...) */
+    GMC_ERR_STATE = -3,     /* graph not in the state the call needs (e.g. no reverse CSR) */
+    GMC_ERR_IO = -4,        /* file could not be read / written / wrong format */
+    GMC_ERR_NOMEM = -5
+} gmc_status;
+
+const char* gmc_last_error(void);
+int gmc_version(void);
+
+/* --- device ------------------------------------------------------------------------------------
+ * replaces shl__init(nthreads, partitioned) (reference apps/output_cpp/src/common_main.h:95-99):
+ * "sockets" become devices. */
+int gmc_device_count(int* count);
+int gmc_init(int device);                          /* cudaSetDevice + context warm-up */
+int gmc_device_info(int* sm_count, size_t* total_bytes, size_t* free_bytes);
+int gmc_sync(void* stream);
+
+/* --- raw device arrays: what shl_array<T>::alloc/copy_from/copy_back become in HBM
+ * (call sites: reference src/backend_cpp/gm_cpp_gen.cc:687-775, 1468-1486). */
+int gmc_malloc(void** dev_ptr, size_t bytes);
+int gmc_free(void* dev_ptr);
+int gmc_h2d(void* dev_dst, const void* host_src, size_t bytes, void* stream);
+int gmc_d2h(void* host_dst, const void* dev_src, size_t bytes, void* stream);
+int gmc_host_register(void* host_ptr, size_t bytes);   /* pin caller-owned host arrays for fast copies */
+int gmc_host_unregister(void* host_ptr);
+
+/* --- device-resident CSR mirror of gm_graph (reference apps/output_cpp/gm_graph/inc/gm_graph.h:119-445) */
+typedef struct gmc_graph gmc_graph;
+enum { GMC_ARR_BEGIN = 0, GMC_ARR_NODE_IDX = 1, GMC_ARR_R_BEGIN = 2, GMC_ARR_R_NODE_IDX = 3,
+       GMC_ARR_E_REV2IDX = 4, GMC_ARR_E_IDX2IDX = 5 };
+
+/* allocate begin[N+1], node_idx[M] in HBM: gm_graph::prepare_external_creation (gm_graph.cc:506-514) */
+int gmc_graph_create(gmc_graph** out, int32_t num_nodes, int32_t num_edges);
+int gmc_graph_destroy(gmc_graph* g);
+int gmc_graph_num_nodes(const gmc_graph* g, int32_t* n);
+int gmc_graph_num_edges(const gmc_graph* g, int32_t* m);
+/* host -> HBM copy of the frozen CSR (the copy_from of shl__G_begin / shl__G_node_idx) */
+int gmc_graph_upload(gmc_graph* g, const int32_t* begin, const int32_t* node_idx, void* stream);
+/* host-built reverse CSR -> HBM (when the caller already holds r_begin / r_node_idx) */
+int gmc_graph_upload_reverse(gmc_graph* g, const int32_t* r_begin, const int32_t* r_node_idx, void* stream);
+/* gm_graph::do_semi_sort on device (gm_graph.cc:468-503, semi_sort_main :380-423): rows ascending by
+ * neighbour id; with want_idx2idx the permutation e_idx2idx is kept (ties: ascending original index). */
+int gmc_graph_semi_sort(gmc_graph* g, int want_idx2idx, void* stream);
+/* gm_graph::make_reverse_edges on device (gm_graph.cc:205-304 incl. do_semi_sort_reverse :293):
+ * builds r_begin, r_node_idx (rows ascending by source id) and, if asked, e_rev2idx (ties: ascending
+ * edge index). */
+int gmc_graph_make_reverse(gmc_graph* g, int want_rev2idx, void* stream);
+int gmc_graph_has_reverse(const gmc_graph* g, int* yes);
+/* HBM -> host copy of one array (`which` = GMC_ARR_*); count is checked against the array length */
+int gmc_graph_download(const gmc_graph* g, int which, int32_t* host_dst, size_t count, void* stream);
+int gmc_graph_device_ptr(const gmc_graph* g, int which, const int32_t** dev_ptr);
+
+/* --- synthetic generators on device (reference apps/output_cpp/gm_graph/src/graph_gen.cc:58-104,159-287).
+ * Same edge distributions as the reference generators but a counter-based RNG (the reference's libc
+ * rand()/drand48() streams are serial), so graphs are NOT edge-for-edge those of the reference; parity
+ * runs feed the same CSR to both sides.  The result is frozen, semi-sorted, with reverse edges. */
+int gmc_graph_generate_uniform(gmc_graph** out, int32_t num_nodes, int32_t num_edges, uint64_t seed);
+int gmc_graph_generate_rmat(gmc_graph** out, int32_t num_nodes, int32_t num_edges, uint64_t seed,
+                            double a, double b, double c, int permute);
+
+/* --- binary CSR file, basic format (reference gm_graph_binary_loader.cc:19-26): bulk read + byte swap */
+int gmc_file_read_header(const char* path, int32_t* num_nodes, int32_t* num_edges);
+int gmc_file_read(const char* path, int32_t* begin, int32_t* node_idx);
+int gmc_file_write(const char* path, int32_t num_nodes, int32_t num_edges, const int32_t* begin,
+                   const int32_t* node_idx);
+
+/* --- PageRank: the generated pagerank() (reference apps/src/pagerank.gm:1-20; emitted loop shape
+ * reconstructed in SURVEY.md 3.1).  rank = 1/N; do { sweep; cnt++ } while (diff > e && cnt < max_iter).
+ * Needs the reverse CSR.  fp64 throughout; per-edge term rank[w]/(double)outdeg(w) as in the reference. */
+typedef struct {
+    int32_t iterations;      /* cnt at exit */
+    double  diff;            /* last diff = sum_t |val_t - rank_t| */
+    float   kernel_ms;       /* device time of the iteration loop (CUDA events, sweep kernels only) */
+    int32_t launches;        /* kernels launched inside that region */
+} gmc_pagerank_info;
+/* result copied to caller-owned HOST memory (what shl_array::copy_back does, gm_cpp_gen.cc:1480) */
+int gmc_pagerank(gmc_graph* g, double e, double d, int32_t max_iter, double* rank_host,
+                 gmc_pagerank_info* info);
+/* result left in caller-provided DEVICE memory (N doubles) */
+int gmc_pagerank_dev(gmc_graph* g, double e, double d, int32_t max_iter, double* rank_dev,
+                     gmc_pagerank_info* info, void* stream);
+
+/* --- PageRank over a destination-range shard (multi-GPU).  A shard owns rows [lo,hi) of
+ * the reverse CSR (r_begin slice rebased to 0, global source ids) and the out-degrees of its own
+ * vertices.  One sweep reads the FULL contribution vector contrib_in[N] (= rank[w]/outdeg[w]) and
+ * writes contrib_out[lo..hi), rank_out[0..hi-lo) and *diff_part (device scalar).  The exchange of the
+ * contrib slices between ranks is done by the caller (NCCL allgather) or by the sweep itself when
+ * peer pointers are registered (gmc_pr_shard_set_peers): then each slice element is also stored into
+ * every peer's contrib_out over NVLink from the kernel epilogue. */
+typedef struct gmc_pr_shard gmc_pr_shard;
+int gmc_pr_shard_create(gmc_pr_shard** out, int32_t num_nodes_global, int32_t lo, int32_t hi,
+                        const int32_t* r_begin_slice_host, const int32_t* r_node_idx_slice_host,
+                        const int32_t* out_degree_slice_host);
+int gmc_pr_shard_destroy(gmc_pr_shard* s);
+int gmc_pr_shard_set_peers(gmc_pr_shard* s, int n_peers, double* const* peer_contrib_even,
+                           double* const* peer_contrib_odd);
+/* contrib[lo..hi) = (1/N)/outdeg, rank[0..hi-lo) = 1/N */
+int gmc_pr_shard_init(gmc_pr_shard* s, double* contrib_full_dev, double* rank_slice_dev, void* stream);
+int gmc_pr_shard_sweep(gmc_pr_shard* s, double d, const double* contrib_in_full_dev,
+                       double* contrib_out_full_dev, const double* rank_in_slice_dev,
+                       double* rank_out_slice_dev, double* diff_part_dev, int parity, void* stream);
+int gmc_pr_shard_launches_per_sweep(const gmc_pr_shard* s, int32_t* n);
+
+/* --- BFS.  One direction-optimizing, frontier-compacted engine behind both reference entry points:
+ *  - generated hop_dist() (reference apps/src/hop_dist.gm:3-31): dist int32, INT_MAX = unreachable;
+ *  - gm_bfs_template<short,...>::do_bfs_forward (reference inc/gm_bfs_template.h:69-271): level int16,
+ *    -2 = unvisited (:725), per-level vertex counts and the state used for each level (:713-719).
+ * The level-to-level state machine follows the reference's transition rules (get_next_state :352-421). */
+typedef struct {
+    int32_t levels;          /* number of BFS levels (root level included) */
+    int32_t reached;         /* vertices reached (root included) */
+    int64_t edges_traversed; /* sum of out-degrees of reached vertices (M_r of SURVEY.md 8d) */
+    float   kernel_ms;       /* device time from first to last kernel */
+    int32_t launches;
+    int32_t bottom_up_levels;
+} gmc_bfs_info;
+int gmc_hop_dist(gmc_graph* g, int32_t root, int32_t* dist_host, gmc_bfs_info* info);
+int gmc_hop_dist_dev(gmc_graph* g, int32_t root, int32_t* dist_dev, gmc_bfs_info* info, void* stream);
+/* use_reverse_edge: traverse in-edges instead of out-edges (template parameter of the reference class).
+ * state_trace / level_count: optional host arrays of capacity trace_cap. */
+int gmc_bfs_levels(gmc_graph* g, int32_t root, int use_reverse_edge, int16_t* level_host,
+                   int32_t* state_trace, int32_t* level_count, int32_t trace_cap, gmc_bfs_info* info);
+/* vertices of every level, concatenated in level order (the reference's global_vector /
+ * level_queue_begin, gm_bfs_template.h:423-447), for do_bfs_reverse and host callback replay.
+ * order_host[N]; level_begin_host[levels+1]. Valid after gmc_bfs_levels on the same graph. */
+int gmc_bfs_level_order(gmc_graph* g, int32_t* order_host, int32_t* level_begin_host, int32_t cap_levels);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

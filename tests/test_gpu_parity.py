@@ -1,0 +1,239 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI (include/gm_cuda.h), against the
+oracle on the same seeded inputs.  BFS distances/levels and CSR builds: bit-exact.  PageRank: the
+north-star tolerance max|gpu - ref| <= 1e-9 at a fixed iteration count (and in practice far tighter:
+rows of in-degree <= 2048 are summed in the reference's order and must be bit-identical)."""
+import numpy as np
+import pytest
+
+import graphs
+
+pytestmark = pytest.mark.gpu
+PR_TOL = 1e-9          # BASELINE.json north_star: max abs diff <= 1e-9 in double at fixed iteration count
+INT_MAX = 2**31 - 1
+
+
+def dev_graph(gm, g):
+    dg = gm.graph_from_csr(g["begin"], g["node_idx"], semi_sort=False, make_reverse=False)
+    dg.upload_reverse(g["r_begin"], g["r_node_idx"])
+    return dg
+
+
+@pytest.fixture(scope="module")
+def g_c1(oracle):
+    return graphs.c1(oracle)
+
+
+@pytest.fixture(scope="module")
+def g_rmat(oracle):
+    return graphs.rmat(oracle, 200000, 3000000)
+
+
+def test_reverse_build_c1(gm, oracle, g_c1):
+    dg = gm.graph_from_csr(g_c1["begin"], g_c1["node_idx"], semi_sort=True, make_reverse=True, want_maps=True)
+    assert np.array_equal(dg.array("node_idx"), g_c1["node_idx"])
+    assert np.array_equal(dg.array("r_begin"), g_c1["r_begin"])
+    assert np.array_equal(dg.array("r_node_idx"), g_c1["r_node_idx"])
+    _, _, r2 = oracle.make_reverse(g_c1["begin"], g_c1["node_idx"], want_rev2idx=True)
+    assert np.array_equal(dg.array("e_rev2idx"), r2)
+
+
+def test_semi_sort_unsorted_input(gm, oracle):
+    b, i = oracle.rmat(50000, 600000, 7, 0.57, 0.19, 0.19, True)     # generator output: rows NOT sorted
+    dg = gm.graph_from_csr(b, i, semi_sort=True, make_reverse=True, want_maps=True)
+    g = graphs.prepared(oracle, b, i)
+    assert np.array_equal(dg.array("node_idx"), g["node_idx"])
+    assert np.array_equal(dg.array("r_begin"), g["r_begin"])
+    assert np.array_equal(dg.array("r_node_idx"), g["r_node_idx"])
+    idx2idx = dg.array("e_idx2idx")
+    assert np.array_equal(np.ascontiguousarray(i)[idx2idx], g["node_idx"])          # it IS the permutation applied
+    rev2idx = dg.array("e_rev2idx")
+    assert np.array_equal(np.sort(rev2idx), np.arange(len(i), dtype=np.int32))
+    src_of_edge = np.repeat(np.arange(g["N"], dtype=np.int32), np.diff(g["begin"]))
+    assert np.array_equal(src_of_edge[rev2idx], g["r_node_idx"])
+    assert np.array_equal(g["node_idx"][rev2idx], np.repeat(np.arange(g["N"], dtype=np.int32), np.diff(g["r_begin"])))
+
+
+def test_pagerank_c1_fixed_20(gm, oracle, g_c1):
+    dg = dev_graph(gm, g_c1)
+    rank, info = dg.pagerank(e=1e-30, d=0.85, max_iter=20)
+    want, it, diff = oracle.pagerank(g_c1["begin"], g_c1["r_begin"], g_c1["r_node_idx"], 1e-30, 0.85, 20)
+    assert info.iterations == it == 20
+    assert np.abs(rank - want).max() <= PR_TOL
+    # no row of C1 is longer than 2048 in-edges: summation order is the reference's => bit-identical
+    assert np.array_equal(rank, want), f"max ulp {graphs.max_ulp(rank, want)}"
+    assert abs(info.diff - diff) <= 1e-12 * max(1.0, abs(diff))
+    assert info.launches > 0
+
+
+def test_pagerank_convergence_exit(gm, oracle, g_c1):
+    """default arguments of the reference driver (pagerank_main.cc:11-16): e=0.001, d=0.85, max=100"""
+    dg = dev_graph(gm, g_c1)
+    rank, info = dg.pagerank(e=0.001, d=0.85, max_iter=100)
+    want, it, _ = oracle.pagerank(g_c1["begin"], g_c1["r_begin"], g_c1["r_node_idx"], 0.001, 0.85, 100)
+    assert info.iterations == it
+    assert np.array_equal(rank, want)
+
+
+@pytest.mark.parametrize("max_iter", [1, 2, 17, 33])
+def test_pagerank_iteration_counts(gm, oracle, g_c1, max_iter):
+    dg = dev_graph(gm, g_c1)
+    rank, info = dg.pagerank(e=1e-30, d=0.85, max_iter=max_iter)
+    want, it, _ = oracle.pagerank(g_c1["begin"], g_c1["r_begin"], g_c1["r_node_idx"], 1e-30, 0.85, max_iter)
+    assert info.iterations == it == max_iter
+    assert np.array_equal(rank, want)
+
+
+def test_pagerank_rmat_hubs(gm, oracle, g_rmat):
+    """power-law rows: hubs above 2048 in-edges take the chunked path (different association)"""
+    assert np.diff(g_rmat["r_begin"]).max() > 2048
+    dg = dev_graph(gm, g_rmat)
+    rank, info = dg.pagerank(e=1e-30, d=0.85, max_iter=20)
+    want, it, _ = oracle.pagerank(g_rmat["begin"], g_rmat["r_begin"], g_rmat["r_node_idx"], 1e-30, 0.85, 20)
+    assert info.iterations == it
+    err = np.abs(rank - want).max()
+    assert err <= PR_TOL
+    assert err <= 1e-15, f"max abs err {err}, max ulp {graphs.max_ulp(rank, want)}"
+
+
+def test_pagerank_device_built_reverse(gm, oracle, g_rmat):
+    dg = gm.graph_from_csr(g_rmat["begin"], g_rmat["node_idx"], semi_sort=True, make_reverse=True)
+    rank, _ = dg.pagerank(max_iter=5)
+    want, _, _ = oracle.pagerank(g_rmat["begin"], g_rmat["r_begin"], g_rmat["r_node_idx"], 1e-30, 0.85, 5)
+    assert np.abs(rank - want).max() <= 1e-15
+
+
+def test_pagerank_needs_reverse(gm, g_c1):
+    from gmb200_loader import load_package
+    dg = gm.graph_from_csr(g_c1["begin"], g_c1["node_idx"], make_reverse=False)
+    with pytest.raises(load_package().GmcError):
+        dg.pagerank()
+
+
+def test_hop_dist_c1(gm, oracle, g_c1):
+    dg = dev_graph(gm, g_c1)
+    dist, info = dg.hop_dist(0)
+    want, _ = oracle.hop_dist(g_c1["begin"], g_c1["node_idx"], 0)
+    assert np.array_equal(dist, want)
+    assert list(dist[:10]) == [0, 4, 4, 4, 4, 4, 4, 4, 5, 5]      # SURVEY.md F10, from the reference binary
+    assert info.reached == 65536 and info.levels == 7
+    assert info.edges_traversed == g_c1["M"]
+
+
+def test_bfs_levels_c1_state_machine(gm, oracle, g_c1):
+    dg = dev_graph(gm, g_c1)
+    lev, info, trace, cnt = dg.bfs_levels(0)
+    want, nl, wtrace, wcnt = oracle.bfs_levels(g_c1["begin"], g_c1["node_idx"], g_c1["r_begin"], g_c1["r_node_idx"], 0)
+    assert np.array_equal(lev, want)
+    assert info.levels == nl
+    assert list(trace) == list(wtrace)        # same direction switches as gm_bfs_template
+    assert list(cnt) == list(wcnt)
+    assert info.bottom_up_levels == sum(1 for s in wtrace if s in (5, 6))
+
+
+@pytest.mark.parametrize("root_kind", ["zero", "first_with_edges", "hub", "random"])
+def test_bfs_rmat_roots(gm, oracle, g_rmat, root_kind):
+    deg = np.diff(g_rmat["begin"])
+    root = {"zero": 0, "first_with_edges": graphs.first_root_with_edges(g_rmat), "hub": int(deg.argmax()),
+            "random": int(np.random.RandomState(1997).randint(g_rmat["N"]))}[root_kind]
+    dg = dev_graph(gm, g_rmat)
+    dist, info = dg.hop_dist(root)
+    want, _ = oracle.hop_dist(g_rmat["begin"], g_rmat["node_idx"], root)
+    assert np.array_equal(dist, want)
+    lev, linfo, trace, cnt = dg.bfs_levels(root)
+    wlev, nl, wtrace, wcnt = oracle.bfs_levels(g_rmat["begin"], g_rmat["node_idx"], g_rmat["r_begin"], g_rmat["r_node_idx"], root)
+    assert np.array_equal(lev, wlev)
+    assert list(trace) == list(wtrace) and list(cnt) == list(wcnt)
+    # hop_dist and the BFS template agree: INT_MAX <-> -2
+    assert np.array_equal(np.where(dist == INT_MAX, -2, dist).astype(np.int16), lev)
+    assert info.reached == int((want != INT_MAX).sum())
+    assert info.edges_traversed == int(deg[want != INT_MAX].sum())
+
+
+def test_bfs_reverse_edges_variant(gm, oracle, g_rmat):
+    """use_reverse_edge=true (template parameter): traversal over in-edges == BFS on the transposed graph"""
+    root = int(np.diff(g_rmat["r_begin"]).argmax())
+    dg = dev_graph(gm, g_rmat)
+    lev, info, _, _ = dg.bfs_levels(root, use_reverse_edge=True)
+    wlev, _, _, _ = oracle.bfs_levels(g_rmat["r_begin"], g_rmat["r_node_idx"], g_rmat["begin"], g_rmat["node_idx"], root)
+    assert np.array_equal(lev, wlev)
+
+
+def test_bfs_level_order(gm, oracle, g_rmat):
+    root = int(np.diff(g_rmat["begin"]).argmax())
+    dg = dev_graph(gm, g_rmat)
+    lev, info, _, cnt = dg.bfs_levels(root)
+    order, lb = dg.bfs_level_order(info.levels)
+    assert list(np.diff(lb)) == list(cnt)
+    for l in range(info.levels):
+        assert np.array_equal(np.sort(order[lb[l]:lb[l + 1]]), np.nonzero(lev == l)[0])
+
+
+def test_bfs_no_reverse_top_down_only(gm, oracle, g_c1):
+    dg = gm.graph_from_csr(g_c1["begin"], g_c1["node_idx"], make_reverse=False)
+    dist, info = dg.hop_dist(0)
+    want, _ = oracle.hop_dist(g_c1["begin"], g_c1["node_idx"], 0)
+    assert np.array_equal(dist, want)
+    assert info.bottom_up_levels == 0
+
+
+def test_micro_graphs(gm, oracle):
+    """hand-checkable cases: path, star, 2-cycle + dangling vertex, isolated vertex, self loop, multi-edge"""
+    cases = {
+        "path": (5, [(0, 1), (1, 2), (2, 3), (3, 4)]),
+        "star_out": (6, [(0, i) for i in range(1, 6)]),
+        "star_in": (6, [(i, 0) for i in range(1, 6)]),
+        "cycle2_dangling": (4, [(0, 1), (1, 0), (1, 2)]),
+        "isolated": (3, [(0, 1)]),
+        "selfloop_multi": (3, [(0, 0), (0, 1), (0, 1), (1, 2), (2, 2)]),
+        "no_edges": (4, []),
+        "single": (1, []),
+    }
+    for name, (n, edges) in cases.items():
+        g = graphs.from_edges(oracle, n, edges)
+        dg = gm.graph_from_csr(g["begin"], g["node_idx"], semi_sort=True, make_reverse=True)
+        assert np.array_equal(dg.array("r_begin"), g["r_begin"]), name
+        assert np.array_equal(dg.array("r_node_idx"), g["r_node_idx"]), name
+        rank, info = dg.pagerank(e=1e-30, d=0.85, max_iter=10)
+        want, it, _ = oracle.pagerank(g["begin"], g["r_begin"], g["r_node_idx"], 1e-30, 0.85, 10)
+        assert info.iterations == it, name
+        assert np.array_equal(rank, want), name
+        for root in range(n):
+            dist, _ = dg.hop_dist(root)
+            wd, _ = oracle.hop_dist(g["begin"], g["node_idx"], root)
+            assert np.array_equal(dist, wd), (name, root)
+            lev, _, _, _ = dg.bfs_levels(root)
+            wl, _, _, _ = oracle.bfs_levels(g["begin"], g["node_idx"], g["r_begin"], g["r_node_idx"], root)
+            assert np.array_equal(lev, wl), (name, root)
+
+
+def test_bad_arguments(gm, g_c1):
+    from gmb200_loader import load_package
+    Err = load_package().GmcError
+    dg = dev_graph(gm, g_c1)
+    with pytest.raises(Err):
+        dg.hop_dist(-1)
+    with pytest.raises(Err):
+        dg.hop_dist(g_c1["N"])
+
+
+def test_device_generators(gm, oracle):
+    """device R-MAT / uniform generators: valid semi-sorted CSR, no self loops (R-MAT), reverse CSR equal
+    to the oracle's build, and a degree skew comparable to the reference generator's."""
+    n, m = 1 << 16, 1 << 20
+    dg = gm.generate_rmat(n, m, seed=1997)
+    b, i = dg.array("begin"), dg.array("node_idx")
+    assert b[0] == 0 and b[-1] == m and np.all(np.diff(b) >= 0)
+    assert i.min() >= 0 and i.max() < n
+    src = np.repeat(np.arange(n, dtype=np.int32), np.diff(b))
+    assert not np.any(src == i)                                  # self edges are redrawn
+    rows_sorted = np.all((np.diff(i) >= 0) | (np.diff(src) > 0))
+    assert rows_sorted
+    rb, ri = oracle.make_reverse(b, i)
+    assert np.array_equal(dg.array("r_begin"), rb) and np.array_equal(dg.array("r_node_idx"), ri)
+    rb_ref, _ = oracle.rmat(n, m, 1997, 0.57, 0.19, 0.19, True)
+    top_dev = np.sort(np.diff(b))[::-1][:n // 100].sum() / m    # edge share of the top 1% sources
+    top_ref = np.sort(np.diff(rb_ref))[::-1][:n // 100].sum() / m
+    assert abs(top_dev - top_ref) < 0.05, (top_dev, top_ref)
+    du = gm.generate_uniform(n, m, seed=5)
+    bu = du.array("begin")
+    assert bu[-1] == m and np.diff(bu).max() < 64
