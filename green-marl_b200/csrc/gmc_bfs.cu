@@ -82,7 +82,7 @@ template <typename L>
 __global__ void __launch_bounds__(BFS_THREADS)
 bfs_topdown(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_idx, const int32_t* __restrict__ cur_queue,
             int32_t cur_count, L next_level, L* __restrict__ level, uint32_t* __restrict__ visited,
-            int32_t* __restrict__ next_queue, int32_t* __restrict__ next_count) {
+            int32_t* __restrict__ next_queue, int32_t* __restrict__ next_count, const uint8_t* __restrict__ edge_mask) {
     __shared__ int32_t s_start[BFS_THREADS];
     __shared__ int32_t s_off[BFS_THREADS + 1];
     __shared__ int32_t s_warp[BFS_THREADS / 32 + 1];
@@ -125,9 +125,11 @@ bfs_topdown(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_
                 int mid = (lo + hi) >> 1;
                 if (s_off[mid] <= j) lo = mid; else hi = mid;
             }
-            u = ld_stream(node_idx + (size_t)s_start[lo] + (j - s_off[lo]));
+            const size_t eidx = (size_t)s_start[lo] + (j - s_off[lo]);
+            u = ld_stream(node_idx + eidx);
             const uint32_t bit = 1u << (u & 31);
-            if (!(visited[u >> 5] & bit)) {                         // test ...
+            // navigator (check_navigator, gm_bfs_template.h:488-492,596-598): filtered edges are not followed
+            if (!(visited[u >> 5] & bit) && (!edge_mask || edge_mask[eidx])) {                     // test ...
                 uint32_t old = atomicOr(&visited[u >> 5], bit);     // ... and test-and-set
                 won = !(old & bit);
                 if (won) level[u] = next_level;
@@ -206,7 +208,8 @@ int ensure_ws(gmc_graph* g) {
 // The traversal.  fwd_* = arrays followed top-down, rev_* = arrays followed bottom-up (NULL: no bottom-up).
 template <typename L>
 int run_bfs(gmc_graph* g, const int32_t* fwd_begin, const int32_t* fwd_idx, const int32_t* rev_begin, const int32_t* rev_idx,
-            int32_t root, L invalid, L* level_out_dev, gmc_bfs_info* info, cudaStream_t st) {
+            int32_t root, L invalid, L* level_out_dev, gmc_bfs_info* info, cudaStream_t st,
+            const uint8_t* edge_mask = nullptr) {
     GMC_REQUIRE(root >= 0 && root < g->N, GMC_ERR_ARG, "bfs: root %d out of range [0,%d)", root, g->N);
     GMC_TRY(ensure_ws(g));
     gmc_bfs_ws* w = g->bfs;
@@ -248,7 +251,7 @@ int run_bfs(gmc_graph* g, const int32_t* fwd_begin, const int32_t* fwd_idx, cons
                 bfs_bottomup<L, false><<<grid, BFS_THREADS, 0, st>>>(rev_begin, rev_idx, n, w->frontier_bm, w->visited, w->next_bm, nl, level, w->queue + next_begin, w->counters);
             launches++; bottom_up++;
         } else {
-            bfs_topdown<L><<<div_up(curr_count, BFS_THREADS), BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue + curr_begin, curr_count, nl, level, w->visited, w->queue + next_begin, w->counters);
+            bfs_topdown<L><<<div_up(curr_count, BFS_THREADS), BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue + curr_begin, curr_count, nl, level, w->visited, w->queue + next_begin, w->counters, edge_mask);
             launches++;
         }
         GMC_CUDA(cudaGetLastError());
@@ -328,8 +331,8 @@ int gmc_hop_dist(gmc_graph* g, int32_t root, int32_t* dist_host, gmc_bfs_info* i
     return gmc_d2h(dist_host, g->bfs->level, sizeof(int32_t) * (size_t)g->N, nullptr);
 }
 
-int gmc_bfs_levels(gmc_graph* g, int32_t root, int use_reverse_edge, int16_t* level_host, int32_t* state_trace,
-                   int32_t* level_count, int32_t trace_cap, gmc_bfs_info* info) {
+int gmc_bfs_levels_masked(gmc_graph* g, int32_t root, int use_reverse_edge, const uint8_t* edge_mask_host, int16_t* level_host,
+                          int32_t* state_trace, int32_t* level_count, int32_t trace_cap, gmc_bfs_info* info) {
     GMC_REQUIRE(g && level_host, GMC_ERR_ARG, "gmc_bfs_levels: NULL");
     GMC_REQUIRE(g->N > 0, GMC_ERR_ARG, "gmc_bfs_levels: empty graph");
     GMC_REQUIRE(!use_reverse_edge || g->has_reverse, GMC_ERR_STATE, "gmc_bfs_levels: use_reverse_edge needs the reverse CSR");
@@ -337,13 +340,29 @@ int gmc_bfs_levels(gmc_graph* g, int32_t root, int use_reverse_edge, int16_t* le
     const int32_t *fb = g->begin, *fi = g->node_idx;
     const int32_t *rb = g->has_reverse ? g->r_begin : nullptr, *ri = g->has_reverse ? g->r_node_idx : nullptr;
     if (use_reverse_edge) { fb = g->r_begin; fi = g->r_node_idx; rb = g->begin; ri = g->node_idx; }
-    GMC_TRY(run_bfs<int16_t>(g, fb, fi, rb, ri, root, (int16_t)-2, (int16_t*)g->bfs->level, info, nullptr));
+    uint8_t* mask_dev = nullptr;
+    if (edge_mask_host) {
+        // a filtered traversal stays top-down: the bottom-up parent scan (check_parent_rrd, :689-708)
+        // has no navigator hook in the reference either
+        rb = ri = nullptr;
+        GMC_TRY(gmc_malloc((void**)&mask_dev, (size_t)(g->M ? g->M : 1)));
+        int rc = gmc_h2d(mask_dev, edge_mask_host, (size_t)g->M, nullptr);
+        if (rc != GMC_OK) { cudaFree(mask_dev); return rc; }
+    }
+    int rc = run_bfs<int16_t>(g, fb, fi, rb, ri, root, (int16_t)-2, (int16_t*)g->bfs->level, info, nullptr, mask_dev);
+    if (mask_dev) cudaFree(mask_dev);
+    GMC_TRY(rc);
     gmc_bfs_ws* w = g->bfs;
     for (int32_t i = 0; i < trace_cap && i < (int32_t)w->state_trace.size(); i++) {
         if (state_trace) state_trace[i] = w->state_trace[i];
         if (level_count) level_count[i] = w->level_count[i];
     }
     return gmc_d2h(level_host, w->level, sizeof(int16_t) * (size_t)g->N, nullptr);
+}
+
+int gmc_bfs_levels(gmc_graph* g, int32_t root, int use_reverse_edge, int16_t* level_host, int32_t* state_trace,
+                   int32_t* level_count, int32_t trace_cap, gmc_bfs_info* info) {
+    return gmc_bfs_levels_masked(g, root, use_reverse_edge, nullptr, level_host, state_trace, level_count, trace_cap, info);
 }
 
 // Vertices of every level in level order (the reference's global_vector / level_queue_begin,

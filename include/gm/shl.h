@@ -1,0 +1,41 @@
+// Shoal entry points used by the Green-Marl drivers and generated code, re-targeted from NUMA nodes to
+// B200 HBM.  libshoal is not part of the reference tree; the surface below is what its call sites need:
+//   shl__init(nthreads, partitioned)           apps/output_cpp/src/common_main.h:95-99
+//   shl__start / shl__end / shl__thread_init    src/backend_cpp/shl_extensions.cc:30-40, gm_cpp_gen.cc:1457
+//   shl__start_timer / step_timer / end_timer   src/backend_cpp/gm_cpp_gen.cc:685,760,769,775,1468-1486
+//   shl__get_rep_id                             src/backend_cpp/gm_cpp_gen.cc:715-716
+//   class Timer                                 src/backend_cpp/gm_cpp_gen.cc:1488-1503
+#ifndef SHL_H_
+#define SHL_H_
+#include <stddef.h>
+#include <sys/time.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+// Selects the device (SHL_DEVICE / GM_CUDA_DEVICE env, default 0), initialises libgm_cuda and returns
+// the number of host threads to use for driver-side work.  Exits if no CUDA device is usable: there is
+// no CPU fallback.
+int shl__init(int nthreads, int partitioned);
+void shl__start(void);            // marks the start of the compute phase (stdout timing contract)
+void shl__end(void);
+void shl__thread_init(void);
+void shl__start_timer(int n_steps);
+double shl__step_timer(const char* label);
+double shl__end_timer(const char* label);
+int shl__get_rep_id(void);
+void* shl__alloc_memory(size_t bytes);
+#ifdef __cplusplus
+}
+class Timer {
+  public:
+    void start() { gettimeofday(&t0, NULL); }
+    double stop() {
+        struct timeval t1;
+        gettimeofday(&t1, NULL);
+        return (t1.tv_sec - t0.tv_sec) * 1000.0 + (t1.tv_usec - t0.tv_usec) * 0.001;
+    }
+  private:
+    struct timeval t0;
+};
+#endif
+#endif

@@ -143,6 +143,12 @@ int gmc_hop_dist_dev(gmc_graph* g, int32_t root, int32_t* dist_dev, gmc_bfs_info
  * state_trace / level_count: optional host arrays of capacity trace_cap. */
 int gmc_bfs_levels(gmc_graph* g, int32_t root, int use_reverse_edge, int16_t* level_host,
                    int32_t* state_trace, int32_t* level_count, int32_t trace_cap, gmc_bfs_info* info);
+/* same traversal restricted to the edges with edge_mask_host[e] != 0 (e indexes the arrays being followed:
+ * node_idx, or r_node_idx with use_reverse_edge): the has_navigator form of the reference template
+ * (check_navigator, gm_bfs_template.h:488-492,596-598).  Stays top-down.  NULL mask = no filter. */
+int gmc_bfs_levels_masked(gmc_graph* g, int32_t root, int use_reverse_edge, const uint8_t* edge_mask_host,
+                          int16_t* level_host, int32_t* state_trace, int32_t* level_count, int32_t trace_cap,
+                          gmc_bfs_info* info);
 /* vertices of every level, concatenated in level order (the reference's global_vector /
  * level_queue_begin, gm_bfs_template.h:423-447), for do_bfs_reverse and host callback replay.
  * order_host[N]; level_begin_host[levels+1]. Valid after gmc_bfs_levels on the same graph. */
