@@ -1,0 +1,381 @@
+#!/usr/bin/env python
+"""bench.py -- the PageRank / BFS hot path of Green-Marl+Shoal on B200 (BASELINE.json metric).
+
+A "step" is one pass of the hot path over one synthetic graph: one call of the generated procedure
+pagerank(G, e=1e-30, d=0.85, max=ITERS) -- ITERS pull sweeps over the reverse CSR with the fused rank
+update and convergence diff (reference apps/src/pagerank.gm:1-20) -- on the LJ-shaped R-MAT graph of
+BASELINE.json configs[1] (4.85 M vertices, 69 M edges, int32 ids, fp64 ranks).
+
+  value     GTEPS = edges x iterations x steps / device time; CSR already resident in HBM (CUDA events on
+            the launching stream, max over ranks).
+  e2e       same metric through the reference-facing C-ABI calls with HOST buffers: per step the CSR +
+            reverse CSR are copied H2D from pinned memory (what the generated procedure's Shoal copy-in
+            does on every call, reference gm_cpp_gen.cc:685-775), the sweeps run, and rank[] is copied
+            back to host memory (copy_back, :1480).
+  roofline  the pull-sweep kernel: algorithmic bytes per sweep (4*M + 40*N) / its average
+            launch duration (each sweep bracketed by CUDA events), against MEASURED_PEAKS.json.
+  cpu_baseline  the reference's own OpenMP code (oracle/_ref: reference gm_graph + the generated loop nest
+            restated in oracle/ref_glue) on this box's host cores, bounded sample, rank 0 at N=1.
+  bfs       extra: hop_dist / gm_bfs_template level-synchronous BFS GTEPS on the same graph (configs[2]).
+
+`--impl reference` times only the CPU reference arm (no GPU code of this repo on that path).
+N>1 (torchrun): destination-range shards, one process per GPU, weak scaling (the graph grows with N).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    # name: (N, M) -- BASELINE.json configs
+    "c1": (65536, 1048576),
+    "lj": (4850000, 69000000),
+    "tw": (41600000, 1470000000),
+}
+RMAT = dict(seed=1997, a=0.57, b=0.19, c=0.19, permute=True)
+
+
+def alg_bytes_pagerank(n, m):
+    """compulsory HBM traffic of one pull sweep, int32 ids / fp64 ranks"""
+    return 4 * m + 40 * n
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0=None, t1=None):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        for ts, line in self.rows:
+            if t0 is not None and not (t0 - 0.05 <= ts <= t1 + 0.15):
+                continue
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); smax.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:    # region shorter than one sample: fall back to every sample taken
+            for ts, line in self.rows:
+                f = [x.strip() for x in line.split(",")]
+                try:
+                    sm.append(float(f[0])); smax.append(float(f[1]))
+                except Exception:
+                    pass
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------------
+# reference arm (CPU): the reference's own gm_graph + generated loop nest, on the host cores
+# --------------------------------------------------------------------------------------------------
+def cpu_reference(begin, node_idx, iters_sample, steps=1, warmup=0, threads=None):
+    """returns dict(value GTEPS, ms_per_step, kind, cores, rank, threads) timing pagerank() of oracle/_ref (or the
+    plain-C oracle port when the reference could not be built) for `iters_sample` iterations per step."""
+    from oracle_lib import Oracle, Ref, have_ref
+    threads = threads or (os.cpu_count() or 1)
+    n, m = len(begin) - 1, len(node_idx)
+    if have_ref():
+        ref = Ref()
+        ref.set_threads(threads)
+        g = ref.from_csr(begin, node_idx)          # reference do_semi_sort + make_reverse_edges
+        times = []
+        rank = None
+        for k in range(warmup + steps):
+            rank, ms = ref.pagerank(g, 1e-30, 0.85, iters_sample)
+            if k >= warmup:
+                times.append(ms)
+        ref.free(g)
+        kind = "reference"
+    else:
+        orc = Oracle()
+        orc.set_threads(threads)
+        idx = np.ascontiguousarray(node_idx).copy()
+        orc.semi_sort(begin, idx)
+        rb, ri = orc.make_reverse(begin, idx)
+        times = []
+        rank = None
+        for k in range(warmup + steps):
+            t = time.perf_counter()
+            rank, _, _ = orc.pagerank(begin, rb, ri, 1e-30, 0.85, iters_sample)
+            if k >= warmup:
+                times.append((time.perf_counter() - t) * 1e3)
+        kind = "port"
+    ms = sum(times) / len(times)
+    return dict(value=m * iters_sample / ms / 1e6, ms_per_step=ms, kind=kind, cores=threads, rank=rank)
+
+
+def run_reference_arm(args, n, m):
+    """bench.py --impl reference: nothing of libgm_cuda on this path.  The graph comes from the
+    reference's own R-MAT generator (create_RMAT_graph, graph_gen.cc:159-287); each step is a bounded
+    sample (ITERS_SAMPLE sweeps) of the pagerank() call."""
+    rank_id = int(os.environ.get("RANK", "0"))
+    if rank_id != 0:
+        return
+    from oracle_lib import Oracle, Ref, have_ref
+    threads = os.cpu_count() or 1
+    iters = args.cpu_iters
+    t0 = time.perf_counter()
+    if have_ref():
+        ref = Ref(); ref.set_threads(threads)
+        g = ref.rmat(n, m, RMAT["seed"], RMAT["a"], RMAT["b"], RMAT["c"], RMAT["permute"])
+        gen_s = time.perf_counter() - t0
+        times = []
+        for k in range(args.warmup + args.steps):
+            _, ms = ref.pagerank(g, 1e-30, 0.85, iters)
+            if k >= args.warmup:
+                times.append(ms)
+        ref.free(g)
+        kind = "reference"
+    else:
+        orc = Oracle(); orc.set_threads(threads)
+        b, i = orc.rmat(n, m, RMAT["seed"], RMAT["a"], RMAT["b"], RMAT["c"], RMAT["permute"])
+        i = np.ascontiguousarray(i).copy()
+        orc.semi_sort(b, i)
+        rb, ri = orc.make_reverse(b, i)
+        gen_s = time.perf_counter() - t0
+        times = []
+        for k in range(args.warmup + args.steps):
+            t = time.perf_counter()
+            orc.pagerank(b, rb, ri, 1e-30, 0.85, iters)
+            if k >= args.warmup:
+                times.append((time.perf_counter() - t) * 1e3)
+        kind = "port"
+    ms = sum(times) / len(times)
+    v = m * iters / ms / 1e6
+    sample = f"{iters} of {args.iters} sweeps per step, same graph shape, all {threads} host threads (OpenMP dynamic,128)"
+    line = {
+        "impl": "reference", "metric": "pagerank_gteps", "value": v, "unit": "GTEPS", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(args, n, m), "nodes": n, "edges": m, "iterations_per_step": iters,
+                   "graph": "reference create_RMAT_graph seed 1997 a=.57 b=.19 c=.19 permuted", "generate_s": round(gen_s, 1)},
+        "cpu_baseline": {"value": v, "unit": "GTEPS", "cores": threads, "kind": kind, "sample": sample},
+        "e2e": {"value": v, "unit": "GTEPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_name(args, n, m):
+    return f"pagerank {args.iters} sweeps, R-MAT {args.workload}-shaped N={n} M={m}, int32 ids, fp64 ranks, d=0.85, e=1e-30"
+
+
+# --------------------------------------------------------------------------------------------------
+# our arm
+# --------------------------------------------------------------------------------------------------
+def run_single(args, n, m):
+    import torch
+    from gmb200_loader import load_package
+    pkg = load_package()
+    lib = pkg.GmCuda()
+    dev = int(os.environ.get("LOCAL_RANK", "0"))
+    lib.init(dev)
+    torch.cuda.set_device(dev)
+    iters = args.iters
+    t0 = time.perf_counter()
+    g = lib.generate_rmat(n, m, RMAT["seed"], RMAT["a"], RMAT["b"], RMAT["c"], RMAT["permute"])
+    lib.sync()
+    gen_s = time.perf_counter() - t0
+
+    stream = torch.cuda.Stream()
+    sp = stream.cuda_stream
+    rank_dev = torch.empty(n, dtype=torch.float64, device="cuda")
+    launches = 0
+    for _ in range(args.warmup):
+        g.pagerank_dev(rank_dev.data_ptr(), 1e-30, 0.85, iters, stream=sp)
+    torch.cuda.synchronize()
+    clocks = ClockSampler(dev)
+    clocks.start()
+    time.sleep(0.25)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    w0 = time.time()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        info = g.pagerank_dev(rank_dev.data_ptr(), 1e-30, 0.85, iters, stream=sp)
+        launches += info.launches
+        assert info.iterations == iters
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    w1 = time.time()
+    ms_total = ev0.elapsed_time(ev1)
+    # keep the clocks sampler running over the per-sweep roofline pass as well
+    sweep_ms, lps = g.pagerank_time_sweeps(0.85, warmup=3, n=max(20, iters), stream=sp)
+    w2 = time.time()
+    clk = clocks.stop(w0, w2)
+    ms_step = ms_total / args.steps
+    value = m * iters / ms_step / 1e6
+    rank_gpu = rank_dev.cpu().numpy()
+
+    # ---- roofline of the dominant kernel (the pull sweep) --------------------------------------
+    peak, peak_kind = measured_peak_gbs()
+    a_bytes = alg_bytes_pagerank(n, m)
+    avg_sweep_ms = float(np.mean(sweep_ms))
+    achieved = a_bytes / avg_sweep_ms / 1e6
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        try:
+            tj = json.load(open(tp))
+            if tj.get("nodes") == n and tj.get("edges") == m:
+                traffic = tj.get("dram_bytes_per_launch")
+        except Exception:
+            pass
+    roofline = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+                "traffic": traffic, "peak_kind": peak_kind, "kernel": "pr_sweep", "alg_bytes_per_launch": a_bytes,
+                "avg_launch_ms": round(avg_sweep_ms, 5), "kernels_per_sweep": lps,
+                "gteps_kernel_only": round(m / avg_sweep_ms / 1e6, 1)}
+
+    # ---- e2e: host buffers through the C ABI, H2D + D2H inside the timed region ---------------------
+    host = {k: g.array(k) for k in ("begin", "node_idx", "r_begin", "r_node_idx")}
+    pinned = {}
+    for k, a in host.items():
+        t = torch.empty(a.shape, dtype=torch.int32).pin_memory()
+        t.numpy()[:] = a
+        pinned[k] = t.numpy()
+    rank_host_t = torch.empty(n, dtype=torch.float64).pin_memory()
+    rank_host = rank_host_t.numpy()
+    h2d = sum(a.nbytes for a in pinned.values())
+    d2h = rank_host.nbytes
+
+    def e2e_step():
+        dg = lib.graph_from_csr(pinned["begin"], pinned["node_idx"], semi_sort=False, make_reverse=False)
+        dg.upload_reverse(pinned["r_begin"], pinned["r_node_idx"])
+        _, inf = dg.pagerank_into(rank_host, 1e-30, 0.85, iters)
+        dg.close()
+        return inf
+
+    for _ in range(min(args.warmup, 2)):
+        e2e_step()
+    lib.sync()
+    t0 = time.perf_counter()
+    e2e_steps = max(1, min(args.steps, 5))
+    for _ in range(e2e_steps):
+        e2e_step()
+    lib.sync()
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+    e2e = {"value": round(m * iters / e2e_ms / 1e6, 3), "unit": "GTEPS", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+           "ms_per_step": round(e2e_ms, 3), "steps": e2e_steps}
+    assert np.array_equal(rank_host, rank_gpu), "e2e result differs from the resident-graph result"
+
+    # ---- BFS (configs[2]) on the same graph: hop_dist over several roots -------------------------
+    deg = np.diff(host["begin"])
+    rs = np.random.RandomState(1997)
+    roots = [int(np.nonzero(deg)[0][0])] + [int(r) for r in rs.choice(np.nonzero(deg)[0], size=7, replace=False)]
+    dist_dev = torch.empty(n, dtype=torch.int32, device="cuda")
+    bfs_ms, bfs_edges, bfs_launches = [], [], 0
+    for r in roots:
+        g.hop_dist_dev(dist_dev.data_ptr(), r, stream=sp)           # warm
+        bi = g.hop_dist_dev(dist_dev.data_ptr(), r, stream=sp)
+        bfs_ms.append(bi.kernel_ms); bfs_edges.append(bi.edges_traversed); bfs_launches += bi.launches
+    bfs = {"metric": "bfs_gteps", "value": round(sum(bfs_edges) / sum(bfs_ms) / 1e6, 3), "unit": "GTEPS",
+           "roots": len(roots), "ms_per_traversal": round(float(np.mean(bfs_ms)), 4),
+           "edges_per_traversal": int(np.mean(bfs_edges)), "what": "hop_dist (direction-optimizing), device time"}
+
+    # ---- CPU baseline: the reference's own code on the host cores, bounded sample -------------------
+    cpu = None
+    parity = None
+    if not args.no_cpu_baseline:
+        c = cpu_reference(host["begin"], host["node_idx"], args.cpu_iters, steps=1, warmup=0)
+        cpu = {"value": round(c["value"], 4), "unit": "GTEPS", "cores": c["cores"], "kind": c["kind"],
+               "sample": f"{args.cpu_iters} of {iters} sweeps of the same graph (identical CSR), one pagerank() call, "
+                         f"all host threads; {c['ms_per_step']:.1f} ms"}
+        # the CPU result doubles as a full-size parity check (same CSR, same iteration count)
+        rk, _ = g.pagerank(1e-30, 0.85, args.cpu_iters)
+        parity = {"max_abs_err_vs_cpu_reference": float(np.abs(rk - c["rank"]).max()), "iterations": args.cpu_iters,
+                  "tolerance": 1e-9}
+
+    line = {
+        "metric": "pagerank_gteps", "value": round(value, 3), "unit": "GTEPS", "n_gpus": 1, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(args, n, m), "nodes": n, "edges": m, "iterations_per_step": iters,
+                   "graph": "device R-MAT generator seed 1997 a=.57 b=.19 c=.19 permuted (counter-based RNG)",
+                   "generate_s": round(gen_s, 2),
+                   "l2": "inputs larger than L2 (index stream %d MB per sweep > 126 MB L2); no explicit flush" % (4 * m // 2**20),
+                   "parallelism": "1 GPU"},
+        "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
+        "bfs": bfs, "parity": parity,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="lj", choices=sorted(WORKLOADS))
+    ap.add_argument("--iters", type=int, default=20, help="pull sweeps per pagerank() call (BASELINE configs: 20)")
+    ap.add_argument("--cpu-iters", type=int, default=5, help="sweeps per CPU-reference sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3        # timing rule: at least 3 warm-up steps
+    n, m = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference_arm(args, n, m)
+        return
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1 or args.gpus > 1:
+        from bench_multi import run_multi
+        run_multi(args, n, m)
+    else:
+        run_single(args, n, m)
+
+
+if __name__ == "__main__":
+    main()

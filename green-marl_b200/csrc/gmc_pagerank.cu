@@ -22,6 +22,7 @@
 // contrib, out-degree, first touch of contrib); the per-edge gathers are served by L2/L1 when
 // contrib[] (8N bytes) fits the 126 MB L2.
 #include "gmc_common.cuh"
+#include <vector>
 
 using namespace gmc;
 
@@ -407,6 +408,34 @@ int gmc_pagerank_dev(gmc_graph* g, double e, double d, int32_t max_iter, double*
         cudaEventElapsedTime(&info->kernel_ms, ev0, ev1);
     }
     cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    return GMC_OK;
+}
+
+// measurement aid for the roofline figure: every sweep bracketed by its own pair of CUDA events
+int gmc_pagerank_time_sweeps(gmc_graph* g, double d, int32_t warmup, int32_t n, float* ms_out, int32_t* launches_per_sweep, void* stream) {
+    GMC_REQUIRE(g && ms_out && n > 0 && warmup >= 0, GMC_ERR_ARG, "gmc_pagerank_time_sweeps: bad args");
+    GMC_REQUIRE(g->N > 0, GMC_ERR_ARG, "gmc_pagerank_time_sweeps: empty graph");
+    cudaStream_t st = as_stream(stream);
+    GMC_TRY(graph_plan(g, st));
+    gmc_pr_shard* s = g->pr;
+    const size_t nn = (size_t)g->N;
+    double* contrib[2] = {g->pr_buf, g->pr_buf + nn};
+    double* rank[2] = {g->pr_buf + 2 * nn, g->pr_buf + 3 * nn};
+    pr_init<<<div_up(g->N, 256), 256, 0, st>>>(g->N, 0, g->N, s->outdeg, contrib[0], rank[0]);
+    std::vector<cudaEvent_t> ev(2 * (size_t)n);
+    for (auto& e : ev) GMC_CUDA(cudaEventCreate(&e));
+    int launches = 0;
+    for (int32_t k = 0; k < warmup + n; k++) {
+        int p = k & 1;
+        launches = 0;
+        if (k >= warmup) GMC_CUDA(cudaEventRecord(ev[2 * (k - warmup)], st));
+        GMC_TRY(launch_sweep(s, d, contrib[p], contrib[p ^ 1], rank[p], rank[p ^ 1], p, nullptr, st, &launches));
+        if (k >= warmup) GMC_CUDA(cudaEventRecord(ev[2 * (k - warmup) + 1], st));
+    }
+    GMC_CUDA(cudaStreamSynchronize(st));
+    for (int32_t k = 0; k < n; k++) GMC_CUDA(cudaEventElapsedTime(&ms_out[k], ev[2 * k], ev[2 * k + 1]));
+    for (auto& e : ev) cudaEventDestroy(e);
+    if (launches_per_sweep) *launches_per_sweep = launches;
     return GMC_OK;
 }
 

@@ -60,6 +60,7 @@ SIGNATURES = {
     "gmc_file_write": (C.c_int, [C.c_char_p, _i32, _i32, _vp, _vp]),
     "gmc_pagerank": (C.c_int, [_vp, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo)]),
     "gmc_pagerank_dev": (C.c_int, [_vp, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo), _vp]),
+    "gmc_pagerank_time_sweeps": (C.c_int, [_vp, C.c_double, _i32, _i32, _vp, C.POINTER(_i32), _vp]),
     "gmc_pr_shard_create": (C.c_int, [C.POINTER(_vp), _i32, _i32, _i32, _vp, _vp, _vp]),
     "gmc_pr_shard_destroy": (C.c_int, [_vp]),
     "gmc_pr_shard_set_peers": (C.c_int, [_vp, C.c_int, _vp, _vp]),
@@ -69,6 +70,7 @@ SIGNATURES = {
     "gmc_hop_dist": (C.c_int, [_vp, _i32, _vp, C.POINTER(BfsInfo)]),
     "gmc_hop_dist_dev": (C.c_int, [_vp, _i32, _vp, C.POINTER(BfsInfo), _vp]),
     "gmc_bfs_levels": (C.c_int, [_vp, _i32, C.c_int, _vp, _vp, _vp, _i32, C.POINTER(BfsInfo)]),
+    "gmc_bfs_levels_masked": (C.c_int, [_vp, _i32, C.c_int, _vp, _vp, _vp, _vp, _i32, C.POINTER(BfsInfo)]),
     "gmc_bfs_level_order": (C.c_int, [_vp, _vp, _vp, _i32]),
 }
 
@@ -226,11 +228,24 @@ class Graph:
         self.lib.check(self.lib.L.gmc_pagerank(self.h, e, d, max_iter, _ptr(rank), C.byref(info)))
         return rank[:self.num_nodes], info
 
+    def pagerank_into(self, rank_host, e=1e-30, d=0.85, max_iter=20):
+        """result into a caller-owned (ideally pinned) host array of N doubles"""
+        assert rank_host.dtype == np.float64 and len(rank_host) >= self.num_nodes
+        info = PagerankInfo()
+        self.lib.check(self.lib.L.gmc_pagerank(self.h, e, d, max_iter, _ptr(rank_host), C.byref(info)))
+        return rank_host, info
+
     def pagerank_dev(self, rank_dev_ptr, e=1e-30, d=0.85, max_iter=20, stream=None):
         info = PagerankInfo()
         self.lib.check(self.lib.L.gmc_pagerank_dev(self.h, e, d, max_iter, _vp(rank_dev_ptr), C.byref(info),
                                                    _vp(stream) if stream else None))
         return info
+
+    def pagerank_time_sweeps(self, d=0.85, warmup=3, n=20, stream=None):
+        ms = np.zeros(n, np.float32); lps = _i32()
+        self.lib.check(self.lib.L.gmc_pagerank_time_sweeps(self.h, d, warmup, n, _ptr(ms), C.byref(lps),
+                                                           _vp(stream) if stream else None))
+        return ms, lps.value
 
     def hop_dist(self, root=0):
         dist = np.zeros(max(self.num_nodes, 1), np.int32)

@@ -103,6 +103,11 @@ int gmc_pagerank(gmc_graph* g, double e, double d, int32_t max_iter, double* ran
 int gmc_pagerank_dev(gmc_graph* g, double e, double d, int32_t max_iter, double* rank_dev,
                      gmc_pagerank_info* info, void* stream);
 
+/* measurement aid (bench.py's roofline figure): rank = 1/N, `warmup` untimed sweeps, then `n` sweeps each
+ * bracketed by its own pair of CUDA events on `stream`; ms_out[i] = device time of timed sweep i. */
+int gmc_pagerank_time_sweeps(gmc_graph* g, double d, int32_t warmup, int32_t n, float* ms_out,
+                             int32_t* launches_per_sweep, void* stream);
+
 /* --- PageRank over a destination-range shard (multi-GPU).  A shard owns rows [lo,hi) of
  * the reverse CSR (r_begin slice rebased to 0, global source ids) and the out-degrees of its own
  * vertices.  One sweep reads the FULL contribution vector contrib_in[N] (= rank[w]/outdeg[w]) and

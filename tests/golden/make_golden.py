@@ -1,0 +1,66 @@
+"""Regenerates tests/golden/*.npz from the REFERENCE ITSELF (oracle/_ref/libgmref.so = the reference's own
+gm_graph runtime, generators and gm_bfs_template compiled from /root/reference by oracle/Makefile, plus the
+restated generated procedures in oracle/ref_glue).  Run in the build container (needs /root/reference):
+
+    make -C oracle && python tests/golden/make_golden.py
+
+The fixtures pin the plain-C oracle (oracle/gm_oracle.c) and, through it, the CUDA path.
+"""
+import hashlib
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+from oracle_lib import Ref  # noqa: E402
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def main():
+    ref = Ref()
+    ref.set_threads(4)
+    # (1) BASELINE config 1: graph_gen 65536 1048576 <f> 0  -> digests + leading values (full arrays are too big to commit)
+    g = ref.uniform(65536, 1048576, 1997)
+    a = ref.arrays(g)
+    rank, _ = ref.pagerank(g, 1e-30, 0.85, 20)
+    dist, _ = ref.hop_dist(g, 0)
+    lev, nl, _ = ref.bfs_levels(g, 0)
+    np.savez_compressed(os.path.join(HERE, "c1_digest.npz"),
+                        N=a["N"], M=a["M"], begin_sha=sha(a["begin"]), node_idx_sha=sha(a["node_idx"]),
+                        r_begin_sha=sha(a["r_begin"]), r_node_idx_sha=sha(a["r_node_idx"]),
+                        rank_sha=sha(rank), rank_head=rank[:64], rank_sum=float(rank.sum()),
+                        dist_sha=sha(dist), dist_head=dist[:64], dist_hist=np.bincount(dist),
+                        lev_sha=sha(lev), n_levels=nl, begin_head=a["begin"][:64], node_idx_head=a["node_idx"][:64])
+    ref.free(g)
+    # (2) small R-MAT (reference create_RMAT_graph), full arrays: CSR, reverse CSR, rank after 20 sweeps, dist / levels from 3 roots
+    g = ref.rmat(4096, 65536, 1997, 0.57, 0.19, 0.19, True)
+    a = ref.arrays(g)
+    rank, _ = ref.pagerank(g, 1e-30, 0.85, 20)
+    rank_conv, _ = ref.pagerank(g, 0.001, 0.85, 100)
+    deg = np.diff(a["begin"])
+    roots = np.array([0, int(np.nonzero(deg)[0][0]), int(deg.argmax())], np.int32)
+    dists = np.stack([ref.hop_dist(g, int(r))[0] for r in roots])
+    levs = np.stack([ref.bfs_levels(g, int(r))[0] for r in roots])
+    np.savez_compressed(os.path.join(HERE, "rmat4096.npz"), begin=a["begin"], node_idx=a["node_idx"],
+                        r_begin=a["r_begin"], r_node_idx=a["r_node_idx"], rank20=rank, rank_conv=rank_conv,
+                        roots=roots, dist=dists, levels=levs)
+    ref.free(g)
+    # (3) uniform 2000 / 30000 (graph_gen type 0 at small size)
+    g = ref.uniform(2000, 30000, 1997)
+    a = ref.arrays(g)
+    rank, _ = ref.pagerank(g, 1e-30, 0.85, 20)
+    dist, _ = ref.hop_dist(g, 0)
+    lev, _, _ = ref.bfs_levels(g, 0)
+    np.savez_compressed(os.path.join(HERE, "uniform2000.npz"), begin=a["begin"], node_idx=a["node_idx"],
+                        r_begin=a["r_begin"], r_node_idx=a["r_node_idx"], rank20=rank, dist=dist, levels=lev)
+    ref.free(g)
+    print("golden fixtures written to", HERE)
+
+
+if __name__ == "__main__":
+    main()
