@@ -63,7 +63,7 @@ int exclusive_scan_i32(const int32_t* in, int32_t* out, size_t n, int32_t* total
 }  // namespace gmc
 
 // The device-resident CSR mirror behind gmc_graph.
-struct gmc_pr_shard;
+struct gmc_pr_plan;
 struct gmc_bfs_ws;
 struct gmc_graph {
     int32_t N = 0, M = 0;
@@ -76,8 +76,7 @@ struct gmc_graph {
     bool semi_sorted = false;
     bool has_reverse = false;
     // lazily built per-algorithm state (invalidated when the CSR changes)
-    gmc_pr_shard* pr = nullptr;     // whole-graph PageRank plan ([0,N) shard over the device arrays)
-    double* pr_buf = nullptr;       // contrib[2][N] + rank[2][N]
+    gmc_pr_plan* pr = nullptr;      // PageRank plan: relabelled entry array, tasks, state buffers (gmc_pagerank.cu)
     gmc_bfs_ws* bfs = nullptr;
 };
 

@@ -1,4 +1,4 @@
-// PageRank pull sweep (K1) with the updater (K2) and init (K3) fused away.
+// PageRank pull sweep (K1) with the updater (K2) and init (K3) fused away -- one launch per iteration.
 //
 // Reference loop being replaced (generated from apps/src/pagerank.gm:8-19, shape in SURVEY.md 3.1):
 //   foreach t: S = sum_{w in InNbrs(t), r_node_idx order} rank[w] / (double)outdeg(w)
@@ -7,357 +7,620 @@
 //
 // Device formulation.  contrib[w] = rank[w]/(double)outdeg(w) is produced once per vertex by the
 // epilogue of the previous sweep (the same IEEE division the reference performs once per EDGE), so a
-// sweep gathers one double per edge.  rank/contrib are ping-ponged, which removes the copy-back loop.
+// sweep gathers one double per edge; rank/contrib are ping-ponged, which removes the copy-back loop.
 //
-// Load balance ("CSR-stream" over a merge-path split): CTA b owns the rows whose coordinate
-// r_begin[t]+t falls in [b*W,(b+1)*W), i.e. about W rows+edges whatever the degree skew.  The CTA
-// streams its contiguous slice of r_node_idx with coalesced read-once loads, gathers contrib[] for every
-// edge into shared memory (8 independent gathers in flight per thread), then one thread per row adds
-// the row's terms from shared memory strictly left to right -- the reference's summation order, so
-// every row of in-degree <= PR_LONG is bit-identical to the CPU result.  Rows longer than PR_LONG
-// (power-law hubs) are cut into PR_CHUNK-edge chunks, one CTA each, and combined in chunk order by a
-// finalize kernel: deterministic, but a different association than left-to-right (<= few ulp).
-//
-// HBM traffic per sweep: 4 B/edge (index stream) + 40 B/vertex (row pointer, old rank, new rank, new
-// contrib, out-degree, first touch of contrib); the per-edge gathers are served by L2/L1 when
-// contrib[] (8N bytes) fits the 126 MB L2.
+// Layout (built once per graph by build_plan, "the plan"): vertices are RELABELLED so that the kernel's
+// two problems -- the random 8-byte gathers and the power-law row lengths -- become layout properties:
+//   id 0            a dummy vertex whose contribution is always 0.0 (padding entries point at it)
+//   ids [1,hot_n)   the hot block: among rows with in-degree > S_MAX, the hot_n-1 vertices with the largest
+//                   OUT-degree (= the most gathered contributions).  Every CTA stages contrib[0,hot_n) in
+//                   shared memory with one TMA bulk copy per sweep; ~half of all gathers of an R-MAT graph
+//                   are then served from shared memory instead of L2 sectors.
+//   ids [.., n_long] the other rows with in-degree > S_MAX, in-degree descending ("long" rows)
+//   ids (n_long, N] rows with in-degree <= S_MAX, in-degree descending ("short" rows)
+// The reverse CSR is rewritten over the new ids into one entry array E:
+//   long rows   row-major, each row padded to a multiple of 4 entries (16-byte aligned, so a lane's int4
+//               never straddles two rows).  Cut into fixed tasks of LT entries whatever the row lengths
+//               (merge-path in the limit): a warp streams its task with 128-bit index loads, 8 gathers in
+//               flight per lane, lane-private accumulation and one butterfly reduction per row end.  A row
+//               cut by a task boundary leaves per-task partials; the last task to arrive (atomic counter)
+//               adds them in task order -- deterministic, no spin-waiting.
+//   short rows  sliced ELL: 32 consecutive rows per slice, column-major, padded to the slice's longest row
+//               (rows are sorted by length, so padding is nil).  One lane per row adds its terms strictly
+//               left to right in the ORIGINAL source order: the reference's summation order, so every row
+//               of in-degree <= S_MAX is bit-identical to the CPU result given bit-identical inputs.
+// HBM traffic per sweep: 4 B/edge (index stream) + 40 B/vertex (row pointer amortised, old rank, new rank,
+// new contrib, out-degree, first touch of contrib); gathers are served by shared memory / L2.
 #include "gmc_common.cuh"
+#include <cub/device/device_radix_sort.cuh>
 #include <vector>
 
 using namespace gmc;
 
-constexpr int PR_THREADS = 256;
-constexpr int PR_W = 2048;        // rows + edges per CTA (merge-path window)
-constexpr int PR_LONG = 2048;     // rows with more in-edges than this take the chunked path
-constexpr int PR_STAGE = PR_W + PR_LONG;   // max edges staged in shared memory by one CTA
-constexpr int PR_CHUNK = 8192;    // edges per CTA on the long-row path
-constexpr int PR_GATHER = 8;      // independent gathers in flight per thread
+constexpr int PR_THREADS = 1024;          // one CTA per SM, 32 independent warps
+constexpr int PR_WARPS = PR_THREADS / 32;
+constexpr int S_MAX = 64;                 // rows up to this in-degree are summed sequentially (bit-exact)
+constexpr int LT = 2048;                  // entries per long-row task (16 warp steps of 128)
+constexpr int ST_COST = 2048;             // cost units per short-row task (slice cost = 32*len + SLICE_OVH)
+constexpr int SLICE_OVH = 68;             // keeps a task at <= 31 slices
+constexpr int HOT_CAP = 28672;            // doubles of shared memory for the hot block (224 KB)
+constexpr unsigned FULL = 0xffffffffu;
 
 struct gmc_pr_ctrl {   // device-side loop control: lets the host enqueue sweeps without a sync per iteration
     double diff;
     int32_t cnt;
     int32_t done;
+    unsigned int arrived;
+    int32_t pad;
 };
 
-struct gmc_pr_shard {
-    int32_t n_global = 0, lo = 0, hi = 0, nrows = 0, nedges = 0;
-    const int32_t* r_begin = nullptr;     // [nrows+1], local edge offsets
-    const int32_t* r_node_idx = nullptr;  // [nedges], global source ids
-    const int32_t* outdeg = nullptr;      // [nrows]
-    bool owns_csr = false;
-    // plan
-    int32_t n_blocks = 0;
-    int32_t* block_first_row = nullptr;   // [n_blocks+1]
-    int32_t n_long = 0, n_long_chunks = 0;
-    int32_t* long_rows = nullptr;         // [n_long] local row ids, ascending
-    int32_t* long_chunk_begin = nullptr;  // [n_long+1]
-    double* long_partials = nullptr;      // [n_long_chunks]
-    double* diff_parts = nullptr;         // [n_blocks + n_long]
-    // peers (multi-GPU direct exchange): device arrays of pointers, one per parity
-    int n_peers = 0;
-    double** peers[2] = {nullptr, nullptr};
+struct SweepArgs {
+    // layout
+    const int32_t* __restrict__ E;
+    const int32_t* __restrict__ lbeg;        // [n_long+1]
+    const int32_t* __restrict__ sbeg;        // [n_slices+1]
+    const int32_t* __restrict__ ltask_row;   // [n_ltasks+1]
+    const int32_t* __restrict__ stask_slice; // [n_stasks+1]
+    const int32_t* __restrict__ outdeg;      // [N+1] by new id
+    int32_t N, n_long, hot_n, EL;
+    int32_t n_ltasks, n_stasks;
+    int32_t lt_lo, lt_hi, st_lo, st_hi;      // task ranges executed by this launch (multi-GPU shards)
+    // split rows
+    double* head_part;                       // [n_ltasks]
+    double* tail_part;                       // [n_ltasks]
+    unsigned int* split_cnt;                 // [n_ltasks]
+    double* diff_parts;                      // [2*n_ltasks + n_stasks]
+    // state
+    const double* __restrict__ contrib_in;   // [N+2]
+    double* contrib_out;
+    const double* __restrict__ rank_in;      // [N+1]
+    double* rank_out;
+    double d, base;
+    // loop control (may be null)
+    gmc_pr_ctrl* ctrl;
+    double e;
+    int32_t max_iter;
+};
+
+struct gmc_pr_plan {
+    int32_t N = 0, M = 0, n_long = 0, hot_n = 1, n_slices = 0, EL = 0, EN = 0, n_ltasks = 0, n_stasks = 0;
+    int32_t *new_of_old = nullptr, *old_of_new = nullptr, *E = nullptr, *lbeg = nullptr, *sbeg = nullptr;
+    int32_t *ltask_row = nullptr, *stask_slice = nullptr, *outdeg = nullptr;
+    double *head_part = nullptr, *tail_part = nullptr, *diff_parts = nullptr;
+    unsigned int* split_cnt = nullptr;
+    double* contrib[2] = {nullptr, nullptr};
+    double* rank[2] = {nullptr, nullptr};
+    gmc_pr_ctrl* ctrl = nullptr;
+    int grid = 0;
+    size_t smem = 0;
 };
 
 namespace {
 
-__global__ void compute_outdeg(const int32_t* __restrict__ begin, int32_t n, int32_t* __restrict__ outdeg) {
-    int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) outdeg[i] = begin[i + 1] - begin[i];
+// ---------------------------------------------------------------------------------------------
+// small PTX helpers: mbarrier + TMA bulk copy (global -> shared), streaming loads/stores
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+    asm volatile(
+        "{\n.reg .pred p;\nWAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\nbra WAIT_%=;\nDONE_%=:\n}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s(void* dst_smem, const void* src_gmem, unsigned bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ int4 ld_idx4(const int4* p) { return __ldcs(p); }       // read-once index stream
+__device__ __forceinline__ double butterfly(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+    return v;
 }
 
-// block_first_row[b] = first local row t with r_begin[t] + t >= b*W   (b = 0..n_blocks; last = nrows)
-__global__ void plan_blocks(const int32_t* __restrict__ r_begin, int32_t nrows, int32_t n_blocks, int32_t* __restrict__ first_row) {
-    int32_t b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b > n_blocks) return;
-    if (b == n_blocks) { first_row[b] = nrows; return; }
-    int64_t target = (int64_t)b * PR_W;
-    int32_t lo = 0, hi = nrows;  // answer in [lo, hi]
-    while (lo < hi) {
-        int32_t mid = lo + ((hi - lo) >> 1);
-        if ((int64_t)r_begin[mid] + mid >= target) hi = mid; else lo = mid + 1;
-    }
-    first_row[b] = lo;
+// ---------------------------------------------------------------------------------------------
+// the sweep
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double gather(const double* hot, const SweepArgs& A, int32_t w) {
+    return (w < A.hot_n) ? hot[w] : __ldg(A.contrib_in + w);
 }
-
-__global__ void flag_long_rows(const int32_t* __restrict__ r_begin, int32_t nrows, int32_t* __restrict__ flag, int32_t* __restrict__ nchunks) {
-    int32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= nrows) return;
-    int32_t len = r_begin[t + 1] - r_begin[t];
-    int32_t is_long = len > PR_LONG;
-    flag[t] = is_long;
-    nchunks[t] = is_long ? (len + PR_CHUNK - 1) / PR_CHUNK : 0;
-}
-
-__global__ void compact_long_rows(const int32_t* __restrict__ r_begin, int32_t nrows, const int32_t* __restrict__ pos,
-                                  const int32_t* __restrict__ chunk_pos, int32_t* __restrict__ long_rows,
-                                  int32_t* __restrict__ long_chunk_begin, int32_t n_long, int32_t n_chunks) {
-    int32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t == 0) long_chunk_begin[n_long] = n_chunks;
-    if (t >= nrows) return;
-    if (r_begin[t + 1] - r_begin[t] > PR_LONG) {
-        long_rows[pos[t]] = t;
-        long_chunk_begin[pos[t]] = chunk_pos[t];
-    }
-}
-
-__global__ void pr_init(int32_t n_global, int32_t lo, int32_t nrows, const int32_t* __restrict__ outdeg,
-                        double* __restrict__ contrib_full, double* __restrict__ rank_slice) {
-    int32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= nrows) return;
-    const double v = 1 / (double)n_global;                 // G.pg_rank = 1 / N  (pagerank.gm:6-7)
-    rank_slice[r] = v;
-    int32_t od = outdeg[r];
-    contrib_full[(size_t)lo + r] = od > 0 ? v / (double)od : 0.0;
-}
-
-struct RowOut {
-    double d, base;
-    const double* rank_in;
-    double* rank_out;
-    double* contrib_out;       // full-length, indexed by global id
-    const int32_t* outdeg;
-    double* const* peers;      // n_peers full-length contrib buffers on other GPUs (may be null)
-    int n_peers;
-    int32_t lo;
-};
 
 // per-row epilogue; mul and add kept separate (no FMA contraction) to match the CPU build's rounding
-__device__ __forceinline__ double finish_row(const RowOut& o, int32_t r, double S) {
-    double val = __dadd_rn(o.base, __dmul_rn(o.d, S));
-    double old = o.rank_in[r];
-    o.rank_out[r] = val;
-    int32_t od = o.outdeg[r];
-    double c = od > 0 ? val / (double)od : 0.0;
-    size_t gi = (size_t)o.lo + r;
-    o.contrib_out[gi] = c;
-    for (int p = 0; p < o.n_peers; p++) o.peers[p][gi] = c;   // NVLink stores into peer HBM
+__device__ __forceinline__ double finish_row(const SweepArgs& A, int32_t id, double S) {
+    const double val = __dadd_rn(A.base, __dmul_rn(A.d, S));
+    const double old = __ldcs(A.rank_in + id);
+    __stcs(A.rank_out + id, val);
+    const int32_t od = __ldcs(A.outdeg + id);
+    A.contrib_out[id] = od > 0 ? val / (double)od : 0.0;
     return fabs(__dsub_rn(val, old));
 }
 
-__device__ __forceinline__ double block_sum(double v, double* sm /*[PR_THREADS/32]*/) {
-    v = warp_sum(v);
-    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
-    __syncthreads();
-    double t = 0.0;
-    if (threadIdx.x < 32) {
-        t = threadIdx.x < (PR_THREADS / 32) ? sm[threadIdx.x] : 0.0;
-        t = warp_sum(t);
-    }
-    return t;  // valid in thread 0
-}
-
-__global__ void __launch_bounds__(PR_THREADS)
-pr_sweep_stream(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx,
-                const int32_t* __restrict__ block_first_row, const double* __restrict__ contrib_in,
-                RowOut o, double* __restrict__ diff_parts, const gmc_pr_ctrl* __restrict__ ctrl) {
-    if (ctrl && ctrl->done) return;
-    __shared__ double s_val[PR_STAGE];
-    __shared__ int32_t s_off[PR_W + 2];
-    __shared__ double s_red[PR_THREADS / 32];
-
-    const int32_t first = block_first_row[blockIdx.x];
-    const int32_t last = block_first_row[blockIdx.x + 1];
-    const int32_t nrows = last - first;
-    for (int32_t i = threadIdx.x; i <= nrows; i += PR_THREADS) s_off[i] = r_begin[first + i];
-    __syncthreads();
-    const int32_t e0 = s_off[0];
-    int32_t nstage_rows = nrows;   // rows reduced from shared memory
-    if (nrows > 0 && s_off[nrows] - s_off[nrows - 1] > PR_LONG) nstage_rows = nrows - 1;   // hub row: chunked path
-    const int32_t ne = s_off[nstage_rows] - e0;
-
-    // stream the index slice, gather contributions into shared memory
-    const int32_t* __restrict__ idx = r_node_idx + e0;
-    for (int32_t base = 0; base < ne; base += PR_THREADS * PR_GATHER) {
-        int32_t w[PR_GATHER];
-        double c[PR_GATHER];
+// first k in [0,32] with e_k > o, e_k ascending across lanes (lane k holds e_k)
+__device__ __forceinline__ int row_search(int32_t e, int32_t o) {
+    int k = 0;
 #pragma unroll
-        for (int k = 0; k < PR_GATHER; k++) {
-            int32_t i = base + k * PR_THREADS + threadIdx.x;
-            w[k] = (i < ne) ? ld_stream(idx + i) : -1;
-        }
-#pragma unroll
-        for (int k = 0; k < PR_GATHER; k++) c[k] = (w[k] >= 0) ? contrib_in[w[k]] : 0.0;
-#pragma unroll
-        for (int k = 0; k < PR_GATHER; k++) {
-            int32_t i = base + k * PR_THREADS + threadIdx.x;
-            if (i < ne) s_val[i] = c[k];
-        }
+    for (int s = 16; s > 0; s >>= 1) {
+        int32_t ek = __shfl_sync(FULL, e, k + s - 1);
+        if (ek <= o) k += s;
     }
-    __syncthreads();
-
-    // one thread per row, left-to-right (the reference's order)
-    double diff = 0.0;
-    for (int32_t r = threadIdx.x; r < nstage_rows; r += PR_THREADS) {
-        int32_t b = s_off[r] - e0, e = s_off[r + 1] - e0;
-        double S = 0.0;
-        for (int32_t j = b; j < e; j++) S = S + s_val[j];
-        diff += finish_row(o, first + r, S);
-    }
-    double tot = block_sum(diff, s_red);
-    if (threadIdx.x == 0) diff_parts[blockIdx.x] = tot;
+    return k;
 }
 
-// hub rows: CTA c sums one PR_CHUNK-edge chunk of one long row
-__global__ void __launch_bounds__(PR_THREADS)
-pr_long_chunks(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx,
-               const int32_t* __restrict__ long_rows, const int32_t* __restrict__ long_chunk_begin, int32_t n_long,
-               const double* __restrict__ contrib_in, double* __restrict__ partials, const gmc_pr_ctrl* __restrict__ ctrl) {
-    if (ctrl && ctrl->done) return;
-    __shared__ double s_red[PR_THREADS / 32];
-    const int32_t c = blockIdx.x;
-    int32_t lo = 0, hi = n_long;   // long_chunk_begin[lo] <= c < long_chunk_begin[hi]
-    while (hi - lo > 1) {
-        int32_t mid = (lo + hi) >> 1;
-        if (long_chunk_begin[mid] <= c) lo = mid; else hi = mid;
+// the last task to deliver a piece of a cut row adds the pieces in task order and finishes the row
+__device__ __forceinline__ void split_arrive(const SweepArgs& A, int lane, int32_t t1, int32_t t2, int32_t row, double piece,
+                                             double* slot, int32_t n_tasks_total) {
+    int last = 0;
+    if (lane == 0) {
+        *slot = piece;
+        __threadfence();
+        unsigned old = atomicAdd(&A.split_cnt[t1], 1u);
+        last = (old == (unsigned)(t2 - t1));
     }
-    const int32_t row = long_rows[lo];
-    const int32_t k = c - long_chunk_begin[lo];
-    const int32_t rb = r_begin[row], re = r_begin[row + 1];
-    const int32_t cb = rb + k * PR_CHUNK;
-    const int32_t ce = min(cb + PR_CHUNK, re);
-    double acc[4] = {0.0, 0.0, 0.0, 0.0};
-    int32_t i = cb + threadIdx.x;
-    for (; i + 3 * PR_THREADS < ce; i += 4 * PR_THREADS) {
-        int32_t w0 = ld_stream(r_node_idx + i), w1 = ld_stream(r_node_idx + i + PR_THREADS);
-        int32_t w2 = ld_stream(r_node_idx + i + 2 * PR_THREADS), w3 = ld_stream(r_node_idx + i + 3 * PR_THREADS);
-        acc[0] += contrib_in[w0]; acc[1] += contrib_in[w1]; acc[2] += contrib_in[w2]; acc[3] += contrib_in[w3];
-    }
-    for (; i < ce; i += PR_THREADS) acc[0] += contrib_in[ld_stream(r_node_idx + i)];
-    double tot = block_sum((acc[0] + acc[1]) + (acc[2] + acc[3]), s_red);
-    if (threadIdx.x == 0) partials[c] = tot;
-}
-
-__global__ void pr_long_finalize(const int32_t* __restrict__ long_rows, const int32_t* __restrict__ long_chunk_begin,
-                                 int32_t n_long, const double* __restrict__ partials, RowOut o,
-                                 double* __restrict__ diff_parts, const gmc_pr_ctrl* __restrict__ ctrl) {
-    if (ctrl && ctrl->done) return;
-    int32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n_long) return;
-    double S = 0.0;
-    for (int32_t c = long_chunk_begin[j]; c < long_chunk_begin[j + 1]; c++) S += partials[c];
-    diff_parts[j] = finish_row(o, long_rows[j], S);
-}
-
-// diff = sum(diff_parts) in a fixed order; then either loop control (ctrl) or plain output (diff_out)
-__global__ void __launch_bounds__(1024)
-pr_reduce_diff(const double* __restrict__ parts, int32_t n_parts, gmc_pr_ctrl* ctrl, double e, int32_t max_iter,
-               double* __restrict__ diff_out) {
-    if (ctrl && ctrl->done) return;
-    __shared__ double sm[32];
+    last = __shfl_sync(FULL, last, 0);
+    if (!last) return;
+    __threadfence();
     double v = 0.0;
-    for (int32_t i = threadIdx.x; i < n_parts; i += 1024) v += parts[i];
-    v = warp_sum(v);
-    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = v;
+    for (int32_t p = t1 + lane; p <= t2; p += 32) v += (p == t1) ? __ldcg(A.tail_part + p) : __ldcg(A.head_part + p);
+    const double S = butterfly(v);
+    if (lane == 0) {
+        A.diff_parts[n_tasks_total + t1] = finish_row(A, row + 1, S);
+        A.split_cnt[t1] = 0u;
+    }
+}
+
+__device__ __forceinline__ void long_task(const SweepArgs& A, const double* hot, int lane, int32_t t) {
+    const int32_t x0 = t * LT;
+    const int32_t x1 = min(x0 + LT, A.EL);
+    const int32_t a = __ldg(A.ltask_row + t);                     // row (0-based; id = row + 1) holding entry x0
+    const int32_t e = (a + lane < A.n_long) ? __ldg(A.lbeg + a + lane + 1) : INT32_MAX;   // end of row a+lane
+    const int32_t rb0 = __ldg(A.lbeg + a);
+    const bool head_split = rb0 < x0;
+    const int kl = row_search(e, x1 - 1);                          // last row of the task (relative)
+    const int32_t e_kl = __shfl_sync(FULL, e, kl);
+    const bool tail_split = e_kl > x1;
+
+    double acc = 0.0, my_sum = 0.0, head_acc = 0.0, tail_acc = 0.0;
+    int acc_row = -1;
+    const int4* __restrict__ E4 = reinterpret_cast<const int4*>(A.E + x0);
+    const int32_t span = x1 - x0;
+    const int nst = (span + 127) >> 7;
+    const int4 zero4 = make_int4(0, 0, 0, 0);
+    int4 nx0 = (4 * lane < span) ? ld_idx4(E4 + lane) : zero4;
+    int4 nx1 = (128 + 4 * lane < span) ? ld_idx4(E4 + 32 + lane) : zero4;
+
+    auto emit = [&](int row, bool in) {
+        // lanes whose entries moved on to a later row hand their finished row to the warp
+        const bool changed = in && row != acc_row && acc_row >= 0;
+        unsigned m = __ballot_sync(FULL, changed);
+        while (m) {
+            const int leader = __ffs(m) - 1;
+            const int R = __shfl_sync(FULL, acc_row, leader);
+            const bool mem = changed && acc_row == R;
+            const unsigned mm = __ballot_sync(FULL, mem);
+            const double tot = butterfly(mem ? acc : 0.0);
+            if (R == 0 && head_split) head_acc += tot;
+            else if (R == kl && tail_split) tail_acc += tot;
+            else if (lane == R) my_sum += tot;
+            m &= ~mm;
+        }
+        if (in && row != acc_row) { acc_row = row; acc = 0.0; }
+    };
+
+    for (int i = 0; i < nst; i += 2) {
+        const int4 c0 = nx0, c1 = nx1;
+        const int32_t o0 = i * 128 + 4 * lane, o1 = o0 + 128;
+        nx0 = (o0 + 256 < span) ? ld_idx4(E4 + (i + 2) * 32 + lane) : zero4;
+        nx1 = (o1 + 256 < span) ? ld_idx4(E4 + (i + 3) * 32 + lane) : zero4;
+        const double v0 = gather(hot, A, c0.x), v1 = gather(hot, A, c0.y), v2 = gather(hot, A, c0.z), v3 = gather(hot, A, c0.w);
+        const double v4 = gather(hot, A, c1.x), v5 = gather(hot, A, c1.y), v6 = gather(hot, A, c1.z), v7 = gather(hot, A, c1.w);
+        const bool in0 = o0 < span, in1 = o1 < span;
+        const int r0 = row_search(e, x0 + o0), r1 = row_search(e, x0 + o1);
+        emit(r0, in0);
+        acc += (v0 + v1) + (v2 + v3);
+        emit(r1, in1);
+        acc += (v4 + v5) + (v6 + v7);
+    }
+    {   // final flush: every lane hands over what it still holds
+        const bool have = acc_row >= 0;
+        unsigned m = __ballot_sync(FULL, have);
+        while (m) {
+            const int leader = __ffs(m) - 1;
+            const int R = __shfl_sync(FULL, acc_row, leader);
+            const bool mem = have && acc_row == R;
+            const unsigned mm = __ballot_sync(FULL, mem);
+            const double tot = butterfly(mem ? acc : 0.0);
+            if (R == 0 && head_split) head_acc += tot;
+            else if (R == kl && tail_split) tail_acc += tot;
+            else if (lane == R) my_sum += tot;
+            m &= ~mm;
+        }
+    }
+    // rows that lie completely inside the task: one lane per row, coalesced epilogue
+    const int k_first = head_split ? 1 : 0;
+    const int k_last = tail_split ? kl - 1 : kl;
+    double diff = 0.0;
+    if (lane >= k_first && lane <= k_last) diff = finish_row(A, a + lane + 1, my_sum);
+    diff = butterfly(diff);
+    if (lane == 0) { A.diff_parts[t] = diff; __threadfence(); }
+    const int32_t n_tasks_total = A.n_ltasks + A.n_stasks;
+    if (head_split) {
+        const int32_t e0 = __shfl_sync(FULL, e, 0);
+        split_arrive(A, lane, rb0 / LT, (e0 - 1) / LT, a, head_acc, A.head_part + t, n_tasks_total);
+    }
+    if (tail_split && !(kl == 0 && head_split))
+        split_arrive(A, lane, t, (e_kl - 1) / LT, a + kl, tail_acc, A.tail_part + t, n_tasks_total);
+}
+
+__device__ __forceinline__ void short_task(const SweepArgs& A, const double* hot, int lane, int32_t u) {
+    const int32_t s_lo = __ldg(A.stask_slice + u), s_hi = __ldg(A.stask_slice + u + 1);
+    const int ns = s_hi - s_lo;                                  // <= 31
+    const int32_t sb = (lane <= ns) ? __ldg(A.sbeg + s_lo + lane) : 0;
+    double diff = 0.0;
+    for (int q = 0; q < ns; q++) {
+        const int32_t base = __shfl_sync(FULL, sb, q);
+        const int L = (__shfl_sync(FULL, sb, q + 1) - base) >> 5;
+        const int32_t id = A.n_long + 1 + (s_lo + q) * 32 + lane;
+        const int32_t* __restrict__ p = A.E + base + lane;
+        double S = 0.0;
+        for (int j = 0; j < L; j += 8) {
+            int32_t w[8];
+            double v[8];
+#pragma unroll
+            for (int k = 0; k < 8; k++) w[k] = (j + k < L) ? __ldcs(p + (j + k) * 32) : 0;
+#pragma unroll
+            for (int k = 0; k < 8; k++) v[k] = gather(hot, A, w[k]);
+#pragma unroll
+            for (int k = 0; k < 8; k++) S = S + v[k];              // left to right: the reference's order (+0.0 for padding)
+        }
+        if (id <= A.N) diff += finish_row(A, id, S);
+    }
+    diff = butterfly(diff);
+    if (lane == 0) { A.diff_parts[A.n_ltasks + u] = diff; __threadfence(); }
+}
+
+__global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
+    if (A.ctrl && A.ctrl->done) return;
+    extern __shared__ __align__(16) double hot[];
+    __shared__ __align__(8) unsigned long long bar;
+    __shared__ double s_red[PR_WARPS];
+    __shared__ int s_last;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    // stage the hot block: contrib_in[0, hot_n) -> shared memory, one TMA bulk copy stream
+    if (tid == 0) mbar_init(&bar, 1);
     __syncthreads();
-    if (threadIdx.x < 32) {
-        double t = sm[threadIdx.x];
-        t = warp_sum(t);
-        if (threadIdx.x == 0) {
-            if (diff_out) *diff_out = t;
-            if (ctrl) {
-                int32_t cnt = ctrl->cnt + 1;
-                ctrl->diff = t;
-                ctrl->cnt = cnt;
-                ctrl->done = !((t > e) && (cnt < max_iter));   // } While ((diff > e) && (cnt < max))
-            }
+    if (tid == 0) {
+        const unsigned bytes = (unsigned)(((A.hot_n + 1) & ~1) * 8);     // multiple of 16
+        mbar_expect_tx(&bar, bytes);
+        const char* src = reinterpret_cast<const char*>(A.contrib_in);
+        char* dst = reinterpret_cast<char*>(hot);
+        for (unsigned off = 0; off < bytes; off += 32768u) tma_bulk_g2s(dst + off, src + off, min(32768u, bytes - off), &bar);
+    }
+    mbar_wait(&bar, 0);
+
+    // tasks: static round-robin over all warps of the grid, long-row tasks first
+    const int32_t n_l = A.lt_hi - A.lt_lo, n_s = A.st_hi - A.st_lo;
+    const int32_t stride = gridDim.x * PR_WARPS;
+    for (int32_t u = blockIdx.x * PR_WARPS + warp; u < n_l + n_s; u += stride) {
+        if (u < n_l) long_task(A, hot, lane, A.lt_lo + u);
+        else short_task(A, hot, lane, A.st_lo + (u - n_l));
+    }
+
+    if (!A.ctrl) return;
+    // the last CTA adds the per-task diff partials in a fixed order and advances the loop control
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        s_last = (atomicAdd(&A.ctrl->arrived, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const int32_t nparts = 2 * A.n_ltasks + A.n_stasks;
+    double v = 0.0;
+    for (int32_t i = tid; i < nparts; i += PR_THREADS) v += __ldcg(A.diff_parts + i);
+    v = butterfly(v);
+    if (lane == 0) s_red[warp] = v;
+    __syncthreads();
+    if (warp == 0) {
+        double t = butterfly(s_red[lane]);
+        if (lane == 0) {
+            const int32_t cnt = A.ctrl->cnt + 1;
+            A.ctrl->diff = t;
+            A.ctrl->cnt = cnt;
+            A.ctrl->done = !((t > A.e) && (cnt < A.max_iter));       // } While ((diff > e) && (cnt < max))
+            A.ctrl->arrived = 0u;
         }
     }
 }
 
-int build_plan(gmc_pr_shard* s, cudaStream_t st) {
-    const int32_t nrows = s->nrows;
-    int64_t work = (int64_t)s->nedges + nrows;
-    s->n_blocks = (int32_t)div_up(work, (int64_t)PR_W);
-    if (s->n_blocks == 0) s->n_blocks = nrows > 0 ? 1 : 0;
-    GMC_TRY(gmc_malloc((void**)&s->block_first_row, sizeof(int32_t) * ((size_t)s->n_blocks + 1)));
-    plan_blocks<<<div_up(s->n_blocks + 1, 256), 256, 0, st>>>(s->r_begin, nrows, s->n_blocks, s->block_first_row);
-    GMC_CUDA(cudaGetLastError());
-    // long rows
-    s->n_long = 0; s->n_long_chunks = 0;
-    if (nrows > 0) {
-        int32_t *flag = nullptr, *nchunks = nullptr, *tot = nullptr;
-        GMC_TRY(gmc_malloc((void**)&flag, sizeof(int32_t) * (size_t)nrows));
-        GMC_TRY(gmc_malloc((void**)&nchunks, sizeof(int32_t) * (size_t)nrows));
-        GMC_TRY(gmc_malloc((void**)&tot, sizeof(int32_t) * 2));
-        flag_long_rows<<<div_up(nrows, 256), 256, 0, st>>>(s->r_begin, nrows, flag, nchunks);
-        GMC_TRY(exclusive_scan_i32(flag, flag, nrows, tot, st));
-        GMC_TRY(exclusive_scan_i32(nchunks, nchunks, nrows, tot + 1, st));
-        int32_t h[2];
-        GMC_CUDA(cudaMemcpyAsync(h, tot, sizeof(h), cudaMemcpyDeviceToHost, st));
-        GMC_CUDA(cudaStreamSynchronize(st));
-        s->n_long = h[0]; s->n_long_chunks = h[1];
-        if (s->n_long > 0) {
-            GMC_TRY(gmc_malloc((void**)&s->long_rows, sizeof(int32_t) * (size_t)s->n_long));
-            GMC_TRY(gmc_malloc((void**)&s->long_chunk_begin, sizeof(int32_t) * ((size_t)s->n_long + 1)));
-            GMC_TRY(gmc_malloc((void**)&s->long_partials, sizeof(double) * (size_t)s->n_long_chunks));
-            compact_long_rows<<<div_up(nrows, 256), 256, 0, st>>>(s->r_begin, nrows, flag, nchunks, s->long_rows, s->long_chunk_begin, s->n_long, s->n_long_chunks);
-            GMC_CUDA(cudaGetLastError());
-        }
-        GMC_CUDA(cudaStreamSynchronize(st));
-        cudaFree(flag); cudaFree(nchunks); cudaFree(tot);
+// ---------------------------------------------------------------------------------------------
+// plan kernels
+// ---------------------------------------------------------------------------------------------
+__global__ void k_degrees(const int32_t* __restrict__ begin, const int32_t* __restrict__ r_begin, int32_t n,
+                          int32_t* __restrict__ outdeg, int32_t* __restrict__ indeg, uint32_t* __restrict__ key_a,
+                          int32_t* __restrict__ ids, int32_t* __restrict__ is_long) {
+    int32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= n) return;
+    const int32_t od = begin[v + 1] - begin[v], id = r_begin[v + 1] - r_begin[v];
+    outdeg[v] = od;
+    indeg[v] = id;
+    const bool lg = id > S_MAX;
+    is_long[v] = lg;
+    key_a[v] = lg ? (uint32_t)(0x7fffffff - od) : 0xffffffffu;    // long rows by out-degree descending, short rows last
+    ids[v] = v;
+}
+
+// hot rank of the first `hot_ids` vertices of the out-degree order, then the final ordering key
+__global__ void k_hot_rank(const int32_t* __restrict__ sorted_ids, int32_t n, int32_t hot_ids, int32_t* __restrict__ hot_rank) {
+    int32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < n) hot_rank[sorted_ids[p]] = p < hot_ids ? p : -1;
+}
+__global__ void k_order_key(const int32_t* __restrict__ indeg, const int32_t* __restrict__ hot_rank, int32_t n,
+                            unsigned long long* __restrict__ key, int32_t* __restrict__ ids) {
+    int32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= n) return;
+    const int32_t hr = hot_rank[v], id = indeg[v];
+    unsigned long long k;
+    if (hr >= 0) k = (unsigned long long)hr;
+    else k = ((unsigned long long)(id > S_MAX ? 1 : 2) << 32) | (unsigned)(0x7fffffff - id);
+    key[v] = k;
+    ids[v] = v;
+}
+__global__ void k_relabel(const int32_t* __restrict__ sorted_ids, int32_t n, int32_t* __restrict__ old_of_new,
+                          int32_t* __restrict__ new_of_old) {
+    int32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p == 0) old_of_new[0] = -1;
+    if (p >= n) return;
+    const int32_t v = sorted_ids[p];
+    old_of_new[p + 1] = v;
+    new_of_old[v] = p + 1;
+}
+// padded long-row lengths (n_long values + a trailing 0), slice lengths (n_slices values + trailing 0), outdeg by new id
+__global__ void k_lengths(const int32_t* __restrict__ old_of_new, const int32_t* __restrict__ indeg, const int32_t* __restrict__ outdeg_old,
+                          int32_t n, int32_t n_long, int32_t n_slices, int32_t* __restrict__ lbeg, int32_t* __restrict__ sbeg,
+                          int32_t* __restrict__ scost, int32_t* __restrict__ outdeg_new) {
+    int32_t j = blockIdx.x * blockDim.x + threadIdx.x;     // 0-based row, id = j+1
+    if (j == 0) { lbeg[n_long] = 0; sbeg[n_slices] = 0; scost[n_slices] = 0; outdeg_new[0] = 0; }
+    if (j >= n) return;
+    const int32_t v = old_of_new[j + 1];
+    outdeg_new[j + 1] = outdeg_old[v];
+    const int32_t len = indeg[v];
+    if (j < n_long) lbeg[j] = (len + 3) & ~3;
+    else if (((j - n_long) & 31) == 0) {
+        const int32_t s = (j - n_long) >> 5;
+        sbeg[s] = 32 * len;                                 // first row of the slice is its longest
+        scost[s] = 32 * len + SLICE_OVH;
     }
-    GMC_TRY(gmc_malloc((void**)&s->diff_parts, sizeof(double) * ((size_t)s->n_blocks + s->n_long + 1)));
+}
+__global__ void k_add_offset(int32_t* __restrict__ a, int32_t n, const int32_t* __restrict__ off) {
+    int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) a[i] += *off;
+}
+// scatter every reverse edge into E, keeping its position inside the row (= the reference's summation order)
+__global__ void k_fill_entries(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t m,
+                               const int32_t* __restrict__ new_of_old, int32_t n_long, const int32_t* __restrict__ lbeg,
+                               const int32_t* __restrict__ sbeg, int32_t* __restrict__ E) {
+    int32_t eidx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (eidx >= m) return;
+    int32_t lo = 0, hi = n;   // r_begin[lo] <= eidx < r_begin[hi]
+    while (hi - lo > 1) {
+        const int32_t mid = lo + ((hi - lo) >> 1);
+        if (r_begin[mid] <= eidx) lo = mid; else hi = mid;
+    }
+    const int32_t k = eidx - r_begin[lo];
+    const int32_t j = new_of_old[lo] - 1;
+    const int32_t w = new_of_old[ld_stream(r_node_idx + eidx)];
+    if (j < n_long) E[lbeg[j] + k] = w;
+    else {
+        const int32_t q = j - n_long;
+        E[sbeg[q >> 5] + k * 32 + (q & 31)] = w;
+    }
+}
+// first[t] = first index j in [0,n] with pos[j] (+ len of j when INCL) > / >= target   (task cut points)
+__global__ void k_ltask_rows(const int32_t* __restrict__ lbeg, int32_t n_long, int32_t n_tasks, int32_t* __restrict__ first) {
+    int32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t > n_tasks) return;
+    if (t == n_tasks) { first[t] = n_long; return; }
+    const int32_t target = t * LT;           // row holding entry `target`: last j with lbeg[j] <= target
+    int32_t lo = 0, hi = n_long;             // lbeg[lo] <= target < lbeg[hi]
+    while (hi - lo > 1) {
+        const int32_t mid = lo + ((hi - lo) >> 1);
+        if (lbeg[mid] <= target) lo = mid; else hi = mid;
+    }
+    first[t] = lo;
+}
+__global__ void k_stask_slices(const int32_t* __restrict__ cpos, int32_t n_slices, int32_t n_tasks, int32_t* __restrict__ first) {
+    int32_t u = blockIdx.x * blockDim.x + threadIdx.x;
+    if (u > n_tasks) return;
+    if (u == n_tasks) { first[u] = n_slices; return; }
+    const int32_t target = u * ST_COST;      // first slice with cpos >= target
+    int32_t lo = 0, hi = n_slices;
+    while (lo < hi) {
+        const int32_t mid = lo + ((hi - lo) >> 1);
+        if (cpos[mid] >= target) hi = mid; else lo = mid + 1;
+    }
+    first[u] = lo;
+}
+__global__ void k_init(SweepArgs A, double* __restrict__ contrib0, double* __restrict__ contrib1, double* __restrict__ rank0) {
+    int32_t id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id > A.N + 1) return;
+    if (id == 0 || id == A.N + 1) { contrib0[id] = 0.0; contrib1[id] = 0.0; if (id == 0) rank0[0] = 0.0; return; }
+    const double v = 1 / (double)A.N;                       // G.pg_rank = 1 / N  (pagerank.gm:6-7)
+    rank0[id] = v;
+    const int32_t od = A.outdeg[id];
+    contrib0[id] = od > 0 ? v / (double)od : 0.0;
+}
+__global__ void k_unpermute(const double* __restrict__ rank_new, const int32_t* __restrict__ new_of_old, int32_t n, double* __restrict__ out) {
+    int32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v < n) out[v] = rank_new[new_of_old[v]];
+}
+
+template <typename K>
+int sort_pairs(K* keys_in, K* keys_out, int32_t* vals_in, int32_t* vals_out, int32_t n, int end_bit, cudaStream_t st) {
+    void* tmp = nullptr;
+    size_t bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, bytes, keys_in, keys_out, vals_in, vals_out, (int64_t)n, 0, end_bit, st);
+    GMC_TRY(gmc_malloc(&tmp, bytes));
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(tmp, bytes, keys_in, keys_out, vals_in, vals_out, (int64_t)n, 0, end_bit, st);
+    cudaStreamSynchronize(st);
+    cudaFree(tmp);
+    if (e != cudaSuccess) { set_error("plan sort: %s", cudaGetErrorString(e)); return GMC_ERR_CUDA; }
     return GMC_OK;
 }
 
-// one sweep = up to 3 launches (+1 reduce); returns the number of kernels launched
-int launch_sweep(gmc_pr_shard* s, double d, const double* contrib_in, double* contrib_out, const double* rank_in,
-                 double* rank_out, int parity, const gmc_pr_ctrl* ctrl, cudaStream_t st, int* launches) {
-    RowOut o;
-    o.d = d;
-    o.base = (1 - d) / (double)s->n_global;     // (1-d) / N, pagerank.gm:11
-    o.rank_in = rank_in; o.rank_out = rank_out; o.contrib_out = contrib_out;
-    o.outdeg = s->outdeg;
-    o.peers = s->n_peers ? s->peers[parity & 1] : nullptr;
-    o.n_peers = s->n_peers;
-    o.lo = s->lo;
-    int n = 0;
-    if (s->n_blocks > 0) {
-        pr_sweep_stream<<<s->n_blocks, PR_THREADS, 0, st>>>(s->r_begin, s->r_node_idx, s->block_first_row, contrib_in, o, s->diff_parts + s->n_long, ctrl);
-        n++;
+void free_plan(gmc_pr_plan* p) {
+    if (!p) return;
+    cudaFree(p->new_of_old); cudaFree(p->old_of_new); cudaFree(p->E); cudaFree(p->lbeg); cudaFree(p->sbeg);
+    cudaFree(p->ltask_row); cudaFree(p->stask_slice); cudaFree(p->outdeg);
+    cudaFree(p->head_part); cudaFree(p->tail_part); cudaFree(p->diff_parts); cudaFree(p->split_cnt);
+    cudaFree(p->contrib[0]); cudaFree(p->contrib[1]); cudaFree(p->rank[0]); cudaFree(p->rank[1]); cudaFree(p->ctrl);
+    delete p;
+}
+
+#define PLAN_TRY(expr) do { rc = (expr); if (rc != GMC_OK) goto fail; } while (0)
+
+int build_plan(gmc_graph* g, gmc_pr_plan** out, cudaStream_t st) {
+    const int32_t n = g->N, m = g->M;
+    gmc_pr_plan* p = new gmc_pr_plan();
+    p->N = n; p->M = m;
+    int rc = GMC_OK;
+    int32_t *outdeg_old = nullptr, *indeg = nullptr, *ids = nullptr, *ids2 = nullptr, *is_long = nullptr, *hot_rank = nullptr, *scost = nullptr;
+    uint32_t *key_a = nullptr, *key_a2 = nullptr;
+    unsigned long long *key_b = nullptr, *key_b2 = nullptr;
+    int32_t* tot = nullptr;
+    const size_t nn = (size_t)n;
+    const unsigned gb = (unsigned)div_up(n, 256);
+    int32_t h[2] = {0, 0};
+    int32_t cost_total = 0;
+
+    PLAN_TRY(gmc_malloc((void**)&outdeg_old, 4 * nn)); PLAN_TRY(gmc_malloc((void**)&indeg, 4 * nn));
+    PLAN_TRY(gmc_malloc((void**)&ids, 4 * nn)); PLAN_TRY(gmc_malloc((void**)&ids2, 4 * nn));
+    PLAN_TRY(gmc_malloc((void**)&is_long, 4 * nn)); PLAN_TRY(gmc_malloc((void**)&hot_rank, 4 * nn));
+    PLAN_TRY(gmc_malloc((void**)&key_a, 4 * nn)); PLAN_TRY(gmc_malloc((void**)&key_a2, 4 * nn));
+    PLAN_TRY(gmc_malloc((void**)&key_b, 8 * nn)); PLAN_TRY(gmc_malloc((void**)&key_b2, 8 * nn));
+    PLAN_TRY(gmc_malloc((void**)&tot, 16));
+    PLAN_TRY(gmc_malloc((void**)&p->new_of_old, 4 * nn)); PLAN_TRY(gmc_malloc((void**)&p->old_of_new, 4 * (nn + 1)));
+    PLAN_TRY(gmc_malloc((void**)&p->outdeg, 4 * (nn + 1)));
+
+    // 1. degrees, number of long rows, the hot block
+    k_degrees<<<gb, 256, 0, st>>>(g->begin, g->r_begin, n, outdeg_old, indeg, key_a, ids, is_long);
+    PLAN_TRY(exclusive_scan_i32(is_long, is_long, nn, tot, st));
+    if (cudaMemcpyAsync(h, tot, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) { rc = GMC_ERR_CUDA; set_error("plan: %s", cudaGetErrorString(cudaGetLastError())); goto fail; }
+    p->n_long = h[0];
+    {
+        const int32_t hot_ids = p->n_long < HOT_CAP - 2 ? p->n_long : HOT_CAP - 2;
+        p->hot_n = hot_ids + 1;                             // ids [0, hot_n): the dummy + the hot block
+        PLAN_TRY(sort_pairs<uint32_t>(key_a, key_a2, ids, ids2, n, 32, st));
+        k_hot_rank<<<gb, 256, 0, st>>>(ids2, n, hot_ids, hot_rank);
+        k_order_key<<<gb, 256, 0, st>>>(indeg, hot_rank, n, key_b, ids);
+        PLAN_TRY(sort_pairs<unsigned long long>(key_b, key_b2, ids, ids2, n, 34, st));
+        k_relabel<<<gb, 256, 0, st>>>(ids2, n, p->old_of_new, p->new_of_old);
     }
-    if (s->n_long > 0) {
-        pr_long_chunks<<<s->n_long_chunks, PR_THREADS, 0, st>>>(s->r_begin, s->r_node_idx, s->long_rows, s->long_chunk_begin, s->n_long, contrib_in, s->long_partials, ctrl);
-        pr_long_finalize<<<div_up(s->n_long, 128), 128, 0, st>>>(s->long_rows, s->long_chunk_begin, s->n_long, s->long_partials, o, s->diff_parts, ctrl);
-        n += 2;
+    // 2. row offsets of both sections
+    p->n_slices = div_up(n - p->n_long, 32);
+    PLAN_TRY(gmc_malloc((void**)&p->lbeg, 4 * ((size_t)p->n_long + 1)));
+    PLAN_TRY(gmc_malloc((void**)&p->sbeg, 4 * ((size_t)p->n_slices + 1)));
+    PLAN_TRY(gmc_malloc((void**)&scost, 4 * ((size_t)p->n_slices + 1)));
+    k_lengths<<<gb, 256, 0, st>>>(p->old_of_new, indeg, outdeg_old, n, p->n_long, p->n_slices, p->lbeg, p->sbeg, scost, p->outdeg);
+    PLAN_TRY(exclusive_scan_i32(p->lbeg, p->lbeg, (size_t)p->n_long + 1, nullptr, st));
+    PLAN_TRY(exclusive_scan_i32(p->sbeg, p->sbeg, (size_t)p->n_slices + 1, nullptr, st));
+    PLAN_TRY(exclusive_scan_i32(scost, scost, (size_t)p->n_slices + 1, nullptr, st));
+    k_add_offset<<<div_up(p->n_slices + 1, 256), 256, 0, st>>>(p->sbeg, p->n_slices + 1, p->lbeg + p->n_long);
+    {
+        int64_t est = (int64_t)m + 3LL * p->n_long + 32LL * S_MAX * 2;   // padding bound (slices mix at most a few lengths)
+        (void)est;
+        if (cudaMemcpyAsync(&h[0], p->lbeg + p->n_long, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+            cudaMemcpyAsync(&h[1], p->sbeg + p->n_slices, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+            cudaMemcpyAsync(&cost_total, scost + p->n_slices, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+            cudaStreamSynchronize(st) != cudaSuccess) { rc = GMC_ERR_CUDA; set_error("plan: %s", cudaGetErrorString(cudaGetLastError())); goto fail; }
     }
-    GMC_CUDA(cudaGetLastError());
-    if (launches) *launches += n;
+    p->EL = h[0];
+    p->EN = h[1];
+    if (p->EL < 0 || p->EN < p->EL) { rc = GMC_ERR_ARG; set_error("pagerank plan: entry array exceeds int32 offsets"); goto fail; }
+    // 3. the entry array
+    PLAN_TRY(gmc_malloc((void**)&p->E, 4 * ((size_t)p->EN + 8)));
+    if (cudaMemsetAsync(p->E, 0, 4 * ((size_t)p->EN + 8), st) != cudaSuccess) { rc = GMC_ERR_CUDA; goto fail; }
+    if (m > 0) k_fill_entries<<<div_up(m, 256), 256, 0, st>>>(g->r_begin, g->r_node_idx, n, m, p->new_of_old, p->n_long, p->lbeg, p->sbeg, p->E);
+    // 4. tasks
+    p->n_ltasks = div_up(p->EL, LT);
+    p->n_stasks = div_up(cost_total, ST_COST);
+    PLAN_TRY(gmc_malloc((void**)&p->ltask_row, 4 * ((size_t)p->n_ltasks + 1)));
+    PLAN_TRY(gmc_malloc((void**)&p->stask_slice, 4 * ((size_t)p->n_stasks + 1)));
+    k_ltask_rows<<<div_up(p->n_ltasks + 1, 256), 256, 0, st>>>(p->lbeg, p->n_long, p->n_ltasks, p->ltask_row);
+    k_stask_slices<<<div_up(p->n_stasks + 1, 256), 256, 0, st>>>(scost, p->n_slices, p->n_stasks, p->stask_slice);
+    {
+        const size_t nl = (size_t)(p->n_ltasks ? p->n_ltasks : 1), nparts = 2 * nl + (size_t)p->n_stasks + 1;
+        PLAN_TRY(gmc_malloc((void**)&p->head_part, 8 * nl)); PLAN_TRY(gmc_malloc((void**)&p->tail_part, 8 * nl));
+        PLAN_TRY(gmc_malloc((void**)&p->split_cnt, 4 * nl)); PLAN_TRY(gmc_malloc((void**)&p->diff_parts, 8 * nparts));
+        cudaMemsetAsync(p->head_part, 0, 8 * nl, st); cudaMemsetAsync(p->tail_part, 0, 8 * nl, st);
+        cudaMemsetAsync(p->split_cnt, 0, 4 * nl, st); cudaMemsetAsync(p->diff_parts, 0, 8 * nparts, st);
+    }
+    // 5. state
+    for (int k = 0; k < 2; k++) {
+        PLAN_TRY(gmc_malloc((void**)&p->contrib[k], 8 * (nn + 4)));
+        PLAN_TRY(gmc_malloc((void**)&p->rank[k], 8 * (nn + 4)));
+    }
+    PLAN_TRY(gmc_malloc((void**)&p->ctrl, sizeof(gmc_pr_ctrl)));
+    p->grid = sm_count();
+    p->smem = (size_t)HOT_CAP * 8;
+    if (cudaFuncSetAttribute(pr_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem) != cudaSuccess ||
+        cudaStreamSynchronize(st) != cudaSuccess) { rc = GMC_ERR_CUDA; set_error("pagerank plan: %s", cudaGetErrorString(cudaGetLastError())); goto fail; }
+fail:
+    cudaFree(outdeg_old); cudaFree(indeg); cudaFree(ids); cudaFree(ids2); cudaFree(is_long); cudaFree(hot_rank); cudaFree(scost);
+    cudaFree(key_a); cudaFree(key_a2); cudaFree(key_b); cudaFree(key_b2); cudaFree(tot);
+    if (rc != GMC_OK) { free_plan(p); return rc; }
+    *out = p;
     return GMC_OK;
 }
 
-void free_shard(gmc_pr_shard* s) {
-    if (!s) return;
-    if (s->owns_csr) { cudaFree((void*)s->r_begin); cudaFree((void*)s->r_node_idx); }
-    cudaFree((void*)s->outdeg);
-    cudaFree(s->block_first_row); cudaFree(s->long_rows); cudaFree(s->long_chunk_begin);
-    cudaFree(s->long_partials); cudaFree(s->diff_parts);
-    cudaFree(s->peers[0]); cudaFree(s->peers[1]);
-    delete s;
+SweepArgs make_args(const gmc_pr_plan* p, double d, int parity, gmc_pr_ctrl* ctrl, double e, int32_t max_iter) {
+    SweepArgs A;
+    A.E = p->E; A.lbeg = p->lbeg; A.sbeg = p->sbeg; A.ltask_row = p->ltask_row; A.stask_slice = p->stask_slice; A.outdeg = p->outdeg;
+    A.N = p->N; A.n_long = p->n_long; A.hot_n = p->hot_n; A.EL = p->EL; A.n_ltasks = p->n_ltasks; A.n_stasks = p->n_stasks;
+    A.lt_lo = 0; A.lt_hi = p->n_ltasks; A.st_lo = 0; A.st_hi = p->n_stasks;
+    A.head_part = p->head_part; A.tail_part = p->tail_part; A.split_cnt = p->split_cnt; A.diff_parts = p->diff_parts;
+    A.contrib_in = p->contrib[parity]; A.contrib_out = p->contrib[parity ^ 1];
+    A.rank_in = p->rank[parity]; A.rank_out = p->rank[parity ^ 1];
+    A.d = d;
+    A.base = (1 - d) / (double)p->N;     // (1-d) / N, pagerank.gm:11
+    A.ctrl = ctrl; A.e = e; A.max_iter = max_iter;
+    return A;
+}
+
+int launch_init(const gmc_pr_plan* p, cudaStream_t st) {
+    SweepArgs A = make_args(p, 0.0, 0, nullptr, 0.0, 0);
+    k_init<<<div_up(p->N + 2, 256), 256, 0, st>>>(A, p->contrib[0], p->contrib[1], p->rank[0]);
+    GMC_CUDA(cudaGetLastError());
+    return GMC_OK;
+}
+
+int launch_sweep(const gmc_pr_plan* p, const SweepArgs& A, cudaStream_t st) {
+    pr_sweep<<<p->grid, PR_THREADS, p->smem, st>>>(A);
+    GMC_CUDA(cudaGetLastError());
+    return GMC_OK;
 }
 
 }  // namespace
 
 void gmc_pr_plan_free(gmc_graph* g) {
-    if (g->pr) { free_shard(g->pr); g->pr = nullptr; }
-    if (g->pr_buf) { cudaFree(g->pr_buf); g->pr_buf = nullptr; }
+    if (g->pr) { free_plan(g->pr); g->pr = nullptr; }
 }
 
 static int graph_plan(gmc_graph* g, cudaStream_t st) {
     if (g->pr) return GMC_OK;
     GMC_REQUIRE(g->has_reverse, GMC_ERR_STATE, "pagerank needs the reverse CSR: call gmc_graph_make_reverse first");
-    gmc_pr_shard* s = new gmc_pr_shard();
-    s->n_global = g->N; s->lo = 0; s->hi = g->N; s->nrows = g->N; s->nedges = g->M;
-    s->r_begin = g->r_begin; s->r_node_idx = g->r_node_idx; s->owns_csr = false;
-    int32_t* od = nullptr;
-    int rc = gmc_malloc((void**)&od, sizeof(int32_t) * (size_t)(g->N ? g->N : 1));
-    if (rc != GMC_OK) { delete s; return rc; }
-    if (g->N) compute_outdeg<<<div_up(g->N, 256), 256, 0, st>>>(g->begin, g->N, od);
-    s->outdeg = od;
-    rc = build_plan(s, st);
-    if (rc == GMC_OK) rc = gmc_malloc((void**)&g->pr_buf, sizeof(double) * 4 * (size_t)(g->N ? g->N : 1) + sizeof(gmc_pr_ctrl));
-    if (rc != GMC_OK) { free_shard(s); return rc; }
-    g->pr = s;
+    gmc_pr_plan* p = nullptr;
+    GMC_TRY(build_plan(g, &p, st));
+    g->pr = p;
     return GMC_OK;
 }
 
@@ -365,41 +628,38 @@ extern "C" {
 
 int gmc_pagerank_dev(gmc_graph* g, double e, double d, int32_t max_iter, double* rank_dev, gmc_pagerank_info* info, void* stream) {
     GMC_REQUIRE(g && rank_dev, GMC_ERR_ARG, "gmc_pagerank_dev: NULL");
+    GMC_REQUIRE(g->N > 0, GMC_ERR_ARG, "gmc_pagerank_dev: empty graph");
     cudaStream_t st = as_stream(stream);
     GMC_TRY(graph_plan(g, st));
-    gmc_pr_shard* s = g->pr;
-    const size_t n = (size_t)g->N;
-    const size_t nn = n ? n : 1;
-    double* contrib[2] = {g->pr_buf, g->pr_buf + nn};
-    double* rank[2] = {g->pr_buf + 2 * nn, g->pr_buf + 3 * nn};
-    gmc_pr_ctrl* ctrl = (gmc_pr_ctrl*)(g->pr_buf + 4 * nn);
-    GMC_CUDA(cudaMemsetAsync(ctrl, 0, sizeof(gmc_pr_ctrl), st));
+    gmc_pr_plan* p = g->pr;
+    GMC_CUDA(cudaMemsetAsync(p->ctrl, 0, sizeof(gmc_pr_ctrl), st));
     cudaEvent_t ev0, ev1;
     GMC_CUDA(cudaEventCreate(&ev0));
     GMC_CUDA(cudaEventCreate(&ev1));
     int launches = 0;
     GMC_CUDA(cudaEventRecord(ev0, st));
-    if (n) { pr_init<<<div_up((int32_t)n, 256), 256, 0, st>>>(g->N, 0, g->N, s->outdeg, contrib[0], rank[0]); launches++; }
+    GMC_TRY(launch_init(p, st));
+    launches++;
     // do { sweep; cnt++ } while (diff > e && cnt < max): sweeps are enqueued in batches; kernels of a
     // finished loop exit at once on ctrl->done, so the host only synchronises once per batch.
-    gmc_pr_ctrl h = {0.0, 0, 0};
+    gmc_pr_ctrl h;
+    memset(&h, 0, sizeof(h));
     int32_t issued = 0;
-    const int32_t BATCH = 16;
+    const int32_t BATCH = 32;
     do {
         int32_t todo = max_iter - issued;
         if (todo > BATCH) todo = BATCH;
         if (todo < 1) todo = 1;   // a do-while body runs at least once (max <= 0 still sweeps once)
         for (int32_t k = 0; k < todo; k++, issued++) {
-            int p = issued & 1;
-            GMC_TRY(launch_sweep(s, d, contrib[p], contrib[p ^ 1], rank[p], rank[p ^ 1], p, ctrl, st, &launches));
-            pr_reduce_diff<<<1, 1024, 0, st>>>(s->diff_parts, s->n_blocks + s->n_long, ctrl, e, max_iter, nullptr);
+            GMC_TRY(launch_sweep(p, make_args(p, d, issued & 1, p->ctrl, e, max_iter), st));
             launches++;
         }
-        GMC_CUDA(cudaMemcpyAsync(&h, ctrl, sizeof(h), cudaMemcpyDeviceToHost, st));
+        GMC_CUDA(cudaMemcpyAsync(&h, p->ctrl, sizeof(h), cudaMemcpyDeviceToHost, st));
         GMC_CUDA(cudaStreamSynchronize(st));
     } while (!h.done);
+    k_unpermute<<<div_up(g->N, 256), 256, 0, st>>>(p->rank[h.cnt & 1], p->new_of_old, g->N, rank_dev);
+    launches++;
     GMC_CUDA(cudaEventRecord(ev1, st));
-    if (n) GMC_CUDA(cudaMemcpyAsync(rank_dev, rank[h.cnt & 1], sizeof(double) * n, cudaMemcpyDeviceToDevice, st));
     GMC_CUDA(cudaStreamSynchronize(st));
     if (info) {
         info->iterations = h.cnt;
@@ -417,103 +677,42 @@ int gmc_pagerank_time_sweeps(gmc_graph* g, double d, int32_t warmup, int32_t n, 
     GMC_REQUIRE(g->N > 0, GMC_ERR_ARG, "gmc_pagerank_time_sweeps: empty graph");
     cudaStream_t st = as_stream(stream);
     GMC_TRY(graph_plan(g, st));
-    gmc_pr_shard* s = g->pr;
-    const size_t nn = (size_t)g->N;
-    double* contrib[2] = {g->pr_buf, g->pr_buf + nn};
-    double* rank[2] = {g->pr_buf + 2 * nn, g->pr_buf + 3 * nn};
-    pr_init<<<div_up(g->N, 256), 256, 0, st>>>(g->N, 0, g->N, s->outdeg, contrib[0], rank[0]);
+    gmc_pr_plan* p = g->pr;
+    GMC_TRY(launch_init(p, st));
     std::vector<cudaEvent_t> ev(2 * (size_t)n);
     for (auto& e : ev) GMC_CUDA(cudaEventCreate(&e));
-    int launches = 0;
     for (int32_t k = 0; k < warmup + n; k++) {
-        int p = k & 1;
-        launches = 0;
         if (k >= warmup) GMC_CUDA(cudaEventRecord(ev[2 * (k - warmup)], st));
-        GMC_TRY(launch_sweep(s, d, contrib[p], contrib[p ^ 1], rank[p], rank[p ^ 1], p, nullptr, st, &launches));
+        GMC_TRY(launch_sweep(p, make_args(p, d, k & 1, nullptr, 0.0, 0), st));
         if (k >= warmup) GMC_CUDA(cudaEventRecord(ev[2 * (k - warmup) + 1], st));
     }
     GMC_CUDA(cudaStreamSynchronize(st));
     for (int32_t k = 0; k < n; k++) GMC_CUDA(cudaEventElapsedTime(&ms_out[k], ev[2 * k], ev[2 * k + 1]));
     for (auto& e : ev) cudaEventDestroy(e);
-    if (launches_per_sweep) *launches_per_sweep = launches;
+    if (launches_per_sweep) *launches_per_sweep = 1;
     return GMC_OK;
 }
 
 int gmc_pagerank(gmc_graph* g, double e, double d, int32_t max_iter, double* rank_host, gmc_pagerank_info* info) {
     GMC_REQUIRE(g && (rank_host || g->N == 0), GMC_ERR_ARG, "gmc_pagerank: NULL");
+    if (g->N == 0) { if (info) memset(info, 0, sizeof(*info)); return GMC_OK; }
     double* tmp = nullptr;
-    GMC_TRY(gmc_malloc((void**)&tmp, sizeof(double) * (size_t)(g->N ? g->N : 1)));
+    GMC_TRY(gmc_malloc((void**)&tmp, sizeof(double) * (size_t)g->N));
     int rc = gmc_pagerank_dev(g, e, d, max_iter, tmp, info, nullptr);
     if (rc == GMC_OK) rc = gmc_d2h(rank_host, tmp, sizeof(double) * (size_t)g->N, nullptr);
     cudaFree(tmp);
     return rc;
 }
 
-// ---- destination-range shards (multi-GPU) -----------------------------------------------------
-int gmc_pr_shard_create(gmc_pr_shard** out, int32_t n_global, int32_t lo, int32_t hi, const int32_t* r_begin_slice,
-                        const int32_t* r_node_idx_slice, const int32_t* outdeg_slice) {
-    GMC_REQUIRE(out && r_begin_slice && outdeg_slice, GMC_ERR_ARG, "gmc_pr_shard_create: NULL");
-    GMC_REQUIRE(0 <= lo && lo <= hi && hi <= n_global, GMC_ERR_ARG, "gmc_pr_shard_create: bad range [%d,%d) of %d", lo, hi, n_global);
-    const int32_t nrows = hi - lo;
-    GMC_REQUIRE(r_begin_slice[0] == 0, GMC_ERR_ARG, "gmc_pr_shard_create: r_begin slice must be rebased to 0");
-    const int32_t ne = r_begin_slice[nrows];
-    GMC_REQUIRE(ne == 0 || r_node_idx_slice, GMC_ERR_ARG, "gmc_pr_shard_create: NULL r_node_idx");
-    gmc_pr_shard* s = new gmc_pr_shard();
-    s->n_global = n_global; s->lo = lo; s->hi = hi; s->nrows = nrows; s->nedges = ne; s->owns_csr = true;
-    int32_t *rb = nullptr, *ri = nullptr, *od = nullptr;
-    int rc = gmc_malloc((void**)&rb, sizeof(int32_t) * ((size_t)nrows + 1));
-    if (rc == GMC_OK) rc = gmc_malloc((void**)&ri, sizeof(int32_t) * (size_t)(ne ? ne : 1));
-    if (rc == GMC_OK) rc = gmc_malloc((void**)&od, sizeof(int32_t) * (size_t)(nrows ? nrows : 1));
-    s->r_begin = rb; s->r_node_idx = ri; s->outdeg = od;
-    if (rc == GMC_OK) rc = gmc_h2d(rb, r_begin_slice, sizeof(int32_t) * ((size_t)nrows + 1), nullptr);
-    if (rc == GMC_OK && ne) rc = gmc_h2d(ri, r_node_idx_slice, sizeof(int32_t) * (size_t)ne, nullptr);
-    if (rc == GMC_OK && nrows) rc = gmc_h2d(od, outdeg_slice, sizeof(int32_t) * (size_t)nrows, nullptr);
-    if (rc == GMC_OK && cudaDeviceSynchronize() != cudaSuccess) rc = GMC_ERR_CUDA;
-    if (rc == GMC_OK) rc = build_plan(s, nullptr);
-    if (rc != GMC_OK) { free_shard(s); return rc; }
-    *out = s;
-    return GMC_OK;
-}
-
-int gmc_pr_shard_destroy(gmc_pr_shard* s) { free_shard(s); return GMC_OK; }
-
-int gmc_pr_shard_set_peers(gmc_pr_shard* s, int n_peers, double* const* even, double* const* odd) {
-    GMC_REQUIRE(s && n_peers >= 0 && (n_peers == 0 || (even && odd)), GMC_ERR_ARG, "gmc_pr_shard_set_peers: bad args");
-    cudaFree(s->peers[0]); cudaFree(s->peers[1]);
-    s->peers[0] = s->peers[1] = nullptr;
-    s->n_peers = 0;
-    if (n_peers == 0) return GMC_OK;
-    GMC_TRY(gmc_malloc((void**)&s->peers[0], sizeof(double*) * n_peers));
-    GMC_TRY(gmc_malloc((void**)&s->peers[1], sizeof(double*) * n_peers));
-    GMC_CUDA(cudaMemcpy(s->peers[0], even, sizeof(double*) * n_peers, cudaMemcpyHostToDevice));
-    GMC_CUDA(cudaMemcpy(s->peers[1], odd, sizeof(double*) * n_peers, cudaMemcpyHostToDevice));
-    s->n_peers = n_peers;
-    return GMC_OK;
-}
-
-int gmc_pr_shard_init(gmc_pr_shard* s, double* contrib_full, double* rank_slice, void* stream) {
-    GMC_REQUIRE(s && contrib_full && rank_slice, GMC_ERR_ARG, "gmc_pr_shard_init: NULL");
-    if (s->nrows) pr_init<<<div_up(s->nrows, 256), 256, 0, as_stream(stream)>>>(s->n_global, s->lo, s->nrows, s->outdeg, contrib_full, rank_slice);
-    GMC_CUDA(cudaGetLastError());
-    return GMC_OK;
-}
-
-// parity selects which registered peer buffer set receives the slice (the one matching contrib_out)
-int gmc_pr_shard_sweep(gmc_pr_shard* s, double d, const double* contrib_in, double* contrib_out, const double* rank_in,
-                       double* rank_out, double* diff_part_dev, int parity, void* stream) {
-    GMC_REQUIRE(s && contrib_in && contrib_out && rank_in && rank_out, GMC_ERR_ARG, "gmc_pr_shard_sweep: NULL");
-    cudaStream_t st = as_stream(stream);
-    GMC_TRY(launch_sweep(s, d, contrib_in, contrib_out, rank_in, rank_out, parity, nullptr, st, nullptr));
-    if (diff_part_dev) {
-        pr_reduce_diff<<<1, 1024, 0, st>>>(s->diff_parts, s->n_blocks + s->n_long, nullptr, 0.0, 0, diff_part_dev);
-        GMC_CUDA(cudaGetLastError());
-    }
-    return GMC_OK;
-}
-
-int gmc_pr_shard_launches_per_sweep(const gmc_pr_shard* s, int32_t* n) {
-    GMC_REQUIRE(s && n, GMC_ERR_ARG, "NULL");
-    *n = (s->n_blocks > 0 ? 1 : 0) + (s->n_long > 0 ? 2 : 0) + 1;
+// layout facts of the plan, for tests and DESIGN.md tables
+int gmc_pagerank_plan_info(gmc_graph* g, gmc_pagerank_plan_info_t* out) {
+    GMC_REQUIRE(g && out, GMC_ERR_ARG, "gmc_pagerank_plan_info: NULL");
+    GMC_REQUIRE(g->N > 0, GMC_ERR_ARG, "gmc_pagerank_plan_info: empty graph");
+    GMC_TRY(graph_plan(g, nullptr));
+    gmc_pr_plan* p = g->pr;
+    out->n_long = p->n_long; out->hot_n = p->hot_n; out->n_slices = p->n_slices; out->long_entries = p->EL;
+    out->total_entries = p->EN; out->n_long_tasks = p->n_ltasks; out->n_short_tasks = p->n_stasks;
+    out->grid = p->grid; out->threads = PR_THREADS; out->smem_bytes = (int32_t)p->smem;
     return GMC_OK;
 }
 

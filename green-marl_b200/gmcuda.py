@@ -24,6 +24,11 @@ class BfsInfo(C.Structure):
                 ("kernel_ms", C.c_float), ("launches", C.c_int32), ("bottom_up_levels", C.c_int32)]
 
 
+class PlanInfo(C.Structure):
+    _fields_ = [(k, C.c_int32) for k in ("n_long", "hot_n", "n_slices", "long_entries", "total_entries", "n_long_tasks",
+                                         "n_short_tasks", "grid", "threads", "smem_bytes")]
+
+
 ARR = dict(begin=0, node_idx=1, r_begin=2, r_node_idx=3, e_rev2idx=4, e_idx2idx=5)
 _vp = C.c_void_p
 _i32 = C.c_int32
@@ -61,12 +66,7 @@ SIGNATURES = {
     "gmc_pagerank": (C.c_int, [_vp, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo)]),
     "gmc_pagerank_dev": (C.c_int, [_vp, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo), _vp]),
     "gmc_pagerank_time_sweeps": (C.c_int, [_vp, C.c_double, _i32, _i32, _vp, C.POINTER(_i32), _vp]),
-    "gmc_pr_shard_create": (C.c_int, [C.POINTER(_vp), _i32, _i32, _i32, _vp, _vp, _vp]),
-    "gmc_pr_shard_destroy": (C.c_int, [_vp]),
-    "gmc_pr_shard_set_peers": (C.c_int, [_vp, C.c_int, _vp, _vp]),
-    "gmc_pr_shard_init": (C.c_int, [_vp, _vp, _vp, _vp]),
-    "gmc_pr_shard_sweep": (C.c_int, [_vp, C.c_double, _vp, _vp, _vp, _vp, _vp, C.c_int, _vp]),
-    "gmc_pr_shard_launches_per_sweep": (C.c_int, [_vp, C.POINTER(_i32)]),
+    "gmc_pagerank_plan_info": (C.c_int, [_vp, C.POINTER(PlanInfo)]),
     "gmc_hop_dist": (C.c_int, [_vp, _i32, _vp, C.POINTER(BfsInfo)]),
     "gmc_hop_dist_dev": (C.c_int, [_vp, _i32, _vp, C.POINTER(BfsInfo), _vp]),
     "gmc_bfs_levels": (C.c_int, [_vp, _i32, C.c_int, _vp, _vp, _vp, _i32, C.POINTER(BfsInfo)]),
@@ -241,6 +241,11 @@ class Graph:
                                                    _vp(stream) if stream else None))
         return info
 
+    def pagerank_plan_info(self):
+        pi = PlanInfo()
+        self.lib.check(self.lib.L.gmc_pagerank_plan_info(self.h, C.byref(pi)))
+        return {k: getattr(pi, k) for k, _ in PlanInfo._fields_}
+
     def pagerank_time_sweeps(self, d=0.85, warmup=3, n=20, stream=None):
         ms = np.zeros(n, np.float32); lps = _i32()
         self.lib.check(self.lib.L.gmc_pagerank_time_sweeps(self.h, d, warmup, n, _ptr(ms), C.byref(lps),
@@ -272,43 +277,3 @@ class Graph:
         lb = np.zeros(n_levels + 1, np.int32)
         self.lib.check(self.lib.L.gmc_bfs_level_order(self.h, _ptr(order), _ptr(lb), n_levels + 1))
         return order[:lb[-1]], lb
-
-
-class PrShard:
-    """Destination-range shard of the PageRank sweep (multi-GPU building block)."""
-
-    def __init__(self, lib, n_global, lo, hi, r_begin_slice, r_node_idx_slice, outdeg_slice):
-        self.lib = lib
-        self.lo, self.hi, self.n_global = lo, hi, n_global
-        rb = _i32arr(r_begin_slice); ri = _i32arr(r_node_idx_slice); od = _i32arr(outdeg_slice)
-        h = _vp()
-        lib.check(lib.L.gmc_pr_shard_create(C.byref(h), n_global, lo, hi, _ptr(rb), _ptr(ri) if len(ri) else None, _ptr(od)))
-        self.h = h
-
-    def close(self):
-        if self.h:
-            self.lib.L.gmc_pr_shard_destroy(self.h)
-            self.h = None
-
-    def __del__(self):
-        try:
-            self.close()
-        except Exception:
-            pass
-
-    def set_peers(self, even_ptrs, odd_ptrs):
-        n = len(even_ptrs)
-        ev = (C.c_void_p * n)(*even_ptrs); od = (C.c_void_p * n)(*odd_ptrs)
-        self.lib.check(self.lib.L.gmc_pr_shard_set_peers(self.h, n, C.cast(ev, _vp), C.cast(od, _vp)))
-
-    def init(self, contrib_full_ptr, rank_slice_ptr, stream=None):
-        self.lib.check(self.lib.L.gmc_pr_shard_init(self.h, _vp(contrib_full_ptr), _vp(rank_slice_ptr), _vp(stream) if stream else None))
-
-    def sweep(self, d, contrib_in, contrib_out, rank_in, rank_out, diff_part=None, parity=0, stream=None):
-        self.lib.check(self.lib.L.gmc_pr_shard_sweep(self.h, d, _vp(contrib_in), _vp(contrib_out), _vp(rank_in), _vp(rank_out),
-                                                     _vp(diff_part) if diff_part else None, parity, _vp(stream) if stream else None))
-
-    def launches_per_sweep(self):
-        n = _i32()
-        self.lib.check(self.lib.L.gmc_pr_shard_launches_per_sweep(self.h, C.byref(n)))
-        return n.value

@@ -108,26 +108,17 @@ int gmc_pagerank_dev(gmc_graph* g, double e, double d, int32_t max_iter, double*
 int gmc_pagerank_time_sweeps(gmc_graph* g, double d, int32_t warmup, int32_t n, float* ms_out,
                              int32_t* launches_per_sweep, void* stream);
 
-/* --- PageRank over a destination-range shard (multi-GPU).  A shard owns rows [lo,hi) of
- * the reverse CSR (r_begin slice rebased to 0, global source ids) and the out-degrees of its own
- * vertices.  One sweep reads the FULL contribution vector contrib_in[N] (= rank[w]/outdeg[w]) and
- * writes contrib_out[lo..hi), rank_out[0..hi-lo) and *diff_part (device scalar).  The exchange of the
- * contrib slices between ranks is done by the caller (NCCL allgather) or by the sweep itself when
- * peer pointers are registered (gmc_pr_shard_set_peers): then each slice element is also stored into
- * every peer's contrib_out over NVLink from the kernel epilogue. */
-typedef struct gmc_pr_shard gmc_pr_shard;
-int gmc_pr_shard_create(gmc_pr_shard** out, int32_t num_nodes_global, int32_t lo, int32_t hi,
-                        const int32_t* r_begin_slice_host, const int32_t* r_node_idx_slice_host,
-                        const int32_t* out_degree_slice_host);
-int gmc_pr_shard_destroy(gmc_pr_shard* s);
-int gmc_pr_shard_set_peers(gmc_pr_shard* s, int n_peers, double* const* peer_contrib_even,
-                           double* const* peer_contrib_odd);
-/* contrib[lo..hi) = (1/N)/outdeg, rank[0..hi-lo) = 1/N */
-int gmc_pr_shard_init(gmc_pr_shard* s, double* contrib_full_dev, double* rank_slice_dev, void* stream);
-int gmc_pr_shard_sweep(gmc_pr_shard* s, double d, const double* contrib_in_full_dev,
-                       double* contrib_out_full_dev, const double* rank_in_slice_dev,
-                       double* rank_out_slice_dev, double* diff_part_dev, int parity, void* stream);
-int gmc_pr_shard_launches_per_sweep(const gmc_pr_shard* s, int32_t* n);
+/* layout facts of the PageRank plan (relabelled entry array, tasks), for tests and reports */
+typedef struct {
+    int32_t n_long;         /* rows with in-degree > 64 (row-major, padded to 4 entries) */
+    int32_t hot_n;          /* contributions staged in shared memory per CTA (dummy vertex included) */
+    int32_t n_slices;       /* sliced-ELL slices (32 rows each) of the rows with in-degree <= 64 */
+    int32_t long_entries;   /* entries of the long-row section (edges + padding) */
+    int32_t total_entries;  /* entries of the whole array */
+    int32_t n_long_tasks, n_short_tasks;
+    int32_t grid, threads, smem_bytes;
+} gmc_pagerank_plan_info_t;
+int gmc_pagerank_plan_info(gmc_graph* g, gmc_pagerank_plan_info_t* out);
 
 /* --- BFS.  One direction-optimizing, frontier-compacted engine behind both reference entry points:
  *  - generated hop_dist() (reference apps/src/hop_dist.gm:3-31): dist int32, INT_MAX = unreachable;
