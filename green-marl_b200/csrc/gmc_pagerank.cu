@@ -31,9 +31,11 @@
 //               of in-degree <= S_MAX is bit-identical to the CPU result given bit-identical inputs.
 // HBM traffic per sweep: 4 B/edge (index stream) + 40 B/vertex (row pointer amortised, old rank, new rank,
 // new contrib, out-degree, first touch of contrib); gathers are served by shared memory / L2.
+#define GMC_EXPERIMENT 1
 #include "gmc_common.cuh"
 #include <cub/device/device_radix_sort.cuh>
 #include <vector>
+#include <stdlib.h>
 
 using namespace gmc;
 
@@ -43,7 +45,12 @@ constexpr int S_MAX = 64;                 // rows up to this in-degree are summe
 constexpr int LT = 2048;                  // entries per long-row task (16 warp steps of 128)
 constexpr int ST_COST = 2048;             // cost units per short-row task (slice cost = 32*len + SLICE_OVH)
 constexpr int SLICE_OVH = 68;             // keeps a task at <= 31 slices
-constexpr int HOT_CAP = 28672;            // doubles of shared memory for the hot block (224 KB)
+constexpr int ZT = 2048;                  // ids per zero-in-degree task
+#ifndef GMC_HOT_CAP
+#define GMC_HOT_CAP 20480
+#endif
+constexpr int HOT_CAP = GMC_HOT_CAP;      // doubles of shared memory for the hot block (160 KB: the rest of the SM's
+                                          // 256 KB stays L1, whose capacity bounds the gathers in flight -- tools/ubench)
 constexpr unsigned FULL = 0xffffffffu;
 
 struct gmc_pr_ctrl {   // device-side loop control: lets the host enqueue sweeps without a sync per iteration
@@ -63,13 +70,13 @@ struct SweepArgs {
     const int32_t* __restrict__ stask_slice; // [n_stasks+1]
     const int32_t* __restrict__ outdeg;      // [N+1] by new id
     int32_t N, n_long, hot_n, EL;
-    int32_t n_ltasks, n_stasks;
-    int32_t lt_lo, lt_hi, st_lo, st_hi;      // task ranges executed by this launch (multi-GPU shards)
+    int32_t n_ltasks, n_stasks, n_ztasks, z0;  // z0 = first id without in-edges
+    int32_t lt_lo, lt_hi, st_lo, st_hi, zt_lo, zt_hi;   // task ranges executed by this launch (multi-GPU shards)
     // split rows
     double* head_part;                       // [n_ltasks]
     double* tail_part;                       // [n_ltasks]
     unsigned int* split_cnt;                 // [n_ltasks]
-    double* diff_parts;                      // [2*n_ltasks + n_stasks]
+    double* diff_parts;                      // [n_ltasks + n_stasks + n_ztasks + n_ltasks]
     // state
     const double* __restrict__ contrib_in;   // [N+2]
     double* contrib_out;
@@ -80,10 +87,11 @@ struct SweepArgs {
     gmc_pr_ctrl* ctrl;
     double e;
     int32_t max_iter;
+    int32_t mode;                            // experiment switches (GMC_EXPERIMENT builds only)
 };
 
 struct gmc_pr_plan {
-    int32_t N = 0, M = 0, n_long = 0, hot_n = 1, n_slices = 0, EL = 0, EN = 0, n_ltasks = 0, n_stasks = 0;
+    int32_t N = 0, M = 0, n_long = 0, n_pos = 0, hot_n = 1, n_slices = 0, nz_slices = 0, EL = 0, EN = 0, n_ltasks = 0, n_stasks = 0, n_ztasks = 0, z0 = 0;
     int32_t *new_of_old = nullptr, *old_of_new = nullptr, *E = nullptr, *lbeg = nullptr, *sbeg = nullptr;
     int32_t *ltask_row = nullptr, *stask_slice = nullptr, *outdeg = nullptr;
     double *head_part = nullptr, *tail_part = nullptr, *diff_parts = nullptr;
@@ -130,6 +138,9 @@ __device__ __forceinline__ double butterfly(double v) {
 // the sweep
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ double gather(const double* hot, const SweepArgs& A, int32_t w) {
+#ifdef GMC_EXPERIMENT
+    if (A.mode & 1) w &= 16383;
+#endif
     return (w < A.hot_n) ? hot[w] : __ldg(A.contrib_in + w);
 }
 
@@ -182,6 +193,12 @@ __device__ __forceinline__ void long_task(const SweepArgs& A, const double* hot,
     const int32_t a = __ldg(A.ltask_row + t);                     // row (0-based; id = row + 1) holding entry x0
     const int32_t e = (a + lane < A.n_long) ? __ldg(A.lbeg + a + lane + 1) : INT32_MAX;   // end of row a+lane
     const int32_t rb0 = __ldg(A.lbeg + a);
+    const int4* __restrict__ E4 = reinterpret_cast<const int4*>(A.E + x0);
+    const int32_t span = x1 - x0;
+    const int nst = (span + 127) >> 7;
+    const int4 zero4 = make_int4(0, 0, 0, 0);
+    int4 nx0 = (4 * lane < span) ? ld_idx4(E4 + lane) : zero4;
+    int4 nx1 = (128 + 4 * lane < span) ? ld_idx4(E4 + 32 + lane) : zero4;
     const bool head_split = rb0 < x0;
     const int kl = row_search(e, x1 - 1);                          // last row of the task (relative)
     const int32_t e_kl = __shfl_sync(FULL, e, kl);
@@ -189,21 +206,14 @@ __device__ __forceinline__ void long_task(const SweepArgs& A, const double* hot,
 
     double acc = 0.0, my_sum = 0.0, head_acc = 0.0, tail_acc = 0.0;
     int acc_row = -1;
-    const int4* __restrict__ E4 = reinterpret_cast<const int4*>(A.E + x0);
-    const int32_t span = x1 - x0;
-    const int nst = (span + 127) >> 7;
-    const int4 zero4 = make_int4(0, 0, 0, 0);
-    int4 nx0 = (4 * lane < span) ? ld_idx4(E4 + lane) : zero4;
-    int4 nx1 = (128 + 4 * lane < span) ? ld_idx4(E4 + 32 + lane) : zero4;
+    int32_t row_end = INT32_MIN;        // end of the lane's current row: forces a search at its first step
 
-    auto emit = [&](int row, bool in) {
-        // lanes whose entries moved on to a later row hand their finished row to the warp
-        const bool changed = in && row != acc_row && acc_row >= 0;
-        unsigned m = __ballot_sync(FULL, changed);
+    // hand the finished rows of the lanes in `who` to the warp: one butterfly per distinct row
+    auto hand_over = [&](bool who) {
+        unsigned m = __ballot_sync(FULL, who);
         while (m) {
-            const int leader = __ffs(m) - 1;
-            const int R = __shfl_sync(FULL, acc_row, leader);
-            const bool mem = changed && acc_row == R;
+            const int R = __shfl_sync(FULL, acc_row, __ffs(m) - 1);
+            const bool mem = who && acc_row == R;
             const unsigned mm = __ballot_sync(FULL, mem);
             const double tot = butterfly(mem ? acc : 0.0);
             if (R == 0 && head_split) head_acc += tot;
@@ -211,7 +221,21 @@ __device__ __forceinline__ void long_task(const SweepArgs& A, const double* hot,
             else if (lane == R) my_sum += tot;
             m &= ~mm;
         }
-        if (in && row != acc_row) { acc_row = row; acc = 0.0; }
+    };
+    // a lane's 4 entries lie in one row (rows are padded to 4); rows change rarely, so the row lookup
+    // (5 shuffles) only runs in steps where some lane has run past the end of its row
+    auto step = [&](int32_t o, bool in, double p) {
+        bool cross = in && o >= row_end;
+#ifdef GMC_EXPERIMENT
+        if ((A.mode & 4) && acc_row >= 0) cross = false;
+#endif
+        if (__any_sync(FULL, cross)) {
+            const int row = row_search(e, o);
+            hand_over(cross && acc_row >= 0);
+            const int32_t re = __shfl_sync(FULL, e, row);
+            if (cross) { acc_row = row; row_end = re; acc = 0.0; }
+        }
+        acc += p;
     };
 
     for (int i = 0; i < nst; i += 2) {
@@ -221,69 +245,106 @@ __device__ __forceinline__ void long_task(const SweepArgs& A, const double* hot,
         nx1 = (o1 + 256 < span) ? ld_idx4(E4 + (i + 3) * 32 + lane) : zero4;
         const double v0 = gather(hot, A, c0.x), v1 = gather(hot, A, c0.y), v2 = gather(hot, A, c0.z), v3 = gather(hot, A, c0.w);
         const double v4 = gather(hot, A, c1.x), v5 = gather(hot, A, c1.y), v6 = gather(hot, A, c1.z), v7 = gather(hot, A, c1.w);
-        const bool in0 = o0 < span, in1 = o1 < span;
-        const int r0 = row_search(e, x0 + o0), r1 = row_search(e, x0 + o1);
-        emit(r0, in0);
-        acc += (v0 + v1) + (v2 + v3);
-        emit(r1, in1);
-        acc += (v4 + v5) + (v6 + v7);
+        step(x0 + o0, o0 < span, (v0 + v1) + (v2 + v3));
+        step(x0 + o1, o1 < span, (v4 + v5) + (v6 + v7));
     }
-    {   // final flush: every lane hands over what it still holds
-        const bool have = acc_row >= 0;
-        unsigned m = __ballot_sync(FULL, have);
-        while (m) {
-            const int leader = __ffs(m) - 1;
-            const int R = __shfl_sync(FULL, acc_row, leader);
-            const bool mem = have && acc_row == R;
-            const unsigned mm = __ballot_sync(FULL, mem);
-            const double tot = butterfly(mem ? acc : 0.0);
-            if (R == 0 && head_split) head_acc += tot;
-            else if (R == kl && tail_split) tail_acc += tot;
-            else if (lane == R) my_sum += tot;
-            m &= ~mm;
-        }
-    }
+    hand_over(acc_row >= 0);
     // rows that lie completely inside the task: one lane per row, coalesced epilogue
     const int k_first = head_split ? 1 : 0;
     const int k_last = tail_split ? kl - 1 : kl;
     double diff = 0.0;
     if (lane >= k_first && lane <= k_last) diff = finish_row(A, a + lane + 1, my_sum);
     diff = butterfly(diff);
-    if (lane == 0) { A.diff_parts[t] = diff; __threadfence(); }
-    const int32_t n_tasks_total = A.n_ltasks + A.n_stasks;
+    if (lane == 0) A.diff_parts[t] = diff;
+    const int32_t split_base = A.n_ltasks + A.n_stasks + A.n_ztasks;
     if (head_split) {
         const int32_t e0 = __shfl_sync(FULL, e, 0);
-        split_arrive(A, lane, rb0 / LT, (e0 - 1) / LT, a, head_acc, A.head_part + t, n_tasks_total);
+        split_arrive(A, lane, rb0 / LT, (e0 - 1) / LT, a, head_acc, A.head_part + t, split_base);
     }
     if (tail_split && !(kl == 0 && head_split))
-        split_arrive(A, lane, t, (e_kl - 1) / LT, a + kl, tail_acc, A.tail_part + t, n_tasks_total);
+        split_arrive(A, lane, t, (e_kl - 1) / LT, a + kl, tail_acc, A.tail_part + t, split_base);
 }
 
+// rows with 1..S_MAX in-edges: one lane per row, terms added strictly left to right.  The loop runs over
+// 8-column chunks; the indices of the next chunk (of this slice or the next one) are always in flight.
 __device__ __forceinline__ void short_task(const SweepArgs& A, const double* hot, int lane, int32_t u) {
     const int32_t s_lo = __ldg(A.stask_slice + u), s_hi = __ldg(A.stask_slice + u + 1);
     const int ns = s_hi - s_lo;                                  // <= 31
     const int32_t sb = (lane <= ns) ? __ldg(A.sbeg + s_lo + lane) : 0;
     double diff = 0.0;
-    for (int q = 0; q < ns; q++) {
-        const int32_t base = __shfl_sync(FULL, sb, q);
-        const int L = (__shfl_sync(FULL, sb, q + 1) - base) >> 5;
+    if (ns <= 0) { if (lane == 0) A.diff_parts[A.n_ltasks + u] = 0.0; return; }
+    int q = 0, j = 0;
+    int32_t base = __shfl_sync(FULL, sb, 0);
+    int L = (__shfl_sync(FULL, sb, 1) - base) >> 5;
+    int32_t w[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) w[k] = (k < L) ? __ldcs(A.E + base + lane + k * 32) : 0;
+    double S = 0.0, old = 0.0;
+    int32_t od = 0;
+    while (q < ns) {
         const int32_t id = A.n_long + 1 + (s_lo + q) * 32 + lane;
-        const int32_t* __restrict__ p = A.E + base + lane;
-        double S = 0.0;
-        for (int j = 0; j < L; j += 8) {
-            int32_t w[8];
-            double v[8];
-#pragma unroll
-            for (int k = 0; k < 8; k++) w[k] = (j + k < L) ? __ldcs(p + (j + k) * 32) : 0;
-#pragma unroll
-            for (int k = 0; k < 8; k++) v[k] = gather(hot, A, w[k]);
-#pragma unroll
-            for (int k = 0; k < 8; k++) S = S + v[k];              // left to right: the reference's order (+0.0 for padding)
+        if (j == 0 && id <= A.N) { old = __ldcs(A.rank_in + id); od = __ldcs(A.outdeg + id); }
+        // where the next chunk lives
+        int nq = q, nj = j + 8;
+        int32_t nbase = base;
+        int nL = L;
+        if (nj >= L) {
+            nq = q + 1; nj = 0;
+            nbase = __shfl_sync(FULL, sb, nq < ns ? nq : 0);
+            nL = nq < ns ? (__shfl_sync(FULL, sb, nq + 1 <= ns ? nq + 1 : 0) - nbase) >> 5 : 0;
         }
-        if (id <= A.N) diff += finish_row(A, id, S);
+        int32_t wn[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) wn[k] = (nj + k < nL) ? __ldcs(A.E + nbase + lane + (nj + k) * 32) : 0;
+        double v[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) v[k] = gather(hot, A, w[k]);
+#pragma unroll
+        for (int k = 0; k < 8; k++) S = S + v[k];                 // left to right: the reference's order (+0.0 for padding)
+        if (nj == 0) {                                            // slice finished
+            if (id <= A.N) {
+                const double val = __dadd_rn(A.base, __dmul_rn(A.d, S));
+                __stcs(A.rank_out + id, val);
+                A.contrib_out[id] = od > 0 ? val / (double)od : 0.0;
+                diff += fabs(__dsub_rn(val, old));
+            }
+            S = 0.0;
+        }
+#pragma unroll
+        for (int k = 0; k < 8; k++) w[k] = wn[k];
+        q = nq; j = nj; base = nbase; L = nL;
     }
     diff = butterfly(diff);
-    if (lane == 0) { A.diff_parts[A.n_ltasks + u] = diff; __threadfence(); }
+    if (lane == 0) A.diff_parts[A.n_ltasks + u] = diff;
+}
+
+// rows without in-edges (the tail of the id space): val = (1-d)/N, a pure streaming update
+__device__ __forceinline__ void zero_task(const SweepArgs& A, int lane, int32_t z) {
+    const int32_t id0 = A.z0 + z * ZT;
+    double diff = 0.0;
+#pragma unroll 1
+    for (int b = 0; b < ZT; b += 256) {
+        double old[8];
+        int32_t od[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const int32_t id = id0 + b + k * 32 + lane;
+            old[k] = id <= A.N ? __ldcs(A.rank_in + id) : 0.0;
+            od[k] = id <= A.N ? __ldcs(A.outdeg + id) : 0;
+        }
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const int32_t id = id0 + b + k * 32 + lane;
+            if (id <= A.N) {
+                const double val = A.base;                       // (1-d)/N + d*0
+                __stcs(A.rank_out + id, val);
+                A.contrib_out[id] = od[k] > 0 ? val / (double)od[k] : 0.0;
+                diff += fabs(__dsub_rn(val, old[k]));
+            }
+        }
+    }
+    diff = butterfly(diff);
+    if (lane == 0) A.diff_parts[A.n_ltasks + A.n_stasks + z] = diff;
 }
 
 __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
@@ -307,11 +368,12 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
     mbar_wait(&bar, 0);
 
     // tasks: static round-robin over all warps of the grid, long-row tasks first
-    const int32_t n_l = A.lt_hi - A.lt_lo, n_s = A.st_hi - A.st_lo;
+    const int32_t n_l = A.lt_hi - A.lt_lo, n_s = A.st_hi - A.st_lo, n_z = A.zt_hi - A.zt_lo;
     const int32_t stride = gridDim.x * PR_WARPS;
-    for (int32_t u = blockIdx.x * PR_WARPS + warp; u < n_l + n_s; u += stride) {
+    for (int32_t u = blockIdx.x * PR_WARPS + warp; u < n_l + n_s + n_z; u += stride) {
         if (u < n_l) long_task(A, hot, lane, A.lt_lo + u);
-        else short_task(A, hot, lane, A.st_lo + (u - n_l));
+        else if (u < n_l + n_s) short_task(A, hot, lane, A.st_lo + (u - n_l));
+        else zero_task(A, lane, A.zt_lo + (u - n_l - n_s));
     }
 
     if (!A.ctrl) return;
@@ -324,7 +386,7 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
     __syncthreads();
     if (!s_last) return;
     __threadfence();
-    const int32_t nparts = 2 * A.n_ltasks + A.n_stasks;
+    const int32_t nparts = 2 * A.n_ltasks + A.n_stasks + A.n_ztasks;
     double v = 0.0;
     for (int32_t i = tid; i < nparts; i += PR_THREADS) v += __ldcg(A.diff_parts + i);
     v = butterfly(v);
@@ -347,7 +409,7 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
 // ---------------------------------------------------------------------------------------------
 __global__ void k_degrees(const int32_t* __restrict__ begin, const int32_t* __restrict__ r_begin, int32_t n,
                           int32_t* __restrict__ outdeg, int32_t* __restrict__ indeg, uint32_t* __restrict__ key_a,
-                          int32_t* __restrict__ ids, int32_t* __restrict__ is_long) {
+                          int32_t* __restrict__ ids, int32_t* __restrict__ is_long, int32_t* __restrict__ is_pos) {
     int32_t v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v >= n) return;
     const int32_t od = begin[v + 1] - begin[v], id = r_begin[v + 1] - r_begin[v];
@@ -355,6 +417,7 @@ __global__ void k_degrees(const int32_t* __restrict__ begin, const int32_t* __re
     indeg[v] = id;
     const bool lg = id > S_MAX;
     is_long[v] = lg;
+    is_pos[v] = id > 0;
     key_a[v] = lg ? (uint32_t)(0x7fffffff - od) : 0xffffffffu;    // long rows by out-degree descending, short rows last
     ids[v] = v;
 }
@@ -398,7 +461,7 @@ __global__ void k_lengths(const int32_t* __restrict__ old_of_new, const int32_t*
     else if (((j - n_long) & 31) == 0) {
         const int32_t s = (j - n_long) >> 5;
         sbeg[s] = 32 * len;                                 // first row of the slice is its longest
-        scost[s] = 32 * len + SLICE_OVH;
+        scost[s] = len > 0 ? 32 * len + SLICE_OVH : 0;          // empty slices belong to the zero tasks
     }
 }
 __global__ void k_add_offset(int32_t* __restrict__ a, int32_t n, const int32_t* __restrict__ off) {
@@ -493,7 +556,7 @@ int build_plan(gmc_graph* g, gmc_pr_plan** out, cudaStream_t st) {
     gmc_pr_plan* p = new gmc_pr_plan();
     p->N = n; p->M = m;
     int rc = GMC_OK;
-    int32_t *outdeg_old = nullptr, *indeg = nullptr, *ids = nullptr, *ids2 = nullptr, *is_long = nullptr, *hot_rank = nullptr, *scost = nullptr;
+    int32_t *outdeg_old = nullptr, *indeg = nullptr, *ids = nullptr, *ids2 = nullptr, *is_long = nullptr, *is_pos = nullptr, *hot_rank = nullptr, *scost = nullptr;
     uint32_t *key_a = nullptr, *key_a2 = nullptr;
     unsigned long long *key_b = nullptr, *key_b2 = nullptr;
     int32_t* tot = nullptr;
@@ -505,6 +568,7 @@ int build_plan(gmc_graph* g, gmc_pr_plan** out, cudaStream_t st) {
     PLAN_TRY(gmc_malloc((void**)&outdeg_old, 4 * nn)); PLAN_TRY(gmc_malloc((void**)&indeg, 4 * nn));
     PLAN_TRY(gmc_malloc((void**)&ids, 4 * nn)); PLAN_TRY(gmc_malloc((void**)&ids2, 4 * nn));
     PLAN_TRY(gmc_malloc((void**)&is_long, 4 * nn)); PLAN_TRY(gmc_malloc((void**)&hot_rank, 4 * nn));
+    PLAN_TRY(gmc_malloc((void**)&is_pos, 4 * nn));
     PLAN_TRY(gmc_malloc((void**)&key_a, 4 * nn)); PLAN_TRY(gmc_malloc((void**)&key_a2, 4 * nn));
     PLAN_TRY(gmc_malloc((void**)&key_b, 8 * nn)); PLAN_TRY(gmc_malloc((void**)&key_b2, 8 * nn));
     PLAN_TRY(gmc_malloc((void**)&tot, 16));
@@ -512,10 +576,12 @@ int build_plan(gmc_graph* g, gmc_pr_plan** out, cudaStream_t st) {
     PLAN_TRY(gmc_malloc((void**)&p->outdeg, 4 * (nn + 1)));
 
     // 1. degrees, number of long rows, the hot block
-    k_degrees<<<gb, 256, 0, st>>>(g->begin, g->r_begin, n, outdeg_old, indeg, key_a, ids, is_long);
+    k_degrees<<<gb, 256, 0, st>>>(g->begin, g->r_begin, n, outdeg_old, indeg, key_a, ids, is_long, is_pos);
     PLAN_TRY(exclusive_scan_i32(is_long, is_long, nn, tot, st));
-    if (cudaMemcpyAsync(h, tot, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) { rc = GMC_ERR_CUDA; set_error("plan: %s", cudaGetErrorString(cudaGetLastError())); goto fail; }
+    PLAN_TRY(exclusive_scan_i32(is_pos, is_pos, nn, tot + 1, st));
+    if (cudaMemcpyAsync(h, tot, 8, cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) { rc = GMC_ERR_CUDA; set_error("plan: %s", cudaGetErrorString(cudaGetLastError())); goto fail; }
     p->n_long = h[0];
+    p->n_pos = h[1];
     {
         const int32_t hot_ids = p->n_long < HOT_CAP - 2 ? p->n_long : HOT_CAP - 2;
         p->hot_n = hot_ids + 1;                             // ids [0, hot_n): the dummy + the hot block
@@ -527,6 +593,9 @@ int build_plan(gmc_graph* g, gmc_pr_plan** out, cudaStream_t st) {
     }
     // 2. row offsets of both sections
     p->n_slices = div_up(n - p->n_long, 32);
+    p->nz_slices = p->n_pos > p->n_long ? div_up(p->n_pos - p->n_long, 32) : 0;     // slices holding a row with in-edges
+    p->z0 = p->n_long + 1 + 32 * p->nz_slices;
+    p->n_ztasks = p->z0 <= n ? div_up(n - p->z0 + 1, ZT) : 0;
     PLAN_TRY(gmc_malloc((void**)&p->lbeg, 4 * ((size_t)p->n_long + 1)));
     PLAN_TRY(gmc_malloc((void**)&p->sbeg, 4 * ((size_t)p->n_slices + 1)));
     PLAN_TRY(gmc_malloc((void**)&scost, 4 * ((size_t)p->n_slices + 1)));
@@ -556,9 +625,9 @@ int build_plan(gmc_graph* g, gmc_pr_plan** out, cudaStream_t st) {
     PLAN_TRY(gmc_malloc((void**)&p->ltask_row, 4 * ((size_t)p->n_ltasks + 1)));
     PLAN_TRY(gmc_malloc((void**)&p->stask_slice, 4 * ((size_t)p->n_stasks + 1)));
     k_ltask_rows<<<div_up(p->n_ltasks + 1, 256), 256, 0, st>>>(p->lbeg, p->n_long, p->n_ltasks, p->ltask_row);
-    k_stask_slices<<<div_up(p->n_stasks + 1, 256), 256, 0, st>>>(scost, p->n_slices, p->n_stasks, p->stask_slice);
+    k_stask_slices<<<div_up(p->n_stasks + 1, 256), 256, 0, st>>>(scost, p->nz_slices, p->n_stasks, p->stask_slice);
     {
-        const size_t nl = (size_t)(p->n_ltasks ? p->n_ltasks : 1), nparts = 2 * nl + (size_t)p->n_stasks + 1;
+        const size_t nl = (size_t)(p->n_ltasks ? p->n_ltasks : 1), nparts = 2 * nl + (size_t)p->n_stasks + (size_t)p->n_ztasks + 1;
         PLAN_TRY(gmc_malloc((void**)&p->head_part, 8 * nl)); PLAN_TRY(gmc_malloc((void**)&p->tail_part, 8 * nl));
         PLAN_TRY(gmc_malloc((void**)&p->split_cnt, 4 * nl)); PLAN_TRY(gmc_malloc((void**)&p->diff_parts, 8 * nparts));
         cudaMemsetAsync(p->head_part, 0, 8 * nl, st); cudaMemsetAsync(p->tail_part, 0, 8 * nl, st);
@@ -575,7 +644,7 @@ int build_plan(gmc_graph* g, gmc_pr_plan** out, cudaStream_t st) {
     if (cudaFuncSetAttribute(pr_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem) != cudaSuccess ||
         cudaStreamSynchronize(st) != cudaSuccess) { rc = GMC_ERR_CUDA; set_error("pagerank plan: %s", cudaGetErrorString(cudaGetLastError())); goto fail; }
 fail:
-    cudaFree(outdeg_old); cudaFree(indeg); cudaFree(ids); cudaFree(ids2); cudaFree(is_long); cudaFree(hot_rank); cudaFree(scost);
+    cudaFree(outdeg_old); cudaFree(indeg); cudaFree(ids); cudaFree(ids2); cudaFree(is_long); cudaFree(is_pos); cudaFree(hot_rank); cudaFree(scost);
     cudaFree(key_a); cudaFree(key_a2); cudaFree(key_b); cudaFree(key_b2); cudaFree(tot);
     if (rc != GMC_OK) { free_plan(p); return rc; }
     *out = p;
@@ -586,13 +655,14 @@ SweepArgs make_args(const gmc_pr_plan* p, double d, int parity, gmc_pr_ctrl* ctr
     SweepArgs A;
     A.E = p->E; A.lbeg = p->lbeg; A.sbeg = p->sbeg; A.ltask_row = p->ltask_row; A.stask_slice = p->stask_slice; A.outdeg = p->outdeg;
     A.N = p->N; A.n_long = p->n_long; A.hot_n = p->hot_n; A.EL = p->EL; A.n_ltasks = p->n_ltasks; A.n_stasks = p->n_stasks;
-    A.lt_lo = 0; A.lt_hi = p->n_ltasks; A.st_lo = 0; A.st_hi = p->n_stasks;
+    A.n_ztasks = p->n_ztasks; A.z0 = p->z0;
+    A.lt_lo = 0; A.lt_hi = p->n_ltasks; A.st_lo = 0; A.st_hi = p->n_stasks; A.zt_lo = 0; A.zt_hi = p->n_ztasks;
     A.head_part = p->head_part; A.tail_part = p->tail_part; A.split_cnt = p->split_cnt; A.diff_parts = p->diff_parts;
     A.contrib_in = p->contrib[parity]; A.contrib_out = p->contrib[parity ^ 1];
     A.rank_in = p->rank[parity]; A.rank_out = p->rank[parity ^ 1];
     A.d = d;
     A.base = (1 - d) / (double)p->N;     // (1-d) / N, pagerank.gm:11
-    A.ctrl = ctrl; A.e = e; A.max_iter = max_iter;
+    A.ctrl = ctrl; A.e = e; A.max_iter = max_iter; A.mode = 0;
     return A;
 }
 
@@ -683,7 +753,14 @@ int gmc_pagerank_time_sweeps(gmc_graph* g, double d, int32_t warmup, int32_t n, 
     for (auto& e : ev) GMC_CUDA(cudaEventCreate(&e));
     for (int32_t k = 0; k < warmup + n; k++) {
         if (k >= warmup) GMC_CUDA(cudaEventRecord(ev[2 * (k - warmup)], st));
-        GMC_TRY(launch_sweep(p, make_args(p, d, k & 1, nullptr, 0.0, 0), st));
+        SweepArgs A = make_args(p, d, k & 1, nullptr, 0.0, 0);
+        if (const char* md = getenv("GMC_PR_MODE")) { A.mode = atoi(md); if (A.mode & 2) A.hot_n = 1; }
+        if (const char* only = getenv("GMC_PR_ONLY")) {      // experiment switch: time one task class alone (results invalid)
+            if (strcmp(only, "long") != 0) A.lt_hi = 0;
+            if (strcmp(only, "short") != 0) A.st_hi = 0;
+            if (strcmp(only, "zero") != 0) A.zt_hi = 0;
+        }
+        GMC_TRY(launch_sweep(p, A, st));
         if (k >= warmup) GMC_CUDA(cudaEventRecord(ev[2 * (k - warmup) + 1], st));
     }
     GMC_CUDA(cudaStreamSynchronize(st));
