@@ -167,6 +167,11 @@ def run_reference_arm(args, n, m):
     from oracle_lib import Oracle, Ref, have_ref
     threads = os.cpu_count() or 1
     iters = args.cpu_iters
+    full_n, full_m = n, m
+    scale = 1
+    if m > 100_000_000:      # bounded sample: the serial reference generator needs ~0.75 s per million edges
+        scale = -(-m // 92_000_000)
+        n, m = n // scale, m // scale
     t0 = time.perf_counter()
     if have_ref():
         ref = Ref(); ref.set_threads(threads)
@@ -196,11 +201,14 @@ def run_reference_arm(args, n, m):
     ms = sum(times) / len(times)
     v = m * iters / ms / 1e6
     sample = f"{iters} of {args.iters} sweeps per step, same graph shape, all {threads} host threads (OpenMP dynamic,128)"
+    if scale > 1:
+        sample += f"; graph scaled 1/{scale} (N={n}, M={m}, same a/b/c and average degree) to bound the serial generator's time"
     line = {
         "impl": "reference", "metric": "pagerank_gteps", "value": v, "unit": "GTEPS", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(args, n, m), "nodes": n, "edges": m, "iterations_per_step": iters,
+        "config": {"workload": workload_name(args, full_n, full_m), "nodes": full_n, "edges": full_m, "sample_nodes": n, "sample_edges": m,
+                   "iterations_per_step": iters,
                    "graph": "reference create_RMAT_graph seed 1997 a=.57 b=.19 c=.19 permuted", "generate_s": round(gen_s, 1)},
         "cpu_baseline": {"value": v, "unit": "GTEPS", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "GTEPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -208,8 +216,8 @@ def run_reference_arm(args, n, m):
     print(json.dumps(line), flush=True)
 
 
-def workload_name(args, n, m):
-    return f"pagerank {args.iters} sweeps, R-MAT {args.workload}-shaped N={n} M={m}, int32 ids, fp64 ranks, d=0.85, e=1e-30"
+def workload_name(args, n, m, workload=None):
+    return f"pagerank {args.iters} sweeps, R-MAT {workload or args.workload}-shaped N={n} M={m}, int32 ids, fp64 ranks, d=0.85, e=1e-30"
 
 
 # --------------------------------------------------------------------------------------------------
@@ -358,21 +366,29 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="lj", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS),
+                    help="default: lj on 1 GPU (BASELINE configs[1]), tw on 2/4/8 GPUs (configs[3])")
+    ap.add_argument("--nodes", type=int, default=None, help="override the workload's vertex count (experiments)")
+    ap.add_argument("--edges", type=int, default=None, help="override the workload's edge count (experiments)")
+    ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--iters", type=int, default=20, help="pull sweeps per pagerank() call (BASELINE configs: 20)")
     ap.add_argument("--cpu-iters", type=int, default=5, help="sweeps per CPU-reference sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3        # timing rule: at least 3 warm-up steps
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    multi = world > 1 or args.gpus > 1
+    if args.workload is None:
+        args.workload = "tw" if multi else "lj"
     n, m = WORKLOADS[args.workload]
+    n, m = args.nodes or n, args.edges or m
     if args.impl == "reference":
         run_reference_arm(args, n, m)
         return
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    if world > 1 or args.gpus > 1:
+    if multi:
         from bench_multi import run_multi
-        run_multi(args, n, m)
+        run_multi(args, n, m, args.workload)
     else:
         run_single(args, n, m)
 

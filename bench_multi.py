@@ -1,0 +1,183 @@
+"""bench.py --gpus N (N > 1): one process per GPU (torch.distributed.run), destination-range shards.
+
+Every rank builds the same synthetic graph with the deterministic device generator (counter-based RNG), plans
+its own shard of the PageRank entry array, and the ranks exchange the new contributions with NCCL after every
+sweep (BASELINE.json configs[3]: the Twitter-shaped R-MAT graph on 2/4/8 B200).  torch.distributed
+is used for the bootstrap (shipping the 128-byte NCCL id), the barriers around the timed region and the
+max-over-ranks reduction of the device times -- not for the data path, which is libgm_cuda's own communicator.
+"""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+
+
+def bootstrap_comm(lib, dist, torch, rank, world):
+    """rank 0 makes the NCCL unique id, everybody receives its 128 bytes, every rank joins (gmc_comm_create)"""
+    uid = torch.from_numpy(lib.comm_unique_id() if rank == 0 else np.zeros(128, np.uint8))
+    if dist.get_backend() == "nccl":
+        t = uid.cuda()
+        dist.broadcast(t, 0)
+        uid = t.cpu()
+    else:
+        dist.broadcast(uid, 0)
+    return lib.comm_create(world, rank, uid.numpy())
+
+
+def max_over_ranks(dist, torch, value):
+    """the slowest rank's device time is the job's time"""
+    t = torch.tensor([float(value)], dtype=torch.float64)
+    if dist.get_backend() == "nccl":
+        t = t.cuda()
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def sum_over_ranks(dist, torch, value):
+    t = torch.tensor([float(value)], dtype=torch.float64)
+    if dist.get_backend() == "nccl":
+        t = t.cuda()
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
+
+
+def run_multi(args, n, m, workload):
+    import torch
+    import torch.distributed as dist
+    from bench import RMAT, ClockSampler, alg_bytes_pagerank, measured_peak_gbs, workload_name
+    from gmb200_loader import load_package
+    rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+    if world == 1 and args.gpus > 1:
+        raise SystemExit("bench.py --gpus N with N > 1 must be launched with torch.distributed.run (one process per GPU)")
+    lib = load_package().GmCuda()
+    lib.init(local)
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    comm = bootstrap_comm(lib, dist, torch, rank, world)
+    iters = args.iters
+
+    t0 = time.perf_counter()
+    g = lib.generate_rmat(n, m, RMAT["seed"], RMAT["a"], RMAT["b"], RMAT["c"], RMAT["permute"])
+    lib.sync()
+    gen_s = time.perf_counter() - t0
+    stream = torch.cuda.Stream()
+    sp = stream.cuda_stream
+    rank_dev = torch.empty(n, dtype=torch.float64, device="cuda")
+    t0 = time.perf_counter()
+    for _ in range(args.warmup):
+        g.pagerank_sharded_dev(comm, rank_dev.data_ptr(), 1e-30, 0.85, iters, stream=sp)
+    torch.cuda.synchronize()
+    warm_s = time.perf_counter() - t0
+
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+        time.sleep(0.25)
+    launches = 0
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    dist.barrier(); torch.cuda.synchronize()
+    w0 = time.time()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        info = g.pagerank_sharded_dev(comm, rank_dev.data_ptr(), 1e-30, 0.85, iters, stream=sp)
+        launches += info.launches
+        assert info.iterations == iters
+    ev1.record(stream)
+    torch.cuda.synchronize(); dist.barrier()
+    w1 = time.time()
+    ms_total = max_over_ranks(dist, torch, ev0.elapsed_time(ev1))
+    ms_step = ms_total / args.steps
+    value = m * iters / ms_step / 1e6
+
+    # per-sweep device times: the shard sweep kernel alone, and the exchange that follows it
+    sweep_ms, exch_ms = g.pagerank_sharded_time_sweeps(comm, 0.85, warmup=3, n=max(20, iters), stream=sp)
+    w2 = time.time()
+    clk = clocks.stop(w0, w2) if rank == 0 else None
+    avg_sweep = max_over_ranks(dist, torch, float(np.mean(sweep_ms)))
+    avg_exch = max_over_ranks(dist, torch, float(np.mean(exch_ms)))
+    peak, peak_kind = measured_peak_gbs()
+    a_bytes = alg_bytes_pagerank(n, m) / world
+    roofline = {"bound": "hbm", "achieved": round(a_bytes / avg_sweep / 1e6, 1), "peak": peak, "unit": "GB/s",
+                "frac": round(a_bytes / avg_sweep / 1e6 / peak, 4), "traffic": None, "peak_kind": peak_kind, "kernel": "pr_sweep (one shard)",
+                "alg_bytes_per_launch": int(a_bytes), "avg_launch_ms": round(avg_sweep, 5),
+                "exchange": {"what": "NCCL grouped broadcasts of the owned contribution ranges (allgather), per sweep",
+                             "avg_ms": round(avg_exch, 5), "recv_bytes_per_rank": int(8 * n * (world - 1) / world),
+                             "recv_gbs_per_rank": round(8 * n * (world - 1) / world / avg_exch / 1e6, 1) if avg_exch > 0 else None,
+                             "nvlink_peak_gbs_per_dir": 900.0}}
+
+    # ---- BFS (configs[4]): sharded hop_dist over a few roots, device time = max over ranks ----------------
+    deg = np.diff(g.array("begin"))
+    nzv = np.nonzero(deg)[0]
+    rs = np.random.RandomState(1997)
+    roots = [int(nzv[0])] + [int(r) for r in rs.choice(nzv, size=3, replace=False)]
+    del deg, nzv
+    dist_dev = torch.empty(n, dtype=torch.int32, device="cuda")
+    bfs_ms, bfs_edges, bfs_levels = [], [], []
+    for r in roots:
+        g.hop_dist_sharded_dev(comm, dist_dev.data_ptr(), r, stream=sp)
+        dist.barrier()
+        bi = g.hop_dist_sharded_dev(comm, dist_dev.data_ptr(), r, stream=sp)
+        bfs_ms.append(max_over_ranks(dist, torch, bi.kernel_ms)); bfs_edges.append(bi.edges_traversed); bfs_levels.append(bi.levels)
+    bfs = {"metric": "bfs_gteps", "value": round(sum(bfs_edges) / sum(bfs_ms) / 1e6, 3), "unit": "GTEPS", "roots": len(roots),
+           "ms_per_traversal": round(float(np.mean(bfs_ms)), 4), "edges_per_traversal": int(np.mean(bfs_edges)),
+           "levels": bfs_levels, "what": "sharded hop_dist (direction-optimizing, bitmap allgather per level), device time, max over ranks"}
+
+    # ---- e2e: host buffers through the C ABI on every rank (CSR + reverse CSR H2D, plan, sweeps + exchange,
+    # rank[] D2H), wall clock between barriers, max over ranks ---------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        host = {k: g.array(k) for k in ("begin", "node_idx", "r_begin", "r_node_idx")}
+        pinned, pin_ok = {}, True
+        for k, a in host.items():
+            try:
+                t = torch.empty(a.shape, dtype=torch.int32).pin_memory()
+            except Exception:
+                t = torch.empty(a.shape, dtype=torch.int32); pin_ok = False
+            t.numpy()[:] = a
+            pinned[k] = t.numpy()
+        del host
+        try:
+            rank_host = torch.empty(n, dtype=torch.float64).pin_memory().numpy()
+        except Exception:
+            rank_host = np.empty(n, np.float64); pin_ok = False
+        h2d = sum(a.nbytes for a in pinned.values())
+        e2e_steps = max(1, min(args.steps, 2))
+        times = []
+        for k in range(1 + e2e_steps):
+            dist.barrier(); lib.sync()
+            t0 = time.perf_counter()
+            dg = lib.graph_from_csr(pinned["begin"], pinned["node_idx"], semi_sort=False, make_reverse=False)
+            dg.upload_reverse(pinned["r_begin"], pinned["r_node_idx"])
+            out = torch.empty(n, dtype=torch.float64, device="cuda")
+            dg.pagerank_sharded_dev(comm, out.data_ptr(), 1e-30, 0.85, iters)
+            lib.d2h(rank_host, out.data_ptr())
+            dg.close()
+            lib.sync(); dist.barrier()
+            if k > 0:
+                times.append(max_over_ranks(dist, torch, (time.perf_counter() - t0) * 1e3))
+        e2e_ms = float(np.mean(times))
+        e2e = {"value": round(m * iters / e2e_ms / 1e6, 3), "unit": "GTEPS", "h2d_bytes_per_step": int(h2d * world),
+               "d2h_bytes_per_step": int(rank_host.nbytes * world), "ms_per_step": round(e2e_ms, 3), "steps": e2e_steps,
+               "pinned": pin_ok, "note": "every rank uploads the whole CSR (replicated) and plans its shard inside the timed region"}
+
+    if rank == 0:
+        line = {
+            "metric": "pagerank_gteps", "value": round(value, 3), "unit": "GTEPS", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(args, n, m, workload), "nodes": n, "edges": m, "iterations_per_step": iters,
+                       "graph": "device R-MAT generator seed 1997 a=.57 b=.19 c=.19 permuted (counter-based RNG), identical on every rank",
+                       "generate_s": round(gen_s, 2), "first_calls_s": round(warm_s, 2),
+                       "l2": "inputs larger than L2 (index stream %d MB per rank per sweep); no explicit flush" % (4 * m // world // 2**20),
+                       "parallelism": f"{world} ranks x 1 GPU, destination-range shards, NCCL allgather of contributions per sweep"},
+            "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": None, "bfs": bfs,
+            "nccl_version": comm.nccl_version(),
+        }
+        print(json.dumps(line), flush=True)
+    comm.barrier()
+    comm.close()
+    dist.destroy_process_group()

@@ -6,4 +6,4 @@ package is a harness only: a ctypes binding used by tests/, bench.py and __graft
 The directory name contains a hyphen, so load it with `load_package()` from `gmb200_loader.py` at the
 repo root (registers it as module `green_marl_b200`).
 """
-from .gmcuda import GmCuda, GmcError, lib_path, Graph  # noqa: F401
+from .gmcuda import GmCuda, GmcError, lib_path, Graph, Comm  # noqa: F401

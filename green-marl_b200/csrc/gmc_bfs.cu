@@ -1,4 +1,4 @@
-// Level-synchronous, direction-optimizing, frontier-compacted BFS (K6/K7/K8).
+// Level-synchronous, direction-optimizing, frontier-compacted BFS (K6/K7/K8), single GPU and sharded.
 //
 // One engine serves both reference entry points:
 //   * generated hop_dist() (apps/src/hop_dist.gm:3-31): dist int32, INT_MAX when unreachable.  The
@@ -6,20 +6,27 @@
 //     frontier instead -- the resulting dist[] is the same BFS distance.
 //   * gm_bfs_template<short,...>::do_bfs_forward (inc/gm_bfs_template.h:69-271): level int16, -2 unvisited.
 // The per-level state machine is the reference's (get_next_state, gm_bfs_template.h:352-421, thresholds
-// :359,:720-721) so the direction switches happen on the same levels as on the CPU.  Device realisation
-// of the seven states:
-//   SMALL, QUE, Q2R, RD, R2Q  -> top-down: expand the current level's queue, test-and-set the visited
-//                                bitmap with atomicOr (the byte fetch_and_or of gm_bitmap.cc:20-27 on
-//                                32-bit words), write the level, append to the next queue
-//                                (warp-aggregated).  The CPU-only "marks without queue" variants
-//                                (Q2R/RD) still emit the queue here: one aggregated atomic per warp.
-//   RRD, RR2Q                 -> bottom-up: one lane per vertex, one warp per visited word; an
-//                                unvisited vertex scans its parents until one is in the frontier
-//                                BITMAP of the current level (check_parent_rrd :689-708 reads
-//                                visited_level[u]==curr; the bitmap carries the same predicate in N/8
-//                                bytes).  The warp publishes its 32 results with one plain store:
-//                                no atomics.  RR2Q additionally emits the queue.
+// :359,:720-721) so the direction switches happen on the same levels as on the CPU.
+//
+// Device realisation.  State: visited / frontier / candidate BITMAPS (N/8 bytes each, L1/L2 resident), the
+// queue of the OWNED vertices of the current level, the level array.  Every level is
+//   top-down  (SMALL, QUE, Q2R, RD, R2Q):
+//       td_prepare  frontier degrees -> CTA-local offsets + fixed-size edge chunks (TD_CHUNK edge slots each),
+//                   so a hub of degree 10^6 becomes 4096 chunks spread over the whole grid;
+//       td_expand   one warp per chunk: coalesced neighbour loads, visited/candidate bitmap probe, atomicOr
+//                   into the candidate bitmap (the byte fetch_and_or of gm_bitmap.cc:20-27 on 32-bit words);
+//   bottom-up (RRD, RR2Q):
+//       bu_scan     one lane per unvisited owned vertex scans its parents until one is in the frontier bitmap
+//                   (check_parent_rrd :689-708 reads visited_level[u]==curr; the bitmap carries the same
+//                   predicate in N/8 bytes); the warp publishes its 32 results with one plain store;
+//   then  finish    new = candidates & ~visited; visited |= new; level[v] = l+1 for the new bits; the owned new
+//                   vertices are compacted into the next queue; the level's vertex count is reduced.
+// Sharded: rank r owns the vertex range [32*r*wpr, 32*(r+1)*wpr); it expands / scans only
+// owned vertices and the candidate bitmaps are exchanged once per level with ncclAllGather (top-down: the
+// full candidate bitmaps, OR-ed by `finish`; bottom-up: the owned slices, in place).  visited, frontier and
+// level[] are replicated, so every rank drives the identical state machine without a count reduction.
 #include "gmc_common.cuh"
+#include "gmc_comm.h"
 #include <limits.h>
 #include <vector>
 
@@ -27,19 +34,30 @@ using namespace gmc;
 
 enum { ST_SMALL = 0, ST_QUE = 1, ST_Q2R = 2, ST_RD = 3, ST_R2Q = 4, ST_RRD = 5, ST_RR2Q = 6 };
 constexpr int BFS_THREADS = 256;
+constexpr int TD_CHUNK = 256;        // edge slots per warp chunk (8 per lane)
+constexpr unsigned FULLMASK = 0xffffffffu;
 
 struct gmc_bfs_ws {
     int32_t N = 0;
-    int32_t words = 0;
-    uint32_t* visited = nullptr;      // [words]
-    uint32_t* frontier_bm = nullptr;  // [words] bitmap of the current level (bottom-up input)
-    uint32_t* next_bm = nullptr;      // [words] bitmap of the next level (bottom-up output)
-    int32_t* queue = nullptr;         // [N] all level queues back to back (global_vector)
-    int32_t* counters = nullptr;      // [4]: 0 = next_count
+    int32_t words = 0;                // ceil(N/32)
+    int world = 1;
+    int32_t wpr = 0;                  // bitmap words owned per rank
+    int32_t wp = 0;                   // padded bitmap length = wpr * world
+    uint32_t* visited = nullptr;      // [wp]
+    uint32_t* frontier_bm = nullptr;  // [wp] bitmap of the current level
+    uint32_t* cand = nullptr;         // [wp] candidates of the next level (top-down) / next level (bottom-up)
+    uint32_t* allcand = nullptr;      // [world*wp] gathered candidate bitmaps (sharded top-down)
+    int32_t* queue[2] = {nullptr, nullptr};   // owned vertices of the current / next level
+    int32_t* blk_off = nullptr;       // [N] CTA-relative exclusive degree offsets of the queue entries
+    int32_t* blk_total = nullptr;     // [ceil(N/256)]
+    int2* chunks = nullptr;           // [M/TD_CHUNK + N/256 + 2] (queue block, chunk-in-block)
+    size_t chunk_cap = 0;
+    int32_t* counters = nullptr;      // [8]: 0 = level count (global), 1 = owned queue count, 2 = nchunks
+    int32_t* h_counters = nullptr;    // pinned [8]
     void* level = nullptr;            // [N] int32 (also used as int16)
     unsigned long long* edge_sum = nullptr;
     // host-side record of the last traversal
-    std::vector<int32_t> level_count, level_queue_begin, state_trace;
+    std::vector<int32_t> level_count, state_trace;
     bool last_is_i16 = false;
     bool valid = false;
 };
@@ -47,8 +65,10 @@ struct gmc_bfs_ws {
 void gmc_bfs_ws_free(gmc_graph* g) {
     gmc_bfs_ws* w = g->bfs;
     if (!w) return;
-    cudaFree(w->visited); cudaFree(w->frontier_bm); cudaFree(w->next_bm); cudaFree(w->queue);
+    cudaFree(w->visited); cudaFree(w->frontier_bm); cudaFree(w->cand); cudaFree(w->allcand);
+    cudaFree(w->queue[0]); cudaFree(w->queue[1]); cudaFree(w->blk_off); cudaFree(w->blk_total); cudaFree(w->chunks);
     cudaFree(w->counters); cudaFree(w->level); cudaFree(w->edge_sum);
+    if (w->h_counters) cudaFreeHost(w->h_counters);
     delete w;
     g->bfs = nullptr;
 }
@@ -57,124 +77,175 @@ namespace {
 
 template <typename L>
 __global__ void bfs_init(L* __restrict__ level, int32_t n, L invalid, int32_t root, uint32_t* __restrict__ visited,
-                         int32_t words, int32_t* __restrict__ queue, int32_t* __restrict__ counters) {
+                         uint32_t* __restrict__ frontier, uint32_t* __restrict__ cand, int32_t wp,
+                         int32_t* __restrict__ queue, int root_owned, int32_t* __restrict__ counters) {
     int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) level[i] = (i == root) ? (L)0 : invalid;
-    if (i < words) visited[i] = (i == (root >> 5)) ? (1u << (root & 31)) : 0u;
-    if (i == 0) { queue[0] = root; counters[0] = 0; }
+    if (i < wp) {
+        const uint32_t b = (i == (root >> 5)) ? (1u << (root & 31)) : 0u;
+        visited[i] = b; frontier[i] = b; cand[i] = 0u;
+    }
+    if (i == 0) { if (root_owned) queue[0] = root; counters[0] = 0; counters[1] = 0; counters[2] = 0; }
 }
 
-// append `v` (when `take`) to the next-level queue with one atomic per warp
-__device__ __forceinline__ void warp_append(bool take, int32_t v, int32_t* __restrict__ out, int32_t* __restrict__ count) {
-    unsigned mask = __ballot_sync(0xffffffffu, take);   // callers keep the warp converged here
-    if (!take) return;
-    int lane = threadIdx.x & 31;
-    int leader = __ffs(mask) - 1;
-    int32_t base = 0;
-    if (lane == leader) base = atomicAdd(count, __popc(mask));
-    base = __shfl_sync(mask, base, leader);
-    out[base + __popc(mask & ((1u << lane) - 1))] = v;
-}
-
-// top-down step: CTA takes BFS_THREADS frontier vertices; their edges are expanded cooperatively
-// (prefix sum of degrees + binary search) so a hub does not serialise on one thread.
-template <typename L>
+// ---- top-down, step 1: degrees of the queued vertices -> CTA-relative offsets + chunk descriptors ----------
 __global__ void __launch_bounds__(BFS_THREADS)
-bfs_topdown(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_idx, const int32_t* __restrict__ cur_queue,
-            int32_t cur_count, L next_level, L* __restrict__ level, uint32_t* __restrict__ visited,
-            int32_t* __restrict__ next_queue, int32_t* __restrict__ next_count, const uint8_t* __restrict__ edge_mask) {
-    __shared__ int32_t s_start[BFS_THREADS];
-    __shared__ int32_t s_off[BFS_THREADS + 1];
-    __shared__ int32_t s_warp[BFS_THREADS / 32 + 1];
+td_prepare(const int32_t* __restrict__ begin, const int32_t* __restrict__ queue, int32_t qcount, int32_t* __restrict__ blk_off,
+           int32_t* __restrict__ blk_total, int2* __restrict__ chunks, int32_t* __restrict__ nchunks) {
+    __shared__ int32_t s_warp[BFS_THREADS / 32];
+    __shared__ int32_t s_c0;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int32_t qi = blockIdx.x * BFS_THREADS + tid;
-    int32_t deg = 0, st = 0;
-    if (qi < cur_count) {
-        int32_t v = cur_queue[qi];
-        st = begin[v];
-        deg = begin[v + 1] - st;
-    }
-    // block exclusive scan of deg
+    int32_t deg = 0;
+    if (qi < qcount) { const int32_t v = queue[qi]; deg = begin[v + 1] - begin[v]; }
     int32_t inc = deg;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        int32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += t;
-    }
+    for (int o = 1; o < 32; o <<= 1) { const int32_t t = __shfl_up_sync(FULLMASK, inc, o); if (lane >= o) inc += t; }
     if (lane == 31) s_warp[wid] = inc;
     __syncthreads();
-    if (tid == 0) {
-        int32_t run = 0;
-        for (int w = 0; w < BFS_THREADS / 32; w++) { int32_t t = s_warp[w]; s_warp[w] = run; run += t; }
-        s_warp[BFS_THREADS / 32] = run;
-    }
+    int32_t woff = 0, total = 0;
+#pragma unroll
+    for (int k = 0; k < BFS_THREADS / 32; k++) { const int32_t t = s_warp[k]; if (k < wid) woff += t; total += t; }
+    if (qi < qcount) blk_off[qi] = inc - deg + woff;
+    const int32_t nch = (total + TD_CHUNK - 1) / TD_CHUNK;
+    if (tid == 0) { blk_total[blockIdx.x] = total; s_c0 = nch ? atomicAdd(nchunks, nch) : 0; }
     __syncthreads();
-    s_start[tid] = st;
-    s_off[tid] = inc - deg + s_warp[wid];
-    const int32_t total = s_warp[BFS_THREADS / 32];
-    if (tid == 0) s_off[BFS_THREADS] = total;
-    __syncthreads();
+    const int32_t c0 = s_c0;
+    for (int32_t k = tid; k < nch; k += BFS_THREADS) chunks[c0 + k] = make_int2((int)blockIdx.x, k);
+}
 
-    for (int32_t j0 = 0; j0 < total; j0 += BFS_THREADS) {
-        int32_t j = j0 + tid;
-        bool won = false;
-        int32_t u = 0;
-        if (j < total) {
-            int lo = 0, hi = BFS_THREADS;   // s_off[lo] <= j < s_off[hi]
-            while (hi - lo > 1) {
-                int mid = (lo + hi) >> 1;
-                if (s_off[mid] <= j) lo = mid; else hi = mid;
-            }
-            const size_t eidx = (size_t)s_start[lo] + (j - s_off[lo]);
-            u = ld_stream(node_idx + eidx);
-            const uint32_t bit = 1u << (u & 31);
-            // navigator (check_navigator, gm_bfs_template.h:488-492,596-598): filtered edges are not followed
-            if (!(visited[u >> 5] & bit) && (!edge_mask || edge_mask[eidx])) {                     // test ...
-                uint32_t old = atomicOr(&visited[u >> 5], bit);     // ... and test-and-set
-                won = !(old & bit);
-                if (won) level[u] = next_level;
+// first k in [0,32] with e_k > pos (lane k holds e_k, ascending)
+__device__ __forceinline__ int window_search(int32_t e, int32_t pos) {
+    int k = 0;
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        const int32_t ek = __shfl_sync(FULLMASK, e, k + s - 1);
+        if (ek <= pos) k += s;
+    }
+    return k;
+}
+
+// ---- top-down, step 2: one warp per chunk of TD_CHUNK edge slots ---------------------------------------------
+__global__ void __launch_bounds__(BFS_THREADS)
+td_expand(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_idx, const int32_t* __restrict__ queue, int32_t qcount,
+          const int32_t* __restrict__ blk_off, const int32_t* __restrict__ blk_total, const int2* __restrict__ chunks,
+          const int32_t* __restrict__ nchunks_p, const uint32_t* __restrict__ visited, uint32_t* __restrict__ cand,
+          const uint8_t* __restrict__ edge_mask) {
+    const int lane = threadIdx.x & 31;
+    const int32_t nchunks = *nchunks_p;
+    const int32_t nwarps = (gridDim.x * BFS_THREADS) >> 5;
+    for (int32_t c = (blockIdx.x * BFS_THREADS + threadIdx.x) >> 5; c < nchunks; c += nwarps) {
+        const int2 ch = chunks[c];
+        const int32_t qbase = ch.x * BFS_THREADS;
+        const int32_t nq = min(BFS_THREADS, qcount - qbase);
+        const int32_t T = blk_total[ch.x];
+        const int32_t s0 = ch.y * TD_CHUNK, s1 = min(s0 + TD_CHUNK, T);
+        // row holding slot s0: last i with off[i] <= s0 (32-ary search over <= 256 offsets)
+        int32_t r0;
+        {
+            const int i1 = lane * 8;
+            const bool p1 = i1 < nq && blk_off[qbase + i1] <= s0;
+            const int seg = 31 - __clz(__ballot_sync(FULLMASK, p1));      // lane 0 always true (off[0] = 0)
+            const int i2 = seg * 8 + lane;
+            const bool p2 = lane < 8 && i2 < nq && blk_off[qbase + i2] <= s0;
+            r0 = seg * 8 + (31 - __clz(__ballot_sync(FULLMASK, p2)));
+        }
+        int32_t w_start = INT_MAX, w_end = INT_MAX, w_bv = 0;
+        auto load_window = [&](int32_t r) {
+            const int32_t row = r + lane;
+            if (row < nq) {
+                w_start = blk_off[qbase + row];
+                w_end = (row + 1 < nq) ? blk_off[qbase + row + 1] : T;
+                w_bv = begin[queue[qbase + row]];
+            } else { w_start = INT_MAX; w_end = INT_MAX; w_bv = 0; }
+        };
+        load_window(r0);
+        for (int32_t p0 = s0; p0 < s1; p0 += 32) {
+            const int32_t pos = p0 + lane;
+            bool todo = pos < s1;
+            while (__any_sync(FULLMASK, todo)) {
+                const int kk = window_search(w_end, pos);
+                const int32_t st = __shfl_sync(FULLMASK, w_start, kk & 31);
+                const int32_t bv = __shfl_sync(FULLMASK, w_bv, kk & 31);
+                if (todo && kk < 32) {
+                    const int32_t eidx = bv + (pos - st);
+                    const int32_t u = ld_stream(node_idx + eidx);
+                    const uint32_t bit = 1u << (u & 31);
+                    const int32_t uw = u >> 5;
+                    // navigator (check_navigator, gm_bfs_template.h:488-492,596-598): filtered edges are not followed
+                    if (!(visited[uw] & bit) && (!edge_mask || edge_mask[eidx]) && !(cand[uw] & bit)) atomicOr(&cand[uw], bit);
+                    todo = false;
+                }
+                if (__any_sync(FULLMASK, todo)) { r0 += 32; load_window(r0); }     // slots beyond the 32-row window
             }
         }
-        warp_append(won, u, next_queue, next_count);
     }
 }
 
-// bottom-up step: warp w owns vertices [32w, 32w+32) = one word of the bitmaps
-template <typename L, bool EMIT>
+// ---- bottom-up: warp w owns vertices [32w, 32w+32) = one word of the bitmaps ------------------------------------
 __global__ void __launch_bounds__(BFS_THREADS)
-bfs_bottomup(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n,
-             const uint32_t* __restrict__ frontier_bm, uint32_t* __restrict__ visited, uint32_t* __restrict__ next_bm,
-             L next_level, L* __restrict__ level, int32_t* __restrict__ next_queue, int32_t* __restrict__ next_count) {
+bu_scan(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t w_lo, int32_t w_hi,
+        const uint32_t* __restrict__ frontier_bm, const uint32_t* __restrict__ visited, uint32_t* __restrict__ cand) {
     const int lane = threadIdx.x & 31;
-    const int32_t w = (blockIdx.x * BFS_THREADS + threadIdx.x) >> 5;
-    const int32_t words = (n + 31) >> 5;
-    if (w >= words) return;
+    const int32_t w = w_lo + ((blockIdx.x * BFS_THREADS + threadIdx.x) >> 5);
+    if (w >= w_hi) return;
     const uint32_t vis = visited[w];
     const int32_t t = (w << 5) + lane;
     bool found = false;
     if (t < n && !((vis >> lane) & 1u)) {
         const int32_t b = r_begin[t], e = r_begin[t + 1];
         for (int32_t nx = b; nx < e; nx++) {
-            int32_t u = r_node_idx[nx];
+            const int32_t u = r_node_idx[nx];
             if ((frontier_bm[u >> 5] >> (u & 31)) & 1u) { found = true; break; }
         }
-        if (found) level[t] = next_level;
     }
-    const uint32_t got = __ballot_sync(0xffffffffu, found);
-    if (lane == 0) {
-        next_bm[w] = got;
-        if (got) visited[w] = vis | got;
-    }
-    if (EMIT) {
-        warp_append(found, t, next_queue, next_count);
-    } else if (lane == 0 && got) {
-        atomicAdd(next_count, __popc(got));
-    }
+    const uint32_t got = __ballot_sync(FULLMASK, found);
+    if (lane == 0) cand[w] = got;
 }
 
-__global__ void queue_to_bitmap(const int32_t* __restrict__ queue, int32_t count, uint32_t* __restrict__ bm) {
-    int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < count) { int32_t v = queue[i]; atomicOr(&bm[v >> 5], 1u << (v & 31)); }
+// ---- end of level: new = candidates & ~visited -> visited, frontier, level[], owned queue, count ------------------
+template <typename L>
+__global__ void __launch_bounds__(BFS_THREADS)
+bfs_finish(int32_t words, int32_t wp, int world, int use_all, uint32_t* __restrict__ cand, const uint32_t* __restrict__ allcand,
+           uint32_t* __restrict__ visited, uint32_t* __restrict__ frontier, L next_level, L* __restrict__ level,
+           int32_t own_lo, int32_t own_hi, int32_t* __restrict__ next_queue, int32_t* __restrict__ counters) {
+    const int lane = threadIdx.x & 31;
+    const int32_t w = blockIdx.x * BFS_THREADS + threadIdx.x;
+    uint32_t nw = 0;
+    if (w < words) {
+        uint32_t c;
+        if (use_all) {
+            c = 0;
+            for (int r = 0; r < world; r++) c |= allcand[(size_t)r * wp + w];
+        } else c = cand[w];
+        cand[w] = 0u;
+        const uint32_t vis = visited[w];
+        nw = c & ~vis;
+        if (nw) visited[w] = vis | nw;
+        frontier[w] = nw;
+    }
+    const int pc = __popc(nw);
+    const bool owned = w >= own_lo && w < own_hi;
+    int tot = pc, own = owned ? pc : 0, pre = own;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULLMASK, pre, o); if (lane >= o) pre += t; }
+    const int own_tot = __shfl_sync(FULLMASK, pre, 31);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(FULLMASK, tot, o);
+    int32_t base = 0;
+    if (lane == 0) {
+        if (tot) atomicAdd(&counters[0], tot);
+        if (own_tot) base = atomicAdd(&counters[1], own_tot);
+    }
+    base = __shfl_sync(FULLMASK, base, 0) + pre - own;
+    uint32_t bits = nw;
+    while (bits) {
+        const int b = __ffs(bits) - 1;
+        bits &= bits - 1;
+        const int32_t v = (w << 5) + b;
+        level[v] = next_level;
+        if (owned) next_queue[base++] = v;
+    }
 }
 
 template <typename L>
@@ -187,77 +258,107 @@ __global__ void sum_reached_degree(const int32_t* __restrict__ begin, const L* _
     if ((threadIdx.x & 31) == 0 && v) atomicAdd(out, (unsigned long long)v);
 }
 
-int ensure_ws(gmc_graph* g) {
-    if (g->bfs) return GMC_OK;
+int ensure_ws(gmc_graph* g, int world) {
+    if (g->bfs && g->bfs->world == world) return GMC_OK;
+    if (g->bfs) gmc_bfs_ws_free(g);
     gmc_bfs_ws* w = new gmc_bfs_ws();
+    g->bfs = w;
     w->N = g->N;
+    w->world = world;
     w->words = (g->N + 31) / 32;
-    size_t wb = sizeof(uint32_t) * (size_t)(w->words ? w->words : 1);
+    w->wpr = div_up(w->words > 0 ? w->words : 1, world);
+    w->wp = w->wpr * world;
+    const size_t wb = sizeof(uint32_t) * (size_t)w->wp;
+    const size_t nn = (size_t)(g->N ? g->N : 1);
+    w->chunk_cap = (size_t)g->M / TD_CHUNK + nn / BFS_THREADS + 2;
     int rc = gmc_malloc((void**)&w->visited, wb);
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->frontier_bm, wb);
-    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->next_bm, wb);
-    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->queue, sizeof(int32_t) * (size_t)(g->N ? g->N : 1));
-    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->counters, sizeof(int32_t) * 4);
-    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->level, sizeof(int32_t) * (size_t)(g->N ? g->N : 1));
+    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->cand, wb);
+    if (rc == GMC_OK && world > 1) rc = gmc_malloc((void**)&w->allcand, wb * (size_t)world);
+    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->queue[0], sizeof(int32_t) * nn);
+    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->queue[1], sizeof(int32_t) * nn);
+    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->blk_off, sizeof(int32_t) * nn);
+    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->blk_total, sizeof(int32_t) * (nn / BFS_THREADS + 1));
+    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->chunks, sizeof(int2) * w->chunk_cap);
+    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->counters, sizeof(int32_t) * 8);
+    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->level, sizeof(int32_t) * nn);
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->edge_sum, sizeof(unsigned long long));
-    g->bfs = w;
+    if (rc == GMC_OK && cudaMallocHost((void**)&w->h_counters, sizeof(int32_t) * 8) != cudaSuccess) {
+        set_error("bfs: cudaMallocHost failed"); rc = GMC_ERR_NOMEM;
+    }
     if (rc != GMC_OK) { gmc_bfs_ws_free(g); return rc; }
     return GMC_OK;
 }
 
 // The traversal.  fwd_* = arrays followed top-down, rev_* = arrays followed bottom-up (NULL: no bottom-up).
 template <typename L>
-int run_bfs(gmc_graph* g, const int32_t* fwd_begin, const int32_t* fwd_idx, const int32_t* rev_begin, const int32_t* rev_idx,
-            int32_t root, L invalid, L* level_out_dev, gmc_bfs_info* info, cudaStream_t st,
+int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_t* fwd_idx, const int32_t* rev_begin,
+            const int32_t* rev_idx, int32_t root, L invalid, L* level_out_dev, gmc_bfs_info* info, cudaStream_t st,
             const uint8_t* edge_mask = nullptr) {
     GMC_REQUIRE(root >= 0 && root < g->N, GMC_ERR_ARG, "bfs: root %d out of range [0,%d)", root, g->N);
-    GMC_TRY(ensure_ws(g));
+    const int world = comm ? comm->world : 1, rank = comm ? comm->rank : 0;
+    GMC_TRY(ensure_ws(g, world));
     gmc_bfs_ws* w = g->bfs;
     const int32_t n = g->N;
     const bool has_reverse = rev_begin != nullptr;
     L* level = level_out_dev ? level_out_dev : (L*)w->level;
-    w->level_count.clear(); w->level_queue_begin.clear(); w->state_trace.clear();
+    w->level_count.clear(); w->state_trace.clear();
     w->valid = false;
+    const int32_t own_lo = min(rank * w->wpr, w->words), own_hi = min((rank + 1) * w->wpr, w->words);   // owned words
+    const bool root_owned = (root >> 5) >= own_lo && (root >> 5) < own_hi;
 
     cudaEvent_t ev0, ev1;
     GMC_CUDA(cudaEventCreate(&ev0));
     GMC_CUDA(cudaEventCreate(&ev1));
     int launches = 0, bottom_up = 0;
     GMC_CUDA(cudaEventRecord(ev0, st));
-    bfs_init<L><<<div_up(n, 256), 256, 0, st>>>(level, n, invalid, root, w->visited, w->words, w->queue, w->counters);
+    int qi = 0;     // queue[qi] = current level
+    bfs_init<L><<<div_up(max(n, w->wp), 256), 256, 0, st>>>(level, n, invalid, root, w->visited, w->frontier_bm, w->cand, w->wp,
+                                                              w->queue[0], root_owned ? 1 : 0, w->counters);
     launches++;
 
     int state = ST_SMALL;
-    int32_t curr_level = 0, curr_begin = 0, next_begin = 1, curr_count = 1, next_count = 0;
-    bool have_queue = true;       // queue[curr_begin, +curr_count) holds the current level
-    bool have_bitmap = false;     // frontier_bm holds the current level
+    int32_t curr_level = 0, curr_count = 1, own_count = root_owned ? 1 : 0;
     const float thr = (float)n * 0.05f;   // RRD_THRESHOLD, gm_bfs_template.h:359 (float arithmetic as in the reference)
+    const unsigned fin_grid = (unsigned)div_up(w->words, BFS_THREADS);
+    const unsigned exp_grid = (unsigned)sm_count() * 8;
     for (;;) {
         w->state_trace.push_back(state);
         w->level_count.push_back(curr_count);
-        w->level_queue_begin.push_back(have_queue ? curr_begin : -1);
         GMC_REQUIRE(sizeof(L) == 4 || curr_level + 1 <= 32767, GMC_ERR_STATE, "bfs: more levels than level_t can hold");
         const L nl = (L)(curr_level + 1);
+        int use_all = 0;
         if (state == ST_RRD || state == ST_RR2Q) {
-            if (!have_bitmap) {   // previous level was top-down: build its bitmap from the queue
-                GMC_CUDA(cudaMemsetAsync(w->frontier_bm, 0, sizeof(uint32_t) * (size_t)w->words, st));
-                queue_to_bitmap<<<div_up(curr_count, 256), 256, 0, st>>>(w->queue + curr_begin, curr_count, w->frontier_bm);
+            if (own_hi > own_lo) {
+                bu_scan<<<div_up((own_hi - own_lo) * 32, BFS_THREADS), BFS_THREADS, 0, st>>>(rev_begin, rev_idx, n, own_lo, own_hi,
+                                                                                            w->frontier_bm, w->visited, w->cand);
                 launches++;
             }
-            const unsigned grid = (unsigned)div_up((int64_t)w->words * 32, (int64_t)BFS_THREADS);
-            if (state == ST_RR2Q)
-                bfs_bottomup<L, true><<<grid, BFS_THREADS, 0, st>>>(rev_begin, rev_idx, n, w->frontier_bm, w->visited, w->next_bm, nl, level, w->queue + next_begin, w->counters);
-            else
-                bfs_bottomup<L, false><<<grid, BFS_THREADS, 0, st>>>(rev_begin, rev_idx, n, w->frontier_bm, w->visited, w->next_bm, nl, level, w->queue + next_begin, w->counters);
-            launches++; bottom_up++;
+            bottom_up++;
+            if (world > 1) GMC_TRY(gmc_comm_allgather(comm, w->cand + (size_t)rank * w->wpr, w->cand, sizeof(uint32_t) * (size_t)w->wpr, st));
         } else {
-            bfs_topdown<L><<<div_up(curr_count, BFS_THREADS), BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue + curr_begin, curr_count, nl, level, w->visited, w->queue + next_begin, w->counters, edge_mask);
-            launches++;
+            if (own_count > 0) {
+                td_prepare<<<div_up(own_count, BFS_THREADS), BFS_THREADS, 0, st>>>(fwd_begin, w->queue[qi], own_count, w->blk_off,
+                                                                                  w->blk_total, w->chunks, w->counters + 2);
+                td_expand<<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[qi], own_count, w->blk_off, w->blk_total,
+                                                            w->chunks, w->counters + 2, w->visited, w->cand, edge_mask);
+                launches += 2;
+            }
+            if (world > 1) {
+                GMC_TRY(gmc_comm_allgather(comm, w->cand, w->allcand, sizeof(uint32_t) * (size_t)w->wp, st));
+                use_all = 1;
+            }
         }
+        bfs_finish<L><<<fin_grid, BFS_THREADS, 0, st>>>(w->words, w->wp, world, use_all, w->cand, w->allcand, w->visited, w->frontier_bm,
+                                                        nl, level, own_lo, own_hi, w->queue[qi ^ 1], w->counters);
+        launches++;
         GMC_CUDA(cudaGetLastError());
-        GMC_CUDA(cudaMemcpyAsync(&next_count, w->counters, sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-        GMC_CUDA(cudaMemsetAsync(w->counters, 0, sizeof(int32_t), st));
+        GMC_CUDA(cudaMemcpyAsync(w->h_counters, w->counters, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        GMC_CUDA(cudaMemsetAsync(w->counters, 0, 4 * sizeof(int32_t), st));
         GMC_CUDA(cudaStreamSynchronize(st));
+        const int32_t next_count = w->h_counters[0];
+        own_count = w->h_counters[1];
+        qi ^= 1;
 
         // get_next_state (gm_bfs_template.h:352-421)
         if (next_count == 0) break;
@@ -277,15 +378,7 @@ int run_bfs(gmc_graph* g, const int32_t* fwd_begin, const int32_t* fwd_idx, cons
             case ST_RRD: if (next_count <= 2 * curr_count) next_state = ST_RR2Q; break;
             case ST_RR2Q: next_state = ST_QUE; break;
         }
-        // finish_level (:423-447).  Device: every top-down state and RR2Q emitted the queue; RRD did not.
-        const bool emitted_queue = (state != ST_RRD);
-        const bool emitted_bitmap = (state == ST_RRD || state == ST_RR2Q);
-        if (emitted_queue) { curr_begin = next_begin; next_begin += next_count; }
-        have_queue = emitted_queue;
-        have_bitmap = emitted_bitmap;
-        if (emitted_bitmap) { uint32_t* t = w->frontier_bm; w->frontier_bm = w->next_bm; w->next_bm = t; }
         curr_count = next_count;
-        next_count = 0;
         curr_level++;
         state = next_state;
     }
@@ -316,27 +409,31 @@ int run_bfs(gmc_graph* g, const int32_t* fwd_begin, const int32_t* fwd_idx, cons
 
 extern "C" {
 
-int gmc_hop_dist_dev(gmc_graph* g, int32_t root, int32_t* dist_dev, gmc_bfs_info* info, void* stream) {
+int gmc_hop_dist_sharded_dev(gmc_graph* g, gmc_comm* comm, int32_t root, int32_t* dist_dev, gmc_bfs_info* info, void* stream) {
     GMC_REQUIRE(g && dist_dev, GMC_ERR_ARG, "gmc_hop_dist_dev: NULL");
     GMC_REQUIRE(g->N > 0, GMC_ERR_ARG, "gmc_hop_dist_dev: empty graph");
-    return run_bfs<int32_t>(g, g->begin, g->node_idx, g->has_reverse ? g->r_begin : nullptr,
+    return run_bfs<int32_t>(g, comm, g->begin, g->node_idx, g->has_reverse ? g->r_begin : nullptr,
                             g->has_reverse ? g->r_node_idx : nullptr, root, INT_MAX, dist_dev, info, as_stream(stream));
+}
+
+int gmc_hop_dist_dev(gmc_graph* g, int32_t root, int32_t* dist_dev, gmc_bfs_info* info, void* stream) {
+    return gmc_hop_dist_sharded_dev(g, nullptr, root, dist_dev, info, stream);
 }
 
 int gmc_hop_dist(gmc_graph* g, int32_t root, int32_t* dist_host, gmc_bfs_info* info) {
     GMC_REQUIRE(g && dist_host, GMC_ERR_ARG, "gmc_hop_dist: NULL");
     GMC_REQUIRE(g->N > 0, GMC_ERR_ARG, "gmc_hop_dist: empty graph");
-    GMC_TRY(ensure_ws(g));
+    GMC_TRY(ensure_ws(g, 1));
     GMC_TRY(gmc_hop_dist_dev(g, root, (int32_t*)g->bfs->level, info, nullptr));
     return gmc_d2h(dist_host, g->bfs->level, sizeof(int32_t) * (size_t)g->N, nullptr);
 }
 
-int gmc_bfs_levels_masked(gmc_graph* g, int32_t root, int use_reverse_edge, const uint8_t* edge_mask_host, int16_t* level_host,
-                          int32_t* state_trace, int32_t* level_count, int32_t trace_cap, gmc_bfs_info* info) {
+int gmc_bfs_levels_sharded(gmc_graph* g, gmc_comm* comm, int32_t root, int use_reverse_edge, const uint8_t* edge_mask_host,
+                           int16_t* level_host, int32_t* state_trace, int32_t* level_count, int32_t trace_cap, gmc_bfs_info* info) {
     GMC_REQUIRE(g && level_host, GMC_ERR_ARG, "gmc_bfs_levels: NULL");
     GMC_REQUIRE(g->N > 0, GMC_ERR_ARG, "gmc_bfs_levels: empty graph");
     GMC_REQUIRE(!use_reverse_edge || g->has_reverse, GMC_ERR_STATE, "gmc_bfs_levels: use_reverse_edge needs the reverse CSR");
-    GMC_TRY(ensure_ws(g));
+    GMC_TRY(ensure_ws(g, comm ? comm->world : 1));
     const int32_t *fb = g->begin, *fi = g->node_idx;
     const int32_t *rb = g->has_reverse ? g->r_begin : nullptr, *ri = g->has_reverse ? g->r_node_idx : nullptr;
     if (use_reverse_edge) { fb = g->r_begin; fi = g->r_node_idx; rb = g->begin; ri = g->node_idx; }
@@ -349,7 +446,7 @@ int gmc_bfs_levels_masked(gmc_graph* g, int32_t root, int use_reverse_edge, cons
         int rc = gmc_h2d(mask_dev, edge_mask_host, (size_t)g->M, nullptr);
         if (rc != GMC_OK) { cudaFree(mask_dev); return rc; }
     }
-    int rc = run_bfs<int16_t>(g, fb, fi, rb, ri, root, (int16_t)-2, (int16_t*)g->bfs->level, info, nullptr, mask_dev);
+    int rc = run_bfs<int16_t>(g, comm, fb, fi, rb, ri, root, (int16_t)-2, (int16_t*)g->bfs->level, info, nullptr, mask_dev);
     if (mask_dev) cudaFree(mask_dev);
     GMC_TRY(rc);
     gmc_bfs_ws* w = g->bfs;
@@ -360,14 +457,19 @@ int gmc_bfs_levels_masked(gmc_graph* g, int32_t root, int use_reverse_edge, cons
     return gmc_d2h(level_host, w->level, sizeof(int16_t) * (size_t)g->N, nullptr);
 }
 
+int gmc_bfs_levels_masked(gmc_graph* g, int32_t root, int use_reverse_edge, const uint8_t* edge_mask_host, int16_t* level_host,
+                          int32_t* state_trace, int32_t* level_count, int32_t trace_cap, gmc_bfs_info* info) {
+    return gmc_bfs_levels_sharded(g, nullptr, root, use_reverse_edge, edge_mask_host, level_host, state_trace, level_count, trace_cap, info);
+}
+
 int gmc_bfs_levels(gmc_graph* g, int32_t root, int use_reverse_edge, int16_t* level_host, int32_t* state_trace,
                    int32_t* level_count, int32_t trace_cap, gmc_bfs_info* info) {
-    return gmc_bfs_levels_masked(g, root, use_reverse_edge, nullptr, level_host, state_trace, level_count, trace_cap, info);
+    return gmc_bfs_levels_sharded(g, nullptr, root, use_reverse_edge, nullptr, level_host, state_trace, level_count, trace_cap, info);
 }
 
 // Vertices of every level in level order (the reference's global_vector / level_queue_begin,
-// gm_bfs_template.h:423-447).  Bottom-up levels keep no device queue, so the order is rebuilt from the
-// level array: ascending vertex id inside a level (the reference's order inside a level is unspecified).
+// gm_bfs_template.h:423-447), rebuilt from the level array: ascending vertex id inside a level (the
+// reference's order inside a level is unspecified).
 int gmc_bfs_level_order(gmc_graph* g, int32_t* order_host, int32_t* level_begin_host, int32_t cap_levels) {
     GMC_REQUIRE(g && order_host && level_begin_host, GMC_ERR_ARG, "gmc_bfs_level_order: NULL");
     GMC_REQUIRE(g->bfs && g->bfs->valid && g->bfs->last_is_i16, GMC_ERR_STATE, "gmc_bfs_level_order: run gmc_bfs_levels first");

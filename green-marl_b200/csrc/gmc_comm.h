@@ -1,0 +1,18 @@
+// Internal: the communicator object behind gmc_comm (include/gm_cuda.h) and the collectives the sharded
+// PageRank / BFS host code calls.  world == 1 (or a NULL communicator) makes every call a local no-op/copy.
+#pragma once
+#include <cuda_runtime.h>
+#include <nccl.h>
+#include <stdint.h>
+
+struct gmc_comm {
+    int world = 1, rank = 0;
+    ncclComm_t nccl = nullptr;
+    void* scratch = nullptr;
+};
+
+int gmc_comm_allgather(gmc_comm* c, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st);
+int gmc_comm_allreduce_sum_f64(gmc_comm* c, const double* send, double* recv, size_t count, cudaStream_t st);
+int gmc_comm_allreduce_sum_i64(gmc_comm* c, const long long* send, long long* recv, size_t count, cudaStream_t st);
+int gmc_comm_allgather_segments(gmc_comm* c, void* buf, size_t elem_bytes, const int64_t* seg_off, const int64_t* seg_len,
+                                int nseg, cudaStream_t st);

@@ -33,6 +33,7 @@
 // new contrib, out-degree, first touch of contrib); gathers are served by shared memory / L2.
 #define GMC_EXPERIMENT 1
 #include "gmc_common.cuh"
+#include "gmc_comm.h"
 #include <cub/device/device_radix_sort.cuh>
 #include <vector>
 #include <stdlib.h>
@@ -69,9 +70,10 @@ struct SweepArgs {
     const int32_t* __restrict__ ltask_row;   // [n_ltasks+1]
     const int32_t* __restrict__ stask_slice; // [n_stasks+1]
     const int32_t* __restrict__ outdeg;      // [N+1] by new id
-    int32_t N, n_long, hot_n, EL;
-    int32_t n_ltasks, n_stasks, n_ztasks, z0;  // z0 = first id without in-edges
-    int32_t lt_lo, lt_hi, st_lo, st_hi, zt_lo, zt_hi;   // task ranges executed by this launch (multi-GPU shards)
+    int32_t N, n_long, hot_n, EL;             // n_long, EL: rows / entries of THIS shard's long section
+    int32_t long_id0, short_id0;              // id of the shard's first long row / of lane 0 of its first slice
+    int32_t n_ltasks, n_stasks, n_ztasks, z0, z_end;  // [z0, z_end): the shard's ids without in-edges
+    int32_t lt_lo, lt_hi, st_lo, st_hi, zt_lo, zt_hi;   // task ranges executed by this launch (experiment switches)
     // split rows
     double* head_part;                       // [n_ltasks]
     double* tail_part;                       // [n_ltasks]
@@ -83,15 +85,24 @@ struct SweepArgs {
     const double* __restrict__ rank_in;      // [N+1]
     double* rank_out;
     double d, base;
-    // loop control (may be null)
+    // loop control (may be null); diff_slot != null: sharded run, the shard's diff goes there and the
+    // loop control is advanced by k_ctrl_combine once every shard's diff is known
     gmc_pr_ctrl* ctrl;
+    double* diff_slot;
     double e;
     int32_t max_iter;
     int32_t mode;                            // experiment switches (GMC_EXPERIMENT builds only)
 };
 
 struct gmc_pr_plan {
-    int32_t N = 0, M = 0, n_long = 0, n_pos = 0, hot_n = 1, n_slices = 0, nz_slices = 0, EL = 0, EN = 0, n_ltasks = 0, n_stasks = 0, n_ztasks = 0, z0 = 0;
+    int world = 1, shard = 0;
+    bool owns_state = true;
+    // global layout facts
+    int32_t N = 0, M = 0, g_n_long = 0, n_pos = 0, hot_n = 1, g_nz_slices = 0, g_z0 = 0;
+    // this shard: long rows [jl0, jl0+n_long), slices [s0, s0+n_slices), zero ids [z0, z_end)
+    int32_t jl0 = 0, n_long = 0, s0 = 0, n_slices = 0, EL = 0, EN = 0, n_ltasks = 0, n_stasks = 0, n_ztasks = 0, z0 = 0, z_end = 0;
+    std::vector<int64_t> seg_off, seg_len;    // [world][3] owned id ranges of every rank (long, short, zero)
+    double* diffs = nullptr;                  // [world] per-shard diffs of the current iteration
     int32_t *new_of_old = nullptr, *old_of_new = nullptr, *E = nullptr, *lbeg = nullptr, *sbeg = nullptr;
     int32_t *ltask_row = nullptr, *stask_slice = nullptr, *outdeg = nullptr;
     double *head_part = nullptr, *tail_part = nullptr, *diff_parts = nullptr;
@@ -182,7 +193,7 @@ __device__ __forceinline__ void split_arrive(const SweepArgs& A, int lane, int32
     for (int32_t p = t1 + lane; p <= t2; p += 32) v += (p == t1) ? __ldcg(A.tail_part + p) : __ldcg(A.head_part + p);
     const double S = butterfly(v);
     if (lane == 0) {
-        A.diff_parts[n_tasks_total + t1] = finish_row(A, row + 1, S);
+        A.diff_parts[n_tasks_total + t1] = finish_row(A, A.long_id0 + row, S);
         A.split_cnt[t1] = 0u;
     }
 }
@@ -253,7 +264,7 @@ __device__ __forceinline__ void long_task(const SweepArgs& A, const double* hot,
     const int k_first = head_split ? 1 : 0;
     const int k_last = tail_split ? kl - 1 : kl;
     double diff = 0.0;
-    if (lane >= k_first && lane <= k_last) diff = finish_row(A, a + lane + 1, my_sum);
+    if (lane >= k_first && lane <= k_last) diff = finish_row(A, A.long_id0 + a + lane, my_sum);
     diff = butterfly(diff);
     if (lane == 0) A.diff_parts[t] = diff;
     const int32_t split_base = A.n_ltasks + A.n_stasks + A.n_ztasks;
@@ -282,7 +293,7 @@ __device__ __forceinline__ void short_task(const SweepArgs& A, const double* hot
     double S = 0.0, old = 0.0;
     int32_t od = 0;
     while (q < ns) {
-        const int32_t id = A.n_long + 1 + (s_lo + q) * 32 + lane;
+        const int32_t id = A.short_id0 + (s_lo + q) * 32 + lane;
         if (j == 0 && id <= A.N) { old = __ldcs(A.rank_in + id); od = __ldcs(A.outdeg + id); }
         // where the next chunk lives
         int nq = q, nj = j + 8;
@@ -329,13 +340,13 @@ __device__ __forceinline__ void zero_task(const SweepArgs& A, int lane, int32_t 
 #pragma unroll
         for (int k = 0; k < 8; k++) {
             const int32_t id = id0 + b + k * 32 + lane;
-            old[k] = id <= A.N ? __ldcs(A.rank_in + id) : 0.0;
-            od[k] = id <= A.N ? __ldcs(A.outdeg + id) : 0;
+            old[k] = id < A.z_end ? __ldcs(A.rank_in + id) : 0.0;
+            od[k] = id < A.z_end ? __ldcs(A.outdeg + id) : 0;
         }
 #pragma unroll
         for (int k = 0; k < 8; k++) {
             const int32_t id = id0 + b + k * 32 + lane;
-            if (id <= A.N) {
+            if (id < A.z_end) {
                 const double val = A.base;                       // (1-d)/N + d*0
                 __stcs(A.rank_out + id, val);
                 A.contrib_out[id] = od[k] > 0 ? val / (double)od[k] : 0.0;
@@ -394,7 +405,10 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
     __syncthreads();
     if (warp == 0) {
         double t = butterfly(s_red[lane]);
-        if (lane == 0) {
+        if (lane == 0 && A.diff_slot) {
+            *A.diff_slot = t;
+            A.ctrl->arrived = 0u;
+        } else if (lane == 0) {
             const int32_t cnt = A.ctrl->cnt + 1;
             A.ctrl->diff = t;
             A.ctrl->cnt = cnt;
@@ -464,14 +478,16 @@ __global__ void k_lengths(const int32_t* __restrict__ old_of_new, const int32_t*
         scost[s] = len > 0 ? 32 * len + SLICE_OVH : 0;          // empty slices belong to the zero tasks
     }
 }
-__global__ void k_add_offset(int32_t* __restrict__ a, int32_t n, const int32_t* __restrict__ off) {
+// dst[i] = src[lo + i] - src[lo] + add, i in [0, cnt): the shard's slice of a global offset array, rebased
+__global__ void k_rebase(const int32_t* __restrict__ src, int32_t lo, int32_t cnt, int32_t add, int32_t* __restrict__ dst) {
     int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) a[i] += *off;
+    if (i < cnt) dst[i] = src[lo + i] - src[lo] + add;
 }
-// scatter every reverse edge into E, keeping its position inside the row (= the reference's summation order)
+// scatter every reverse edge whose destination row belongs to the shard into E, keeping its position inside
+// the row (= the reference's summation order).  jl0/nl: the shard's long rows, s0/ns: its slices.
 __global__ void k_fill_entries(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t m,
-                               const int32_t* __restrict__ new_of_old, int32_t n_long, const int32_t* __restrict__ lbeg,
-                               const int32_t* __restrict__ sbeg, int32_t* __restrict__ E) {
+                               const int32_t* __restrict__ new_of_old, int32_t g_n_long, int32_t jl0, int32_t nl, int32_t s0, int32_t ns,
+                               const int32_t* __restrict__ lbeg, const int32_t* __restrict__ sbeg, int32_t* __restrict__ E) {
     int32_t eidx = blockIdx.x * blockDim.x + threadIdx.x;
     if (eidx >= m) return;
     int32_t lo = 0, hi = n;   // r_begin[lo] <= eidx < r_begin[hi]
@@ -481,19 +497,23 @@ __global__ void k_fill_entries(const int32_t* __restrict__ r_begin, const int32_
     }
     const int32_t k = eidx - r_begin[lo];
     const int32_t j = new_of_old[lo] - 1;
-    const int32_t w = new_of_old[ld_stream(r_node_idx + eidx)];
-    if (j < n_long) E[lbeg[j] + k] = w;
-    else {
-        const int32_t q = j - n_long;
-        E[sbeg[q >> 5] + k * 32 + (q & 31)] = w;
+    if (j < g_n_long) {
+        const int32_t jj = j - jl0;
+        if (jj < 0 || jj >= nl) return;
+        E[lbeg[jj] + k] = new_of_old[ld_stream(r_node_idx + eidx)];
+    } else {
+        const int32_t q = j - g_n_long;
+        const int32_t sl = (q >> 5) - s0;
+        if (sl < 0 || sl >= ns) return;
+        E[sbeg[sl] + k * 32 + (q & 31)] = new_of_old[ld_stream(r_node_idx + eidx)];
     }
 }
-// first[t] = first index j in [0,n] with pos[j] (+ len of j when INCL) > / >= target   (task cut points)
+// first[t] = row holding entry t*LT: last j with lbeg[j] <= target   (task cut points)
 __global__ void k_ltask_rows(const int32_t* __restrict__ lbeg, int32_t n_long, int32_t n_tasks, int32_t* __restrict__ first) {
     int32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t > n_tasks) return;
     if (t == n_tasks) { first[t] = n_long; return; }
-    const int32_t target = t * LT;           // row holding entry `target`: last j with lbeg[j] <= target
+    const int32_t target = t * LT;
     int32_t lo = 0, hi = n_long;             // lbeg[lo] <= target < lbeg[hi]
     while (hi - lo > 1) {
         const int32_t mid = lo + ((hi - lo) >> 1);
@@ -526,6 +546,16 @@ __global__ void k_unpermute(const double* __restrict__ rank_new, const int32_t* 
     int32_t v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v < n) out[v] = rank_new[new_of_old[v]];
 }
+// sharded loop control: diff = sum of the shards' diffs in rank order; cnt++; done = !(diff > e && cnt < max)
+__global__ void k_ctrl_combine(gmc_pr_ctrl* ctrl, const double* __restrict__ diffs, int world, double e, int32_t max_iter) {
+    if (threadIdx.x != 0 || blockIdx.x != 0 || ctrl->done) return;
+    double t = 0.0;
+    for (int r = 0; r < world; r++) t += diffs[r];
+    const int32_t cnt = ctrl->cnt + 1;
+    ctrl->diff = t;
+    ctrl->cnt = cnt;
+    ctrl->done = !((t > e) && (cnt < max_iter));
+}
 
 template <typename K>
 int sort_pairs(K* keys_in, K* keys_out, int32_t* vals_in, int32_t* vals_out, int32_t n, int end_bit, cudaStream_t st) {
@@ -545,25 +575,33 @@ void free_plan(gmc_pr_plan* p) {
     cudaFree(p->new_of_old); cudaFree(p->old_of_new); cudaFree(p->E); cudaFree(p->lbeg); cudaFree(p->sbeg);
     cudaFree(p->ltask_row); cudaFree(p->stask_slice); cudaFree(p->outdeg);
     cudaFree(p->head_part); cudaFree(p->tail_part); cudaFree(p->diff_parts); cudaFree(p->split_cnt);
-    cudaFree(p->contrib[0]); cudaFree(p->contrib[1]); cudaFree(p->rank[0]); cudaFree(p->rank[1]); cudaFree(p->ctrl);
+    if (p->owns_state) {
+        cudaFree(p->contrib[0]); cudaFree(p->contrib[1]); cudaFree(p->rank[0]); cudaFree(p->rank[1]); cudaFree(p->ctrl); cudaFree(p->diffs);
+    }
     delete p;
 }
 
 #define PLAN_TRY(expr) do { rc = (expr); if (rc != GMC_OK) goto fail; } while (0)
+#define PLAN_CUDA(expr) do { if ((expr) != cudaSuccess) { rc = GMC_ERR_CUDA; set_error("pagerank plan: %s", cudaGetErrorString(cudaGetLastError())); goto fail; } } while (0)
 
-int build_plan(gmc_graph* g, gmc_pr_plan** out, cudaStream_t st) {
+// Plan of shard `rank` of `world` (world == 1: the whole graph).  `state_of`: borrow the state buffers of
+// another plan of the same graph (emulated shards on one device) instead of allocating them.
+int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, gmc_pr_plan** out, cudaStream_t st) {
     const int32_t n = g->N, m = g->M;
     gmc_pr_plan* p = new gmc_pr_plan();
-    p->N = n; p->M = m;
+    p->N = n; p->M = m; p->world = world; p->shard = rank;
+    p->owns_state = state_of == nullptr;
     int rc = GMC_OK;
-    int32_t *outdeg_old = nullptr, *indeg = nullptr, *ids = nullptr, *ids2 = nullptr, *is_long = nullptr, *is_pos = nullptr, *hot_rank = nullptr, *scost = nullptr;
+    int32_t *outdeg_old = nullptr, *indeg = nullptr, *ids = nullptr, *ids2 = nullptr, *is_long = nullptr, *is_pos = nullptr, *hot_rank = nullptr;
+    int32_t *g_lbeg = nullptr, *g_sbeg = nullptr, *g_scost = nullptr, *scost = nullptr;
     uint32_t *key_a = nullptr, *key_a2 = nullptr;
     unsigned long long *key_b = nullptr, *key_b2 = nullptr;
     int32_t* tot = nullptr;
     const size_t nn = (size_t)n;
     const unsigned gb = (unsigned)div_up(n, 256);
     int32_t h[2] = {0, 0};
-    int32_t cost_total = 0;
+    int32_t g_n_slices = 0, jl1 = 0, s1 = 0, cost_total = 0;
+    std::vector<int32_t> h_lbeg, h_sbeg, h_scost, cutsL((size_t)world + 1), cutsS((size_t)world + 1), cutsZ((size_t)world + 1);
 
     PLAN_TRY(gmc_malloc((void**)&outdeg_old, 4 * nn)); PLAN_TRY(gmc_malloc((void**)&indeg, 4 * nn));
     PLAN_TRY(gmc_malloc((void**)&ids, 4 * nn)); PLAN_TRY(gmc_malloc((void**)&ids2, 4 * nn));
@@ -575,15 +613,16 @@ int build_plan(gmc_graph* g, gmc_pr_plan** out, cudaStream_t st) {
     PLAN_TRY(gmc_malloc((void**)&p->new_of_old, 4 * nn)); PLAN_TRY(gmc_malloc((void**)&p->old_of_new, 4 * (nn + 1)));
     PLAN_TRY(gmc_malloc((void**)&p->outdeg, 4 * (nn + 1)));
 
-    // 1. degrees, number of long rows, the hot block
+    // 1. degrees, number of long rows, the hot block, the relabelling (identical on every rank)
     k_degrees<<<gb, 256, 0, st>>>(g->begin, g->r_begin, n, outdeg_old, indeg, key_a, ids, is_long, is_pos);
     PLAN_TRY(exclusive_scan_i32(is_long, is_long, nn, tot, st));
     PLAN_TRY(exclusive_scan_i32(is_pos, is_pos, nn, tot + 1, st));
-    if (cudaMemcpyAsync(h, tot, 8, cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) { rc = GMC_ERR_CUDA; set_error("plan: %s", cudaGetErrorString(cudaGetLastError())); goto fail; }
-    p->n_long = h[0];
+    PLAN_CUDA(cudaMemcpyAsync(h, tot, 8, cudaMemcpyDeviceToHost, st));
+    PLAN_CUDA(cudaStreamSynchronize(st));
+    p->g_n_long = h[0];
     p->n_pos = h[1];
     {
-        const int32_t hot_ids = p->n_long < HOT_CAP - 2 ? p->n_long : HOT_CAP - 2;
+        const int32_t hot_ids = p->g_n_long < HOT_CAP - 2 ? p->g_n_long : HOT_CAP - 2;
         p->hot_n = hot_ids + 1;                             // ids [0, hot_n): the dummy + the hot block
         PLAN_TRY(sort_pairs<uint32_t>(key_a, key_a2, ids, ids2, n, 32, st));
         k_hot_rank<<<gb, 256, 0, st>>>(ids2, n, hot_ids, hot_rank);
@@ -591,41 +630,65 @@ int build_plan(gmc_graph* g, gmc_pr_plan** out, cudaStream_t st) {
         PLAN_TRY(sort_pairs<unsigned long long>(key_b, key_b2, ids, ids2, n, 34, st));
         k_relabel<<<gb, 256, 0, st>>>(ids2, n, p->old_of_new, p->new_of_old);
     }
-    // 2. row offsets of both sections
-    p->n_slices = div_up(n - p->n_long, 32);
-    p->nz_slices = p->n_pos > p->n_long ? div_up(p->n_pos - p->n_long, 32) : 0;     // slices holding a row with in-edges
-    p->z0 = p->n_long + 1 + 32 * p->nz_slices;
-    p->n_ztasks = p->z0 <= n ? div_up(n - p->z0 + 1, ZT) : 0;
+    // 2. global row offsets of both sections, then the shard cuts (host: gmc_shard_cuts)
+    g_n_slices = div_up(n - p->g_n_long, 32);
+    p->g_nz_slices = p->n_pos > p->g_n_long ? div_up(p->n_pos - p->g_n_long, 32) : 0;     // slices holding a row with in-edges
+    p->g_z0 = p->g_n_long + 1 + 32 * p->g_nz_slices;
+    PLAN_TRY(gmc_malloc((void**)&g_lbeg, 4 * ((size_t)p->g_n_long + 1)));
+    PLAN_TRY(gmc_malloc((void**)&g_sbeg, 4 * ((size_t)g_n_slices + 1)));
+    PLAN_TRY(gmc_malloc((void**)&g_scost, 4 * ((size_t)g_n_slices + 1)));
+    k_lengths<<<gb, 256, 0, st>>>(p->old_of_new, indeg, outdeg_old, n, p->g_n_long, g_n_slices, g_lbeg, g_sbeg, g_scost, p->outdeg);
+    PLAN_TRY(exclusive_scan_i32(g_lbeg, g_lbeg, (size_t)p->g_n_long + 1, nullptr, st));
+    PLAN_TRY(exclusive_scan_i32(g_sbeg, g_sbeg, (size_t)g_n_slices + 1, nullptr, st));
+    PLAN_TRY(exclusive_scan_i32(g_scost, g_scost, (size_t)g_n_slices + 1, nullptr, st));
+    h_lbeg.resize((size_t)p->g_n_long + 1); h_sbeg.resize((size_t)g_n_slices + 1); h_scost.resize((size_t)g_n_slices + 1);
+    PLAN_CUDA(cudaMemcpyAsync(h_lbeg.data(), g_lbeg, 4 * h_lbeg.size(), cudaMemcpyDeviceToHost, st));
+    PLAN_CUDA(cudaMemcpyAsync(h_sbeg.data(), g_sbeg, 4 * h_sbeg.size(), cudaMemcpyDeviceToHost, st));
+    PLAN_CUDA(cudaMemcpyAsync(h_scost.data(), g_scost, 4 * h_scost.size(), cudaMemcpyDeviceToHost, st));
+    PLAN_CUDA(cudaStreamSynchronize(st));
+    if (h_lbeg[p->g_n_long] < 0 || h_sbeg[g_n_slices] < 0 || (int64_t)h_lbeg[p->g_n_long] + h_sbeg[g_n_slices] > 0x7fffff00LL) {
+        rc = GMC_ERR_ARG; set_error("pagerank plan: entry array exceeds int32 offsets"); goto fail;
+    }
+    PLAN_TRY(gmc_shard_cuts(h_lbeg.data(), p->g_n_long, world, 1, cutsL.data()));
+    PLAN_TRY(gmc_shard_cuts(h_scost.data(), p->g_nz_slices, world, 1, cutsS.data()));
+    {
+        const int32_t nz = n + 1 - p->g_z0 > 0 ? n + 1 - p->g_z0 : 0;           // ids [g_z0, N] have no in-edges
+        const int32_t per = div_up(div_up(nz, world), ZT) * ZT;
+        for (int r = 0; r <= world; r++) { int64_t c = (int64_t)p->g_z0 + (int64_t)r * per; cutsZ[r] = (int32_t)(c < n + 1 ? c : n + 1); }
+        cutsZ[world] = n + 1;
+    }
+    p->seg_off.assign((size_t)world * 3, 0); p->seg_len.assign((size_t)world * 3, 0);
+    for (int r = 0; r < world; r++) {
+        p->seg_off[r * 3 + 0] = 1 + cutsL[r];                         p->seg_len[r * 3 + 0] = cutsL[r + 1] - cutsL[r];
+        const int64_t sa = (int64_t)p->g_n_long + 1 + 32LL * cutsS[r], sb = (int64_t)p->g_n_long + 1 + 32LL * cutsS[r + 1];
+        p->seg_off[r * 3 + 1] = sa;                                   p->seg_len[r * 3 + 1] = (sb < n + 1 ? sb : n + 1) - sa;
+        p->seg_off[r * 3 + 2] = cutsZ[r];                             p->seg_len[r * 3 + 2] = cutsZ[r + 1] - cutsZ[r];
+    }
+    p->jl0 = cutsL[rank]; jl1 = cutsL[rank + 1]; p->n_long = jl1 - p->jl0;
+    p->s0 = cutsS[rank]; s1 = cutsS[rank + 1]; p->n_slices = s1 - p->s0;
+    p->z0 = cutsZ[rank]; p->z_end = cutsZ[rank + 1];
+    p->n_ztasks = div_up(p->z_end - p->z0, ZT);
+    p->EL = h_lbeg[jl1] - h_lbeg[p->jl0];
+    p->EN = p->EL + (h_sbeg[s1] - h_sbeg[p->s0]);
+    cost_total = h_scost[s1] - h_scost[p->s0];
     PLAN_TRY(gmc_malloc((void**)&p->lbeg, 4 * ((size_t)p->n_long + 1)));
     PLAN_TRY(gmc_malloc((void**)&p->sbeg, 4 * ((size_t)p->n_slices + 1)));
     PLAN_TRY(gmc_malloc((void**)&scost, 4 * ((size_t)p->n_slices + 1)));
-    k_lengths<<<gb, 256, 0, st>>>(p->old_of_new, indeg, outdeg_old, n, p->n_long, p->n_slices, p->lbeg, p->sbeg, scost, p->outdeg);
-    PLAN_TRY(exclusive_scan_i32(p->lbeg, p->lbeg, (size_t)p->n_long + 1, nullptr, st));
-    PLAN_TRY(exclusive_scan_i32(p->sbeg, p->sbeg, (size_t)p->n_slices + 1, nullptr, st));
-    PLAN_TRY(exclusive_scan_i32(scost, scost, (size_t)p->n_slices + 1, nullptr, st));
-    k_add_offset<<<div_up(p->n_slices + 1, 256), 256, 0, st>>>(p->sbeg, p->n_slices + 1, p->lbeg + p->n_long);
-    {
-        int64_t est = (int64_t)m + 3LL * p->n_long + 32LL * S_MAX * 2;   // padding bound (slices mix at most a few lengths)
-        (void)est;
-        if (cudaMemcpyAsync(&h[0], p->lbeg + p->n_long, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
-            cudaMemcpyAsync(&h[1], p->sbeg + p->n_slices, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
-            cudaMemcpyAsync(&cost_total, scost + p->n_slices, 4, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
-            cudaStreamSynchronize(st) != cudaSuccess) { rc = GMC_ERR_CUDA; set_error("plan: %s", cudaGetErrorString(cudaGetLastError())); goto fail; }
-    }
-    p->EL = h[0];
-    p->EN = h[1];
-    if (p->EL < 0 || p->EN < p->EL) { rc = GMC_ERR_ARG; set_error("pagerank plan: entry array exceeds int32 offsets"); goto fail; }
-    // 3. the entry array
+    k_rebase<<<div_up(p->n_long + 1, 256), 256, 0, st>>>(g_lbeg, p->jl0, p->n_long + 1, 0, p->lbeg);
+    k_rebase<<<div_up(p->n_slices + 1, 256), 256, 0, st>>>(g_sbeg, p->s0, p->n_slices + 1, p->EL, p->sbeg);
+    k_rebase<<<div_up(p->n_slices + 1, 256), 256, 0, st>>>(g_scost, p->s0, p->n_slices + 1, 0, scost);
+    // 3. the shard's entry array
     PLAN_TRY(gmc_malloc((void**)&p->E, 4 * ((size_t)p->EN + 8)));
-    if (cudaMemsetAsync(p->E, 0, 4 * ((size_t)p->EN + 8), st) != cudaSuccess) { rc = GMC_ERR_CUDA; goto fail; }
-    if (m > 0) k_fill_entries<<<div_up(m, 256), 256, 0, st>>>(g->r_begin, g->r_node_idx, n, m, p->new_of_old, p->n_long, p->lbeg, p->sbeg, p->E);
+    PLAN_CUDA(cudaMemsetAsync(p->E, 0, 4 * ((size_t)p->EN + 8), st));
+    if (m > 0) k_fill_entries<<<div_up(m, 256), 256, 0, st>>>(g->r_begin, g->r_node_idx, n, m, p->new_of_old, p->g_n_long, p->jl0, p->n_long,
+                                                               p->s0, p->n_slices, p->lbeg, p->sbeg, p->E);
     // 4. tasks
     p->n_ltasks = div_up(p->EL, LT);
     p->n_stasks = div_up(cost_total, ST_COST);
     PLAN_TRY(gmc_malloc((void**)&p->ltask_row, 4 * ((size_t)p->n_ltasks + 1)));
     PLAN_TRY(gmc_malloc((void**)&p->stask_slice, 4 * ((size_t)p->n_stasks + 1)));
     k_ltask_rows<<<div_up(p->n_ltasks + 1, 256), 256, 0, st>>>(p->lbeg, p->n_long, p->n_ltasks, p->ltask_row);
-    k_stask_slices<<<div_up(p->n_stasks + 1, 256), 256, 0, st>>>(scost, p->nz_slices, p->n_stasks, p->stask_slice);
+    k_stask_slices<<<div_up(p->n_stasks + 1, 256), 256, 0, st>>>(scost, p->n_slices, p->n_stasks, p->stask_slice);
     {
         const size_t nl = (size_t)(p->n_ltasks ? p->n_ltasks : 1), nparts = 2 * nl + (size_t)p->n_stasks + (size_t)p->n_ztasks + 1;
         PLAN_TRY(gmc_malloc((void**)&p->head_part, 8 * nl)); PLAN_TRY(gmc_malloc((void**)&p->tail_part, 8 * nl));
@@ -633,18 +696,25 @@ int build_plan(gmc_graph* g, gmc_pr_plan** out, cudaStream_t st) {
         cudaMemsetAsync(p->head_part, 0, 8 * nl, st); cudaMemsetAsync(p->tail_part, 0, 8 * nl, st);
         cudaMemsetAsync(p->split_cnt, 0, 4 * nl, st); cudaMemsetAsync(p->diff_parts, 0, 8 * nparts, st);
     }
-    // 5. state
-    for (int k = 0; k < 2; k++) {
-        PLAN_TRY(gmc_malloc((void**)&p->contrib[k], 8 * (nn + 4)));
-        PLAN_TRY(gmc_malloc((void**)&p->rank[k], 8 * (nn + 4)));
+    // 5. state (replicated on every rank: the gather needs the whole contribution vector)
+    if (state_of) {
+        for (int k = 0; k < 2; k++) { p->contrib[k] = state_of->contrib[k]; p->rank[k] = state_of->rank[k]; }
+        p->ctrl = state_of->ctrl; p->diffs = state_of->diffs;
+    } else {
+        for (int k = 0; k < 2; k++) {
+            PLAN_TRY(gmc_malloc((void**)&p->contrib[k], 8 * (nn + 4)));
+            PLAN_TRY(gmc_malloc((void**)&p->rank[k], 8 * (nn + 4)));
+        }
+        PLAN_TRY(gmc_malloc((void**)&p->ctrl, sizeof(gmc_pr_ctrl)));
+        PLAN_TRY(gmc_malloc((void**)&p->diffs, 8 * (size_t)(world > 1 ? world : 1)));
     }
-    PLAN_TRY(gmc_malloc((void**)&p->ctrl, sizeof(gmc_pr_ctrl)));
     p->grid = sm_count();
     p->smem = (size_t)HOT_CAP * 8;
-    if (cudaFuncSetAttribute(pr_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem) != cudaSuccess ||
-        cudaStreamSynchronize(st) != cudaSuccess) { rc = GMC_ERR_CUDA; set_error("pagerank plan: %s", cudaGetErrorString(cudaGetLastError())); goto fail; }
+    PLAN_CUDA(cudaFuncSetAttribute(pr_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem));
+    PLAN_CUDA(cudaStreamSynchronize(st));
 fail:
     cudaFree(outdeg_old); cudaFree(indeg); cudaFree(ids); cudaFree(ids2); cudaFree(is_long); cudaFree(is_pos); cudaFree(hot_rank); cudaFree(scost);
+    cudaFree(g_lbeg); cudaFree(g_sbeg); cudaFree(g_scost);
     cudaFree(key_a); cudaFree(key_a2); cudaFree(key_b); cudaFree(key_b2); cudaFree(tot);
     if (rc != GMC_OK) { free_plan(p); return rc; }
     *out = p;
@@ -655,14 +725,15 @@ SweepArgs make_args(const gmc_pr_plan* p, double d, int parity, gmc_pr_ctrl* ctr
     SweepArgs A;
     A.E = p->E; A.lbeg = p->lbeg; A.sbeg = p->sbeg; A.ltask_row = p->ltask_row; A.stask_slice = p->stask_slice; A.outdeg = p->outdeg;
     A.N = p->N; A.n_long = p->n_long; A.hot_n = p->hot_n; A.EL = p->EL; A.n_ltasks = p->n_ltasks; A.n_stasks = p->n_stasks;
-    A.n_ztasks = p->n_ztasks; A.z0 = p->z0;
+    A.long_id0 = p->jl0 + 1; A.short_id0 = p->g_n_long + 1 + 32 * p->s0;
+    A.n_ztasks = p->n_ztasks; A.z0 = p->z0; A.z_end = p->z_end;
     A.lt_lo = 0; A.lt_hi = p->n_ltasks; A.st_lo = 0; A.st_hi = p->n_stasks; A.zt_lo = 0; A.zt_hi = p->n_ztasks;
     A.head_part = p->head_part; A.tail_part = p->tail_part; A.split_cnt = p->split_cnt; A.diff_parts = p->diff_parts;
     A.contrib_in = p->contrib[parity]; A.contrib_out = p->contrib[parity ^ 1];
     A.rank_in = p->rank[parity]; A.rank_out = p->rank[parity ^ 1];
     A.d = d;
     A.base = (1 - d) / (double)p->N;     // (1-d) / N, pagerank.gm:11
-    A.ctrl = ctrl; A.e = e; A.max_iter = max_iter; A.mode = 0;
+    A.ctrl = ctrl; A.diff_slot = nullptr; A.e = e; A.max_iter = max_iter; A.mode = 0;
     return A;
 }
 
@@ -685,30 +756,30 @@ void gmc_pr_plan_free(gmc_graph* g) {
     if (g->pr) { free_plan(g->pr); g->pr = nullptr; }
 }
 
-static int graph_plan(gmc_graph* g, cudaStream_t st) {
-    if (g->pr) return GMC_OK;
+static int graph_plan(gmc_graph* g, int world, int rank, cudaStream_t st) {
+    if (g->pr && g->pr->world == world && g->pr->shard == rank) return GMC_OK;
     GMC_REQUIRE(g->has_reverse, GMC_ERR_STATE, "pagerank needs the reverse CSR: call gmc_graph_make_reverse first");
+    gmc_pr_plan_free(g);
     gmc_pr_plan* p = nullptr;
-    GMC_TRY(build_plan(g, &p, st));
+    GMC_TRY(build_plan(g, world, rank, nullptr, &p, st));
     g->pr = p;
     return GMC_OK;
 }
 
-extern "C" {
-
-int gmc_pagerank_dev(gmc_graph* g, double e, double d, int32_t max_iter, double* rank_dev, gmc_pagerank_info* info, void* stream) {
-    GMC_REQUIRE(g && rank_dev, GMC_ERR_ARG, "gmc_pagerank_dev: NULL");
-    GMC_REQUIRE(g->N > 0, GMC_ERR_ARG, "gmc_pagerank_dev: empty graph");
-    cudaStream_t st = as_stream(stream);
-    GMC_TRY(graph_plan(g, st));
-    gmc_pr_plan* p = g->pr;
-    GMC_CUDA(cudaMemsetAsync(p->ctrl, 0, sizeof(gmc_pr_ctrl), st));
+// The iteration loop over a set of shard plans living on this device: one plan and a communicator (a real
+// rank), or `world` plans and no communicator (emulated shards: the exchange is the shared state itself).
+static int run_pagerank(gmc_graph* g, gmc_pr_plan* const* plans, int nplans, gmc_comm* comm, double e, double d, int32_t max_iter,
+                        double* rank_dev, gmc_pagerank_info* info, cudaStream_t st) {
+    gmc_pr_plan* p0 = plans[0];
+    const int world = p0->world;
+    const bool sharded = world > 1;
+    GMC_CUDA(cudaMemsetAsync(p0->ctrl, 0, sizeof(gmc_pr_ctrl), st));
     cudaEvent_t ev0, ev1;
     GMC_CUDA(cudaEventCreate(&ev0));
     GMC_CUDA(cudaEventCreate(&ev1));
     int launches = 0;
     GMC_CUDA(cudaEventRecord(ev0, st));
-    GMC_TRY(launch_init(p, st));
+    GMC_TRY(launch_init(p0, st));
     launches++;
     // do { sweep; cnt++ } while (diff > e && cnt < max): sweeps are enqueued in batches; kernels of a
     // finished loop exit at once on ctrl->done, so the host only synchronises once per batch.
@@ -721,13 +792,28 @@ int gmc_pagerank_dev(gmc_graph* g, double e, double d, int32_t max_iter, double*
         if (todo > BATCH) todo = BATCH;
         if (todo < 1) todo = 1;   // a do-while body runs at least once (max <= 0 still sweeps once)
         for (int32_t k = 0; k < todo; k++, issued++) {
-            GMC_TRY(launch_sweep(p, make_args(p, d, issued & 1, p->ctrl, e, max_iter), st));
-            launches++;
+            for (int i = 0; i < nplans; i++) {
+                SweepArgs A = make_args(plans[i], d, issued & 1, p0->ctrl, e, max_iter);
+                if (sharded) A.diff_slot = p0->diffs + plans[i]->shard;
+                GMC_TRY(launch_sweep(plans[i], A, st));
+                launches++;
+            }
+            if (sharded) {
+                if (comm) {
+                    // the exchange step: every rank's new contributions (3 id ranges per rank) and its diff
+                    GMC_TRY(gmc_comm_allgather_segments(comm, p0->contrib[(issued & 1) ^ 1], 8, p0->seg_off.data(), p0->seg_len.data(), 3, st));
+                    GMC_TRY(gmc_comm_allgather(comm, p0->diffs + p0->shard, p0->diffs, 8, st));
+                }
+                k_ctrl_combine<<<1, 32, 0, st>>>(p0->ctrl, p0->diffs, world, e, max_iter);
+                launches++;
+            }
         }
-        GMC_CUDA(cudaMemcpyAsync(&h, p->ctrl, sizeof(h), cudaMemcpyDeviceToHost, st));
+        GMC_CUDA(cudaMemcpyAsync(&h, p0->ctrl, sizeof(h), cudaMemcpyDeviceToHost, st));
         GMC_CUDA(cudaStreamSynchronize(st));
     } while (!h.done);
-    k_unpermute<<<div_up(g->N, 256), 256, 0, st>>>(p->rank[h.cnt & 1], p->new_of_old, g->N, rank_dev);
+    if (sharded && comm)      // the result vector: gather the owned slices of rank[] once
+        GMC_TRY(gmc_comm_allgather_segments(comm, p0->rank[h.cnt & 1], 8, p0->seg_off.data(), p0->seg_len.data(), 3, st));
+    k_unpermute<<<div_up(g->N, 256), 256, 0, st>>>(p0->rank[h.cnt & 1], p0->new_of_old, g->N, rank_dev);
     launches++;
     GMC_CUDA(cudaEventRecord(ev1, st));
     GMC_CUDA(cudaStreamSynchronize(st));
@@ -741,18 +827,56 @@ int gmc_pagerank_dev(gmc_graph* g, double e, double d, int32_t max_iter, double*
     return GMC_OK;
 }
 
+extern "C" {
+
+int gmc_pagerank_sharded_dev(gmc_graph* g, gmc_comm* comm, double e, double d, int32_t max_iter, double* rank_dev,
+                             gmc_pagerank_info* info, void* stream) {
+    GMC_REQUIRE(g && rank_dev, GMC_ERR_ARG, "gmc_pagerank_dev: NULL");
+    GMC_REQUIRE(g->N > 0, GMC_ERR_ARG, "gmc_pagerank_dev: empty graph");
+    cudaStream_t st = as_stream(stream);
+    const int world = comm ? comm->world : 1, rank = comm ? comm->rank : 0;
+    GMC_TRY(graph_plan(g, world, rank, st));
+    gmc_pr_plan* p = g->pr;
+    return run_pagerank(g, &p, 1, world > 1 ? comm : nullptr, e, d, max_iter, rank_dev, info, st);
+}
+
+int gmc_pagerank_dev(gmc_graph* g, double e, double d, int32_t max_iter, double* rank_dev, gmc_pagerank_info* info, void* stream) {
+    return gmc_pagerank_sharded_dev(g, nullptr, e, d, max_iter, rank_dev, info, stream);
+}
+
+int gmc_pagerank_emulated_shards_dev(gmc_graph* g, int world, double e, double d, int32_t max_iter, double* rank_dev,
+                                     gmc_pagerank_info* info, void* stream) {
+    GMC_REQUIRE(g && rank_dev && world >= 1 && world <= 64, GMC_ERR_ARG, "gmc_pagerank_emulated_shards_dev: bad args");
+    GMC_REQUIRE(g->N > 0, GMC_ERR_ARG, "gmc_pagerank_emulated_shards_dev: empty graph");
+    GMC_REQUIRE(g->has_reverse, GMC_ERR_STATE, "pagerank needs the reverse CSR: call gmc_graph_make_reverse first");
+    cudaStream_t st = as_stream(stream);
+    std::vector<gmc_pr_plan*> plans;
+    int rc = GMC_OK;
+    for (int r = 0; r < world && rc == GMC_OK; r++) {
+        gmc_pr_plan* p = nullptr;
+        rc = build_plan(g, world, r, r ? plans[0] : nullptr, &p, st);
+        if (rc == GMC_OK) plans.push_back(p);
+    }
+    if (rc == GMC_OK) rc = run_pagerank(g, plans.data(), world, nullptr, e, d, max_iter, rank_dev, info, st);
+    for (size_t i = plans.size(); i-- > 0;) free_plan(plans[i]);      // plan 0 (the state owner) last
+    return rc;
+}
+
 // measurement aid for the roofline figure: every sweep bracketed by its own pair of CUDA events
-int gmc_pagerank_time_sweeps(gmc_graph* g, double d, int32_t warmup, int32_t n, float* ms_out, int32_t* launches_per_sweep, void* stream) {
-    GMC_REQUIRE(g && ms_out && n > 0 && warmup >= 0, GMC_ERR_ARG, "gmc_pagerank_time_sweeps: bad args");
+int gmc_pagerank_sharded_time_sweeps(gmc_graph* g, gmc_comm* comm, double d, int32_t warmup, int32_t n, float* sweep_ms,
+                                     float* exchange_ms, void* stream) {
+    GMC_REQUIRE(g && sweep_ms && n > 0 && warmup >= 0, GMC_ERR_ARG, "gmc_pagerank_time_sweeps: bad args");
     GMC_REQUIRE(g->N > 0, GMC_ERR_ARG, "gmc_pagerank_time_sweeps: empty graph");
     cudaStream_t st = as_stream(stream);
-    GMC_TRY(graph_plan(g, st));
+    const int world = comm ? comm->world : 1, rank = comm ? comm->rank : 0;
+    GMC_TRY(graph_plan(g, world, rank, st));
     gmc_pr_plan* p = g->pr;
     GMC_TRY(launch_init(p, st));
-    std::vector<cudaEvent_t> ev(2 * (size_t)n);
+    std::vector<cudaEvent_t> ev(3 * (size_t)n);
     for (auto& e : ev) GMC_CUDA(cudaEventCreate(&e));
     for (int32_t k = 0; k < warmup + n; k++) {
-        if (k >= warmup) GMC_CUDA(cudaEventRecord(ev[2 * (k - warmup)], st));
+        const bool timed = k >= warmup;
+        if (timed) GMC_CUDA(cudaEventRecord(ev[3 * (k - warmup)], st));
         SweepArgs A = make_args(p, d, k & 1, nullptr, 0.0, 0);
         if (const char* md = getenv("GMC_PR_MODE")) { A.mode = atoi(md); if (A.mode & 2) A.hot_n = 1; }
         if (const char* only = getenv("GMC_PR_ONLY")) {      // experiment switch: time one task class alone (results invalid)
@@ -761,13 +885,22 @@ int gmc_pagerank_time_sweeps(gmc_graph* g, double d, int32_t warmup, int32_t n, 
             if (strcmp(only, "zero") != 0) A.zt_hi = 0;
         }
         GMC_TRY(launch_sweep(p, A, st));
-        if (k >= warmup) GMC_CUDA(cudaEventRecord(ev[2 * (k - warmup) + 1], st));
+        if (timed) GMC_CUDA(cudaEventRecord(ev[3 * (k - warmup) + 1], st));
+        if (world > 1) GMC_TRY(gmc_comm_allgather_segments(comm, p->contrib[(k & 1) ^ 1], 8, p->seg_off.data(), p->seg_len.data(), 3, st));
+        if (timed) GMC_CUDA(cudaEventRecord(ev[3 * (k - warmup) + 2], st));
     }
     GMC_CUDA(cudaStreamSynchronize(st));
-    for (int32_t k = 0; k < n; k++) GMC_CUDA(cudaEventElapsedTime(&ms_out[k], ev[2 * k], ev[2 * k + 1]));
+    for (int32_t k = 0; k < n; k++) {
+        GMC_CUDA(cudaEventElapsedTime(&sweep_ms[k], ev[3 * k], ev[3 * k + 1]));
+        if (exchange_ms) GMC_CUDA(cudaEventElapsedTime(&exchange_ms[k], ev[3 * k + 1], ev[3 * k + 2]));
+    }
     for (auto& e : ev) cudaEventDestroy(e);
-    if (launches_per_sweep) *launches_per_sweep = 1;
     return GMC_OK;
+}
+
+int gmc_pagerank_time_sweeps(gmc_graph* g, double d, int32_t warmup, int32_t n, float* ms_out, int32_t* launches_per_sweep, void* stream) {
+    if (launches_per_sweep) *launches_per_sweep = 1;
+    return gmc_pagerank_sharded_time_sweeps(g, nullptr, d, warmup, n, ms_out, nullptr, stream);
 }
 
 int gmc_pagerank(gmc_graph* g, double e, double d, int32_t max_iter, double* rank_host, gmc_pagerank_info* info) {
@@ -785,7 +918,7 @@ int gmc_pagerank(gmc_graph* g, double e, double d, int32_t max_iter, double* ran
 int gmc_pagerank_plan_info(gmc_graph* g, gmc_pagerank_plan_info_t* out) {
     GMC_REQUIRE(g && out, GMC_ERR_ARG, "gmc_pagerank_plan_info: NULL");
     GMC_REQUIRE(g->N > 0, GMC_ERR_ARG, "gmc_pagerank_plan_info: empty graph");
-    GMC_TRY(graph_plan(g, nullptr));
+    if (!g->pr) GMC_TRY(graph_plan(g, 1, 0, nullptr));
     gmc_pr_plan* p = g->pr;
     out->n_long = p->n_long; out->hot_n = p->hot_n; out->n_slices = p->n_slices; out->long_entries = p->EL;
     out->total_entries = p->EN; out->n_long_tasks = p->n_ltasks; out->n_short_tasks = p->n_stasks;

@@ -72,6 +72,17 @@ SIGNATURES = {
     "gmc_bfs_levels": (C.c_int, [_vp, _i32, C.c_int, _vp, _vp, _vp, _i32, C.POINTER(BfsInfo)]),
     "gmc_bfs_levels_masked": (C.c_int, [_vp, _i32, C.c_int, _vp, _vp, _vp, _vp, _i32, C.POINTER(BfsInfo)]),
     "gmc_bfs_level_order": (C.c_int, [_vp, _vp, _vp, _i32]),
+    "gmc_comm_unique_id": (C.c_int, [_vp]),
+    "gmc_comm_create": (C.c_int, [C.POINTER(_vp), C.c_int, C.c_int, _vp]),
+    "gmc_comm_destroy": (C.c_int, [_vp]),
+    "gmc_comm_info": (C.c_int, [_vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "gmc_comm_barrier": (C.c_int, [_vp, _vp]),
+    "gmc_shard_cuts": (C.c_int, [_vp, _i32, C.c_int, _i32, _vp]),
+    "gmc_pagerank_sharded_dev": (C.c_int, [_vp, _vp, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo), _vp]),
+    "gmc_pagerank_emulated_shards_dev": (C.c_int, [_vp, C.c_int, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo), _vp]),
+    "gmc_pagerank_sharded_time_sweeps": (C.c_int, [_vp, _vp, C.c_double, _i32, _i32, _vp, _vp, _vp]),
+    "gmc_hop_dist_sharded_dev": (C.c_int, [_vp, _vp, _i32, _vp, C.POINTER(BfsInfo), _vp]),
+    "gmc_bfs_levels_sharded": (C.c_int, [_vp, _vp, _i32, C.c_int, _vp, _vp, _vp, _vp, _i32, C.POINTER(BfsInfo)]),
 }
 
 
@@ -143,6 +154,25 @@ class GmCuda:
         self.check(self.L.gmc_graph_generate_uniform(C.byref(h), n, m, seed))
         return Graph(self, h)
 
+    # ---- multi-GPU -----------------------------------------------------------------------
+    def comm_unique_id(self):
+        """128 opaque bytes (ncclUniqueId); made on rank 0 and shipped to the other ranks by the host side"""
+        buf = np.zeros(128, np.uint8)
+        self.check(self.L.gmc_comm_unique_id(_ptr(buf)))
+        return buf
+
+    def comm_create(self, world, rank, unique_id=None):
+        h = _vp()
+        uid = None if unique_id is None else np.ascontiguousarray(unique_id, dtype=np.uint8)
+        self.check(self.L.gmc_comm_create(C.byref(h), world, rank, _ptr(uid)))
+        return Comm(self, h, world, rank)
+
+    def shard_cuts(self, prefix, world, align=1):
+        prefix = _i32arr(prefix)
+        cuts = np.zeros(world + 1, np.int32)
+        self.check(self.L.gmc_shard_cuts(_ptr(prefix), len(prefix) - 1, world, align, _ptr(cuts)))
+        return cuts
+
     # ---- files ---------------------------------------------------------------------------
     def file_read(self, path):
         n = _i32(); m = _i32()
@@ -172,6 +202,26 @@ class GmCuda:
 
     def sync(self, stream=None):
         self.check(self.L.gmc_sync(_vp(stream) if stream else None))
+
+
+class Comm:
+    """gmc_comm: this process's rank in a one-process-per-GPU NCCL communicator."""
+
+    def __init__(self, lib, handle, world, rank):
+        self.lib, self.h, self.world, self.rank = lib, handle, world, rank
+
+    def barrier(self, stream=None):
+        self.lib.check(self.lib.L.gmc_comm_barrier(self.h, _vp(stream) if stream else None))
+
+    def nccl_version(self):
+        v = C.c_int()
+        self.lib.check(self.lib.L.gmc_comm_info(self.h, None, None, C.byref(v)))
+        return v.value
+
+    def close(self):
+        if self.h:
+            self.lib.L.gmc_comm_destroy(self.h)
+            self.h = None
 
 
 class Graph:
@@ -240,6 +290,46 @@ class Graph:
         self.lib.check(self.lib.L.gmc_pagerank_dev(self.h, e, d, max_iter, _vp(rank_dev_ptr), C.byref(info),
                                                    _vp(stream) if stream else None))
         return info
+
+    def pagerank_sharded_dev(self, comm, rank_dev_ptr, e=1e-30, d=0.85, max_iter=20, stream=None):
+        info = PagerankInfo()
+        self.lib.check(self.lib.L.gmc_pagerank_sharded_dev(self.h, comm.h if comm else None, e, d, max_iter, _vp(rank_dev_ptr),
+                                                           C.byref(info), _vp(stream) if stream else None))
+        return info
+
+    def pagerank_emulated_shards(self, world, e=1e-30, d=0.85, max_iter=20):
+        """test aid: `world` shard plans swept one after the other on this device; returns host ranks"""
+        n = self.num_nodes
+        dev = self.lib.malloc(8 * max(n, 1))
+        try:
+            info = PagerankInfo()
+            self.lib.check(self.lib.L.gmc_pagerank_emulated_shards_dev(self.h, world, e, d, max_iter, _vp(dev), C.byref(info), None))
+            rank = np.zeros(max(n, 1), np.float64)
+            self.lib.d2h(rank, dev)
+        finally:
+            self.lib.free(dev)
+        return rank[:n], info
+
+    def pagerank_sharded_time_sweeps(self, comm, d=0.85, warmup=3, n=20, stream=None):
+        sw = np.zeros(n, np.float32); ex = np.zeros(n, np.float32)
+        self.lib.check(self.lib.L.gmc_pagerank_sharded_time_sweeps(self.h, comm.h if comm else None, d, warmup, n, _ptr(sw), _ptr(ex),
+                                                                   _vp(stream) if stream else None))
+        return sw, ex
+
+    def hop_dist_sharded_dev(self, comm, dist_dev_ptr, root=0, stream=None):
+        info = BfsInfo()
+        self.lib.check(self.lib.L.gmc_hop_dist_sharded_dev(self.h, comm.h if comm else None, root, _vp(dist_dev_ptr), C.byref(info),
+                                                           _vp(stream) if stream else None))
+        return info
+
+    def bfs_levels_sharded(self, comm, root=0, use_reverse_edge=False, cap=256):
+        lev = np.zeros(max(self.num_nodes, 1), np.int16)
+        trace = np.full(cap, -1, np.int32); cnt = np.zeros(cap, np.int32)
+        info = BfsInfo()
+        self.lib.check(self.lib.L.gmc_bfs_levels_sharded(self.h, comm.h if comm else None, root, int(use_reverse_edge), None, _ptr(lev),
+                                                         _ptr(trace), _ptr(cnt), cap, C.byref(info)))
+        k = min(info.levels, cap)
+        return lev[:self.num_nodes], info, trace[:k], cnt[:k]
 
     def pagerank_plan_info(self):
         pi = PlanInfo()

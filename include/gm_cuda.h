@@ -150,6 +150,40 @@ int gmc_bfs_levels_masked(gmc_graph* g, int32_t root, int use_reverse_edge, cons
  * order_host[N]; level_begin_host[levels+1]. Valid after gmc_bfs_levels on the same graph. */
 int gmc_bfs_level_order(gmc_graph* g, int32_t* order_host, int32_t* level_begin_host, int32_t cap_levels);
 
+/* --- multi-GPU: one process per GPU, destination-vertex ranges per rank.  Shoal's
+ * replicate / partition placement (reference src/backend_cpp/gm_cpp_gen.cc:181-227: shl__malloc_array with
+ * is_ro / is_indexed) becomes: CSR and bitmaps replicated, the streamed entry array / owned rows partitioned.
+ * The communicator wraps NCCL (bound at run time); rank 0 makes the id, the host side ships its 128 bytes to
+ * the other ranks (bench.py uses torch.distributed for that), every rank calls gmc_comm_create. */
+#define GMC_COMM_ID_BYTES 128
+typedef struct gmc_comm gmc_comm;
+int gmc_comm_unique_id(void* id128);
+int gmc_comm_create(gmc_comm** out, int world, int rank, const void* id128);   /* world == 1: no NCCL needed */
+int gmc_comm_destroy(gmc_comm* c);
+int gmc_comm_info(const gmc_comm* c, int* world, int* rank, int* nccl_version);
+int gmc_comm_barrier(gmc_comm* c, void* stream);     /* device-side barrier (1-element allreduce) + stream sync */
+/* host-side balanced partition of a prefix-sum array into `world` contiguous ranges (cuts[world+1]) */
+int gmc_shard_cuts(const int32_t* prefix, int32_t n, int world, int32_t align, int32_t* cuts);
+
+/* PageRank over destination-range shards: rank r sweeps only its share of the entry array, then the new
+ * contributions are allgathered (NCCL over NVLink) before the next sweep; diff is combined in rank order, so
+ * every rank leaves the loop on the same iteration.  rank_dev receives the full vector on every rank. */
+int gmc_pagerank_sharded_dev(gmc_graph* g, gmc_comm* comm, double e, double d, int32_t max_iter, double* rank_dev,
+                             gmc_pagerank_info* info, void* stream);
+/* test aid: the `world` shard sweeps run one after the other on this device (no NCCL): same plan code,
+ * same kernels, same result as a `world`-rank run */
+int gmc_pagerank_emulated_shards_dev(gmc_graph* g, int world, double e, double d, int32_t max_iter, double* rank_dev,
+                                     gmc_pagerank_info* info, void* stream);
+/* per-iteration device times of a sharded run: sweep_ms / exchange_ms [n], measured with CUDA events */
+int gmc_pagerank_sharded_time_sweeps(gmc_graph* g, gmc_comm* comm, double d, int32_t warmup, int32_t n, float* sweep_ms,
+                                     float* exchange_ms, void* stream);
+
+/* BFS over vertex-range shards: per level each rank expands / scans its owned vertices, then the candidate
+ * bitmaps are exchanged with ncclAllGather.  dist_dev / level_host receive the full array on every rank. */
+int gmc_hop_dist_sharded_dev(gmc_graph* g, gmc_comm* comm, int32_t root, int32_t* dist_dev, gmc_bfs_info* info, void* stream);
+int gmc_bfs_levels_sharded(gmc_graph* g, gmc_comm* comm, int32_t root, int use_reverse_edge, const uint8_t* edge_mask_host,
+                           int16_t* level_host, int32_t* state_trace, int32_t* level_count, int32_t trace_cap, gmc_bfs_info* info);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,54 @@
+"""Worker of test_two_rank_nccl_run / gpurun --gpus N checks: every rank builds the same graph, runs the sharded
+PageRank / hop_dist / BFS levels through the C ABI and compares with its own single-GPU run of the same calls."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from gmb200_loader import load_package  # noqa: E402
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", "0"))
+    n, m = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (300000, 4000000)
+    dist.init_process_group("gloo")
+    lib = load_package().GmCuda()
+    lib.init(local)
+    torch.cuda.set_device(local)
+    uid = torch.from_numpy(lib.comm_unique_id() if rank == 0 else np.zeros(128, np.uint8))
+    dist.broadcast(uid, 0)
+    comm = lib.comm_create(world, rank, uid.numpy())
+    g = lib.generate_rmat(n, m, 1997)
+    out = torch.empty(n, dtype=torch.float64, device="cuda")
+    info = g.pagerank_sharded_dev(comm, out.data_ptr(), 1e-30, 0.85, 20)
+    sharded = out.cpu().numpy()
+    one, info1 = g.pagerank(1e-30, 0.85, 20)
+    assert info.iterations == info1.iterations == 20
+    err = float(np.abs(sharded - one).max())
+    assert err <= 1e-12, f"rank {rank}: sharded pagerank differs from single-GPU by {err}"
+    # every rank must hold the same bits
+    ref = torch.from_numpy(sharded.copy()); dist.broadcast(ref, 0)
+    assert np.array_equal(ref.numpy(), sharded), "ranks disagree on the PageRank vector"
+    deg = np.diff(g.array("begin"))
+    for root in [int(np.nonzero(deg)[0][0]), int(np.argmax(deg))]:
+        d_dev = torch.empty(n, dtype=torch.int32, device="cuda")
+        bi = g.hop_dist_sharded_dev(comm, d_dev.data_ptr(), root)
+        d_one, bi1 = g.hop_dist(root)
+        assert np.array_equal(d_dev.cpu().numpy(), d_one), f"rank {rank}: sharded hop_dist differs (root {root})"
+        assert bi.levels == bi1.levels and bi.reached == bi1.reached
+        lev, li, trace, cnt = g.bfs_levels_sharded(comm, root)
+        lev1, li1, trace1, cnt1 = g.bfs_levels(root)
+        assert np.array_equal(lev, lev1) and list(trace) == list(trace1) and list(cnt) == list(cnt1)
+    comm.barrier()
+    if rank == 0:
+        print(f"multi_gpu_worker ok: world {world}, pagerank max|sharded-single| = {err:.3e}, nccl {comm.nccl_version()}", flush=True)
+    comm.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
