@@ -122,6 +122,7 @@ __device__ __forceinline__ int window_search(int32_t e, int32_t pos) {
         const int32_t ek = __shfl_sync(FULLMASK, e, k + s - 1);
         if (ek <= pos) k += s;
     }
+    if (__shfl_sync(FULLMASK, e, 31) <= pos) k = 32;      // beyond the 32-row window
     return k;
 }
 

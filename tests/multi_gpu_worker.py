@@ -38,7 +38,14 @@ def main():
         d_dev = torch.empty(n, dtype=torch.int32, device="cuda")
         bi = g.hop_dist_sharded_dev(comm, d_dev.data_ptr(), root)
         d_one, bi1 = g.hop_dist(root)
-        assert np.array_equal(d_dev.cpu().numpy(), d_one), f"rank {rank}: sharded hop_dist differs (root {root})"
+        d_sh = d_dev.cpu().numpy()
+        if not np.array_equal(d_sh, d_one):
+            bad = np.nonzero(d_sh != d_one)[0]
+            lev_s, _, tr_s, cnt_s = g.bfs_levels_sharded(comm, root)
+            lev_1, _, tr_1, cnt_1 = g.bfs_levels(root)
+            raise AssertionError(f"rank {rank}: sharded hop_dist differs (root {root}): {len(bad)} vertices, first {bad[:8]}, "
+                                 f"sharded {d_sh[bad[:8]]} single {d_one[bad[:8]]}; levels {bi.levels}/{bi1.levels} reached {bi.reached}/{bi1.reached}; "
+                                 f"trace sharded {list(tr_s)} {list(cnt_s)} single {list(tr_1)} {list(cnt_1)}")
         assert bi.levels == bi1.levels and bi.reached == bi1.reached
         lev, li, trace, cnt = g.bfs_levels_sharded(comm, root)
         lev1, li1, trace1, cnt1 = g.bfs_levels(root)

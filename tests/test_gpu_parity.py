@@ -237,3 +237,47 @@ def test_device_generators(gm, oracle):
     du = gm.generate_uniform(n, m, seed=5)
     bu = du.array("begin")
     assert bu[-1] == m and np.diff(bu).max() < 64
+
+
+def test_bfs_many_low_degree_rows(gm, oracle):
+    """top-down chunks that span far more than 32 frontier rows (degree-0/1 vertices): a root fanning out to
+    6000 vertices, every third of them a dead end, the others with one edge into a long tail"""
+    k = 6000
+    edges = [(0, 1 + i) for i in range(k)]
+    edges += [(1 + i, 1 + k + i) for i in range(k) if i % 3]                 # degree 0 / 1 rows interleaved
+    edges += [(1 + k + i, 1 + 2 * k + (i // 7)) for i in range(k) if i % 3]  # converge 7:1
+    n = 1 + 2 * k + k // 7 + 2
+    g = graphs.from_edges(oracle, n, edges)
+    for has_rev in (True, False):
+        dg = dev_graph(gm, g) if has_rev else gm.graph_from_csr(g["begin"], g["node_idx"], semi_sort=False, make_reverse=False)
+        dist, info = dg.hop_dist(0)
+        want, _ = oracle.hop_dist(g["begin"], g["node_idx"], 0)
+        assert np.array_equal(dist, want)
+        assert info.levels == 4
+
+
+@pytest.mark.parametrize("n,m", [(300000, 4000000), (50000, 5000000)])
+def test_bfs_invariants_device_graph(gm, n, m):
+    """size-independent BFS properties on a device-generated R-MAT graph, several roots, repeated runs:
+    no edge (u,v) with dist[v] > dist[u]+1, every reached vertex has a parent at dist-1, runs repeat bit for bit"""
+    g = gm.generate_rmat(n, m, 1997)
+    b, idx = g.array("begin"), g.array("node_idx")
+    deg = np.diff(b)
+    src = np.repeat(np.arange(n, dtype=np.int32), deg)
+    roots = [int(np.nonzero(deg)[0][0]), int(np.argmax(deg)), int(np.nonzero(deg == 1)[0][0])]
+    for root in roots:
+        first = None
+        for _ in range(3):
+            d, _ = g.hop_dist(root)
+            if first is None:
+                first = d.copy()
+            assert np.array_equal(d, first)
+        du, dv = first[src].astype(np.int64), first[idx].astype(np.int64)
+        assert not np.any((du < INT_MAX) & (dv > du + 1))
+        best = np.full(n, INT_MAX, np.int64)
+        np.minimum.at(best, idx, np.where(du < INT_MAX, du + 1, INT_MAX))
+        reached = (first < INT_MAX) & (np.arange(n) != root)
+        assert np.array_equal(best[reached], first[reached].astype(np.int64)) and first[root] == 0
+        lev, _, _, cnt = g.bfs_levels(root)
+        assert np.array_equal(np.where(lev >= 0, lev.astype(np.int64), INT_MAX), first.astype(np.int64))
+        assert cnt.sum() == int((first < INT_MAX).sum())
