@@ -1,0 +1,49 @@
+"""The drop-in check: the reference's UNCHANGED drivers -- apps/output_cpp/src/pagerank_main.cc,
+hop_dist_main.cc, gm_graph/src/graph_gen_main.cc, compiled from /root/reference against include/gm and linked to
+libgm_cuda.so (green-marl_b200/Makefile, target apps; the binaries travel to the GPU box prebuilt) -- run with the
+reference's command lines and print the reference's result lines with the oracle's values."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "green-marl_b200", "bin")
+
+
+def run(exe, *args):
+    path = os.path.join(BIN, exe)
+    assert os.path.exists(path), f"{path} missing: run __graft_entry__.build() where /root/reference is present"
+    r = subprocess.run([path] + [str(a) for a in args], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    return r.stdout
+
+
+def test_reference_drivers_run_unchanged(gm, oracle, tmp_path):
+    f = str(tmp_path / "c1.bin")
+    # graph_gen <N> <M> <file> <type 0 = uniform multigraph>, seed 1997 (graph_gen_main.cc:20-61)
+    run("graph_gen", 65536, 1048576, f, 0)
+    b, i = oracle.uniform_random(65536, 1048576, 1997)
+    want = str(tmp_path / "want.bin")
+    assert oracle.store_binary(want, b, i)                     # the generator stores the rows as filled, unsorted
+    assert open(f, "rb").read() == open(want, "rb").read(), "graph_gen output differs from the reference's file"
+    i = np.ascontiguousarray(i).copy()
+    oracle.semi_sort(b, i)                                     # load_binary ends with do_semi_sort
+    rb, ri = oracle.make_reverse(b, i)
+
+    # pagerank <graph> <threads> <nfs> [max_iter] [e] [d]   (pagerank_main.cc:11-16,50-62)
+    out = run("pagerank", f, 4, "/dev/null", 20, 1e-30, 0.85)
+    rank, it, _ = oracle.pagerank(b, rb, ri, 1e-30, 0.85, 20)
+    got = [float(x) for x in re.findall(r"rank\[\d\] = ([0-9.]+)", out)]
+    assert len(got) == 4 and it == 20
+    assert got == [float("%0.9f" % v) for v in rank[:4]]
+    assert "running time=" in out and "reverse edge creation time=" in out and "CRC shl__G_pg_rank" in out
+
+    # hop_dist <graph> <threads> <nfs>: root 0, prints dist[0..9]  (hop_dist_main.cc:21,37)
+    out = run("hop_dist", f, 4, "/dev/null")
+    dist, _ = oracle.hop_dist(b, i, 0)
+    got = [int(x) for x in re.findall(r"dist\[\d\] = (-?\d+)", out)]
+    assert got == [int(v) for v in dist[:10]]
