@@ -104,9 +104,11 @@ def run_multi(args, n, m, workload):
     roofline = {"bound": "hbm", "achieved": round(a_bytes / avg_sweep / 1e6, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(a_bytes / avg_sweep / 1e6 / peak, 4), "traffic": None, "peak_kind": peak_kind, "kernel": "pr_sweep (one shard)",
                 "alg_bytes_per_launch": int(a_bytes), "avg_launch_ms": round(avg_sweep, 5),
-                "exchange": {"what": "NCCL grouped broadcasts of the owned contribution ranges (allgather), per sweep",
+                "exchange": {"path": g.pagerank_exchange_path(),
+                             "what": "peer-memory: contributions stored into the peers' HBM over NVLink from the sweep epilogue, avg_ms = wait for the peers' flags; "
+                                     "nccl: grouped broadcasts of the owned contribution ranges after the sweep",
                              "avg_ms": round(avg_exch, 5), "recv_bytes_per_rank": int(8 * n * (world - 1) / world),
-                             "recv_gbs_per_rank": round(8 * n * (world - 1) / world / avg_exch / 1e6, 1) if avg_exch > 0 else None,
+                             "recv_gbs_per_rank": round(8 * n * (world - 1) / world / ((avg_sweep + avg_exch) if g.pagerank_exchange_path() == "peer-memory" else avg_exch) / 1e6, 1),
                              "nvlink_peak_gbs_per_dir": 900.0}}
 
     # ---- BFS (configs[4]): sharded hop_dist over a few roots, device time = max over ranks ----------------
@@ -155,6 +157,7 @@ def run_multi(args, n, m, workload):
             out = torch.empty(n, dtype=torch.float64, device="cuda")
             dg.pagerank_sharded_dev(comm, out.data_ptr(), 1e-30, 0.85, iters)
             lib.d2h(rank_host, out.data_ptr())
+            comm.barrier()          # nobody unmaps / frees its state block while a peer may still store into it
             dg.close()
             lib.sync(); dist.barrier()
             if k > 0:
@@ -173,7 +176,7 @@ def run_multi(args, n, m, workload):
                        "graph": "device R-MAT generator seed 1997 a=.57 b=.19 c=.19 permuted (counter-based RNG), identical on every rank",
                        "generate_s": round(gen_s, 2), "first_calls_s": round(warm_s, 2),
                        "l2": "inputs larger than L2 (index stream %d MB per rank per sweep); no explicit flush" % (4 * m // world // 2**20),
-                       "parallelism": f"{world} ranks x 1 GPU, destination-range shards, NCCL allgather of contributions per sweep"},
+                       "parallelism": f"{world} ranks x 1 GPU, destination-range shards, contributions exchanged per sweep (" + g.pagerank_exchange_path() + ")"},
             "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": None, "bfs": bfs,
             "nccl_version": comm.nccl_version(),
         }

@@ -12,6 +12,7 @@
 #include <dlfcn.h>
 #include <stdlib.h>
 #include <mutex>
+#include <vector>
 
 using namespace gmc;
 
@@ -122,6 +123,59 @@ int gmc_comm_allgather_segments(gmc_comm* c, void* buf, size_t elem_bytes, const
         }
     GMC_NCCL(g_api.GroupEnd());
     return GMC_OK;
+}
+
+// Peer mapping of one device allocation per rank (cudaMalloc'ed, `local_base` = its base address): the CUDA IPC
+// handles travel through the communicator itself (in-place allgather of 64-byte handles), every rank opens the
+// other ranks' handles.  peer_bases[r] = rank r's block as seen from this process (own rank: local_base).
+// Returns GMC_ERR_STATE when IPC is not available (callers fall back to NCCL for the data path).
+int gmc_comm_ipc_open_all(gmc_comm* c, void* local_base, void** peer_bases, cudaStream_t st) {
+    GMC_REQUIRE(c && c->world > 1 && local_base && peer_bases, GMC_ERR_ARG, "gmc_comm_ipc_open_all: bad args");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    if (getenv("GMC_NO_P2P")) { set_error("peer mapping disabled by GMC_NO_P2P"); return GMC_ERR_STATE; }
+    cudaIpcMemHandle_t mine;
+    if (cudaIpcGetMemHandle(&mine, local_base) != cudaSuccess) {
+        set_error("cudaIpcGetMemHandle: %s", cudaGetErrorString(cudaGetLastError()));
+        return GMC_ERR_STATE;
+    }
+    std::vector<cudaIpcMemHandle_t> all((size_t)c->world);
+    char* stage = nullptr;
+    GMC_TRY(gmc_malloc((void**)&stage, 64 * (size_t)c->world));
+    int rc = GMC_OK;
+    if (cudaMemcpyAsync(stage + 64 * (size_t)c->rank, &mine, 64, cudaMemcpyHostToDevice, st) != cudaSuccess) rc = GMC_ERR_CUDA;
+    if (rc == GMC_OK) rc = gmc_comm_allgather(c, stage + 64 * (size_t)c->rank, stage, 64, st);
+    if (rc == GMC_OK && (cudaMemcpyAsync(all.data(), stage, 64 * (size_t)c->world, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+                         cudaStreamSynchronize(st) != cudaSuccess)) rc = GMC_ERR_CUDA;
+    cudaFree(stage);
+    if (rc != GMC_OK) { set_error("gmc_comm_ipc_open_all: handle exchange failed"); return rc; }
+    int ok = 1;
+    for (int r = 0; r < c->world; r++) {
+        peer_bases[r] = nullptr;
+        if (r == c->rank) { peer_bases[r] = local_base; continue; }
+        if (ok && cudaIpcOpenMemHandle(&peer_bases[r], all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+            set_error("cudaIpcOpenMemHandle(rank %d): %s", r, cudaGetErrorString(cudaGetLastError()));
+            peer_bases[r] = nullptr;
+            ok = 0;
+        }
+    }
+    // every rank must take the same path: agree on success
+    long long *flag = nullptr, h = ok;
+    GMC_TRY(gmc_malloc((void**)&flag, 16));
+    cudaMemcpyAsync(flag, &h, 8, cudaMemcpyHostToDevice, st);
+    rc = gmc_comm_allreduce_sum_i64(c, flag, flag + 1, 1, st);
+    if (rc == GMC_OK && (cudaMemcpyAsync(&h, flag + 1, 8, cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess)) rc = GMC_ERR_CUDA;
+    cudaFree(flag);
+    if (rc == GMC_OK && h != c->world) rc = GMC_ERR_STATE;
+    if (rc != GMC_OK) {
+        for (int r = 0; r < c->world; r++)
+            if (r != c->rank && peer_bases[r]) { cudaIpcCloseMemHandle(peer_bases[r]); peer_bases[r] = nullptr; }
+    }
+    return rc;
+}
+
+void gmc_comm_ipc_close_all(int world, int rank, void** peer_bases) {
+    for (int r = 0; r < world; r++)
+        if (r != rank && peer_bases[r]) { cudaIpcCloseMemHandle(peer_bases[r]); peer_bases[r] = nullptr; }
 }
 
 extern "C" {

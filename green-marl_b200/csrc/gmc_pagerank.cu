@@ -59,8 +59,13 @@ struct gmc_pr_ctrl {   // device-side loop control: lets the host enqueue sweeps
     int32_t cnt;
     int32_t done;
     unsigned int arrived;
+    unsigned int next;      // dynamic task counter of the running sweep (reset by its last CTA)
+    int32_t error;          // 1: a peer's end-of-sweep flag did not arrive in time (sharded runs)
     int32_t pad;
 };
+constexpr int MAX_PEERS = 7;            // peer-memory exchange up to 8 ranks (one NVSwitch domain); beyond: NCCL
+constexpr int SYNC_RANKS = 64;          // slots of the sync area at the end of the state block
+constexpr long long PEER_TIMEOUT_CYCLES = 8000000000LL;    // ~4 s at 1.9 GHz: a dead peer fails the call, not the box
 
 struct SweepArgs {
     // layout
@@ -85,10 +90,20 @@ struct SweepArgs {
     const double* __restrict__ rank_in;      // [N+1]
     double* rank_out;
     double d, base;
-    // loop control (may be null); diff_slot != null: sharded run, the shard's diff goes there and the
-    // loop control is advanced by k_ctrl_combine once every shard's diff is known
+    // loop control.  loop == 0: a free-standing sweep (timing aid), cnt/done untouched.  diff_slot != null: sharded
+    // run, the shard's diff goes there and the loop control is advanced by k_ctrl_combine once every shard's
+    // diff is known
     gmc_pr_ctrl* ctrl;
     double* diff_slot;
+    int32_t loop;
+    // peer-memory exchange (sharded, ranks mapped with CUDA IPC): every new contribution is also stored into the
+    // peers' contrib_out over NVLink from the row epilogue; the last CTA publishes diff + the sweep's sequence number
+    int32_t npeers;
+    unsigned int seq;
+    unsigned int* my_flag;
+    double* peer_out[MAX_PEERS];
+    double* peer_diff[MAX_PEERS];
+    unsigned int* peer_flag[MAX_PEERS];
     double e;
     int32_t max_iter;
     int32_t mode;                            // experiment switches (GMC_EXPERIMENT builds only)
@@ -102,7 +117,14 @@ struct gmc_pr_plan {
     // this shard: long rows [jl0, jl0+n_long), slices [s0, s0+n_slices), zero ids [z0, z_end)
     int32_t jl0 = 0, n_long = 0, s0 = 0, n_slices = 0, EL = 0, EN = 0, n_ltasks = 0, n_stasks = 0, n_ztasks = 0, z0 = 0, z_end = 0;
     std::vector<int64_t> seg_off, seg_len;    // [world][3] owned id ranges of every rank (long, short, zero)
-    double* diffs = nullptr;                  // [world] per-shard diffs of the current iteration
+    // state block (one allocation, so that one CUDA IPC handle maps it into the peers):
+    //   contrib[0] [N+4] | contrib[1] [N+4] | diffs [2][SYNC_RANKS] doubles | flags [SYNC_RANKS] u32
+    double* block = nullptr;
+    double* diffs = nullptr;                  // per-shard diffs, double-buffered by sweep parity
+    unsigned int* flags = nullptr;            // flags[r] = sequence number of rank r's last completed sweep
+    bool p2p = false;                         // peers mapped: contributions are pushed from the sweep epilogue
+    void* peer_base[MAX_PEERS + 1] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    unsigned int seq = 0;                     // sweeps issued so far (identical on every rank)
     int32_t *new_of_old = nullptr, *old_of_new = nullptr, *E = nullptr, *lbeg = nullptr, *sbeg = nullptr;
     int32_t *ltask_row = nullptr, *stask_slice = nullptr, *outdeg = nullptr;
     double *head_part = nullptr, *tail_part = nullptr, *diff_parts = nullptr;
@@ -155,13 +177,29 @@ __device__ __forceinline__ double gather(const double* hot, const SweepArgs& A, 
     return (w < A.hot_n) ? hot[w] : __ldg(A.contrib_in + w);
 }
 
+// new contribution of vertex id: local copy + one copy per peer (fire-and-forget NVLink stores, coalesced across lanes)
+__device__ __forceinline__ void put_contrib(const SweepArgs& A, int32_t id, double c) {
+    A.contrib_out[id] = c;
+#pragma unroll
+    for (int p = 0; p < MAX_PEERS; p++)
+        if (p < A.npeers) A.peer_out[p][id] = c;
+}
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
 // per-row epilogue; mul and add kept separate (no FMA contraction) to match the CPU build's rounding
 __device__ __forceinline__ double finish_row(const SweepArgs& A, int32_t id, double S) {
     const double val = __dadd_rn(A.base, __dmul_rn(A.d, S));
     const double old = __ldcs(A.rank_in + id);
     __stcs(A.rank_out + id, val);
     const int32_t od = __ldcs(A.outdeg + id);
-    A.contrib_out[id] = od > 0 ? val / (double)od : 0.0;
+    put_contrib(A, id, od > 0 ? val / (double)od : 0.0);
     return fabs(__dsub_rn(val, old));
 }
 
@@ -316,7 +354,7 @@ __device__ __forceinline__ void short_task(const SweepArgs& A, const double* hot
             if (id <= A.N) {
                 const double val = __dadd_rn(A.base, __dmul_rn(A.d, S));
                 __stcs(A.rank_out + id, val);
-                A.contrib_out[id] = od > 0 ? val / (double)od : 0.0;
+                put_contrib(A, id, od > 0 ? val / (double)od : 0.0);
                 diff += fabs(__dsub_rn(val, old));
             }
             S = 0.0;
@@ -349,7 +387,7 @@ __device__ __forceinline__ void zero_task(const SweepArgs& A, int lane, int32_t 
             if (id < A.z_end) {
                 const double val = A.base;                       // (1-d)/N + d*0
                 __stcs(A.rank_out + id, val);
-                A.contrib_out[id] = od[k] > 0 ? val / (double)od[k] : 0.0;
+                put_contrib(A, id, od[k] > 0 ? val / (double)od[k] : 0.0);
                 diff += fabs(__dsub_rn(val, old[k]));
             }
         }
@@ -359,7 +397,7 @@ __device__ __forceinline__ void zero_task(const SweepArgs& A, int lane, int32_t 
 }
 
 __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
-    if (A.ctrl && A.ctrl->done) return;
+    if (A.loop && A.ctrl->done) return;
     extern __shared__ __align__(16) double hot[];
     __shared__ __align__(8) unsigned long long bar;
     __shared__ double s_red[PR_WARPS];
@@ -378,20 +416,23 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
     }
     mbar_wait(&bar, 0);
 
-    // tasks: static round-robin over all warps of the grid, long-row tasks first
+    // tasks, long-row tasks first: a warp's first task is static, the following ones come from a device-wide
+    // counter (task costs vary with the row mix; a static round-robin left a tail of ~10 % at the final barrier)
     const int32_t n_l = A.lt_hi - A.lt_lo, n_s = A.st_hi - A.st_lo, n_z = A.zt_hi - A.zt_lo;
-    const int32_t stride = gridDim.x * PR_WARPS;
-    for (int32_t u = blockIdx.x * PR_WARPS + warp; u < n_l + n_s + n_z; u += stride) {
+    const int32_t total = n_l + n_s + n_z, nwarps = gridDim.x * PR_WARPS;
+    int32_t u = blockIdx.x * PR_WARPS + warp;
+    while (u < total) {
         if (u < n_l) long_task(A, hot, lane, A.lt_lo + u);
         else if (u < n_l + n_s) short_task(A, hot, lane, A.st_lo + (u - n_l));
         else zero_task(A, lane, A.zt_lo + (u - n_l - n_s));
+        if (lane == 0) u = nwarps + (int32_t)atomicAdd(&A.ctrl->next, 1u);
+        u = __shfl_sync(FULL, u, 0);
     }
 
-    if (!A.ctrl) return;
     // the last CTA adds the per-task diff partials in a fixed order and advances the loop control
     __syncthreads();
     if (tid == 0) {
-        __threadfence();
+        if (A.npeers > 0) __threadfence_system(); else __threadfence();
         s_last = (atomicAdd(&A.ctrl->arrived, 1u) == gridDim.x - 1);
     }
     __syncthreads();
@@ -405,15 +446,20 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
     __syncthreads();
     if (warp == 0) {
         double t = butterfly(s_red[lane]);
+        if (lane == 0) { A.ctrl->arrived = 0u; A.ctrl->next = 0u; }
         if (lane == 0 && A.diff_slot) {
             *A.diff_slot = t;
-            A.ctrl->arrived = 0u;
-        } else if (lane == 0) {
+            for (int p = 0; p < A.npeers; p++) *A.peer_diff[p] = t;
+        } else if (lane == 0 && A.loop) {
             const int32_t cnt = A.ctrl->cnt + 1;
             A.ctrl->diff = t;
             A.ctrl->cnt = cnt;
             A.ctrl->done = !((t > A.e) && (cnt < A.max_iter));       // } While ((diff > e) && (cnt < max))
-            A.ctrl->arrived = 0u;
+        }
+        if (lane == 0 && A.my_flag) {      // every store of this sweep (all CTAs) is ordered before the flags
+            __threadfence_system();
+            *A.my_flag = A.seq;
+            for (int p = 0; p < A.npeers; p++) st_release_sys(A.peer_flag[p], A.seq);
         }
     }
 }
@@ -547,10 +593,27 @@ __global__ void k_unpermute(const double* __restrict__ rank_new, const int32_t* 
     if (v < n) out[v] = rank_new[new_of_old[v]];
 }
 // sharded loop control: diff = sum of the shards' diffs in rank order; cnt++; done = !(diff > e && cnt < max)
-__global__ void k_ctrl_combine(gmc_pr_ctrl* ctrl, const double* __restrict__ diffs, int world, double e, int32_t max_iter) {
+// wait until every rank has published sequence number `seq` (its sweep, with all its remote stores, is complete)
+__device__ bool wait_peers(const unsigned int* flags, int world, unsigned int seq) {
+    for (int r = 0; r < world; r++) {
+        const long long t0 = clock64();
+        while ((int)(ld_acquire_sys(flags + r) - seq) < 0) {
+            if (clock64() - t0 > PEER_TIMEOUT_CYCLES) return false;
+            __nanosleep(200);
+        }
+    }
+    return true;
+}
+__global__ void k_wait_peers(gmc_pr_ctrl* ctrl, const unsigned int* flags, int world, unsigned int seq) {
+    if (threadIdx.x != 0 || blockIdx.x != 0 || ctrl->error) return;
+    if (!wait_peers(flags, world, seq)) ctrl->error = 1;
+}
+__global__ void k_ctrl_combine(gmc_pr_ctrl* ctrl, const double* diffs, int world, double e, int32_t max_iter,
+                               const unsigned int* flags, unsigned int seq) {
     if (threadIdx.x != 0 || blockIdx.x != 0 || ctrl->done) return;
+    if (flags && !wait_peers(flags, world, seq)) { ctrl->error = 1; ctrl->done = 1; return; }
     double t = 0.0;
-    for (int r = 0; r < world; r++) t += diffs[r];
+    for (int r = 0; r < world; r++) t += __ldcg(diffs + r);
     const int32_t cnt = ctrl->cnt + 1;
     ctrl->diff = t;
     ctrl->cnt = cnt;
@@ -576,7 +639,8 @@ void free_plan(gmc_pr_plan* p) {
     cudaFree(p->ltask_row); cudaFree(p->stask_slice); cudaFree(p->outdeg);
     cudaFree(p->head_part); cudaFree(p->tail_part); cudaFree(p->diff_parts); cudaFree(p->split_cnt);
     if (p->owns_state) {
-        cudaFree(p->contrib[0]); cudaFree(p->contrib[1]); cudaFree(p->rank[0]); cudaFree(p->rank[1]); cudaFree(p->ctrl); cudaFree(p->diffs);
+        if (p->p2p) gmc_comm_ipc_close_all(p->world, p->shard, p->peer_base);
+        cudaFree(p->block); cudaFree(p->rank[0]); cudaFree(p->rank[1]); cudaFree(p->ctrl);
     }
     delete p;
 }
@@ -699,14 +763,17 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
     // 5. state (replicated on every rank: the gather needs the whole contribution vector)
     if (state_of) {
         for (int k = 0; k < 2; k++) { p->contrib[k] = state_of->contrib[k]; p->rank[k] = state_of->rank[k]; }
-        p->ctrl = state_of->ctrl; p->diffs = state_of->diffs;
+        p->ctrl = state_of->ctrl; p->diffs = state_of->diffs; p->flags = state_of->flags;
     } else {
-        for (int k = 0; k < 2; k++) {
-            PLAN_TRY(gmc_malloc((void**)&p->contrib[k], 8 * (nn + 4)));
-            PLAN_TRY(gmc_malloc((void**)&p->rank[k], 8 * (nn + 4)));
-        }
+        if (world > SYNC_RANKS) { rc = GMC_ERR_ARG; set_error("pagerank: at most %d shards", SYNC_RANKS); goto fail; }
+        const size_t stride = nn + 4, sync_doubles = 2 * SYNC_RANKS + SYNC_RANKS / 2;
+        PLAN_TRY(gmc_malloc((void**)&p->block, 8 * (2 * stride + sync_doubles)));
+        p->contrib[0] = p->block; p->contrib[1] = p->block + stride;
+        p->diffs = p->block + 2 * stride;
+        p->flags = reinterpret_cast<unsigned int*>(p->block + 2 * stride + 2 * SYNC_RANKS);
+        PLAN_CUDA(cudaMemsetAsync(p->diffs, 0, 8 * sync_doubles, st));
+        for (int k = 0; k < 2; k++) PLAN_TRY(gmc_malloc((void**)&p->rank[k], 8 * (nn + 4)));
         PLAN_TRY(gmc_malloc((void**)&p->ctrl, sizeof(gmc_pr_ctrl)));
-        PLAN_TRY(gmc_malloc((void**)&p->diffs, 8 * (size_t)(world > 1 ? world : 1)));
     }
     p->grid = sm_count();
     p->smem = (size_t)HOT_CAP * 8;
@@ -721,24 +788,50 @@ fail:
     return GMC_OK;
 }
 
-SweepArgs make_args(const gmc_pr_plan* p, double d, int parity, gmc_pr_ctrl* ctrl, double e, int32_t max_iter) {
+// sweep: index of the sweep inside the call (0-based).  From the third sweep on the rows without in-edges are
+// skipped: their value is the constant (1-d)/N, both ping-pong buffers hold it (and its contribution) after two
+// sweeps, and their |val - old| is exactly 0 -- the stored diff partials of sweep 1 stay valid.
+SweepArgs make_args(const gmc_pr_plan* p, double d, int sweep, gmc_pr_ctrl* ctrl, int loop, double e, int32_t max_iter) {
+    const int parity = sweep & 1;
     SweepArgs A;
     A.E = p->E; A.lbeg = p->lbeg; A.sbeg = p->sbeg; A.ltask_row = p->ltask_row; A.stask_slice = p->stask_slice; A.outdeg = p->outdeg;
     A.N = p->N; A.n_long = p->n_long; A.hot_n = p->hot_n; A.EL = p->EL; A.n_ltasks = p->n_ltasks; A.n_stasks = p->n_stasks;
     A.long_id0 = p->jl0 + 1; A.short_id0 = p->g_n_long + 1 + 32 * p->s0;
     A.n_ztasks = p->n_ztasks; A.z0 = p->z0; A.z_end = p->z_end;
-    A.lt_lo = 0; A.lt_hi = p->n_ltasks; A.st_lo = 0; A.st_hi = p->n_stasks; A.zt_lo = 0; A.zt_hi = p->n_ztasks;
+    A.lt_lo = 0; A.lt_hi = p->n_ltasks; A.st_lo = 0; A.st_hi = p->n_stasks; A.zt_lo = 0; A.zt_hi = sweep >= 2 ? 0 : p->n_ztasks;
     A.head_part = p->head_part; A.tail_part = p->tail_part; A.split_cnt = p->split_cnt; A.diff_parts = p->diff_parts;
     A.contrib_in = p->contrib[parity]; A.contrib_out = p->contrib[parity ^ 1];
     A.rank_in = p->rank[parity]; A.rank_out = p->rank[parity ^ 1];
     A.d = d;
     A.base = (1 - d) / (double)p->N;     // (1-d) / N, pagerank.gm:11
-    A.ctrl = ctrl; A.diff_slot = nullptr; A.e = e; A.max_iter = max_iter; A.mode = 0;
+    A.ctrl = ctrl; A.loop = loop; A.diff_slot = nullptr; A.e = e; A.max_iter = max_iter; A.mode = 0;
+    A.npeers = 0; A.seq = 0; A.my_flag = nullptr;
+    for (int q = 0; q < MAX_PEERS; q++) { A.peer_out[q] = nullptr; A.peer_diff[q] = nullptr; A.peer_flag[q] = nullptr; }
     return A;
 }
 
+// sharded sweep number `sweep` of the call: where the shard's diff goes, and (peers mapped) where the copies go
+void set_exchange_args(const gmc_pr_plan* p0, const gmc_pr_plan* p, int sweep, unsigned int seq, SweepArgs& A) {
+    const size_t stride = (size_t)p0->N + 4;
+    const int par = sweep & 1;
+    A.diff_slot = p0->diffs + par * SYNC_RANKS + p->shard;
+    if (!p0->p2p) return;
+    A.seq = seq;
+    A.my_flag = p0->flags + p->shard;
+    int q = 0;
+    for (int r = 0; r < p0->world; r++) {
+        if (r == p->shard) continue;
+        double* base = static_cast<double*>(p0->peer_base[r]);
+        A.peer_out[q] = base + (par ^ 1) * stride;
+        A.peer_diff[q] = base + 2 * stride + par * SYNC_RANKS + p->shard;
+        A.peer_flag[q] = reinterpret_cast<unsigned int*>(base + 2 * stride + 2 * SYNC_RANKS) + p->shard;
+        q++;
+    }
+    A.npeers = q;
+}
+
 int launch_init(const gmc_pr_plan* p, cudaStream_t st) {
-    SweepArgs A = make_args(p, 0.0, 0, nullptr, 0.0, 0);
+    SweepArgs A = make_args(p, 0.0, 0, p->ctrl, 0, 0.0, 0);
     k_init<<<div_up(p->N + 2, 256), 256, 0, st>>>(A, p->contrib[0], p->contrib[1], p->rank[0]);
     GMC_CUDA(cudaGetLastError());
     return GMC_OK;
@@ -763,6 +856,20 @@ static int graph_plan(gmc_graph* g, int world, int rank, cudaStream_t st) {
     gmc_pr_plan* p = nullptr;
     GMC_TRY(build_plan(g, world, rank, nullptr, &p, st));
     g->pr = p;
+    return GMC_OK;
+}
+
+// Map the peers' state blocks (once per plan).  Every rank takes the same path: all mapped, or all on NCCL.
+static int plan_map_peers(gmc_pr_plan* p, gmc_comm* comm, cudaStream_t st) {
+    if (!comm || comm->world == 1 || p->p2p || p->peer_base[p->shard]) return GMC_OK;
+    p->peer_base[p->shard] = p->block;        // marks "tried"
+    if (comm->world > MAX_PEERS + 1) return GMC_OK;
+    void* bases[MAX_PEERS + 1];
+    const int rc = gmc_comm_ipc_open_all(comm, p->block, bases, st);
+    if (rc == GMC_OK) {
+        for (int r = 0; r < comm->world; r++) p->peer_base[r] = bases[r];
+        p->p2p = true;
+    } else if (rc != GMC_ERR_STATE) return rc;
     return GMC_OK;
 }
 
@@ -793,24 +900,28 @@ static int run_pagerank(gmc_graph* g, gmc_pr_plan* const* plans, int nplans, gmc
         if (todo < 1) todo = 1;   // a do-while body runs at least once (max <= 0 still sweeps once)
         for (int32_t k = 0; k < todo; k++, issued++) {
             for (int i = 0; i < nplans; i++) {
-                SweepArgs A = make_args(plans[i], d, issued & 1, p0->ctrl, e, max_iter);
-                if (sharded) A.diff_slot = p0->diffs + plans[i]->shard;
+                SweepArgs A = make_args(plans[i], d, issued, p0->ctrl, 1, e, max_iter);
+                if (sharded) set_exchange_args(p0, plans[i], issued, p0->seq + 1, A);
                 GMC_TRY(launch_sweep(plans[i], A, st));
                 launches++;
             }
             if (sharded) {
-                if (comm) {
-                    // the exchange step: every rank's new contributions (3 id ranges per rank) and its diff
+                double* dslot = p0->diffs + (issued & 1) * SYNC_RANKS;
+                p0->seq++;
+                if (comm && !p0->p2p) {
+                    // exchange step over NCCL: every rank's new contributions (3 id ranges per rank) and its diff
                     GMC_TRY(gmc_comm_allgather_segments(comm, p0->contrib[(issued & 1) ^ 1], 8, p0->seg_off.data(), p0->seg_len.data(), 3, st));
-                    GMC_TRY(gmc_comm_allgather(comm, p0->diffs + p0->shard, p0->diffs, 8, st));
+                    GMC_TRY(gmc_comm_allgather(comm, dslot + p0->shard, dslot, 8, st));
                 }
-                k_ctrl_combine<<<1, 32, 0, st>>>(p0->ctrl, p0->diffs, world, e, max_iter);
+                // peers mapped: the contributions and diffs were pushed by the sweeps themselves; wait for the flags
+                k_ctrl_combine<<<1, 32, 0, st>>>(p0->ctrl, dslot, world, e, max_iter, p0->p2p ? p0->flags : nullptr, p0->seq);
                 launches++;
             }
         }
         GMC_CUDA(cudaMemcpyAsync(&h, p0->ctrl, sizeof(h), cudaMemcpyDeviceToHost, st));
         GMC_CUDA(cudaStreamSynchronize(st));
     } while (!h.done);
+    if (h.error) { set_error("pagerank: a peer rank did not finish its sweep in time (peer-memory exchange)"); return GMC_ERR_STATE; }
     if (sharded && comm)      // the result vector: gather the owned slices of rank[] once
         GMC_TRY(gmc_comm_allgather_segments(comm, p0->rank[h.cnt & 1], 8, p0->seg_off.data(), p0->seg_len.data(), 3, st));
     k_unpermute<<<div_up(g->N, 256), 256, 0, st>>>(p0->rank[h.cnt & 1], p0->new_of_old, g->N, rank_dev);
@@ -837,6 +948,7 @@ int gmc_pagerank_sharded_dev(gmc_graph* g, gmc_comm* comm, double e, double d, i
     const int world = comm ? comm->world : 1, rank = comm ? comm->rank : 0;
     GMC_TRY(graph_plan(g, world, rank, st));
     gmc_pr_plan* p = g->pr;
+    GMC_TRY(plan_map_peers(p, comm, st));
     return run_pagerank(g, &p, 1, world > 1 ? comm : nullptr, e, d, max_iter, rank_dev, info, st);
 }
 
@@ -871,13 +983,16 @@ int gmc_pagerank_sharded_time_sweeps(gmc_graph* g, gmc_comm* comm, double d, int
     const int world = comm ? comm->world : 1, rank = comm ? comm->rank : 0;
     GMC_TRY(graph_plan(g, world, rank, st));
     gmc_pr_plan* p = g->pr;
+    GMC_TRY(plan_map_peers(p, comm, st));
+    GMC_CUDA(cudaMemsetAsync(p->ctrl, 0, sizeof(gmc_pr_ctrl), st));
     GMC_TRY(launch_init(p, st));
     std::vector<cudaEvent_t> ev(3 * (size_t)n);
     for (auto& e : ev) GMC_CUDA(cudaEventCreate(&e));
     for (int32_t k = 0; k < warmup + n; k++) {
         const bool timed = k >= warmup;
         if (timed) GMC_CUDA(cudaEventRecord(ev[3 * (k - warmup)], st));
-        SweepArgs A = make_args(p, d, k & 1, nullptr, 0.0, 0);
+        SweepArgs A = make_args(p, d, k, p->ctrl, 0, 0.0, 0);
+        if (world > 1) set_exchange_args(p, p, k, p->seq + 1, A);
         if (const char* md = getenv("GMC_PR_MODE")) { A.mode = atoi(md); if (A.mode & 2) A.hot_n = 1; }
         if (const char* only = getenv("GMC_PR_ONLY")) {      // experiment switch: time one task class alone (results invalid)
             if (strcmp(only, "long") != 0) A.lt_hi = 0;
@@ -886,7 +1001,11 @@ int gmc_pagerank_sharded_time_sweeps(gmc_graph* g, gmc_comm* comm, double d, int
         }
         GMC_TRY(launch_sweep(p, A, st));
         if (timed) GMC_CUDA(cudaEventRecord(ev[3 * (k - warmup) + 1], st));
-        if (world > 1) GMC_TRY(gmc_comm_allgather_segments(comm, p->contrib[(k & 1) ^ 1], 8, p->seg_off.data(), p->seg_len.data(), 3, st));
+        if (world > 1) {
+            p->seq++;
+            if (p->p2p) k_wait_peers<<<1, 32, 0, st>>>(p->ctrl, p->flags, world, p->seq);
+            else GMC_TRY(gmc_comm_allgather_segments(comm, p->contrib[(k & 1) ^ 1], 8, p->seg_off.data(), p->seg_len.data(), 3, st));
+        }
         if (timed) GMC_CUDA(cudaEventRecord(ev[3 * (k - warmup) + 2], st));
     }
     GMC_CUDA(cudaStreamSynchronize(st));
@@ -912,6 +1031,14 @@ int gmc_pagerank(gmc_graph* g, double e, double d, int32_t max_iter, double* ran
     if (rc == GMC_OK) rc = gmc_d2h(rank_host, tmp, sizeof(double) * (size_t)g->N, nullptr);
     cudaFree(tmp);
     return rc;
+}
+
+// how the current plan exchanges contributions between ranks: 0 = single rank, 1 = NCCL allgather after the sweep,
+// 2 = peer-memory stores from the sweep epilogue (CUDA IPC mapping over NVLink)
+int gmc_pagerank_exchange_path(gmc_graph* g, int* path) {
+    GMC_REQUIRE(g && path, GMC_ERR_ARG, "gmc_pagerank_exchange_path: NULL");
+    *path = !g->pr || g->pr->world == 1 ? 0 : (g->pr->p2p ? 2 : 1);
+    return GMC_OK;
 }
 
 // layout facts of the plan, for tests and DESIGN.md tables

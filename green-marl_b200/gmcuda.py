@@ -80,6 +80,7 @@ SIGNATURES = {
     "gmc_shard_cuts": (C.c_int, [_vp, _i32, C.c_int, _i32, _vp]),
     "gmc_pagerank_sharded_dev": (C.c_int, [_vp, _vp, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo), _vp]),
     "gmc_pagerank_emulated_shards_dev": (C.c_int, [_vp, C.c_int, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo), _vp]),
+    "gmc_pagerank_exchange_path": (C.c_int, [_vp, C.POINTER(C.c_int)]),
     "gmc_pagerank_sharded_time_sweeps": (C.c_int, [_vp, _vp, C.c_double, _i32, _i32, _vp, _vp, _vp]),
     "gmc_hop_dist_sharded_dev": (C.c_int, [_vp, _vp, _i32, _vp, C.POINTER(BfsInfo), _vp]),
     "gmc_bfs_levels_sharded": (C.c_int, [_vp, _vp, _i32, C.c_int, _vp, _vp, _vp, _vp, _i32, C.POINTER(BfsInfo)]),
@@ -309,6 +310,11 @@ class Graph:
         finally:
             self.lib.free(dev)
         return rank[:n], info
+
+    def pagerank_exchange_path(self):
+        v = C.c_int()
+        self.lib.check(self.lib.L.gmc_pagerank_exchange_path(self.h, C.byref(v)))
+        return {0: "single", 1: "nccl", 2: "peer-memory"}[v.value]
 
     def pagerank_sharded_time_sweeps(self, comm, d=0.85, warmup=3, n=20, stream=None):
         sw = np.zeros(n, np.float32); ex = np.zeros(n, np.float32)

@@ -174,6 +174,10 @@ int gmc_pagerank_sharded_dev(gmc_graph* g, gmc_comm* comm, double e, double d, i
  * same kernels, same result as a `world`-rank run */
 int gmc_pagerank_emulated_shards_dev(gmc_graph* g, int world, double e, double d, int32_t max_iter, double* rank_dev,
                                      gmc_pagerank_info* info, void* stream);
+/* how the last sharded call exchanged contributions: 0 = single rank, 1 = NCCL grouped broadcasts after each sweep,
+ * 2 = stores into the peers' memory (CUDA IPC mapping, NVLink) from the sweep's row epilogue + sequence flags.
+ * Path 2 is taken when every rank could map every peer (world <= 8); GMC_NO_P2P=1 forces path 1. */
+int gmc_pagerank_exchange_path(gmc_graph* g, int* path);
 /* per-iteration device times of a sharded run: sweep_ms / exchange_ms [n], measured with CUDA events */
 int gmc_pagerank_sharded_time_sweeps(gmc_graph* g, gmc_comm* comm, double d, int32_t warmup, int32_t n, float* sweep_ms,
                                      float* exchange_ms, void* stream);

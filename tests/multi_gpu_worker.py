@@ -26,6 +26,9 @@ def main():
     out = torch.empty(n, dtype=torch.float64, device="cuda")
     info = g.pagerank_sharded_dev(comm, out.data_ptr(), 1e-30, 0.85, 20)
     sharded = out.cpu().numpy()
+    path = g.pagerank_exchange_path()
+    if os.environ.get("GMC_NO_P2P"):
+        assert path == "nccl"
     one, info1 = g.pagerank(1e-30, 0.85, 20)
     assert info.iterations == info1.iterations == 20
     err = float(np.abs(sharded - one).max())
@@ -52,7 +55,7 @@ def main():
         assert np.array_equal(lev, lev1) and list(trace) == list(trace1) and list(cnt) == list(cnt1)
     comm.barrier()
     if rank == 0:
-        print(f"multi_gpu_worker ok: world {world}, pagerank max|sharded-single| = {err:.3e}, nccl {comm.nccl_version()}", flush=True)
+        print(f"multi_gpu_worker ok: world {world}, exchange {path}, pagerank max|sharded-single| = {err:.3e}, nccl {comm.nccl_version()}", flush=True)
     comm.close()
     dist.destroy_process_group()
 
