@@ -97,6 +97,9 @@ def run_multi(args, n, m, workload):
     sweep_ms, exch_ms = g.pagerank_sharded_time_sweeps(comm, 0.85, warmup=3, n=max(20, iters), stream=sp)
     w2 = time.time()
     clk = clocks.stop(w0, w2) if rank == 0 else None
+    per_rank = torch.zeros(world, dtype=torch.float64, device="cuda")
+    per_rank[rank] = float(np.mean(sweep_ms))
+    dist.all_reduce(per_rank)
     avg_sweep = max_over_ranks(dist, torch, float(np.mean(sweep_ms)))
     avg_exch = max_over_ranks(dist, torch, float(np.mean(exch_ms)))
     peak, peak_kind = measured_peak_gbs()
@@ -104,6 +107,7 @@ def run_multi(args, n, m, workload):
     roofline = {"bound": "hbm", "achieved": round(a_bytes / avg_sweep / 1e6, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(a_bytes / avg_sweep / 1e6 / peak, 4), "traffic": None, "peak_kind": peak_kind, "kernel": "pr_sweep (one shard)",
                 "alg_bytes_per_launch": int(a_bytes), "avg_launch_ms": round(avg_sweep, 5),
+                "avg_launch_ms_per_rank": [round(float(x), 4) for x in per_rank.cpu().numpy()],
                 "exchange": {"path": g.pagerank_exchange_path(),
                              "what": "peer-memory: contributions stored into the peers' HBM over NVLink from the sweep epilogue, avg_ms = wait for the peers' flags; "
                                      "nccl: grouped broadcasts of the owned contribution ranges after the sweep",
@@ -152,8 +156,7 @@ def run_multi(args, n, m, workload):
         for k in range(1 + e2e_steps):
             dist.barrier(); lib.sync()
             t0 = time.perf_counter()
-            dg = lib.graph_from_csr(pinned["begin"], pinned["node_idx"], semi_sort=False, make_reverse=False)
-            dg.upload_reverse(pinned["r_begin"], pinned["r_node_idx"])
+            dg = lib.graph_from_csr_sharded(comm, pinned["begin"], pinned["node_idx"], pinned["r_begin"], pinned["r_node_idx"])
             out = torch.empty(n, dtype=torch.float64, device="cuda")
             dg.pagerank_sharded_dev(comm, out.data_ptr(), 1e-30, 0.85, iters)
             lib.d2h(rank_host, out.data_ptr())
@@ -163,9 +166,9 @@ def run_multi(args, n, m, workload):
             if k > 0:
                 times.append(max_over_ranks(dist, torch, (time.perf_counter() - t0) * 1e3))
         e2e_ms = float(np.mean(times))
-        e2e = {"value": round(m * iters / e2e_ms / 1e6, 3), "unit": "GTEPS", "h2d_bytes_per_step": int(h2d * world),
+        e2e = {"value": round(m * iters / e2e_ms / 1e6, 3), "unit": "GTEPS", "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(rank_host.nbytes * world), "ms_per_step": round(e2e_ms, 3), "steps": e2e_steps,
-               "pinned": pin_ok, "note": "every rank uploads the whole CSR (replicated) and plans its shard inside the timed region"}
+               "pinned": pin_ok, "note": "each rank copies its 1/world slice of the CSR host->device, the slices are allgathered over NVLink, every rank plans its shard; all inside the timed region"}
 
     if rank == 0:
         line = {

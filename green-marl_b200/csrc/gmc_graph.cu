@@ -3,8 +3,11 @@
 // :380-423,468-503 (semi sort).  Sorting uses CUB's radix / segmented sort from the CUDA toolkit
 // (library code, untimed graph-build step); histogram, scan and scatter/gather kernels are ours.
 #include "gmc_common.cuh"
+#include "gmc_comm.h"
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_segmented_sort.cuh>
+#include <algorithm>
+#include <vector>
 
 using namespace gmc;
 
@@ -198,6 +201,40 @@ int gmc_graph_make_reverse(gmc_graph* g, int want_rev2idx, void* stream) {
     g->e_rev2idx = nullptr;
     if (want_rev2idx) g->e_rev2idx = vals_out; else cudaFree(vals_out);
     g->has_reverse = true;
+    return GMC_OK;
+}
+
+// Sharded copy-in (multi-GPU e2e path): every rank copies only its 1/world slice of each CSR array from its host
+// memory over PCIe, the slices are then allgathered between the GPUs over NVLink, so the job moves the graph
+// host->device once instead of `world` times.  Host arrays are the full arrays (only the rank's slice is read).
+int gmc_graph_upload_sharded(gmc_graph* g, gmc_comm* comm, const int32_t* begin, const int32_t* node_idx, const int32_t* r_begin,
+                             const int32_t* r_node_idx, void* stream) {
+    GMC_REQUIRE(g && begin && (node_idx || g->M == 0), GMC_ERR_ARG, "gmc_graph_upload_sharded: NULL");
+    if (!comm || comm->world == 1) {
+        GMC_TRY(gmc_graph_upload(g, begin, node_idx, stream));
+        return r_begin ? gmc_graph_upload_reverse(g, r_begin, r_node_idx, stream) : GMC_OK;
+    }
+    gmc_graph_invalidate_plans(g);
+    cudaStream_t st = as_stream(stream);
+    const int W = comm->world, R = comm->rank;
+    if (r_begin) {
+        if (!g->r_begin) GMC_TRY(gmc_malloc((void**)&g->r_begin, sizeof(int32_t) * ((size_t)g->N + 1)));
+        if (!g->r_node_idx) GMC_TRY(gmc_malloc((void**)&g->r_node_idx, sizeof(int32_t) * (size_t)(g->M ? g->M : 1)));
+    }
+    struct Arr { int32_t* dev; const int32_t* host; int64_t len; };
+    const Arr arrs[4] = {{g->begin, begin, (int64_t)g->N + 1}, {g->node_idx, node_idx, (int64_t)g->M},
+                         {g->r_begin, r_begin, (int64_t)g->N + 1}, {g->r_node_idx, r_node_idx, (int64_t)g->M}};
+    std::vector<int64_t> off((size_t)W), len((size_t)W);
+    for (int a = 0; a < (r_begin ? 4 : 2); a++) {
+        const int64_t L = arrs[a].len, per = (L + W - 1) / W;
+        for (int r = 0; r < W; r++) { off[r] = std::min<int64_t>(L, r * per); len[r] = std::min<int64_t>(L, (r + 1) * per) - off[r]; }
+        if (len[R] > 0)
+            GMC_CUDA(cudaMemcpyAsync(arrs[a].dev + off[R], arrs[a].host + off[R], sizeof(int32_t) * (size_t)len[R], cudaMemcpyHostToDevice, st));
+        GMC_TRY(gmc_comm_allgather_segments(comm, arrs[a].dev, sizeof(int32_t), off.data(), len.data(), 1, st));
+    }
+    GMC_CUDA(cudaStreamSynchronize(st));
+    g->semi_sorted = false;
+    g->has_reverse = r_begin != nullptr;
     return GMC_OK;
 }
 

@@ -47,6 +47,7 @@ constexpr int LT = 2048;                  // entries per long-row task (16 warp 
 constexpr int ST_COST = 2048;             // cost units per short-row task (slice cost = 32*len + SLICE_OVH)
 constexpr int SLICE_OVH = 68;             // keeps a task at <= 31 slices
 constexpr int ZT = 2048;                  // ids per zero-in-degree task
+constexpr int SHARD_ROW_COST = 4;         // entries one row epilogue weighs when the shards of a multi-rank run are cut
 #ifndef GMC_HOT_CAP
 #define GMC_HOT_CAP 20480
 #endif
@@ -65,6 +66,8 @@ struct gmc_pr_ctrl {   // device-side loop control: lets the host enqueue sweeps
 };
 constexpr int MAX_PEERS = 7;            // peer-memory exchange up to 8 ranks (one NVSwitch domain); beyond: NCCL
 constexpr int SYNC_RANKS = 64;          // slots of the sync area at the end of the state block
+// doubles per contribution buffer inside the state block: N+2 used, rounded up to 256 bytes (TMA bulk source alignment)
+static inline size_t state_stride(int32_t n) { return (((size_t)n + 4 + 31) / 32) * 32; }
 constexpr long long PEER_TIMEOUT_CYCLES = 8000000000LL;    // ~4 s at 1.9 GHz: a dead peer fails the call, not the box
 
 struct SweepArgs {
@@ -118,7 +121,7 @@ struct gmc_pr_plan {
     int32_t jl0 = 0, n_long = 0, s0 = 0, n_slices = 0, EL = 0, EN = 0, n_ltasks = 0, n_stasks = 0, n_ztasks = 0, z0 = 0, z_end = 0;
     std::vector<int64_t> seg_off, seg_len;    // [world][3] owned id ranges of every rank (long, short, zero)
     // state block (one allocation, so that one CUDA IPC handle maps it into the peers):
-    //   contrib[0] [N+4] | contrib[1] [N+4] | diffs [2][SYNC_RANKS] doubles | flags [SYNC_RANKS] u32
+    //   contrib[0] [stride] | contrib[1] [stride] | diffs [2][SYNC_RANKS] doubles | flags [SYNC_RANKS] u32
     double* block = nullptr;
     double* diffs = nullptr;                  // per-shard diffs, double-buffered by sweep parity
     unsigned int* flags = nullptr;            // flags[r] = sequence number of rank r's last completed sweep
@@ -713,8 +716,19 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
     if (h_lbeg[p->g_n_long] < 0 || h_sbeg[g_n_slices] < 0 || (int64_t)h_lbeg[p->g_n_long] + h_sbeg[g_n_slices] > 0x7fffff00LL) {
         rc = GMC_ERR_ARG; set_error("pagerank plan: entry array exceeds int32 offsets"); goto fail;
     }
-    PLAN_TRY(gmc_shard_cuts(h_lbeg.data(), p->g_n_long, world, 1, cutsL.data()));
-    PLAN_TRY(gmc_shard_cuts(h_scost.data(), p->g_nz_slices, world, 1, cutsS.data()));
+    if (world > 1) {
+        // shard cuts balance entries + SHARD_ROW_COST per row: a row's epilogue (28 B of HBM traffic, a division and, with
+        // mapped peers, world-1 remote stores) weighs a few entries; with entry counts alone the ranks owning the short
+        // tail rows were 2x slower than the others on the TW-shaped graph (profiles/r1e_bench_8gpu_tw_unbalanced.json)
+        std::vector<int32_t> cl(h_lbeg), cs(h_scost);
+        for (int32_t j = 0; j <= p->g_n_long; j++) cl[j] += j * SHARD_ROW_COST;
+        for (int32_t q = 0; q <= p->g_nz_slices; q++) cs[q] += q * (32 * SHARD_ROW_COST - SLICE_OVH);
+        PLAN_TRY(gmc_shard_cuts(cl.data(), p->g_n_long, world, 1, cutsL.data()));
+        PLAN_TRY(gmc_shard_cuts(cs.data(), p->g_nz_slices, world, 1, cutsS.data()));
+    } else {
+        PLAN_TRY(gmc_shard_cuts(h_lbeg.data(), p->g_n_long, world, 1, cutsL.data()));
+        PLAN_TRY(gmc_shard_cuts(h_scost.data(), p->g_nz_slices, world, 1, cutsS.data()));
+    }
     {
         const int32_t nz = n + 1 - p->g_z0 > 0 ? n + 1 - p->g_z0 : 0;           // ids [g_z0, N] have no in-edges
         const int32_t per = div_up(div_up(nz, world), ZT) * ZT;
@@ -766,7 +780,7 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
         p->ctrl = state_of->ctrl; p->diffs = state_of->diffs; p->flags = state_of->flags;
     } else {
         if (world > SYNC_RANKS) { rc = GMC_ERR_ARG; set_error("pagerank: at most %d shards", SYNC_RANKS); goto fail; }
-        const size_t stride = nn + 4, sync_doubles = 2 * SYNC_RANKS + SYNC_RANKS / 2;
+        const size_t stride = state_stride(n), sync_doubles = 2 * SYNC_RANKS + SYNC_RANKS / 2;
         PLAN_TRY(gmc_malloc((void**)&p->block, 8 * (2 * stride + sync_doubles)));
         p->contrib[0] = p->block; p->contrib[1] = p->block + stride;
         p->diffs = p->block + 2 * stride;
@@ -812,7 +826,7 @@ SweepArgs make_args(const gmc_pr_plan* p, double d, int sweep, gmc_pr_ctrl* ctrl
 
 // sharded sweep number `sweep` of the call: where the shard's diff goes, and (peers mapped) where the copies go
 void set_exchange_args(const gmc_pr_plan* p0, const gmc_pr_plan* p, int sweep, unsigned int seq, SweepArgs& A) {
-    const size_t stride = (size_t)p0->N + 4;
+    const size_t stride = state_stride(p0->N);
     const int par = sweep & 1;
     A.diff_slot = p0->diffs + par * SYNC_RANKS + p->shard;
     if (!p0->p2p) return;

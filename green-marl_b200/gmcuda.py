@@ -80,6 +80,7 @@ SIGNATURES = {
     "gmc_shard_cuts": (C.c_int, [_vp, _i32, C.c_int, _i32, _vp]),
     "gmc_pagerank_sharded_dev": (C.c_int, [_vp, _vp, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo), _vp]),
     "gmc_pagerank_emulated_shards_dev": (C.c_int, [_vp, C.c_int, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo), _vp]),
+    "gmc_graph_upload_sharded": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "gmc_pagerank_exchange_path": (C.c_int, [_vp, C.POINTER(C.c_int)]),
     "gmc_pagerank_sharded_time_sweeps": (C.c_int, [_vp, _vp, C.c_double, _i32, _i32, _vp, _vp, _vp]),
     "gmc_hop_dist_sharded_dev": (C.c_int, [_vp, _vp, _i32, _vp, C.POINTER(BfsInfo), _vp]),
@@ -143,6 +144,15 @@ class GmCuda:
             self.check(self.L.gmc_graph_semi_sort(h, int(want_maps), None))
         if make_reverse:
             self.check(self.L.gmc_graph_make_reverse(h, int(want_maps), None))
+        return g
+
+    def graph_from_csr_sharded(self, comm, begin, node_idx, r_begin, r_node_idx):
+        """multi-GPU copy-in: this rank uploads its slice of each array, the slices are allgathered over NVLink"""
+        h = _vp()
+        self.check(self.L.gmc_graph_create(C.byref(h), len(begin) - 1, len(node_idx)))
+        g = Graph(self, h)
+        self.check(self.L.gmc_graph_upload_sharded(h, comm.h if comm else None, _ptr(begin), _ptr(node_idx), _ptr(r_begin),
+                                                   _ptr(r_node_idx), None))
         return g
 
     def generate_rmat(self, n, m, seed=1997, a=0.57, b=0.19, c=0.19, permute=True):

@@ -165,6 +165,11 @@ int gmc_comm_barrier(gmc_comm* c, void* stream);     /* device-side barrier (1-e
 /* host-side balanced partition of a prefix-sum array into `world` contiguous ranges (cuts[world+1]) */
 int gmc_shard_cuts(const int32_t* prefix, int32_t n, int world, int32_t align, int32_t* cuts);
 
+/* sharded copy-in: each rank copies its 1/world slice of every CSR array host->device, the slices are allgathered
+ * over NVLink (the job moves the graph across PCIe once, not `world` times).  r_begin may be NULL (no reverse CSR). */
+int gmc_graph_upload_sharded(gmc_graph* g, gmc_comm* comm, const int32_t* begin, const int32_t* node_idx,
+                             const int32_t* r_begin, const int32_t* r_node_idx, void* stream);
+
 /* PageRank over destination-range shards: rank r sweeps only its share of the entry array, then the new
  * contributions are allgathered (NCCL over NVLink) before the next sweep; diff is combined in rank order, so
  * every rank leaves the loop on the same iteration.  rank_dev receives the full vector on every rank. */

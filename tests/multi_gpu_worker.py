@@ -53,6 +53,13 @@ def main():
         lev, li, trace, cnt = g.bfs_levels_sharded(comm, root)
         lev1, li1, trace1, cnt1 = g.bfs_levels(root)
         assert np.array_equal(lev, lev1) and list(trace) == list(trace1) and list(cnt) == list(cnt1)
+    # sharded copy-in: slices uploaded by their ranks + NVLink allgather reproduce the arrays on every rank
+    host = {k: g.array(k) for k in ("begin", "node_idx", "r_begin", "r_node_idx")}
+    g2 = lib.graph_from_csr_sharded(comm, host["begin"], host["node_idx"], host["r_begin"], host["r_node_idx"])
+    for k, a in host.items():
+        assert np.array_equal(g2.array(k), a), f"rank {rank}: sharded upload of {k} differs"
+    comm.barrier()
+    g2.close()
     comm.barrier()
     if rank == 0:
         print(f"multi_gpu_worker ok: world {world}, exchange {path}, pagerank max|sharded-single| = {err:.3e}, nccl {comm.nccl_version()}", flush=True)
