@@ -8,10 +8,10 @@ BASELINE.json configs[1] (4.85 M vertices, 69 M edges, int32 ids, fp64 ranks).
 
   value     GTEPS = edges x iterations x steps / device time; CSR already resident in HBM (CUDA events on
             the launching stream, max over ranks).
-  e2e       same metric through the reference-facing C-ABI calls with HOST buffers: per step the CSR +
-            reverse CSR are copied H2D from pinned memory (what the generated procedure's Shoal copy-in
-            does on every call, reference gm_cpp_gen.cc:685-775), the sweeps run, and rank[] is copied
-            back to host memory (copy_back, :1480).
+  e2e       same metric through the reference-facing C-ABI calls with HOST buffers: per step begin[] and the
+            reverse CSR (the arrays the generated procedure reads, copied in by its Shoal prologue on every call,
+            reference gm_cpp_gen.cc:685-775) go H2D from pinned memory, the plan is built, the sweeps run,
+            and rank[] is copied back to host memory (copy_back, :1480).
   roofline  the pull-sweep kernel: algorithmic bytes per sweep (4*M + 40*N) / its average
             launch duration (each sweep bracketed by CUDA events), against MEASURED_PEAKS.json.
   cpu_baseline  the reference's own OpenMP code (oracle/_ref: reference gm_graph + the generated loop nest
@@ -289,25 +289,31 @@ def run_single(args, n, m):
     # ---- e2e: host buffers through the C ABI, H2D + D2H inside the timed region ---------------------
     host = {k: g.array(k) for k in ("begin", "node_idx", "r_begin", "r_node_idx")}
     pinned = {}
-    for k, a in host.items():
-        t = torch.empty(a.shape, dtype=torch.int32).pin_memory()
-        t.numpy()[:] = a
+    for k in ("begin", "r_begin", "r_node_idx"):      # what the generated pagerank() copies in (no node_idx: pull only)
+        t = torch.empty(host[k].shape, dtype=torch.int32).pin_memory()
+        t.numpy()[:] = host[k]
         pinned[k] = t.numpy()
     rank_host_t = torch.empty(n, dtype=torch.float64).pin_memory()
     rank_host = rank_host_t.numpy()
     h2d = sum(a.nbytes for a in pinned.values())
     d2h = rank_host.nbytes
+    parts = {"h2d_ms": [], "plan_and_sweeps_ms": []}
 
     def e2e_step():
-        dg = lib.graph_from_csr(pinned["begin"], pinned["node_idx"], semi_sort=False, make_reverse=False)
-        dg.upload_reverse(pinned["r_begin"], pinned["r_node_idx"])
+        t_a = time.perf_counter()
+        dg = lib.graph_pull_only(pinned["begin"], pinned["r_begin"], pinned["r_node_idx"])
+        t_b = time.perf_counter()
         _, inf = dg.pagerank_into(rank_host, 1e-30, 0.85, iters)
+        t_c = time.perf_counter()
         dg.close()
+        parts["h2d_ms"].append((t_b - t_a) * 1e3); parts["plan_and_sweeps_ms"].append((t_c - t_b) * 1e3)
         return inf
 
     for _ in range(min(args.warmup, 2)):
         e2e_step()
     lib.sync()
+    for v in parts.values():
+        v.clear()
     t0 = time.perf_counter()
     e2e_steps = max(1, min(args.steps, 5))
     for _ in range(e2e_steps):
@@ -315,7 +321,12 @@ def run_single(args, n, m):
     lib.sync()
     e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
     e2e = {"value": round(m * iters / e2e_ms / 1e6, 3), "unit": "GTEPS", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-           "ms_per_step": round(e2e_ms, 3), "steps": e2e_steps}
+           "ms_per_step": round(e2e_ms, 3), "steps": e2e_steps,
+           "breakdown_ms": {"h2d_begin_rbegin_rnodeidx": round(float(np.mean(parts["h2d_ms"])), 3),
+                            "plan_20_sweeps_d2h": round(float(np.mean(parts["plan_and_sweeps_ms"])), 3)},
+           "h2d_gbs": round(h2d / float(np.mean(parts["h2d_ms"])) / 1e6, 1)}
+    if os.environ.get("GMC_BENCH_DEBUG"):
+        sys.stderr.write("e2e parts: %r\n" % ({k: [round(x, 1) for x in v] for k, v in parts.items()},))
     assert np.array_equal(rank_host, rank_gpu), "e2e result differs from the resident-graph result"
 
     # ---- BFS (configs[2]) on the same graph: hop_dist over several roots -------------------------

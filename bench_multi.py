@@ -100,6 +100,10 @@ def run_multi(args, n, m, workload):
     per_rank = torch.zeros(world, dtype=torch.float64, device="cuda")
     per_rank[rank] = float(np.mean(sweep_ms))
     dist.all_reduce(per_rank)
+    pi = g.pagerank_plan_info()
+    shard_stats = torch.zeros(world, 4, dtype=torch.float64, device="cuda")
+    shard_stats[rank] = torch.tensor([pi["n_long"], pi["n_slices"], pi["long_entries"], pi["total_entries"]], dtype=torch.float64)
+    dist.all_reduce(shard_stats)
     avg_sweep = max_over_ranks(dist, torch, float(np.mean(sweep_ms)))
     avg_exch = max_over_ranks(dist, torch, float(np.mean(exch_ms)))
     peak, peak_kind = measured_peak_gbs()
@@ -108,6 +112,7 @@ def run_multi(args, n, m, workload):
                 "frac": round(a_bytes / avg_sweep / 1e6 / peak, 4), "traffic": None, "peak_kind": peak_kind, "kernel": "pr_sweep (one shard)",
                 "alg_bytes_per_launch": int(a_bytes), "avg_launch_ms": round(avg_sweep, 5),
                 "avg_launch_ms_per_rank": [round(float(x), 4) for x in per_rank.cpu().numpy()],
+                "shards_long_rows_slices_long_entries_entries": [[int(x) for x in row] for row in shard_stats.cpu().numpy()],
                 "exchange": {"path": g.pagerank_exchange_path(),
                              "what": "peer-memory: contributions stored into the peers' HBM over NVLink from the sweep epilogue, avg_ms = wait for the peers' flags; "
                                      "nccl: grouped broadcasts of the owned contribution ranges after the sweep",
@@ -136,7 +141,7 @@ def run_multi(args, n, m, workload):
     # rank[] D2H), wall clock between barriers, max over ranks ---------------------------------------------
     e2e = None
     if not args.no_e2e:
-        host = {k: g.array(k) for k in ("begin", "node_idx", "r_begin", "r_node_idx")}
+        host = {k: g.array(k) for k in ("begin", "r_begin", "r_node_idx")}     # what pagerank() reads: pull only
         pinned, pin_ok = {}, True
         for k, a in host.items():
             try:
@@ -156,7 +161,7 @@ def run_multi(args, n, m, workload):
         for k in range(1 + e2e_steps):
             dist.barrier(); lib.sync()
             t0 = time.perf_counter()
-            dg = lib.graph_from_csr_sharded(comm, pinned["begin"], pinned["node_idx"], pinned["r_begin"], pinned["r_node_idx"])
+            dg = lib.graph_pull_only(pinned["begin"], pinned["r_begin"], pinned["r_node_idx"], comm=comm)
             out = torch.empty(n, dtype=torch.float64, device="cuda")
             dg.pagerank_sharded_dev(comm, out.data_ptr(), 1e-30, 0.85, iters)
             lib.d2h(rank_host, out.data_ptr())

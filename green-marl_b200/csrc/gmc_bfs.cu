@@ -297,6 +297,7 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             const int32_t* rev_idx, int32_t root, L invalid, L* level_out_dev, gmc_bfs_info* info, cudaStream_t st,
             const uint8_t* edge_mask = nullptr) {
     GMC_REQUIRE(root >= 0 && root < g->N, GMC_ERR_ARG, "bfs: root %d out of range [0,%d)", root, g->N);
+    GMC_REQUIRE(g->has_forward, GMC_ERR_STATE, "bfs: the forward CSR (node_idx) was not uploaded for this graph");
     const int world = comm ? comm->world : 1, rank = comm ? comm->rank : 0;
     GMC_TRY(ensure_ws(g, world));
     gmc_bfs_ws* w = g->bfs;

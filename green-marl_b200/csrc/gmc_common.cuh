@@ -62,6 +62,8 @@ int exclusive_scan_i32(const int32_t* in, int32_t* out, size_t n, int32_t* total
 
 }  // namespace gmc
 
+extern "C" int gmc_malloc_ipc(void** p, size_t bytes);   // internal: plain cudaMalloc (IPC-exportable); gmc_malloc uses the memory pool
+
 // The device-resident CSR mirror behind gmc_graph.
 struct gmc_pr_plan;
 struct gmc_bfs_ws;
@@ -75,6 +77,7 @@ struct gmc_graph {
     int32_t* e_idx2idx = nullptr;   // [M] optional
     bool semi_sorted = false;
     bool has_reverse = false;
+    bool has_forward = true;        // false: node_idx was not copied in (pull-only graph: PageRank needs begin + the reverse CSR)
     // lazily built per-algorithm state (invalidated when the CSR changes)
     gmc_pr_plan* pr = nullptr;      // PageRank plan: relabelled entry array, tasks, state buffers (gmc_pagerank.cu)
     gmc_bfs_ws* bfs = nullptr;

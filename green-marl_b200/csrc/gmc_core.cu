@@ -164,13 +164,43 @@ int gmc_sync(void* stream) {
     return GMC_OK;
 }
 
+// Device arrays come from the device's default memory pool with an unbounded release threshold: graph / plan
+// objects are created and destroyed per call on the reference-facing path (a fresh gm_graph mirror and plan per
+// pagerank() call), and cudaMalloc/cudaFree of hundreds of MB cost milliseconds each and serialise on the driver.
+// The allocation is made on the legacy default stream and completed before returning, so the pointer may be used
+// on any stream; cudaFree() accepts pool allocations (memory goes back to the pool).
+static int pool_ready_for_device = -1;
 int gmc_malloc(void** p, size_t bytes) {
     GMC_REQUIRE(p, GMC_ERR_ARG, "gmc_malloc: NULL");
+    *p = nullptr;
+    int dev = 0;
+    GMC_CUDA(cudaGetDevice(&dev));
+    if (pool_ready_for_device != dev) {
+        cudaMemPool_t pool;
+        GMC_CUDA(cudaDeviceGetDefaultMemPool(&pool, dev));
+        unsigned long long keep = ~0ull;
+        GMC_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+        pool_ready_for_device = dev;
+    }
+    cudaError_t e = cudaMallocAsync(p, bytes ? bytes : 1, (cudaStream_t)0);
+    if (e == cudaSuccess) e = cudaStreamSynchronize((cudaStream_t)0);
+    if (e == cudaErrorMemoryAllocation) {
+        cudaGetLastError();
+        set_error("gmc_malloc: out of device memory (%zu bytes)", bytes);
+        return GMC_ERR_NOMEM;
+    }
+    GMC_CUDA(e);
+    return GMC_OK;
+}
+
+// plain cudaMalloc: memory that is exported to peer processes with CUDA IPC (pool memory cannot be)
+int gmc_malloc_ipc(void** p, size_t bytes) {
+    GMC_REQUIRE(p, GMC_ERR_ARG, "gmc_malloc_ipc: NULL");
     *p = nullptr;
     cudaError_t e = cudaMalloc(p, bytes ? bytes : 1);
     if (e == cudaErrorMemoryAllocation) {
         cudaGetLastError();
-        set_error("gmc_malloc: out of device memory (%zu bytes)", bytes);
+        set_error("gmc_malloc_ipc: out of device memory (%zu bytes)", bytes);
         return GMC_ERR_NOMEM;
     }
     GMC_CUDA(e);

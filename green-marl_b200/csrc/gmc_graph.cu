@@ -87,11 +87,14 @@ int gmc_graph_num_edges(const gmc_graph* g, int32_t* m) { GMC_REQUIRE(g && m, GM
 int gmc_graph_has_reverse(const gmc_graph* g, int* yes) { GMC_REQUIRE(g && yes, GMC_ERR_ARG, "NULL"); *yes = g->has_reverse; return GMC_OK; }
 
 int gmc_graph_upload(gmc_graph* g, const int32_t* begin, const int32_t* node_idx, void* stream) {
-    GMC_REQUIRE(g && begin && (node_idx || g->M == 0), GMC_ERR_ARG, "gmc_graph_upload: NULL");
+    GMC_REQUIRE(g && begin, GMC_ERR_ARG, "gmc_graph_upload: NULL");
     gmc_graph_invalidate_plans(g);
     cudaStream_t st = as_stream(stream);
     GMC_CUDA(cudaMemcpyAsync(g->begin, begin, sizeof(int32_t) * ((size_t)g->N + 1), cudaMemcpyHostToDevice, st));
-    if (g->M) GMC_CUDA(cudaMemcpyAsync(g->node_idx, node_idx, sizeof(int32_t) * (size_t)g->M, cudaMemcpyHostToDevice, st));
+    // node_idx == NULL: a pull-only graph (what the generated pagerank() copies in: begin, r_begin, r_node_idx);
+    // everything that follows out-edges (BFS, semi-sort, reverse build) then fails with GMC_ERR_STATE
+    g->has_forward = node_idx != nullptr || g->M == 0;
+    if (g->M && node_idx) GMC_CUDA(cudaMemcpyAsync(g->node_idx, node_idx, sizeof(int32_t) * (size_t)g->M, cudaMemcpyHostToDevice, st));
     GMC_CUDA(cudaStreamSynchronize(st));
     g->semi_sorted = false;
     g->has_reverse = false;
@@ -115,6 +118,7 @@ int gmc_graph_upload_reverse(gmc_graph* g, const int32_t* r_begin, const int32_t
 // (gm_graph.cc:468-503).  Stable => ties keep ascending original edge index.
 int gmc_graph_semi_sort(gmc_graph* g, int want_idx2idx, void* stream) {
     GMC_REQUIRE(g, GMC_ERR_ARG, "gmc_graph_semi_sort: NULL");
+    GMC_REQUIRE(g->has_forward, GMC_ERR_STATE, "gmc_graph_semi_sort: node_idx was not uploaded");
     if (g->semi_sorted && (!want_idx2idx || g->e_idx2idx)) return GMC_OK;
     cudaStream_t st = as_stream(stream);
     gmc_graph_invalidate_plans(g);
@@ -163,6 +167,7 @@ int gmc_graph_semi_sort(gmc_graph* g, int want_idx2idx, void* stream) {
 // make_reverse_edges + do_semi_sort_reverse (gm_graph.cc:233-293), minus its nondeterministic tie order.
 int gmc_graph_make_reverse(gmc_graph* g, int want_rev2idx, void* stream) {
     GMC_REQUIRE(g, GMC_ERR_ARG, "gmc_graph_make_reverse: NULL");
+    GMC_REQUIRE(g->has_forward || g->has_reverse, GMC_ERR_STATE, "gmc_graph_make_reverse: node_idx was not uploaded");
     if (g->has_reverse && (!want_rev2idx || g->e_rev2idx)) return GMC_OK;
     cudaStream_t st = as_stream(stream);
     gmc_graph_invalidate_plans(g);
@@ -209,7 +214,7 @@ int gmc_graph_make_reverse(gmc_graph* g, int want_rev2idx, void* stream) {
 // host->device once instead of `world` times.  Host arrays are the full arrays (only the rank's slice is read).
 int gmc_graph_upload_sharded(gmc_graph* g, gmc_comm* comm, const int32_t* begin, const int32_t* node_idx, const int32_t* r_begin,
                              const int32_t* r_node_idx, void* stream) {
-    GMC_REQUIRE(g && begin && (node_idx || g->M == 0), GMC_ERR_ARG, "gmc_graph_upload_sharded: NULL");
+    GMC_REQUIRE(g && begin, GMC_ERR_ARG, "gmc_graph_upload_sharded: NULL");
     if (!comm || comm->world == 1) {
         GMC_TRY(gmc_graph_upload(g, begin, node_idx, stream));
         return r_begin ? gmc_graph_upload_reverse(g, r_begin, r_node_idx, stream) : GMC_OK;
@@ -225,7 +230,9 @@ int gmc_graph_upload_sharded(gmc_graph* g, gmc_comm* comm, const int32_t* begin,
     const Arr arrs[4] = {{g->begin, begin, (int64_t)g->N + 1}, {g->node_idx, node_idx, (int64_t)g->M},
                          {g->r_begin, r_begin, (int64_t)g->N + 1}, {g->r_node_idx, r_node_idx, (int64_t)g->M}};
     std::vector<int64_t> off((size_t)W), len((size_t)W);
+    g->has_forward = node_idx != nullptr || g->M == 0;
     for (int a = 0; a < (r_begin ? 4 : 2); a++) {
+        if (!arrs[a].host) continue;      // node_idx not given: pull-only graph
         const int64_t L = arrs[a].len, per = (L + W - 1) / W;
         for (int r = 0; r < W; r++) { off[r] = std::min<int64_t>(L, r * per); len[r] = std::min<int64_t>(L, (r + 1) * per) - off[r]; }
         if (len[R] > 0)
@@ -241,7 +248,7 @@ int gmc_graph_upload_sharded(gmc_graph* g, gmc_comm* comm, const int32_t* begin,
 static int array_of(const gmc_graph* g, int which, const int32_t** p, size_t* len) {
     switch (which) {
         case GMC_ARR_BEGIN: *p = g->begin; *len = (size_t)g->N + 1; break;
-        case GMC_ARR_NODE_IDX: *p = g->node_idx; *len = (size_t)g->M; break;
+        case GMC_ARR_NODE_IDX: *p = g->has_forward ? g->node_idx : nullptr; *len = (size_t)g->M; break;
         case GMC_ARR_R_BEGIN: *p = g->has_reverse ? g->r_begin : nullptr; *len = (size_t)g->N + 1; break;
         case GMC_ARR_R_NODE_IDX: *p = g->has_reverse ? g->r_node_idx : nullptr; *len = (size_t)g->M; break;
         case GMC_ARR_E_REV2IDX: *p = g->e_rev2idx; *len = (size_t)g->M; break;

@@ -42,12 +42,12 @@ using namespace gmc;
 
 constexpr int PR_THREADS = 1024;          // one CTA per SM, 32 independent warps
 constexpr int PR_WARPS = PR_THREADS / 32;
-constexpr int S_MAX = 64;                 // rows up to this in-degree are summed sequentially (bit-exact)
+constexpr int S_MAX = 512;                // rows up to this in-degree are summed sequentially, one lane per row (bit-exact)
 constexpr int LT = 2048;                  // entries per long-row task (16 warp steps of 128)
 constexpr int ST_COST = 2048;             // cost units per short-row task (slice cost = 32*len + SLICE_OVH)
 constexpr int SLICE_OVH = 68;             // keeps a task at <= 31 slices
 constexpr int ZT = 2048;                  // ids per zero-in-degree task
-constexpr int SHARD_ROW_COST = 4;         // entries one row epilogue weighs when the shards of a multi-rank run are cut
+constexpr int SHARD_ROW_COST = 6;         // entries one row epilogue weighs when the shards of a multi-rank run are cut
 #ifndef GMC_HOT_CAP
 #define GMC_HOT_CAP 20480
 #endif
@@ -472,13 +472,13 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
 // ---------------------------------------------------------------------------------------------
 __global__ void k_degrees(const int32_t* __restrict__ begin, const int32_t* __restrict__ r_begin, int32_t n,
                           int32_t* __restrict__ outdeg, int32_t* __restrict__ indeg, uint32_t* __restrict__ key_a,
-                          int32_t* __restrict__ ids, int32_t* __restrict__ is_long, int32_t* __restrict__ is_pos) {
+                          int32_t* __restrict__ ids, int32_t* __restrict__ is_long, int32_t* __restrict__ is_pos, int32_t s_max) {
     int32_t v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v >= n) return;
     const int32_t od = begin[v + 1] - begin[v], id = r_begin[v + 1] - r_begin[v];
     outdeg[v] = od;
     indeg[v] = id;
-    const bool lg = id > S_MAX;
+    const bool lg = id > s_max;
     is_long[v] = lg;
     is_pos[v] = id > 0;
     key_a[v] = lg ? (uint32_t)(0x7fffffff - od) : 0xffffffffu;    // long rows by out-degree descending, short rows last
@@ -491,13 +491,13 @@ __global__ void k_hot_rank(const int32_t* __restrict__ sorted_ids, int32_t n, in
     if (p < n) hot_rank[sorted_ids[p]] = p < hot_ids ? p : -1;
 }
 __global__ void k_order_key(const int32_t* __restrict__ indeg, const int32_t* __restrict__ hot_rank, int32_t n,
-                            unsigned long long* __restrict__ key, int32_t* __restrict__ ids) {
+                            unsigned long long* __restrict__ key, int32_t* __restrict__ ids, int32_t s_max) {
     int32_t v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v >= n) return;
     const int32_t hr = hot_rank[v], id = indeg[v];
     unsigned long long k;
     if (hr >= 0) k = (unsigned long long)hr;
-    else k = ((unsigned long long)(id > S_MAX ? 1 : 2) << 32) | (unsigned)(0x7fffffff - id);
+    else k = ((unsigned long long)(id > s_max ? 1 : 2) << 32) | (unsigned)(0x7fffffff - id);
     key[v] = k;
     ids[v] = v;
 }
@@ -667,7 +667,7 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
     const size_t nn = (size_t)n;
     const unsigned gb = (unsigned)div_up(n, 256);
     int32_t h[2] = {0, 0};
-    int32_t g_n_slices = 0, jl1 = 0, s1 = 0, cost_total = 0;
+    int32_t g_n_slices = 0, jl1 = 0, s1 = 0, cost_total = 0, s_max = S_MAX;
     std::vector<int32_t> h_lbeg, h_sbeg, h_scost, cutsL((size_t)world + 1), cutsS((size_t)world + 1), cutsZ((size_t)world + 1);
 
     PLAN_TRY(gmc_malloc((void**)&outdeg_old, 4 * nn)); PLAN_TRY(gmc_malloc((void**)&indeg, 4 * nn));
@@ -681,7 +681,8 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
     PLAN_TRY(gmc_malloc((void**)&p->outdeg, 4 * (nn + 1)));
 
     // 1. degrees, number of long rows, the hot block, the relabelling (identical on every rank)
-    k_degrees<<<gb, 256, 0, st>>>(g->begin, g->r_begin, n, outdeg_old, indeg, key_a, ids, is_long, is_pos);
+    if (const char* sm = getenv("GMC_PR_SMAX")) { s_max = atoi(sm); if (s_max < 64) s_max = 64; if (s_max > 4096) s_max = 4096; }   // experiments (>= 64: a long task holds at most 32 rows)
+    k_degrees<<<gb, 256, 0, st>>>(g->begin, g->r_begin, n, outdeg_old, indeg, key_a, ids, is_long, is_pos, s_max);
     PLAN_TRY(exclusive_scan_i32(is_long, is_long, nn, tot, st));
     PLAN_TRY(exclusive_scan_i32(is_pos, is_pos, nn, tot + 1, st));
     PLAN_CUDA(cudaMemcpyAsync(h, tot, 8, cudaMemcpyDeviceToHost, st));
@@ -693,7 +694,7 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
         p->hot_n = hot_ids + 1;                             // ids [0, hot_n): the dummy + the hot block
         PLAN_TRY(sort_pairs<uint32_t>(key_a, key_a2, ids, ids2, n, 32, st));
         k_hot_rank<<<gb, 256, 0, st>>>(ids2, n, hot_ids, hot_rank);
-        k_order_key<<<gb, 256, 0, st>>>(indeg, hot_rank, n, key_b, ids);
+        k_order_key<<<gb, 256, 0, st>>>(indeg, hot_rank, n, key_b, ids, s_max);
         PLAN_TRY(sort_pairs<unsigned long long>(key_b, key_b2, ids, ids2, n, 34, st));
         k_relabel<<<gb, 256, 0, st>>>(ids2, n, p->old_of_new, p->new_of_old);
     }
@@ -720,9 +721,13 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
         // shard cuts balance entries + SHARD_ROW_COST per row: a row's epilogue (28 B of HBM traffic, a division and, with
         // mapped peers, world-1 remote stores) weighs a few entries; with entry counts alone the ranks owning the short
         // tail rows were 2x slower than the others on the TW-shaped graph (profiles/r1e_bench_8gpu_tw_unbalanced.json)
-        std::vector<int32_t> cl(h_lbeg), cs(h_scost);
+        std::vector<int32_t> cl(h_lbeg), cs((size_t)p->g_nz_slices + 1);
         for (int32_t j = 0; j <= p->g_n_long; j++) cl[j] += j * SHARD_ROW_COST;
-        for (int32_t q = 0; q <= p->g_nz_slices; q++) cs[q] += q * (32 * SHARD_ROW_COST - SLICE_OVH);
+        cs[0] = 0;
+        for (int32_t q = 0; q < p->g_nz_slices; q++) {          // a slice is processed in 8-column chunks
+            const int32_t len = (h_sbeg[q + 1] - h_sbeg[q]) >> 5;
+            cs[q + 1] = cs[q] + 32 * (((len + 7) & ~7) + SHARD_ROW_COST);
+        }
         PLAN_TRY(gmc_shard_cuts(cl.data(), p->g_n_long, world, 1, cutsL.data()));
         PLAN_TRY(gmc_shard_cuts(cs.data(), p->g_nz_slices, world, 1, cutsS.data()));
     } else {
@@ -781,7 +786,8 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
     } else {
         if (world > SYNC_RANKS) { rc = GMC_ERR_ARG; set_error("pagerank: at most %d shards", SYNC_RANKS); goto fail; }
         const size_t stride = state_stride(n), sync_doubles = 2 * SYNC_RANKS + SYNC_RANKS / 2;
-        PLAN_TRY(gmc_malloc((void**)&p->block, 8 * (2 * stride + sync_doubles)));
+        if (world > 1) PLAN_TRY(gmc_malloc_ipc((void**)&p->block, 8 * (2 * stride + sync_doubles)));   // exported to the peers
+        else PLAN_TRY(gmc_malloc((void**)&p->block, 8 * (2 * stride + sync_doubles)));
         p->contrib[0] = p->block; p->contrib[1] = p->block + stride;
         p->diffs = p->block + 2 * stride;
         p->flags = reinterpret_cast<unsigned int*>(p->block + 2 * stride + 2 * SYNC_RANKS);

@@ -146,6 +146,14 @@ class GmCuda:
             self.check(self.L.gmc_graph_make_reverse(h, int(want_maps), None))
         return g
 
+    def graph_pull_only(self, begin, r_begin, r_node_idx, comm=None):
+        """what the generated pagerank() copies in: begin (out-degrees) + the reverse CSR; no node_idx (no BFS on it)"""
+        h = _vp()
+        self.check(self.L.gmc_graph_create(C.byref(h), len(begin) - 1, len(r_node_idx)))
+        g = Graph(self, h)
+        self.check(self.L.gmc_graph_upload_sharded(h, comm.h if comm else None, _ptr(begin), None, _ptr(r_begin), _ptr(r_node_idx), None))
+        return g
+
     def graph_from_csr_sharded(self, comm, begin, node_idx, r_begin, r_node_idx):
         """multi-GPU copy-in: this rank uploads its slice of each array, the slices are allgathered over NVLink"""
         h = _vp()

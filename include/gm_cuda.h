@@ -57,7 +57,10 @@ int gmc_graph_create(gmc_graph** out, int32_t num_nodes, int32_t num_edges);
 int gmc_graph_destroy(gmc_graph* g);
 int gmc_graph_num_nodes(const gmc_graph* g, int32_t* n);
 int gmc_graph_num_edges(const gmc_graph* g, int32_t* m);
-/* host -> HBM copy of the frozen CSR (the copy_from of shl__G_begin / shl__G_node_idx) */
+/* host -> HBM copy of the frozen CSR (the copy_from of shl__G_begin / shl__G_node_idx).  node_idx may be NULL: a
+ * pull-only graph, exactly the arrays the generated pagerank() copies in (G_begin for the out-degrees, G_r_begin,
+ * G_r_node_idx: reference src/backend_cpp/gm_cpp_gen.cc:685-775 emits one shl array per array the procedure reads);
+ * calls that follow out-edges (BFS, semi-sort, reverse build) then return GMC_ERR_STATE. */
 int gmc_graph_upload(gmc_graph* g, const int32_t* begin, const int32_t* node_idx, void* stream);
 /* host-built reverse CSR -> HBM (when the caller already holds r_begin / r_node_idx) */
 int gmc_graph_upload_reverse(gmc_graph* g, const int32_t* r_begin, const int32_t* r_node_idx, void* stream);

@@ -281,3 +281,16 @@ def test_bfs_invariants_device_graph(gm, n, m):
         lev, _, _, cnt = g.bfs_levels(root)
         assert np.array_equal(np.where(lev >= 0, lev.astype(np.int64), INT_MAX), first.astype(np.int64))
         assert cnt.sum() == int((first < INT_MAX).sum())
+
+
+def test_pull_only_graph(gm, oracle, g_c1):
+    """the copy-in of the generated pagerank(): begin + reverse CSR only; out-edge traversals refuse loudly"""
+    from gmb200_loader import load_package
+    dg = gm.graph_pull_only(g_c1["begin"], g_c1["r_begin"], g_c1["r_node_idx"])
+    rank, info = dg.pagerank(e=1e-30, d=0.85, max_iter=20)
+    want, _, _ = oracle.pagerank(g_c1["begin"], g_c1["r_begin"], g_c1["r_node_idx"], 1e-30, 0.85, 20)
+    assert np.array_equal(rank, want)
+    with pytest.raises(load_package().GmcError):
+        dg.hop_dist(0)
+    with pytest.raises(load_package().GmcError):
+        dg.array("node_idx")
