@@ -45,6 +45,27 @@ WORKLOADS = {
 RMAT = dict(seed=1997, a=0.57, b=0.19, c=0.19, permute=True)
 
 
+_REAL_STDOUT = None
+
+
+def capture_stdout():
+    """stdout carries exactly ONE JSON line: native code under us (the reference's print_crc, NCCL banners) writes to
+    fd 1, so fd 1 is pointed at stderr for the whole run and the line goes to a duplicate of the original fd 1."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def alg_bytes_pagerank(n, m):
     """compulsory HBM traffic of one pull sweep, int32 ids / fp64 ranks"""
     return 4 * m + 40 * n
@@ -213,7 +234,7 @@ def run_reference_arm(args, n, m):
         "cpu_baseline": {"value": v, "unit": "GTEPS", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "GTEPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_name(args, n, m, workload=None):
@@ -368,7 +389,7 @@ def run_single(args, n, m):
         "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
         "bfs": bfs, "parity": parity,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
@@ -386,6 +407,7 @@ def main():
     ap.add_argument("--cpu-iters", type=int, default=5, help="sweeps per CPU-reference sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
+    capture_stdout()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3        # timing rule: at least 3 warm-up steps
     world = int(os.environ.get("WORLD_SIZE", "1"))
