@@ -43,9 +43,14 @@ using namespace gmc;
 constexpr int PR_THREADS = 1024;          // one CTA per SM, 32 independent warps
 constexpr int PR_WARPS = PR_THREADS / 32;
 constexpr int S_MAX = 512;                // rows up to this in-degree are summed sequentially, one lane per row (bit-exact)
-constexpr int LT = 2048;                  // entries per long-row task (16 warp steps of 128)
-constexpr int ST_COST = 2048;             // cost units per short-row task (slice cost = 32*len + SLICE_OVH)
-constexpr int SLICE_OVH = 68;             // keeps a task at <= 31 slices
+constexpr int LT = 2048;                  // entries per long-row task, default (16 warp steps of 128); power of two
+constexpr int ST_COST = 2048;             // cost units per short-row task, default (slice cost = 32*len + slice_ovh)
+constexpr int SLICE_OVH = 68;             // keeps a default task at <= 31 slices (one lane per slice offset)
+// shards with many entries run 4x / 2x larger tasks: the start and the end of a task (metadata chain, row
+// hand-over, split-row arrival) are latency chains without gathers in flight; measured on the LJ-shaped graph
+// 0.2149 -> 0.2015 ms per sweep (gpurun_out/r1k_variants2.log), while graphs with few tasks per warp keep the small ones
+constexpr int LT_BIG = 8192, ST_COST_BIG = 4096, SLICE_OVH_BIG = 136;
+constexpr int64_t BIG_TASK_ENTRIES = 24000000;   // per-shard entries from which the large tasks are used
 constexpr int ZT = 2048;                  // ids per zero-in-degree task
 constexpr int SHARD_ROW_COST = 6;         // entries one row epilogue weighs when the shards of a multi-rank run are cut
 #ifndef GMC_HOT_CAP
@@ -79,6 +84,7 @@ struct SweepArgs {
     const int32_t* __restrict__ stask_slice; // [n_stasks+1]
     const int32_t* __restrict__ outdeg;      // [N+1] by new id
     int32_t N, n_long, hot_n, EL;             // n_long, EL: rows / entries of THIS shard's long section
+    int32_t LT, lt_shift;                     // entries per long-row task = 1 << lt_shift
     int32_t long_id0, short_id0;              // id of the shard's first long row / of lane 0 of its first slice
     int32_t n_ltasks, n_stasks, n_ztasks, z0, z_end;  // [z0, z_end): the shard's ids without in-edges
     int32_t lt_lo, lt_hi, st_lo, st_hi, zt_lo, zt_hi;   // task ranges executed by this launch (experiment switches)
@@ -118,6 +124,7 @@ struct gmc_pr_plan {
     // global layout facts
     int32_t N = 0, M = 0, g_n_long = 0, n_pos = 0, hot_n = 1, g_nz_slices = 0, g_z0 = 0;
     // this shard: long rows [jl0, jl0+n_long), slices [s0, s0+n_slices), zero ids [z0, z_end)
+    int32_t lt = LT, lt_shift = 11, st_cost = ST_COST, slice_ovh = SLICE_OVH;     // task sizes of this plan
     int32_t jl0 = 0, n_long = 0, s0 = 0, n_slices = 0, EL = 0, EN = 0, n_ltasks = 0, n_stasks = 0, n_ztasks = 0, z0 = 0, z_end = 0;
     std::vector<int64_t> seg_off, seg_len;    // [world][3] owned id ranges of every rank (long, short, zero)
     // state block (one allocation, so that one CUDA IPC handle maps it into the peers):
@@ -240,8 +247,8 @@ __device__ __forceinline__ void split_arrive(const SweepArgs& A, int lane, int32
 }
 
 __device__ __forceinline__ void long_task(const SweepArgs& A, const double* hot, int lane, int32_t t) {
-    const int32_t x0 = t * LT;
-    const int32_t x1 = min(x0 + LT, A.EL);
+    const int32_t x0 = t << A.lt_shift;
+    const int32_t x1 = min(x0 + A.LT, A.EL);
     const int32_t a = __ldg(A.ltask_row + t);                     // row (0-based; id = row + 1) holding entry x0
     const int32_t e = (a + lane < A.n_long) ? __ldg(A.lbeg + a + lane + 1) : INT32_MAX;   // end of row a+lane
     const int32_t rb0 = __ldg(A.lbeg + a);
@@ -311,10 +318,10 @@ __device__ __forceinline__ void long_task(const SweepArgs& A, const double* hot,
     const int32_t split_base = A.n_ltasks + A.n_stasks + A.n_ztasks;
     if (head_split) {
         const int32_t e0 = __shfl_sync(FULL, e, 0);
-        split_arrive(A, lane, rb0 / LT, (e0 - 1) / LT, a, head_acc, A.head_part + t, split_base);
+        split_arrive(A, lane, rb0 >> A.lt_shift, (e0 - 1) >> A.lt_shift, a, head_acc, A.head_part + t, split_base);
     }
     if (tail_split && !(kl == 0 && head_split))
-        split_arrive(A, lane, t, (e_kl - 1) / LT, a + kl, tail_acc, A.tail_part + t, split_base);
+        split_arrive(A, lane, t, (e_kl - 1) >> A.lt_shift, a + kl, tail_acc, A.tail_part + t, split_base);
 }
 
 // rows with 1..S_MAX in-edges: one lane per row, terms added strictly left to right.  The loop runs over
@@ -513,7 +520,7 @@ __global__ void k_relabel(const int32_t* __restrict__ sorted_ids, int32_t n, int
 // padded long-row lengths (n_long values + a trailing 0), slice lengths (n_slices values + trailing 0), outdeg by new id
 __global__ void k_lengths(const int32_t* __restrict__ old_of_new, const int32_t* __restrict__ indeg, const int32_t* __restrict__ outdeg_old,
                           int32_t n, int32_t n_long, int32_t n_slices, int32_t* __restrict__ lbeg, int32_t* __restrict__ sbeg,
-                          int32_t* __restrict__ scost, int32_t* __restrict__ outdeg_new) {
+                          int32_t* __restrict__ scost, int32_t* __restrict__ outdeg_new, int32_t slice_ovh) {
     int32_t j = blockIdx.x * blockDim.x + threadIdx.x;     // 0-based row, id = j+1
     if (j == 0) { lbeg[n_long] = 0; sbeg[n_slices] = 0; scost[n_slices] = 0; outdeg_new[0] = 0; }
     if (j >= n) return;
@@ -524,7 +531,7 @@ __global__ void k_lengths(const int32_t* __restrict__ old_of_new, const int32_t*
     else if (((j - n_long) & 31) == 0) {
         const int32_t s = (j - n_long) >> 5;
         sbeg[s] = 32 * len;                                 // first row of the slice is its longest
-        scost[s] = len > 0 ? 32 * len + SLICE_OVH : 0;          // empty slices belong to the zero tasks
+        scost[s] = len > 0 ? 32 * len + slice_ovh : 0;          // empty slices belong to the zero tasks
     }
 }
 // dst[i] = src[lo + i] - src[lo] + add, i in [0, cnt): the shard's slice of a global offset array, rebased
@@ -558,11 +565,11 @@ __global__ void k_fill_entries(const int32_t* __restrict__ r_begin, const int32_
     }
 }
 // first[t] = row holding entry t*LT: last j with lbeg[j] <= target   (task cut points)
-__global__ void k_ltask_rows(const int32_t* __restrict__ lbeg, int32_t n_long, int32_t n_tasks, int32_t* __restrict__ first) {
+__global__ void k_ltask_rows(const int32_t* __restrict__ lbeg, int32_t n_long, int32_t n_tasks, int32_t lt, int32_t* __restrict__ first) {
     int32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t > n_tasks) return;
     if (t == n_tasks) { first[t] = n_long; return; }
-    const int32_t target = t * LT;
+    const int32_t target = t * lt;
     int32_t lo = 0, hi = n_long;             // lbeg[lo] <= target < lbeg[hi]
     while (hi - lo > 1) {
         const int32_t mid = lo + ((hi - lo) >> 1);
@@ -570,11 +577,11 @@ __global__ void k_ltask_rows(const int32_t* __restrict__ lbeg, int32_t n_long, i
     }
     first[t] = lo;
 }
-__global__ void k_stask_slices(const int32_t* __restrict__ cpos, int32_t n_slices, int32_t n_tasks, int32_t* __restrict__ first) {
+__global__ void k_stask_slices(const int32_t* __restrict__ cpos, int32_t n_slices, int32_t n_tasks, int32_t st_cost, int32_t* __restrict__ first) {
     int32_t u = blockIdx.x * blockDim.x + threadIdx.x;
     if (u > n_tasks) return;
     if (u == n_tasks) { first[u] = n_slices; return; }
-    const int32_t target = u * ST_COST;      // first slice with cpos >= target
+    const int32_t target = u * st_cost;      // first slice with cpos >= target
     int32_t lo = 0, hi = n_slices;
     while (lo < hi) {
         const int32_t mid = lo + ((hi - lo) >> 1);
@@ -705,7 +712,16 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
     PLAN_TRY(gmc_malloc((void**)&g_lbeg, 4 * ((size_t)p->g_n_long + 1)));
     PLAN_TRY(gmc_malloc((void**)&g_sbeg, 4 * ((size_t)g_n_slices + 1)));
     PLAN_TRY(gmc_malloc((void**)&g_scost, 4 * ((size_t)g_n_slices + 1)));
-    k_lengths<<<gb, 256, 0, st>>>(p->old_of_new, indeg, outdeg_old, n, p->g_n_long, g_n_slices, g_lbeg, g_sbeg, g_scost, p->outdeg);
+    // task sizes: large tasks for large shards (a long task may hold at most 32 rows: LT <= 31 * (s_max + 1))
+    if ((int64_t)m / world >= BIG_TASK_ENTRIES && (int64_t)LT_BIG <= 31LL * (s_max + 1)) {
+        p->lt = LT_BIG; p->st_cost = ST_COST_BIG; p->slice_ovh = SLICE_OVH_BIG;
+    }
+    if (const char* big = getenv("GMC_PR_BIGTASKS")) {            // tests / experiments: force either task size
+        const bool on = atoi(big) != 0 && (int64_t)LT_BIG <= 31LL * (s_max + 1);
+        p->lt = on ? LT_BIG : LT; p->st_cost = on ? ST_COST_BIG : ST_COST; p->slice_ovh = on ? SLICE_OVH_BIG : SLICE_OVH;
+    }
+    for (p->lt_shift = 0; (1 << p->lt_shift) < p->lt; p->lt_shift++) {}
+    k_lengths<<<gb, 256, 0, st>>>(p->old_of_new, indeg, outdeg_old, n, p->g_n_long, g_n_slices, g_lbeg, g_sbeg, g_scost, p->outdeg, p->slice_ovh);
     PLAN_TRY(exclusive_scan_i32(g_lbeg, g_lbeg, (size_t)p->g_n_long + 1, nullptr, st));
     PLAN_TRY(exclusive_scan_i32(g_sbeg, g_sbeg, (size_t)g_n_slices + 1, nullptr, st));
     PLAN_TRY(exclusive_scan_i32(g_scost, g_scost, (size_t)g_n_slices + 1, nullptr, st));
@@ -766,12 +782,12 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
     if (m > 0) k_fill_entries<<<div_up(m, 256), 256, 0, st>>>(g->r_begin, g->r_node_idx, n, m, p->new_of_old, p->g_n_long, p->jl0, p->n_long,
                                                                p->s0, p->n_slices, p->lbeg, p->sbeg, p->E);
     // 4. tasks
-    p->n_ltasks = div_up(p->EL, LT);
-    p->n_stasks = div_up(cost_total, ST_COST);
+    p->n_ltasks = div_up(p->EL, p->lt);
+    p->n_stasks = div_up(cost_total, p->st_cost);
     PLAN_TRY(gmc_malloc((void**)&p->ltask_row, 4 * ((size_t)p->n_ltasks + 1)));
     PLAN_TRY(gmc_malloc((void**)&p->stask_slice, 4 * ((size_t)p->n_stasks + 1)));
-    k_ltask_rows<<<div_up(p->n_ltasks + 1, 256), 256, 0, st>>>(p->lbeg, p->n_long, p->n_ltasks, p->ltask_row);
-    k_stask_slices<<<div_up(p->n_stasks + 1, 256), 256, 0, st>>>(scost, p->n_slices, p->n_stasks, p->stask_slice);
+    k_ltask_rows<<<div_up(p->n_ltasks + 1, 256), 256, 0, st>>>(p->lbeg, p->n_long, p->n_ltasks, p->lt, p->ltask_row);
+    k_stask_slices<<<div_up(p->n_stasks + 1, 256), 256, 0, st>>>(scost, p->n_slices, p->n_stasks, p->st_cost, p->stask_slice);
     {
         const size_t nl = (size_t)(p->n_ltasks ? p->n_ltasks : 1), nparts = 2 * nl + (size_t)p->n_stasks + (size_t)p->n_ztasks + 1;
         PLAN_TRY(gmc_malloc((void**)&p->head_part, 8 * nl)); PLAN_TRY(gmc_malloc((void**)&p->tail_part, 8 * nl));
@@ -815,7 +831,7 @@ SweepArgs make_args(const gmc_pr_plan* p, double d, int sweep, gmc_pr_ctrl* ctrl
     const int parity = sweep & 1;
     SweepArgs A;
     A.E = p->E; A.lbeg = p->lbeg; A.sbeg = p->sbeg; A.ltask_row = p->ltask_row; A.stask_slice = p->stask_slice; A.outdeg = p->outdeg;
-    A.N = p->N; A.n_long = p->n_long; A.hot_n = p->hot_n; A.EL = p->EL; A.n_ltasks = p->n_ltasks; A.n_stasks = p->n_stasks;
+    A.N = p->N; A.n_long = p->n_long; A.hot_n = p->hot_n; A.EL = p->EL; A.LT = p->lt; A.lt_shift = p->lt_shift; A.n_ltasks = p->n_ltasks; A.n_stasks = p->n_stasks;
     A.long_id0 = p->jl0 + 1; A.short_id0 = p->g_n_long + 1 + 32 * p->s0;
     A.n_ztasks = p->n_ztasks; A.z0 = p->z0; A.z_end = p->z_end;
     A.lt_lo = 0; A.lt_hi = p->n_ltasks; A.st_lo = 0; A.st_hi = p->n_stasks; A.zt_lo = 0; A.zt_hi = sweep >= 2 ? 0 : p->n_ztasks;

@@ -95,6 +95,19 @@ def test_pagerank_rmat_hubs(gm, oracle, g_rmat):
     assert err <= 1e-15, f"max abs err {err}, max ulp {graphs.max_ulp(rank, want)}"
 
 
+@pytest.mark.parametrize("big", ["0", "1"])
+def test_pagerank_task_sizes(gm, oracle, g_rmat, g_c1, big, monkeypatch):
+    """both task-size sets of the sweep plan (default 2048/2048; large shards 8192/4096, normally chosen from the
+    shard's entry count) must give the same result on the same graph: rows cut by task boundaries, <= 30 slices per task"""
+    monkeypatch.setenv("GMC_PR_BIGTASKS", big)
+    for g in (g_rmat, g_c1):
+        dg = dev_graph(gm, g)
+        rank, info = dg.pagerank(e=1e-30, d=0.85, max_iter=20)
+        want, it, _ = oracle.pagerank(g["begin"], g["r_begin"], g["r_node_idx"], 1e-30, 0.85, 20)
+        assert info.iterations == it
+        assert np.abs(rank - want).max() <= 1e-15
+
+
 def test_pagerank_device_built_reverse(gm, oracle, g_rmat):
     dg = gm.graph_from_csr(g_rmat["begin"], g_rmat["node_idx"], semi_sort=True, make_reverse=True)
     rank, _ = dg.pagerank(max_iter=5)
