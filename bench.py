@@ -320,7 +320,7 @@ def run_single(args, n, m):
     d2h = rank_host.nbytes
     parts = {"h2d_ms": [], "plan_and_sweeps_ms": []}
 
-    def e2e_step():
+    def e2e_step_parts():          # un-overlapped: copy-in, then plan + sweeps + copy-back (only for the breakdown)
         t_a = time.perf_counter()
         dg = lib.graph_pull_only(pinned["begin"], pinned["r_begin"], pinned["r_node_idx"])
         t_b = time.perf_counter()
@@ -330,11 +330,19 @@ def run_single(args, n, m):
         parts["h2d_ms"].append((t_b - t_a) * 1e3); parts["plan_and_sweeps_ms"].append((t_c - t_b) * 1e3)
         return inf
 
+    def e2e_step():                # the call a user makes: gmc_pagerank_host_csr (copy-in overlapped with the plan build)
+        _, inf = lib.pagerank_host_csr(pinned["begin"], pinned["r_begin"], pinned["r_node_idx"], rank_host, 1e-30, 0.85, iters)
+        return inf
+
     for _ in range(min(args.warmup, 2)):
         e2e_step()
+        e2e_step_parts()
     lib.sync()
     for v in parts.values():
         v.clear()
+    for _ in range(2):
+        e2e_step_parts()
+    lib.sync()
     t0 = time.perf_counter()
     e2e_steps = max(1, min(args.steps, 5))
     for _ in range(e2e_steps):
@@ -343,7 +351,9 @@ def run_single(args, n, m):
     e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
     e2e = {"value": round(m * iters / e2e_ms / 1e6, 3), "unit": "GTEPS", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
            "ms_per_step": round(e2e_ms, 3), "steps": e2e_steps,
-           "breakdown_ms": {"h2d_begin_rbegin_rnodeidx": round(float(np.mean(parts["h2d_ms"])), 3),
+           "call": "gmc_pagerank_host_csr (pinned host CSR in, host rank[] out; copy-in overlapped with the plan build)",
+           "breakdown_ms": {"what": "the same work un-overlapped (upload, then gmc_pagerank)",
+                            "h2d_begin_rbegin_rnodeidx": round(float(np.mean(parts["h2d_ms"])), 3),
                             "plan_20_sweeps_d2h": round(float(np.mean(parts["plan_and_sweeps_ms"])), 3)},
            "h2d_gbs": round(h2d / float(np.mean(parts["h2d_ms"])) / 1e6, 1)}
     if os.environ.get("GMC_BENCH_DEBUG"):

@@ -64,6 +64,14 @@ int exclusive_scan_i32(const int32_t* in, int32_t* out, size_t n, int32_t* total
 
 extern "C" int gmc_malloc_ipc(void** p, size_t bytes);   // internal: plain cudaMalloc (IPC-exportable); gmc_malloc uses the memory pool
 
+struct gmc_pending_upload {
+    static constexpr int MAX_CHUNKS = 8;
+    cudaEvent_t small = nullptr;
+    int nchunks = 0;
+    cudaEvent_t chunk[MAX_CHUNKS] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    int32_t end[MAX_CHUNKS] = {0, 0, 0, 0, 0, 0, 0, 0};
+};
+
 // The device-resident CSR mirror behind gmc_graph.
 struct gmc_pr_plan;
 struct gmc_bfs_ws;
@@ -78,6 +86,9 @@ struct gmc_graph {
     bool semi_sorted = false;
     bool has_reverse = false;
     bool has_forward = true;        // false: node_idx was not copied in (pull-only graph: PageRank needs begin + the reverse CSR)
+    // copy-in still in flight (gmc_pagerank_host_csr): begin/r_begin are complete once `small` has fired, r_node_idx[0, end[k])
+    // once chunk[k] has; the PageRank plan builder waits on them on its own stream, chunk by chunk (no host sync)
+    struct gmc_pending_upload* pending = nullptr;
     // lazily built per-algorithm state (invalidated when the CSR changes)
     gmc_pr_plan* pr = nullptr;      // PageRank plan: relabelled entry array, tasks, state buffers (gmc_pagerank.cu)
     gmc_bfs_ws* bfs = nullptr;

@@ -539,14 +539,32 @@ __global__ void k_rebase(const int32_t* __restrict__ src, int32_t lo, int32_t cn
     int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < cnt) dst[i] = src[lo + i] - src[lo] + add;
 }
-// scatter every reverse edge whose destination row belongs to the shard into E, keeping its position inside
-// the row (= the reference's summation order).  jl0/nl: the shard's long rows, s0/ns: its slices.
-__global__ void k_fill_entries(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t m,
-                               const int32_t* __restrict__ new_of_old, int32_t g_n_long, int32_t jl0, int32_t nl, int32_t s0, int32_t ns,
-                               const int32_t* __restrict__ lbeg, const int32_t* __restrict__ sbeg, int32_t* __restrict__ E) {
-    int32_t eidx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (eidx >= m) return;
+// hint[b] = row holding reverse edge b * FILL_TILE (b <= ceil(m / FILL_TILE): the last one is n): narrows the per-edge
+// row search of k_fill_entries from log2(N) global steps to the few rows one tile of edges spans
+constexpr int FILL_TILE = 2048;
+__global__ void k_row_hints(const int32_t* __restrict__ r_begin, int32_t n, int32_t m, int32_t n_hints, int32_t* __restrict__ hint) {
+    int32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n_hints) return;
+    const int64_t e64 = (int64_t)b * FILL_TILE;
+    if (e64 >= m) { hint[b] = n; return; }
+    const int32_t eidx = (int32_t)e64;
     int32_t lo = 0, hi = n;   // r_begin[lo] <= eidx < r_begin[hi]
+    while (hi - lo > 1) {
+        const int32_t mid = lo + ((hi - lo) >> 1);
+        if (r_begin[mid] <= eidx) lo = mid; else hi = mid;
+    }
+    hint[b] = lo;
+}
+// scatter the reverse edges [e_lo, e_hi) whose destination row belongs to the shard into E, keeping the position inside
+// the row (= the reference's summation order).  jl0/nl: the shard's long rows, s0/ns: its slices.
+__global__ void k_fill_entries(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t e_lo, int32_t e_hi,
+                               const int32_t* __restrict__ hint, const int32_t* __restrict__ new_of_old, int32_t g_n_long, int32_t jl0,
+                               int32_t nl, int32_t s0, int32_t ns, const int32_t* __restrict__ lbeg, const int32_t* __restrict__ sbeg,
+                               int32_t* __restrict__ E) {
+    const int64_t e64 = (int64_t)e_lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e64 >= e_hi) return;
+    const int32_t eidx = (int32_t)e64;
+    int32_t lo = hint[eidx / FILL_TILE], hi = min(hint[eidx / FILL_TILE + 1] + 1, n);   // r_begin[lo] <= eidx < r_begin[hi]
     while (hi - lo > 1) {
         const int32_t mid = lo + ((hi - lo) >> 1);
         if (r_begin[mid] <= eidx) lo = mid; else hi = mid;
@@ -671,6 +689,7 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
     uint32_t *key_a = nullptr, *key_a2 = nullptr;
     unsigned long long *key_b = nullptr, *key_b2 = nullptr;
     int32_t* tot = nullptr;
+    int32_t* hints = nullptr;
     const size_t nn = (size_t)n;
     const unsigned gb = (unsigned)div_up(n, 256);
     int32_t h[2] = {0, 0};
@@ -687,6 +706,7 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
     PLAN_TRY(gmc_malloc((void**)&p->new_of_old, 4 * nn)); PLAN_TRY(gmc_malloc((void**)&p->old_of_new, 4 * (nn + 1)));
     PLAN_TRY(gmc_malloc((void**)&p->outdeg, 4 * (nn + 1)));
 
+    if (g->pending) PLAN_CUDA(cudaStreamWaitEvent(st, g->pending->small, 0));       // begin / r_begin have landed
     // 1. degrees, number of long rows, the hot block, the relabelling (identical on every rank)
     if (const char* sm = getenv("GMC_PR_SMAX")) { s_max = atoi(sm); if (s_max < 64) s_max = 64; if (s_max > 4096) s_max = 4096; }   // experiments (>= 64: a long task holds at most 32 rows)
     k_degrees<<<gb, 256, 0, st>>>(g->begin, g->r_begin, n, outdeg_old, indeg, key_a, ids, is_long, is_pos, s_max);
@@ -779,8 +799,23 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
     // 3. the shard's entry array
     PLAN_TRY(gmc_malloc((void**)&p->E, 4 * ((size_t)p->EN + 8)));
     PLAN_CUDA(cudaMemsetAsync(p->E, 0, 4 * ((size_t)p->EN + 8), st));
-    if (m > 0) k_fill_entries<<<div_up(m, 256), 256, 0, st>>>(g->r_begin, g->r_node_idx, n, m, p->new_of_old, p->g_n_long, p->jl0, p->n_long,
-                                                               p->s0, p->n_slices, p->lbeg, p->sbeg, p->E);
+    if (m > 0) {
+        const int32_t n_hints = div_up(m, FILL_TILE) + 1;
+        PLAN_TRY(gmc_malloc((void**)&hints, 4 * (size_t)n_hints));
+        k_row_hints<<<div_up(n_hints, 256), 256, 0, st>>>(g->r_begin, n, m, n_hints, hints);
+        // r_node_idx may still be arriving over PCIe (gmc_pagerank_host_csr): fill chunk by chunk as the copies land
+        const gmc_pending_upload* pu = g->pending;
+        const int nch = pu ? pu->nchunks : 1;
+        int32_t e_lo = 0;
+        for (int c = 0; c < nch; c++) {
+            const int32_t e_hi = pu ? pu->end[c] : m;
+            if (pu) PLAN_CUDA(cudaStreamWaitEvent(st, pu->chunk[c], 0));
+            if (e_hi > e_lo)
+                k_fill_entries<<<div_up(e_hi - e_lo, 256), 256, 0, st>>>(g->r_begin, g->r_node_idx, n, e_lo, e_hi, hints, p->new_of_old, p->g_n_long,
+                                                                         p->jl0, p->n_long, p->s0, p->n_slices, p->lbeg, p->sbeg, p->E);
+            e_lo = e_hi;
+        }
+    }
     // 4. tasks
     p->n_ltasks = div_up(p->EL, p->lt);
     p->n_stasks = div_up(cost_total, p->st_cost);
@@ -818,7 +853,7 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
 fail:
     cudaFree(outdeg_old); cudaFree(indeg); cudaFree(ids); cudaFree(ids2); cudaFree(is_long); cudaFree(is_pos); cudaFree(hot_rank); cudaFree(scost);
     cudaFree(g_lbeg); cudaFree(g_sbeg); cudaFree(g_scost);
-    cudaFree(key_a); cudaFree(key_a2); cudaFree(key_b); cudaFree(key_b2); cudaFree(tot);
+    cudaFree(key_a); cudaFree(key_a2); cudaFree(key_b); cudaFree(key_b2); cudaFree(tot); cudaFree(hints);
     if (rc != GMC_OK) { free_plan(p); return rc; }
     *out = p;
     return GMC_OK;
@@ -1071,6 +1106,60 @@ int gmc_pagerank(gmc_graph* g, double e, double d, int32_t max_iter, double* ran
 
 // how the current plan exchanges contributions between ranks: 0 = single rank, 1 = NCCL allgather after the sweep,
 // 2 = peer-memory stores from the sweep epilogue (CUDA IPC mapping over NVLink)
+// The generated pagerank() procedure as ONE call on host arrays: Shoal copy-in of begin / r_begin / r_node_idx
+// (gm_cpp_gen.cc:685-775), the do-while loop nest, copy_back of the rank array (:1480).  The copy-in runs on its own
+// stream in chunks; the plan builder starts as soon as the two offset arrays have landed (degrees, sorts, relabelling
+// need nothing else) and fills the entry array chunk by chunk behind the PCIe copy, so ~2 ms of plan building hide
+// behind the 5.7 ms the LJ-shaped copy-in takes.  Host arrays should be pinned (gmc_host_register) for full PCIe rate.
+int gmc_pagerank_host_csr(int32_t num_nodes, int32_t num_edges, const int32_t* begin, const int32_t* r_begin, const int32_t* r_node_idx,
+                          double e, double d, int32_t max_iter, double* rank_host, gmc_pagerank_info* info) {
+    GMC_REQUIRE(num_nodes >= 0 && num_edges >= 0 && begin && r_begin && (r_node_idx || num_edges == 0) && (rank_host || num_nodes == 0),
+                GMC_ERR_ARG, "gmc_pagerank_host_csr: bad args");
+    if (num_nodes == 0) { if (info) memset(info, 0, sizeof(*info)); return GMC_OK; }
+    gmc_graph* g = nullptr;
+    GMC_TRY(gmc_graph_create(&g, num_nodes, num_edges));
+    gmc_pending_upload pu;
+    cudaStream_t cs = nullptr;
+    double* tmp = nullptr;
+    int rc = GMC_OK;
+    const size_t nb = sizeof(int32_t) * ((size_t)num_nodes + 1);
+    auto fail = [&](const char* what) { set_error("gmc_pagerank_host_csr: %s: %s", what, cudaGetErrorString(cudaGetLastError())); rc = GMC_ERR_CUDA; };
+    do {
+        g->has_forward = num_edges == 0;           // pull-only graph: node_idx is not copied in
+        if ((rc = gmc_malloc((void**)&g->r_begin, nb)) != GMC_OK) break;
+        if ((rc = gmc_malloc((void**)&g->r_node_idx, sizeof(int32_t) * (size_t)(num_edges ? num_edges : 1))) != GMC_OK) break;
+        if ((rc = gmc_malloc((void**)&tmp, sizeof(double) * (size_t)num_nodes)) != GMC_OK) break;
+        // non-blocking: the allocator and the plan kernels use the legacy default stream, which must not wait for the copies
+        if (cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) != cudaSuccess) { fail("stream"); break; }
+        if (cudaEventCreateWithFlags(&pu.small, cudaEventDisableTiming) != cudaSuccess) { fail("event"); break; }
+        if (cudaMemcpyAsync(g->begin, begin, nb, cudaMemcpyHostToDevice, cs) != cudaSuccess ||
+            cudaMemcpyAsync(g->r_begin, r_begin, nb, cudaMemcpyHostToDevice, cs) != cudaSuccess ||
+            cudaEventRecord(pu.small, cs) != cudaSuccess) { fail("copy-in"); break; }
+        pu.nchunks = num_edges >= (1 << 22) ? gmc_pending_upload::MAX_CHUNKS : 1;
+        bool ok = true;
+        for (int c = 0; c < pu.nchunks && ok; c++) {
+            const int32_t lo = (int32_t)((int64_t)num_edges * c / pu.nchunks), hi = (int32_t)((int64_t)num_edges * (c + 1) / pu.nchunks);
+            pu.end[c] = hi;
+            ok = cudaEventCreateWithFlags(&pu.chunk[c], cudaEventDisableTiming) == cudaSuccess;
+            if (ok && hi > lo) ok = cudaMemcpyAsync(g->r_node_idx + lo, r_node_idx + lo, sizeof(int32_t) * (size_t)(hi - lo), cudaMemcpyHostToDevice, cs) == cudaSuccess;
+            if (ok) ok = cudaEventRecord(pu.chunk[c], cs) == cudaSuccess;
+        }
+        if (!ok) { fail("copy-in"); break; }
+        g->has_reverse = true;
+        g->pending = &pu;
+        rc = gmc_pagerank_dev(g, e, d, max_iter, tmp, info, nullptr);       // plan (waits on the events) + sweeps
+        g->pending = nullptr;
+        if (rc == GMC_OK) rc = gmc_d2h(rank_host, tmp, sizeof(double) * (size_t)num_nodes, nullptr);
+    } while (0);
+    if (cs) { cudaStreamSynchronize(cs); cudaStreamDestroy(cs); }
+    if (pu.small) cudaEventDestroy(pu.small);
+    for (int c = 0; c < gmc_pending_upload::MAX_CHUNKS; c++) if (pu.chunk[c]) cudaEventDestroy(pu.chunk[c]);
+    cudaFree(tmp);
+    g->pending = nullptr;
+    gmc_graph_destroy(g);
+    return rc;
+}
+
 int gmc_pagerank_exchange_path(gmc_graph* g, int* path) {
     GMC_REQUIRE(g && path, GMC_ERR_ARG, "gmc_pagerank_exchange_path: NULL");
     *path = !g->pr || g->pr->world == 1 ? 0 : (g->pr->p2p ? 2 : 1);

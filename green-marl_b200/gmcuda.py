@@ -65,6 +65,7 @@ SIGNATURES = {
     "gmc_file_write": (C.c_int, [C.c_char_p, _i32, _i32, _vp, _vp]),
     "gmc_pagerank": (C.c_int, [_vp, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo)]),
     "gmc_pagerank_dev": (C.c_int, [_vp, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo), _vp]),
+    "gmc_pagerank_host_csr": (C.c_int, [_i32, _i32, _vp, _vp, _vp, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo)]),
     "gmc_pagerank_time_sweeps": (C.c_int, [_vp, C.c_double, _i32, _i32, _vp, C.POINTER(_i32), _vp]),
     "gmc_pagerank_plan_info": (C.c_int, [_vp, C.POINTER(PlanInfo)]),
     "gmc_hop_dist": (C.c_int, [_vp, _i32, _vp, C.POINTER(BfsInfo)]),
@@ -153,6 +154,17 @@ class GmCuda:
         g = Graph(self, h)
         self.check(self.L.gmc_graph_upload_sharded(h, comm.h if comm else None, _ptr(begin), None, _ptr(r_begin), _ptr(r_node_idx), None))
         return g
+
+    def pagerank_host_csr(self, begin, r_begin, r_node_idx, rank_host, e=1e-30, d=0.85, max_iter=20):
+        """the generated pagerank() on host arrays in one call: copy-in (overlapped with the plan build), sweeps, copy-back"""
+        n, m = len(begin) - 1, len(r_node_idx)
+        assert rank_host.dtype == np.float64 and len(rank_host) >= n
+        for a in (begin, r_begin, r_node_idx):
+            assert a.dtype == np.int32 and a.flags["C_CONTIGUOUS"]
+        info = PagerankInfo()
+        self.check(self.L.gmc_pagerank_host_csr(n, m, _ptr(begin), _ptr(r_begin), _ptr(r_node_idx), e, d, max_iter, _ptr(rank_host),
+                                                C.byref(info)))
+        return rank_host, info
 
     def graph_from_csr_sharded(self, comm, begin, node_idx, r_begin, r_node_idx):
         """multi-GPU copy-in: this rank uploads its slice of each array, the slices are allgathered over NVLink"""

@@ -106,6 +106,15 @@ int gmc_pagerank(gmc_graph* g, double e, double d, int32_t max_iter, double* ran
 int gmc_pagerank_dev(gmc_graph* g, double e, double d, int32_t max_iter, double* rank_dev,
                      gmc_pagerank_info* info, void* stream);
 
+/* The whole generated procedure on HOST arrays in one call: copy-in of what pagerank() reads (begin for the
+ * out-degrees, r_begin, r_node_idx: the Shoal copy-in of gm_cpp_gen.cc:685-775), the loop nest, copy_back of
+ * the rank array (:1480).  Same result as gmc_graph_upload + gmc_graph_upload_reverse + gmc_pagerank; the
+ * difference is overlap: the copy-in runs on its own stream and the sweep plan is built behind it.  Pin the
+ * arrays (gmc_host_register) for full PCIe rate.  Nothing stays on the device afterwards. */
+int gmc_pagerank_host_csr(int32_t num_nodes, int32_t num_edges, const int32_t* begin, const int32_t* r_begin,
+                          const int32_t* r_node_idx, double e, double d, int32_t max_iter, double* rank_host,
+                          gmc_pagerank_info* info);
+
 /* measurement aid (bench.py's roofline figure): rank = 1/N, `warmup` untimed sweeps, then `n` sweeps each
  * bracketed by its own pair of CUDA events on `stream`; ms_out[i] = device time of timed sweep i. */
 int gmc_pagerank_time_sweeps(gmc_graph* g, double d, int32_t warmup, int32_t n, float* ms_out,

@@ -108,6 +108,25 @@ def test_pagerank_task_sizes(gm, oracle, g_rmat, g_c1, big, monkeypatch):
         assert np.abs(rank - want).max() <= 1e-15
 
 
+def test_pagerank_host_csr_one_call(gm, oracle, g_rmat, g_c1):
+    """gmc_pagerank_host_csr (copy-in overlapped with the plan build, chunked entry fill) == upload + gmc_pagerank, bit for bit;
+    5 M edges: above the chunking threshold, so the entry array is filled in 8 chunks behind the copies"""
+    big = graphs.rmat(oracle, 300000, 5000000)
+    for g in (g_c1, g_rmat, big):
+        rank = np.zeros(g["N"], np.float64)
+        _, info = gm.pagerank_host_csr(g["begin"], g["r_begin"], g["r_node_idx"], rank, 1e-30, 0.85, 20)
+        want, it, _ = oracle.pagerank(g["begin"], g["r_begin"], g["r_node_idx"], 1e-30, 0.85, 20)
+        assert info.iterations == it
+        assert np.abs(rank - want).max() <= 1e-15
+        ref_rank, _ = dev_graph(gm, g).pagerank(e=1e-30, d=0.85, max_iter=20)
+        assert np.array_equal(rank, ref_rank)
+    # degenerate inputs: no edges / no vertices
+    b = np.zeros(6, np.int32); ri = np.zeros(0, np.int32); rank = np.zeros(5, np.float64)
+    gm.pagerank_host_csr(b, b, ri, rank, 1e-30, 0.85, 3)
+    assert np.allclose(rank, 0.15 / 5)
+    gm.pagerank_host_csr(np.zeros(1, np.int32), np.zeros(1, np.int32), ri, np.zeros(0, np.float64), 1e-30, 0.85, 3)
+
+
 def test_pagerank_device_built_reverse(gm, oracle, g_rmat):
     dg = gm.graph_from_csr(g_rmat["begin"], g_rmat["node_idx"], semi_sort=True, make_reverse=True)
     rank, _ = dg.pagerank(max_iter=5)

@@ -6,7 +6,7 @@ from gmb200_loader import load_package
 L = load_package().GmCuda(); L.init(0)
 n, m = (4850000, 69000000) if len(sys.argv) < 3 else (int(sys.argv[1]), int(sys.argv[2]))
 want = None
-for smax in [64, 96, 128, 192, 256, 384, 512, 1024]:
+for smax in [272, 384, 512, 768, 1024, 2048, 4096]:
     os.environ["GMC_PR_SMAX"] = str(smax)
     g = L.generate_rmat(n, m, 1997)
     pi = g.pagerank_plan_info()
