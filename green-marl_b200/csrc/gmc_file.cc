@@ -79,3 +79,123 @@ int gmc_file_write(const char* path, int32_t n, int32_t m, const int32_t* begin,
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------
+// EDGE_LIST text ingest: gm_edge_list_graph_reader::builtGraph (apps/output_cpp/gm_graph/src/
+// gm_edge_list_graph_reader.cc:68-171).  Lines "src dst" or "src *" (vertex only), blank lines and lines starting
+// with '#' skipped (:99,:140), tokens separated by blanks / tabs (:101,:105); every id that occurs becomes a vertex,
+// numbered densely in ascending raw-id order (:112-117, ids below LOOKUP_SIZE = 80 000 000, :66).  The reference reads
+// the file three times with getline/strtok and inserts into a std::map; here the file is mapped once, the lines
+// are parsed by all host threads, and the (src, dst) pairs go to the device as 64-bit keys where one radix sort
+// yields the semi-sorted CSR (gmc_gen.cu: gmc_graph_from_edge_keys).  Input need not be sorted by source
+// (the reference asserts it, :146); on sorted input the result is identical.
+// ---------------------------------------------------------------------------------------------------------
+#include <fcntl.h>
+#include <omp.h>
+#include <string.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+static const int64_t EDGE_LIST_LOOKUP_SIZE = 80000000;
+
+namespace {
+struct ParsedLines {
+    std::vector<int32_t> src, dst, lone;
+    int64_t max_id = -1;
+    long bad_line = -1;          // byte offset of the first malformed line
+};
+inline bool is_blank(char c) { return c == ' ' || c == '\t'; }
+// one token of decimal digits -> id; false when it is not a non-negative integer below LOOKUP_SIZE
+inline bool parse_id(const char*& p, const char* end, int64_t& v) {
+    const char* q = p;
+    if (q < end && *q == '+') q++;
+    if (q >= end || *q < '0' || *q > '9') return false;
+    int64_t x = 0;
+    while (q < end && *q >= '0' && *q <= '9') { x = x * 10 + (*q - '0'); if (x >= EDGE_LIST_LOOKUP_SIZE) return false; q++; }
+    if (q < end && !is_blank(*q) && *q != '\r' && *q != '\n') return false;
+    p = q; v = x;
+    return true;
+}
+void parse_range(const char* base, const char* p, const char* end, ParsedLines& out) {
+    while (p < end) {
+        const char* line = p;
+        const char* eol = (const char*)memchr(p, '\n', (size_t)(end - p));
+        if (!eol) eol = end;
+        p = eol + 1;
+        if (eol == line || *line == '#') continue;
+        const char* q = line;
+        while (q < eol && is_blank(*q)) q++;
+        if (q == eol || *q == '\r') continue;
+        int64_t a, b;
+        bool ok = parse_id(q, eol, a);
+        while (ok && q < eol && is_blank(*q)) q++;
+        if (ok && q < eol && *q == '*') {
+            out.lone.push_back((int32_t)a);
+            if (a > out.max_id) out.max_id = a;
+            continue;
+        }
+        ok = ok && parse_id(q, eol, b);
+        if (!ok) { if (out.bad_line < 0) out.bad_line = (long)(line - base); continue; }
+        out.src.push_back((int32_t)a); out.dst.push_back((int32_t)b);
+        if (a > out.max_id) out.max_id = a;
+        if (b > out.max_id) out.max_id = b;
+    }
+}
+}  // namespace
+
+// internal (gmc_gen.cu): edge keys (src << 32 | dst) in host memory -> device graph, semi-sorted (+ reverse CSR)
+extern "C" int gmc_graph_from_edge_keys(gmc_graph** out, int32_t n, int32_t m, const uint64_t* keys_host, int make_reverse);
+
+extern "C" int gmc_edge_list_read(const char* path, gmc_graph** out, int make_reverse) {
+    GMC_REQUIRE(path && out, GMC_ERR_ARG, "gmc_edge_list_read: NULL");
+    *out = nullptr;
+    int fd = open(path, O_RDONLY);
+    GMC_REQUIRE(fd >= 0, GMC_ERR_IO, "gmc_edge_list_read: cannot open %s", path);
+    struct stat sb;
+    if (fstat(fd, &sb) != 0) { close(fd); set_error("gmc_edge_list_read: cannot stat %s", path); return GMC_ERR_IO; }
+    const size_t sz = (size_t)sb.st_size;
+    const char* base = sz ? (const char*)mmap(nullptr, sz, PROT_READ, MAP_PRIVATE, fd, 0) : "";
+    close(fd);
+    if (sz && base == MAP_FAILED) { set_error("gmc_edge_list_read: cannot map %s", path); return GMC_ERR_IO; }
+    const int T = sz > (1u << 20) ? omp_get_max_threads() : 1;
+    std::vector<ParsedLines> parts((size_t)T);
+    std::vector<size_t> cut((size_t)T + 1);
+    for (int t = 0; t <= T; t++) {          // chunk borders moved forward to the next line start
+        size_t c = sz / (size_t)T * (size_t)t;
+        if (t == T) c = sz;
+        else if (t > 0) { const char* nl = (const char*)memchr(base + c, '\n', sz - c); c = nl ? (size_t)(nl - base) + 1 : sz; }
+        cut[t] = c;
+    }
+#pragma omp parallel for num_threads(T) schedule(static, 1)
+    for (int t = 0; t < T; t++)
+        if (cut[t + 1] > cut[t]) parse_range(base, base + cut[t], base + cut[t + 1], parts[t]);
+    if (sz) munmap((void*)base, sz);
+    int64_t max_id = -1, m64 = 0;
+    for (auto& p : parts) {
+        if (p.bad_line >= 0) { set_error("gmc_edge_list_read: %s: malformed line at byte %ld (want \"src dst\" or \"src *\", ids in [0, %lld))", path, p.bad_line, (long long)EDGE_LIST_LOOKUP_SIZE); return GMC_ERR_IO; }
+        if (p.max_id > max_id) max_id = p.max_id;
+        m64 += (int64_t)p.src.size();
+    }
+    GMC_REQUIRE(m64 <= 0x7fffff00LL, GMC_ERR_ARG, "gmc_edge_list_read: %lld edges exceed the 32-bit edge_t build", (long long)m64);
+    // ids that occur, numbered densely in ascending raw order
+    std::vector<int32_t> lookup((size_t)(max_id + 1), 0);
+#pragma omp parallel for num_threads(T) schedule(static, 1)
+    for (int t = 0; t < T; t++) {
+        for (int32_t a : parts[t].src) lookup[a] = 1;       // racing writers all store 1
+        for (int32_t b : parts[t].dst) lookup[b] = 1;
+        for (int32_t a : parts[t].lone) lookup[a] = 1;
+    }
+    int32_t n = 0;
+    for (int64_t i = 0; i <= max_id; i++) { const int32_t present = lookup[i]; lookup[i] = present ? n : -1; n += present; }
+    std::vector<uint64_t> keys((size_t)(m64 ? m64 : 1));
+    std::vector<int64_t> off((size_t)T + 1, 0);
+    for (int t = 0; t < T; t++) off[t + 1] = off[t] + (int64_t)parts[t].src.size();
+#pragma omp parallel for num_threads(T) schedule(static, 1)
+    for (int t = 0; t < T; t++) {
+        const auto& p = parts[t];
+        uint64_t* k = keys.data() + off[t];
+        for (size_t i = 0; i < p.src.size(); i++) k[i] = ((uint64_t)(uint32_t)lookup[p.src[i]] << 32) | (uint32_t)lookup[p.dst[i]];
+    }
+    return gmc_graph_from_edge_keys(out, n, (int32_t)m64, keys.data(), make_reverse);
+}

@@ -114,6 +114,25 @@ int keys_to_graph(gmc_graph** out, int32_t n, int32_t m, uint64_t* keys, uint64_
 
 extern "C" {
 
+// internal entry of the EDGE_LIST ingest (gmc_file.cc): host edge keys (src << 32 | dst) -> device graph.  One radix sort
+// of the keys is the reference's add_edge + freeze + do_semi_sort (gm_edge_list_graph_reader.cc:137-168).
+int gmc_graph_from_edge_keys(gmc_graph** out, int32_t n, int32_t m, const uint64_t* keys_host, int make_reverse) {
+    GMC_REQUIRE(out && n >= 0 && m >= 0 && (keys_host || m == 0), GMC_ERR_ARG, "gmc_graph_from_edge_keys: bad args");
+    uint64_t *k0 = nullptr, *k1 = nullptr;
+    GMC_TRY(gmc_malloc((void**)&k0, sizeof(uint64_t) * (size_t)(m ? m : 1)));
+    int rc = gmc_malloc((void**)&k1, sizeof(uint64_t) * (size_t)(m ? m : 1));
+    if (rc == GMC_OK && m && cudaMemcpy(k0, keys_host, sizeof(uint64_t) * (size_t)m, cudaMemcpyHostToDevice) != cudaSuccess) {
+        set_error("edge keys copy-in: %s", cudaGetErrorString(cudaGetLastError())); rc = GMC_ERR_CUDA;
+    }
+    if (rc == GMC_OK) rc = keys_to_graph(out, n, m, k0, k1);
+    cudaFree(k0); cudaFree(k1);
+    if (rc == GMC_OK && make_reverse) {
+        rc = gmc_graph_make_reverse(*out, 0, nullptr);
+        if (rc != GMC_OK) { gmc_graph_destroy(*out); *out = nullptr; }
+    }
+    return rc;
+}
+
 int gmc_graph_generate_uniform(gmc_graph** out, int32_t n, int32_t m, uint64_t seed) {
     GMC_REQUIRE(out && n > 0 && m >= 0, GMC_ERR_ARG, "gmc_graph_generate_uniform: bad args");
     uint64_t *k0 = nullptr, *k1 = nullptr;

@@ -63,6 +63,7 @@ SIGNATURES = {
     "gmc_file_read_header": (C.c_int, [C.c_char_p, C.POINTER(_i32), C.POINTER(_i32)]),
     "gmc_file_read": (C.c_int, [C.c_char_p, _vp, _vp]),
     "gmc_file_write": (C.c_int, [C.c_char_p, _i32, _i32, _vp, _vp]),
+    "gmc_edge_list_read": (C.c_int, [C.c_char_p, C.POINTER(_vp), C.c_int]),
     "gmc_pagerank": (C.c_int, [_vp, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo)]),
     "gmc_pagerank_dev": (C.c_int, [_vp, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo), _vp]),
     "gmc_pagerank_host_csr": (C.c_int, [_i32, _i32, _vp, _vp, _vp, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo)]),
@@ -174,6 +175,12 @@ class GmCuda:
         self.check(self.L.gmc_graph_upload_sharded(h, comm.h if comm else None, _ptr(begin), _ptr(node_idx), _ptr(r_begin),
                                                    _ptr(r_node_idx), None))
         return g
+
+    def edge_list_read(self, path, make_reverse=True):
+        """EDGE_LIST text file -> resident graph (ids densified, rows semi-sorted, reverse CSR on request)"""
+        h = _vp()
+        self.check(self.L.gmc_edge_list_read(path.encode(), C.byref(h), int(make_reverse)))
+        return Graph(self, h)
 
     def generate_rmat(self, n, m, seed=1997, a=0.57, b=0.19, c=0.19, permute=True):
         h = _vp()

@@ -257,6 +257,34 @@ bool gm_graph::load_binary(char* filename) {
     return true;
 }
 
+// EDGE_LIST ingest: parse + CSR build + semi-sort + reverse CSR in one device-side call, then the host view
+// the generated code reads (public begin/node_idx/r_begin/r_node_idx pointers) is downloaded from the mirror.
+bool gm_graph::load_edge_list(char* filename, std::vector<VALUE_TYPE>& vprop_schema, std::vector<VALUE_TYPE>& eprop_schema,
+                              std::vector<void*>& vertex_props, std::vector<void*>& edge_props, bool use_hdfs) {
+    assert(!use_hdfs);
+    (void)vertex_props; (void)edge_props;
+    if (!vprop_schema.empty() || !eprop_schema.empty()) {
+        fprintf(stderr, "load_edge_list: property columns are not supported by libgm_cuda\n");
+        return false;
+    }
+    clear_graph();
+    gmc_graph* d = NULL;
+    if (gmc_edge_list_read(filename, &d, 0) != GMC_OK) {
+        fprintf(stderr, "%s\n", gmc_last_error());
+        return false;
+    }
+    int32_t n = 0, m = 0;
+    gmc_graph_num_nodes(d, &n); gmc_graph_num_edges(d, &m);
+    allocate_memory_for_frozen_graph(n, m);
+    dev_check(gmc_graph_download(d, GMC_ARR_BEGIN, begin, (size_t)n + 1, NULL), "load_edge_list(download)");
+    if (m) dev_check(gmc_graph_download(d, GMC_ARR_NODE_IDX, node_idx, (size_t)m, NULL), "load_edge_list(download)");
+    _dev = d;                     // the parsed graph IS the device mirror
+    _dev_has_reverse = false;
+    _frozen = _semi_sorted = true;
+    make_reverse_edges();         // as the reference reader ends (:168-169); fills r_begin / r_node_idx / e_rev2idx
+    return true;
+}
+
 bool gm_graph::store_binary(char* filename) {
     if (!_frozen) freeze();
     if (gmc_file_write(filename, _numNodes, _numEdges, begin, node_idx) != GMC_OK) {

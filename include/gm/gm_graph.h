@@ -86,6 +86,10 @@ class gm_graph {
     void prepare_external_creation(node_t n, edge_t m, bool clean_key_id_mappings);
     bool store_binary(char* filename);
     bool load_binary(char* filename);
+    // ---- EDGE_LIST text (reference gm_edge_list_graph_reader.cc:5-18,68-171); property columns are not read:
+    // the schemas must be empty, as they are for gm_format_converter's plain edge lists ----
+    bool load_edge_list(char* filename, std::vector<VALUE_TYPE>& vprop_schema, std::vector<VALUE_TYPE>& eprop_schema,
+                        std::vector<void*>& vertex_props, std::vector<void*>& edge_props, bool use_hdfs = false);
 
     inline edge_t get_edge_idx(edge_id e) { return e_id2idx == NULL ? e : e_id2idx[e]; }
     inline node_t get_node_idx(node_id n) { return n; }

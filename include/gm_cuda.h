@@ -90,6 +90,12 @@ int gmc_file_read(const char* path, int32_t* begin, int32_t* node_idx);
 int gmc_file_write(const char* path, int32_t num_nodes, int32_t num_edges, const int32_t* begin,
                    const int32_t* node_idx);
 
+/* --- EDGE_LIST text ingest (reference gm_edge_list_graph_reader.cc:68-171, gm_graph::load_edge_list without
+ * property columns; the format gm_format_converter reads, README.md:24-35): lines "src dst" or "src *", '#'
+ * comments, ids densified in ascending order.  Parsed by all host threads, CSR + semi-sort (+ reverse CSR)
+ * built on the device; the graph stays resident (download with gmc_graph_download). */
+int gmc_edge_list_read(const char* path, gmc_graph** out, int make_reverse);
+
 /* --- PageRank: the generated pagerank() (reference apps/src/pagerank.gm:1-20; emitted loop shape
  * reconstructed in SURVEY.md 3.1).  rank = 1/N; do { sweep; cnt++ } while (diff > e && cnt < max_iter).
  * Needs the reverse CSR.  fp64 throughout; per-edge term rank[w]/(double)outdeg(w) as in the reference. */

@@ -388,3 +388,63 @@ int orc_bfs_levels(int32_t N, const int32_t* begin, const int32_t* node_idx,
     free(queue);
     return curr_level + 1;
 }
+
+
+/* EDGE_LIST reader: gm_edge_list_graph_reader.cc:68-171 (builtGraph).  Pass 1 marks the ids that occur
+ * (:91-110), the lookup table numbers them densely in ascending raw-id order (:112-117), pass 2 adds the edges
+ * (:137-160); freeze() lays the rows out by source with the edges in file order, do_semi_sort() (:168) sorts
+ * every row by destination.  The reference's fixed LOOKUP_SIZE (80 000 000, :66) is the id bound kept here. */
+#define ORC_LOOKUP_SIZE 80000000
+static int orc_el_line(char* line, long* a, long* b, int* star) {
+    if (strlen(line) == 0 || line[0] == '#') return 0;                  /* :99, :140 */
+    char* save = NULL;
+    char* p = strtok_r(line, " \t", &save);                             /* :101 */
+    if (!p) return 0;
+    *a = atol(p);
+    p = strtok_r(NULL, " \t\n\r", &save);                               /* :105 */
+    if (!p) return -1;
+    *star = (*p == '*');
+    if (!*star) *b = atol(p);
+    return 1;
+}
+int orc_edge_list_read(const char* path, int32_t* N, int32_t* M, int32_t* begin, int32_t* node_idx) {
+    FILE* f = fopen(path, "r");
+    if (!f) return -1;
+    int32_t* lookup = (int32_t*)malloc(sizeof(int32_t) * (size_t)ORC_LOOKUP_SIZE);
+    for (long i = 0; i < ORC_LOOKUP_SIZE; i++) lookup[i] = -1;
+    char line[1024];
+    long a = 0, b = 0; int star = 0, rc = 0;
+    int64_t m = 0;
+    while (fgets(line, sizeof line, f)) {
+        line[strcspn(line, "\n")] = 0;
+        int k = orc_el_line(line, &a, &b, &star);
+        if (k < 0 || (k > 0 && (a < 0 || a >= ORC_LOOKUP_SIZE || (!star && (b < 0 || b >= ORC_LOOKUP_SIZE))))) { rc = -2; break; }
+        if (k == 0) continue;
+        lookup[a] = 1;
+        if (!star) { lookup[b] = 1; m++; }
+    }
+    int32_t n = 0;
+    for (long i = 0; i < ORC_LOOKUP_SIZE; i++) lookup[i] = lookup[i] > 0 ? n++ : -1;
+    *N = n; *M = (int32_t)m;
+    if (rc == 0 && begin) {
+        int32_t* deg = (int32_t*)calloc((size_t)n + 1, sizeof(int32_t));
+        rewind(f);
+        while (fgets(line, sizeof line, f)) {
+            line[strcspn(line, "\n")] = 0;
+            if (orc_el_line(line, &a, &b, &star) > 0 && !star) deg[lookup[a]]++;
+        }
+        begin[0] = 0;
+        for (int32_t i = 0; i < n; i++) begin[i + 1] = begin[i] + deg[i];
+        memset(deg, 0, sizeof(int32_t) * ((size_t)n + 1));
+        rewind(f);
+        while (fgets(line, sizeof line, f)) {
+            line[strcspn(line, "\n")] = 0;
+            if (orc_el_line(line, &a, &b, &star) > 0 && !star) { int32_t s = lookup[a]; node_idx[begin[s] + deg[s]++] = lookup[b]; }
+        }
+        free(deg);
+        orc_semi_sort(n, begin, node_idx, NULL);
+    }
+    free(lookup);
+    fclose(f);
+    return rc;
+}

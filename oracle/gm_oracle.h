@@ -43,6 +43,13 @@ int orc_store_binary(const char* path, int32_t N, int32_t M, const int32_t* begi
 int orc_load_binary_header(const char* path, int32_t* N, int32_t* M);
 int orc_load_binary(const char* path, int32_t* begin, int32_t* node_idx);
 
+/* --- EDGE_LIST ingest: gm_edge_list_graph_reader::builtGraph (gm_edge_list_graph_reader.cc:68-171).
+ * Lines "src dst" or "src *" (a vertex without an edge on this line), blank lines and lines starting with
+ * '#' skipped, tokens separated by blanks/tabs; every id seen (source, destination, "*"-line vertex) gets a
+ * vertex, numbered densely in ascending order of the raw id (:104-124); edges keep file order per source
+ * (freeze), then do_semi_sort.  Two calls: counts first (begin == NULL), then the fill. */
+int orc_edge_list_read(const char* path, int32_t* N, int32_t* M, int32_t* begin, int32_t* node_idx);
+
 /* --- generated pagerank(): apps/src/pagerank.gm:1-20 (emitters: see ref_glue/pagerank.cc) ---
  * returns the number of iterations executed; *diff_out = last diff. */
 int orc_pagerank(int32_t N, const int32_t* begin, const int32_t* r_begin, const int32_t* r_node_idx,

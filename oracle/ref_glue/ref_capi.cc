@@ -71,6 +71,14 @@ void* ref_graph_load(const char* path) {
     if (!g->load_binary((char*)path)) { delete g; return NULL; }
     return g;
 }
+// the reference's EDGE_LIST reader (gm_edge_list_graph_reader.cc:68-171), no property columns
+void* ref_graph_load_edge_list(const char* path) {
+    gm_graph* g = new gm_graph();
+    std::vector<VALUE_TYPE> vs, es;
+    std::vector<void*> vp, ep;
+    if (!g->load_edge_list((char*)path, vs, es, vp, ep, false)) { delete g; return NULL; }
+    return g;
+}
 int ref_graph_store(void* h, const char* path) { return ((gm_graph*)h)->store_binary((char*)path) ? 1 : 0; }
 void ref_graph_free(void* h) { delete (gm_graph*)h; }
 int32_t ref_graph_num_nodes(void* h) { return ((gm_graph*)h)->num_nodes(); }

@@ -69,6 +69,17 @@ class Oracle:
             return None
         return begin, idx[:M.value]
 
+    def edge_list_read(self, path):
+        """EDGE_LIST ingest (ids densified, rows semi-sorted): returns begin, node_idx or None"""
+        self.L.orc_edge_list_read.argtypes = [C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_void_p, C.c_void_p]
+        N = C.c_int32(); M = C.c_int32()
+        if self.L.orc_edge_list_read(path.encode(), C.byref(N), C.byref(M), None, None) != 0:
+            return None
+        begin = np.zeros(N.value + 1, np.int32); idx = np.zeros(max(M.value, 1), np.int32)
+        if self.L.orc_edge_list_read(path.encode(), C.byref(N), C.byref(M), begin.ctypes.data, idx.ctypes.data) != 0:
+            return None
+        return begin, idx[:M.value]
+
     def pagerank(self, begin, r_begin, r_node_idx, e=1e-30, d=0.85, max_iter=20):
         N = len(begin) - 1
         rank = np.zeros(max(N, 1), np.float64); diff = C.c_double()
@@ -105,6 +116,8 @@ class Ref:
         L.ref_graph_from_csr.restype = vp; L.ref_graph_from_csr.argtypes = [C.c_int32, C.c_int32, _i32p, _i32p]
         L.ref_graph_load.restype = vp; L.ref_graph_load.argtypes = [C.c_char_p]
         L.ref_graph_store.argtypes = [vp, C.c_char_p]
+        if hasattr(L, "ref_graph_load_edge_list"):
+            L.ref_graph_load_edge_list.restype = vp; L.ref_graph_load_edge_list.argtypes = [C.c_char_p]
         L.ref_graph_free.argtypes = [vp]
         for f in ("num_nodes", "num_edges"):
             getattr(L, "ref_graph_" + f).argtypes = [vp]; getattr(L, "ref_graph_" + f).restype = C.c_int32
@@ -128,6 +141,9 @@ class Ref:
 
     def load(self, path):
         return self.L.ref_graph_load(path.encode())
+
+    def load_edge_list(self, path):
+        return self.L.ref_graph_load_edge_list(path.encode())
 
     def store(self, g, path):
         return self.L.ref_graph_store(g, path.encode()) == 1
