@@ -52,7 +52,14 @@ constexpr int SLICE_OVH = 68;             // keeps a default task at <= 31 slice
 constexpr int LT_BIG = 8192, ST_COST_BIG = 4096, SLICE_OVH_BIG = 136;
 constexpr int64_t BIG_TASK_ENTRIES = 24000000;   // per-shard entries from which the large tasks are used
 constexpr int ZT = 2048;                  // ids per zero-in-degree task
-constexpr int SHARD_ROW_COST = 6;         // entries one row epilogue weighs when the shards of a multi-rank run are cut
+// entries one row epilogue weighs when the shards of a multi-rank run are cut.  The epilogue stores the new contribution
+// into every peer (world-1 NVLink stores per row), so the weight grows with the world size.  Measured on the TW-shaped
+// graph (max / min sweep time over ranks): 2 ranks: weight 0 -> 3.05 / 2.81 ms, 2 -> 3.12 / 2.82, 6 -> 3.23 / 2.65;
+// 8 ranks: 6 -> 1.12 / 0.87, 14 -> 1.00 / 0.85, 26 -> 1.05 / 0.80 (profiles/r1p_shard_row_cost.txt)
+static inline int shard_row_cost(int world) {
+    if (const char* c = getenv("GMC_PR_ROWCOST")) return atoi(c);      // experiments
+    return world > 2 ? 2 * (world - 2) : 0;
+}
 #ifndef GMC_HOT_CAP
 #define GMC_HOT_CAP 20480
 #endif
@@ -754,16 +761,23 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
         rc = GMC_ERR_ARG; set_error("pagerank plan: entry array exceeds int32 offsets"); goto fail;
     }
     if (world > 1) {
-        // shard cuts balance entries + SHARD_ROW_COST per row: a row's epilogue (28 B of HBM traffic, a division and, with
+        // shard cuts balance entries + shard_row_cost(world) per row: a row's epilogue (28 B of HBM traffic, a division and, with
         // mapped peers, world-1 remote stores) weighs a few entries; with entry counts alone the ranks owning the short
         // tail rows were 2x slower than the others on the TW-shaped graph (profiles/r1e_bench_8gpu_tw_unbalanced.json)
-        std::vector<int32_t> cl(h_lbeg), cs((size_t)p->g_nz_slices + 1);
-        for (int32_t j = 0; j <= p->g_n_long; j++) cl[j] += j * SHARD_ROW_COST;
-        cs[0] = 0;
+        const int row_cost = shard_row_cost(world);
+        std::vector<int64_t> wl((size_t)p->g_n_long + 1), ws((size_t)p->g_nz_slices + 1);
+        for (int32_t j = 0; j <= p->g_n_long; j++) wl[j] = (int64_t)h_lbeg[j] + (int64_t)j * row_cost;
+        ws[0] = 0;
         for (int32_t q = 0; q < p->g_nz_slices; q++) {          // a slice is processed in 8-column chunks
             const int32_t len = (h_sbeg[q + 1] - h_sbeg[q]) >> 5;
-            cs[q + 1] = cs[q] + 32 * (((len + 7) & ~7) + SHARD_ROW_COST);
+            ws[q + 1] = ws[q] + 32LL * (((len + 7) & ~7) + row_cost);
         }
+        // gmc_shard_cuts takes int32 prefixes: scale the weights down when their total does not fit (only ratios matter)
+        int sh = 0;
+        while (((wl[p->g_n_long] > ws[p->g_nz_slices] ? wl[p->g_n_long] : ws[p->g_nz_slices]) >> sh) > 0x7fffff00LL) sh++;
+        std::vector<int32_t> cl(wl.size()), cs(ws.size());
+        for (size_t j = 0; j < wl.size(); j++) cl[j] = (int32_t)(wl[j] >> sh);
+        for (size_t q = 0; q < ws.size(); q++) cs[q] = (int32_t)(ws[q] >> sh);
         PLAN_TRY(gmc_shard_cuts(cl.data(), p->g_n_long, world, 1, cutsL.data()));
         PLAN_TRY(gmc_shard_cuts(cs.data(), p->g_nz_slices, world, 1, cutsS.data()));
     } else {
