@@ -1,0 +1,177 @@
+// Triangle counting: the generated triangle_counting() (reference apps/src/triangle_counting.gm:1-13) on the device.
+//
+//   Foreach(v: G.Nodes) Foreach(u: v.Nbrs)(u > v) Foreach(w: v.Nbrs)(w > u) If (w.HasEdgeTo(u)) T += 1;
+//
+// The C++ back end emits it as three nested loops over the out-edge slots of v (schedule(dynamic,128) over v, a private
+// counter per thread combined with ATOMIC_ADD) with G.has_edge_to(w, u) -- a binary search of u in the semi-sorted row
+// of w (gm_graph.cc:60-66,589-633) -- innermost: d(v)^2/2 searches per vertex.  Counted here is the same multiset
+// (edge SLOTS i, j of row v with idx[i] > v, idx[j] > idx[i] and an edge idx[j] -> idx[i]; parallel edges of row v count
+// per slot, the membership test is boolean), but per slot i the inner loop becomes one sorted-list intersection:
+//     A = slots of row v with value > u            (a suffix of the semi-sorted row, multiplicity kept)
+//     B = sources w > u of the in-edges of u       (a suffix of the reverse row of u, ascending by source)
+//     count_i = #{ a in A : value(a) in B }
+// evaluated by binary-searching the shorter side in the longer one.  Work item = one edge slot; a warp takes 32
+// consecutive slots, lanes finish the small intersections alone and the warp goes through the large ones together.
+// The count is an integer sum, so the result is exact and independent of the order of evaluation.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "gmc_common.cuh"
+
+using namespace gmc;
+
+namespace {
+
+constexpr int TC_THREADS = 256;
+constexpr int TC_TILE = 2048;          // edge slots per row hint
+constexpr int TC_SOLO = 12;            // intersections whose shorter side is at most this long are done by one lane
+constexpr unsigned FULLM = 0xffffffffu;
+
+__global__ void tc_row_hints(const int32_t* __restrict__ begin, int32_t n, int32_t m, int32_t n_hints, int32_t* __restrict__ hint) {
+    int32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n_hints) return;
+    const int64_t e64 = (int64_t)b * TC_TILE;
+    if (e64 >= m) { hint[b] = n; return; }
+    const int32_t e = (int32_t)e64;
+    int32_t lo = 0, hi = n;            // begin[lo] <= e < begin[hi]
+    while (hi - lo > 1) {
+        const int32_t mid = lo + ((hi - lo) >> 1);
+        if (begin[mid] <= e) lo = mid; else hi = mid;
+    }
+    hint[b] = lo;
+}
+
+// first position in [lo, hi) whose value is > x (values ascending)
+__device__ __forceinline__ int32_t upper_bound(const int32_t* __restrict__ a, int32_t lo, int32_t hi, int32_t x) {
+    while (lo < hi) {
+        const int32_t mid = lo + ((hi - lo) >> 1);
+        if (__ldg(a + mid) <= x) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+__device__ __forceinline__ int32_t lower_bound(const int32_t* __restrict__ a, int32_t lo, int32_t hi, int32_t x) {
+    while (lo < hi) {
+        const int32_t mid = lo + ((hi - lo) >> 1);
+        if (__ldg(a + mid) < x) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+__device__ __forceinline__ bool contains(const int32_t* __restrict__ a, int32_t lo, int32_t hi, int32_t x) {
+    const int32_t p = lower_bound(a, lo, hi, x);
+    return p < hi && __ldg(a + p) == x;
+}
+
+// contribution of positions [k0, k1) (stride `step`) of the shorter side of one intersection
+__device__ __forceinline__ unsigned long long intersect_part(const int32_t* __restrict__ idx, const int32_t* __restrict__ ridx,
+                                                             int32_t a_lo, int32_t a_hi, int32_t b_lo, int32_t b_hi, int32_t k0, int32_t step) {
+    unsigned long long c = 0;
+    if (a_hi - a_lo <= b_hi - b_lo) {                 // walk the slots of row v, look each value up among the in-neighbours of u
+        for (int32_t a = a_lo + k0; a < a_hi; a += step) c += contains(ridx, b_lo, b_hi, __ldg(idx + a)) ? 1u : 0u;
+    } else {                                          // walk the distinct in-neighbours of u, count their slots in row v
+        for (int32_t b = b_lo + k0; b < b_hi; b += step) {
+            const int32_t w = __ldg(ridx + b);
+            if (b > b_lo && __ldg(ridx + b - 1) == w) continue;          // parallel edges w -> u: the test is boolean
+            const int32_t p = lower_bound(idx, a_lo, a_hi, w);
+            if (p < a_hi && __ldg(idx + p) == w) c += (unsigned long long)(upper_bound(idx, p, a_hi, w) - p);
+        }
+    }
+    return c;
+}
+
+__global__ void __launch_bounds__(TC_THREADS) tc_count(const int32_t* __restrict__ begin, const int32_t* __restrict__ idx,
+                                                        const int32_t* __restrict__ rbegin, const int32_t* __restrict__ ridx,
+                                                        const int32_t* __restrict__ hint, int32_t n, int32_t e_lo, int32_t e_hi,
+                                                        unsigned int* __restrict__ next_chunk, unsigned long long* __restrict__ total) {
+    const int lane = threadIdx.x & 31;
+    unsigned long long cnt = 0;
+    const int64_t n_chunks = ((int64_t)e_hi - e_lo + 31) >> 5;
+    for (;;) {
+        unsigned int ch = 0;
+        if (lane == 0) ch = atomicAdd(next_chunk, 1u);
+        ch = __shfl_sync(FULLM, ch, 0);
+        if ((int64_t)ch >= n_chunks) break;
+        const int64_t e64 = (int64_t)e_lo + ((int64_t)ch << 5) + lane;
+        int32_t a_lo = 0, a_hi = 0, b_lo = 0, b_hi = 0;
+        if (e64 < e_hi) {
+            const int32_t e = (int32_t)e64;
+            int32_t lo = __ldg(hint + e / TC_TILE), hi = min(__ldg(hint + e / TC_TILE + 1) + 1, n);    // begin[lo] <= e < begin[hi]
+            while (hi - lo > 1) {
+                const int32_t mid = lo + ((hi - lo) >> 1);
+                if (__ldg(begin + mid) <= e) lo = mid; else hi = mid;
+            }
+            const int32_t v = lo, u = __ldg(idx + e);
+            if (u > v) {
+                a_hi = __ldg(begin + v + 1);
+                a_lo = upper_bound(idx, e + 1, a_hi, u);                        // slots of row v with value > u
+                b_hi = __ldg(rbegin + u + 1);
+                if (a_lo < a_hi) b_lo = upper_bound(ridx, __ldg(rbegin + u), b_hi, u); else b_hi = 0;   // in-neighbours of u that are > u
+            }
+        }
+        const int32_t work = min(a_hi - a_lo, b_hi - b_lo);
+        if (work > 0 && work <= TC_SOLO) cnt += intersect_part(idx, ridx, a_lo, a_hi, b_lo, b_hi, 0, 1);
+        unsigned big = __ballot_sync(FULLM, work > TC_SOLO);
+        while (big) {
+            const int src = __ffs(big) - 1;
+            big &= big - 1;
+            const int32_t A0 = __shfl_sync(FULLM, a_lo, src), A1 = __shfl_sync(FULLM, a_hi, src);
+            const int32_t B0 = __shfl_sync(FULLM, b_lo, src), B1 = __shfl_sync(FULLM, b_hi, src);
+            cnt += intersect_part(idx, ridx, A0, A1, B0, B1, lane, 32);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(FULLM, cnt, o);
+    if (lane == 0 && cnt) atomicAdd(total, cnt);
+}
+
+}  // namespace
+
+extern "C" {
+
+// edge slots [e_lo, e_hi) of the forward CSR: the count is a plain sum over slots, so a multi-GPU job gives every rank a
+// slice of the slots and adds the partial counts (no exchange step on the path)
+int gmc_triangle_counting_range(gmc_graph* g, int64_t e_lo, int64_t e_hi, int64_t* count, float* kernel_ms, void* stream) {
+    GMC_REQUIRE(g && count, GMC_ERR_ARG, "gmc_triangle_counting: NULL");
+    GMC_REQUIRE(g->has_forward, GMC_ERR_STATE, "triangle_counting: the forward CSR (node_idx) was not uploaded for this graph");
+    // rows must be ascending (semi-sorted), the assumption has_edge_to's binary search makes in the reference too (gm_graph.cc:592)
+    GMC_REQUIRE(g->has_reverse, GMC_ERR_STATE, "triangle_counting needs the reverse CSR: call gmc_graph_make_reverse first");
+    GMC_REQUIRE(e_lo >= 0 && e_lo <= e_hi && e_hi <= g->M, GMC_ERR_ARG, "gmc_triangle_counting: slot range [%lld, %lld) outside [0, %d]",
+                (long long)e_lo, (long long)e_hi, g->M);
+    *count = 0;
+    if (kernel_ms) *kernel_ms = 0.f;
+    if (e_hi == e_lo) return GMC_OK;
+    cudaStream_t st = as_stream(stream);
+    const int32_t n = g->N, m = g->M;
+    const int32_t n_hints = div_up(m, TC_TILE) + 1;
+    int32_t* hints = nullptr;
+    unsigned long long* total = nullptr;      // [0] = count, [1] (as u32) = chunk counter
+    GMC_TRY(gmc_malloc((void**)&hints, 4 * (size_t)n_hints));
+    int rc = gmc_malloc((void**)&total, 16);
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    if (rc == GMC_OK && (cudaEventCreate(&ev0) != cudaSuccess || cudaEventCreate(&ev1) != cudaSuccess)) { set_error("triangle_counting: event"); rc = GMC_ERR_CUDA; }
+    unsigned long long h = 0;
+    if (rc == GMC_OK) {
+        cudaMemsetAsync(total, 0, 16, st);
+        cudaEventRecord(ev0, st);
+        tc_row_hints<<<div_up(n_hints, 256), 256, 0, st>>>(g->begin, n, m, n_hints, hints);
+        tc_count<<<sm_count() * 8, TC_THREADS, 0, st>>>(g->begin, g->node_idx, g->r_begin, g->r_node_idx, hints, n, (int32_t)e_lo, (int32_t)e_hi,
+                                                         reinterpret_cast<unsigned int*>(total + 1), total);
+        cudaEventRecord(ev1, st);
+        if (cudaMemcpyAsync(&h, total, 8, cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
+            set_error("triangle_counting: %s", cudaGetErrorString(cudaGetLastError())); rc = GMC_ERR_CUDA;
+        }
+    }
+    if (rc == GMC_OK) {
+        *count = (int64_t)h;
+        if (kernel_ms) cudaEventElapsedTime(kernel_ms, ev0, ev1);
+    }
+    if (ev0) cudaEventDestroy(ev0);
+    if (ev1) cudaEventDestroy(ev1);
+    cudaFree(hints); cudaFree(total);
+    return rc;
+}
+
+int gmc_triangle_counting(gmc_graph* g, int64_t* count, float* kernel_ms) {
+    GMC_REQUIRE(g, GMC_ERR_ARG, "gmc_triangle_counting: NULL");
+    return gmc_triangle_counting_range(g, 0, g->M, count, kernel_ms, nullptr);
+}
+
+}  // extern "C"

@@ -69,6 +69,8 @@ SIGNATURES = {
     "gmc_pagerank_host_csr": (C.c_int, [_i32, _i32, _vp, _vp, _vp, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo)]),
     "gmc_pagerank_time_sweeps": (C.c_int, [_vp, C.c_double, _i32, _i32, _vp, C.POINTER(_i32), _vp]),
     "gmc_pagerank_plan_info": (C.c_int, [_vp, C.POINTER(PlanInfo)]),
+    "gmc_triangle_counting": (C.c_int, [_vp, C.POINTER(C.c_int64), C.POINTER(C.c_float)]),
+    "gmc_triangle_counting_range": (C.c_int, [_vp, C.c_int64, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_float), _vp]),
     "gmc_hop_dist": (C.c_int, [_vp, _i32, _vp, C.POINTER(BfsInfo)]),
     "gmc_hop_dist_dev": (C.c_int, [_vp, _i32, _vp, C.POINTER(BfsInfo), _vp]),
     "gmc_bfs_levels": (C.c_int, [_vp, _i32, C.c_int, _vp, _vp, _vp, _i32, C.POINTER(BfsInfo)]),
@@ -315,6 +317,15 @@ class Graph:
         info = PagerankInfo()
         self.lib.check(self.lib.L.gmc_pagerank(self.h, e, d, max_iter, _ptr(rank), C.byref(info)))
         return rank[:self.num_nodes], info
+
+    def triangle_counting(self, e_lo=None, e_hi=None):
+        """returns (count, device ms); with a slot range: the partial count of edge slots [e_lo, e_hi)"""
+        cnt = C.c_int64(); ms = C.c_float()
+        if e_lo is None:
+            self.lib.check(self.lib.L.gmc_triangle_counting(self.h, C.byref(cnt), C.byref(ms)))
+        else:
+            self.lib.check(self.lib.L.gmc_triangle_counting_range(self.h, e_lo, e_hi, C.byref(cnt), C.byref(ms), None))
+        return cnt.value, ms.value
 
     def pagerank_into(self, rank_host, e=1e-30, d=0.85, max_iter=20):
         """result into a caller-owned (ideally pinned) host array of N doubles"""

@@ -168,6 +168,14 @@ int gmc_bfs_levels_masked(gmc_graph* g, int32_t root, int use_reverse_edge, cons
  * order_host[N]; level_begin_host[levels+1]. Valid after gmc_bfs_levels on the same graph. */
 int gmc_bfs_level_order(gmc_graph* g, int32_t* order_host, int32_t* level_begin_host, int32_t cap_levels);
 
+/* --- triangle_counting: the generated triangle_counting() (reference
+ * apps/src/triangle_counting.gm:1-13): T = #{(v, slot i, slot j) : u = nbr_i(v) > v, w = nbr_j(v) > u, edge w -> u},
+ * the inner has_edge_to loop (gm_graph.cc:60-66,589-633) evaluated as one sorted-list intersection per edge slot.
+ * Needs ascending rows and the reverse CSR.  Exact (integer) result.  kernel_ms (nullable) = device time.
+ * _range counts the edge slots [e_lo, e_hi) only: ranks of a multi-GPU job take slices and add their counts. */
+int gmc_triangle_counting(gmc_graph* g, int64_t* count, float* kernel_ms);
+int gmc_triangle_counting_range(gmc_graph* g, int64_t e_lo, int64_t e_hi, int64_t* count, float* kernel_ms, void* stream);
+
 /* --- multi-GPU: one process per GPU, destination-vertex ranges per rank.  Shoal's
  * replicate / partition placement (reference src/backend_cpp/gm_cpp_gen.cc:181-227: shl__malloc_array with
  * is_ro / is_indexed) becomes: CSR and bitmaps replicated, the streamed entry array / owned rows partitioned.

@@ -448,3 +448,41 @@ int orc_edge_list_read(const char* path, int32_t* N, int32_t* M, int32_t* begin,
     fclose(f);
     return rc;
 }
+
+
+/* get_edge_idx_for_src_dest, gm_graph.cc:589-633 (rows semi-sorted): the reference's own search, ends compared first,
+ * then bisection over the inclusive range; != NIL_EDGE is has_edge_to (:60-66). */
+static int orc_has_edge_to(const int32_t* begin, const int32_t* node_idx, int32_t src, int32_t to) {
+    int32_t b = begin[src], e = begin[src + 1] - 1;
+    if (b > e) return 0;
+    if (to == node_idx[b] || to == node_idx[e]) return 1;
+    while (b < e) {
+        if (to < node_idx[b] || to > node_idx[e]) return 0;
+        int32_t mid = (b + e) / 2, mv = node_idx[mid];
+        if (to == mv) return 1;
+        if (to < mv) { if (e == mid) return 0; e = mid; }
+        else { if (b == mid) return 0; b = mid; }
+    }
+    return 0;
+}
+/* triangle_counting.gm:5-11 as the C++ back end emits it: parallel over v (dynamic,128), private counter + atomic add */
+int64_t orc_triangle_counting(int32_t N, const int32_t* begin, const int32_t* node_idx) {
+    int64_t T = 0;
+#pragma omp parallel
+    {
+        int64_t T_prv = 0;
+#pragma omp for nowait schedule(dynamic, 128)
+        for (int32_t v = 0; v < N; v++)
+            for (int32_t ui = begin[v]; ui < begin[v + 1]; ui++) {
+                int32_t u = node_idx[ui];
+                if (!(u > v)) continue;
+                for (int32_t wi = begin[v]; wi < begin[v + 1]; wi++) {
+                    int32_t w = node_idx[wi];
+                    if (w > u && orc_has_edge_to(begin, node_idx, w, u)) T_prv += 1;
+                }
+            }
+#pragma omp atomic
+        T += T_prv;
+    }
+    return T;
+}

@@ -50,6 +50,10 @@ int orc_load_binary(const char* path, int32_t* begin, int32_t* node_idx);
  * (freeze), then do_semi_sort.  Two calls: counts first (begin == NULL), then the fill. */
 int orc_edge_list_read(const char* path, int32_t* N, int32_t* M, int32_t* begin, int32_t* node_idx);
 
+/* --- generated triangle_counting(): apps/src/triangle_counting.gm:1-13; three nested loops over the out-edge slots of v
+ * (filters u > v, w > u) with G.has_edge_to(w, u) innermost = the binary search of gm_graph.cc:589-633. */
+int64_t orc_triangle_counting(int32_t N, const int32_t* begin, const int32_t* node_idx);
+
 /* --- generated pagerank(): apps/src/pagerank.gm:1-20 (emitters: see ref_glue/pagerank.cc) ---
  * returns the number of iterations executed; *diff_out = last diff. */
 int orc_pagerank(int32_t N, const int32_t* begin, const int32_t* r_begin, const int32_t* r_node_idx,

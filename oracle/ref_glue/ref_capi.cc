@@ -79,6 +79,27 @@ void* ref_graph_load_edge_list(const char* path) {
     if (!g->load_edge_list((char*)path, vs, es, vp, ep, false)) { delete g; return NULL; }
     return g;
 }
+// triangle_counting.gm:5-11 over the reference's REAL gm_graph::has_edge_to (gm_graph.cc:60-66,589-633)
+long long ref_triangle_counting(void* h) {
+    gm_graph& G = *(gm_graph*)h;
+    int64_t T = 0;
+#pragma omp parallel
+    {
+        int64_t T_prv = 0;
+#pragma omp for nowait schedule(dynamic, 128)
+        for (node_t v = 0; v < G.num_nodes(); v++)
+            for (edge_t u_idx = G.begin[v]; u_idx < G.begin[v + 1]; u_idx++) {
+                node_t u = G.node_idx[u_idx];
+                if (u > v)
+                    for (edge_t w_idx = G.begin[v]; w_idx < G.begin[v + 1]; w_idx++) {
+                        node_t w = G.node_idx[w_idx];
+                        if (w > u && G.has_edge_to(w, u)) T_prv = T_prv + 1;
+                    }
+            }
+        ATOMIC_ADD<int64_t>(&T, T_prv);
+    }
+    return T;
+}
 int ref_graph_store(void* h, const char* path) { return ((gm_graph*)h)->store_binary((char*)path) ? 1 : 0; }
 void ref_graph_free(void* h) { delete (gm_graph*)h; }
 int32_t ref_graph_num_nodes(void* h) { return ((gm_graph*)h)->num_nodes(); }

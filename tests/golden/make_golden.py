@@ -62,5 +62,24 @@ def main():
     print("golden fixtures written to", HERE)
 
 
+def triangle_counts():
+    """triangle_counts.json: the generated triangle_counting() loop nest over the reference's own gm_graph::has_edge_to
+    (oracle/ref_glue/ref_capi.cc: ref_triangle_counting) on the two full fixtures written by main()"""
+    import json
+    ref = Ref()
+    tc = {}
+    for name in ("rmat4096", "uniform2000"):
+        z = np.load(os.path.join(HERE, name + ".npz"))
+        g = ref.from_csr(z["begin"], z["node_idx"])
+        tc[name] = ref.triangle_counting(g)
+        ref.free(g)
+    json.dump(tc, open(os.path.join(HERE, "triangle_counts.json"), "w"))
+    print("triangle counts", tc)
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "triangles":
+        triangle_counts()
+    else:
+        main()
+        triangle_counts()

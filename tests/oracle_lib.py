@@ -69,6 +69,11 @@ class Oracle:
             return None
         return begin, idx[:M.value]
 
+    def triangle_counting(self, begin, node_idx):
+        self.L.orc_triangle_counting.restype = C.c_int64
+        self.L.orc_triangle_counting.argtypes = [C.c_int32, _i32p, _i32p]
+        return int(self.L.orc_triangle_counting(len(begin) - 1, begin, np.ascontiguousarray(node_idx)))
+
     def edge_list_read(self, path):
         """EDGE_LIST ingest (ids densified, rows semi-sorted): returns begin, node_idx or None"""
         self.L.orc_edge_list_read.argtypes = [C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_void_p, C.c_void_p]
@@ -141,6 +146,10 @@ class Ref:
 
     def load(self, path):
         return self.L.ref_graph_load(path.encode())
+
+    def triangle_counting(self, g):
+        self.L.ref_triangle_counting.restype = C.c_longlong; self.L.ref_triangle_counting.argtypes = [C.c_void_p]
+        return int(self.L.ref_triangle_counting(g))
 
     def load_edge_list(self, path):
         return self.L.ref_graph_load_edge_list(path.encode())

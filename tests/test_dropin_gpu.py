@@ -47,3 +47,15 @@ def test_reference_drivers_run_unchanged(gm, oracle, tmp_path):
     dist, _ = oracle.hop_dist(b, i, 0)
     got = [int(x) for x in re.findall(r"dist\[\d\] = (-?\d+)", out)]
     assert got == [int(v) for v in dist[:10]]
+
+
+def test_triangle_counting_driver_unchanged(gm, oracle, tmp_path):
+    """apps/output_cpp/src/triangle_counting_main.cc, unchanged: prints `number of triangles: <T>`"""
+    f = str(tmp_path / "r.bin")
+    b, i = oracle.rmat(20000, 400000, 1997, 0.57, 0.19, 0.19, True)
+    assert oracle.store_binary(f, b, i)
+    i = np.ascontiguousarray(i).copy()
+    oracle.semi_sort(b, i)
+    out = run("triangle_counting", f, 4, "/dev/null")
+    got = re.findall(r"number of triangles: (-?\d+)", out)
+    assert got and int(got[0]) == oracle.triangle_counting(b, i)
