@@ -53,7 +53,8 @@ struct gmc_bfs_ws {
     int2* chunks = nullptr;           // [M/TD_CHUNK + N/256 + 2] (queue block, chunk-in-block)
     size_t chunk_cap = 0;
     int32_t* counters = nullptr;      // [8]: 0 = level count (global), 1 = owned queue count, 2 = nchunks
-    int32_t* h_counters = nullptr;    // pinned [8]
+    int32_t* h_counters = nullptr;    // pinned + mapped [8]: 0 = level count, 1 = owned count, 2 = sequence number of the level that wrote them
+    int32_t seq = 0;
     void* level = nullptr;            // [N] int32 (also used as int16)
     unsigned long long* edge_sum = nullptr;
     // host-side record of the last traversal
@@ -85,7 +86,7 @@ __global__ void bfs_init(L* __restrict__ level, int32_t n, L invalid, int32_t ro
         const uint32_t b = (i == (root >> 5)) ? (1u << (root & 31)) : 0u;
         visited[i] = b; frontier[i] = b; cand[i] = 0u;
     }
-    if (i == 0) { if (root_owned) queue[0] = root; counters[0] = 0; counters[1] = 0; counters[2] = 0; }
+    if (i == 0) { if (root_owned) queue[0] = root; counters[0] = 0; counters[1] = 0; counters[2] = 0; counters[3] = 0; }
 }
 
 // ---- top-down, step 1: degrees of the queued vertices -> CTA-relative offsets + chunk descriptors ----------
@@ -209,7 +210,8 @@ template <typename L>
 __global__ void __launch_bounds__(BFS_THREADS)
 bfs_finish(int32_t words, int32_t wp, int world, int use_all, uint32_t* __restrict__ cand, const uint32_t* __restrict__ allcand,
            uint32_t* __restrict__ visited, uint32_t* __restrict__ frontier, L next_level, L* __restrict__ level,
-           int32_t own_lo, int32_t own_hi, int32_t* __restrict__ next_queue, int32_t* __restrict__ counters) {
+           int32_t own_lo, int32_t own_hi, int32_t* __restrict__ next_queue, int32_t* __restrict__ counters,
+           volatile int32_t* __restrict__ host_out, int32_t seq) {
     const int lane = threadIdx.x & 31;
     const int32_t w = blockIdx.x * BFS_THREADS + threadIdx.x;
     uint32_t nw = 0;
@@ -239,13 +241,37 @@ bfs_finish(int32_t words, int32_t wp, int world, int use_all, uint32_t* __restri
         if (own_tot) base = atomicAdd(&counters[1], own_tot);
     }
     base = __shfl_sync(FULLMASK, base, 0) + pre - own;
-    uint32_t bits = nw;
-    while (bits) {
-        const int b = __ffs(bits) - 1;
-        bits &= bits - 1;
-        const int32_t v = (w << 5) + b;
-        level[v] = next_level;
-        if (owned) next_queue[base++] = v;
+    // the warp goes through its non-empty words together: lane b takes bit b of the word, so the level[] and queue
+    // stores of one word are one coalesced 128-byte store each (a lane per word wrote 32 scattered elements in turn)
+    unsigned has = __ballot_sync(FULLMASK, nw != 0u);
+    while (has) {
+        const int src = __ffs(has) - 1;
+        has &= has - 1;
+        const uint32_t bits = __shfl_sync(FULLMASK, nw, src);
+        const int32_t qb = __shfl_sync(FULLMASK, base, src);
+        const int own_s = __shfl_sync(FULLMASK, (int)owned, src);
+        const int32_t v = ((w - lane + src) << 5) + lane;
+        if ((bits >> lane) & 1u) {
+            level[v] = next_level;
+            if (own_s) next_queue[qb + __popc(bits & ((1u << lane) - 1u))] = v;
+        }
+    }
+    // the last block to finish publishes the two level counts straight into the host's (mapped, pinned) memory and
+    // resets the device counters: the host polls the sequence number instead of a memcpy + memset + stream sync per level
+    __shared__ int s_last;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_last = (atomicAdd(&counters[3], 1) == (int)gridDim.x - 1);
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x == 0) {
+        __threadfence();
+        host_out[0] = atomicAdd(&counters[0], 0);
+        host_out[1] = atomicAdd(&counters[1], 0);
+        counters[0] = 0; counters[1] = 0; counters[2] = 0; counters[3] = 0;
+        __threadfence_system();
+        host_out[2] = seq;
     }
 }
 
@@ -287,6 +313,7 @@ int ensure_ws(gmc_graph* g, int world) {
     if (rc == GMC_OK && cudaMallocHost((void**)&w->h_counters, sizeof(int32_t) * 8) != cudaSuccess) {
         set_error("bfs: cudaMallocHost failed"); rc = GMC_ERR_NOMEM;
     }
+    if (rc == GMC_OK) memset(w->h_counters, 0, sizeof(int32_t) * 8);
     if (rc != GMC_OK) { gmc_bfs_ws_free(g); return rc; }
     return GMC_OK;
 }
@@ -352,12 +379,21 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             }
         }
         bfs_finish<L><<<fin_grid, BFS_THREADS, 0, st>>>(w->words, w->wp, world, use_all, w->cand, w->allcand, w->visited, w->frontier_bm,
-                                                        nl, level, own_lo, own_hi, w->queue[qi ^ 1], w->counters);
+                                                        nl, level, own_lo, own_hi, w->queue[qi ^ 1], w->counters, w->h_counters, ++w->seq);
         launches++;
         GMC_CUDA(cudaGetLastError());
-        GMC_CUDA(cudaMemcpyAsync(w->h_counters, w->counters, 2 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-        GMC_CUDA(cudaMemsetAsync(w->counters, 0, 4 * sizeof(int32_t), st));
-        GMC_CUDA(cudaStreamSynchronize(st));
+        {   // wait for the level's counts: poll the sequence number bfs_finish's last block writes into pinned memory
+            volatile int32_t* h = w->h_counters;
+            unsigned spins = 0;
+            while (h[2] != w->seq) {
+                if ((++spins & 0x3fffu) == 0) {            // a failed launch or a fault would never publish: ask the stream now and then
+                    const cudaError_t q = cudaStreamQuery(st);
+                    if (q != cudaErrorNotReady && q != cudaSuccess) { set_error("bfs: %s", cudaGetErrorString(q)); return GMC_ERR_CUDA; }
+                    if (q == cudaSuccess && h[2] != w->seq) { set_error("bfs: level counts were not published"); return GMC_ERR_CUDA; }
+                }
+            }
+            __sync_synchronize();
+        }
         const int32_t next_count = w->h_counters[0];
         own_count = w->h_counters[1];
         qi ^= 1;
