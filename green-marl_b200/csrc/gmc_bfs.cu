@@ -35,6 +35,7 @@ using namespace gmc;
 enum { ST_SMALL = 0, ST_QUE = 1, ST_Q2R = 2, ST_RD = 3, ST_R2Q = 4, ST_RRD = 5, ST_RR2Q = 6 };
 constexpr int BFS_THREADS = 256;
 constexpr int TD_CHUNK = 256;        // edge slots per warp chunk (8 per lane)
+constexpr int TD_BATCHED_MAX_FRONTIER = 8192;   // owned frontier vertices up to which td_expand batches a lane's 8 loads
 constexpr unsigned FULLMASK = 0xffffffffu;
 
 struct gmc_bfs_ws {
@@ -128,6 +129,7 @@ __device__ __forceinline__ int window_search(int32_t e, int32_t pos) {
 }
 
 // ---- top-down, step 2: one warp per chunk of TD_CHUNK edge slots ---------------------------------------------
+template <bool BATCHED>
 __global__ void __launch_bounds__(BFS_THREADS)
 td_expand(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_idx, const int32_t* __restrict__ queue, int32_t qcount,
           const int32_t* __restrict__ blk_off, const int32_t* __restrict__ blk_total, const int2* __restrict__ chunks,
@@ -162,24 +164,58 @@ td_expand(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_id
             } else { w_start = INT_MAX; w_end = INT_MAX; w_bv = 0; }
         };
         load_window(r0);
-        for (int32_t p0 = s0; p0 < s1; p0 += 32) {
-            const int32_t pos = p0 + lane;
+        if (!BATCHED) {
+            // large frontiers: one 32-slot step at a time; 64 resident warps per SM hide the two dependent loads of a step
+            for (int32_t p0 = s0; p0 < s1; p0 += 32) {
+                const int32_t pos = p0 + lane;
+                bool todo = pos < s1;
+                while (__any_sync(FULLMASK, todo)) {
+                    const int kk = window_search(w_end, pos);
+                    const int32_t st = __shfl_sync(FULLMASK, w_start, kk & 31);
+                    const int32_t bv = __shfl_sync(FULLMASK, w_bv, kk & 31);
+                    if (todo && kk < 32) {
+                        const int32_t eidx = bv + (pos - st);
+                        const int32_t u = ld_stream(node_idx + eidx);
+                        const uint32_t bit = 1u << (u & 31);
+                        const int32_t uw = u >> 5;
+                        // navigator (check_navigator, gm_bfs_template.h:488-492,596-598): filtered edges are not followed
+                        if (!(visited[uw] & bit) && (!edge_mask || edge_mask[eidx]) && !(cand[uw] & bit)) atomicOr(&cand[uw], bit);
+                        todo = false;
+                    }
+                    if (__any_sync(FULLMASK, todo)) { r0 += 32; load_window(r0); }     // slots beyond the 32-row window
+                }
+            }
+        } else {
+        // small frontiers (few chunks, the level is a latency chain): three phases per chunk so that the 8 loads of a lane
+        // are in flight together: (1) edge index of each of the lane's 8 slots (row lookup inside the 32-row window,
+        // shuffles only), (2) the 8 neighbour ids, (3) the 8 bitmap probes
+        int32_t eidx[TD_CHUNK / 32];
+#pragma unroll
+        for (int j = 0; j < TD_CHUNK / 32; j++) {
+            const int32_t pos = s0 + j * 32 + lane;
             bool todo = pos < s1;
+            eidx[j] = -1;
             while (__any_sync(FULLMASK, todo)) {
                 const int kk = window_search(w_end, pos);
                 const int32_t st = __shfl_sync(FULLMASK, w_start, kk & 31);
                 const int32_t bv = __shfl_sync(FULLMASK, w_bv, kk & 31);
-                if (todo && kk < 32) {
-                    const int32_t eidx = bv + (pos - st);
-                    const int32_t u = ld_stream(node_idx + eidx);
-                    const uint32_t bit = 1u << (u & 31);
-                    const int32_t uw = u >> 5;
-                    // navigator (check_navigator, gm_bfs_template.h:488-492,596-598): filtered edges are not followed
-                    if (!(visited[uw] & bit) && (!edge_mask || edge_mask[eidx]) && !(cand[uw] & bit)) atomicOr(&cand[uw], bit);
-                    todo = false;
-                }
+                if (todo && kk < 32) { eidx[j] = bv + (pos - st); todo = false; }
                 if (__any_sync(FULLMASK, todo)) { r0 += 32; load_window(r0); }     // slots beyond the 32-row window
             }
+        }
+        int32_t u[TD_CHUNK / 32];
+#pragma unroll
+        for (int j = 0; j < TD_CHUNK / 32; j++) u[j] = eidx[j] >= 0 ? ld_stream(node_idx + eidx[j]) : -1;
+        uint32_t vis[TD_CHUNK / 32];
+#pragma unroll
+        for (int j = 0; j < TD_CHUNK / 32; j++) vis[j] = u[j] >= 0 ? visited[u[j] >> 5] : 0xffffffffu;
+#pragma unroll
+        for (int j = 0; j < TD_CHUNK / 32; j++) {
+            if (u[j] < 0) continue;
+            const uint32_t bit = 1u << (u[j] & 31);
+            const int32_t uw = u[j] >> 5;
+            if (!(vis[j] & bit) && (!edge_mask || edge_mask[eidx[j]]) && !(cand[uw] & bit)) atomicOr(&cand[uw], bit);
+        }
         }
     }
 }
@@ -369,8 +405,12 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             if (own_count > 0) {
                 td_prepare<<<div_up(own_count, BFS_THREADS), BFS_THREADS, 0, st>>>(fwd_begin, w->queue[qi], own_count, w->blk_off,
                                                                                   w->blk_total, w->chunks, w->counters + 2);
-                td_expand<<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[qi], own_count, w->blk_off, w->blk_total,
-                                                            w->chunks, w->counters + 2, w->visited, w->cand, edge_mask);
+                if (own_count <= TD_BATCHED_MAX_FRONTIER)
+                    td_expand<true><<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[qi], own_count, w->blk_off, w->blk_total,
+                                                                      w->chunks, w->counters + 2, w->visited, w->cand, edge_mask);
+                else
+                    td_expand<false><<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[qi], own_count, w->blk_off, w->blk_total,
+                                                                       w->chunks, w->counters + 2, w->visited, w->cand, edge_mask);
                 launches += 2;
             }
             if (world > 1) {
