@@ -61,10 +61,13 @@ static inline int shard_row_cost(int world) {
     return world > 2 ? 2 * (world - 2) : 0;
 }
 #ifndef GMC_HOT_CAP
-#define GMC_HOT_CAP 20480
+#define GMC_HOT_CAP 16640
 #endif
-constexpr int HOT_CAP = GMC_HOT_CAP;      // doubles of shared memory for the hot block (160 KB: the rest of the SM's
-                                          // 256 KB stays L1, whose capacity bounds the gathers in flight -- tools/ubench)
+// doubles of shared memory for the hot block: 130 KB, the 132 KB carve-out step, so that 124 KB of the SM's 256 KB stay L1.
+// The number of missing gathers an SM keeps in flight grows with the L1 left (tools/ubench), and the L1 itself serves
+// the next-hottest sources; measured per sweep on the LJ-shaped graph (profiles/r1s_hot_cap.txt): 3900 doubles
+// 0.2002 ms, 8000 0.1966, 12600 0.1914, 16640 0.1907, 20480 0.2000, 24576 0.2412
+constexpr int HOT_CAP = GMC_HOT_CAP;
 constexpr unsigned FULL = 0xffffffffu;
 
 struct gmc_pr_ctrl {   // device-side loop control: lets the host enqueue sweeps without a sync per iteration
@@ -429,7 +432,12 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
         mbar_expect_tx(&bar, bytes);
         const char* src = reinterpret_cast<const char*>(A.contrib_in);
         char* dst = reinterpret_cast<char*>(hot);
-        for (unsigned off = 0; off < bytes; off += 32768u) tma_bulk_g2s(dst + off, src + off, min(32768u, bytes - off), &bar);
+        // every CTA copies the same bytes: start at a different 16 KB piece per CTA so they do not queue on the same L2 lines
+        const unsigned pieces = (bytes + 16383u) / 16384u;
+        for (unsigned k = 0; k < pieces; k++) {
+            const unsigned off = ((k + blockIdx.x) % pieces) * 16384u;
+            tma_bulk_g2s(dst + off, src + off, min(16384u, bytes - off), &bar);
+        }
     }
     mbar_wait(&bar, 0);
 
