@@ -24,7 +24,11 @@ namespace {
 constexpr int TC_THREADS = 256;
 constexpr int TC_TILE = 2048;          // edge slots per row hint
 constexpr int TC_SOLO = 12;            // intersections whose shorter side is at most this long are done by one lane
+constexpr int TC_HEAVY = 2048;         // intersections whose shorter side is longer than this are cut into segments ...
+constexpr int TC_SEG = 1024;           // ... of this many elements, handed to the second kernel (one warp per segment)
 constexpr unsigned FULLM = 0xffffffffu;
+
+struct TcSeg { int32_t a_lo, a_hi, b_lo, b_hi, k0, k1; };
 
 __global__ void tc_row_hints(const int32_t* __restrict__ begin, int32_t n, int32_t m, int32_t n_hints, int32_t* __restrict__ hint) {
     int32_t b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -62,12 +66,15 @@ __device__ __forceinline__ bool contains(const int32_t* __restrict__ a, int32_t 
 
 // contribution of positions [k0, k1) (stride `step`) of the shorter side of one intersection
 __device__ __forceinline__ unsigned long long intersect_part(const int32_t* __restrict__ idx, const int32_t* __restrict__ ridx,
-                                                             int32_t a_lo, int32_t a_hi, int32_t b_lo, int32_t b_hi, int32_t k0, int32_t step) {
+                                                             int32_t a_lo, int32_t a_hi, int32_t b_lo, int32_t b_hi, int32_t k0, int32_t step,
+                                                             int32_t k1 = INT32_MAX) {
     unsigned long long c = 0;
     if (a_hi - a_lo <= b_hi - b_lo) {                 // walk the slots of row v, look each value up among the in-neighbours of u
-        for (int32_t a = a_lo + k0; a < a_hi; a += step) c += contains(ridx, b_lo, b_hi, __ldg(idx + a)) ? 1u : 0u;
+        const int32_t a_end = (int32_t)min((int64_t)a_hi, (int64_t)a_lo + k1);
+        for (int32_t a = a_lo + k0; a < a_end; a += step) c += contains(ridx, b_lo, b_hi, __ldg(idx + a)) ? 1u : 0u;
     } else {                                          // walk the distinct in-neighbours of u, count their slots in row v
-        for (int32_t b = b_lo + k0; b < b_hi; b += step) {
+        const int32_t b_end = (int32_t)min((int64_t)b_hi, (int64_t)b_lo + k1);
+        for (int32_t b = b_lo + k0; b < b_end; b += step) {
             const int32_t w = __ldg(ridx + b);
             if (b > b_lo && __ldg(ridx + b - 1) == w) continue;          // parallel edges w -> u: the test is boolean
             const int32_t p = lower_bound(idx, a_lo, a_hi, w);
@@ -80,7 +87,8 @@ __device__ __forceinline__ unsigned long long intersect_part(const int32_t* __re
 __global__ void __launch_bounds__(TC_THREADS) tc_count(const int32_t* __restrict__ begin, const int32_t* __restrict__ idx,
                                                         const int32_t* __restrict__ rbegin, const int32_t* __restrict__ ridx,
                                                         const int32_t* __restrict__ hint, int32_t n, int32_t e_lo, int32_t e_hi,
-                                                        unsigned int* __restrict__ next_chunk, unsigned long long* __restrict__ total) {
+                                                        unsigned int* __restrict__ next_chunk, unsigned long long* __restrict__ total,
+                                                        TcSeg* __restrict__ segs, unsigned int* __restrict__ n_segs, unsigned int seg_cap) {
     const int lane = threadIdx.x & 31;
     unsigned long long cnt = 0;
     const int64_t n_chunks = ((int64_t)e_hi - e_lo + 31) >> 5;
@@ -106,7 +114,17 @@ __global__ void __launch_bounds__(TC_THREADS) tc_count(const int32_t* __restrict
                 if (a_lo < a_hi) b_lo = upper_bound(ridx, __ldg(rbegin + u), b_hi, u); else b_hi = 0;   // in-neighbours of u that are > u
             }
         }
-        const int32_t work = min(a_hi - a_lo, b_hi - b_lo);
+        int32_t work = min(a_hi - a_lo, b_hi - b_lo);
+        // heavy intersections (hub x hub: up to ~1e5 elements on the shorter side, tens of ms for one warp) are cut into
+        // fixed segments of the shorter side and left to tc_heavy; if the segment list is full they stay here
+        if (work > TC_HEAVY) {
+            const unsigned ns = (unsigned)((work + TC_SEG - 1) / TC_SEG);
+            const unsigned at = atomicAdd(n_segs, ns);
+            if (at + ns <= seg_cap) {
+                for (unsigned k = 0; k < ns; k++) segs[at + k] = TcSeg{a_lo, a_hi, b_lo, b_hi, (int32_t)(k * TC_SEG), (int32_t)min((int64_t)work, (int64_t)(k + 1) * TC_SEG)};
+                work = 0;
+            }      // list full: the counter stays beyond the capacity, so every later request fails too; unwritten slots are zero (no work)
+        }
         if (work > 0 && work <= TC_SOLO) cnt += intersect_part(idx, ridx, a_lo, a_hi, b_lo, b_hi, 0, 1);
         unsigned big = __ballot_sync(FULLM, work > TC_SOLO);
         while (big) {
@@ -116,6 +134,26 @@ __global__ void __launch_bounds__(TC_THREADS) tc_count(const int32_t* __restrict
             const int32_t B0 = __shfl_sync(FULLM, b_lo, src), B1 = __shfl_sync(FULLM, b_hi, src);
             cnt += intersect_part(idx, ridx, A0, A1, B0, B1, lane, 32);
         }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(FULLM, cnt, o);
+    if (lane == 0 && cnt) atomicAdd(total, cnt);
+}
+
+// second pass: one warp per segment of a heavy intersection
+__global__ void __launch_bounds__(TC_THREADS) tc_heavy(const int32_t* __restrict__ idx, const int32_t* __restrict__ ridx, const TcSeg* __restrict__ segs,
+                                                        const unsigned int* __restrict__ n_segs, unsigned int seg_cap,
+                                                        unsigned int* __restrict__ next_seg, unsigned long long* __restrict__ total) {
+    const int lane = threadIdx.x & 31;
+    const unsigned int n = min(*n_segs, seg_cap);
+    unsigned long long cnt = 0;
+    for (;;) {
+        unsigned int sgi = 0;
+        if (lane == 0) sgi = atomicAdd(next_seg, 1u);
+        sgi = __shfl_sync(FULLM, sgi, 0);
+        if (sgi >= n) break;
+        const TcSeg sg = segs[sgi];
+        cnt += intersect_part(idx, ridx, sg.a_lo, sg.a_hi, sg.b_lo, sg.b_hi, sg.k0 + lane, 32, sg.k1);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(FULLM, cnt, o);
@@ -142,18 +180,25 @@ int gmc_triangle_counting_range(gmc_graph* g, int64_t e_lo, int64_t e_hi, int64_
     const int32_t n = g->N, m = g->M;
     const int32_t n_hints = div_up(m, TC_TILE) + 1;
     int32_t* hints = nullptr;
-    unsigned long long* total = nullptr;      // [0] = count, [1] (as u32) = chunk counter
+    unsigned long long* total = nullptr;      // [0] = count, [1] (as 2 x u32) = chunk counter, segment count, [2] = segment cursor
+    TcSeg* segs = nullptr;
+    const unsigned seg_cap = 1u << 22;        // 4 M segments of 1024 elements (96 MB); beyond that heavy items are done in place
     GMC_TRY(gmc_malloc((void**)&hints, 4 * (size_t)n_hints));
-    int rc = gmc_malloc((void**)&total, 16);
+    int rc = gmc_malloc((void**)&total, 32);
+    if (rc == GMC_OK) rc = gmc_malloc((void**)&segs, sizeof(TcSeg) * (size_t)seg_cap);
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     if (rc == GMC_OK && (cudaEventCreate(&ev0) != cudaSuccess || cudaEventCreate(&ev1) != cudaSuccess)) { set_error("triangle_counting: event"); rc = GMC_ERR_CUDA; }
     unsigned long long h = 0;
     if (rc == GMC_OK) {
-        cudaMemsetAsync(total, 0, 16, st);
+        cudaMemsetAsync(total, 0, 32, st);
+        cudaMemsetAsync(segs, 0, sizeof(TcSeg) * (size_t)seg_cap, st);
         cudaEventRecord(ev0, st);
         tc_row_hints<<<div_up(n_hints, 256), 256, 0, st>>>(g->begin, n, m, n_hints, hints);
         tc_count<<<sm_count() * 8, TC_THREADS, 0, st>>>(g->begin, g->node_idx, g->r_begin, g->r_node_idx, hints, n, (int32_t)e_lo, (int32_t)e_hi,
-                                                         reinterpret_cast<unsigned int*>(total + 1), total);
+                                                         reinterpret_cast<unsigned int*>(total + 1), total, segs,
+                                                         reinterpret_cast<unsigned int*>(total + 1) + 1, seg_cap);
+        tc_heavy<<<sm_count() * 8, TC_THREADS, 0, st>>>(g->node_idx, g->r_node_idx, segs, reinterpret_cast<unsigned int*>(total + 1) + 1, seg_cap,
+                                                         reinterpret_cast<unsigned int*>(total + 2), total);
         cudaEventRecord(ev1, st);
         if (cudaMemcpyAsync(&h, total, 8, cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
             set_error("triangle_counting: %s", cudaGetErrorString(cudaGetLastError())); rc = GMC_ERR_CUDA;
@@ -165,7 +210,7 @@ int gmc_triangle_counting_range(gmc_graph* g, int64_t e_lo, int64_t e_hi, int64_
     }
     if (ev0) cudaEventDestroy(ev0);
     if (ev1) cudaEventDestroy(ev1);
-    cudaFree(hints); cudaFree(total);
+    cudaFree(hints); cudaFree(total); cudaFree(segs);
     return rc;
 }
 
