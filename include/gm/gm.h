@@ -1,6 +1,6 @@
 // Root header for applications (counterpart of the reference's gm.h:14-38), restricted to the modules
-// the PageRank / BFS hot path touches.  Collections, maps, DFS and the auto-main support are out of
-// scope of this library.
+// the PageRank / BFS hot path and its direct callers touch (gm_seq for bc's Node_Sequence).  Sets, maps,
+// DFS and the auto-main support are out of scope of this library.
 #ifndef GM_H_
 #define GM_H_
 #include <math.h>
@@ -20,4 +20,5 @@
 #include "gm_bitmap.h"
 #include "gm_mem_helper.h"
 #include "gm_bfs_template.h"
+#include "gm_seq.h"
 #endif

@@ -486,3 +486,44 @@ int64_t orc_triangle_counting(int32_t N, const int32_t* begin, const int32_t* no
     }
     return T;
 }
+
+
+/* comp_BC, apps/src/bc.gm:4-29.  Levels from the BFS template restatement above; forward pass level by level
+ * (visit_fw), reverse pass from the deepest level back to the root (do_bfs_reverse, gm_bfs_template.h:273-312). */
+void orc_comp_bc(int32_t N, const int32_t* begin, const int32_t* node_idx, const int32_t* r_begin,
+                 const int32_t* r_node_idx, const int32_t* seeds, int32_t n_seeds, float* bc) {
+    int16_t* lev = (int16_t*)malloc(sizeof(int16_t) * (size_t)(N > 0 ? N : 1));
+    float* sigma = (float*)malloc(sizeof(float) * (size_t)(N > 0 ? N : 1));
+    float* delta = (float*)malloc(sizeof(float) * (size_t)(N > 0 ? N : 1));
+    for (int32_t t = 0; t < N; t++) bc[t] = 0.0f;                                   /* bc.gm:6 */
+    for (int32_t k = 0; k < n_seeds; k++) {
+        const int32_t s = seeds[k];
+        for (int32_t t = 0; t < N; t++) sigma[t] = 0.0f;                            /* bc.gm:13 */
+        sigma[s] = 1.0f;                                                            /* bc.gm:14 */
+        const int nl = orc_bfs_levels(N, begin, node_idx, r_begin, r_node_idx, 1, s, lev, NULL, NULL, 0);
+        for (int l = 0; l < nl; l++)                                                /* InBFS, bc.gm:17-20 */
+            for (int32_t v = 0; v < N; v++) {
+                if (lev[v] != l) continue;
+                float S = 0.0f;
+                for (int32_t e = r_begin[v]; e < r_begin[v + 1]; e++) {
+                    const int32_t w = r_node_idx[e];
+                    if (lev[w] != l - 1) continue;
+                    S = S + sigma[w];
+                }
+                sigma[v] = S;
+            }
+        for (int l = nl - 1; l >= 0; l--)                                           /* InReverse, bc.gm:21-27 */
+            for (int32_t v = 0; v < N; v++) {
+                if (lev[v] != l) continue;
+                float S = 0.0f;
+                for (int32_t e = begin[v]; e < begin[v + 1]; e++) {
+                    const int32_t w = node_idx[e];
+                    if (lev[w] != l + 1) continue;                                  /* is_down_edge */
+                    S = S + sigma[v] / sigma[w] * (1 + delta[w]);
+                }
+                delta[v] = S;
+                bc[v] = bc[v] + delta[v];
+            }
+    }
+    free(lev); free(sigma); free(delta);
+}

@@ -54,6 +54,13 @@ int orc_edge_list_read(const char* path, int32_t* N, int32_t* M, int32_t* begin,
  * (filters u > v, w > u) with G.has_edge_to(w, u) innermost = the binary search of gm_graph.cc:589-633. */
 int64_t orc_triangle_counting(int32_t N, const int32_t* begin, const int32_t* node_idx);
 
+/* --- generated comp_BC(): apps/src/bc.gm:4-29 over gm_bfs_template<short,...,save_child> (visit_fw: sigma over the
+ * UpNbrs, gm_cpp_gen_foreach.cc:163-175; visit_rv: delta over the down edges, gm_bfs_template.h:273-319,496-524).
+ * float arithmetic, sums in edge order.  The shipped bc.gm overwrites the root's sigma with 0 (no v != s filter), so
+ * NaNs are the expected output wherever a vertex has a BFS child; bc is compared NaN-aware. */
+void orc_comp_bc(int32_t N, const int32_t* begin, const int32_t* node_idx, const int32_t* r_begin,
+                 const int32_t* r_node_idx, const int32_t* seeds, int32_t n_seeds, float* bc);
+
 /* --- generated pagerank(): apps/src/pagerank.gm:1-20 (emitters: see ref_glue/pagerank.cc) ---
  * returns the number of iterations executed; *diff_out = last diff. */
 int orc_pagerank(int32_t N, const int32_t* begin, const int32_t* r_begin, const int32_t* r_node_idx,

@@ -79,6 +79,51 @@ void* ref_graph_load_edge_list(const char* path) {
     if (!g->load_edge_list((char*)path, vs, es, vp, ep, false)) { delete g; return NULL; }
     return g;
 }
+// comp_BC (apps/src/bc.gm:4-29) as the C++ back end emits it, over the reference's REAL gm_bfs_template (save_child)
+class ref_bc_bfs : public gm_bfs_template<short, true, false, false, true> {
+  public:
+    ref_bc_bfs(gm_graph& _G, float* bc, float* sg, float* dl) : gm_bfs_template<short, true, false, false, true>(_G), G(_G), G_BC(bc), G_sigma(sg), G_delta(dl) {}
+  private:
+    gm_graph& G; float* G_BC; float* G_sigma; float* G_delta;
+  protected:
+    virtual void visit_fw(node_t v) {
+        float S = (float)0;
+        for (edge_t w_idx = G.r_begin[v]; w_idx < G.r_begin[v + 1]; w_idx++) {
+            node_t w = G.r_node_idx[w_idx];
+            if (get_level(w) != (get_curr_level() - 1)) continue;
+            S = S + G_sigma[w];
+        }
+        G_sigma[v] = S;
+    }
+    virtual void visit_rv(node_t v) {
+        float S = (float)0;
+        for (edge_t w_idx = G.begin[v]; w_idx < G.begin[v + 1]; w_idx++) {
+            if (!is_down_edge(w_idx)) continue;
+            node_t w = G.node_idx[w_idx];
+            S = S + G_sigma[v] / G_sigma[w] * (1 + G_delta[w]);
+        }
+        G_delta[v] = S;
+        G_BC[v] = G_BC[v] + G_delta[v];
+    }
+    virtual bool check_navigator(node_t, edge_t) { return true; }
+};
+void ref_comp_bc(void* h, const int32_t* seeds, int32_t n_seeds, float* bc) {
+    gm_graph& G = *(gm_graph*)h;
+    const node_t N = G.num_nodes();
+    std::vector<float> sigma(N > 0 ? N : 1), delta(N > 0 ? N : 1);
+    for (node_t t = 0; t < N; t++) bc[t] = 0;
+    for (int32_t k = 0; k < n_seeds; k++) {
+        node_t s = seeds[k];
+        for (node_t t = 0; t < N; t++) sigma[t] = 0;
+        sigma[s] = 1;
+        // deliberately leaked: the reference's destructor does `delete[] down_edge_set` on a `new std::set`
+        // (gm_bfs_template.h:31,40), undefined behaviour that crashes under glibc when save_child is on
+        ref_bc_bfs* B = new ref_bc_bfs(G, bc, &sigma[0], &delta[0]);
+        B->prepare(s, gm_rt_get_num_threads());
+        B->do_bfs_forward();
+        B->do_bfs_reverse();
+    }
+}
 // triangle_counting.gm:5-11 over the reference's REAL gm_graph::has_edge_to (gm_graph.cc:60-66,589-633)
 long long ref_triangle_counting(void* h) {
     gm_graph& G = *(gm_graph*)h;

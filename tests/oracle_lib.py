@@ -74,6 +74,15 @@ class Oracle:
         self.L.orc_triangle_counting.argtypes = [C.c_int32, _i32p, _i32p]
         return int(self.L.orc_triangle_counting(len(begin) - 1, begin, np.ascontiguousarray(node_idx)))
 
+    def comp_bc(self, begin, node_idx, r_begin, r_node_idx, seeds):
+        N = len(begin) - 1
+        self.L.orc_comp_bc.restype = None
+        self.L.orc_comp_bc.argtypes = [C.c_int32, _i32p, _i32p, _i32p, _i32p, _i32p, C.c_int32, C.c_void_p]
+        bc = np.zeros(max(N, 1), np.float32)
+        sd = np.ascontiguousarray(seeds, np.int32)
+        self.L.orc_comp_bc(N, begin, np.ascontiguousarray(node_idx), r_begin, np.ascontiguousarray(r_node_idx), sd, len(sd), bc.ctypes.data)
+        return bc[:N]
+
     def edge_list_read(self, path):
         """EDGE_LIST ingest (ids densified, rows semi-sorted): returns begin, node_idx or None"""
         self.L.orc_edge_list_read.argtypes = [C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_void_p, C.c_void_p]
@@ -150,6 +159,15 @@ class Ref:
     def triangle_counting(self, g):
         self.L.ref_triangle_counting.restype = C.c_longlong; self.L.ref_triangle_counting.argtypes = [C.c_void_p]
         return int(self.L.ref_triangle_counting(g))
+
+    def comp_bc(self, g, seeds):
+        N = self.L.ref_graph_num_nodes(g)
+        self.L.ref_comp_bc.restype = None
+        self.L.ref_comp_bc.argtypes = [C.c_void_p, _i32p, C.c_int32, C.c_void_p]
+        bc = np.zeros(max(N, 1), np.float32)
+        sd = np.ascontiguousarray(seeds, np.int32)
+        self.L.ref_comp_bc(g, sd, len(sd), bc.ctypes.data)
+        return bc[:N]
 
     def load_edge_list(self, path):
         return self.L.ref_graph_load_edge_list(path.encode())

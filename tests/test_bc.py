@@ -1,0 +1,86 @@
+"""comp_BC (apps/src/bc.gm) through the facade's gm_bfs_template: device traversal, the generated
+visit_fw / visit_rv callbacks replayed on the host.  The oracle (plain C) is checked against the same generated class over
+the reference's own gm_bfs_template (oracle/_ref).  bc.gm as shipped yields NaN wherever a vertex has a BFS child (the
+root's sigma is overwritten by an empty sum), so arrays are compared NaN-aware, bit for bit otherwise."""
+import os
+import re
+import subprocess
+import numpy as np
+import pytest
+
+import graphs
+from oracle_lib import have_ref
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "green-marl_b200", "bin")
+
+
+def same(a, b):
+    return a.shape == b.shape and np.array_equal(np.isnan(a), np.isnan(b)) and np.array_equal(a[~np.isnan(a)].view(np.uint32), b[~np.isnan(b)].view(np.uint32))
+
+
+@pytest.mark.skipif(not have_ref(), reason="oracle/_ref not built (no /root/reference on this box)")
+def test_oracle_matches_reference_bfs_template(oracle, ref):
+    # one thread: with several, the reference's down-edge marking races (a thread that finds u's bit already set reads
+    # visited_level[u] before the thread that set the bit has written it, gm_bfs_template.h:596-622, and skips the edge),
+    # so its output is not deterministic; the single-thread run is the semantics: every edge to level + 1 is a down edge
+    ref.set_threads(1)
+    for n, m, seed in [(300, 2000, 5), (5000, 60000, 3), (20000, 400000, 7)]:
+        g = ref.rmat(n, m, seed)
+        a = ref.arrays(g)
+        nz = np.nonzero(np.diff(a["begin"]))[0]
+        seeds = [int(nz[k]) for k in (0, 5, 9)] + [0]
+        want = ref.comp_bc(g, seeds)
+        got = oracle.comp_bc(a["begin"], a["node_idx"], a["r_begin"], a["r_node_idx"], seeds)
+        assert same(got, want)
+        assert np.isnan(want).any() and (want == 0).any()       # the shipped bc.gm's degenerate output, see module docstring
+        ref.free(g)
+    ref.set_threads(min(8, os.cpu_count() or 1))
+
+
+def test_oracle_tiny(oracle):
+    # path 0 -> 1 -> 2: from seed 0 the inner vertices (0, 1) have a child -> NaN, the leaf 2 stays 0
+    g = graphs.from_edges(oracle, 4, [(0, 1), (1, 2)])
+    bc = oracle.comp_bc(g["begin"], g["node_idx"], g["r_begin"], g["r_node_idx"], [0])
+    assert np.isnan(bc[0]) and np.isnan(bc[1]) and bc[2] == 0 and bc[3] == 0
+
+
+@pytest.mark.gpu
+def test_comp_bc_facade_parity(gm, oracle, tmp_path):
+    exe = os.path.join(BIN, "bc_check")
+    assert os.path.exists(exe), f"{exe} missing: run __graft_entry__.build() where /root/reference is present"
+    for k, (n, m) in enumerate([(3000, 40000), (200000, 3000000)]):
+        g = graphs.rmat(oracle, n, m, seed=11 + k)
+        f = str(tmp_path / f"g{k}.bin"); out = str(tmp_path / f"bc{k}.f32")
+        assert oracle.store_binary(f, g["begin"], g["node_idx"])
+        nz = np.nonzero(np.diff(g["begin"]))[0]
+        seeds = [int(nz[0]), int(nz[len(nz) // 2]), int(np.diff(g["begin"]).argmax()), 1]
+        r = subprocess.run([exe, f, out] + [str(s) for s in seeds], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        got = np.fromfile(out, np.float32)
+        want = oracle.comp_bc(g["begin"], g["node_idx"], g["r_begin"], g["r_node_idx"], seeds)
+        assert same(got, want)
+
+
+@pytest.mark.gpu
+def test_bc_driver_unchanged(gm, oracle, tmp_path):
+    """apps/output_cpp/src/bc_main.cc, unchanged: 5 seeds from gm_rand32 (the reference's xorshift, quirk included), prints BC[0..3]"""
+    g = graphs.rmat(oracle, 20000, 400000)
+    f = str(tmp_path / "r.bin")
+    assert oracle.store_binary(f, g["begin"], g["node_idx"])
+    r = subprocess.run([os.path.join(BIN, "bc"), f, "4", "/dev/null"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    # gm_rand32 (gm_rand.cc:10-23): x ^= x << 13; x = x >> 17 (assignment, as in the reference); x ^= x << 5
+    def i32(x):
+        x &= 0xffffffff
+        return x - (1 << 32) if x & 0x80000000 else x
+    x, seeds = i32(2463534242), []
+    while len(seeds) < 5:
+        x = i32(x ^ (x << 13)); x = x >> 17; x = i32(x ^ (x << 5))
+        if x < g["N"]:
+            seeds.append(x)
+    want = oracle.comp_bc(g["begin"], g["node_idx"], g["r_begin"], g["r_node_idx"], seeds)
+    got = re.findall(r"BC\[\d\] = (\S+)", r.stdout)
+    assert len(got) == 4
+    for k in range(4):
+        assert (np.isnan(want[k]) and "nan" in got[k].lower()) or float(got[k]) == float("%0.9f" % want[k])
