@@ -157,23 +157,30 @@ def run_multi(args, n, m, workload):
             rank_host = np.empty(n, np.float64); pin_ok = False
         h2d = sum(a.nbytes for a in pinned.values())
         e2e_steps = max(1, min(args.steps, 2))
-        times = []
+        times, parts = [], {}
         for k in range(1 + e2e_steps):
             dist.barrier(); lib.sync()
             t0 = time.perf_counter()
             dg = lib.graph_pull_only(pinned["begin"], pinned["r_begin"], pinned["r_node_idx"], comm=comm)
+            t1 = time.perf_counter()
             out = torch.empty(n, dtype=torch.float64, device="cuda")
             dg.pagerank_sharded_dev(comm, out.data_ptr(), 1e-30, 0.85, iters)
+            t2 = time.perf_counter()
             lib.d2h(rank_host, out.data_ptr())
+            t3 = time.perf_counter()
             comm.barrier()          # nobody unmaps / frees its state block while a peer may still store into it
             dg.close()
             lib.sync(); dist.barrier()
+            t4 = time.perf_counter()
             if k > 0:
-                times.append(max_over_ranks(dist, torch, (time.perf_counter() - t0) * 1e3))
+                times.append(max_over_ranks(dist, torch, (t4 - t0) * 1e3))
+                for name, dt in (("copy_in_and_allgather", t1 - t0), ("plan_peer_mapping_sweeps", t2 - t1), ("d2h_rank", t3 - t2), ("teardown", t4 - t3)):
+                    parts.setdefault(name, []).append(max_over_ranks(dist, torch, dt * 1e3))
         e2e_ms = float(np.mean(times))
         e2e = {"value": round(m * iters / e2e_ms / 1e6, 3), "unit": "GTEPS", "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(rank_host.nbytes * world), "ms_per_step": round(e2e_ms, 3), "steps": e2e_steps,
-               "pinned": pin_ok, "note": "each rank copies its 1/world slice of the CSR host->device, the slices are allgathered over NVLink, every rank plans its shard; all inside the timed region"}
+               "pinned": pin_ok,
+               "breakdown_ms_max_over_ranks": {k: round(float(np.mean(v)), 2) for k, v in parts.items()}, "note": "each rank copies its 1/world slice of the CSR host->device, the slices are allgathered over NVLink, every rank plans its shard; all inside the timed region"}
 
     if rank == 0:
         line = {
