@@ -211,8 +211,11 @@ int gmc_comm_create(gmc_comm** out, int world, int rank, const void* id128) {
     return GMC_OK;
 }
 
+extern "C" void gmc_pr_release_cached_state(void);     // gmc_pagerank.cu: retired peer-mapped state block
+
 int gmc_comm_destroy(gmc_comm* c) {
     if (!c) return GMC_OK;
+    if (c->world > 1) gmc_pr_release_cached_state();
     if (c->nccl) g_api.CommDestroy(c->nccl);
     delete c;
     return GMC_OK;
