@@ -343,14 +343,18 @@ def run_single(args, n, m):
     for _ in range(2):
         e2e_step_parts()
     lib.sync()
-    t0 = time.perf_counter()
     e2e_steps = max(1, min(args.steps, 5))
+    e2e_all = []
+    t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        e2e_step()
+        t_s = time.perf_counter()
+        e2e_step()                      # returns with rank[] in host memory: the call is synchronous
+        e2e_all.append((time.perf_counter() - t_s) * 1e3)
     lib.sync()
     e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
     e2e = {"value": round(m * iters / e2e_ms / 1e6, 3), "unit": "GTEPS", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
            "ms_per_step": round(e2e_ms, 3), "steps": e2e_steps,
+           "ms_each_step": [round(x, 3) for x in e2e_all],
            "call": "gmc_pagerank_host_csr (pinned host CSR in, host rank[] out; copy-in overlapped with the plan build)",
            "breakdown_ms": {"what": "the same work un-overlapped (upload, then gmc_pagerank)",
                             "h2d_begin_rbegin_rnodeidx": round(float(np.mean(parts["h2d_ms"])), 3),
