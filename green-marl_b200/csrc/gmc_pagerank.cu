@@ -35,6 +35,7 @@
 #include "gmc_common.cuh"
 #include "gmc_comm.h"
 #include <cub/device/device_radix_sort.cuh>
+#include <mutex>
 #include <vector>
 #include <stdlib.h>
 
@@ -1239,10 +1240,23 @@ int gmc_pagerank_host_csr(int32_t num_nodes, int32_t num_edges, const int32_t* b
     GMC_REQUIRE(num_nodes >= 0 && num_edges >= 0 && begin && r_begin && (r_node_idx || num_edges == 0) && (rank_host || num_nodes == 0),
                 GMC_ERR_ARG, "gmc_pagerank_host_csr: bad args");
     if (num_nodes == 0) { if (info) memset(info, 0, sizeof(*info)); return GMC_OK; }
+    // the copy stream and the events are made once per process (creating them per call costs driver round trips whose
+    // latency is not bounded); calls are serialised on them
+    static std::mutex mtx;
+    static cudaStream_t cs = nullptr;
+    static gmc_pending_upload pu;
+    std::lock_guard<std::mutex> lock(mtx);
+    if (!cs) {
+        // non-blocking: the allocator and the plan kernels use the legacy default stream, which must not wait for the copies
+        cudaStream_t s2 = nullptr;
+        bool ok = cudaStreamCreateWithFlags(&s2, cudaStreamNonBlocking) == cudaSuccess &&
+                  cudaEventCreateWithFlags(&pu.small, cudaEventDisableTiming) == cudaSuccess;
+        for (int c = 0; c < gmc_pending_upload::MAX_CHUNKS && ok; c++) ok = cudaEventCreateWithFlags(&pu.chunk[c], cudaEventDisableTiming) == cudaSuccess;
+        if (!ok) { set_error("gmc_pagerank_host_csr: stream/event: %s", cudaGetErrorString(cudaGetLastError())); return GMC_ERR_CUDA; }
+        cs = s2;
+    }
     gmc_graph* g = nullptr;
     GMC_TRY(gmc_graph_create(&g, num_nodes, num_edges));
-    gmc_pending_upload pu;
-    cudaStream_t cs = nullptr;
     double* tmp = nullptr;
     int rc = GMC_OK;
     const size_t nb = sizeof(int32_t) * ((size_t)num_nodes + 1);
@@ -1252,9 +1266,6 @@ int gmc_pagerank_host_csr(int32_t num_nodes, int32_t num_edges, const int32_t* b
         if ((rc = gmc_malloc((void**)&g->r_begin, nb)) != GMC_OK) break;
         if ((rc = gmc_malloc((void**)&g->r_node_idx, sizeof(int32_t) * (size_t)(num_edges ? num_edges : 1))) != GMC_OK) break;
         if ((rc = gmc_malloc((void**)&tmp, sizeof(double) * (size_t)num_nodes)) != GMC_OK) break;
-        // non-blocking: the allocator and the plan kernels use the legacy default stream, which must not wait for the copies
-        if (cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking) != cudaSuccess) { fail("stream"); break; }
-        if (cudaEventCreateWithFlags(&pu.small, cudaEventDisableTiming) != cudaSuccess) { fail("event"); break; }
         if (cudaMemcpyAsync(g->begin, begin, nb, cudaMemcpyHostToDevice, cs) != cudaSuccess ||
             cudaMemcpyAsync(g->r_begin, r_begin, nb, cudaMemcpyHostToDevice, cs) != cudaSuccess ||
             cudaEventRecord(pu.small, cs) != cudaSuccess) { fail("copy-in"); break; }
@@ -1263,8 +1274,7 @@ int gmc_pagerank_host_csr(int32_t num_nodes, int32_t num_edges, const int32_t* b
         for (int c = 0; c < pu.nchunks && ok; c++) {
             const int32_t lo = (int32_t)((int64_t)num_edges * c / pu.nchunks), hi = (int32_t)((int64_t)num_edges * (c + 1) / pu.nchunks);
             pu.end[c] = hi;
-            ok = cudaEventCreateWithFlags(&pu.chunk[c], cudaEventDisableTiming) == cudaSuccess;
-            if (ok && hi > lo) ok = cudaMemcpyAsync(g->r_node_idx + lo, r_node_idx + lo, sizeof(int32_t) * (size_t)(hi - lo), cudaMemcpyHostToDevice, cs) == cudaSuccess;
+            if (hi > lo) ok = cudaMemcpyAsync(g->r_node_idx + lo, r_node_idx + lo, sizeof(int32_t) * (size_t)(hi - lo), cudaMemcpyHostToDevice, cs) == cudaSuccess;
             if (ok) ok = cudaEventRecord(pu.chunk[c], cs) == cudaSuccess;
         }
         if (!ok) { fail("copy-in"); break; }
@@ -1274,9 +1284,7 @@ int gmc_pagerank_host_csr(int32_t num_nodes, int32_t num_edges, const int32_t* b
         g->pending = nullptr;
         if (rc == GMC_OK) rc = gmc_d2h(rank_host, tmp, sizeof(double) * (size_t)num_nodes, nullptr);
     } while (0);
-    if (cs) { cudaStreamSynchronize(cs); cudaStreamDestroy(cs); }
-    if (pu.small) cudaEventDestroy(pu.small);
-    for (int c = 0; c < gmc_pending_upload::MAX_CHUNKS; c++) if (pu.chunk[c]) cudaEventDestroy(pu.chunk[c]);
+    cudaStreamSynchronize(cs);          // the host arrays are not read after the call returns, whatever happened
     cudaFree(tmp);
     g->pending = nullptr;
     gmc_graph_destroy(g);
