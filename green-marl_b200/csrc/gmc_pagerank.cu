@@ -31,7 +31,8 @@
 //               of in-degree <= S_MAX is bit-identical to the CPU result given bit-identical inputs.
 // HBM traffic per sweep: 4 B/edge (index stream) + 40 B/vertex (row pointer amortised, old rank, new rank,
 // new contrib, out-degree, first touch of contrib); gathers are served by shared memory / L2.
-#define GMC_EXPERIMENT 1
+// -DGMC_EXPERIMENT (tools/build_variant.sh) compiles the GMC_PR_MODE switches of the microbenchmark drivers into the sweep;
+// the product build has none of them
 #include "gmc_common.cuh"
 #include "gmc_comm.h"
 #include <cub/device/device_radix_sort.cuh>
