@@ -71,6 +71,7 @@ SIGNATURES = {
     "gmc_pagerank_plan_info": (C.c_int, [_vp, C.POINTER(PlanInfo)]),
     "gmc_triangle_counting": (C.c_int, [_vp, C.POINTER(C.c_int64), C.POINTER(C.c_float)]),
     "gmc_triangle_counting_range": (C.c_int, [_vp, C.c_int64, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_float), _vp]),
+    "gmc_triangle_counting_sharded": (C.c_int, [_vp, _vp, C.POINTER(C.c_int64), C.POINTER(C.c_float), _vp]),
     "gmc_hop_dist": (C.c_int, [_vp, _i32, _vp, C.POINTER(BfsInfo)]),
     "gmc_hop_dist_dev": (C.c_int, [_vp, _i32, _vp, C.POINTER(BfsInfo), _vp]),
     "gmc_bfs_levels": (C.c_int, [_vp, _i32, C.c_int, _vp, _vp, _vp, _i32, C.POINTER(BfsInfo)]),
@@ -325,6 +326,11 @@ class Graph:
             self.lib.check(self.lib.L.gmc_triangle_counting(self.h, C.byref(cnt), C.byref(ms)))
         else:
             self.lib.check(self.lib.L.gmc_triangle_counting_range(self.h, e_lo, e_hi, C.byref(cnt), C.byref(ms), None))
+        return cnt.value, ms.value
+
+    def triangle_counting_sharded(self, comm):
+        cnt = C.c_int64(); ms = C.c_float()
+        self.lib.check(self.lib.L.gmc_triangle_counting_sharded(self.h, comm.h if comm else None, C.byref(cnt), C.byref(ms), None))
         return cnt.value, ms.value
 
     def pagerank_into(self, rank_host, e=1e-30, d=0.85, max_iter=20):

@@ -219,6 +219,10 @@ int gmc_hop_dist_sharded_dev(gmc_graph* g, gmc_comm* comm, int32_t root, int32_t
 int gmc_bfs_levels_sharded(gmc_graph* g, gmc_comm* comm, int32_t root, int use_reverse_edge, const uint8_t* edge_mask_host,
                            int16_t* level_host, int32_t* state_trace, int32_t* level_count, int32_t trace_cap, gmc_bfs_info* info);
 
+/* triangle_counting on several ranks: rank r counts the edge slots [r*M/world, (r+1)*M/world) of the replicated graph, one
+ * 8-byte allreduce adds the partial counts (the procedure has no other exchange step); every rank returns the total. */
+int gmc_triangle_counting_sharded(gmc_graph* g, gmc_comm* comm, int64_t* count, float* kernel_ms, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

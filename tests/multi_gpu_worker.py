@@ -53,6 +53,10 @@ def main():
         lev, li, trace, cnt = g.bfs_levels_sharded(comm, root)
         lev1, li1, trace1, cnt1 = g.bfs_levels(root)
         assert np.array_equal(lev, lev1) and list(trace) == list(trace1) and list(cnt) == list(cnt1)
+    # triangle counting: slot ranges per rank + one allreduce == the single-GPU count, on every rank
+    t_all, _ = g.triangle_counting_sharded(comm)
+    t_one, _ = g.triangle_counting()
+    assert t_all == t_one and t_one > 0, f"rank {rank}: sharded triangle count {t_all} != {t_one}"
     # sharded copy-in: slices uploaded by their ranks + NVLink allgather reproduce the arrays on every rank
     host = {k: g.array(k) for k in ("begin", "node_idx", "r_begin", "r_node_idx")}
     g2 = lib.graph_from_csr_sharded(comm, host["begin"], host["node_idx"], host["r_begin"], host["r_node_idx"])
