@@ -649,11 +649,14 @@ __global__ void k_ltask_rows(const int32_t* __restrict__ lbeg, int32_t n_long, i
     }
     first[t] = lo;
 }
-__global__ void k_stask_slices(const int32_t* __restrict__ cpos, int32_t n_slices, int32_t n_tasks, int32_t st_cost, int32_t* __restrict__ first) {
+// short tasks: the first n_big ones hold st_cost cost units, the rest (the tail of the sweep: the last tasks handed out)
+// a quarter of that, so that the warps finish closer together
+__global__ void k_stask_slices(const int32_t* __restrict__ cpos, int32_t n_slices, int32_t n_tasks, int32_t st_cost, int32_t n_big, int32_t tail_shift,
+                               int32_t* __restrict__ first) {
     int32_t u = blockIdx.x * blockDim.x + threadIdx.x;
     if (u > n_tasks) return;
     if (u == n_tasks) { first[u] = n_slices; return; }
-    const int32_t target = u * st_cost;      // first slice with cpos >= target
+    const int32_t target = u <= n_big ? u * st_cost : n_big * st_cost + (u - n_big) * (st_cost >> tail_shift);      // first slice with cpos >= target
     int32_t lo = 0, hi = n_slices;
     while (lo < hi) {
         const int32_t mid = lo + ((hi - lo) >> 1);
@@ -777,7 +780,7 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
     const size_t nn = (size_t)n;
     const unsigned gb = (unsigned)div_up(n, 256);
     int32_t h[2] = {0, 0};
-    int32_t g_n_slices = 0, jl1 = 0, s1 = 0, cost_total = 0, s_max = S_MAX;
+    int32_t g_n_slices = 0, jl1 = 0, s1 = 0, cost_total = 0, s_max = S_MAX, n_big = 0, tail_shift = 2;
     std::vector<int32_t> h_lbeg, h_sbeg, h_scost, cutsL((size_t)world + 1), cutsS((size_t)world + 1), cutsZ((size_t)world + 1);
 
     PLAN_TRY(gmc_malloc((void**)&outdeg_old, 4 * nn)); PLAN_TRY(gmc_malloc((void**)&indeg, 4 * nn));
@@ -915,11 +918,19 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
     }
     // 4. tasks
     p->n_ltasks = div_up(p->EL, p->lt);
-    p->n_stasks = div_up(cost_total, p->st_cost);
+    // ~7/8 of the short-row cost in full-size tasks, the last eighth in quarter-size ones (tail of the sweep)
+    {
+        int big16 = 14, sh = 2;                                                        // experiments: GMC_PR_TAIL="<sixteenths in big tasks>,<shift>"
+        if (const char* t = getenv("GMC_PR_TAIL")) sscanf(t, "%d,%d", &big16, &sh);
+        tail_shift = sh;
+        n_big = (int32_t)((int64_t)cost_total * big16 / 16 / p->st_cost);
+    }
+    if (getenv("GMC_PR_NO_SMALL_TAIL")) n_big = div_up(cost_total, p->st_cost);       // experiments
+    p->n_stasks = n_big + div_up(cost_total > n_big * p->st_cost ? cost_total - n_big * p->st_cost : 0, p->st_cost >> tail_shift);
     PLAN_TRY(gmc_malloc((void**)&p->ltask_row, 4 * ((size_t)p->n_ltasks + 1)));
     PLAN_TRY(gmc_malloc((void**)&p->stask_slice, 4 * ((size_t)p->n_stasks + 1)));
     k_ltask_rows<<<div_up(p->n_ltasks + 1, 256), 256, 0, st>>>(p->lbeg, p->n_long, p->n_ltasks, p->lt, p->ltask_row);
-    k_stask_slices<<<div_up(p->n_stasks + 1, 256), 256, 0, st>>>(scost, p->n_slices, p->n_stasks, p->st_cost, p->stask_slice);
+    k_stask_slices<<<div_up(p->n_stasks + 1, 256), 256, 0, st>>>(scost, p->n_slices, p->n_stasks, p->st_cost, n_big, tail_shift, p->stask_slice);
     {
         const size_t nl = (size_t)(p->n_ltasks ? p->n_ltasks : 1), nparts = 2 * nl + (size_t)p->n_stasks + (size_t)p->n_ztasks + 1;
         PLAN_TRY(gmc_malloc((void**)&p->head_part, 8 * nl)); PLAN_TRY(gmc_malloc((void**)&p->tail_part, 8 * nl));
