@@ -424,16 +424,21 @@ __device__ __forceinline__ void zero_task(const SweepArgs& A, int lane, int32_t 
 }
 
 __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
-    if (A.loop && A.ctrl->done) return;
     extern __shared__ __align__(16) double hot[];
     __shared__ __align__(8) unsigned long long bar;
     __shared__ double s_red[PR_WARPS];
     __shared__ int s_last;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    // stage the hot block: contrib_in[0, hot_n) -> shared memory, one TMA bulk copy stream
     if (tid == 0) mbar_init(&bar, 1);
     __syncthreads();
+    // programmatic dependent launch: the CTAs of sweep k+1 take their SMs as the CTAs of sweep k leave them and wait
+    // here (everything above touches no global memory) until sweep k has completed and its stores are visible
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (A.loop && A.ctrl->done) return;
+
+    // stage the hot block: contrib_in[0, hot_n) -> shared memory, one TMA bulk copy stream
     if (tid == 0) {
         const unsigned bytes = (unsigned)(((A.hot_n + 1) & ~1) * 8);     // multiple of 16
         mbar_expect_tx(&bar, bytes);
@@ -1025,8 +1030,20 @@ int launch_init(const gmc_pr_plan* p, cudaStream_t st) {
 }
 
 int launch_sweep(const gmc_pr_plan* p, const SweepArgs& A, cudaStream_t st) {
-    pr_sweep<<<p->grid, PR_THREADS, p->smem, st>>>(A);
-    GMC_CUDA(cudaGetLastError());
+    // launched with programmatic stream serialization: the next sweep's CTAs may become resident while this one's tail
+    // drains (pr_sweep orders itself behind its predecessor with griddepcontrol.wait); GMC_PR_NO_PDL=1 = plain launch
+    static const bool pdl = getenv("GMC_PR_NO_PDL") == nullptr;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)p->grid);
+    cfg.blockDim = dim3(PR_THREADS);
+    cfg.dynamicSmemBytes = p->smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    GMC_CUDA(cudaLaunchKernelEx(&cfg, pr_sweep, A));
     return GMC_OK;
 }
 
