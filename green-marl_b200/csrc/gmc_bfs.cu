@@ -62,6 +62,7 @@ struct gmc_bfs_ws {
     std::vector<int32_t> level_count, state_trace;
     bool last_is_i16 = false;
     bool valid = false;
+    int last_launches = 0;
 };
 
 void gmc_bfs_ws_free(gmc_graph* g) {
@@ -358,7 +359,7 @@ int ensure_ws(gmc_graph* g, int world) {
 template <typename L>
 int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_t* fwd_idx, const int32_t* rev_begin,
             const int32_t* rev_idx, int32_t root, L invalid, L* level_out_dev, gmc_bfs_info* info, cudaStream_t st,
-            const uint8_t* edge_mask = nullptr) {
+            const uint8_t* edge_mask = nullptr, bool save_child = false) {
     GMC_REQUIRE(root >= 0 && root < g->N, GMC_ERR_ARG, "bfs: root %d out of range [0,%d)", root, g->N);
     GMC_REQUIRE(g->has_forward, GMC_ERR_STATE, "bfs: the forward CSR (node_idx) was not uploaded for this graph");
     const int world = comm ? comm->world : 1, rank = comm ? comm->rank : 0;
@@ -366,6 +367,8 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     gmc_bfs_ws* w = g->bfs;
     const int32_t n = g->N;
     const bool has_reverse = rev_begin != nullptr;
+    // a save_child instantiation never switches QUE / Q2R -> RRD directly (gm_bfs_template.h:374,:389), only RD -> RRD (:398)
+    const bool rrd_direct = has_reverse && !save_child;
     L* level = level_out_dev ? level_out_dev : (L*)w->level;
     w->level_count.clear(); w->state_trace.clear();
     w->valid = false;
@@ -444,10 +447,10 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
         switch (state) {
             case ST_SMALL: if (next_count >= 128) next_state = ST_QUE; break;
             case ST_QUE:
-                if ((float)next_count >= thr) next_state = has_reverse ? ST_RRD : ST_RD;
+                if ((float)next_count >= thr) next_state = rrd_direct ? ST_RRD : ST_RD;
                 else if (next_count >= 1024 && next_count >= curr_count * 5) next_state = ST_Q2R;
                 break;
-            case ST_Q2R: next_state = (has_reverse && (float)next_count >= thr) ? ST_RRD : ST_RD; break;
+            case ST_Q2R: next_state = (rrd_direct && (float)next_count >= thr) ? ST_RRD : ST_RD; break;
             case ST_RD:
                 if (has_reverse && (float)next_count >= thr) next_state = ST_RRD;
                 else if (next_count <= 2 * curr_count) next_state = ST_R2Q;
@@ -464,6 +467,7 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     GMC_CUDA(cudaStreamSynchronize(st));
     w->valid = true;
     w->last_is_i16 = sizeof(L) == 2;
+    w->last_launches = launches;
     if (info) {
         info->levels = curr_level + 1;
         int32_t reached = 0;
@@ -484,6 +488,22 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
 }
 
 }  // namespace
+
+// internal (gmc_bc.cu): forward traversal whose int16 levels stay in the workspace; level counts and states are the host record
+int gmc_bfs_levels_resident(gmc_graph* g, int32_t root, bool save_child, const int16_t** level_dev, const int32_t** level_count,
+                            const int32_t** state_trace, int32_t* n_levels, int32_t* launches, cudaStream_t st) {
+    GMC_TRY(ensure_ws(g, 1));
+    GMC_TRY(run_bfs<int16_t>(g, nullptr, g->begin, g->node_idx, g->has_reverse ? g->r_begin : nullptr,
+                             g->has_reverse ? g->r_node_idx : nullptr, root, (int16_t)-2, (int16_t*)g->bfs->level, nullptr, st,
+                             nullptr, save_child));
+    gmc_bfs_ws* w = g->bfs;
+    *level_dev = (const int16_t*)w->level;
+    *level_count = w->level_count.data();
+    *state_trace = w->state_trace.data();
+    *n_levels = (int32_t)w->level_count.size();
+    if (launches) *launches = w->last_launches;
+    return GMC_OK;
+}
 
 extern "C" {
 
@@ -510,6 +530,8 @@ int gmc_bfs_levels_sharded(gmc_graph* g, gmc_comm* comm, int32_t root, int use_r
                            int16_t* level_host, int32_t* state_trace, int32_t* level_count, int32_t trace_cap, gmc_bfs_info* info) {
     GMC_REQUIRE(g && level_host, GMC_ERR_ARG, "gmc_bfs_levels: NULL");
     GMC_REQUIRE(g->N > 0, GMC_ERR_ARG, "gmc_bfs_levels: empty graph");
+    const bool save_child = (use_reverse_edge & GMC_BFS_SAVE_CHILD) != 0;
+    use_reverse_edge &= GMC_BFS_REVERSE_EDGE;
     GMC_REQUIRE(!use_reverse_edge || g->has_reverse, GMC_ERR_STATE, "gmc_bfs_levels: use_reverse_edge needs the reverse CSR");
     GMC_TRY(ensure_ws(g, comm ? comm->world : 1));
     const int32_t *fb = g->begin, *fi = g->node_idx;
@@ -524,7 +546,7 @@ int gmc_bfs_levels_sharded(gmc_graph* g, gmc_comm* comm, int32_t root, int use_r
         int rc = gmc_h2d(mask_dev, edge_mask_host, (size_t)g->M, nullptr);
         if (rc != GMC_OK) { cudaFree(mask_dev); return rc; }
     }
-    int rc = run_bfs<int16_t>(g, comm, fb, fi, rb, ri, root, (int16_t)-2, (int16_t*)g->bfs->level, info, nullptr, mask_dev);
+    int rc = run_bfs<int16_t>(g, comm, fb, fi, rb, ri, root, (int16_t)-2, (int16_t*)g->bfs->level, info, nullptr, mask_dev, save_child);
     if (mask_dev) cudaFree(mask_dev);
     GMC_TRY(rc);
     gmc_bfs_ws* w = g->bfs;

@@ -24,6 +24,10 @@ class BfsInfo(C.Structure):
                 ("kernel_ms", C.c_float), ("launches", C.c_int32), ("bottom_up_levels", C.c_int32)]
 
 
+class BcInfo(C.Structure):
+    _fields_ = [("seeds", C.c_int32), ("launches", C.c_int32), ("max_levels", C.c_int32), ("device_ms", C.c_float)]
+
+
 class PlanInfo(C.Structure):
     _fields_ = [(k, C.c_int32) for k in ("n_long", "hot_n", "n_slices", "long_entries", "total_entries", "n_long_tasks",
                                          "n_short_tasks", "grid", "threads", "smem_bytes")]
@@ -72,6 +76,8 @@ SIGNATURES = {
     "gmc_triangle_counting": (C.c_int, [_vp, C.POINTER(C.c_int64), C.POINTER(C.c_float)]),
     "gmc_triangle_counting_range": (C.c_int, [_vp, C.c_int64, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_float), _vp]),
     "gmc_triangle_counting_sharded": (C.c_int, [_vp, _vp, C.POINTER(C.c_int64), C.POINTER(C.c_float), _vp]),
+    "gmc_comp_bc": (C.c_int, [_vp, _vp, _i32, _vp, C.POINTER(BcInfo)]),
+    "gmc_comp_bc_adj": (C.c_int, [_vp, _vp, _i32, _vp, C.POINTER(BcInfo)]),
     "gmc_hop_dist": (C.c_int, [_vp, _i32, _vp, C.POINTER(BfsInfo)]),
     "gmc_hop_dist_dev": (C.c_int, [_vp, _i32, _vp, C.POINTER(BfsInfo), _vp]),
     "gmc_bfs_levels": (C.c_int, [_vp, _i32, C.c_int, _vp, _vp, _vp, _i32, C.POINTER(BfsInfo)]),
@@ -327,6 +333,14 @@ class Graph:
         else:
             self.lib.check(self.lib.L.gmc_triangle_counting_range(self.h, e_lo, e_hi, C.byref(cnt), C.byref(ms), None))
         return cnt.value, ms.value
+
+    def comp_bc(self, seeds, adj=False):
+        """comp_BC (bc.gm; adj=True: bc_adj.gm) over the given seeds in order: returns (BC float32[N], BcInfo)"""
+        seeds = np.ascontiguousarray(seeds, dtype=np.int32)
+        bc = np.empty(max(self.num_nodes, 1), np.float32)
+        info = BcInfo()
+        self.lib.check((self.lib.L.gmc_comp_bc_adj if adj else self.lib.L.gmc_comp_bc)(self.h, _ptr(seeds), len(seeds), _ptr(bc), C.byref(info)))
+        return bc[:self.num_nodes], info
 
     def triangle_counting_sharded(self, comm):
         cnt = C.c_int64(); ms = C.c_float()

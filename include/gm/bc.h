@@ -18,4 +18,6 @@
 #include "gm.h"
 
 void comp_BC(gm_graph& G, float* G_BC, gm_node_seq& Seeds);
+// the same procedure in its literal generated form: a gm_bfs_template subclass with visit_fw / visit_rv on the host
+void comp_BC_via_template(gm_graph& G, float* G_BC, gm_node_seq& Seeds);
 #endif

@@ -5,7 +5,9 @@
 // from root level by level, calling visit_fw(t) while get_curr_level() is t's level and
 // do_end_of_level_fw() after each level; do_bfs_reverse() walks the levels back calling visit_rv(t) /
 // do_end_of_level_rv(); is_down_edge(e) is true for an edge t->u with level(u) == level(t)+1 (:483-524,
-// :581-622); check_navigator(u, e) filters edges (:488-492); levels are level_t with -2 = unvisited (:725).
+// :581-622) unless t's level was expanded bottom-up, where the reference marks nothing (:215-259,:689-708; a save_child
+// instance reaches those states only through RD -> RRD, :398-400); check_navigator(u, e) filters edges (:488-492);
+// levels are level_t with -2 = unvisited (:725).
 //
 // Device formulation: the TRAVERSAL (the reference's iterate_neighbor_que/rd + check_parent_rrd state
 // machine, :69-271,:352-421) runs on the GPU in one call (gmc_bfs_levels*, include/gm_cuda.h) over the
@@ -81,7 +83,8 @@ class gm_bfs_template {
         std::vector<int16_t> lev16(n > 0 ? n : 1);
         std::vector<int32_t> trace(LEVEL_CAP), counts(LEVEL_CAP);
         gmc_bfs_info info;
-        int rc = gmc_bfs_levels_masked(dev, root, use_reverse_edge ? 1 : 0, has_navigator ? &mask[0] : NULL, &lev16[0],
+        const int flags = (use_reverse_edge ? GMC_BFS_REVERSE_EDGE : 0) | (save_child ? GMC_BFS_SAVE_CHILD : 0);
+        int rc = gmc_bfs_levels_masked(dev, root, flags, has_navigator ? &mask[0] : NULL, &lev16[0],
                                        &trace[0], &counts[0], LEVEL_CAP, &info);
         if (rc != GMC_OK) die("gmc_bfs_levels");
         const int nlev = info.levels;
@@ -105,7 +108,8 @@ class gm_bfs_template {
         level_queue_begin.assign(lbegin.begin(), lbegin.begin() + nlev);
         state_trace.assign(trace.begin(), trace.begin() + nlev);
 
-        if (save_child) {   // edges t->u with level(u) == level(t)+1 that pass the navigator
+        if (save_child) {   // edges t->u with level(u) == level(t)+1 that pass the navigator, of the levels expanded top-down:
+                            // the bottom-up states mark none (check_parent_rrd, reference :689-708)
             delete[] down_edge_array;
             down_edge_array = new unsigned char[m > 0 ? m : 1];
 #pragma omp parallel for schedule(dynamic, 128) num_threads(num_thread)
@@ -113,8 +117,9 @@ class gm_bfs_template {
                 edge_t b, e;
                 get_range(b, e, t);
                 const level_t lt = visited_level[t];
+                const bool marking = lt != __INVALID_LEVEL && state_trace[lt] != ST_RRD && state_trace[lt] != ST_RR2Q;
                 for (edge_t nx = b; nx < e; nx++) {
-                    bool down = lt != __INVALID_LEVEL && visited_level[get_node(nx)] == (level_t)(lt + 1);
+                    bool down = marking && visited_level[get_node(nx)] == (level_t)(lt + 1);
                     if (down && has_navigator) down = mask[nx] != 0;
                     down_edge_array[nx] = down ? 1 : 0;
                 }

@@ -153,8 +153,15 @@ typedef struct {
 } gmc_bfs_info;
 int gmc_hop_dist(gmc_graph* g, int32_t root, int32_t* dist_host, gmc_bfs_info* info);
 int gmc_hop_dist_dev(gmc_graph* g, int32_t root, int32_t* dist_dev, gmc_bfs_info* info, void* stream);
-/* use_reverse_edge: traverse in-edges instead of out-edges (template parameter of the reference class).
- * state_trace / level_count: optional host arrays of capacity trace_cap. */
+/* use_reverse_edge: the template parameters of the reference class that change the traversal, as flags:
+ * GMC_BFS_REVERSE_EDGE (= 1, so a plain boolean keeps working) follows in-edges instead of out-edges;
+ * GMC_BFS_SAVE_CHILD selects the state machine of a save_child instantiation, which never switches QUE / Q2R -> RRD
+ * directly (gm_bfs_template.h:374,:389), only RD -> RRD (:398-400).  Levels do not depend on it; the states do, and the
+ * reference marks down edges only on the levels it expands top-down (states below GMC_BFS_ST_RRD).
+ * state_trace / level_count: optional host arrays of capacity trace_cap; states are the reference's (:713-719). */
+enum { GMC_BFS_REVERSE_EDGE = 1, GMC_BFS_SAVE_CHILD = 2 };
+enum { GMC_BFS_ST_SMALL = 0, GMC_BFS_ST_QUE = 1, GMC_BFS_ST_Q2R = 2, GMC_BFS_ST_RD = 3, GMC_BFS_ST_R2Q = 4,
+       GMC_BFS_ST_RRD = 5, GMC_BFS_ST_RR2Q = 6 };
 int gmc_bfs_levels(gmc_graph* g, int32_t root, int use_reverse_edge, int16_t* level_host,
                    int32_t* state_trace, int32_t* level_count, int32_t trace_cap, gmc_bfs_info* info);
 /* same traversal restricted to the edges with edge_mask_host[e] != 0 (e indexes the arrays being followed:
@@ -167,6 +174,25 @@ int gmc_bfs_levels_masked(gmc_graph* g, int32_t root, int use_reverse_edge, cons
  * level_queue_begin, gm_bfs_template.h:423-447), for do_bfs_reverse and host callback replay.
  * order_host[N]; level_begin_host[levels+1]. Valid after gmc_bfs_levels on the same graph. */
 int gmc_bfs_level_order(gmc_graph* g, int32_t* order_host, int32_t* level_begin_host, int32_t cap_levels);
+
+/* --- comp_BC: the generated comp_BC() (reference apps/src/bc.gm:4-29) with the two traversal
+ * callbacks on the device: per seed one BFS, visit_fw (sigma over the UpNbrs, gm_cpp_gen_foreach.cc:163-175) per level in
+ * ascending order, visit_rv (delta over the down edges, gm_bfs_template.h:273-319,496-524; BC += delta) per level in
+ * descending order.  float arithmetic, every vertex's sum in edge-slot order as in the reference's loops, so BC is
+ * bit-identical to the CPU result of a single-thread run (NaN where the reference yields NaN; with several threads the
+ * reference's down-edge marking races).  Kept reference behaviour: a level expanded bottom-up (state RRD / RR2Q) has no
+ * down edges -- check_parent_rrd (:689-708) does not mark them -- so its vertices get delta = 0.  Seeds are processed in the given order;
+ * bc_host[N] is overwritten.  Needs the forward and the reverse CSR. */
+typedef struct gmc_bc_info {
+    int32_t seeds;        /* traversals done */
+    int32_t launches;     /* kernels launched (traversal + bucketing + 2 per level) */
+    int32_t max_levels;   /* deepest traversal */
+    float device_ms;      /* device time of the whole call up to the copy-out */
+} gmc_bc_info;
+int gmc_comp_bc(gmc_graph* g, const int32_t* seeds, int32_t n_seeds, float* bc_host, gmc_bc_info* info);
+/* the same procedure as apps/src/bc_adj.gm:4-29 writes it: InBFS(v: G.Nodes From s)(v != s) / InReverse(v != s) -- both
+ * passes skip the root, whose sigma therefore stays 1 (bc.gm overwrites it with an empty sum: all-zero sigma, NaN delta) */
+int gmc_comp_bc_adj(gmc_graph* g, const int32_t* seeds, int32_t n_seeds, float* bc_host, gmc_bc_info* info);
 
 /* --- triangle_counting: the generated triangle_counting() (reference
  * apps/src/triangle_counting.gm:1-13): T = #{(v, slot i, slot j) : u = nbr_i(v) > v, w = nbr_j(v) > u, edge w -> u},

@@ -290,10 +290,13 @@ int orc_hop_dist(int32_t N, const int32_t* begin, const int32_t* node_idx, int32
  * The level of a vertex does not depend on which state discovered it; the state trace is exported
  * so the device state machine can be checked against the reference's direction switches. */
 enum { ST_SMALL = 0, ST_QUE, ST_Q2R, ST_RD, ST_R2Q, ST_RRD, ST_RR2Q };
-int orc_bfs_levels(int32_t N, const int32_t* begin, const int32_t* node_idx,
-                   const int32_t* r_begin, const int32_t* r_node_idx, int has_reverse,
-                   int32_t root, int16_t* levels, int32_t* state_trace, int32_t* level_count,
-                   int32_t trace_cap) {
+/* save_child (template parameter, :14): the direct QUE / Q2R -> RRD switches are disabled (:374,:389), the RD -> RRD
+ * one is not (:398-400) */
+static int bfs_levels_impl(int32_t N, const int32_t* begin, const int32_t* node_idx,
+                           const int32_t* r_begin, const int32_t* r_node_idx, int has_reverse, int save_child,
+                           int32_t root, int16_t* levels, int32_t* state_trace, int32_t* level_count,
+                           int32_t trace_cap) {
+    const int rrd_direct = has_reverse && !save_child;
     const int16_t INVALID = -2;                       /* __INVALID_LEVEL, :725 */
     const int THRESHOLD1 = 128, THRESHOLD2 = 1024;    /* :720-721 */
     const float RRD_THRESHOLD = 0.05f;                /* :359 (float arithmetic in the comparisons) */
@@ -363,10 +366,10 @@ int orc_bfs_levels(int32_t N, const int32_t* begin, const int32_t* node_idx,
         switch (state) {
         case ST_SMALL: if (next_count >= THRESHOLD1) next_state = ST_QUE; break;
         case ST_QUE:
-            if ((float)next_count >= thr) next_state = has_reverse ? ST_RRD : ST_RD;
+            if ((float)next_count >= thr) next_state = rrd_direct ? ST_RRD : ST_RD;
             else if (next_count >= THRESHOLD2 && next_count >= curr_count * 5) next_state = ST_Q2R;
             break;
-        case ST_Q2R: next_state = (has_reverse && (float)next_count >= thr) ? ST_RRD : ST_RD; break;
+        case ST_Q2R: next_state = (rrd_direct && (float)next_count >= thr) ? ST_RRD : ST_RD; break;
         case ST_RD:
             if ((float)next_count >= thr) next_state = ST_RRD;
             else if (next_count <= 2 * curr_count) next_state = ST_R2Q;
@@ -387,6 +390,18 @@ int orc_bfs_levels(int32_t N, const int32_t* begin, const int32_t* node_idx,
     }
     free(queue);
     return curr_level + 1;
+}
+int orc_bfs_levels(int32_t N, const int32_t* begin, const int32_t* node_idx,
+                   const int32_t* r_begin, const int32_t* r_node_idx, int has_reverse,
+                   int32_t root, int16_t* levels, int32_t* state_trace, int32_t* level_count,
+                   int32_t trace_cap) {
+    return bfs_levels_impl(N, begin, node_idx, r_begin, r_node_idx, has_reverse, 0, root, levels, state_trace, level_count, trace_cap);
+}
+int orc_bfs_levels_save_child(int32_t N, const int32_t* begin, const int32_t* node_idx,
+                              const int32_t* r_begin, const int32_t* r_node_idx, int has_reverse,
+                              int32_t root, int16_t* levels, int32_t* state_trace, int32_t* level_count,
+                              int32_t trace_cap) {
+    return bfs_levels_impl(N, begin, node_idx, r_begin, r_node_idx, has_reverse, 1, root, levels, state_trace, level_count, trace_cap);
 }
 
 
@@ -489,19 +504,24 @@ int64_t orc_triangle_counting(int32_t N, const int32_t* begin, const int32_t* no
 
 
 /* comp_BC, apps/src/bc.gm:4-29.  Levels from the BFS template restatement above; forward pass level by level
- * (visit_fw), reverse pass from the deepest level back to the root (do_bfs_reverse, gm_bfs_template.h:273-312). */
-void orc_comp_bc(int32_t N, const int32_t* begin, const int32_t* node_idx, const int32_t* r_begin,
-                 const int32_t* r_node_idx, const int32_t* seeds, int32_t n_seeds, float* bc) {
+ * (visit_fw), reverse pass from the deepest level back to the root (do_bfs_reverse, gm_bfs_template.h:273-312).
+ * Down edges (save_child): iterate_neighbor_small/que/rd mark every edge into level + 1 (:496-509,:603-617,:663-677);
+ * the bottom-up levels do not -- check_parent_rrd (:689-708) has no save_down_edge call -- so the out-edges of a level
+ * that was expanded in state RRD or RR2Q are NOT down edges (single-thread semantics; with several threads the marking
+ * in the que/rd states also races, see tests/test_bc.py). */
+static void comp_bc_impl(int32_t N, const int32_t* begin, const int32_t* node_idx, const int32_t* r_begin,
+                         const int32_t* r_node_idx, const int32_t* seeds, int32_t n_seeds, float* bc, int first_level) {
     int16_t* lev = (int16_t*)malloc(sizeof(int16_t) * (size_t)(N > 0 ? N : 1));
     float* sigma = (float*)malloc(sizeof(float) * (size_t)(N > 0 ? N : 1));
     float* delta = (float*)malloc(sizeof(float) * (size_t)(N > 0 ? N : 1));
+    int32_t* trace = (int32_t*)malloc(sizeof(int32_t) * 32768);                     /* level_t = short */
     for (int32_t t = 0; t < N; t++) bc[t] = 0.0f;                                   /* bc.gm:6 */
     for (int32_t k = 0; k < n_seeds; k++) {
         const int32_t s = seeds[k];
         for (int32_t t = 0; t < N; t++) sigma[t] = 0.0f;                            /* bc.gm:13 */
         sigma[s] = 1.0f;                                                            /* bc.gm:14 */
-        const int nl = orc_bfs_levels(N, begin, node_idx, r_begin, r_node_idx, 1, s, lev, NULL, NULL, 0);
-        for (int l = 0; l < nl; l++)                                                /* InBFS, bc.gm:17-20 */
+        const int nl = bfs_levels_impl(N, begin, node_idx, r_begin, r_node_idx, 1, 1, s, lev, trace, NULL, 32768);
+        for (int l = first_level; l < nl; l++)                                      /* InBFS, bc.gm:17-20 */
             for (int32_t v = 0; v < N; v++) {
                 if (lev[v] != l) continue;
                 float S = 0.0f;
@@ -512,18 +532,29 @@ void orc_comp_bc(int32_t N, const int32_t* begin, const int32_t* node_idx, const
                 }
                 sigma[v] = S;
             }
-        for (int l = nl - 1; l >= 0; l--)                                           /* InReverse, bc.gm:21-27 */
+        for (int l = nl - 1; l >= first_level; l--)                                 /* InReverse, bc.gm:21-27 */
             for (int32_t v = 0; v < N; v++) {
                 if (lev[v] != l) continue;
                 float S = 0.0f;
+                const int marked = trace[l] != ST_RRD && trace[l] != ST_RR2Q;
                 for (int32_t e = begin[v]; e < begin[v + 1]; e++) {
                     const int32_t w = node_idx[e];
-                    if (lev[w] != l + 1) continue;                                  /* is_down_edge */
+                    if (!marked || lev[w] != l + 1) continue;                       /* is_down_edge */
                     S = S + sigma[v] / sigma[w] * (1 + delta[w]);
                 }
                 delta[v] = S;
                 bc[v] = bc[v] + delta[v];
             }
     }
-    free(lev); free(sigma); free(delta);
+    free(lev); free(sigma); free(delta); free(trace);
+}
+void orc_comp_bc(int32_t N, const int32_t* begin, const int32_t* node_idx, const int32_t* r_begin,
+                 const int32_t* r_node_idx, const int32_t* seeds, int32_t n_seeds, float* bc) {
+    comp_bc_impl(N, begin, node_idx, r_begin, r_node_idx, seeds, n_seeds, bc, 0);
+}
+/* apps/src/bc_adj.gm:4-29: InBFS(v: G.Nodes From s)(v != s) / InReverse(v != s) -- the root (the only vertex of level 0)
+ * is skipped by both passes, so its sigma stays 1 and the path counts are the real ones */
+void orc_comp_bc_adj(int32_t N, const int32_t* begin, const int32_t* node_idx, const int32_t* r_begin,
+                     const int32_t* r_node_idx, const int32_t* seeds, int32_t n_seeds, float* bc) {
+    comp_bc_impl(N, begin, node_idx, r_begin, r_node_idx, seeds, n_seeds, bc, 1);
 }

@@ -60,6 +60,8 @@ int64_t orc_triangle_counting(int32_t N, const int32_t* begin, const int32_t* no
  * NaNs are the expected output wherever a vertex has a BFS child; bc is compared NaN-aware. */
 void orc_comp_bc(int32_t N, const int32_t* begin, const int32_t* node_idx, const int32_t* r_begin,
                  const int32_t* r_node_idx, const int32_t* seeds, int32_t n_seeds, float* bc);
+void orc_comp_bc_adj(int32_t N, const int32_t* begin, const int32_t* node_idx, const int32_t* r_begin,
+                     const int32_t* r_node_idx, const int32_t* seeds, int32_t n_seeds, float* bc);
 
 /* --- generated pagerank(): apps/src/pagerank.gm:1-20 (emitters: see ref_glue/pagerank.cc) ---
  * returns the number of iterations executed; *diff_out = last diff. */
@@ -76,6 +78,11 @@ int orc_hop_dist(int32_t N, const int32_t* begin, const int32_t* node_idx, int32
  * each level; level_count (nullable, same capacity) the vertex count of each level.
  * has_reverse = G.has_reverse_edge() (enables the bottom-up states).  Returns number of levels. */
 int orc_bfs_levels(int32_t N, const int32_t* begin, const int32_t* node_idx,
+                   const int32_t* r_begin, const int32_t* r_node_idx, int has_reverse,
+                   int32_t root, int16_t* levels, int32_t* state_trace, int32_t* level_count,
+                   int32_t trace_cap);
+/* the same traversal under the state machine of a save_child instantiation (gm_bfs_template.h:374,:389) */
+int orc_bfs_levels_save_child(int32_t N, const int32_t* begin, const int32_t* node_idx,
                    const int32_t* r_begin, const int32_t* r_node_idx, int has_reverse,
                    int32_t root, int16_t* levels, int32_t* state_trace, int32_t* level_count,
                    int32_t trace_cap);

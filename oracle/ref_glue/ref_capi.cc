@@ -82,11 +82,14 @@ void* ref_graph_load_edge_list(const char* path) {
 // comp_BC (apps/src/bc.gm:4-29) as the C++ back end emits it, over the reference's REAL gm_bfs_template (save_child)
 class ref_bc_bfs : public gm_bfs_template<short, true, false, false, true> {
   public:
-    ref_bc_bfs(gm_graph& _G, float* bc, float* sg, float* dl) : gm_bfs_template<short, true, false, false, true>(_G), G(_G), G_BC(bc), G_sigma(sg), G_delta(dl) {}
+    ref_bc_bfs(gm_graph& _G, float* bc, float* sg, float* dl, node_t _s, bool _adj)
+        : gm_bfs_template<short, true, false, false, true>(_G), G(_G), G_BC(bc), G_sigma(sg), G_delta(dl), s(_s), adj(_adj) {}
   private:
     gm_graph& G; float* G_BC; float* G_sigma; float* G_delta;
+    node_t s; bool adj;       // adj: bc_adj.gm:17,21 -- InBFS(v: G.Nodes From s)(v != s) / InReverse(v != s)
   protected:
     virtual void visit_fw(node_t v) {
+        if (adj && v == s) return;
         float S = (float)0;
         for (edge_t w_idx = G.r_begin[v]; w_idx < G.r_begin[v + 1]; w_idx++) {
             node_t w = G.r_node_idx[w_idx];
@@ -96,6 +99,7 @@ class ref_bc_bfs : public gm_bfs_template<short, true, false, false, true> {
         G_sigma[v] = S;
     }
     virtual void visit_rv(node_t v) {
+        if (adj && v == s) return;
         float S = (float)0;
         for (edge_t w_idx = G.begin[v]; w_idx < G.begin[v + 1]; w_idx++) {
             if (!is_down_edge(w_idx)) continue;
@@ -107,7 +111,7 @@ class ref_bc_bfs : public gm_bfs_template<short, true, false, false, true> {
     }
     virtual bool check_navigator(node_t, edge_t) { return true; }
 };
-void ref_comp_bc(void* h, const int32_t* seeds, int32_t n_seeds, float* bc) {
+static void ref_comp_bc_impl(void* h, const int32_t* seeds, int32_t n_seeds, float* bc, bool adj) {
     gm_graph& G = *(gm_graph*)h;
     const node_t N = G.num_nodes();
     std::vector<float> sigma(N > 0 ? N : 1), delta(N > 0 ? N : 1);
@@ -118,12 +122,15 @@ void ref_comp_bc(void* h, const int32_t* seeds, int32_t n_seeds, float* bc) {
         sigma[s] = 1;
         // deliberately leaked: the reference's destructor does `delete[] down_edge_set` on a `new std::set`
         // (gm_bfs_template.h:31,40), undefined behaviour that crashes under glibc when save_child is on
-        ref_bc_bfs* B = new ref_bc_bfs(G, bc, &sigma[0], &delta[0]);
+        ref_bc_bfs* B = new ref_bc_bfs(G, bc, &sigma[0], &delta[0], s, adj);
         B->prepare(s, gm_rt_get_num_threads());
         B->do_bfs_forward();
         B->do_bfs_reverse();
     }
 }
+void ref_comp_bc(void* h, const int32_t* seeds, int32_t n_seeds, float* bc) { ref_comp_bc_impl(h, seeds, n_seeds, bc, false); }
+// apps/src/bc_adj.gm:4-29: the same procedure with the (v != s) filters
+void ref_comp_bc_adj(void* h, const int32_t* seeds, int32_t n_seeds, float* bc) { ref_comp_bc_impl(h, seeds, n_seeds, bc, true); }
 // triangle_counting.gm:5-11 over the reference's REAL gm_graph::has_edge_to (gm_graph.cc:60-66,589-633)
 long long ref_triangle_counting(void* h) {
     gm_graph& G = *(gm_graph*)h;

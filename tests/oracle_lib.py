@@ -74,13 +74,15 @@ class Oracle:
         self.L.orc_triangle_counting.argtypes = [C.c_int32, _i32p, _i32p]
         return int(self.L.orc_triangle_counting(len(begin) - 1, begin, np.ascontiguousarray(node_idx)))
 
-    def comp_bc(self, begin, node_idx, r_begin, r_node_idx, seeds):
+    def comp_bc(self, begin, node_idx, r_begin, r_node_idx, seeds, adj=False):
+        """bc.gm; adj=True: bc_adj.gm (the (v != s) filters)"""
         N = len(begin) - 1
-        self.L.orc_comp_bc.restype = None
-        self.L.orc_comp_bc.argtypes = [C.c_int32, _i32p, _i32p, _i32p, _i32p, _i32p, C.c_int32, C.c_void_p]
+        fn = self.L.orc_comp_bc_adj if adj else self.L.orc_comp_bc
+        fn.restype = None
+        fn.argtypes = [C.c_int32, _i32p, _i32p, _i32p, _i32p, _i32p, C.c_int32, C.c_void_p]
         bc = np.zeros(max(N, 1), np.float32)
         sd = np.ascontiguousarray(seeds, np.int32)
-        self.L.orc_comp_bc(N, begin, np.ascontiguousarray(node_idx), r_begin, np.ascontiguousarray(r_node_idx), sd, len(sd), bc.ctypes.data)
+        fn(N, begin, np.ascontiguousarray(node_idx), r_begin, np.ascontiguousarray(r_node_idx), sd, len(sd), bc.ctypes.data)
         return bc[:N]
 
     def edge_list_read(self, path):
@@ -160,13 +162,14 @@ class Ref:
         self.L.ref_triangle_counting.restype = C.c_longlong; self.L.ref_triangle_counting.argtypes = [C.c_void_p]
         return int(self.L.ref_triangle_counting(g))
 
-    def comp_bc(self, g, seeds):
+    def comp_bc(self, g, seeds, adj=False):
         N = self.L.ref_graph_num_nodes(g)
-        self.L.ref_comp_bc.restype = None
-        self.L.ref_comp_bc.argtypes = [C.c_void_p, _i32p, C.c_int32, C.c_void_p]
+        fn = self.L.ref_comp_bc_adj if adj else self.L.ref_comp_bc
+        fn.restype = None
+        fn.argtypes = [C.c_void_p, _i32p, C.c_int32, C.c_void_p]
         bc = np.zeros(max(N, 1), np.float32)
         sd = np.ascontiguousarray(seeds, np.int32)
-        self.L.ref_comp_bc(g, sd, len(sd), bc.ctypes.data)
+        fn(g, sd, len(sd), bc.ctypes.data)
         return bc[:N]
 
     def load_edge_list(self, path):

@@ -1,7 +1,9 @@
-"""comp_BC (apps/src/bc.gm) through the facade's gm_bfs_template: device traversal, the generated
-visit_fw / visit_rv callbacks replayed on the host.  The oracle (plain C) is checked against the same generated class over
-the reference's own gm_bfs_template (oracle/_ref).  bc.gm as shipped yields NaN wherever a vertex has a BFS child (the
-root's sigma is overwritten by an empty sum), so arrays are compared NaN-aware, bit for bit otherwise."""
+"""comp_BC (apps/src/bc.gm, bc_adj.gm): the device procedure (gmc_comp_bc / gmc_comp_bc_adj: traversal
+and both callbacks as kernels) and the facade's gm_bfs_template (device traversal, arbitrary visit_fw / visit_rv callbacks
+replayed on the host).  The oracle (plain C) is checked against the same generated class over the reference's own
+gm_bfs_template (oracle/_ref).  bc.gm as shipped yields NaN wherever a vertex has a BFS child (the root's sigma is
+overwritten by an empty sum), so arrays are compared NaN-aware, bit for bit otherwise; bc_adj.gm (the (v != s) filters)
+is the variant with real path counts, which is what exercises the float arithmetic."""
 import os
 import re
 import subprocess
@@ -34,6 +36,10 @@ def test_oracle_matches_reference_bfs_template(oracle, ref):
         got = oracle.comp_bc(a["begin"], a["node_idx"], a["r_begin"], a["r_node_idx"], seeds)
         assert same(got, want)
         assert np.isnan(want).any() and (want == 0).any()       # the shipped bc.gm's degenerate output, see module docstring
+        want = ref.comp_bc(g, seeds, adj=True)
+        got = oracle.comp_bc(a["begin"], a["node_idx"], a["r_begin"], a["r_node_idx"], seeds, adj=True)
+        assert same(got, want)
+        assert not np.isnan(want).any() and (want > 0).any()    # bc_adj.gm: real dependencies
         ref.free(g)
     ref.set_threads(min(8, os.cpu_count() or 1))
 
@@ -45,18 +51,55 @@ def test_oracle_tiny(oracle):
     assert np.isnan(bc[0]) and np.isnan(bc[1]) and bc[2] == 0 and bc[3] == 0
 
 
+def test_oracle_adj_tiny(oracle):
+    # diamond 0 -> {1, 2} -> 3 -> 4 from seed 0: sigma = 1,1,1,2,2; delta(3) = 1, delta(1) = delta(2) = 1/2 * (1 + 1) = 1
+    g = graphs.from_edges(oracle, 5, [(0, 1), (0, 2), (1, 3), (2, 3), (3, 4)])
+    bc = oracle.comp_bc(g["begin"], g["node_idx"], g["r_begin"], g["r_node_idx"], [0], adj=True)
+    assert bc.tolist() == [0.0, 1.0, 1.0, 1.0, 0.0]
+
+
 @pytest.mark.gpu
-def test_comp_bc_facade_parity(gm, oracle, tmp_path):
+def test_comp_bc_device_parity(gm, oracle):
+    """gmc_comp_bc / gmc_comp_bc_adj through the C ABI against the oracle, bit for bit (NaN-aware)"""
+    cases = [graphs.from_edges(oracle, 5, [(0, 1), (0, 2), (1, 3), (2, 3), (3, 4)]),
+             graphs.rmat(oracle, 3000, 40000, seed=11), graphs.rmat(oracle, 200000, 3000000, seed=12),
+             graphs.prepared(oracle, *oracle.uniform_random(50000, 400000, 5))]
+    for g in cases:
+        G = gm.graph_from_csr(g["begin"], g["node_idx"], semi_sort=False, make_reverse=True)
+        deg = np.diff(g["begin"])
+        nz = np.nonzero(deg)[0]
+        seeds = [int(nz[0]), int(nz[len(nz) // 2]), int(deg.argmax()), int(np.diff(g["r_begin"]).argmax()), 1, int(nz[0])]
+        for adj in (False, True):
+            got, info = G.comp_bc(seeds, adj=adj)
+            want = oracle.comp_bc(g["begin"], g["node_idx"], g["r_begin"], g["r_node_idx"], seeds, adj=adj)
+            assert same(got, want), (g["N"], adj)
+            assert info.seeds == len(seeds) and info.launches > 0 and info.device_ms > 0
+            if adj and g["N"] > 100:
+                assert not np.isnan(want).any() and (want > 0).any()
+        got, _ = G.comp_bc([], adj=True)
+        assert not got.any()
+        with pytest.raises(Exception):
+            G.comp_bc([g["N"]])
+        G.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("via_template", [False, True])
+def test_comp_bc_facade_parity(gm, oracle, tmp_path, via_template):
     exe = os.path.join(BIN, "bc_check")
     assert os.path.exists(exe), f"{exe} missing: run __graft_entry__.build() where /root/reference is present"
+    env = dict(os.environ)
+    if via_template:
+        env["GM_BC_VIA_TEMPLATE"] = "1"
     for k, (n, m) in enumerate([(3000, 40000), (200000, 3000000)]):
         g = graphs.rmat(oracle, n, m, seed=11 + k)
         f = str(tmp_path / f"g{k}.bin"); out = str(tmp_path / f"bc{k}.f32")
         assert oracle.store_binary(f, g["begin"], g["node_idx"])
         nz = np.nonzero(np.diff(g["begin"]))[0]
         seeds = [int(nz[0]), int(nz[len(nz) // 2]), int(np.diff(g["begin"]).argmax()), 1]
-        r = subprocess.run([exe, f, out] + [str(s) for s in seeds], capture_output=True, text=True, timeout=300)
+        r = subprocess.run([exe, f, out] + [str(s) for s in seeds], capture_output=True, text=True, timeout=300, env=env)
         assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        assert ("comp_BC: seeds=" in r.stdout) != via_template      # the device procedure reports itself
         got = np.fromfile(out, np.float32)
         want = oracle.comp_bc(g["begin"], g["node_idx"], g["r_begin"], g["r_node_idx"], seeds)
         assert same(got, want)
