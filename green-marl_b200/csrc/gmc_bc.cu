@@ -12,10 +12,11 @@
 // (gm_cpp_gen_foreach.cc:163-175), visit_rv(v) walks the out-edge slots of v that save_child marked as down edges
 // (gm_bfs_template.h:496-524: an edge into level + 1, marked by the top-down expansion only), levels in ascending order forward (do_bfs_forward :69-271) and
 // descending order backward (do_bfs_reverse :273-312).  Here: the traversal is the device BFS (gmc_bfs.cu), the visited
-// vertices are bucketed by level once, then two launches per level and direction.  A warp owns a vertex: its lanes load 32
+// vertices are bucketed by level once, then two launches per level and direction.  8 lanes own a vertex: they load 8
 // edge slots at a time (coalesced ids, gathered levels and values) and every lane adds the matching terms in slot order
 // with __fadd_rn / __fdiv_rn / __fmul_rn -- the float sums are the reference's, term by term, whatever the degree; rows of
-// 1024 slots or more are handed to a second kernel (a CTA per row, terms staged in shared memory, one in-order add chain).
+// 1024 slots or more are handed to a second kernel (a CTA per row, matching terms compacted into shared memory in slot
+// order, one in-order add chain).
 //
 // Kept reference behaviour: the InBFS body has no (v != s) filter, so the root's sigma = 1 is overwritten by its empty
 // UpNbrs sum; with the shipped bc.gm every sigma is 0 and delta is NaN wherever a vertex has a BFS child.
@@ -33,8 +34,12 @@ int gmc_bfs_levels_resident(gmc_graph* g, int32_t root, bool save_child, const i
 namespace {
 
 constexpr int BC_THREADS = 256;
+constexpr int BC_GROUP = 8;            // lanes per vertex in bc_level
 constexpr int BC_HEAVY = 1024;         // rows with at least this many edge slots go to bc_heavy (a CTA per row)
-constexpr int BC_CHUNK = 2048;         // slots per shared-memory chunk of bc_heavy
+constexpr int BCH_THREADS = 1024;      // bc_heavy: threads per CTA (32 warps: the cross-warp scan is one warp wide)
+constexpr int BC_PER_THREAD = 8;       // bc_heavy: consecutive slots per thread and chunk
+constexpr int BC_CHUNK = BCH_THREADS * BC_PER_THREAD;   // slots per chunk (32 KB of terms in shared memory)
+static_assert(BCH_THREADS == 1024, "bc_heavy scans 32 warp totals with one warp");
 constexpr unsigned FULLM = 0xffffffffu;
 
 // order[level_begin[l] + k] = the k-th vertex of level l (k in arrival order: vertices of one level do not depend on each other)
@@ -72,49 +77,67 @@ __device__ __forceinline__ void bc_store(int32_t v, float S, float* __restrict__
     else sigma[v] = S;                                           // v.sigma = Sum ...
 }
 
-// The callback of every vertex of one level (order[lo, hi)), a warp per vertex: 32 edge slots per step, the matching
-// terms added in slot order by every lane.  Rows of BC_HEAVY slots or more are queued for bc_heavy instead.
+// The callback of every vertex of one level (order[lo, hi)), 8 lanes per vertex (4 vertices per warp: most rows are short,
+// and a vertex is a chain of five dependent loads -- order, row offsets, ids, levels, values -- so what counts is how many
+// are in flight): 8 edge slots per step, the matching terms added in slot order by every lane of the group.  Rows of
+// BC_HEAVY slots or more are queued for bc_heavy instead.
 template <bool REV>
 __global__ void __launch_bounds__(BC_THREADS)
 bc_level(const int32_t* __restrict__ row_begin, const int32_t* __restrict__ row_idx, const int16_t* __restrict__ level,
          const int32_t* __restrict__ order, int32_t lo, int32_t hi, int want, float* __restrict__ sigma, float* __restrict__ delta,
          float* __restrict__ bc, int32_t* __restrict__ heavy_list, int32_t* __restrict__ heavy_count) {
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, gl = lane & (BC_GROUP - 1), grp = lane / BC_GROUP;
+    constexpr int GPW = 32 / BC_GROUP;                       // groups per warp
     const int32_t nw = (gridDim.x * BC_THREADS) >> 5;
-    for (int32_t i = lo + ((blockIdx.x * BC_THREADS + threadIdx.x) >> 5); i < hi; i += nw) {
-        const int32_t v = order[i];
-        const int32_t b = row_begin[v], e = row_begin[v + 1];
-        if (e - b >= BC_HEAVY) {
-            if (lane == 0) heavy_list[atomicAdd(heavy_count, 1)] = v;
-            continue;
+    for (int32_t base = lo + ((blockIdx.x * BC_THREADS + threadIdx.x) >> 5) * GPW; base < hi; base += nw * GPW) {   // warp-uniform
+        const int32_t i = base + grp;
+        bool mine = i < hi;
+        int32_t v = 0, b = 0, e = 0;
+        if (mine) {
+            v = order[i];
+            b = row_begin[v];
+            e = row_begin[v + 1];
+            if (e - b >= BC_HEAVY) {
+                if (gl == 0) heavy_list[atomicAdd(heavy_count, 1)] = v;
+                mine = false;
+                e = b;
+            }
         }
-        const float sv = REV ? sigma[v] : 0.0f;
+        const float sv = (REV && mine) ? sigma[v] : 0.0f;
+        int steps = (e - b + BC_GROUP - 1) / BC_GROUP;
+#pragma unroll
+        for (int o = BC_GROUP; o < 32; o <<= 1) steps = max(steps, __shfl_xor_sync(FULLM, steps, o));
         float S = 0.0f;
-        for (int32_t p = b; p < e; p += 32) {
-            const int32_t q = p + lane;
+        for (int t = 0; t < steps; t++) {
+            const int32_t q = b + t * BC_GROUP + gl;
             float x = 0.0f;
             bool m = false;
             if (q < e) x = bc_term<REV>(ld_stream(row_idx + q), level, want, sigma, delta, sv, m);
-            unsigned mask = __ballot_sync(FULLM, m);
-            while (mask) {                               // slot order = the reference's loop order
-                const int j = __ffs(mask) - 1;
-                mask &= mask - 1;
-                S = __fadd_rn(S, __shfl_sync(FULLM, x, j));
+            unsigned gm = (__ballot_sync(FULLM, m) >> (grp * BC_GROUP)) & ((1u << BC_GROUP) - 1u);    // the group's matches
+            while (__any_sync(FULLM, gm != 0u)) {            // slot order = the reference's loop order
+                const int j = gm ? __ffs(gm) - 1 : 0;
+                const float xj = __shfl_sync(FULLM, x, grp * BC_GROUP + j);
+                if (gm) S = __fadd_rn(S, xj);
+                gm &= gm - 1u;
             }
         }
-        if (lane == 0) bc_store<REV>(v, S, sigma, delta, bc);
+        if (mine && gl == 0) bc_store<REV>(v, S, sigma, delta, bc);
     }
 }
 
-// The long rows of the level, a CTA per row: all threads turn BC_CHUNK slots into terms in shared memory (0 for a slot
-// that does not match: S + (+0) == S bit for bit, and no partial sum here is ever -0 -- every term is >= +0, NaN or
-// +Inf), then the first warp adds them in slot order, 4 clocks per term instead of a memory round trip per 32 slots.
+// The long rows of the level, a CTA per row.  Per chunk of BC_CHUNK slots every thread turns 8 consecutive slots into
+// terms (all loads of a chunk in flight at once), the matching ones are compacted in slot order into shared memory (one
+// block-wide exclusive scan of the per-thread match counts), then the first warp adds them in that order: one fadd (4
+// clocks) per matching term instead of a memory round trip per 32 slots.  The chain itself is what bit-identical float
+// sums cost; everything around it is parallel.
 template <bool REV>
-__global__ void __launch_bounds__(BC_THREADS)
+__global__ void __launch_bounds__(BCH_THREADS)
 bc_heavy(const int32_t* __restrict__ row_begin, const int32_t* __restrict__ row_idx, const int16_t* __restrict__ level, int want,
          float* __restrict__ sigma, float* __restrict__ delta, float* __restrict__ bc, const int32_t* __restrict__ heavy_list,
          const int32_t* __restrict__ heavy_count) {
-    __shared__ __align__(16) float xs[BC_CHUNK];
+    __shared__ __align__(16) float xs[BC_CHUNK + 4];
+    __shared__ int32_t wsum[BCH_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int32_t n = *heavy_count;
     for (int32_t h = blockIdx.x; h < n; h += gridDim.x) {
         const int32_t v = heavy_list[h];
@@ -122,30 +145,48 @@ bc_heavy(const int32_t* __restrict__ row_begin, const int32_t* __restrict__ row_
         const float sv = REV ? sigma[v] : 0.0f;
         float S = 0.0f;
         for (int32_t p = b; p < e; p += BC_CHUNK) {
+            float x[BC_PER_THREAD];
+            unsigned mbits = 0u;
 #pragma unroll
-            for (int k = threadIdx.x; k < BC_CHUNK; k += BC_THREADS) {
-                const int32_t q = p + k;
-                bool m;
-                xs[k] = q < e ? bc_term<REV>(ld_stream(row_idx + q), level, want, sigma, delta, sv, m) : 0.0f;
+            for (int k = 0; k < BC_PER_THREAD; k++) {
+                const int32_t q = p + tid * BC_PER_THREAD + k;
+                bool m = false;
+                x[k] = q < e ? bc_term<REV>(ld_stream(row_idx + q), level, want, sigma, delta, sv, m) : 0.0f;
+                if (m) mbits |= 1u << k;
             }
+            const int c = __popc(mbits);
+            int incl = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULLM, incl, o); if (lane >= o) incl += t; }
+            if (lane == 31) wsum[warp] = incl;
             __syncthreads();
-            if (threadIdx.x < 32) {
-                const int cnt = min(BC_CHUNK, e - p);        // slots past the row end hold 0: whole float4 groups are safe
+            const int wv = wsum[lane];                        // BCH_THREADS / 32 == 32 warps
+            int wincl = wv;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULLM, wincl, o); if (lane >= o) wincl += t; }
+            const int total = __shfl_sync(FULLM, wincl, 31);
+            int pos = __shfl_sync(FULLM, wincl - wv, warp) + incl - c;
+#pragma unroll
+            for (int k = 0; k < BC_PER_THREAD; k++)
+                if ((mbits >> k) & 1u) xs[pos++] = x[k];
+            if (tid < 4) xs[total + tid] = 0.0f;              // the chain reads whole float4 groups: + (+0) changes nothing
+            __syncthreads();
+            if (warp == 0) {
                 const float4* x4 = reinterpret_cast<const float4*>(xs);
 #pragma unroll 4
-                for (int k = 0; k < (cnt + 3) >> 2; k++) {
+                for (int k = 0; k < (total + 3) >> 2; k++) {
                     const float4 t = x4[k];
                     S = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(S, t.x), t.y), t.z), t.w);
                 }
             }
             __syncthreads();
         }
-        if (threadIdx.x == 0) bc_store<REV>(v, S, sigma, delta, bc);
+        if (tid == 0) bc_store<REV>(v, S, sigma, delta, bc);
     }
 }
 
 inline unsigned level_grid(int32_t count) {
-    const int64_t want = div_up((int64_t)count * 32, (int64_t)BC_THREADS);
+    const int64_t want = div_up((int64_t)count * BC_GROUP, (int64_t)BC_THREADS);
     const int64_t cap = (int64_t)sm_count() * 8;
     return (unsigned)(want < cap ? (want > 0 ? want : 1) : cap);
 }
@@ -181,7 +222,7 @@ static int comp_bc(gmc_graph* g, const int32_t* seeds, int32_t n_seeds, float* b
     GMC_TRY(gmc_malloc((void**)&B.cursor, sizeof(int32_t) * MAX_LEVELS));
     GMC_TRY(gmc_malloc((void**)&B.heavy_list, sizeof(int32_t) * n));
     GMC_TRY(gmc_malloc((void**)&B.heavy_count, sizeof(int32_t) * 2 * MAX_LEVELS));      // one counter per level and direction
-    const unsigned heavy_grid = (unsigned)sm_count() * 4;
+    const unsigned heavy_grid = (unsigned)sm_count() * 2;
     cudaEvent_t ev0, ev1;
     GMC_CUDA(cudaEventCreate(&ev0));
     GMC_CUDA(cudaEventCreate(&ev1));
@@ -215,7 +256,7 @@ static int comp_bc(gmc_graph* g, const int32_t* seeds, int32_t n_seeds, float* b
         for (int32_t l = first_level; l < nl; l++) {
             bc_level<false><<<level_grid(level_count[l]), BC_THREADS, 0, st>>>(g->r_begin, g->r_node_idx, level, B.order, lb[l], lb[l + 1],
                                                                                l - 1, B.sigma, B.delta, B.bc, B.heavy_list, B.heavy_count + 2 * l);
-            bc_heavy<false><<<heavy_grid, BC_THREADS, 0, st>>>(g->r_begin, g->r_node_idx, level, l - 1, B.sigma, B.delta, B.bc,
+            bc_heavy<false><<<heavy_grid, BCH_THREADS, 0, st>>>(g->r_begin, g->r_node_idx, level, l - 1, B.sigma, B.delta, B.bc,
                                                                B.heavy_list, B.heavy_count + 2 * l);
             launches += 2;
         }
@@ -226,7 +267,7 @@ static int comp_bc(gmc_graph* g, const int32_t* seeds, int32_t n_seeds, float* b
             const int want = marked ? l + 1 : -1;
             bc_level<true><<<level_grid(level_count[l]), BC_THREADS, 0, st>>>(g->begin, g->node_idx, level, B.order, lb[l], lb[l + 1], want,
                                                                               B.sigma, B.delta, B.bc, B.heavy_list, B.heavy_count + 2 * l + 1);
-            bc_heavy<true><<<heavy_grid, BC_THREADS, 0, st>>>(g->begin, g->node_idx, level, want, B.sigma, B.delta, B.bc, B.heavy_list,
+            bc_heavy<true><<<heavy_grid, BCH_THREADS, 0, st>>>(g->begin, g->node_idx, level, want, B.sigma, B.delta, B.bc, B.heavy_list,
                                                               B.heavy_count + 2 * l + 1);
             launches += 2;
         }
