@@ -12,7 +12,7 @@
 // (gm_cpp_gen_foreach.cc:163-175), visit_rv(v) walks the out-edge slots of v that save_child marked as down edges
 // (gm_bfs_template.h:496-524: an edge into level + 1, marked by the top-down expansion only), levels in ascending order forward (do_bfs_forward :69-271) and
 // descending order backward (do_bfs_reverse :273-312).  Here: the traversal is the device BFS (gmc_bfs.cu), the visited
-// vertices are bucketed by level once, then two launches per level and direction.  8 lanes own a vertex: they load 8
+// vertices are bucketed by level once, then two launches per level and direction.  A warp owns a vertex: it loads 32
 // edge slots at a time (coalesced ids, gathered levels and values) and every lane adds the matching terms in slot order
 // with __fadd_rn / __fdiv_rn / __fmul_rn -- the float sums are the reference's, term by term, whatever the degree; rows of
 // 1024 slots or more are handed to a second kernel (a CTA per row, matching terms compacted into shared memory in slot
@@ -22,6 +22,7 @@
 // UpNbrs sum; with the shipped bc.gm every sigma is 0 and delta is NaN wherever a vertex has a BFS child.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <vector>
 #include "gmc_common.cuh"
 
@@ -34,7 +35,7 @@ int gmc_bfs_levels_resident(gmc_graph* g, int32_t root, bool save_child, const i
 namespace {
 
 constexpr int BC_THREADS = 256;
-constexpr int BC_GROUP = 8;            // lanes per vertex in bc_level
+constexpr int BC_GROUP_DEFAULT = 32;   // lanes per vertex in bc_level (8 and 16 measured within 6 % on LJ-shaped: profiles/r1ag)
 constexpr int BC_HEAVY = 1024;         // rows with at least this many edge slots go to bc_heavy (a CTA per row)
 constexpr int BCH_THREADS = 1024;      // bc_heavy: threads per CTA (32 warps: the cross-warp scan is one warp wide)
 constexpr int BC_PER_THREAD = 8;       // bc_heavy: consecutive slots per thread and chunk
@@ -77,15 +78,14 @@ __device__ __forceinline__ void bc_store(int32_t v, float S, float* __restrict__
     else sigma[v] = S;                                           // v.sigma = Sum ...
 }
 
-// The callback of every vertex of one level (order[lo, hi)), 8 lanes per vertex (4 vertices per warp: most rows are short,
-// and a vertex is a chain of five dependent loads -- order, row offsets, ids, levels, values -- so what counts is how many
-// are in flight): 8 edge slots per step, the matching terms added in slot order by every lane of the group.  Rows of
-// BC_HEAVY slots or more are queued for bc_heavy instead.
-template <bool REV>
+// The callback of every vertex of one level (order[lo, hi)), BC_GROUP lanes per vertex (32 / BC_GROUP vertices per warp):
+// BC_GROUP edge slots per step, the matching terms added in slot order by every lane of the group.  Rows of heavy_min
+// slots or more are queued for bc_heavy instead.
+template <bool REV, int BC_GROUP>
 __global__ void __launch_bounds__(BC_THREADS)
 bc_level(const int32_t* __restrict__ row_begin, const int32_t* __restrict__ row_idx, const int16_t* __restrict__ level,
          const int32_t* __restrict__ order, int32_t lo, int32_t hi, int want, float* __restrict__ sigma, float* __restrict__ delta,
-         float* __restrict__ bc, int32_t* __restrict__ heavy_list, int32_t* __restrict__ heavy_count) {
+         float* __restrict__ bc, int32_t* __restrict__ heavy_list, int32_t* __restrict__ heavy_count, int32_t heavy_min) {
     const int lane = threadIdx.x & 31, gl = lane & (BC_GROUP - 1), grp = lane / BC_GROUP;
     constexpr int GPW = 32 / BC_GROUP;                       // groups per warp
     const int32_t nw = (gridDim.x * BC_THREADS) >> 5;
@@ -97,7 +97,7 @@ bc_level(const int32_t* __restrict__ row_begin, const int32_t* __restrict__ row_
             v = order[i];
             b = row_begin[v];
             e = row_begin[v + 1];
-            if (e - b >= BC_HEAVY) {
+            if (e - b >= heavy_min) {
                 if (gl == 0) heavy_list[atomicAdd(heavy_count, 1)] = v;
                 mine = false;
                 e = b;
@@ -113,7 +113,7 @@ bc_level(const int32_t* __restrict__ row_begin, const int32_t* __restrict__ row_
             float x = 0.0f;
             bool m = false;
             if (q < e) x = bc_term<REV>(ld_stream(row_idx + q), level, want, sigma, delta, sv, m);
-            unsigned gm = (__ballot_sync(FULLM, m) >> (grp * BC_GROUP)) & ((1u << BC_GROUP) - 1u);    // the group's matches
+            unsigned gm = (__ballot_sync(FULLM, m) >> (grp * BC_GROUP)) & (BC_GROUP == 32 ? FULLM : (1u << (BC_GROUP & 31)) - 1u);   // the group's matches
             while (__any_sync(FULLM, gm != 0u)) {            // slot order = the reference's loop order
                 const int j = gm ? __ffs(gm) - 1 : 0;
                 const float xj = __shfl_sync(FULLM, x, grp * BC_GROUP + j);
@@ -185,10 +185,18 @@ bc_heavy(const int32_t* __restrict__ row_begin, const int32_t* __restrict__ row_
     }
 }
 
-inline unsigned level_grid(int32_t count) {
-    const int64_t want = div_up((int64_t)count * BC_GROUP, (int64_t)BC_THREADS);
+inline unsigned level_grid(int32_t count, int group) {
+    const int64_t want = div_up((int64_t)count * group, (int64_t)BC_THREADS);
     const int64_t cap = (int64_t)sm_count() * 8;
     return (unsigned)(want < cap ? (want > 0 ? want : 1) : cap);
+}
+
+template <bool REV>
+void launch_level(int group, unsigned grid, cudaStream_t st, const int32_t* rb, const int32_t* ri, const int16_t* level, const int32_t* order,
+                  int32_t lo, int32_t hi, int want, float* sigma, float* delta, float* bc, int32_t* hl, int32_t* hc, int32_t heavy_min) {
+    if (group == 32) bc_level<REV, 32><<<grid, BC_THREADS, 0, st>>>(rb, ri, level, order, lo, hi, want, sigma, delta, bc, hl, hc, heavy_min);
+    else if (group == 16) bc_level<REV, 16><<<grid, BC_THREADS, 0, st>>>(rb, ri, level, order, lo, hi, want, sigma, delta, bc, hl, hc, heavy_min);
+    else bc_level<REV, 8><<<grid, BC_THREADS, 0, st>>>(rb, ri, level, order, lo, hi, want, sigma, delta, bc, hl, hc, heavy_min);
 }
 
 struct BcBuffers {
@@ -223,6 +231,10 @@ static int comp_bc(gmc_graph* g, const int32_t* seeds, int32_t n_seeds, float* b
     GMC_TRY(gmc_malloc((void**)&B.heavy_list, sizeof(int32_t) * n));
     GMC_TRY(gmc_malloc((void**)&B.heavy_count, sizeof(int32_t) * 2 * MAX_LEVELS));      // one counter per level and direction
     const unsigned heavy_grid = (unsigned)sm_count() * 2;
+    // experiment knobs (tools/bc_bench.py): lanes per vertex (8 | 16 | 32) and the row length from which bc_heavy takes over
+    int group = BC_GROUP_DEFAULT, heavy_min = BC_HEAVY;
+    if (const char* t = getenv("GMC_BC_GROUP")) { const int v = atoi(t); if (v == 8 || v == 16 || v == 32) group = v; }
+    if (const char* t = getenv("GMC_BC_HEAVY")) { const int v = atoi(t); if (v >= 32) heavy_min = v; }
     cudaEvent_t ev0, ev1;
     GMC_CUDA(cudaEventCreate(&ev0));
     GMC_CUDA(cudaEventCreate(&ev1));
@@ -254,8 +266,8 @@ static int comp_bc(gmc_graph* g, const int32_t* seeds, int32_t n_seeds, float* b
         bc_bucket<<<(unsigned)div_up(n, (size_t)BC_THREADS), BC_THREADS, 0, st>>>(level, g->N, B.level_begin, B.cursor, B.order);
         launches += 2;
         for (int32_t l = first_level; l < nl; l++) {
-            bc_level<false><<<level_grid(level_count[l]), BC_THREADS, 0, st>>>(g->r_begin, g->r_node_idx, level, B.order, lb[l], lb[l + 1],
-                                                                               l - 1, B.sigma, B.delta, B.bc, B.heavy_list, B.heavy_count + 2 * l);
+            launch_level<false>(group, level_grid(level_count[l], group), st, g->r_begin, g->r_node_idx, level, B.order, lb[l], lb[l + 1],
+                                l - 1, B.sigma, B.delta, B.bc, B.heavy_list, B.heavy_count + 2 * l, heavy_min);
             bc_heavy<false><<<heavy_grid, BCH_THREADS, 0, st>>>(g->r_begin, g->r_node_idx, level, l - 1, B.sigma, B.delta, B.bc,
                                                                B.heavy_list, B.heavy_count + 2 * l);
             launches += 2;
@@ -265,8 +277,8 @@ static int comp_bc(gmc_graph* g, const int32_t* seeds, int32_t n_seeds, float* b
             // (gm_bfs_template.h:689-708) does not mark them; its vertices get delta = 0 (level -1 matches nothing)
             const bool marked = state[l] != GMC_BFS_ST_RRD && state[l] != GMC_BFS_ST_RR2Q;
             const int want = marked ? l + 1 : -1;
-            bc_level<true><<<level_grid(level_count[l]), BC_THREADS, 0, st>>>(g->begin, g->node_idx, level, B.order, lb[l], lb[l + 1], want,
-                                                                              B.sigma, B.delta, B.bc, B.heavy_list, B.heavy_count + 2 * l + 1);
+            launch_level<true>(group, level_grid(level_count[l], group), st, g->begin, g->node_idx, level, B.order, lb[l], lb[l + 1], want,
+                               B.sigma, B.delta, B.bc, B.heavy_list, B.heavy_count + 2 * l + 1, heavy_min);
             bc_heavy<true><<<heavy_grid, BCH_THREADS, 0, st>>>(g->begin, g->node_idx, level, want, B.sigma, B.delta, B.bc, B.heavy_list,
                                                               B.heavy_count + 2 * l + 1);
             launches += 2;

@@ -108,11 +108,14 @@ class Oracle:
         sweeps = self.L.orc_hop_dist(N, begin, np.ascontiguousarray(node_idx), root, dist)
         return dist[:N], sweeps
 
-    def bfs_levels(self, begin, node_idx, r_begin, r_node_idx, root=0, has_reverse=True, cap=256):
+    def bfs_levels(self, begin, node_idx, r_begin, r_node_idx, root=0, has_reverse=True, cap=256, save_child=False):
         N = len(begin) - 1
         lev = np.zeros(max(N, 1), np.int16)
         trace = np.full(cap, -1, np.int32); cnt = np.zeros(cap, np.int32)
-        n = self.L.orc_bfs_levels(N, begin, np.ascontiguousarray(node_idx), r_begin, np.ascontiguousarray(r_node_idx),
+        fn = self.L.orc_bfs_levels_save_child if save_child else self.L.orc_bfs_levels
+        fn.argtypes = self.L.orc_bfs_levels.argtypes
+        fn.restype = self.L.orc_bfs_levels.restype
+        n = fn(N, begin, np.ascontiguousarray(node_idx), r_begin, np.ascontiguousarray(r_node_idx),
                                   int(has_reverse), root, lev, _opt(trace), _opt(cnt), cap)
         return lev[:N], n, trace[:min(n, cap)], cnt[:min(n, cap)]
 

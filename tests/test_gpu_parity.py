@@ -175,6 +175,10 @@ def test_bfs_rmat_roots(gm, oracle, g_rmat, root_kind):
     wlev, nl, wtrace, wcnt = oracle.bfs_levels(g_rmat["begin"], g_rmat["node_idx"], g_rmat["r_begin"], g_rmat["r_node_idx"], root)
     assert np.array_equal(lev, wlev)
     assert list(trace) == list(wtrace) and list(cnt) == list(wcnt)
+    # the state machine of a save_child instantiation (flag 2): same levels, no direct QUE / Q2R -> RRD switch
+    slev, _, strace, scnt = dg.bfs_levels(root, use_reverse_edge=2)
+    _, _, wstrace, _ = oracle.bfs_levels(g_rmat["begin"], g_rmat["node_idx"], g_rmat["r_begin"], g_rmat["r_node_idx"], root, save_child=True)
+    assert np.array_equal(slev, wlev) and list(scnt) == list(wcnt) and list(strace) == list(wstrace)
     # hop_dist and the BFS template agree: INT_MAX <-> -2
     assert np.array_equal(np.where(dist == INT_MAX, -2, dist).astype(np.int16), lev)
     assert info.reached == int((want != INT_MAX).sum())

@@ -20,6 +20,15 @@ for n, m in [(1000000, 16000000), (4850000, 69000000)]:
     out["runs"].append({"nodes": n, "edges": m, "seeds": len(seeds), "device_ms": round(ms, 3), "ms_per_seed": round(ms / len(seeds), 3),
                         "launches": info.launches, "max_levels": info.max_levels, "repeatable": bool(np.array_equal(bc, bc2, equal_nan=True)),
                         "bc_max": float(np.nanmax(bc)), "GTEPS_2M_per_seed": round(2 * m / (ms / len(seeds)) / 1e6, 1)})
+    if n == 4850000:      # where the time goes: the traversals alone (save_child state machine), then the knobs of the two callbacks' kernels
+        out["bfs_ms_8_seeds"] = round(sum(g.bfs_levels(sd, use_reverse_edge=2)[1].kernel_ms for sd in seeds), 3)
+        out["knobs"] = []
+        for grp, heavy in [(8, 1024), (32, 1024), (16, 1024), (8, 256), (8, 4096), (32, 256)]:
+            os.environ["GMC_BC_GROUP"] = str(grp); os.environ["GMC_BC_HEAVY"] = str(heavy)
+            t = min(g.comp_bc(seeds, adj=True)[1].device_ms for _ in range(2))
+            got = g.comp_bc(seeds, adj=True)[0]
+            out["knobs"].append({"group": grp, "heavy_min": heavy, "device_ms": round(t, 3), "same_bits": bool(np.array_equal(got, bc, equal_nan=True))})
+        os.environ.pop("GMC_BC_GROUP"); os.environ.pop("GMC_BC_HEAVY")
     if n == 1000000:
         o = Oracle()
         a = {k: g.array(k) for k in ("begin", "node_idx", "r_begin", "r_node_idx")}
