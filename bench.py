@@ -17,6 +17,7 @@ BASELINE.json configs[1] (4.85 M vertices, 69 M edges, int32 ids, fp64 ranks).
   cpu_baseline  the reference's own OpenMP code (oracle/_ref: reference gm_graph + the generated loop nest
             restated in oracle/ref_glue) on this box's host cores, bounded sample, rank 0 at N=1.
   bfs       extra: hop_dist / gm_bfs_template level-synchronous BFS GTEPS on the same graph (configs[2]).
+  extras    comp_BC (bc_adj.gm, 8 seeds) and triangle_counting on the same graph, device time.
 
 `--impl reference` times only the CPU reference arm (no GPU code of this repo on that path).
 N>1 (torchrun): destination-range shards, one process per GPU, weak scaling (the graph grows with N).
@@ -378,6 +379,18 @@ def run_single(args, n, m):
            "roots": len(roots), "ms_per_traversal": round(float(np.mean(bfs_ms)), 4),
            "edges_per_traversal": int(np.mean(bfs_edges)), "what": "hop_dist (direction-optimizing), device time"}
 
+    # ---- the other generated procedures on the same graph: comp_BC (bc_adj.gm) and triangle_counting ------
+    extras = {}
+    try:
+        _, bci = g.comp_bc(roots[:1], adj=True)                          # warm
+        _, bci = g.comp_bc(roots, adj=True)
+        extras["comp_bc"] = {"what": "gmc_comp_bc_adj, device time incl. the traversals", "seeds": len(roots),
+                             "ms_per_seed": round(bci.device_ms / len(roots), 3), "launches": int(bci.launches)}
+        tcount, tms = g.triangle_counting()
+        extras["triangle_counting"] = {"T": int(tcount), "device_ms": round(tms, 3)}
+    except Exception as ex:                                              # secondary figures: reported, never fatal to the line
+        extras["error"] = repr(ex)
+
     # ---- CPU baseline: the reference's own code on the host cores, bounded sample -------------------
     cpu = None
     parity = None
@@ -401,7 +414,7 @@ def run_single(args, n, m):
                    "l2": "inputs larger than L2 (index stream %d MB per sweep > 126 MB L2); no explicit flush" % (4 * m // 2**20),
                    "parallelism": "1 GPU"},
         "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
-        "bfs": bfs, "parity": parity,
+        "bfs": bfs, "extras": extras, "parity": parity,
     }
     emit(line)
 

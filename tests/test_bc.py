@@ -127,3 +127,24 @@ def test_bc_driver_unchanged(gm, oracle, tmp_path):
     assert len(got) == 4
     for k in range(4):
         assert (np.isnan(want[k]) and "nan" in got[k].lower()) or float(got[k]) == float("%0.9f" % want[k])
+
+
+@pytest.mark.gpu
+def test_bc_random_driver_unchanged(gm, oracle, tmp_path):
+    """apps/output_cpp/src/bc_random_main.cc, unchanged: bc_random(G, BC, 10), seeds = rand() % N from libc's default stream"""
+    import sys
+    g = graphs.rmat(oracle, 20000, 400000)
+    f = str(tmp_path / "r.bin")
+    assert oracle.store_binary(f, g["begin"], g["node_idx"])
+    r = subprocess.run([os.path.join(BIN, "bc_random"), f, "4", "/dev/null"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "bc_random: seeds=10" in r.stdout
+    draws = subprocess.run([sys.executable, "-c", "import ctypes; L = ctypes.CDLL('libc.so.6'); print(*[L.rand() for _ in range(10)])"],
+                           capture_output=True, text=True, timeout=60)
+    seeds = [int(x) % g["N"] for x in draws.stdout.split()]
+    assert len(seeds) == 10
+    want = oracle.comp_bc(g["begin"], g["node_idx"], g["r_begin"], g["r_node_idx"], seeds)
+    got = re.findall(r"BC\[\d\] = (\S+)", r.stdout)
+    assert len(got) == 4
+    for k in range(4):
+        assert (np.isnan(want[k]) and "nan" in got[k].lower()) or float(got[k]) == float("%0.9f" % want[k])
