@@ -77,9 +77,45 @@ def triangle_counts():
     print("triangle counts", tc)
 
 
+def bc_golden():
+    """bc_golden.npz: comp_BC as generated from apps/src/bc.gm and apps/src/bc_adj.gm (oracle/ref_glue/ref_capi.cc: the
+    generated gm_bfs_template<short, true, false, false, true> subclass over the reference's REAL template), ONE host
+    thread (the reference's down-edge marking races with several), on the two full fixtures written by main().  Both graphs
+    are large enough for the traversal to reach the bottom-up states, whose levels carry no down edges."""
+    ref = Ref()
+    ref.set_threads(1)
+    out = {}
+    for name in ("rmat4096", "uniform2000"):
+        z = np.load(os.path.join(HERE, name + ".npz"))
+        g = ref.from_csr(z["begin"], z["node_idx"])
+        deg = np.diff(z["begin"])
+        nz = np.nonzero(deg)[0]
+        seeds = np.array([int(nz[0]), int(nz[len(nz) // 2]), int(deg.argmax()), 1, int(nz[0])], np.int32)
+        out[name + "_seeds"] = seeds
+        out[name + "_bc"] = ref.comp_bc(g, seeds)
+        out[name + "_bc_adj"] = ref.comp_bc(g, seeds, adj=True)
+        ref.free(g)
+    # (3) the reference's create_RMAT_graph(5000, 60000, seed 3): from vertex 18 the save_child traversal expands level 4 (332
+    # vertices with children) bottom-up.  The graph is not stored: the oracle's generator reproduces it (checked by the digest)
+    g = ref.rmat(5000, 60000, 3)
+    a = ref.arrays(g)
+    seeds = np.array([18, 0, 7], np.int32)
+    out["rmat5000_params"] = np.array([5000, 60000, 3], np.int64)
+    out["rmat5000_csr_sha"] = sha(np.concatenate([a["begin"], a["node_idx"], a["r_begin"], a["r_node_idx"]]))
+    out["rmat5000_seeds"] = seeds
+    out["rmat5000_bc"] = ref.comp_bc(g, seeds)
+    out["rmat5000_bc_adj"] = ref.comp_bc(g, seeds, adj=True)
+    ref.free(g)
+    np.savez_compressed(os.path.join(HERE, "bc_golden.npz"), **out)
+    print("bc golden:", {k: (v.shape, int(np.isnan(v).sum())) for k, v in out.items() if k.endswith("_bc") or k.endswith("_bc_adj")})
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "triangles":
         triangle_counts()
+    elif len(sys.argv) > 1 and sys.argv[1] == "bc":
+        bc_golden()
     else:
         main()
         triangle_counts()
+        bc_golden()

@@ -44,6 +44,35 @@ def test_oracle_matches_reference_bfs_template(oracle, ref):
     ref.set_threads(min(8, os.cpu_count() or 1))
 
 
+def golden_bc_case(oracle, name):
+    gold = os.path.join(ROOT, "tests", "golden")
+    b = np.load(os.path.join(gold, "bc_golden.npz"))
+    if name == "rmat5000":      # not stored: the oracle's generator reproduces the reference's graph, pinned by a digest
+        import hashlib
+        n, m, seed = (int(x) for x in b["rmat5000_params"])
+        z = graphs.rmat(oracle, n, m, seed=seed)
+        cat = np.concatenate([z["begin"], z["node_idx"], z["r_begin"], z["r_node_idx"]])
+        assert hashlib.sha256(np.ascontiguousarray(cat).tobytes()).hexdigest() == str(b["rmat5000_csr_sha"])
+    else:
+        z = np.load(os.path.join(gold, name + ".npz"))
+    return z, b
+
+
+@pytest.mark.parametrize("name", ["rmat4096", "uniform2000", "rmat5000"])
+def test_oracle_matches_golden(oracle, name):
+    """tests/golden/bc_golden.npz (make_golden.py bc): the reference's own template, single thread; travels to the GPU box"""
+    z, b = golden_bc_case(oracle, name)
+    seeds = b[name + "_seeds"]
+    for adj, key in ((False, "_bc"), (True, "_bc_adj")):
+        got = oracle.comp_bc(z["begin"], z["node_idx"], z["r_begin"], z["r_node_idx"], seeds, adj=adj)
+        assert same(got, b[name + key])
+    assert not np.isnan(b[name + "_bc_adj"]).any() and (b[name + "_bc_adj"] > 0).any()
+    if name == "rmat5000":
+        # this case exercises the unmarked bottom-up levels: the save_child traversal from seeds[0] expands an inner level in RRD
+        _, _, trace, cnt = oracle.bfs_levels(z["begin"], z["node_idx"], z["r_begin"], z["r_node_idx"], int(seeds[0]), save_child=True)
+        assert 5 in list(trace)[:-1]
+
+
 def test_oracle_tiny(oracle):
     # path 0 -> 1 -> 2: from seed 0 the inner vertices (0, 1) have a child -> NaN, the leaf 2 stays 0
     g = graphs.from_edges(oracle, 4, [(0, 1), (1, 2)])
