@@ -98,7 +98,7 @@ bc_level(const int32_t* __restrict__ row_begin, const int32_t* __restrict__ row_
             b = row_begin[v];
             e = row_begin[v + 1];
             if (e - b >= heavy_min) {
-                if (gl == 0) heavy_list[atomicAdd(heavy_count, 1)] = v;
+                if (gl == 0 && heavy_count) heavy_list[atomicAdd(heavy_count, 1)] = v;      // NULL: the long rows are already listed
                 mine = false;
                 e = b;
             }
@@ -134,13 +134,14 @@ template <bool REV>
 __global__ void __launch_bounds__(BCH_THREADS)
 bc_heavy(const int32_t* __restrict__ row_begin, const int32_t* __restrict__ row_idx, const int16_t* __restrict__ level, int want,
          float* __restrict__ sigma, float* __restrict__ delta, float* __restrict__ bc, const int32_t* __restrict__ heavy_list,
-         const int32_t* __restrict__ heavy_count) {
+         const int32_t* __restrict__ heavy_count, int only_level) {
     __shared__ __align__(16) float xs[BC_CHUNK + 4];
     __shared__ int32_t wsum[BCH_THREADS / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int32_t n = *heavy_count;
     for (int32_t h = blockIdx.x; h < n; h += gridDim.x) {
         const int32_t v = heavy_list[h];
+        if (only_level >= 0 && (int)level[v] != only_level) continue;      // list of the long rows of all levels (overlap mode)
         const int32_t b = row_begin[v], e = row_begin[v + 1];
         const float sv = REV ? sigma[v] : 0.0f;
         float S = 0.0f;
@@ -191,6 +192,15 @@ inline unsigned level_grid(int32_t count, int group) {
     return (unsigned)(want < cap ? (want > 0 ? want : 1) : cap);
 }
 
+// overlap mode: the long rows by direction (in-degree for visit_fw, out-degree for visit_rv), once per call
+__global__ void bc_classify(const int32_t* __restrict__ begin, const int32_t* __restrict__ r_begin, int32_t n, int32_t heavy_min,
+                            int32_t* __restrict__ fw_list, int32_t* __restrict__ rv_list, int32_t* __restrict__ counts) {
+    const int32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= n) return;
+    if (r_begin[v + 1] - r_begin[v] >= heavy_min) fw_list[atomicAdd(&counts[0], 1)] = v;
+    if (begin[v + 1] - begin[v] >= heavy_min) rv_list[atomicAdd(&counts[1], 1)] = v;
+}
+
 template <bool REV>
 void launch_level(int group, unsigned grid, cudaStream_t st, const int32_t* rb, const int32_t* ri, const int16_t* level, const int32_t* order,
                   int32_t lo, int32_t hi, int want, float* sigma, float* delta, float* bc, int32_t* hl, int32_t* hc, int32_t heavy_min) {
@@ -202,9 +212,16 @@ void launch_level(int group, unsigned grid, cudaStream_t st, const int32_t* rb, 
 struct BcBuffers {
     float *bc = nullptr, *sigma = nullptr, *delta = nullptr;
     int32_t *order = nullptr, *level_begin = nullptr, *cursor = nullptr, *heavy_list = nullptr, *heavy_count = nullptr;
+    int32_t *rv_list = nullptr, *cls_count = nullptr;       // overlap mode
+    cudaStream_t s1 = nullptr, s2 = nullptr;
+    cudaEvent_t join = nullptr, heavy_done = nullptr;
     ~BcBuffers() {
         cudaFree(bc); cudaFree(sigma); cudaFree(delta); cudaFree(order); cudaFree(level_begin); cudaFree(cursor);
-        cudaFree(heavy_list); cudaFree(heavy_count);
+        cudaFree(heavy_list); cudaFree(heavy_count); cudaFree(rv_list); cudaFree(cls_count);
+        if (join) cudaEventDestroy(join);
+        if (heavy_done) cudaEventDestroy(heavy_done);
+        if (s1) cudaStreamDestroy(s1);
+        if (s2) cudaStreamDestroy(s2);
     }
 };
 
@@ -235,13 +252,54 @@ static int comp_bc(gmc_graph* g, const int32_t* seeds, int32_t n_seeds, float* b
     int group = BC_GROUP_DEFAULT, heavy_min = BC_HEAVY;
     if (const char* t = getenv("GMC_BC_GROUP")) { const int v = atoi(t); if (v == 8 || v == 16 || v == 32) group = v; }
     if (const char* t = getenv("GMC_BC_HEAVY")) { const int v = atoi(t); if (v >= 32) heavy_min = v; }
+    // GMC_BC_OVERLAP=1 (experimental, not yet measured): the long rows are listed once per call by degree, and bc_level /
+    // bc_heavy of a level -- independent of each other -- run on two streams that join after every level
+    const bool overlap = getenv("GMC_BC_OVERLAP") != nullptr && atoi(getenv("GMC_BC_OVERLAP")) != 0;
+    if (overlap) {
+        GMC_CUDA(cudaStreamCreateWithFlags(&B.s1, cudaStreamNonBlocking));
+        GMC_CUDA(cudaStreamCreateWithFlags(&B.s2, cudaStreamNonBlocking));
+        GMC_CUDA(cudaEventCreateWithFlags(&B.join, cudaEventDisableTiming));
+        GMC_CUDA(cudaEventCreateWithFlags(&B.heavy_done, cudaEventDisableTiming));
+        GMC_TRY(gmc_malloc((void**)&B.rv_list, sizeof(int32_t) * n));
+        GMC_TRY(gmc_malloc((void**)&B.cls_count, sizeof(int32_t) * 2));
+        st = B.s1;
+    }
+    std::vector<int32_t> lb;                          // level offsets of the current seed
+    const int16_t* level_cur = nullptr;               // ... its levels and level counts (run_level reads them)
+    const int32_t* level_count_cur = nullptr;
     cudaEvent_t ev0, ev1;
     GMC_CUDA(cudaEventCreate(&ev0));
     GMC_CUDA(cudaEventCreate(&ev1));
     GMC_CUDA(cudaEventRecord(ev0, st));
     GMC_CUDA(cudaMemsetAsync(B.bc, 0, sizeof(float) * n, st));
     int32_t launches = 0, max_levels = 0;
-    std::vector<int32_t> lb;
+    if (overlap) {
+        GMC_CUDA(cudaMemsetAsync(B.cls_count, 0, sizeof(int32_t) * 2, st));
+        bc_classify<<<(unsigned)div_up(n, (size_t)BC_THREADS), BC_THREADS, 0, st>>>(g->begin, g->r_begin, g->N, heavy_min, B.heavy_list,
+                                                                                   B.rv_list, B.cls_count);
+        launches++;
+    }
+    // one level of one direction: the short rows on `st`; the long rows behind them (default) or beside them (overlap)
+    auto run_level = [&](bool rev, int32_t l, int want) -> bool {
+        const int32_t* rb = rev ? g->begin : g->r_begin;
+        const int32_t* ri = rev ? g->node_idx : g->r_node_idx;
+        const unsigned grid = level_grid(level_count_cur[l], group);
+        int32_t* queue_count = overlap ? nullptr : B.heavy_count + 2 * l + (rev ? 1 : 0);
+        const int32_t* list = overlap ? (rev ? B.rv_list : B.heavy_list) : B.heavy_list;
+        const int32_t* list_count = overlap ? B.cls_count + (rev ? 1 : 0) : queue_count;
+        cudaStream_t hs = st;
+        if (overlap) {
+            hs = B.s2;
+            if (cudaEventRecord(B.join, st) != cudaSuccess || cudaStreamWaitEvent(hs, B.join, 0) != cudaSuccess) return false;
+        }
+        if (rev) launch_level<true>(group, grid, st, rb, ri, level_cur, B.order, lb[l], lb[l + 1], want, B.sigma, B.delta, B.bc, B.heavy_list, queue_count, heavy_min);
+        else launch_level<false>(group, grid, st, rb, ri, level_cur, B.order, lb[l], lb[l + 1], want, B.sigma, B.delta, B.bc, B.heavy_list, queue_count, heavy_min);
+        if (rev) bc_heavy<true><<<heavy_grid, BCH_THREADS, 0, hs>>>(rb, ri, level_cur, want, B.sigma, B.delta, B.bc, list, list_count, overlap ? l : -1);
+        else bc_heavy<false><<<heavy_grid, BCH_THREADS, 0, hs>>>(rb, ri, level_cur, want, B.sigma, B.delta, B.bc, list, list_count, overlap ? l : -1);
+        if (overlap && (cudaEventRecord(B.heavy_done, hs) != cudaSuccess || cudaStreamWaitEvent(st, B.heavy_done, 0) != cudaSuccess)) return false;
+        launches += 2;
+        return true;
+    };
     int rc = GMC_OK;
     for (int32_t k = 0; k < n_seeds && rc == GMC_OK; k++) {
         const int16_t* level = nullptr;
@@ -250,6 +308,8 @@ static int comp_bc(gmc_graph* g, const int32_t* seeds, int32_t n_seeds, float* b
         rc = gmc_bfs_levels_resident(g, seeds[k], true, &level, &level_count, &state, &nl, &bfs_launches, st);
         if (rc != GMC_OK) break;
         launches += bfs_launches;
+        level_cur = level;
+        level_count_cur = level_count;
         if (nl > max_levels) max_levels = nl;
         lb.assign((size_t)nl + 1, 0);
         for (int32_t l = 0; l < nl; l++) lb[l + 1] = lb[l] + level_count[l];
@@ -265,24 +325,15 @@ static int comp_bc(gmc_graph* g, const int32_t* seeds, int32_t n_seeds, float* b
         bc_seed<<<1, 1, 0, st>>>(B.sigma, seeds[k]);
         bc_bucket<<<(unsigned)div_up(n, (size_t)BC_THREADS), BC_THREADS, 0, st>>>(level, g->N, B.level_begin, B.cursor, B.order);
         launches += 2;
-        for (int32_t l = first_level; l < nl; l++) {
-            launch_level<false>(group, level_grid(level_count[l], group), st, g->r_begin, g->r_node_idx, level, B.order, lb[l], lb[l + 1],
-                                l - 1, B.sigma, B.delta, B.bc, B.heavy_list, B.heavy_count + 2 * l, heavy_min);
-            bc_heavy<false><<<heavy_grid, BCH_THREADS, 0, st>>>(g->r_begin, g->r_node_idx, level, l - 1, B.sigma, B.delta, B.bc,
-                                                               B.heavy_list, B.heavy_count + 2 * l);
-            launches += 2;
-        }
-        for (int32_t l = nl - 1; l >= first_level; l--) {
+        bool ok = true;
+        for (int32_t l = first_level; l < nl && ok; l++) ok = run_level(false, l, l - 1);
+        for (int32_t l = nl - 1; l >= first_level && ok; l--) {
             // a level the traversal expanded bottom-up has no down edges in the reference: check_parent_rrd
             // (gm_bfs_template.h:689-708) does not mark them; its vertices get delta = 0 (level -1 matches nothing)
             const bool marked = state[l] != GMC_BFS_ST_RRD && state[l] != GMC_BFS_ST_RR2Q;
-            const int want = marked ? l + 1 : -1;
-            launch_level<true>(group, level_grid(level_count[l], group), st, g->begin, g->node_idx, level, B.order, lb[l], lb[l + 1], want,
-                               B.sigma, B.delta, B.bc, B.heavy_list, B.heavy_count + 2 * l + 1, heavy_min);
-            bc_heavy<true><<<heavy_grid, BCH_THREADS, 0, st>>>(g->begin, g->node_idx, level, want, B.sigma, B.delta, B.bc, B.heavy_list,
-                                                              B.heavy_count + 2 * l + 1);
-            launches += 2;
+            ok = run_level(true, l, marked ? l + 1 : -1);
         }
+        if (!ok) { set_error("gmc_comp_bc: %s", cudaGetErrorString(cudaGetLastError())); rc = GMC_ERR_CUDA; break; }
         cudaError_t ce = cudaGetLastError();
         if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);           // lb is rewritten for the next seed
         if (ce != cudaSuccess) { set_error("gmc_comp_bc: %s", cudaGetErrorString(ce)); rc = GMC_ERR_CUDA; }
