@@ -179,6 +179,55 @@ def cpu_reference(begin, node_idx, iters_sample, steps=1, warmup=0, threads=None
     return dict(value=m * iters_sample / ms / 1e6, ms_per_step=ms, kind=kind, cores=threads, rank=rank)
 
 
+def cpu_reference_bfs(host, roots, gpu_dists, g, n_ref_roots):
+    """BFS CPU baseline + LJ-size parity.  Times the reference's hop_dist (apps/src/hop_dist.gm, generated loop nest
+    restated in oracle/ref_glue over the reference gm_graph) and its gm_bfs_template<short,true,false,false,false>
+    (inc/gm_bfs_template.h, the reference header itself) on `n_ref_roots` of the timed roots, all host threads;
+    checks the device dist[] of EVERY timed root bit for bit against the CPU result (reference for the sampled roots,
+    the plain-C oracle port for the rest) and the device gm_bfs_template levels against the reference's."""
+    from oracle_lib import Oracle, Ref, have_ref
+    threads = os.cpu_count() or 1
+    begin, node_idx = host["begin"], host["node_idx"]
+    deg = np.diff(begin).astype(np.int64)
+    orc = Oracle(); orc.set_threads(threads)
+    checked, mismatches, lev_checked, lev_mismatch = 0, 0, 0, 0
+    hop_ms, hop_edges, tpl_ms, tpl_edges = [], [], [], []
+    kind = "port"
+    ref = g_ref = None
+    if have_ref():
+        ref = Ref(); ref.set_threads(threads)
+        g_ref = ref.from_csr(begin, node_idx)
+        kind = "reference"
+    for k, r in enumerate(roots):
+        if k < n_ref_roots and ref is not None:
+            want, ms = ref.hop_dist(g_ref, r)
+            hop_ms.append(ms); hop_edges.append(int(deg[want != np.iinfo(np.int32).max].sum()))
+            lev, _, ms2 = ref.bfs_levels(g_ref, r)
+            tpl_ms.append(ms2); tpl_edges.append(hop_edges[-1])
+            glev, _, _, _ = g.bfs_levels(r)
+            lev_checked += 1; lev_mismatch += int(not np.array_equal(glev, lev))
+        else:
+            t = time.perf_counter()
+            want, _ = orc.hop_dist(begin, node_idx, r)
+            if k < n_ref_roots:
+                hop_ms.append((time.perf_counter() - t) * 1e3); hop_edges.append(int(deg[want != np.iinfo(np.int32).max].sum()))
+        checked += 1
+        mismatches += int(not np.array_equal(want, gpu_dists[r]))
+    if ref is not None:
+        ref.free(g_ref)
+    cpu = {"value": round(sum(hop_edges) / sum(hop_ms) / 1e6, 4), "unit": "GTEPS", "cores": threads, "kind": kind,
+           "sample": f"hop_dist on {len(hop_ms)} of the {len(roots)} timed roots, same CSR, all host threads; {np.mean(hop_ms):.1f} ms per traversal",
+           "ms_per_traversal": round(float(np.mean(hop_ms)), 2)}
+    if tpl_ms:
+        cpu["bfs_template"] = {"value": round(sum(tpl_edges) / sum(tpl_ms) / 1e6, 4), "unit": "GTEPS",
+                               "ms_per_traversal": round(float(np.mean(tpl_ms)), 2),
+                               "what": "reference gm_bfs_template<short,true,false,false,false>::do_bfs_forward, same roots"}
+    parity = {"dist_roots_checked": checked, "dist_roots_mismatching": mismatches, "bit_exact": mismatches == 0 and lev_mismatch == 0,
+              "template_levels_checked": lev_checked, "template_levels_mismatching": lev_mismatch,
+              "against": "reference hop_dist / gm_bfs_template for the sampled roots, oracle port (orc_hop_dist) for the others"}
+    return cpu, parity
+
+
 def run_reference_arm(args, n, m):
     """bench.py --impl reference: nothing of libgm_cuda on this path.  The graph comes from the
     reference's own R-MAT generator (create_RMAT_graph, graph_gen.cc:159-287); each step is a bounded
@@ -204,9 +253,25 @@ def run_reference_arm(args, n, m):
             _, ms = ref.pagerank(g, 1e-30, 0.85, iters)
             if k >= args.warmup:
                 times.append(ms)
+        # BFS (configs[2]/[4]) on the same graph: the reference's hop_dist and gm_bfs_template, a few roots
+        arr = ref.arrays(g)
+        deg = np.diff(arr["begin"]).astype(np.int64)
+        nz = np.nonzero(deg)[0]
+        broots = [int(nz[0])] + [int(r) for r in np.random.RandomState(1997).choice(nz, size=max(0, args.cpu_bfs_roots - 1), replace=False)]
+        hop_ms, hop_e, tpl_ms = [], [], []
+        for r in broots:
+            dist, ms_h = ref.hop_dist(g, r)
+            hop_ms.append(ms_h); hop_e.append(int(deg[dist != np.iinfo(np.int32).max].sum()))
+            _, _, ms_t = ref.bfs_levels(g, r)
+            tpl_ms.append(ms_t)
+        bfs_ref = {"metric": "bfs_gteps", "value": round(sum(hop_e) / sum(hop_ms) / 1e6, 4), "unit": "GTEPS", "roots": len(broots),
+                   "ms_per_traversal": round(float(np.mean(hop_ms)), 2), "what": "reference hop_dist, all host threads",
+                   "bfs_template": {"value": round(sum(hop_e) / sum(tpl_ms) / 1e6, 4), "unit": "GTEPS", "ms_per_traversal": round(float(np.mean(tpl_ms)), 2)}}
+        del arr, deg, nz
         ref.free(g)
         kind = "reference"
     else:
+        bfs_ref = None
         orc = Oracle(); orc.set_threads(threads)
         b, i = orc.rmat(n, m, RMAT["seed"], RMAT["a"], RMAT["b"], RMAT["c"], RMAT["permute"])
         i = np.ascontiguousarray(i).copy()
@@ -234,6 +299,7 @@ def run_reference_arm(args, n, m):
                    "graph": "reference create_RMAT_graph seed 1997 a=.57 b=.19 c=.19 permuted", "generate_s": round(gen_s, 1)},
         "cpu_baseline": {"value": v, "unit": "GTEPS", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "GTEPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "bfs": bfs_ref,
     }
     emit(line)
 
@@ -365,19 +431,36 @@ def run_single(args, n, m):
         sys.stderr.write("e2e parts: %r\n" % ({k: [round(x, 1) for x in v] for k, v in parts.items()},))
     assert np.array_equal(rank_host, rank_gpu), "e2e result differs from the resident-graph result"
 
-    # ---- BFS (configs[2]) on the same graph: hop_dist over several roots -------------------------
+    # ---- BFS (configs[2]) on the same graph: hop_dist over 16 roots + the gm_bfs_template traversal ------
     deg = np.diff(host["begin"])
     rs = np.random.RandomState(1997)
-    roots = [int(np.nonzero(deg)[0][0])] + [int(r) for r in rs.choice(np.nonzero(deg)[0], size=7, replace=False)]
+    roots = [int(np.nonzero(deg)[0][0])] + [int(r) for r in rs.choice(np.nonzero(deg)[0], size=15, replace=False)]
     dist_dev = torch.empty(n, dtype=torch.int32, device="cuda")
-    bfs_ms, bfs_edges, bfs_launches = [], [], 0
+    bfs_ms, bfs_edges, bfs_launches, bfs_abytes, bfs_dists = [], [], 0, [], {}
     for r in roots:
         g.hop_dist_dev(dist_dev.data_ptr(), r, stream=sp)           # warm
         bi = g.hop_dist_dev(dist_dev.data_ptr(), r, stream=sp)
         bfs_ms.append(bi.kernel_ms); bfs_edges.append(bi.edges_traversed); bfs_launches += bi.launches
+        # A_BFS = 4*M_r + N_r*(4 + sizeof(level)) + 2*ceil(N/8)*L   (level = int32 dist for hop_dist)
+        bfs_abytes.append(4 * bi.edges_traversed + bi.reached * 8 + 2 * ((n + 7) // 8) * bi.levels)
+        bfs_dists[r] = dist_dev.cpu().numpy()
+    a_bfs = float(np.sum(bfs_abytes)) / float(np.sum(bfs_ms)) / 1e6
     bfs = {"metric": "bfs_gteps", "value": round(sum(bfs_edges) / sum(bfs_ms) / 1e6, 3), "unit": "GTEPS",
            "roots": len(roots), "ms_per_traversal": round(float(np.mean(bfs_ms)), 4),
-           "edges_per_traversal": int(np.mean(bfs_edges)), "what": "hop_dist (direction-optimizing), device time"}
+           "edges_per_traversal": int(np.mean(bfs_edges)), "what": "hop_dist (direction-optimizing), device time",
+           "gpu_launches": int(bfs_launches),
+           "roofline": {"bound": "hbm", "achieved": round(a_bfs, 1), "peak": peak, "unit": "GB/s", "frac": round(a_bfs / peak, 4),
+                        "traffic": None, "peak_kind": peak_kind, "kernel": "whole traversal (td_prepare/td_expand/bu_scan/bfs_finish per level)",
+                        "alg_bytes_per_traversal": int(np.mean(bfs_abytes)),
+                        "formula": "A_BFS = 4*M_r + N_r*(4+4) + 2*ceil(N/8)*L over the traversal's device time"}}
+    # gm_bfs_template<short,...> traversal (bc / kosaraju's InBFS) on the first 4 roots
+    tl_ms, tl_edges = [], []
+    for r in roots[:4]:
+        g.bfs_levels(r)
+        _, li, _, _ = g.bfs_levels(r)
+        tl_ms.append(li.kernel_ms); tl_edges.append(li.edges_traversed)
+    bfs["bfs_template"] = {"value": round(sum(tl_edges) / sum(tl_ms) / 1e6, 3), "unit": "GTEPS", "roots": len(tl_ms),
+                           "ms_per_traversal": round(float(np.mean(tl_ms)), 4), "what": "gmc_bfs_levels (gm_bfs_template<short> levels), device time"}
 
     # ---- the other generated procedures on the same graph: comp_BC (bc_adj.gm) and triangle_counting ------
     extras = {}
@@ -403,6 +486,7 @@ def run_single(args, n, m):
         rk, _ = g.pagerank(1e-30, 0.85, args.cpu_iters)
         parity = {"max_abs_err_vs_cpu_reference": float(np.abs(rk - c["rank"]).max()), "iterations": args.cpu_iters,
                   "tolerance": 1e-9}
+        bfs["cpu_baseline"], bfs["parity"] = cpu_reference_bfs(host, roots, bfs_dists, g, args.cpu_bfs_roots)
 
     line = {
         "metric": "pagerank_gteps", "value": round(value, 3), "unit": "GTEPS", "n_gpus": 1, "steps": args.steps,
@@ -431,7 +515,8 @@ def main():
     ap.add_argument("--edges", type=int, default=None, help="override the workload's edge count (experiments)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--iters", type=int, default=20, help="pull sweeps per pagerank() call (BASELINE configs: 20)")
-    ap.add_argument("--cpu-iters", type=int, default=5, help="sweeps per CPU-reference sample")
+    ap.add_argument("--cpu-iters", type=int, default=20, help="sweeps per CPU-reference sample (the config's 20: one full pagerank() call)")
+    ap.add_argument("--cpu-bfs-roots", type=int, default=3, help="roots on which the reference's hop_dist / gm_bfs_template are timed")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     capture_stdout()

@@ -42,7 +42,14 @@
 
 using namespace gmc;
 
-constexpr int PR_THREADS = 1024;          // one CTA per SM, 32 independent warps
+#ifndef GMC_PR_THREADS
+#define GMC_PR_THREADS 1024
+#endif
+#ifndef GMC_PR_CTAS
+#define GMC_PR_CTAS 1
+#endif
+constexpr int PR_THREADS = GMC_PR_THREADS;    // one CTA per SM, 32 independent warps (experiment builds: 512, 1 or 2 CTAs per SM)
+constexpr int PR_CTAS = GMC_PR_CTAS;
 constexpr int PR_WARPS = PR_THREADS / 32;
 constexpr int S_MAX = 512;                // rows up to this in-degree are summed sequentially, one lane per row (bit-exact)
 constexpr int LT = 2048;                  // entries per long-row task, default (16 warp steps of 128); power of two
@@ -201,7 +208,11 @@ __device__ __forceinline__ double gather(const double* hot, const SweepArgs& A, 
 #ifdef GMC_EXPERIMENT
     if (A.mode & 1) w &= 16383;
 #endif
+#ifdef GMC_COLD_LDG
     return (w < A.hot_n) ? hot[w] : __ldg(A.contrib_in + w);
+#else
+    return (w < A.hot_n) ? hot[w] : __ldcg(A.contrib_in + w);    // cold gathers bypass L1 (see HOT_CAP)
+#endif
 }
 
 // new contribution of vertex id: local copy + one copy per peer (fire-and-forget NVLink stores, coalesced across lanes)
@@ -423,7 +434,7 @@ __device__ __forceinline__ void zero_task(const SweepArgs& A, int lane, int32_t 
     if (lane == 0) A.diff_parts[A.n_ltasks + A.n_stasks + z] = diff;
 }
 
-__global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
+__global__ void __launch_bounds__(PR_THREADS, PR_CTAS) pr_sweep(const SweepArgs A) {
     extern __shared__ __align__(16) double hot[];
     __shared__ __align__(8) unsigned long long bar;
     __shared__ double s_red[PR_WARPS];
@@ -482,7 +493,7 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
     if (lane == 0) s_red[warp] = v;
     __syncthreads();
     if (warp == 0) {
-        double t = butterfly(s_red[lane]);
+        double t = butterfly(lane < PR_WARPS ? s_red[lane] : 0.0);
         if (lane == 0) { A.ctrl->arrived = 0u; A.ctrl->next = 0u; }
         if (lane == 0 && A.diff_slot) {
             *A.diff_slot = t;
@@ -967,7 +978,7 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
         for (int k = 0; k < 2; k++) PLAN_TRY(gmc_malloc((void**)&p->rank[k], 8 * (nn + 4)));
         PLAN_TRY(gmc_malloc((void**)&p->ctrl, sizeof(gmc_pr_ctrl)));
     }
-    p->grid = sm_count();
+    p->grid = sm_count() * PR_CTAS;
     p->smem = (size_t)HOT_CAP * 8;
     PLAN_CUDA(cudaFuncSetAttribute(pr_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem));
     PLAN_CUDA(cudaStreamSynchronize(st));
