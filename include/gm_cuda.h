@@ -128,13 +128,25 @@ int gmc_pagerank_time_sweeps(gmc_graph* g, double d, int32_t warmup, int32_t n, 
 
 /* layout facts of the PageRank plan (relabelled entry array, tasks), for tests and reports */
 typedef struct {
-    int32_t n_long;         /* rows with in-degree > 64 (row-major, padded to 4 entries) */
+    int32_t n_long;         /* rows with in-degree > 512 (row-major, padded to 4 entries) */
     int32_t hot_n;          /* contributions staged in shared memory per CTA (dummy vertex included) */
-    int32_t n_slices;       /* sliced-ELL slices (32 rows each) of the rows with in-degree <= 64 */
+    int32_t n_slices;       /* sliced-ELL slices (32 rows each) of the rows with in-degree <= 512 */
     int32_t long_entries;   /* entries of the long-row section (edges + padding) */
     int32_t total_entries;  /* entries of the whole array */
     int32_t n_long_tasks, n_short_tasks;
     int32_t grid, threads, smem_bytes;
+    /* tiered layout (green-marl_b200/csrc/gmc_pr_plan.h) */
+    int32_t n_pos;          /* rows with in-edges: the rows a steady-state sweep processes */
+    int32_t n_src;          /* vertices with out-edges: the contributions a sweep can gather */
+    int32_t tiers;          /* warm source tiers (entry streams beside the home stream) */
+    int32_t segments;       /* (row, tier) segments = part slots beyond the home parts */
+    int32_t split_rows;     /* rows with at least one segment (finished by pr_combine) */
+    int32_t part_slots;
+    int32_t tier_ctas;      /* CTAs that start in a tier stream */
+    int32_t home_entries;   /* entry slots of the home stream */
+    int64_t hot0_entries;   /* gathers of the home stream served by tier 0 (shared memory) */
+    int64_t cold_entries;   /* gathers of the home stream that go to L2 */
+    int64_t segment_entries;/* entry slots of the tier streams (shared-memory gathers) */
 } gmc_pagerank_plan_info_t;
 int gmc_pagerank_plan_info(gmc_graph* g, gmc_pagerank_plan_info_t* out);
 

@@ -330,3 +330,41 @@ def test_pull_only_graph(gm, oracle, g_c1):
         dg.hop_dist(0)
     with pytest.raises(load_package().GmcError):
         dg.array("node_idx")
+
+
+@pytest.mark.parametrize("tiers,kmin,big", [(16, 3, "0"), (31, 1, "0"), (3, 2, "1"), (16, 6, "1")])
+def test_pagerank_tiered_streams(gm, oracle, g_rmat, tiers, kmin, big, monkeypatch):
+    """the tiered layout (gmc_pr_plan.h) forced onto the 200 K / 3 M graph: (row, tier) segments in their own entry streams,
+    partial sums through the part slots, pr_combine finishing the split rows -- against the oracle, and the plan must
+    really have segments.  Production graphs get it from 4 M edges on (LJ- and TW-shaped runs, bench.py parity)."""
+    monkeypatch.setenv("GMC_PR_TIER_MIN_EDGES", "0")
+    monkeypatch.setenv("GMC_PR_TIERS", str(tiers))
+    monkeypatch.setenv("GMC_PR_KMIN", str(kmin))
+    monkeypatch.setenv("GMC_PR_BIGTASKS", big)
+    dg = dev_graph(gm, g_rmat)
+    pi = dg.pagerank_plan_info()
+    assert pi["tiers"] >= 3 and pi["segments"] > 0 and pi["split_rows"] > 0 and pi["part_slots"] == pi["segments"] + pi["split_rows"]
+    assert pi["tier_ctas"] > 0
+    rank, info = dg.pagerank(e=1e-30, d=0.85, max_iter=20)
+    want, it, diff = oracle.pagerank(g_rmat["begin"], g_rmat["r_begin"], g_rmat["r_node_idx"], 1e-30, 0.85, 20)
+    assert info.iterations == it == 20
+    err = np.abs(rank - want).max()
+    assert err <= 1e-15, f"max abs err {err}, max ulp {graphs.max_ulp(rank, want)}"
+    assert abs(info.diff - diff) <= 1e-12 * max(1.0, abs(diff))
+    # deterministic: a second plan of the same graph gives the same bits (nothing depends on the CTA schedule)
+    rank2, _ = dev_graph(gm, g_rmat).pagerank(e=1e-30, d=0.85, max_iter=20)
+    assert np.array_equal(rank, rank2)
+    # convergence exit through pr_combine's loop control
+    rank3, info3 = dg.pagerank(e=1e-4, d=0.85, max_iter=100)
+    want3, it3, _ = oracle.pagerank(g_rmat["begin"], g_rmat["r_begin"], g_rmat["r_node_idx"], 1e-4, 0.85, 100)
+    assert info3.iterations == it3 and np.abs(rank3 - want3).max() <= 1e-15
+
+
+def test_pagerank_tiered_emulated_shards(gm, oracle, g_rmat, monkeypatch):
+    """shard plans of the tiered layout (3 shards on one device, shared state): same result as the oracle"""
+    monkeypatch.setenv("GMC_PR_TIER_MIN_EDGES", "0")
+    dg = dev_graph(gm, g_rmat)
+    rank, info = dg.pagerank_emulated_shards(3, e=1e-30, d=0.85, max_iter=20)
+    want, it, _ = oracle.pagerank(g_rmat["begin"], g_rmat["r_begin"], g_rmat["r_node_idx"], 1e-30, 0.85, 20)
+    assert info.iterations == it
+    assert np.abs(rank - want).max() <= 1e-15
