@@ -133,6 +133,21 @@ int gmc_comm_ipc_open_all(gmc_comm* c, void* local_base, void** peer_bases, cuda
     GMC_REQUIRE(c && c->world > 1 && local_base && peer_bases, GMC_ERR_ARG, "gmc_comm_ipc_open_all: bad args");
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     if (getenv("GMC_NO_P2P")) { set_error("peer mapping disabled by GMC_NO_P2P"); return GMC_ERR_STATE; }
+    if (c->local) {
+        // all ranks in one process (gmc_group, peer access already enabled): the pointers themselves are exchanged
+        unsigned long long mine_p = (unsigned long long)(uintptr_t)local_base, *stage_p = nullptr;
+        std::vector<unsigned long long> all_p((size_t)c->world);
+        GMC_TRY(gmc_malloc((void**)&stage_p, 8 * (size_t)c->world));
+        int rc2 = GMC_OK;
+        if (cudaMemcpyAsync(stage_p + c->rank, &mine_p, 8, cudaMemcpyHostToDevice, st) != cudaSuccess) rc2 = GMC_ERR_CUDA;
+        if (rc2 == GMC_OK) rc2 = gmc_comm_allgather(c, stage_p + c->rank, stage_p, 8, st);
+        if (rc2 == GMC_OK && (cudaMemcpyAsync(all_p.data(), stage_p, 8 * (size_t)c->world, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+                              cudaStreamSynchronize(st) != cudaSuccess)) rc2 = GMC_ERR_CUDA;
+        cudaFree(stage_p);
+        if (rc2 != GMC_OK) { set_error("gmc_comm_ipc_open_all: pointer exchange failed"); return rc2; }
+        for (int r = 0; r < c->world; r++) peer_bases[r] = (void*)(uintptr_t)all_p[(size_t)r];
+        return GMC_OK;
+    }
     cudaIpcMemHandle_t mine;
     if (cudaIpcGetMemHandle(&mine, local_base) != cudaSuccess) {
         set_error("cudaIpcGetMemHandle: %s", cudaGetErrorString(cudaGetLastError()));
@@ -173,7 +188,8 @@ int gmc_comm_ipc_open_all(gmc_comm* c, void* local_base, void** peer_bases, cuda
     return rc;
 }
 
-void gmc_comm_ipc_close_all(int world, int rank, void** peer_bases) {
+void gmc_comm_ipc_close_all(int world, int rank, void** peer_bases, bool local) {
+    if (local) { for (int r = 0; r < world; r++) if (r != rank) peer_bases[r] = nullptr; return; }      // plain pointers: nothing to unmap
     for (int r = 0; r < world; r++)
         if (r != rank && peer_bases[r]) { cudaIpcCloseMemHandle(peer_bases[r]); peer_bases[r] = nullptr; }
 }

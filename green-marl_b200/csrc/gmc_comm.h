@@ -9,6 +9,8 @@ struct gmc_comm {
     int world = 1, rank = 0;
     ncclComm_t nccl = nullptr;
     void* scratch = nullptr;
+    bool local = false;     // every rank lives in THIS process (gmc_group): peers are reached with plain device pointers
+    int device = -1;        // local ranks: the CUDA device of this rank
 };
 
 int gmc_comm_allgather(gmc_comm* c, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st);
@@ -17,4 +19,4 @@ int gmc_comm_allreduce_sum_i64(gmc_comm* c, const long long* send, long long* re
 int gmc_comm_allgather_segments(gmc_comm* c, void* buf, size_t elem_bytes, const int64_t* seg_off, const int64_t* seg_len,
                                 int nseg, cudaStream_t st);
 int gmc_comm_ipc_open_all(gmc_comm* c, void* local_base, void** peer_bases, cudaStream_t st);
-void gmc_comm_ipc_close_all(int world, int rank, void** peer_bases);
+void gmc_comm_ipc_close_all(int world, int rank, void** peer_bases, bool local);

@@ -169,7 +169,7 @@ int gmc_sync(void* stream) {
 // pagerank() call), and cudaMalloc/cudaFree of hundreds of MB cost milliseconds each and serialise on the driver.
 // The allocation is made on the legacy default stream and completed before returning, so the pointer may be used
 // on any stream; cudaFree() accepts pool allocations (memory goes back to the pool).
-static int pool_ready_for_device = -1;
+static thread_local int pool_ready_for_device = -1;     // per thread: a device group runs one host thread per device
 int gmc_malloc(void** p, size_t bytes) {
     GMC_REQUIRE(p, GMC_ERR_ARG, "gmc_malloc: NULL");
     *p = nullptr;

@@ -138,6 +138,7 @@ struct gmc_pr_plan {
     double* diffs = nullptr;                  // per-shard diffs, double-buffered by sweep parity
     unsigned int* flags = nullptr;            // flags[r] = sequence number of rank r's last completed sweep
     bool p2p = false;                         // peers mapped: contributions are pushed from the sweep epilogue
+    bool peer_local = false;                  // ... with plain pointers (all ranks in this process), nothing to unmap
     void* peer_base[MAX_PEERS + 1] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     unsigned int seq = 0;                     // sweeps issued so far (identical on every rank)
     size_t block_bytes = 0;
@@ -686,16 +687,17 @@ struct SymCache {
     double* block = nullptr;
     size_t bytes = 0;
     int world = 0, rank = 0;
-    bool p2p = false;
+    bool p2p = false, local = false;
     void* peer_base[MAX_PEERS + 1] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     unsigned long long gen = 0, peer_gen[MAX_PEERS + 1] = {0, 0, 0, 0, 0, 0, 0, 0};
 };
-SymCache g_sym;
-unsigned long long g_block_gen = 0;
+// per thread: the ranks of a device group (gmc_group.cu) are threads of one process, each with its own device and block
+thread_local SymCache g_sym;
+thread_local unsigned long long g_block_gen = 0;
 
 void sym_cache_release() {
     if (!g_sym.block) return;
-    if (g_sym.p2p) gmc_comm_ipc_close_all(g_sym.world, g_sym.rank, g_sym.peer_base);
+    if (g_sym.p2p) gmc_comm_ipc_close_all(g_sym.world, g_sym.rank, g_sym.peer_base, g_sym.local);
     cudaFree(g_sym.block);
     g_sym = SymCache();
 }
@@ -705,7 +707,7 @@ void free_plan(gmc_pr_plan* p) {
     if (p->owns_state && p->block_ipc && p->block && !getenv("GMC_NO_BLOCK_CACHE")) {      // retire the block instead of unmapping it
         sym_cache_release();
         g_sym.block = p->block; g_sym.bytes = p->block_bytes; g_sym.world = p->world; g_sym.rank = p->shard; g_sym.p2p = p->p2p;
-        g_sym.gen = p->gen;
+        g_sym.gen = p->gen; g_sym.local = p->peer_local;
         for (int r = 0; r <= MAX_PEERS; r++) { g_sym.peer_base[r] = p->peer_base[r]; g_sym.peer_gen[r] = p->peer_gen[r]; }
         p->block = nullptr; p->p2p = false;
     }
@@ -715,7 +717,7 @@ void free_plan(gmc_pr_plan* p) {
     cudaFree(L.pbeg); cudaFree(L.prow); cudaFree(L.sched_dev); cudaFree(L.streams_dev);
     cudaFree(p->head_part); cudaFree(p->tail_part); cudaFree(p->diff_parts); cudaFree(p->split_cnt); cudaFree(p->parts);
     if (p->owns_state) {
-        if (p->p2p) gmc_comm_ipc_close_all(p->world, p->shard, p->peer_base);
+        if (p->p2p) gmc_comm_ipc_close_all(p->world, p->shard, p->peer_base, p->peer_local);
         cudaFree(p->block); cudaFree(p->rank[0]); cudaFree(p->rank[1]); cudaFree(p->ctrl);
     }
     delete p;
@@ -779,7 +781,7 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
         const size_t stride = state_stride(n), nh = (size_t)L.NH, sync_doubles = 2 * SYNC_RANKS + SYNC_RANKS / 2;
         p->block_bytes = 8 * (2 * stride + 2 * nh + sync_doubles);
         if (world > 1 && g_sym.block && g_sym.bytes == p->block_bytes && g_sym.world == world && g_sym.rank == rank) {
-            p->block = g_sym.block; p->block_ipc = true; p->block_cached = true; p->gen = g_sym.gen;
+            p->block = g_sym.block; p->block_ipc = true; p->block_cached = true; p->gen = g_sym.gen; p->peer_local = g_sym.local;
             for (int r = 0; r <= MAX_PEERS; r++) { p->peer_base[r] = g_sym.p2p ? g_sym.peer_base[r] : nullptr; p->peer_gen[r] = g_sym.peer_gen[r]; }
             p->peer_base[rank] = nullptr;                 // plan_map_peers validates the mappings before they are used
             g_sym = SymCache();
@@ -928,9 +930,10 @@ static int plan_map_peers(gmc_pr_plan* p, gmc_comm* comm, cudaStream_t st) {
     for (int r = 0; r < W; r++) reuse = reuse && all[2 * r + 1] == 1ull && all[2 * r] == (r == p->shard ? p->gen : p->peer_gen[r]) && (r == p->shard || p->peer_base[r]);
     if (reuse) { p->p2p = true; return GMC_OK; }
     for (int r = 0; r < W; r++)               // stale mappings of a cached block (a peer has a new allocation)
-        if (r != p->shard && p->peer_base[r]) { cudaIpcCloseMemHandle(p->peer_base[r]); p->peer_base[r] = nullptr; }
+        if (r != p->shard && p->peer_base[r]) { if (!p->peer_local) cudaIpcCloseMemHandle(p->peer_base[r]); p->peer_base[r] = nullptr; }
     void* bases[MAX_PEERS + 1];
     rc = gmc_comm_ipc_open_all(comm, p->block, bases, st);
+    p->peer_local = comm->local;
     if (rc == GMC_OK) {
         for (int r = 0; r < W; r++) { p->peer_base[r] = bases[r]; p->peer_gen[r] = all[2 * r]; }
         p->p2p = true;

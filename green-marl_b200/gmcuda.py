@@ -97,6 +97,14 @@ SIGNATURES = {
     "gmc_pagerank_exchange_path": (C.c_int, [_vp, C.POINTER(C.c_int)]),
     "gmc_pagerank_sharded_time_sweeps": (C.c_int, [_vp, _vp, C.c_double, _i32, _i32, _vp, _vp, _vp]),
     "gmc_hop_dist_sharded_dev": (C.c_int, [_vp, _vp, _i32, _vp, C.POINTER(BfsInfo), _vp]),
+    "gmc_group_create": (C.c_int, [C.POINTER(_vp), C.c_int, _vp]),
+    "gmc_group_destroy": (C.c_int, [_vp]),
+    "gmc_group_size": (C.c_int, [_vp, C.POINTER(C.c_int)]),
+    "gmc_group_graph_upload": (C.c_int, [_vp, _i32, _i32, _vp, _vp, _vp, _vp]),
+    "gmc_group_graph_free": (C.c_int, [_vp]),
+    "gmc_group_pagerank": (C.c_int, [_vp, C.c_double, C.c_double, _i32, _vp, C.POINTER(PagerankInfo)]),
+    "gmc_group_hop_dist": (C.c_int, [_vp, _i32, _vp, C.POINTER(BfsInfo)]),
+    "gmc_group_exchange_path": (C.c_int, [_vp, C.POINTER(C.c_int)]),
     "gmc_bfs_levels_sharded": (C.c_int, [_vp, _vp, _i32, C.c_int, _vp, _vp, _vp, _vp, _i32, C.POINTER(BfsInfo)]),
 }
 
@@ -204,6 +212,15 @@ class GmCuda:
         return Graph(self, h)
 
     # ---- multi-GPU -----------------------------------------------------------------------
+    def group(self, ndev, devices=None):
+        """device group: `ndev` GPUs driven by this one process (gmc_group_*)"""
+        h = _vp()
+        dv = None
+        if devices is not None:
+            dv = (C.c_int * ndev)(*devices)
+        self.check(self.L.gmc_group_create(C.byref(h), ndev, dv))
+        return Group(self, h)
+
     def comm_unique_id(self):
         """128 opaque bytes (ncclUniqueId); made on rank 0 and shipped to the other ranks by the host side"""
         buf = np.zeros(128, np.uint8)
@@ -251,6 +268,47 @@ class GmCuda:
 
     def sync(self, stream=None):
         self.check(self.L.gmc_sync(_vp(stream) if stream else None))
+
+
+class Group:
+    """1/2/4/8 GPUs behind one process: CSR replicated, rows partitioned, one host thread per device inside the library"""
+
+    def __init__(self, lib, handle):
+        self.lib, self.h = lib, handle
+
+    def upload(self, begin, node_idx, r_begin=None, r_node_idx=None):
+        self._keep = [np.ascontiguousarray(a, dtype=np.int32) if a is not None else None for a in (begin, node_idx, r_begin, r_node_idx)]
+        b, i, rb, ri = self._keep
+        self.n, self.m = len(b) - 1, (len(i) if i is not None else len(ri))
+        self.lib.check(self.lib.L.gmc_group_graph_upload(self.h, self.n, self.m, _ptr(b), _ptr(i) if i is not None else None,
+                                                         _ptr(rb) if rb is not None else None, _ptr(ri) if ri is not None else None))
+
+    def pagerank(self, e=1e-30, d=0.85, max_iter=20, out=None):
+        rank = out if out is not None else np.zeros(max(self.n, 1), np.float64)
+        info = PagerankInfo()
+        self.lib.check(self.lib.L.gmc_group_pagerank(self.h, e, d, max_iter, _ptr(rank), C.byref(info)))
+        return rank[:self.n], info
+
+    def hop_dist(self, root=0, out=None):
+        dist = out if out is not None else np.zeros(max(self.n, 1), np.int32)
+        info = BfsInfo()
+        self.lib.check(self.lib.L.gmc_group_hop_dist(self.h, root, _ptr(dist), C.byref(info)))
+        return dist[:self.n], info
+
+    def exchange_path(self):
+        p = C.c_int()
+        self.lib.check(self.lib.L.gmc_group_exchange_path(self.h, C.byref(p)))
+        return {0: "single", 1: "nccl", 2: "peer-memory"}.get(p.value, str(p.value))
+
+    def size(self):
+        k = C.c_int()
+        self.lib.check(self.lib.L.gmc_group_size(self.h, C.byref(k)))
+        return k.value
+
+    def close(self):
+        if self.h:
+            self.lib.L.gmc_group_destroy(self.h)
+            self.h = None
 
 
 class Comm:

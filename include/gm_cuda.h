@@ -251,6 +251,24 @@ int gmc_pagerank_exchange_path(gmc_graph* g, int* path);
 int gmc_pagerank_sharded_time_sweeps(gmc_graph* g, gmc_comm* comm, double d, int32_t warmup, int32_t n, float* sweep_ms,
                                      float* exchange_ms, void* stream);
 
+/* --- device group: 1/2/4/8 GPUs behind ONE call of ONE process (one host thread per device inside the library).  This is
+ * what the reference's placement switch maps to -- shl__init(nthreads, partitioned), apps/output_cpp/src/common_main.h:95-99;
+ * scripts/run.sh:86-92 (-r replicate / -p partition) -- and how the unchanged drivers reach more than one B200
+ * (GM_CUDA_DEVICES=N, host/shl.cc).  The CSR is replicated (every device copies 1/N of it over its own PCIe link, the slices
+ * are allgathered over NVLink), rows are partitioned into destination ranges, the peers' state blocks are reached with plain
+ * device pointers (cudaDeviceEnablePeerAccess); results land in the caller's ONE host array, each device copying its slice.
+ * devices == NULL: devices 0..ndev-1.  A group holds one graph at a time. */
+typedef struct gmc_group gmc_group;
+int gmc_group_create(gmc_group** out, int ndev, const int* devices);
+int gmc_group_destroy(gmc_group* grp);
+int gmc_group_size(const gmc_group* grp, int* ndev);
+int gmc_group_graph_upload(gmc_group* grp, int32_t num_nodes, int32_t num_edges, const int32_t* begin, const int32_t* node_idx,
+                           const int32_t* r_begin, const int32_t* r_node_idx);     /* node_idx may be NULL (pull-only), r_* too */
+int gmc_group_graph_free(gmc_group* grp);
+int gmc_group_pagerank(gmc_group* grp, double e, double d, int32_t max_iter, double* rank_host, gmc_pagerank_info* info);
+int gmc_group_hop_dist(gmc_group* grp, int32_t root, int32_t* dist_host, gmc_bfs_info* info);
+int gmc_group_exchange_path(gmc_group* grp, int* path);     /* as gmc_pagerank_exchange_path, of the last gmc_group_pagerank */
+
 /* BFS over vertex-range shards: per level each rank expands / scans its owned vertices, then the candidate
  * bitmaps are exchanged with ncclAllGather.  dist_dev / level_host receive the full array on every rank. */
 int gmc_hop_dist_sharded_dev(gmc_graph* g, gmc_comm* comm, int32_t root, int32_t* dist_dev, gmc_bfs_info* info, void* stream);
