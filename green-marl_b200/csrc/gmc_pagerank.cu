@@ -59,7 +59,7 @@ static inline int shard_row_cost(int world) {
     return world > 2 ? 2 * (world - 2) : 0;
 }
 constexpr unsigned FULL = 0xffffffffu;
-constexpr int MAX_STREAMS = prp::MAX_TIERS + 1;
+constexpr int MAX_STREAMS = prp::MAX_TIERS + 2;      // home + tiers 0..31
 
 struct gmc_pr_ctrl {   // device-side loop control: lets the host enqueue sweeps without a sync per iteration
     double diff;
@@ -95,6 +95,7 @@ struct SweepArgs {
     int32_t n_ztasks, z0, z_end, zt_on;       // [z0, z_end): the shard's ids without in-edges; zt_on: run their tasks this sweep
     int32_t dp_short, dp_zero, dp_cut, dp_total, n_cb;   // diff_parts layout; n_cb = pr_combine blocks (their partials follow dp_total)
     int32_t hot0_bytes;                       // bytes of tier 0 worth staging (small graphs do not fill it)
+    int32_t cold_warps;                       // warps of a CTA that prefer home tasks (L2 gathers) to their tier's tasks
     // cut rows of the long sections, parts of the split rows
     double* head_part;                       // [n_ltslots]
     double* tail_part;                       // [n_ltslots]
@@ -451,7 +452,8 @@ __device__ __forceinline__ void zero_task(const SweepArgs& A, int lane, int32_t 
 __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
     extern __shared__ __align__(16) double hot[];
     __shared__ __align__(8) unsigned long long bar;
-    __shared__ Stream s_st;
+    __shared__ Stream s_st, s_home;
+    __shared__ int s_skip;
     const int tid = threadIdx.x, lane = tid & 31;
 
     if (tid == 0) mbar_init(&bar, 1);
@@ -462,20 +464,32 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (A.loop && A.ctrl->done) return;
 
+    // Every CTA stages the tiers of its list one after the other.  While a tier is staged its warps draw tasks from two
+    // device-wide counters: the tier's stream (shared-memory gathers) and the home stream (L2 gathers; runs with any tier
+    // staged in SPLIT mode, with tier 0 -- the only list entry -- in MIXED mode).  The first cold_warps warps prefer home
+    // tasks, the others the tier's, and each falls back to the other kind: both gather paths of the SM stay busy.
+    if (tid == 0) s_home = A.streams[0];
     unsigned phase = 0;
+    const bool cold_first = (tid >> 5) < A.cold_warps;
+    bool home_left = true;
     for (int i = 0; i < SCHED_W; i++) {
-        // the streams of this CTA: up to SCHED_W - 1 tiers, then home (stream 0), which every CTA ends with
-        const int s = i < SCHED_W - 1 ? __ldg(A.sched + blockIdx.x * SCHED_W + i) : 0;
-        if (i > 0) __syncthreads();                  // every warp has left the previous stream: hot[] and s_st may change
-        if (tid == 0) s_st = A.streams[s];
+        const int s = __ldg(A.sched + blockIdx.x * SCHED_W + i);
+        if (s == 0) break;
+        if (i > 0) __syncthreads();                  // every warp has left the previous tier: hot[] and s_st may change
+        if (tid == 0) {
+            s_st = A.streams[s];
+            // a later list entry (a place to help) is staged only while it has tasks left
+            s_skip = i > 0 && *(volatile unsigned int*)&A.ctrl->next[s] >= (unsigned)(s_st.n_ltasks + s_st.n_stasks);
+        }
         __syncthreads();
         const Stream& st = s_st;
-        const int32_t n_l = st.n_ltasks, n_s = st.n_stasks, n_z = (s == 0 && A.zt_on) ? A.n_ztasks : 0;
-        const int32_t total = n_l + n_s + n_z;
-        if (total > 0) {
-            // stage the tier: hot_in[hot_off, hot_off + HT) -> shared memory, one TMA bulk copy stream
+        const Stream& hm = s_home;
+        const int32_t h_l = hm.n_ltasks, h_s = hm.n_stasks, h_total = h_l + h_s + (A.zt_on ? A.n_ztasks : 0);
+        const int32_t t_l = st.n_ltasks, t_total = t_l + st.n_stasks;
+        if (s_skip) continue;
+        {   // stage the tier: hot_in[hot_off, hot_off + HT) -> shared memory, one TMA bulk copy stream
             if (tid == 0) {
-                const unsigned bytes = s == 0 ? (unsigned)A.hot0_bytes : (unsigned)(HT * 8);
+                const unsigned bytes = s == 1 ? (unsigned)A.hot0_bytes : (unsigned)(HT * 8);
                 mbar_expect_tx(&bar, bytes);
                 const char* src = reinterpret_cast<const char*>(A.hot_in + st.hot_off);
                 char* dst = reinterpret_cast<char*>(hot);
@@ -488,23 +502,32 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
             }
             mbar_wait(&bar, phase);
             phase ^= 1u;
-            // tasks come from the stream's device-wide counter, long tasks first (task costs vary with the row mix)
-            for (;;) {
-                int32_t u = 0;
-                if (lane == 0) u = (int32_t)atomicAdd(&A.ctrl->next[s], 1u);
-                u = __shfl_sync(FULL, u, 0);
-                if (u >= total) break;
-                if (s == 0) {
-                    if (u < n_l) long_task<false>(A, st, hot, lane, u);
-                    else if (u < n_l + n_s) short_task<false>(A, st, hot, lane, u - n_l);
-                    else zero_task(A, lane, u - n_l - n_s);
-                } else {
-                    if (u < n_l) long_task<true>(A, st, hot, lane, u);
-                    else short_task<true>(A, st, hot, lane, u - n_l);
-                }
-            }
         }
-        if (s == 0) break;
+        bool tier_left = t_total > 0;
+        home_left = home_left && h_total > 0;
+        for (;;) {
+            bool did = false;
+#pragma unroll 1
+            for (int pass = 0; pass < 2 && !did; pass++) {
+                const bool want_home = (pass == 0) == cold_first;
+                if (want_home ? !home_left : !tier_left) continue;
+                int32_t u = 0;
+                if (lane == 0) u = (int32_t)atomicAdd(&A.ctrl->next[want_home ? 0 : s], 1u);
+                u = __shfl_sync(FULL, u, 0);
+                if (want_home) {
+                    if (u >= h_total) { home_left = false; continue; }
+                    if (u < h_l) long_task<false>(A, hm, hot, lane, u);
+                    else if (u < h_l + h_s) short_task<false>(A, hm, hot, lane, u - h_l);
+                    else zero_task(A, lane, u - h_l - h_s);
+                } else {
+                    if (u >= t_total) { tier_left = false; continue; }
+                    if (u < t_l) long_task<true>(A, st, hot, lane, u);
+                    else short_task<true>(A, st, hot, lane, u - t_l);
+                }
+                did = true;
+            }
+            if (!did) break;
+        }
     }
 }
 
@@ -548,7 +571,7 @@ __global__ void __launch_bounds__(CB_THREADS, 1) pr_combine(const SweepArgs A) {
     __syncthreads();
     if (warp == 0) {
         const double t = butterfly(lane < CB_THREADS / 32 ? s_red[lane] : 0.0);
-        if (lane <= A.T) A.ctrl->next[lane] = 0u;
+        for (int i2 = lane; i2 < MAX_STREAMS; i2 += 32) A.ctrl->next[i2] = 0u;
         if (lane == 0) A.ctrl->arrived = 0u;
         if (lane == 0 && A.diff_slot) {
             *A.diff_slot = t;
@@ -824,6 +847,10 @@ SweepArgs make_args(const gmc_pr_plan* p, double d, int sweep, gmc_pr_ctrl* ctrl
     {
         const int32_t want = L.n_src + 1 < HT ? L.n_src + 1 : HT;         // slot 0 + the tier-0 sources that exist
         A.hot0_bytes = ((want + 1) & ~1) * 8;                              // multiple of 16 bytes
+    }
+    {
+        static const int cw = env_int("GMC_PR_COLD_WARPS", (PR_THREADS / 32) * 3 / 8);      // 12 of 32 warps
+        A.cold_warps = L.split ? cw : PR_THREADS / 32;
     }
     A.head_part = p->head_part; A.tail_part = p->tail_part; A.split_cnt = p->split_cnt; A.diff_parts = p->diff_parts; A.parts = p->parts;
     A.contrib_in = p->contrib[parity]; A.contrib_out = p->contrib[parity ^ 1];
@@ -1184,7 +1211,7 @@ int gmc_pagerank_plan_info(gmc_graph* g, gmc_pagerank_plan_info_t* out) {
     out->home_entries = L.streams[0].entries; out->hot0_entries = L.hot0_entries; out->cold_entries = L.cold_entries; out->segment_entries = L.seg_entries;
     {
         int c = 0;
-        for (int b = 0; b < p->grid; b++) c += L.sched[(size_t)b * SCHED_W] != 0;
+        for (int b = 0; b < p->grid; b++) c += L.sched[(size_t)b * SCHED_W] > 1;          // CTAs that start in a warm tier
         out->tier_ctas = c;
     }
     return GMC_OK;

@@ -13,15 +13,19 @@
 //               into its slot, so the hotpack of the next sweep is complete when the sweep ends.
 //   ids         rows are relabelled 1..N by (in-degree > S_MAX, in-degree > 0, none) and in-degree descending; rank[],
 //               contrib[] and the multi-GPU exchange live in this id space (coalesced epilogues).
-//   stream 0    "home": every row of the shard with the entries whose source is in tier 0 (entry value = slot < HT, served by
-//               shared memory) or is not served by a tier stream (entry value = HT + id, an L2 gather).  Long rows
-//               (in-degree > S_MAX) row-major in fixed-size tasks, the others as sliced ELL: exactly the two task classes of
-//               round 1, original source order kept inside a row.
-//   stream t    (t = 1..T) the SEGMENTS of tier t: the entries of one row whose sources lie in tier t, if there are at least
+//   stream 0    "home": every row of the shard with the entries that no tier stream serves (entry value = HT + id, an L2
+//               gather; 0 = padding).  Long rows (in-degree > S_MAX) row-major in fixed-size tasks, the others as sliced
+//               ELL: the two task classes of round 1, original source order kept inside a row.
+//   stream t+1  (t = 0..T) the SEGMENTS of tier t: the entries of one row whose sources lie in tier t, if there are at least
 //               KMIN of them (fewer stay cold entries of the home row: a segment costs a partial sum written and read once,
-//               ~1.25 sector operations, so it must replace at least ~2 cold gathers).  Entry value = slot inside the tier.
-//               Segments sorted by length: the long ones row-major in tasks, the others sliced ELL -- the same two task
-//               classes again, run by CTAs that hold tier t instead of tier 0.  No gather of a tier stream leaves the SM.
+//               ~1.25 sector operations, so it must replace at least ~2 cold gathers; tier 0: KMIN = 1).  Entry value = slot
+//               inside the tier.  Segments sorted by length: the long ones row-major in tasks, the others sliced ELL -- the
+//               same two task classes again.  No gather of a tier stream leaves the SM.
+//   two modes   SPLIT (graphs with warm tiers, T >= 1): home holds cold entries only, so a home task runs on ANY CTA
+//               whatever tier it has staged, and every SM keeps both of its gather paths busy at once: some warps on its
+//               tier's stream (shared memory), the others on home tasks (L2 sectors).  MIXED (small graphs, T = 0): tier-0
+//               entries stay inside the home rows (entry value = slot < HT), every CTA stages tier 0, no row is split and
+//               every short row is added in exactly the reference's order (bit-identical to the CPU result).
 //   parts       a row with segments ("split row") owns 1 + nseg consecutive part slots: slot 0 for the home part, then one
 //               per segment in tier order.  Tasks store partial sums there; the combine kernel adds them in slot order and
 //               runs the row epilogue: deterministic whatever the CTA schedule, no atomics or fences in the sweep.
@@ -53,9 +57,9 @@ constexpr int HT = PRP_HT;             // slots per tier block (130 KB of double
 constexpr int HT_REAL = HT - 1;        // slot 0 of a tier is the dummy
 constexpr int S_MAX = PRP_S_MAX;            // rows / segments up to this length are summed by one lane, left to right
 constexpr int PIECE = 512;             // entries of a long row one plan thread walks
-constexpr int MAX_TIERS = 31;          // warm tiers 1..31 (segment mask = one 32-bit word, tier number = 5 key bits)
+constexpr int MAX_TIERS = 31;          // tiers 0..31 (segment mask = one 32-bit word, tier number = 5 key bits)
 constexpr int ZT = 2048;               // ids per zero-in-degree task
-constexpr int SCHED_W = 4;             // streams a CTA visits: up to 3 tiers, then home
+constexpr int SCHED_W = 4;             // tier streams a CTA may stage one after the other
 constexpr uint32_t OD_SPLIT = 0x80000000u, OD_HOT = 0x40000000u, OD_MASK = 0x3fffffffu;   // od_flags[id]
 
 struct Config {
@@ -99,7 +103,8 @@ struct Plan {
     int32_t n_sbeg = 0, n_ltslots = 0, n_stslots = 0;
     int32_t dp_short = 0, dp_zero = 0, dp_cut = 0, dp_total = 0;     // diff_parts: [home long | home short | zero | cut rows]
     int64_t hot0_entries = 0, cold_entries = 0, seg_entries = 0;
-    Stream streams[MAX_TIERS + 1];
+    int32_t split = 0;                            // 1: SPLIT mode (see the header)
+    Stream streams[MAX_TIERS + 2];                // [0] home, [t + 1] tier t
     std::vector<int64_t> seg_off, seg_len;        // [world][3] id ranges owned by every rank (long, short, zero)
     std::vector<int32_t> sched;                   // [grid][SCHED_W] streams a CTA visits (0 = home ends the list)
     // device (backend) arrays
@@ -223,14 +228,15 @@ struct RelabelF {
 struct ByIdF {         // arrays indexed by the new id, and the gather code of every vertex
     const int32_t *old_of_new, *outdeg, *hotslot_old;
     int32_t *od_flags, *hotslot, *idslot, *code;
+    int32_t split;
     PRP_HD void operator()(int64_t p) const {
         const int32_t id = (int32_t)p + 1, v = old_of_new[id], slot = hotslot_old[v];
         if (p == 0) { od_flags[0] = 0; hotslot[0] = -1; }
         od_flags[id] = (int32_t)((uint32_t)outdeg[v] | (slot >= 0 ? OD_HOT : 0u));
         hotslot[id] = slot;
         if (slot >= 0) idslot[slot] = id;
-        // entry code of a source: tier 0 -> its slot (< HT); warm tier -> -slot; no slot -> HT + id
-        code[v] = slot < 0 ? HT + id : (slot < HT ? slot : -slot);
+        // entry code of a source: served by a tier stream -> -slot; tier 0 in MIXED mode -> its slot (< HT); no slot -> HT + id
+        code[v] = slot < 0 ? HT + id : ((slot < HT && !split) ? slot : -slot);
     }
 };
 // global row offsets by in-degree (shard cuts only): padded long rows, slice lengths and costs
@@ -247,26 +253,26 @@ struct GlobalLenF {
 };
 
 struct RowCtx {        // the shard's rows: r in [0, nl) long rows (id = jl0 + 1 + r), r >= nl short rows (id = short_id0 + r - nl)
-    int32_t n, nl, jl0, short_id0, T, kmin;
+    int32_t n, nl, jl0, short_id0, tlo, T, kmin;       // tiers tlo..T have streams (tlo = 0 in SPLIT mode, 1 otherwise)
     const int32_t *old_of_new, *r_begin, *r_node_idx, *code;
     PRP_HD int32_t id_of(int32_t r) const { return r < nl ? jl0 + 1 + r : short_id0 + (r - nl); }
 };
 
 // emits the segment records of one row from its per-tier counts; returns the number of entries that move to segments
 template <typename CNT>
-PRP_HD int32_t emit_segments(const CNT* cnt, int T, int kmin, int32_t r, uint32_t* mask_out, int32_t* nrec, unsigned long long* rec_key,
+PRP_HD int32_t emit_segments(const CNT* cnt, int tlo, int T, int kmin, int32_t r, uint32_t* mask_out, int32_t* nrec, unsigned long long* rec_key,
                              int32_t* rec_j, int32_t rec_cap, int32_t* err) {
     uint32_t mask = 0;
     int32_t tot = 0;
     int ns = 0;
-    for (int t = 1; t <= T; t++)
-        if ((int32_t)cnt[t] >= kmin) { mask |= 1u << t; tot += (int32_t)cnt[t]; ns++; }
+    for (int t = tlo; t <= T; t++)
+        if ((int32_t)cnt[t] >= (t == 0 ? 1 : kmin)) { mask |= 1u << t; tot += (int32_t)cnt[t]; ns++; }
     *mask_out = mask;
     if (ns) {
         int32_t base = atomic_add_i32(nrec, ns);
         if (base + ns > rec_cap) { *err = 2; return tot; }
         int j = 1;
-        for (int t = 1; t <= T; t++)
+        for (int t = tlo; t <= T; t++)
             if (mask >> t & 1u) { rec_key[base] = seg_key(t, (int32_t)cnt[t], r); rec_j[base] = j++; base++; }
     }
     return tot;
@@ -282,7 +288,7 @@ struct CountShortF {   // item i: short row r = nl + i
         const int32_t r = c.nl + (int32_t)i, id = c.short_id0 + (int32_t)i;
         if (id > c.n) { segmask[r] = 0; home_len[r] = 0; return; }
         const int32_t v = c.old_of_new[id], rb = c.r_begin[v], len = c.r_begin[v + 1] - rb;
-        if (c.T == 0 || len < c.kmin) { segmask[r] = 0; home_len[r] = len; return; }
+        if (c.tlo > c.T || len < (c.tlo == 0 ? 1 : c.kmin)) { segmask[r] = 0; home_len[r] = len; return; }
         uint16_t cnt[MAX_TIERS + 1];
         for (int t = 0; t <= c.T; t++) cnt[t] = 0;
         for (int32_t k = 0; k < len; k++) {
@@ -290,7 +296,7 @@ struct CountShortF {   // item i: short row r = nl + i
             if (cd < 0) cnt[(-cd) / HT]++;
         }
         uint32_t mask;
-        const int32_t tot = emit_segments(cnt, c.T, c.kmin, r, &mask, nrec, rec_key, rec_j, rec_cap, err);
+        const int32_t tot = emit_segments(cnt, c.tlo, c.T, c.kmin, r, &mask, nrec, rec_key, rec_j, rec_cap, err);
         segmask[r] = mask;
         home_len[r] = len - tot;
     }
@@ -313,7 +319,7 @@ struct PieceRowF {
         piece_row[p] = last_le(piece_first, nl, (int32_t)p);
     }
 };
-struct PieceCountF {   // per-tier counts of one piece -> G[(t-1) * nps + p]
+struct PieceCountF {   // per-tier counts of one piece -> G[t * nps + p]
     RowCtx c;
     const int32_t *piece_first, *piece_row;
     int32_t nps;
@@ -328,7 +334,7 @@ struct PieceCountF {   // per-tier counts of one piece -> G[(t-1) * nps + p]
             const int32_t cd = c.code[c.r_node_idx[rb + k]];
             if (cd < 0) cnt[(-cd) / HT]++;
         }
-        for (int t = 1; t <= c.T; t++) G[(size_t)(t - 1) * nps + p] = cnt[t];
+        for (int t = c.tlo; t <= c.T; t++) G[(size_t)t * nps + p] = cnt[t];
     }
 };
 struct LongRowF {      // G scanned (exclusive): totals of long row j -> segments
@@ -344,19 +350,19 @@ struct LongRowF {      // G scanned (exclusive): totals of long row j -> segment
         const int32_t p0 = piece_first[j], p1 = piece_first[j + 1];
         int32_t cnt[MAX_TIERS + 1];
         cnt[0] = 0;
-        for (int t = 1; t <= c.T; t++) cnt[t] = G[(size_t)(t - 1) * nps + p1] - G[(size_t)(t - 1) * nps + p0];
+        for (int t = c.tlo; t <= c.T; t++) cnt[t] = G[(size_t)t * nps + p1] - G[(size_t)t * nps + p0];
         uint32_t mask = 0;
-        const int32_t tot = c.T ? emit_segments(cnt, c.T, c.kmin, (int32_t)j, &mask, nrec, rec_key, rec_j, rec_cap, err) : 0;
+        const int32_t tot = c.tlo <= c.T ? emit_segments(cnt, c.tlo, c.T, c.kmin, (int32_t)j, &mask, nrec, rec_key, rec_j, rec_cap, err) : 0;
         segmask[j] = mask;
         home_len[j] = len - tot;
     }
 };
-struct TierBoundF {    // item t-1, t = 1..T+1: first sorted segment of tier t and first one of it that is not long
+struct TierBoundF {    // item t = 0..T+1: first sorted segment of tier t and first one of it that is not long
     const unsigned long long* keys;
     int32_t nseg, T;
     int32_t *tier_q, *tier_mid;      // [T + 2]
     PRP_HD void operator()(int64_t i) const {
-        const int t = (int)i + 1;
+        const int t = (int)i;
         if (t > T) { tier_q[t] = nseg; tier_mid[t] = nseg; return; }
         tier_q[t] = lower_bound_i<unsigned long long>(keys, 0, nseg, (unsigned long long)t << 59);
         tier_mid[t] = lower_bound_i<unsigned long long>(keys, 0, nseg, ((unsigned long long)t << 59) | ((unsigned long long)(0xffffffffu - (uint32_t)S_MAX) << 27));
@@ -493,12 +499,12 @@ struct FillShortF {    // item i: short row r = nl + i; its home entries go to c
         }
         SegCursor cur;
         int j = 1;
-        for (int t = 1; t <= c.T; t++)
+        for (int t = 0; t <= c.T; t++)
             if (mask >> t & 1u) { const int32_t s = f.pslot[r] + j++; cur.pos[t] = f.seg_ebase[s]; cur.stride[t] = f.seg_estride[s]; }
         for (int32_t k = 0; k < len; k++) {
             const int32_t src = c.r_node_idx[rb + k], cd = c.code[src];
-            const int t = cd < 0 ? (-cd) / HT : 0;
-            if (t && (mask >> t & 1u)) { f.E[cur.pos[t]] = (-cd) - t * HT; cur.pos[t] += cur.stride[t]; }
+            const int t = cd < 0 ? (-cd) / HT : -1;
+            if (t >= 0 && (mask >> t & 1u)) { f.E[cur.pos[t]] = (-cd) - t * HT; cur.pos[t] += cur.stride[t]; }
             else { f.E[h] = home_value(f, cd, src); h += 32; }
         }
     }
@@ -517,10 +523,10 @@ struct FillPieceF {    // one piece of a long row: the scanned piece table says 
         SegCursor cur;
         int32_t moved = 0;
         int jj = 1;
-        for (int t = 1; t <= c.T; t++)
+        for (int t = 0; t <= c.T; t++)
             if (mask >> t & 1u) {
                 const int32_t s = f.pslot[j] + jj++;
-                const int32_t before = G[(size_t)(t - 1) * nps + p] - G[(size_t)(t - 1) * nps + p0];
+                const int32_t before = G[(size_t)t * nps + p] - G[(size_t)t * nps + p0];
                 cur.stride[t] = f.seg_estride[s];
                 cur.pos[t] = f.seg_ebase[s] + before * cur.stride[t];
                 moved += before;
@@ -528,8 +534,8 @@ struct FillPieceF {    // one piece of a long row: the scanned piece table says 
         int32_t h = f.eoff[j] + (k0 - moved);
         for (int32_t k = k0; k < k1; k++) {
             const int32_t src = c.r_node_idx[rb + k], cd = c.code[src];
-            const int t = cd < 0 ? (-cd) / HT : 0;
-            if (t && (mask >> t & 1u)) { f.E[cur.pos[t]] = (-cd) - t * HT; cur.pos[t] += cur.stride[t]; }
+            const int t = cd < 0 ? (-cd) / HT : -1;
+            if (t >= 0 && (mask >> t & 1u)) { f.E[cur.pos[t]] = (-cd) - t * HT; cur.pos[t] += cur.stride[t]; }
             else f.E[h++] = home_value(f, cd, src);
         }
     }
@@ -554,55 +560,54 @@ static inline void shard_cuts(const int64_t* prefix, int32_t n, int world, int32
 }
 
 
-// Which streams every CTA visits.  A tier stream gets CTAs in proportion to its share of the sweep's cost (shared-memory gathers
-// for the tiers; for home the slower of its shared-memory and its L2 gathers); tiers too small for one CTA are grouped, up to
-// SCHED_W - 1 per CTA.  Every tier CTA ends in the home stream, so rounding up is harmless: it joins the others early.
+// Which tier streams every CTA stages, in order (sched[b][i] = stream number, 0 ends the list).  Home tasks need no tier in
+// SPLIT mode and are taken by the warps of every CTA beside its tier's tasks, so only the tier streams are apportioned: CTAs in
+// proportion to the entries of a tier (all shared-memory gathers, same cost each); tiers too small for one CTA are grouped, up
+// to SCHED_W - 1 per CTA; every list ends with stream 1 (tier 0, the largest) as a place to help once the own work is done.
+// MIXED mode: every CTA stages tier 0 (its stream is empty; the home rows gather from it).
 static inline void make_schedule(const Config& cfg, Plan& P) {
     const int G = cfg.grid > 0 ? cfg.grid : 1;
     P.sched.assign((size_t)G * SCHED_W, 0);
-    if (P.T == 0) return;
-    std::vector<double> c((size_t)P.T + 1, 0.0);
-    const double hot = (double)P.hot0_entries / cfg.r_smem, cold = (double)P.cold_entries / cfg.r_miss;
-    c[0] = std::max(hot, cold) + 0.25 * std::min(hot, cold);
-    double total = c[0];
-    for (int t = 1; t <= P.T; t++) { c[t] = (double)P.streams[t].entries / cfg.r_smem * cfg.tier_scale; total += c[t]; }
+    for (int b = 0; b < G; b++) P.sched[(size_t)b * SCHED_W] = 1;
+    if (!P.split) return;
+    const int NTS = P.T + 1;                       // tier streams 1..NTS
+    std::vector<double> c((size_t)NTS + 1, 0.0);
+    double total = 0;
+    for (int s = 1; s <= NTS; s++) { c[s] = (double)P.streams[s].entries * (s == 1 ? 1.0 : cfg.tier_scale) + 1.0; total += c[s]; }
     double per = total / G;
-    if (per <= 0) per = 1;
-    const int budget = G / 2 > 0 ? G / 2 : 1;
-    for (int attempt = 0; attempt < 64; attempt++, per *= 1.15) {
-        std::vector<int32_t> s((size_t)G * SCHED_W, 0);
-        int b = 0, t = 1;
-        bool ok = true;
-        while (t <= P.T) {
-            if (b >= budget) { ok = false; break; }
-            if (c[t] >= 0.75 * per) {
-                int k = (int)((c[t] + per - 1e-9) / per);
-                if (k < 1) k = 1;
-                if (b + k > budget) { ok = false; break; }
-                for (int i = 0; i < k; i++) s[(size_t)(b + i) * SCHED_W] = t;
-                b += k; t++;
-            } else {
-                double sum = 0;
-                int cnt = 0;
-                while (t <= P.T && cnt < SCHED_W - 1 && (cnt == 0 || sum + c[t] <= 1.1 * per)) { s[(size_t)b * SCHED_W + cnt] = t; sum += c[t]; cnt++; t++; }
-                b++;
-            }
+    for (int attempt = 0; attempt < 200; attempt++, per *= 1.03) {
+        std::vector<int> k((size_t)NTS + 1, 0);    // CTAs of a big tier; 0 = grouped
+        std::vector<std::vector<int>> groups;
+        int used = 0;
+        for (int s = 1; s <= NTS;) {
+            if (c[s] >= 0.75 * per) { k[s] = std::max(1, (int)(c[s] / per + 0.5)); used += k[s]; s++; continue; }
+            std::vector<int> g;
+            double sum = 0;
+            while (s <= NTS && c[s] < 0.75 * per && (int)g.size() < SCHED_W - 1 && (g.empty() || sum + c[s] <= 1.1 * per)) { g.push_back(s); sum += c[s]; s++; }
+            groups.push_back(g); used++;
         }
-        if (ok) { P.sched = s; return; }
-    }
-    // last resort (tiny grids): the tiers in groups of SCHED_W - 1 on the first CTAs, wrapping around
-    {
-        std::vector<int32_t> s((size_t)G * SCHED_W, 0);
-        std::vector<int> fill((size_t)G, 0);
+        if (used > G) continue;
+        for (; used < G; used++) {                 // leftover CTAs go where a CTA has the most entries to run
+            int best = 0;
+            double load = -1;
+            for (int s = 1; s <= NTS; s++) if (k[s] > 0 && c[s] / k[s] > load) { load = c[s] / k[s]; best = s; }
+            if (!best) break;
+            k[best]++;
+        }
+        std::vector<int32_t> sc((size_t)G * SCHED_W, 0);
         int b = 0;
-        for (int t = 1; t <= P.T; t++) {
-            int tries = 0;
-            while (fill[b] >= SCHED_W - 1 && tries++ < G) b = (b + 1) % G;
-            if (fill[b] >= SCHED_W - 1) { P.T = t - 1; break; }       // cannot happen with G * (SCHED_W - 1) >= MAX_TIERS
-            s[(size_t)b * SCHED_W + fill[b]++] = t;
-            if (fill[b] >= SCHED_W - 1) b = (b + 1) % G;
+        for (int s = 1; s <= NTS; s++) for (int i = 0; i < k[s] && b < G; i++) sc[(size_t)(b++) * SCHED_W] = s;
+        for (auto& g : groups) { if (b >= G) break; for (size_t i = 0; i < g.size(); i++) sc[(size_t)b * SCHED_W + i] = g[i]; b++; }
+        for (; b < G; b++) sc[(size_t)b * SCHED_W] = 1;
+        for (int bb = 0; bb < G; bb++) {           // the helper entry
+            int32_t* row = &sc[(size_t)bb * SCHED_W];
+            int len = 0;
+            bool has1 = false;
+            while (len < SCHED_W && row[len]) { has1 = has1 || row[len] == 1; len++; }
+            if (!has1 && len < SCHED_W) row[len] = 1;
         }
-        P.sched = s;
+        P.sched = sc;
+        return;
     }
 }
 
@@ -641,7 +646,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     int32_t h3[4] = {0, 0, 0, 0};
     std::vector<int32_t> cutsL((size_t)world + 1), cutsS((size_t)world + 1), cutsZ((size_t)world + 1);
     std::vector<long long> h_tier_out(MAX_TIERS + 2, 0);
-    int32_t g_n_slices = 0, nl = 0, ns = 0, nrows = 0, short_id0 = 0, nps = 0, rec_cap = 0, nseg = 0, X = 0, herr = 0;
+    int32_t tlo = 1, g_n_slices = 0, nl = 0, ns = 0, nrows = 0, short_id0 = 0, nps = 0, rec_cap = 0, nseg = 0, X = 0, herr = 0;
     uint32_t* segmask = nullptr;
     int32_t *home_len = nullptr, *nrec = nullptr, *rec_j = nullptr, *rec_j2 = nullptr, *np = nullptr, *piece_row = nullptr, *G = nullptr;
     unsigned long long *rec_key = nullptr, *rec_key2 = nullptr;
@@ -677,13 +682,15 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
         const int full = (P.n_src + HT_REAL - 1) / HT_REAL;      // tiers needed to give every source a slot
         if (T > full - 1) T = full - 1 > 0 ? full - 1 : 0;
         P.T = T; P.NH = (T + 1) * HT;
+        P.split = T >= 1 ? 1 : 0;
     }
+    tlo = P.split ? 0 : 1;
     be.pfor(n, HotF{so_ids, outdeg, hotslot_old, (P.T + 1) * HT_REAL});
     be.pfor((int64_t)(P.T + 1) * 64, TierSumF{so_ids, outdeg, (P.T + 1) * HT_REAL, n, tier_out});
     PRP_TRY(be.alloc((void**)&P.idslot, 4 * (size_t)P.NH));
     PRP_TRY(be.zero(P.idslot, 4 * (size_t)P.NH));
     be.pfor(n, RelabelF{sr_ids, P.new_of_old, P.old_of_new});
-    be.pfor(n, ByIdF{P.old_of_new, outdeg, hotslot_old, P.od_flags, P.hotslot, P.idslot, code});
+    be.pfor(n, ByIdF{P.old_of_new, outdeg, hotslot_old, P.od_flags, P.hotslot, P.idslot, code, P.split});
 
     // ---- 2. task sizes, the shard's rows
     P.lt = cfg.lt; P.st_cost = cfg.st_cost; P.slice_ovh = cfg.slice_ovh;
@@ -726,13 +733,14 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     nrows = nl + 32 * ns;
     short_id0 = P.g_n_long + 1 + 32 * P.s0;
     if (nrows >= (1 << 27)) { P.error = "pagerank plan: more than 2^27 rows in one shard"; rc = -1; goto done; }
-    rc_ = RowCtx{n, nl, P.jl0, short_id0, P.T, cfg.kmin, P.old_of_new, in.r_begin, in.r_node_idx, code};
+    rc_ = RowCtx{n, nl, P.jl0, short_id0, tlo, P.T, cfg.kmin, P.old_of_new, in.r_begin, in.r_node_idx, code};
 
     // ---- 3. pass 1 over the shard's reverse edges: (row, tier) counts -> segments, home lengths
     PRP_TRY(tmp.get(&segmask, (size_t)nrows + 1)); PRP_TRY(tmp.get(&home_len, (size_t)nrows + 32)); PRP_TRY(tmp.get(&nrec, 1));
     PRP_TRY(be.zero(nrec, 4)); PRP_TRY(be.zero(home_len, 4 * ((size_t)nrows + 32)));
     {
-        const int64_t cap = P.T ? std::min<int64_t>((int64_t)P.T * nrows, (int64_t)m / cfg.kmin + 1) + 1 : 1;
+        // a row has at most one record per tier, and a record stands for >= 1 (tier 0) / >= kmin entries
+        const int64_t cap = tlo <= P.T ? std::min<int64_t>((int64_t)(P.T + 1 - tlo) * nrows, (int64_t)m / (tlo == 0 ? 1 : cfg.kmin) + 1) + 1 : 1;
         if (cap > 0x7fffff00LL) { P.error = "pagerank plan: too many segment records"; rc = -1; goto done; }
         rec_cap = (int32_t)cap;
     }
@@ -740,16 +748,16 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     PRP_TRY(tmp.get(&rec_j, (size_t)rec_cap)); PRP_TRY(tmp.get(&rec_j2, (size_t)rec_cap));
     nps = (int32_t)std::min<int64_t>((int64_t)m / PIECE + nl + 2, 0x7fffff00LL);
     PRP_TRY(tmp.get(&np, (size_t)nl + 1)); PRP_TRY(tmp.get(&piece_row, (size_t)nps));
-    PRP_TRY(tmp.get(&G, (size_t)(P.T ? P.T : 1) * nps));
+    PRP_TRY(tmp.get(&G, (size_t)(P.T + 1) * nps));
     PRP_TRY(be.edges_ready());
     be.pfor((int64_t)32 * ns, CountShortF{rc_, segmask, home_len, nrec, rec_j, err, rec_key, rec_cap});
     be.pfor((int64_t)nl + 1, PieceNumF{rc_, np});
     PRP_TRY(be.scan_i32(np, (size_t)nl + 1));                               // np = piece_first from here on
     be.pfor(nps, PieceRowF{np, nl, piece_row});
-    if (P.T) {
-        PRP_TRY(be.zero(G, 4 * (size_t)P.T * nps));
+    if (tlo <= P.T) {
+        PRP_TRY(be.zero(G, 4 * (size_t)(P.T + 1) * nps));
         be.pfor(nps, PieceCountF{rc_, np, piece_row, nps, G});
-        PRP_TRY(be.scan_i32(G, (size_t)P.T * nps));
+        PRP_TRY(be.scan_i32(G, (size_t)(P.T + 1) * nps));
     }
     be.pfor(nl, LongRowF{rc_, np, G, nps, segmask, home_len, nrec, rec_j, err, rec_key, rec_cap});
     PRP_TRY(be.d2h(&nseg, nrec, 4));
@@ -761,7 +769,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     PRP_TRY(tmp.get(&tier_q, MAX_TIERS + 3)); PRP_TRY(tmp.get(&tier_mid, MAX_TIERS + 3));
     PRP_TRY(be.zero(tier_q, 4 * (MAX_TIERS + 3))); PRP_TRY(be.zero(tier_mid, 4 * (MAX_TIERS + 3)));
     if (nseg > 0) PRP_TRY(be.sort_u64(rec_key, rec_key2, rec_j, rec_j2, nseg, 64));
-    be.pfor(P.T + 1, TierBoundF{rec_key2, nseg, P.T, tier_q, tier_mid});
+    be.pfor(P.T + 2, TierBoundF{rec_key2, nseg, P.T, tier_q, tier_mid});
     PRP_TRY(tmp.get(&nparts, (size_t)nrows + 1)); PRP_TRY(tmp.get(&issplit, (size_t)nrows + 1));
     be.pfor((int64_t)nrows + 1, PartsF{segmask, nrows, nparts, issplit});
     PRP_TRY(be.scan_i32(nparts, (size_t)nrows + 1));                        // nparts = pslot from here on
@@ -796,7 +804,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
         // eoff indices: home long [0, nl], home slices [nl, nl + ns], tier t long [nl+ns+tq[t], nl+ns+tm[t]], sliced from there to tq[t+1]
         h_idx.clear();
         h_idx.push_back(0); h_idx.push_back(nl); h_idx.push_back(nl + ns);
-        for (int t = 1; t <= P.T; t++) { h_idx.push_back(nl + ns + h_tq[t]); h_idx.push_back(nl + ns + h_tm[t]); h_idx.push_back(nl + ns + h_tq[t + 1]); }
+        for (int t = 0; t <= P.T; t++) { h_idx.push_back(nl + ns + h_tq[t]); h_idx.push_back(nl + ns + h_tm[t]); h_idx.push_back(nl + ns + h_tq[t + 1]); }      // stream t + 1
         h_idx.push_back(X);
         h_val.assign(h_idx.size(), 0);
         PRP_TRY(tmp.get(&gidx, h_idx.size())); PRP_TRY(tmp.get(&gout, h_idx.size()));
@@ -806,7 +814,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
         P.EN = h_val.back();
         if (P.EN < 0) { P.error = "pagerank plan: entry array exceeds int32 offsets"; rc = -1; goto done; }
         int32_t sb = 0, lto = 0, sto = 0;
-        for (int s = 0; s <= P.T; s++) {
+        for (int s = 0; s <= P.T + 1; s++) {
             Stream& st = S[s];
             int32_t i_long, i_mid, i_end, v_long, v_mid, v_end;
             if (s == 0) { i_long = 0; i_mid = nl; i_end = nl + ns; v_long = h_val[0]; v_mid = h_val[1]; v_end = h_val[2]; }
@@ -829,22 +837,22 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
             st.n_stasks = n_st;
             st.n_big = n_big;
             st.st_off = sto; sto += st.n_stasks + 1;
-            st.meta_off = s == 0 ? 0 : h_tq[s];
-            st.n_rows = s == 0 ? nrows : h_tq[s + 1] - h_tq[s];
-            st.hot_off = s * HT;
+            st.meta_off = s == 0 ? 0 : h_tq[s - 1];
+            st.n_rows = s == 0 ? nrows : h_tq[s] - h_tq[s - 1];
+            st.hot_off = s == 0 ? 0 : (s - 1) * HT;
             st.i_mid = i_mid;
         }
         P.n_sbeg = sb; P.n_ltslots = lto; P.n_stslots = sto;
         PRP_TRY(be.alloc((void**)&P.sbeg, 4 * (size_t)sb)); PRP_TRY(tmp.get(&scost, (size_t)sb));
         PRP_TRY(be.alloc((void**)&P.ltask_row, 4 * (size_t)lto)); PRP_TRY(be.alloc((void**)&P.stask_slice, 4 * (size_t)sto));
-        for (int s = 0; s <= P.T; s++) {
+        for (int s = 0; s <= P.T + 1; s++) {
             Stream& st = S[s];
             const int32_t i_end = s == 0 ? nl + ns : h_idx[3 * s + 2];
             be.pfor((int64_t)st.n_slices + 1, SbegF{P.eoff, st.i_mid, s == 0 ? 1 : 32, st.n_slices, i_end, P.sbeg + st.sbeg_off});
             be.pfor((int64_t)st.n_slices + 1, SliceCostF{P.sbeg + st.sbeg_off, st.n_slices, P.slice_ovh, scost + st.sbeg_off});
         }
         PRP_TRY(be.scan_i32(scost, (size_t)sb));
-        for (int s = 0; s <= P.T; s++) {
+        for (int s = 0; s <= P.T + 1; s++) {
             Stream& st = S[s];
             be.pfor((int64_t)st.n_ltasks + 1, LtaskF{P.eoff + st.lbeg_off, st.n_long, st.n_ltasks, P.lt, st.e_long, P.ltask_row + st.lt_off});
             be.pfor((int64_t)st.n_stasks + 1, StaskF{scost + st.sbeg_off, st.n_slices, st.n_stasks, P.st_cost, st.n_big, s == 0 ? cfg.tail_shift : 0, P.stask_slice + st.st_off});
@@ -866,9 +874,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     {
         Stream* S = P.streams;
         int64_t seg_total = 0;
-        for (int s = 1; s <= P.T; s++) {
-            const int32_t i_long = h_idx[3 * s], i_end = h_idx[3 * s + 2];
-            (void)i_long; (void)i_end;
+        for (int s = 1; s <= P.T + 1; s++) {
             const int64_t slots = (int64_t)h_val[3 * s + 2] - h_val[3 * s];
             S[s].entries = (int32_t)std::min<int64_t>(slots, 0x7fffffff);
             seg_total += slots;
@@ -878,7 +884,8 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
         P.hot0_entries = (int64_t)((double)h_tier_out[0] * (frac < 1.0 ? frac : 1.0));
         const int64_t home_slots = (int64_t)h_val[2] - h_val[0];
         S[0].entries = (int32_t)std::min<int64_t>(home_slots, 0x7fffffff);
-        P.cold_entries = home_slots > P.hot0_entries ? home_slots - P.hot0_entries : 0;
+        // SPLIT: home holds cold entries only; MIXED: the tier-0 entries are in the home rows too
+        P.cold_entries = P.split ? home_slots : (home_slots > P.hot0_entries ? home_slots - P.hot0_entries : 0);
     }
 
     // ---- 8. diff_parts layout and the CTA schedule
@@ -889,8 +896,8 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     make_schedule(cfg, P);
     PRP_TRY(be.alloc((void**)&P.sched_dev, 4 * P.sched.size()));
     PRP_TRY(be.h2d(P.sched_dev, P.sched.data(), 4 * P.sched.size()));
-    PRP_TRY(be.alloc((void**)&P.streams_dev, sizeof(Stream) * (MAX_TIERS + 1)));
-    PRP_TRY(be.h2d(P.streams_dev, P.streams, sizeof(Stream) * (MAX_TIERS + 1)));
+    PRP_TRY(be.alloc((void**)&P.streams_dev, sizeof(Stream) * (MAX_TIERS + 2)));
+    PRP_TRY(be.h2d(P.streams_dev, P.streams, sizeof(Stream) * (MAX_TIERS + 2)));
     PRP_TRY(be.sync());
 done:
     if (rc != 0 && P.error.empty()) P.error = be.last_error();

@@ -107,21 +107,26 @@ int main(int argc, char** argv) {
     }
     const prp::Plan& P0 = plans[0];
     const int HT = prp::HT;
+    int sched_bad = 0;
     printf("N=%d M=%d T=%d world=%d: n_long %d n_pos %d n_src %d | rank0: EN %d (%.3f x M/world) segs %d split rows %d parts %d; sched:", n, m, P0.T, world,
            P0.g_n_long, P0.n_pos, P0.n_src, P0.EN, (double)P0.EN * world / m, P0.n_seg, P0.K, P0.n_parts);
-    for (int b = 0; b < 148; b++) if (P0.sched[(size_t)b * prp::SCHED_W]) { printf(" ["); for (int i = 0; i < prp::SCHED_W && P0.sched[(size_t)b * prp::SCHED_W + i]; i++) printf("%d ", P0.sched[(size_t)b * prp::SCHED_W + i]); printf("]"); }
-    printf("\n");
+    {   // every tier stream must be on some CTA's list; print CTAs per first stream
+        std::vector<int> first(prp::MAX_TIERS + 3, 0), seen(prp::MAX_TIERS + 3, 0);
+        for (int b = 0; b < 148; b++) { first[P0.sched[(size_t)b * prp::SCHED_W]]++; for (int i = 0; i < prp::SCHED_W; i++) seen[P0.sched[(size_t)b * prp::SCHED_W + i]] = 1; }
+        for (int s2 = 1; s2 <= P0.T + 1; s2++) { printf(" s%d:%d", s2, first[s2]); if (!seen[s2] && (P0.split || s2 == 1)) { printf("(UNSCHEDULED)"); sched_bad++; } }
+        printf(" split=%d\n", P0.split);
+    }
 
     // ---- check 1: edge coverage.  got[id] = multiset of source ids found in the streams
-    int bad = 0;
+    int bad = sched_bad;
     std::vector<std::vector<int32_t>> got((size_t)n + 1);
     std::vector<int32_t> slot_row;      // part slot -> row id (through pbeg / prow)
     for (int r = 0; r < world; r++) {
         const prp::Plan& P = plans[r];
         slot_row.assign((size_t)P.n_parts + 1, -1);
         for (int32_t k = 0; k < P.K; k++) for (int32_t s = P.pbeg[k]; s < P.pbeg[k + 1]; s++) slot_row[s] = P.prow[k];
-        auto decode = [&](int s, int32_t x) -> int32_t { return s == 0 ? (x < HT ? P.idslot[x] : x - HT) : P.idslot[s * HT + x]; };
-        for (int s = 0; s <= P.T; s++) {
+        auto decode = [&](int s, int32_t x) -> int32_t { return s == 0 ? (x < HT ? P.idslot[x] : x - HT) : P.idslot[(s - 1) * HT + x]; };
+        for (int s = 0; s <= P.T + 1; s++) {
             const prp::Stream& st = P.streams[s];
             if (st.e_long & 3) { printf("FAIL: stream %d long section not 16-byte aligned\n", s); bad++; }
             for (int32_t j = 0; j < st.n_long; j++) {
@@ -197,9 +202,9 @@ int main(int argc, char** argv) {
                 if (of & prp::OD_HOT) hout[P.hotslot[id]] = c;
             };
             auto home_finish = [&](int32_t id, double S) { if ((uint32_t)P.od_flags[id] & prp::OD_SPLIT) part[P.home_slot[id]] = S; else finish(id, S); };
-            for (int s = 0; s <= P.T; s++) {
+            for (int s = 0; s <= P.T + 1; s++) {
                 const prp::Stream& st = P.streams[s];
-                auto val = [&](int32_t x) -> double { return s == 0 ? (x < HT ? hin[x] : cin[x - HT]) : hin[s * HT + x]; };
+                auto val = [&](int32_t x) -> double { return s == 0 ? (x < HT ? hin[x] : cin[x - HT]) : hin[(s - 1) * HT + x]; };
                 for (int32_t j = 0; j < st.n_long; j++) {
                     double S = 0.0;
                     for (int32_t x = P.eoff[st.lbeg_off + j]; x < P.eoff[st.lbeg_off + j + 1]; x++) S += val(P.E[x]);

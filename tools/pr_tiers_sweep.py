@@ -1,5 +1,5 @@
 """Experiment driver: per-sweep time of the LJ-shaped graph for a list of plan settings (env switches of build_plan), one process each.
-usage: python tools/pr_tiers_sweep.py ["TIERS,KMIN,SCALE[,RSMEM,RMISS]" ...]"""
+usage: python tools/pr_tiers_sweep.py ["TIERS,KMIN,SCALE[,COLD_WARPS]" ...]"""
 import os, sys, subprocess
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if len(sys.argv) > 1 and sys.argv[1] == "one":
@@ -16,9 +16,10 @@ if len(sys.argv) > 1 and sys.argv[1] == "one":
         sys.argv[2], ms.min(), ms.mean(), ab / ms.mean() / 1e6, info.kernel_ms, pi["tiers"], pi["segments"], pi["split_rows"], pi["tier_ctas"],
         pi["cold_entries"] / 1e6, pi["hot0_entries"] / 1e6, pi["segment_entries"] / 1e6), flush=True)
 else:
-    cfgs = sys.argv[1:] or ["16,3,1.0", "0,3,1.0", "8,3,1.0", "24,3,1.0", "16,2,1.0", "16,4,1.0", "16,3,0.8", "16,3,1.25", "16,3,1.5"]
+    cfgs = sys.argv[1:] or ["16,3,1.0,12", "0,3,1.0", "16,4,1.0,12", "16,6,1.0,12", "16,3,1.0,8", "16,3,1.0,16", "16,3,1.0,20", "8,3,1.0,12", "24,3,1.0,12",
+                            "16,3,1.3,12", "16,2,1.0,12", "31,4,1.0,12"]
     for c in cfgs:
         f = c.split(",")
         env = dict(os.environ, GMC_PR_TIERS=f[0], GMC_PR_KMIN=f[1], GMC_PR_TIER_SCALE=f[2])
-        if len(f) >= 5: env["GMC_PR_RATES"] = f[3] + "," + f[4]
+        if len(f) >= 4: env["GMC_PR_COLD_WARPS"] = f[3]
         subprocess.run([sys.executable, __file__, "one", c], env=env)
