@@ -4,6 +4,7 @@
 #include <string.h>
 #include "gm_graph.h"
 #include "gm_cuda.h"
+#include "shl.h"
 
 int GM_SIZE_CHECK_VAR;   // the 32/32 link-time size-check symbol (reference gm_graph.cc:652)
 
@@ -24,10 +25,31 @@ gm_graph::~gm_graph() {
     delete_frozen_graph();
 }
 
+// the graph whose CSR the device group currently holds (and whether its reverse CSR is there)
+static const gm_graph* g_group_owner = NULL;
+static bool g_group_has_reverse = false;
+
 void gm_graph::invalidate_device_mirror() {
     if (_dev) gmc_graph_destroy(_dev);
     _dev = NULL;
     _dev_has_reverse = false;
+    if (g_group_owner == this) {
+        if (shl__device_group()) gmc_group_graph_free(shl__device_group());
+        g_group_owner = NULL;
+    }
+}
+
+struct gmc_group* gm_graph::group_mirror() {
+    gmc_group* grp = shl__device_group();
+    if (!grp) return NULL;
+    if (!_frozen) freeze();
+    if (g_group_owner != this || (_reverse_edge && !g_group_has_reverse)) {
+        dev_check(gmc_group_graph_upload(grp, _numNodes, _numEdges, begin, node_idx, _reverse_edge ? r_begin : NULL,
+                                         _reverse_edge ? r_node_idx : NULL), "group_mirror(upload)");
+        g_group_owner = this;
+        g_group_has_reverse = _reverse_edge;
+    }
+    return grp;
 }
 
 gmc_graph* gm_graph::device_mirror() {

@@ -8,6 +8,26 @@ void hop_dist(gm_graph& G, int32_t* G_dist, node_t& root) {
     gm_rt_initialize();
     G.freeze();
 
+    if (gmc_group* grp = G.group_mirror()) {      // GM_CUDA_DEVICES > 1: vertex-range shards over the device group
+        shl__start_timer(10);
+        shl__end_timer("SHOAL_Copyin");
+        gmc_bfs_info ginfo;
+        shl__start();
+        if (G.num_nodes() > 0 && gmc_group_hop_dist(grp, root, G_dist, &ginfo) != GMC_OK) {
+            fprintf(stderr, "hop_dist: %s\n", gmc_last_error());
+            exit(EXIT_FAILURE);
+        }
+        shl__end();
+        if (G.num_nodes() > 0) {
+            int ndev = 0;
+            gmc_group_size(grp, &ndev);
+            printf("hop_dist: levels=%d reached=%d edges=%lld bottom_up_levels=%d device_ms=%.3f launches=%d devices=%d\n", ginfo.levels,
+                   ginfo.reached, (long long)ginfo.edges_traversed, ginfo.bottom_up_levels, ginfo.kernel_ms, ginfo.launches, ndev);
+        }
+        printf("CRC shl__G_dist 0x%04x\n", (unsigned)shl__crc16(G_dist, sizeof(int32_t) * (size_t)G.num_nodes()));
+        gm_rt_cleanup();
+        return;
+    }
     shl__start_timer(10);
     gmc_graph* dev = G.device_mirror();
     shl_array<int32_t>* a_dist = shl__malloc_array<int32_t>(G.num_nodes(), "shl__G_dist", false, false, true, false, true, true);

@@ -14,6 +14,28 @@ void pagerank(gm_graph& G, double e, double d, int32_t max, double* G_pg_rank) {
     G.freeze();
     G.make_reverse_edges();
 
+    if (gmc_group* grp = G.group_mirror()) {
+        // GM_CUDA_DEVICES > 1: the same procedure over the device group -- copy-in = every device takes 1/N of the CSR over
+        // its own PCIe link + NVLink allgather; the loop nest = sharded sweeps with the exchange fused into the epilogue;
+        // copy-back = every device writes its slice of rank[] into G_pg_rank
+        shl__start_timer(10);
+        shl__end_timer("SHOAL_Copyin");
+        gmc_pagerank_info ginfo;
+        shl__start();
+        if (G.num_nodes() > 0 && gmc_group_pagerank(grp, e, d, max, G_pg_rank, &ginfo) != GMC_OK) {
+            fprintf(stderr, "pagerank: %s\n", gmc_last_error());
+            exit(EXIT_FAILURE);
+        }
+        shl__end();
+        if (G.num_nodes() > 0) {
+            int ndev = 0;
+            gmc_group_size(grp, &ndev);
+            printf("pagerank: iterations=%d diff=%.6e device_ms=%.3f launches=%d devices=%d\n", ginfo.iterations, ginfo.diff, ginfo.kernel_ms, ginfo.launches, ndev);
+        }
+        printf("CRC shl__G_pg_rank 0x%04x\n", (unsigned)shl__crc16(G_pg_rank, sizeof(double) * (size_t)G.num_nodes()));
+        gm_rt_cleanup();
+        return;
+    }
     shl__start_timer(10);
     gmc_graph* dev = G.device_mirror();   // copy-in of begin / r_begin / r_node_idx (no-op when resident)
     shl_array<double>* a_rank = shl__malloc_array<double>(G.num_nodes(), "shl__G_pg_rank", false, false, true, false, true, true);

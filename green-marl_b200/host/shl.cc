@@ -11,6 +11,7 @@
 #include "gm_cuda.h"
 
 static int g_device = -1;
+static gmc_group* g_group = NULL;      // GM_CUDA_DEVICES > 1: every generated procedure runs over this device group
 static struct timeval g_t_compute, g_t_timer;
 static double g_compute_ms = 0.0;
 
@@ -31,6 +32,17 @@ int shl__init(int nthreads, int partitioned) {
         exit(EXIT_FAILURE);   // libgm_cuda has no CPU path
     }
     g_device = dev;
+    // Placement switch of the reference (shl__init(nthreads, partitioned); run.sh -p / -r) re-targeted: GM_CUDA_DEVICES=N
+    // runs the generated procedures over N B200s of this box -- CSR replicated, rows partitioned (csrc/gmc_group.cu)
+    int ndev = 1;
+    if (const char* nd = getenv("GM_CUDA_DEVICES")) ndev = atoi(nd);
+    if (ndev > 1 && !g_group) {
+        if (gmc_group_create(&g_group, ndev, NULL) != GMC_OK) {
+            fprintf(stderr, "shl__init: GM_CUDA_DEVICES=%d: %s\n", ndev, gmc_last_error());
+            exit(EXIT_FAILURE);
+        }
+        printf("SHOAL (libgm_cuda) device group: %d devices, CSR replicated, rows partitioned by destination range\n", ndev);
+    }
     int sms = 0;
     size_t total = 0, avail = 0;
     gmc_device_info(&sms, &total, &avail);
@@ -55,6 +67,7 @@ double shl__step_timer(const char* label) {
 }
 double shl__end_timer(const char* label) { return shl__step_timer(label); }
 int shl__get_rep_id(void) { return g_device < 0 ? 0 : g_device; }
+struct gmc_group* shl__device_group(void) { return g_group; }
 void* shl__alloc_memory(size_t bytes) { return malloc(bytes); }
 
 // CRC-16/CCITT-FALSE (poly 0x1021, init 0xFFFF).  The polynomial libshoal's print_crc uses cannot be

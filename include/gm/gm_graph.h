@@ -107,6 +107,9 @@ class gm_graph {
     // ---- device mirror (new) ----
     gmc_graph* device_mirror();          // creates / refreshes the HBM copy of the frozen CSR (+ reverse CSR)
     void invalidate_device_mirror();
+    // GM_CUDA_DEVICES > 1: the frozen CSR (+ reverse CSR when built) replicated on every device of the group
+    // (shl__device_group()); returns NULL when no group is active.  The group holds one graph at a time.
+    struct gmc_group* group_mirror();
 
   private:
     void delete_frozen_graph();

@@ -24,6 +24,10 @@ double shl__step_timer(const char* label);
 double shl__end_timer(const char* label);
 int shl__get_rep_id(void);
 void* shl__alloc_memory(size_t bytes);
+// libgm_cuda extension: the device group selected at shl__init (GM_CUDA_DEVICES=2|4|8), NULL when one device is used.
+// The reference chooses NUMA placement at the same point (common_main.h:95-99, scripts/run.sh -r / -p).
+struct gmc_group;
+struct gmc_group* shl__device_group(void);
 #ifdef __cplusplus
 }
 class Timer {

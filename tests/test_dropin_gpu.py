@@ -14,10 +14,11 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 BIN = os.path.join(ROOT, "green-marl_b200", "bin")
 
 
-def run(exe, *args):
+def run(exe, *args, env=None):
     path = os.path.join(BIN, exe)
     assert os.path.exists(path), f"{path} missing: run __graft_entry__.build() where /root/reference is present"
-    r = subprocess.run([path] + [str(a) for a in args], capture_output=True, text=True, timeout=300)
+    r = subprocess.run([path] + [str(a) for a in args], capture_output=True, text=True, timeout=300,
+                       env=dict(os.environ, **env) if env else None)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     return r.stdout
 
@@ -59,3 +60,28 @@ def test_triangle_counting_driver_unchanged(gm, oracle, tmp_path):
     out = run("triangle_counting", f, 4, "/dev/null")
     got = re.findall(r"number of triangles: (-?\d+)", out)
     assert got and int(got[0]) == oracle.triangle_counting(b, i)
+
+
+@pytest.mark.parametrize("ndev", [2, 4, 8])
+def test_reference_drivers_on_a_device_group(gm, oracle, tmp_path, ndev):
+    """GM_CUDA_DEVICES=N: the same unchanged drivers over N GPUs of the box (device group selected in shl__init, the
+    reference's placement switch, common_main.h:95-99): same printed values as the oracle"""
+    if gm.device_count() < ndev:
+        pytest.skip(f"needs {ndev} GPUs")
+    f = str(tmp_path / "r.bin")
+    b, i = oracle.rmat(200000, 3000000, 1997, 0.57, 0.19, 0.19, True)
+    assert oracle.store_binary(f, b, i)
+    i = np.ascontiguousarray(i).copy()
+    oracle.semi_sort(b, i)
+    rb, ri = oracle.make_reverse(b, i)
+    env = {"GM_CUDA_DEVICES": str(ndev), "GMC_PR_TIER_MIN_EDGES": "0"}
+    out = run("pagerank", f, 4, "/dev/null", 20, 1e-30, 0.85, env=env)
+    rank, it, _ = oracle.pagerank(b, rb, ri, 1e-30, 0.85, 20)
+    got = [float(x) for x in re.findall(r"rank\[\d\] = ([0-9.]+)", out)]
+    assert got == [float("%0.9f" % v) for v in rank[:4]]
+    assert f"devices={ndev}" in out and "device group" in out
+    out = run("hop_dist", f, 4, "/dev/null", env=env)
+    dist, _ = oracle.hop_dist(b, i, 0)
+    got = [int(x) for x in re.findall(r"dist\[\d\] = (-?\d+)", out)]
+    assert got == [int(v) for v in dist[:10]]
+    assert f"devices={ndev}" in out
