@@ -38,7 +38,21 @@ constexpr int TD_CHUNK = 256;        // edge slots per warp chunk (8 per lane)
 constexpr int TD_BATCHED_MAX_FRONTIER = 8192;   // owned frontier vertices up to which td_expand batches a lane's 8 loads
 constexpr unsigned FULLMASK = 0xffffffffu;
 
+// Device-side traversal control (single-GPU runs): the reference's level-to-level state machine (get_next_state,
+// gm_bfs_template.h:352-421) is evaluated by the last block of bfs_finish, so the host enqueues the kernels of several
+// levels at once -- each kernel looks at the state and leaves at once when the level is not its kind -- instead of waiting
+// for the counts of every level (~25 us of launch + PCIe round trip per level, 8 levels per traversal on the LJ-shaped graph).
+constexpr int BFS_TRACE_CAP = 1024;
+struct BfsCtl {
+    int32_t state, curr_level, curr_count, own_count, qi, done, n_trace, overflow;
+    float thr;
+    int32_t has_reverse, rrd_direct, pad;
+    int32_t trace_state[BFS_TRACE_CAP], trace_count[BFS_TRACE_CAP];
+};
+__device__ __forceinline__ bool ctl_bottom_up(int st) { return st == ST_RRD || st == ST_RR2Q; }
+
 struct gmc_bfs_ws {
+    BfsCtl* ctl = nullptr;            // device
     int32_t N = 0;
     int32_t words = 0;                // ceil(N/32)
     int world = 1;
@@ -70,7 +84,7 @@ void gmc_bfs_ws_free(gmc_graph* g) {
     if (!w) return;
     cudaFree(w->visited); cudaFree(w->frontier_bm); cudaFree(w->cand); cudaFree(w->allcand);
     cudaFree(w->queue[0]); cudaFree(w->queue[1]); cudaFree(w->blk_off); cudaFree(w->blk_total); cudaFree(w->chunks);
-    cudaFree(w->counters); cudaFree(w->level); cudaFree(w->edge_sum);
+    cudaFree(w->counters); cudaFree(w->level); cudaFree(w->edge_sum); cudaFree(w->ctl);
     if (w->h_counters) cudaFreeHost(w->h_counters);
     delete w;
     g->bfs = nullptr;
@@ -91,14 +105,28 @@ __global__ void bfs_init(L* __restrict__ level, int32_t n, L invalid, int32_t ro
     if (i == 0) { if (root_owned) queue[0] = root; counters[0] = 0; counters[1] = 0; counters[2] = 0; counters[3] = 0; }
 }
 
+__global__ void bfs_ctl_init(BfsCtl* ctl, float thr, int has_reverse, int rrd_direct) {
+    ctl->state = ST_SMALL; ctl->curr_level = 0; ctl->curr_count = 1; ctl->own_count = 1; ctl->qi = 0; ctl->done = 0;
+    ctl->n_trace = 1; ctl->overflow = 0; ctl->thr = thr; ctl->has_reverse = has_reverse; ctl->rrd_direct = rrd_direct;
+    ctl->trace_state[0] = ST_SMALL; ctl->trace_count[0] = 1;
+}
+
 // ---- top-down, step 1: degrees of the queued vertices -> CTA-relative offsets + chunk descriptors ----------
 __global__ void __launch_bounds__(BFS_THREADS)
 td_prepare(const int32_t* __restrict__ begin, const int32_t* __restrict__ queue, int32_t qcount, int32_t* __restrict__ blk_off,
-           int32_t* __restrict__ blk_total, int2* __restrict__ chunks, int32_t* __restrict__ nchunks) {
+           int32_t* __restrict__ blk_total, int2* __restrict__ chunks, int32_t* __restrict__ nchunks,
+           const int32_t* __restrict__ queue_alt = nullptr, const BfsCtl* __restrict__ ctl = nullptr) {
     __shared__ int32_t s_warp[BFS_THREADS / 32];
     __shared__ int32_t s_c0;
+    if (ctl) {     // device-driven traversal: a top-down level? then the owned frontier is queue[qi], own_count long
+        if (ctl->done || ctl_bottom_up(ctl->state)) return;
+        qcount = ctl->own_count;
+        if (ctl->qi) queue = queue_alt;
+    }
+    for (int32_t qblk = blockIdx.x; qblk * BFS_THREADS < qcount; qblk += gridDim.x) {
+    __syncthreads();
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int32_t qi = blockIdx.x * BFS_THREADS + tid;
+    const int32_t qi = qblk * BFS_THREADS + tid;
     int32_t deg = 0;
     if (qi < qcount) { const int32_t v = queue[qi]; deg = begin[v + 1] - begin[v]; }
     int32_t inc = deg;
@@ -111,10 +139,11 @@ td_prepare(const int32_t* __restrict__ begin, const int32_t* __restrict__ queue,
     for (int k = 0; k < BFS_THREADS / 32; k++) { const int32_t t = s_warp[k]; if (k < wid) woff += t; total += t; }
     if (qi < qcount) blk_off[qi] = inc - deg + woff;
     const int32_t nch = (total + TD_CHUNK - 1) / TD_CHUNK;
-    if (tid == 0) { blk_total[blockIdx.x] = total; s_c0 = nch ? atomicAdd(nchunks, nch) : 0; }
+    if (tid == 0) { blk_total[qblk] = total; s_c0 = nch ? atomicAdd(nchunks, nch) : 0; }
     __syncthreads();
     const int32_t c0 = s_c0;
-    for (int32_t k = tid; k < nch; k += BFS_THREADS) chunks[c0 + k] = make_int2((int)blockIdx.x, k);
+    for (int32_t k = tid; k < nch; k += BFS_THREADS) chunks[c0 + k] = make_int2((int)qblk, k);
+    }
 }
 
 // first k in [0,32] with e_k > pos (lane k holds e_k, ascending)
@@ -135,8 +164,14 @@ __global__ void __launch_bounds__(BFS_THREADS)
 td_expand(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_idx, const int32_t* __restrict__ queue, int32_t qcount,
           const int32_t* __restrict__ blk_off, const int32_t* __restrict__ blk_total, const int2* __restrict__ chunks,
           const int32_t* __restrict__ nchunks_p, const uint32_t* __restrict__ visited, uint32_t* __restrict__ cand,
-          const uint8_t* __restrict__ edge_mask) {
+          const uint8_t* __restrict__ edge_mask, const int32_t* __restrict__ queue_alt = nullptr, const BfsCtl* __restrict__ ctl = nullptr) {
     const int lane = threadIdx.x & 31;
+    if (ctl) {     // device-driven traversal: both forms are enqueued, the one that fits the frontier runs
+        if (ctl->done || ctl_bottom_up(ctl->state)) return;
+        qcount = ctl->own_count;
+        if ((qcount <= TD_BATCHED_MAX_FRONTIER) != BATCHED) return;
+        if (ctl->qi) queue = queue_alt;
+    }
     const int32_t nchunks = *nchunks_p;
     const int32_t nwarps = (gridDim.x * BFS_THREADS) >> 5;
     for (int32_t c = (blockIdx.x * BFS_THREADS + threadIdx.x) >> 5; c < nchunks; c += nwarps) {
@@ -224,10 +259,12 @@ td_expand(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_id
 // ---- bottom-up: warp w owns vertices [32w, 32w+32) = one word of the bitmaps ------------------------------------
 __global__ void __launch_bounds__(BFS_THREADS)
 bu_scan(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t w_lo, int32_t w_hi,
-        const uint32_t* __restrict__ frontier_bm, const uint32_t* __restrict__ visited, uint32_t* __restrict__ cand) {
+        const uint32_t* __restrict__ frontier_bm, const uint32_t* __restrict__ visited, uint32_t* __restrict__ cand,
+        const BfsCtl* __restrict__ ctl = nullptr) {
     const int lane = threadIdx.x & 31;
-    const int32_t w = w_lo + ((blockIdx.x * BFS_THREADS + threadIdx.x) >> 5);
-    if (w >= w_hi) return;
+    if (ctl && (ctl->done || !ctl_bottom_up(ctl->state))) return;
+    const int32_t wstep = (gridDim.x * BFS_THREADS) >> 5;
+    for (int32_t w = w_lo + ((blockIdx.x * BFS_THREADS + threadIdx.x) >> 5); w < w_hi; w += wstep) {
     const uint32_t vis = visited[w];
     const int32_t t = (w << 5) + lane;
     bool found = false;
@@ -240,6 +277,7 @@ bu_scan(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_
     }
     const uint32_t got = __ballot_sync(FULLMASK, found);
     if (lane == 0) cand[w] = got;
+    }
 }
 
 // ---- end of level: new = candidates & ~visited -> visited, frontier, level[], owned queue, count ------------------
@@ -248,8 +286,16 @@ __global__ void __launch_bounds__(BFS_THREADS)
 bfs_finish(int32_t words, int32_t wp, int world, int use_all, uint32_t* __restrict__ cand, const uint32_t* __restrict__ allcand,
            uint32_t* __restrict__ visited, uint32_t* __restrict__ frontier, L next_level, L* __restrict__ level,
            int32_t own_lo, int32_t own_hi, int32_t* __restrict__ next_queue, int32_t* __restrict__ counters,
-           volatile int32_t* __restrict__ host_out, int32_t seq) {
+           volatile int32_t* __restrict__ host_out, int32_t seq, int32_t* __restrict__ queue_alt = nullptr, BfsCtl* ctl = nullptr) {
     const int lane = threadIdx.x & 31;
+    if (ctl) {     // device-driven traversal: level number and queue come from the control block
+        if (ctl->done) {      // the traversal ended earlier in this batch of launches: only tell the host
+            if (blockIdx.x == 0 && threadIdx.x == 0) { host_out[1] = 1; __threadfence_system(); host_out[2] = seq; }
+            return;
+        }
+        next_level = (L)(ctl->curr_level + 1);
+        if (!ctl->qi) next_queue = queue_alt;       // next = queue[qi ^ 1]; next_queue = queue[0], queue_alt = queue[1]
+    }
     const int32_t w = blockIdx.x * BFS_THREADS + threadIdx.x;
     uint32_t nw = 0;
     if (w < words) {
@@ -304,9 +350,44 @@ bfs_finish(int32_t words, int32_t wp, int world, int use_all, uint32_t* __restri
     __syncthreads();
     if (s_last && threadIdx.x == 0) {
         __threadfence();
-        host_out[0] = atomicAdd(&counters[0], 0);
-        host_out[1] = atomicAdd(&counters[1], 0);
+        const int32_t next_count = atomicAdd(&counters[0], 0), own = atomicAdd(&counters[1], 0);
         counters[0] = 0; counters[1] = 0; counters[2] = 0; counters[3] = 0;
+        if (!ctl) { host_out[0] = next_count; host_out[1] = own; }
+        else {
+            // get_next_state (gm_bfs_template.h:352-421), same arithmetic as the host loop of run_bfs
+            const int state = ctl->state;
+            const int32_t curr_count = ctl->curr_count;
+            const float thr = ctl->thr;
+            const bool has_reverse = ctl->has_reverse != 0, rrd_direct = ctl->rrd_direct != 0;
+            int next_state = state, done = next_count == 0;
+            switch (state) {
+                case ST_SMALL: if (next_count >= 128) next_state = ST_QUE; break;
+                case ST_QUE:
+                    if ((float)next_count >= thr) next_state = rrd_direct ? ST_RRD : ST_RD;
+                    else if (next_count >= 1024 && next_count >= curr_count * 5) next_state = ST_Q2R;
+                    break;
+                case ST_Q2R: next_state = (rrd_direct && (float)next_count >= thr) ? ST_RRD : ST_RD; break;
+                case ST_RD:
+                    if (has_reverse && (float)next_count >= thr) next_state = ST_RRD;
+                    else if (next_count <= 2 * curr_count) next_state = ST_R2Q;
+                    break;
+                case ST_R2Q: next_state = ST_QUE; break;
+                case ST_RRD: if (next_count <= 2 * curr_count) next_state = ST_RR2Q; break;
+                case ST_RR2Q: next_state = ST_QUE; break;
+            }
+            if (!done) {
+                const int32_t k = ctl->n_trace;
+                if (k >= BFS_TRACE_CAP) { ctl->overflow = 1; done = 1; }
+                else {
+                    ctl->trace_state[k] = next_state; ctl->trace_count[k] = next_count; ctl->n_trace = k + 1;
+                    ctl->state = next_state; ctl->curr_count = next_count; ctl->own_count = own;
+                    ctl->curr_level = ctl->curr_level + 1; ctl->qi = ctl->qi ^ 1;
+                }
+            }
+            ctl->done = done;
+            __threadfence();
+            host_out[0] = next_count; host_out[1] = done;
+        }
         __threadfence_system();
         host_out[2] = seq;
     }
@@ -347,6 +428,7 @@ int ensure_ws(gmc_graph* g, int world) {
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->counters, sizeof(int32_t) * 8);
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->level, sizeof(int32_t) * nn);
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->edge_sum, sizeof(unsigned long long));
+    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->ctl, sizeof(BfsCtl));
     if (rc == GMC_OK && cudaMallocHost((void**)&w->h_counters, sizeof(int32_t) * 8) != cudaSuccess) {
         set_error("bfs: cudaMallocHost failed"); rc = GMC_ERR_NOMEM;
     }
@@ -390,7 +472,62 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     const float thr = (float)n * 0.05f;   // RRD_THRESHOLD, gm_bfs_template.h:359 (float arithmetic as in the reference)
     const unsigned fin_grid = (unsigned)div_up(w->words, BFS_THREADS);
     const unsigned exp_grid = (unsigned)sm_count() * 8;
-    for (;;) {
+    bool device_driven = world == 1 && getenv("GMC_BFS_HOST_LOOP") == nullptr;
+    if (device_driven) {
+        // Single GPU: the kernels of several levels are enqueued back to back, the state machine runs on the device
+        // (BfsCtl); the host only looks at the `done` word the last bfs_finish of a batch publishes.
+        BfsCtl* ctl = w->ctl;
+        bfs_ctl_init<<<1, 1, 0, st>>>(ctl, thr, has_reverse ? 1 : 0, rrd_direct ? 1 : 0);
+        launches++;
+        const unsigned prep_grid = (unsigned)sm_count() * 4, scan_grid = (unsigned)sm_count() * 16;
+        int batch = 5;          // levels per batch: most traversals of a power-law graph end within 6..9 levels
+        bool done = false;
+        for (int guard = 0; !done && guard < BFS_TRACE_CAP + 8; guard += batch, batch = 2) {
+            for (int b = 0; b < batch; b++) {
+                if (has_reverse) { bu_scan<<<scan_grid, BFS_THREADS, 0, st>>>(rev_begin, rev_idx, n, own_lo, own_hi, w->frontier_bm, w->visited, w->cand, ctl); launches++; }
+                td_prepare<<<prep_grid, BFS_THREADS, 0, st>>>(fwd_begin, w->queue[0], 0, w->blk_off, w->blk_total, w->chunks, w->counters + 2, w->queue[1], ctl);
+                td_expand<true><<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[0], 0, w->blk_off, w->blk_total, w->chunks,
+                                                                  w->counters + 2, w->visited, w->cand, edge_mask, w->queue[1], ctl);
+                td_expand<false><<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[0], 0, w->blk_off, w->blk_total, w->chunks,
+                                                                   w->counters + 2, w->visited, w->cand, edge_mask, w->queue[1], ctl);
+                bfs_finish<L><<<fin_grid, BFS_THREADS, 0, st>>>(w->words, w->wp, 1, 0, w->cand, w->allcand, w->visited, w->frontier_bm, (L)0, level,
+                                                                own_lo, own_hi, w->queue[0], w->counters, w->h_counters, ++w->seq, w->queue[1], ctl);
+                launches += 4;
+            }
+            GMC_CUDA(cudaGetLastError());
+            volatile int32_t* h = w->h_counters;
+            unsigned spins = 0;
+            while (h[2] != w->seq) {
+                if ((++spins & 0x3fffu) == 0) {
+                    const cudaError_t q = cudaStreamQuery(st);
+                    if (q != cudaErrorNotReady && q != cudaSuccess) { set_error("bfs: %s", cudaGetErrorString(q)); return GMC_ERR_CUDA; }
+                    if (q == cudaSuccess && h[2] != w->seq) { set_error("bfs: level counts were not published"); return GMC_ERR_CUDA; }
+                }
+            }
+            __sync_synchronize();
+            done = h[1] != 0;
+        }
+        GMC_CUDA(cudaEventRecord(ev1, st));
+        static thread_local BfsCtl hc;
+        GMC_CUDA(cudaMemcpyAsync(&hc, ctl, sizeof(BfsCtl), cudaMemcpyDeviceToHost, st));
+        GMC_CUDA(cudaStreamSynchronize(st));
+        if (!done || hc.overflow) device_driven = false;       // more levels than the trace holds: the host-driven loop below takes over
+        else {
+            for (int k = 0; k < hc.n_trace; k++) {
+                w->state_trace.push_back(hc.trace_state[k]); w->level_count.push_back(hc.trace_count[k]);
+                if (hc.trace_state[k] == ST_RRD || hc.trace_state[k] == ST_RR2Q) bottom_up++;
+            }
+            curr_level = hc.n_trace - 1;
+            GMC_REQUIRE(sizeof(L) == 4 || curr_level + 1 <= 32767, GMC_ERR_STATE, "bfs: more levels than level_t can hold");
+        }
+        if (!device_driven) {       // start over on the host-driven path
+            GMC_CUDA(cudaEventRecord(ev0, st));
+            bfs_init<L><<<div_up(max(n, w->wp), 256), 256, 0, st>>>(level, n, invalid, root, w->visited, w->frontier_bm, w->cand, w->wp,
+                                                                      w->queue[0], root_owned ? 1 : 0, w->counters);
+            launches++; bottom_up = 0;
+        }
+    }
+    for (; !device_driven;) {
         w->state_trace.push_back(state);
         w->level_count.push_back(curr_count);
         GMC_REQUIRE(sizeof(L) == 4 || curr_level + 1 <= 32767, GMC_ERR_STATE, "bfs: more levels than level_t can hold");
@@ -463,7 +600,7 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
         curr_level++;
         state = next_state;
     }
-    GMC_CUDA(cudaEventRecord(ev1, st));
+    if (!device_driven) GMC_CUDA(cudaEventRecord(ev1, st));
     GMC_CUDA(cudaStreamSynchronize(st));
     w->valid = true;
     w->last_is_i16 = sizeof(L) == 2;

@@ -368,3 +368,24 @@ def test_pagerank_tiered_emulated_shards(gm, oracle, g_rmat, monkeypatch):
     want, it, _ = oracle.pagerank(g_rmat["begin"], g_rmat["r_begin"], g_rmat["r_node_idx"], 1e-30, 0.85, 20)
     assert info.iterations == it
     assert np.abs(rank - want).max() <= 1e-15
+
+
+def test_bfs_host_loop_and_deep_graph(gm, oracle, g_rmat, monkeypatch):
+    """single-GPU traversals are device-driven (state machine in bfs_finish, kernels of several levels enqueued at once); the
+    host-driven loop (multi-GPU runs, GMC_BFS_HOST_LOOP=1, graphs deeper than the device trace) must give the same levels and
+    trace.  A path graph of 3000 vertices has 3000 levels: more than the device trace holds -> falls back to the host loop."""
+    root = graphs.first_root_with_edges(g_rmat)
+    lev, _, trace, cnt = dev_graph(gm, g_rmat).bfs_levels(root)
+    monkeypatch.setenv("GMC_BFS_HOST_LOOP", "1")
+    lev2, _, trace2, cnt2 = dev_graph(gm, g_rmat).bfs_levels(root)
+    monkeypatch.delenv("GMC_BFS_HOST_LOOP")
+    assert np.array_equal(lev, lev2) and list(trace) == list(trace2) and list(cnt) == list(cnt2)
+    n = 3000
+    begin = np.minimum(np.arange(n + 1), n - 1).astype(np.int32)          # v -> v + 1
+    idx = np.arange(1, n, dtype=np.int32)
+    dg = gm.graph_from_csr(begin, idx, semi_sort=True, make_reverse=True)
+    dist, info = dg.hop_dist(0)
+    assert np.array_equal(dist, np.arange(n, dtype=np.int32)) and info.levels == n
+    dist, info = dg.hop_dist(n - 200)                                     # 200 levels: inside the device trace
+    want = np.full(n, INT_MAX, np.int32); want[n - 200:] = np.arange(200)
+    assert np.array_equal(dist, want) and info.levels == 200
