@@ -389,3 +389,47 @@ def test_bfs_host_loop_and_deep_graph(gm, oracle, g_rmat, monkeypatch):
     dist, info = dg.hop_dist(n - 200)                                     # 200 levels: inside the device trace
     want = np.full(n, INT_MAX, np.int32); want[n - 200:] = np.arange(200)
     assert np.array_equal(dist, want) and info.levels == 200
+
+
+def _ks(a, b):
+    """Kolmogorov-Smirnov distance of two integer samples (max gap of their CDFs)"""
+    hi = int(max(a.max(), b.max())) + 1
+    ca = np.cumsum(np.bincount(a, minlength=hi)) / len(a)
+    cb = np.cumsum(np.bincount(b, minlength=hi)) / len(b)
+    return float(np.abs(ca - cb).max())
+
+
+def test_device_generator_matches_reference_distribution(gm, oracle):
+    """the device R-MAT generator makes every benchmarked graph: its in- and out-degree distributions must be the reference
+    generator's (create_RMAT_graph, graph_gen.cc:159-287, restated edge for edge by the oracle) -- KS distance of the degree
+    CDFs <= 0.01, share of vertices without in-edges (it sets the roofline bytes) within 1 point, top-0.1 % edge share within
+    2 points, maximum degree within 15 % -- at 2^18 vertices / 2^22 edges, three seeds against one reference graph"""
+    n, m = 1 << 18, 1 << 22
+    rb, ri = oracle.rmat(n, m, 1997, 0.57, 0.19, 0.19, True)
+    ref_out = np.diff(rb).astype(np.int64)
+    ref_in = np.bincount(ri, minlength=n).astype(np.int64)
+    for seed in (1997, 5, 77):
+        dg = gm.generate_rmat(n, m, seed=seed)
+        b, i = dg.array("begin"), dg.array("node_idx")
+        out_d = np.diff(b).astype(np.int64)
+        in_d = np.bincount(i, minlength=n).astype(np.int64)
+        for name, d, r in (("out", out_d, ref_out), ("in", in_d, ref_in)):
+            assert _ks(d, r) <= 0.01, (seed, name, _ks(d, r))
+            assert abs(float((d == 0).mean()) - float((r == 0).mean())) <= 0.01, (seed, name)
+            top = lambda x: np.sort(x)[::-1][:n // 1000].sum() / m
+            assert abs(top(d) - top(r)) <= 0.02, (seed, name, top(d), top(r))
+            assert abs(d.max() - r.max()) <= 0.15 * r.max(), (seed, name, d.max(), r.max())
+
+
+def test_device_generator_golden_digest(gm):
+    """bit-for-bit reproducibility of the device generator across rounds: sha-256 of the generated CSR against the committed
+    fixture (tests/golden/device_rmat_digest.json, written by tools/gen_digest.py on a B200)"""
+    import hashlib, json, os
+    p = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "device_rmat_digest.json")
+    if not os.path.exists(p):
+        pytest.skip("fixture not generated yet (tools/gen_digest.py)")
+    for name, want in json.load(open(p)).items():
+        dg = gm.generate_rmat(want["n"], want["m"], seed=want["seed"])
+        b, i = dg.array("begin"), dg.array("node_idx")
+        assert hashlib.sha256(np.ascontiguousarray(b).tobytes()).hexdigest() == want["sha256_begin"], name
+        assert hashlib.sha256(np.ascontiguousarray(i).tobytes()).hexdigest() == want["sha256_node_idx"], name
