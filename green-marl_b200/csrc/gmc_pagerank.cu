@@ -677,6 +677,13 @@ struct CudaBackend {
                 if (cudaStreamWaitEvent(st, g->pending->chunk[c], 0) != cudaSuccess) return fail("wait for edges");
         return 0;
     }
+    int edge_chunks() { return g->pending ? g->pending->nchunks : 1; }
+    int edge_chunk_ready(int c, int32_t* e_end) {
+        if (!g->pending) { *e_end = g->M; return 0; }
+        if (cudaStreamWaitEvent(st, g->pending->chunk[c], 0) != cudaSuccess) return fail("wait for edges");
+        *e_end = g->pending->end[c];
+        return 0;
+    }
     std::string last_error() { return err.empty() ? std::string(gmc_last_error()) : err; }
     template <class F>
     void pfor(int64_t n, const F& f) {

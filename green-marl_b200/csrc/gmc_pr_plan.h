@@ -284,10 +284,13 @@ struct CountShortF {   // item i: short row r = nl + i
     int32_t *home_len, *nrec, *rec_j, *err;
     unsigned long long* rec_key;
     int32_t rec_cap;
+    int32_t e_lo, e_hi;    // this pass handles the rows whose LAST edge lies in [e_lo, e_hi) (copy-in still in flight: the edges
+                           // arrive in chunks); rows without edges go with e_lo == 0
     PRP_HD void operator()(int64_t i) const {
         const int32_t r = c.nl + (int32_t)i, id = c.short_id0 + (int32_t)i;
-        if (id > c.n) { segmask[r] = 0; home_len[r] = 0; return; }
+        if (id > c.n) { if (e_lo == 0) { segmask[r] = 0; home_len[r] = 0; } return; }
         const int32_t v = c.old_of_new[id], rb = c.r_begin[v], len = c.r_begin[v + 1] - rb;
+        if (len == 0 ? e_lo != 0 : (rb + len - 1 < e_lo || rb + len - 1 >= e_hi)) return;
         if (c.tlo > c.T || len < (c.tlo == 0 ? 1 : c.kmin)) { segmask[r] = 0; home_len[r] = len; return; }
         uint16_t cnt[MAX_TIERS + 1];
         for (int t = 0; t <= c.T; t++) cnt[t] = 0;
@@ -324,10 +327,12 @@ struct PieceCountF {   // per-tier counts of one piece -> G[t * nps + p]
     const int32_t *piece_first, *piece_row;
     int32_t nps;
     int32_t* G;
+    int32_t e_lo, e_hi;    // pieces whose last edge lies in [e_lo, e_hi)
     PRP_HD void operator()(int64_t p) const {
         if (p >= piece_first[c.nl]) return;
         const int32_t j = piece_row[p], v = c.old_of_new[c.jl0 + 1 + j], rb = c.r_begin[v], len = c.r_begin[v + 1] - rb;
         const int32_t k0 = ((int32_t)p - piece_first[j]) * PIECE, k1 = std::min(len, k0 + PIECE);
+        if (rb + k1 - 1 < e_lo || rb + k1 - 1 >= e_hi) return;
         uint16_t cnt[MAX_TIERS + 1];
         for (int t = 0; t <= c.T; t++) cnt[t] = 0;
         for (int32_t k = k0; k < k1; k++) {
@@ -749,16 +754,26 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     nps = (int32_t)std::min<int64_t>((int64_t)m / PIECE + nl + 2, 0x7fffff00LL);
     PRP_TRY(tmp.get(&np, (size_t)nl + 1)); PRP_TRY(tmp.get(&piece_row, (size_t)nps));
     PRP_TRY(tmp.get(&G, (size_t)(P.T + 1) * nps));
-    PRP_TRY(be.edges_ready());
-    be.pfor((int64_t)32 * ns, CountShortF{rc_, segmask, home_len, nrec, rec_j, err, rec_key, rec_cap});
     be.pfor((int64_t)nl + 1, PieceNumF{rc_, np});
     PRP_TRY(be.scan_i32(np, (size_t)nl + 1));                               // np = piece_first from here on
     be.pfor(nps, PieceRowF{np, nl, piece_row});
-    if (tlo <= P.T) {
-        PRP_TRY(be.zero(G, 4 * (size_t)(P.T + 1) * nps));
-        be.pfor(nps, PieceCountF{rc_, np, piece_row, nps, G});
-        PRP_TRY(be.scan_i32(G, (size_t)(P.T + 1) * nps));
+    if (tlo <= P.T) PRP_TRY(be.zero(G, 4 * (size_t)(P.T + 1) * nps));
+    {
+        // the reverse edges may still be arriving over PCIe (gmc_pagerank_host_csr): count chunk by chunk behind the copies
+        const int nch = be.edge_chunks();
+        int32_t e_lo = 0;
+        for (int ch = 0; ch < nch; ch++) {
+            int32_t e_hi = m;
+            PRP_TRY(be.edge_chunk_ready(ch, &e_hi));
+            if (ch == nch - 1) e_hi = m > 0 ? m : 1;
+            if (e_hi > e_lo || ch == 0) {
+                be.pfor((int64_t)32 * ns, CountShortF{rc_, segmask, home_len, nrec, rec_j, err, rec_key, rec_cap, e_lo, e_hi > e_lo ? e_hi : e_lo + 1});
+                if (tlo <= P.T) be.pfor(nps, PieceCountF{rc_, np, piece_row, nps, G, e_lo, e_hi});
+            }
+            if (e_hi > e_lo) e_lo = e_hi;
+        }
     }
+    if (tlo <= P.T) PRP_TRY(be.scan_i32(G, (size_t)(P.T + 1) * nps));
     be.pfor(nl, LongRowF{rc_, np, G, nps, segmask, home_len, nrec, rec_j, err, rec_key, rec_cap});
     PRP_TRY(be.d2h(&nseg, nrec, 4));
     PRP_TRY(be.d2h(&herr, err, 4));

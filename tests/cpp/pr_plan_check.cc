@@ -21,6 +21,9 @@ struct CpuBackend {
     int sync() { return 0; }
     int begin_offsets_ready() { return 0; }
     int edges_ready() { return 0; }
+    int n_chunks = 1, m_edges = 0;      // the check also runs the chunked pass 1 (edges arriving in pieces)
+    int edge_chunks() { return n_chunks; }
+    int edge_chunk_ready(int c, int32_t* e_end) { *e_end = (int32_t)((int64_t)m_edges * (c + 1) / n_chunks); return 0; }
     std::string last_error() { return err; }
     template <class F>
     void pfor(int64_t n, const F& f) {
@@ -96,6 +99,7 @@ int main(int argc, char** argv) {
     }
 
     CpuBackend be;
+    be.m_edges = m; be.n_chunks = getenv("PRP_CHUNKS") ? atoi(getenv("PRP_CHUNKS")) : 1;
     prp::Config cfg;
     cfg.tiers = tiers; cfg.kmin = kmin; cfg.tier_min_edges = 0;
     cfg.row_cost = world > 2 ? 2 * (world - 2) : 0;

@@ -29,6 +29,14 @@ def test_plan_small_tiers(checker, args):
     assert r.returncode == 0 and r.stdout.strip().endswith("OK"), r.stdout[-3000:]
 
 
+def test_plan_chunked_edge_arrival(checker):
+    """pass 1 runs chunk by chunk behind the copy-in of the edges (gmc_pagerank_host_csr): any chunking gives the same plan"""
+    for chunks in ("3", "8"):
+        env = dict(os.environ, PRP_CHUNKS=chunks)
+        r = subprocess.run([checker["small"]] + "14 400000 16 3 2".split(), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600, env=env)
+        assert r.returncode == 0 and r.stdout.strip().endswith("OK"), r.stdout[-3000:]
+
+
 def test_plan_big_tasks(checker):
     env = dict(os.environ, PRP_BIGTASKS="1")
     r = subprocess.run([checker["mid"], "16", "3000000", "16", "3", "1"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900, env=env)
