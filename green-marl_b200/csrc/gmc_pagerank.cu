@@ -95,6 +95,7 @@ struct SweepArgs {
     int32_t n_ztasks, z0, z_end, zt_on;       // [z0, z_end): the shard's ids without in-edges; zt_on: run their tasks this sweep
     int32_t dp_short, dp_zero, dp_cut, dp_total, n_cb;   // diff_parts layout; n_cb = pr_combine blocks (their partials follow dp_total)
     int32_t hot0_bytes;                       // bytes of tier 0 worth staging (small graphs do not fill it)
+    int32_t split;                            // SPLIT mode (home tasks run with any tier staged)
     int32_t cold_warps;                       // warps of a CTA that prefer home tasks (L2 gathers) to their tier's tasks
     // cut rows of the long sections, parts of the split rows
     double* head_part;                       // [n_ltslots]
@@ -479,7 +480,10 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
         if (tid == 0) {
             s_st = A.streams[s];
             // a later list entry (a place to help) is staged only while it has tasks left
-            s_skip = i > 0 && *(volatile unsigned int*)&A.ctrl->next[s] >= (unsigned)(s_st.n_ltasks + s_st.n_stasks);
+            // (MIXED mode: tier 0 is staged for the home tasks, its own stream is empty)
+            const bool tier_done = *(volatile unsigned int*)&A.ctrl->next[s] >= (unsigned)(s_st.n_ltasks + s_st.n_stasks);
+            const bool home_done = *(volatile unsigned int*)&A.ctrl->next[0] >= (unsigned)(s_home.n_ltasks + s_home.n_stasks + (A.zt_on ? A.n_ztasks : 0));
+            s_skip = i > 0 && tier_done && (home_done || !(A.split || s == 1));
         }
         __syncthreads();
         const Stream& st = s_st;
@@ -505,12 +509,13 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
         }
         bool tier_left = t_total > 0;
         home_left = home_left && h_total > 0;
+        const bool home_ok = A.split || s == 1;        // MIXED mode: the home rows gather from tier 0
         for (;;) {
             bool did = false;
 #pragma unroll 1
             for (int pass = 0; pass < 2 && !did; pass++) {
                 const bool want_home = (pass == 0) == cold_first;
-                if (want_home ? !home_left : !tier_left) continue;
+                if (want_home ? !(home_left && home_ok) : !tier_left) continue;
                 int32_t u = 0;
                 if (lane == 0) u = (int32_t)atomicAdd(&A.ctrl->next[want_home ? 0 : s], 1u);
                 u = __shfl_sync(FULL, u, 0);
@@ -533,7 +538,7 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
 
 // Second launch of a sweep: the split rows (parts added in slot order + epilogue), then the last block to finish adds the
 // diff partials of both kernels in a fixed order, advances the loop control and resets the task counters.
-__global__ void __launch_bounds__(CB_THREADS, 1) pr_combine(const SweepArgs A) {
+__global__ void __launch_bounds__(CB_THREADS, 2) pr_combine(const SweepArgs A) {
     __shared__ double s_red[CB_THREADS / 32];
     __shared__ int s_last;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -773,6 +778,7 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
         // experiment / test switches; the defaults are the product
         cfg.tiers = env_int("GMC_PR_TIERS", cfg.tiers);
         cfg.kmin = env_int("GMC_PR_KMIN", cfg.kmin);
+        cfg.split = env_int("GMC_PR_SPLIT", cfg.split);
         if (cfg.kmin < 1) cfg.kmin = 1;
         if (const char* v = getenv("GMC_PR_TIER_MIN_EDGES")) cfg.tier_min_edges = atoll(v);
         if (const char* v = getenv("GMC_PR_TIER_SCALE")) cfg.tier_scale = atof(v);
@@ -858,6 +864,7 @@ SweepArgs make_args(const gmc_pr_plan* p, double d, int sweep, gmc_pr_ctrl* ctrl
     {
         static const int cw = env_int("GMC_PR_COLD_WARPS", (PR_THREADS / 32) * 3 / 8);      // 12 of 32 warps
         A.cold_warps = L.split ? cw : PR_THREADS / 32;
+        A.split = L.split;
     }
     A.head_part = p->head_part; A.tail_part = p->tail_part; A.split_cnt = p->split_cnt; A.diff_parts = p->diff_parts; A.parts = p->parts;
     A.contrib_in = p->contrib[parity]; A.contrib_out = p->contrib[parity ^ 1];

@@ -64,13 +64,14 @@ constexpr uint32_t OD_SPLIT = 0x80000000u, OD_HOT = 0x40000000u, OD_MASK = 0x3ff
 
 struct Config {
     int tiers = 16;                    // warm tiers wanted (0: the single hot block of round 1)
-    int kmin = 3;                      // entries from which a (row, tier) group becomes a segment
+    int kmin = 4;                      // entries from which a (row, tier) group becomes a segment
     int64_t tier_min_edges = 4 << 20;  // smaller graphs keep T = 0 (every short row stays bit-identical to the CPU order)
     int lt = 2048, st_cost = 2048, slice_ovh = 68;     // task sizes (entries per long task, cost units per short task)
     int tail_big16 = 14, tail_shift = 2;               // home short tasks: 14/16 of the cost in full tasks, the rest in quarter ones
     int grid = 148;                    // CTAs of the sweep
     int row_cost = 0;                  // shard cuts: entries one row epilogue weighs (grows with the world size)
-    double tier_scale = 1.0;           // multiplier on the CTAs given to the tier streams
+    double tier_scale = 1.25;          // multiplier on the CTAs given to the tier streams
+    int split = 0;                     // 1: SPLIT mode (tier 0 as a segment stream, home = cold entries only); see the header
     double r_smem = 2.4, r_miss = 0.75;   // gathers per clock and SM: shared memory / L2 (sched model)
 };
 
@@ -574,6 +575,43 @@ static inline void make_schedule(const Config& cfg, Plan& P) {
     const int G = cfg.grid > 0 ? cfg.grid : 1;
     P.sched.assign((size_t)G * SCHED_W, 0);
     for (int b = 0; b < G; b++) P.sched[(size_t)b * SCHED_W] = 1;
+    if (!P.split && P.T > 0) {
+        // MIXED mode with warm tiers: home tasks need tier 0, so a CTA is either a home CTA (list = tier 0 only) or a tier CTA
+        // (its warm tiers, then tier 0 to join the home tasks).  Tier CTAs in proportion to the modelled cost: shared-memory
+        // gathers for the tiers; for home the slower of its shared-memory and its L2 gathers.
+        std::vector<double> c((size_t)P.T + 2, 0.0);
+        const double hot = (double)P.hot0_entries / cfg.r_smem, cold = (double)P.cold_entries / cfg.r_miss;
+        double total = std::max(hot, cold) + 0.25 * std::min(hot, cold);
+        for (int s = 2; s <= P.T + 1; s++) { c[s] = (double)P.streams[s].entries / cfg.r_smem * cfg.tier_scale; total += c[s]; }
+        double per = total / G;
+        if (per <= 0) per = 1;
+        const int budget = G * 3 / 5 > 0 ? G * 3 / 5 : 1;
+        for (int attempt = 0; attempt < 200; attempt++, per *= 1.05) {
+            std::vector<int32_t> sc((size_t)G * SCHED_W, 0);
+            int b = 0, s = 2;
+            bool ok = true;
+            while (s <= P.T + 1) {
+                if (b >= budget) { ok = false; break; }
+                if (c[s] >= 0.75 * per) {
+                    int k = std::max(1, (int)(c[s] / per + 0.999));
+                    if (b + k > budget) { ok = false; break; }
+                    for (int i = 0; i < k; i++) { sc[(size_t)(b + i) * SCHED_W] = s; sc[(size_t)(b + i) * SCHED_W + 1] = 1; }
+                    b += k; s++;
+                } else {
+                    double sum = 0;
+                    int cnt = 0;
+                    while (s <= P.T + 1 && cnt < SCHED_W - 1 && (cnt == 0 || sum + c[s] <= 1.1 * per)) { sc[(size_t)b * SCHED_W + cnt] = s; sum += c[s]; cnt++; s++; }
+                    sc[(size_t)b * SCHED_W + cnt] = 1;
+                    b++;
+                }
+            }
+            if (!ok) continue;
+            for (; b < G; b++) sc[(size_t)b * SCHED_W] = 1;
+            P.sched = sc;
+            return;
+        }
+        return;
+    }
     if (!P.split) return;
     const int NTS = P.T + 1;                       // tier streams 1..NTS
     std::vector<double> c((size_t)NTS + 1, 0.0);
@@ -687,7 +725,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
         const int full = (P.n_src + HT_REAL - 1) / HT_REAL;      // tiers needed to give every source a slot
         if (T > full - 1) T = full - 1 > 0 ? full - 1 : 0;
         P.T = T; P.NH = (T + 1) * HT;
-        P.split = T >= 1 ? 1 : 0;
+        P.split = (T >= 1 && cfg.split) ? 1 : 0;
     }
     tlo = P.split ? 0 : 1;
     be.pfor(n, HotF{so_ids, outdeg, hotslot_old, (P.T + 1) * HT_REAL});

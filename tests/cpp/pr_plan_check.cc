@@ -102,6 +102,7 @@ int main(int argc, char** argv) {
     be.m_edges = m; be.n_chunks = getenv("PRP_CHUNKS") ? atoi(getenv("PRP_CHUNKS")) : 1;
     prp::Config cfg;
     cfg.tiers = tiers; cfg.kmin = kmin; cfg.tier_min_edges = 0;
+    cfg.split = getenv("PRP_SPLIT") ? atoi(getenv("PRP_SPLIT")) : 1;
     cfg.row_cost = world > 2 ? 2 * (world - 2) : 0;
     if (const char* big = getenv("PRP_BIGTASKS")) if (atoi(big)) { cfg.lt = 8192; cfg.st_cost = 4096; cfg.slice_ovh = 136; }
     std::vector<prp::Plan> plans((size_t)world);

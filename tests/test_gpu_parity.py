@@ -332,8 +332,8 @@ def test_pull_only_graph(gm, oracle, g_c1):
         dg.array("node_idx")
 
 
-@pytest.mark.parametrize("tiers,kmin,big", [(16, 3, "0"), (31, 1, "0"), (3, 2, "1"), (16, 6, "1")])
-def test_pagerank_tiered_streams(gm, oracle, g_rmat, tiers, kmin, big, monkeypatch):
+@pytest.mark.parametrize("tiers,kmin,big,split", [(16, 3, "0", "0"), (31, 1, "0", "1"), (3, 2, "1", "0"), (16, 6, "1", "1"), (16, 4, "0", "1")])
+def test_pagerank_tiered_streams(gm, oracle, g_rmat, tiers, kmin, big, split, monkeypatch):
     """the tiered layout (gmc_pr_plan.h) forced onto the 200 K / 3 M graph: (row, tier) segments in their own entry streams,
     partial sums through the part slots, pr_combine finishing the split rows -- against the oracle, and the plan must
     really have segments.  Production graphs get it from 4 M edges on (LJ- and TW-shaped runs, bench.py parity)."""
@@ -341,6 +341,7 @@ def test_pagerank_tiered_streams(gm, oracle, g_rmat, tiers, kmin, big, monkeypat
     monkeypatch.setenv("GMC_PR_TIERS", str(tiers))
     monkeypatch.setenv("GMC_PR_KMIN", str(kmin))
     monkeypatch.setenv("GMC_PR_BIGTASKS", big)
+    monkeypatch.setenv("GMC_PR_SPLIT", split)
     dg = dev_graph(gm, g_rmat)
     pi = dg.pagerank_plan_info()
     assert pi["tiers"] >= 3 and pi["segments"] > 0 and pi["split_rows"] > 0 and pi["part_slots"] == pi["segments"] + pi["split_rows"]

@@ -25,8 +25,10 @@ def checker(tmp_path_factory):
 @pytest.mark.parametrize("args", ["12 65536 3 3 1", "12 65536 8 2 1", "14 400000 16 3 1", "14 400000 31 3 2", "13 200000 5 1 3",
                                   "15 1000000 12 2 4 11", "10 3000 4 3 1", "12 65536 0 3 2", "8 300 31 1 1"])
 def test_plan_small_tiers(checker, args):
-    r = subprocess.run([checker["small"]] + args.split(), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
-    assert r.returncode == 0 and r.stdout.strip().endswith("OK"), r.stdout[-3000:]
+    for split in ("1", "0"):          # SPLIT mode (tier 0 as a segment stream) and MIXED mode with warm tiers
+        r = subprocess.run([checker["small"]] + args.split(), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600,
+                           env=dict(os.environ, PRP_SPLIT=split))
+        assert r.returncode == 0 and r.stdout.strip().endswith("OK"), r.stdout[-3000:]
 
 
 def test_plan_chunked_edge_arrival(checker):

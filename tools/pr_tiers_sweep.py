@@ -1,5 +1,5 @@
 """Experiment driver: per-sweep time of the LJ-shaped graph for a list of plan settings (env switches of build_plan), one process each.
-usage: python tools/pr_tiers_sweep.py ["TIERS,KMIN,SCALE[,COLD_WARPS]" ...]"""
+usage: python tools/pr_tiers_sweep.py ["TIERS,KMIN,SCALE[,COLD_WARPS[,SPLIT]]" ...]"""
 import os, sys, subprocess
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if len(sys.argv) > 1 and sys.argv[1] == "one":
@@ -22,4 +22,5 @@ else:
         f = c.split(",")
         env = dict(os.environ, GMC_PR_TIERS=f[0], GMC_PR_KMIN=f[1], GMC_PR_TIER_SCALE=f[2])
         if len(f) >= 4: env["GMC_PR_COLD_WARPS"] = f[3]
+        if len(f) >= 5: env["GMC_PR_SPLIT"] = f[4]
         subprocess.run([sys.executable, __file__, "one", c], env=env)
