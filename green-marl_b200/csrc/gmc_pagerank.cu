@@ -65,7 +65,8 @@ struct gmc_pr_ctrl {   // device-side loop control: lets the host enqueue sweeps
     double diff;
     int32_t cnt;
     int32_t done;
-    unsigned int arrived;   // pr_combine blocks that have finished
+    unsigned int arrived;   // blocks that have finished their share of the split rows
+    unsigned int bar;       // grid barrier of pr_sweep: arrivals of all launches since the control block was cleared
     int32_t error;          // 1: a peer's end-of-sweep flag did not arrive in time (sharded runs)
     unsigned int next[MAX_STREAMS];     // dynamic task counter of every stream of the running sweep (reset by pr_combine)
 };
@@ -96,6 +97,9 @@ struct SweepArgs {
     int32_t dp_short, dp_zero, dp_cut, dp_total, n_cb;   // diff_parts layout; n_cb = pr_combine blocks (their partials follow dp_total)
     int32_t hot0_bytes;                       // bytes of tier 0 worth staging (small graphs do not fill it)
     int32_t split;                            // SPLIT mode (home tasks run with any tier staged)
+    int32_t cold_s;                           // stream number of the cold stream (0: none)
+    int32_t fused;                            // 1: the split rows are finished at the end of pr_sweep (grid barrier), no pr_combine launch
+    unsigned int bar_target;                  // value of ctrl->bar when every CTA of this launch has arrived
     int32_t cold_warps;                       // warps of a CTA that prefer home tasks (L2 gathers) to their tier's tasks
     // cut rows of the long sections, parts of the split rows
     double* head_part;                       // [n_ltslots]
@@ -155,6 +159,7 @@ struct gmc_pr_plan {
     double* rank[2] = {nullptr, nullptr};
     gmc_pr_ctrl* ctrl = nullptr;
     int grid = 0, n_cb = 1;
+    unsigned int bar_arrivals = 0;            // state owner: CTAs that will have arrived at ctrl->bar after the launches enqueued so far
     size_t smem = 0;
 };
 
@@ -194,9 +199,9 @@ __device__ __forceinline__ double butterfly(double v) {
 // ---------------------------------------------------------------------------------------------
 // home entries: value < HT = slot of tier 0 (shared memory), otherwise HT + id (L2; cold gathers bypass L1, whose capacity the
 // hot block has taken); tier entries: slot inside the staged tier
-template <bool TIER>
+template <bool SMEM>
 __device__ __forceinline__ double gather(const double* hot, const double* cin_m, int32_t w) {
-    if (TIER) return hot[w];
+    if (SMEM) return hot[w];
     return (w < HT) ? hot[w] : __ldcg(cin_m + w);
 }
 
@@ -253,7 +258,10 @@ __device__ __forceinline__ int row_search(int32_t e, int32_t o) {
 
 // the last task to deliver a piece of a cut row adds the pieces in task order and finishes the row.  t1..t2: the tasks
 // (stream-local numbers) the row spans; slots of the cut-row arrays are st.lt_off + task
-template <bool TIER>
+// MODE of a task: 0 = home stream (rows finished by their epilogue or the home part slot; gathers from the staged tier 0 and
+// from L2), 1 = tier stream (segments: sums go to part slots; shared-memory gathers only), 2 = cold stream (segments of
+// cold entries: part slots; L2 gathers -- runs with any tier staged, slot 0 of every tier being the padding's 0.0)
+template <int MODE>
 __device__ __forceinline__ void split_arrive(const SweepArgs& A, const Stream& st, int lane, int32_t t1, int32_t t2, int32_t row, double piece,
                                              double* slot) {
     int last = 0;
@@ -270,14 +278,16 @@ __device__ __forceinline__ void split_arrive(const SweepArgs& A, const Stream& s
     for (int32_t p = t1 + lane; p <= t2; p += 32) v += (p == t1) ? __ldcg(A.tail_part + st.lt_off + p) : __ldcg(A.head_part + st.lt_off + p);
     const double S = butterfly(v);
     if (lane == 0) {
+        constexpr bool TIER = MODE != 0;
         if (TIER) __stcg(A.parts + __ldg(A.seg_slot + st.meta_off + row), S);
         else A.diff_parts[A.dp_cut + t1] = finish_home(A, A.long_id0 + row, S);
         A.split_cnt[st.lt_off + t1] = 0u;
     }
 }
 
-template <bool TIER>
+template <int MODE>
 __device__ __forceinline__ void long_task(const SweepArgs& A, const Stream& st, const double* hot, int lane, int32_t t) {
+    constexpr bool TIER = MODE != 0, SMEM = MODE == 1;
     const double* cin_m = A.contrib_in - HT;
     const int32_t* __restrict__ lbeg = A.eoff + st.lbeg_off;
     const int32_t x0 = st.e_long + (t << A.lt_shift);
@@ -333,8 +343,8 @@ __device__ __forceinline__ void long_task(const SweepArgs& A, const Stream& st, 
         const int32_t o0 = i * 128 + 4 * lane, o1 = o0 + 128;
         nx0 = (o0 + 256 < span) ? ld_idx4(E4 + (i + 2) * 32 + lane) : zero4;
         nx1 = (o1 + 256 < span) ? ld_idx4(E4 + (i + 3) * 32 + lane) : zero4;
-        const double v0 = gather<TIER>(hot, cin_m, c0.x), v1 = gather<TIER>(hot, cin_m, c0.y), v2 = gather<TIER>(hot, cin_m, c0.z), v3 = gather<TIER>(hot, cin_m, c0.w);
-        const double v4 = gather<TIER>(hot, cin_m, c1.x), v5 = gather<TIER>(hot, cin_m, c1.y), v6 = gather<TIER>(hot, cin_m, c1.z), v7 = gather<TIER>(hot, cin_m, c1.w);
+        const double v0 = gather<SMEM>(hot, cin_m, c0.x), v1 = gather<SMEM>(hot, cin_m, c0.y), v2 = gather<SMEM>(hot, cin_m, c0.z), v3 = gather<SMEM>(hot, cin_m, c0.w);
+        const double v4 = gather<SMEM>(hot, cin_m, c1.x), v5 = gather<SMEM>(hot, cin_m, c1.y), v6 = gather<SMEM>(hot, cin_m, c1.z), v7 = gather<SMEM>(hot, cin_m, c1.w);
         step(x0 + o0, o0 < span, (v0 + v1) + (v2 + v3));
         step(x0 + o1, o1 < span, (v4 + v5) + (v6 + v7));
     }
@@ -352,16 +362,17 @@ __device__ __forceinline__ void long_task(const SweepArgs& A, const Stream& st, 
     }
     if (head_split) {
         const int32_t e0 = __shfl_sync(FULL, e, 0);
-        split_arrive<TIER>(A, st, lane, (rb0 - st.e_long) >> A.lt_shift, (e0 - 1 - st.e_long) >> A.lt_shift, a, head_acc, A.head_part + st.lt_off + t);
+        split_arrive<MODE>(A, st, lane, (rb0 - st.e_long) >> A.lt_shift, (e0 - 1 - st.e_long) >> A.lt_shift, a, head_acc, A.head_part + st.lt_off + t);
     }
     if (tail_split && !(kl == 0 && head_split))
-        split_arrive<TIER>(A, st, lane, t, (e_kl - 1 - st.e_long) >> A.lt_shift, a + kl, tail_acc, A.tail_part + st.lt_off + t);
+        split_arrive<MODE>(A, st, lane, t, (e_kl - 1 - st.e_long) >> A.lt_shift, a + kl, tail_acc, A.tail_part + st.lt_off + t);
 }
 
 // rows / segments of up to S_MAX entries: one lane per row, terms added strictly left to right.  The loop runs over
 // 8-column chunks; the indices of the next chunk (of this slice or the next one) are always in flight.
-template <bool TIER>
+template <int MODE>
 __device__ __forceinline__ void short_task(const SweepArgs& A, const Stream& st, const double* hot, int lane, int32_t u) {
+    constexpr bool TIER = MODE != 0, SMEM = MODE == 1;
     const double* cin_m = A.contrib_in - HT;
     const int32_t* __restrict__ sbeg = A.sbeg + st.sbeg_off;
     const int32_t s_lo = __ldg(A.stask_slice + st.st_off + u), s_hi = __ldg(A.stask_slice + st.st_off + u + 1);
@@ -401,7 +412,7 @@ __device__ __forceinline__ void short_task(const SweepArgs& A, const Stream& st,
         for (int k = 0; k < 8; k++) wn[k] = (nj + k < nL) ? __ldcs(A.E + nbase + lane + (nj + k) * 32) : 0;
         double v[8];
 #pragma unroll
-        for (int k = 0; k < 8; k++) v[k] = gather<TIER>(hot, cin_m, w[k]);
+        for (int k = 0; k < 8; k++) v[k] = gather<SMEM>(hot, cin_m, w[k]);
 #pragma unroll
         for (int k = 0; k < 8; k++) S = S + v[k];                 // left to right: the reference's order (+0.0 for padding)
         if (nj == 0) {                                            // slice finished
@@ -450,10 +461,67 @@ __device__ __forceinline__ void zero_task(const SweepArgs& A, int lane, int32_t 
     if (lane == 0) A.diff_parts[A.dp_zero + z] = diff;
 }
 
+// The split rows (parts added in slot order + epilogue), then the last block to finish adds the diff partials of the whole
+// sweep in a fixed order, advances the loop control and resets the task counters.  Runs behind a grid barrier at the end of
+// pr_sweep (default) or as the kernel pr_combine (GMC_PR_TWO_KERNELS=1).
+template <int NT>
+__device__ __forceinline__ void combine_rows(const SweepArgs& A, double* s_red, int* s_last) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    double diff = 0.0;
+    for (int32_t k = blockIdx.x * NT + tid; k < A.K; k += gridDim.x * NT) {
+        const int32_t p0 = __ldg(A.pbeg + k), p1 = __ldg(A.pbeg + k + 1), id = __ldg(A.prow + k);
+        double S = 0.0;
+        for (int32_t p = p0; p < p1; p++) S += __ldcg(A.parts + p);        // home part, then the segments in tier order
+        diff += finish_row(A, id, (uint32_t)__ldcs(A.od_flags + id), __ldcs(A.rank_in + id), S);
+    }
+    diff = butterfly(diff);
+    if (lane == 0) s_red[warp] = diff;
+    __syncthreads();
+    if (warp == 0) {
+        const double t = butterfly(lane < NT / 32 ? s_red[lane] : 0.0);
+        if (lane == 0) A.diff_parts[A.dp_total + blockIdx.x] = t;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        if (A.npeers > 0) __threadfence_system(); else __threadfence();
+        *s_last = (atomicAdd(&A.ctrl->arrived, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!*s_last) return;
+    __threadfence();
+    const int32_t nparts = A.dp_total + A.n_cb;
+    double v = 0.0;
+    for (int32_t i = tid; i < nparts; i += NT) v += __ldcg(A.diff_parts + i);
+    v = butterfly(v);
+    if (lane == 0) s_red[warp] = v;
+    __syncthreads();
+    if (warp == 0) {
+        const double t = butterfly(lane < NT / 32 ? s_red[lane] : 0.0);
+        for (int i2 = lane; i2 < MAX_STREAMS; i2 += 32) A.ctrl->next[i2] = 0u;
+        if (lane == 0) A.ctrl->arrived = 0u;
+        if (lane == 0 && A.diff_slot) {
+            *A.diff_slot = t;
+            for (int p = 0; p < A.npeers; p++) *A.peer_diff[p] = t;
+        } else if (lane == 0 && A.loop) {
+            const int32_t cnt = A.ctrl->cnt + 1;
+            A.ctrl->diff = t;
+            A.ctrl->cnt = cnt;
+            A.ctrl->done = !((t > A.e) && (cnt < A.max_iter));       // } While ((diff > e) && (cnt < max))
+        }
+        if (lane == 0 && A.my_flag) {      // every store of this sweep (both kernels, all blocks) is ordered before the flags
+            __threadfence_system();
+            *A.my_flag = A.seq;
+            for (int p = 0; p < A.npeers; p++) st_release_sys(A.peer_flag[p], A.seq);
+        }
+    }
+}
+
 __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
     extern __shared__ __align__(16) double hot[];
     __shared__ __align__(8) unsigned long long bar;
-    __shared__ Stream s_st, s_home;
+    __shared__ Stream s_st, s_home, s_cold;
+    __shared__ double s_red[PR_THREADS / 32];
+    __shared__ int s_last;
     __shared__ int s_skip;
     const int tid = threadIdx.x, lane = tid & 31;
 
@@ -469,10 +537,10 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
     // device-wide counters: the tier's stream (shared-memory gathers) and the home stream (L2 gathers; runs with any tier
     // staged in SPLIT mode, with tier 0 -- the only list entry -- in MIXED mode).  The first cold_warps warps prefer home
     // tasks, the others the tier's, and each falls back to the other kind: both gather paths of the SM stay busy.
-    if (tid == 0) s_home = A.streams[0];
+    if (tid == 0) { s_home = A.streams[0]; s_cold = A.streams[A.cold_s]; }      // cold_s == 0: no cold stream (its task count is forced to 0 below)
     unsigned phase = 0;
     const bool cold_first = (tid >> 5) < A.cold_warps;
-    bool home_left = true;
+    bool home_left = true, cold_left = A.cold_s != 0;
     for (int i = 0; i < SCHED_W; i++) {
         const int s = __ldg(A.sched + blockIdx.x * SCHED_W + i);
         if (s == 0) break;
@@ -483,13 +551,15 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
             // (MIXED mode: tier 0 is staged for the home tasks, its own stream is empty)
             const bool tier_done = *(volatile unsigned int*)&A.ctrl->next[s] >= (unsigned)(s_st.n_ltasks + s_st.n_stasks);
             const bool home_done = *(volatile unsigned int*)&A.ctrl->next[0] >= (unsigned)(s_home.n_ltasks + s_home.n_stasks + (A.zt_on ? A.n_ztasks : 0));
-            s_skip = i > 0 && tier_done && (home_done || !(A.split || s == 1));
+            const bool cold_done = !A.cold_s || *(volatile unsigned int*)&A.ctrl->next[A.cold_s] >= (unsigned)(s_cold.n_ltasks + s_cold.n_stasks);
+            s_skip = i > 0 && tier_done && (home_done || !(A.split || s == 1)) && cold_done;
         }
         __syncthreads();
         const Stream& st = s_st;
         const Stream& hm = s_home;
         const int32_t h_l = hm.n_ltasks, h_s = hm.n_stasks, h_total = h_l + h_s + (A.zt_on ? A.n_ztasks : 0);
         const int32_t t_l = st.n_ltasks, t_total = t_l + st.n_stasks;
+        const int32_t c_l = A.cold_s ? s_cold.n_ltasks : 0, c_total = A.cold_s ? c_l + s_cold.n_stasks : 0;
         if (s_skip) continue;
         {   // stage the tier: hot_in[hot_off, hot_off + HT) -> shared memory, one TMA bulk copy stream
             if (tid == 0) {
@@ -509,90 +579,68 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
         }
         bool tier_left = t_total > 0;
         home_left = home_left && h_total > 0;
+        cold_left = cold_left && c_total > 0;
         const bool home_ok = A.split || s == 1;        // MIXED mode: the home rows gather from tier 0
+        // task sources in this warp's order of preference.  Warps of a tier CTA: the first cold_warps start with the
+        // cold stream (L2 gathers), the others with the tier's tasks (shared memory) -- both gather paths of the SM stay
+        // busy; warps of a home CTA: home tasks first, the cold stream when home is exhausted.  0 = home, 1 = tier, 2 = cold
+        int order[3];
+        if (A.split) { order[0] = cold_first ? 0 : 1; order[1] = cold_first ? 1 : 0; order[2] = 2; }
+        else if (s == 1) { order[0] = 0; order[1] = 2; order[2] = 1; }
+        else { order[0] = cold_first ? 2 : 1; order[1] = cold_first ? 1 : 2; order[2] = 0; }
         for (;;) {
             bool did = false;
 #pragma unroll 1
-            for (int pass = 0; pass < 2 && !did; pass++) {
-                const bool want_home = (pass == 0) == cold_first;
-                if (want_home ? !(home_left && home_ok) : !tier_left) continue;
+            for (int pass = 0; pass < 3 && !did; pass++) {
+                const int src = order[pass];
+                if (src == 0 ? !(home_left && home_ok) : (src == 1 ? !tier_left : !cold_left)) continue;
                 int32_t u = 0;
-                if (lane == 0) u = (int32_t)atomicAdd(&A.ctrl->next[want_home ? 0 : s], 1u);
+                if (lane == 0) u = (int32_t)atomicAdd(&A.ctrl->next[src == 0 ? 0 : (src == 1 ? s : A.cold_s)], 1u);
                 u = __shfl_sync(FULL, u, 0);
-                if (want_home) {
+                if (src == 0) {
                     if (u >= h_total) { home_left = false; continue; }
-                    if (u < h_l) long_task<false>(A, hm, hot, lane, u);
-                    else if (u < h_l + h_s) short_task<false>(A, hm, hot, lane, u - h_l);
+                    if (u < h_l) long_task<0>(A, hm, hot, lane, u);
+                    else if (u < h_l + h_s) short_task<0>(A, hm, hot, lane, u - h_l);
                     else zero_task(A, lane, u - h_l - h_s);
-                } else {
+                } else if (src == 1) {
                     if (u >= t_total) { tier_left = false; continue; }
-                    if (u < t_l) long_task<true>(A, st, hot, lane, u);
-                    else short_task<true>(A, st, hot, lane, u - t_l);
+                    if (u < t_l) long_task<1>(A, st, hot, lane, u);
+                    else short_task<1>(A, st, hot, lane, u - t_l);
+                } else {
+                    if (u >= c_total) { cold_left = false; continue; }
+                    if (u < c_l) long_task<2>(A, s_cold, hot, lane, u);
+                    else short_task<2>(A, s_cold, hot, lane, u - c_l);
                 }
                 did = true;
             }
             if (!did) break;
         }
     }
+    if (!A.fused) return;
+    // ---- every task of the sweep is done once all CTAs have passed this grid barrier (cooperative launch: they are all
+    // resident); then the split rows.  bar counts arrivals of all launches of the call: this launch ends at bar_target.
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        atomicAdd(&A.ctrl->bar, 1u);
+        const long long t0 = clock64();
+        while ((int)(*(volatile unsigned int*)&A.ctrl->bar - A.bar_target) < 0) {
+            if (clock64() - t0 > PEER_TIMEOUT_CYCLES) { A.ctrl->error = 2; break; }       // never hang the device
+            __nanosleep(64);
+        }
+        __threadfence();
+    }
+    __syncthreads();
+    combine_rows<PR_THREADS>(A, s_red, &s_last);
 }
 
-// Second launch of a sweep: the split rows (parts added in slot order + epilogue), then the last block to finish adds the
-// diff partials of both kernels in a fixed order, advances the loop control and resets the task counters.
 __global__ void __launch_bounds__(CB_THREADS, 2) pr_combine(const SweepArgs A) {
     __shared__ double s_red[CB_THREADS / 32];
     __shared__ int s_last;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (A.loop && A.ctrl->done) return;
-    const int32_t k = blockIdx.x * CB_THREADS + tid;
-    double diff = 0.0;
-    if (k < A.K) {
-        const int32_t p0 = __ldg(A.pbeg + k), p1 = __ldg(A.pbeg + k + 1), id = __ldg(A.prow + k);
-        double S = 0.0;
-        for (int32_t p = p0; p < p1; p++) S += __ldcg(A.parts + p);        // home part, then the segments in tier order
-        diff = finish_row(A, id, (uint32_t)__ldcs(A.od_flags + id), __ldcs(A.rank_in + id), S);
-    }
-    diff = butterfly(diff);
-    if (lane == 0) s_red[warp] = diff;
-    __syncthreads();
-    if (warp == 0) {
-        const double t = butterfly(lane < CB_THREADS / 32 ? s_red[lane] : 0.0);
-        if (lane == 0) A.diff_parts[A.dp_total + blockIdx.x] = t;
-    }
-    __syncthreads();
-    if (tid == 0) {
-        if (A.npeers > 0) __threadfence_system(); else __threadfence();
-        s_last = (atomicAdd(&A.ctrl->arrived, 1u) == gridDim.x - 1);
-    }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    const int32_t nparts = A.dp_total + A.n_cb;
-    double v = 0.0;
-    for (int32_t i = tid; i < nparts; i += CB_THREADS) v += __ldcg(A.diff_parts + i);
-    v = butterfly(v);
-    if (lane == 0) s_red[warp] = v;
-    __syncthreads();
-    if (warp == 0) {
-        const double t = butterfly(lane < CB_THREADS / 32 ? s_red[lane] : 0.0);
-        for (int i2 = lane; i2 < MAX_STREAMS; i2 += 32) A.ctrl->next[i2] = 0u;
-        if (lane == 0) A.ctrl->arrived = 0u;
-        if (lane == 0 && A.diff_slot) {
-            *A.diff_slot = t;
-            for (int p = 0; p < A.npeers; p++) *A.peer_diff[p] = t;
-        } else if (lane == 0 && A.loop) {
-            const int32_t cnt = A.ctrl->cnt + 1;
-            A.ctrl->diff = t;
-            A.ctrl->cnt = cnt;
-            A.ctrl->done = !((t > A.e) && (cnt < A.max_iter));       // } While ((diff > e) && (cnt < max))
-        }
-        if (lane == 0 && A.my_flag) {      // every store of this sweep (both kernels, all blocks) is ordered before the flags
-            __threadfence_system();
-            *A.my_flag = A.seq;
-            for (int p = 0; p < A.npeers; p++) st_release_sys(A.peer_flag[p], A.seq);
-        }
-    }
+    combine_rows<CB_THREADS>(A, s_red, &s_last);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -779,6 +827,8 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
         cfg.tiers = env_int("GMC_PR_TIERS", cfg.tiers);
         cfg.kmin = env_int("GMC_PR_KMIN", cfg.kmin);
         cfg.split = env_int("GMC_PR_SPLIT", cfg.split);
+        cfg.cold_stream = env_int("GMC_PR_COLD_STREAM", cfg.cold_stream);
+        cfg.kcold = env_int("GMC_PR_KCOLD", cfg.kcold);
         if (cfg.kmin < 1) cfg.kmin = 1;
         if (const char* v = getenv("GMC_PR_TIER_MIN_EDGES")) cfg.tier_min_edges = atoll(v);
         if (const char* v = getenv("GMC_PR_TIER_SCALE")) cfg.tier_scale = atof(v);
@@ -800,6 +850,7 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
     // cut-row arrays of the long sections, diff partials, part slots
     {
         p->n_cb = L.K > 0 ? (L.K + CB_THREADS - 1) / CB_THREADS : 1;
+        if (p->n_cb < sm_count()) p->n_cb = sm_count();          // fused mode: one partial per CTA of pr_sweep
         const size_t nl = (size_t)(L.n_ltslots ? L.n_ltslots : 1), nparts = (size_t)L.dp_total + (size_t)p->n_cb + 1;
         PLAN_TRY(gmc_malloc((void**)&p->head_part, 8 * nl)); PLAN_TRY(gmc_malloc((void**)&p->tail_part, 8 * nl));
         PLAN_TRY(gmc_malloc((void**)&p->split_cnt, 4 * nl)); PLAN_TRY(gmc_malloc((void**)&p->diff_parts, 8 * nparts));
@@ -865,6 +916,11 @@ SweepArgs make_args(const gmc_pr_plan* p, double d, int sweep, gmc_pr_ctrl* ctrl
         static const int cw = env_int("GMC_PR_COLD_WARPS", (PR_THREADS / 32) * 3 / 8);      // 12 of 32 warps
         A.cold_warps = L.split ? cw : PR_THREADS / 32;
         A.split = L.split;
+        A.cold_s = L.thi > L.T ? L.thi + 1 : 0;
+        static const int two = env_int("GMC_PR_TWO_KERNELS", 0);
+        A.fused = two ? 0 : 1;
+        A.bar_target = 0;
+        if (!L.split) A.cold_warps = L.thi > L.T ? env_int("GMC_PR_COLD_WARPS", (PR_THREADS / 32) * 3 / 8) : 0;
     }
     A.head_part = p->head_part; A.tail_part = p->tail_part; A.split_cnt = p->split_cnt; A.diff_parts = p->diff_parts; A.parts = p->parts;
     A.contrib_in = p->contrib[parity]; A.contrib_out = p->contrib[parity ^ 1];
@@ -907,29 +963,50 @@ int launch_init(const gmc_pr_plan* p, cudaStream_t st) {
     return GMC_OK;
 }
 
-// one sweep = pr_sweep + pr_combine, both launched with programmatic stream serialization: the next kernel's blocks may
-// become resident while this one's tail drains (they order themselves behind it with griddepcontrol.wait);
-// GMC_PR_NO_PDL=1 = plain launches
-int launch_sweep(const gmc_pr_plan* p, const SweepArgs& A, cudaStream_t st) {
+// One sweep = one launch of pr_sweep: cooperative (every CTA resident: the grid barrier before the split rows) and with
+// programmatic stream serialization (the next sweep's CTAs take their SMs while this one's tail drains; they order
+// themselves behind it with griddepcontrol.wait).  GMC_PR_NO_PDL=1 = plain cooperative launches; GMC_PR_TWO_KERNELS=1 = no
+// barrier, the split rows in a second kernel (pr_combine).  `state` = the plan that owns the control block.
+int launch_sweep(gmc_pr_plan* state, const gmc_pr_plan* p, SweepArgs A, cudaStream_t st) {
     static const bool pdl = getenv("GMC_PR_NO_PDL") == nullptr;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
+    static int coop_pdl_ok = 1;              // cleared when the driver refuses the two attributes together
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeCooperative;
+    at[0].val.cooperative = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)p->grid);
     cfg.blockDim = dim3(PR_THREADS);
     cfg.dynamicSmemBytes = p->smem;
     cfg.stream = st;
-    cfg.attrs = at;
+    if (A.fused) {
+        state->bar_arrivals += (unsigned)p->grid;
+        A.bar_target = state->bar_arrivals;
+        A.n_cb = p->grid;
+        cfg.attrs = at;
+        cfg.numAttrs = (pdl && coop_pdl_ok) ? 2 : 1;
+        cudaError_t e = cudaLaunchKernelEx(&cfg, pr_sweep, A);
+        if (e != cudaSuccess && cfg.numAttrs == 2) {       // cooperative + programmatic serialization not accepted: cooperative only
+            cudaGetLastError();
+            coop_pdl_ok = 0;
+            cfg.numAttrs = 1;
+            e = cudaLaunchKernelEx(&cfg, pr_sweep, A);
+        }
+        GMC_CUDA(e);
+        return GMC_OK;
+    }
+    cfg.attrs = at + 1;
     cfg.numAttrs = pdl ? 1 : 0;
     GMC_CUDA(cudaLaunchKernelEx(&cfg, pr_sweep, A));
-    cfg.gridDim = dim3((unsigned)p->n_cb);
+    cfg.gridDim = dim3((unsigned)(p->L.K > 0 ? (p->L.K + CB_THREADS - 1) / CB_THREADS : 1));
+    A.n_cb = (int32_t)cfg.gridDim.x;
     cfg.blockDim = dim3(CB_THREADS);
     cfg.dynamicSmemBytes = 0;
     GMC_CUDA(cudaLaunchKernelEx(&cfg, pr_combine, A));
     return GMC_OK;
 }
-constexpr int LAUNCHES_PER_SWEEP = 2;
+constexpr int LAUNCHES_PER_SWEEP = 1;
 
 }  // namespace
 
@@ -990,6 +1067,7 @@ static int run_pagerank(gmc_graph* g, gmc_pr_plan* const* plans, int nplans, gmc
     const int world = p0->world;
     const bool sharded = world > 1;
     GMC_CUDA(cudaMemsetAsync(p0->ctrl, 0, sizeof(gmc_pr_ctrl), st));
+    p0->bar_arrivals = 0;
     cudaEvent_t ev0, ev1;
     GMC_CUDA(cudaEventCreate(&ev0));
     GMC_CUDA(cudaEventCreate(&ev1));
@@ -1011,7 +1089,7 @@ static int run_pagerank(gmc_graph* g, gmc_pr_plan* const* plans, int nplans, gmc
             for (int i = 0; i < nplans; i++) {
                 SweepArgs A = make_args(plans[i], d, issued, p0->ctrl, 1, e, max_iter);
                 if (sharded) set_exchange_args(p0, plans[i], issued, p0->seq + 1, A);
-                GMC_TRY(launch_sweep(plans[i], A, st));
+                GMC_TRY(launch_sweep(p0, plans[i], A, st));
                 launches += LAUNCHES_PER_SWEEP;
             }
             if (sharded) {
@@ -1032,7 +1110,7 @@ static int run_pagerank(gmc_graph* g, gmc_pr_plan* const* plans, int nplans, gmc
         GMC_CUDA(cudaMemcpyAsync(&h, p0->ctrl, sizeof(h), cudaMemcpyDeviceToHost, st));
         GMC_CUDA(cudaStreamSynchronize(st));
     } while (!h.done);
-    if (h.error) { set_error("pagerank: a peer rank did not finish its sweep in time (peer-memory exchange)"); return GMC_ERR_STATE; }
+    if (h.error) { set_error(h.error == 2 ? "pagerank: the grid barrier of pr_sweep timed out" : "pagerank: a peer rank did not finish its sweep in time (peer-memory exchange)"); return GMC_ERR_STATE; }
     if (sharded && comm)      // the result vector: gather the owned slices of rank[] once
         GMC_TRY(gmc_comm_allgather_segments(comm, p0->rank[h.cnt & 1], 8, p0->L.seg_off.data(), p0->L.seg_len.data(), 3, st));
     k_unpermute<<<div_up(g->N, 256), 256, 0, st>>>(p0->rank[h.cnt & 1], p0->L.new_of_old, g->N, rank_dev);
@@ -1096,6 +1174,7 @@ int gmc_pagerank_sharded_time_sweeps(gmc_graph* g, gmc_comm* comm, double d, int
     gmc_pr_plan* p = g->pr;
     GMC_TRY(plan_map_peers(p, comm, st));
     GMC_CUDA(cudaMemsetAsync(p->ctrl, 0, sizeof(gmc_pr_ctrl), st));
+    p->bar_arrivals = 0;
     GMC_TRY(launch_init(p, st));
     std::vector<cudaEvent_t> ev(3 * (size_t)n);
     for (auto& e : ev) GMC_CUDA(cudaEventCreate(&e));
@@ -1104,7 +1183,7 @@ int gmc_pagerank_sharded_time_sweeps(gmc_graph* g, gmc_comm* comm, double d, int
         if (timed) GMC_CUDA(cudaEventRecord(ev[3 * (k - warmup)], st));
         SweepArgs A = make_args(p, d, k, p->ctrl, 0, 0.0, 0);
         if (world > 1) set_exchange_args(p, p, k, p->seq + 1, A);
-        GMC_TRY(launch_sweep(p, A, st));
+        GMC_TRY(launch_sweep(p, p, A, st));
         if (timed) GMC_CUDA(cudaEventRecord(ev[3 * (k - warmup) + 1], st));
         if (world > 1) {
             p->seq++;
@@ -1222,7 +1301,7 @@ int gmc_pagerank_plan_info(gmc_graph* g, gmc_pagerank_plan_info_t* out) {
     out->total_entries = L.EN; out->n_long_tasks = L.streams[0].n_ltasks; out->n_short_tasks = L.streams[0].n_stasks;
     out->grid = p->grid; out->threads = PR_THREADS; out->smem_bytes = (int32_t)p->smem;
     out->n_pos = L.n_pos; out->n_src = L.n_src; out->tiers = L.T; out->segments = L.n_seg; out->split_rows = L.K; out->part_slots = L.n_parts;
-    out->home_entries = L.streams[0].entries; out->hot0_entries = L.hot0_entries; out->cold_entries = L.cold_entries; out->segment_entries = L.seg_entries;
+    out->home_entries = L.streams[0].entries; out->hot0_entries = L.hot0_entries; out->cold_entries = L.cold_entries; out->segment_entries = L.seg_entries; out->cold_stream_entries = L.cold_stream_entries;
     {
         int c = 0;
         for (int b = 0; b < p->grid; b++) c += L.sched[(size_t)b * SCHED_W] > 1;          // CTAs that start in a warm tier

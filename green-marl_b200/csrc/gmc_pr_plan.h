@@ -71,6 +71,8 @@ struct Config {
     int grid = 148;                    // CTAs of the sweep
     int row_cost = 0;                  // shard cuts: entries one row epilogue weighs (grows with the world size)
     double tier_scale = 1.25;          // multiplier on the CTAs given to the tier streams
+    int cold_stream = 1;               // MIXED mode with warm tiers: the cold entries of split rows get their own stream (class T + 1)
+    int kcold = 4;                     // ... when the row has at least this many of them
     int split = 0;                     // 1: SPLIT mode (tier 0 as a segment stream, home = cold entries only); see the header
     double r_smem = 2.4, r_miss = 0.75;   // gathers per clock and SM: shared memory / L2 (sched model)
 };
@@ -97,13 +99,14 @@ struct Stream {
 struct Plan {
     int32_t N = 0, M = 0, world = 1, shard = 0;
     int32_t T = 0, NH = HT;
+    int32_t thi = 0;                              // highest class with a stream: T, or T + 1 = the cold stream (stream thi + 1)
     int32_t g_n_long = 0, n_pos = 0, n_src = 0, g_nz_slices = 0, g_z0 = 0;
     int32_t lt = 2048, lt_shift = 11, st_cost = 2048, slice_ovh = 68, minpad = 72;
     int32_t jl0 = 0, n_long = 0, s0 = 0, n_slices = 0, z0 = 0, z_end = 0, n_ztasks = 0;
     int32_t EN = 0, n_eoff = 0, n_seg = 0, K = 0, n_parts = 0;
     int32_t n_sbeg = 0, n_ltslots = 0, n_stslots = 0;
     int32_t dp_short = 0, dp_zero = 0, dp_cut = 0, dp_total = 0;     // diff_parts: [home long | home short | zero | cut rows]
-    int64_t hot0_entries = 0, cold_entries = 0, seg_entries = 0;
+    int64_t hot0_entries = 0, cold_entries = 0, seg_entries = 0, cold_stream_entries = 0;
     int32_t split = 0;                            // 1: SPLIT mode (see the header)
     Stream streams[MAX_TIERS + 2];                // [0] home, [t + 1] tier t
     std::vector<int64_t> seg_off, seg_len;        // [world][3] id ranges owned by every rank (long, short, zero)
@@ -254,26 +257,28 @@ struct GlobalLenF {
 };
 
 struct RowCtx {        // the shard's rows: r in [0, nl) long rows (id = jl0 + 1 + r), r >= nl short rows (id = short_id0 + r - nl)
-    int32_t n, nl, jl0, short_id0, tlo, T, kmin;       // tiers tlo..T have streams (tlo = 0 in SPLIT mode, 1 otherwise)
+    int32_t n, nl, jl0, short_id0, tlo, T, thi, kmin, kcold;   // thi = T, or T + 1 = the cold class when it has a stream       // tiers tlo..T have streams (tlo = 0 in SPLIT mode, 1 otherwise)
     const int32_t *old_of_new, *r_begin, *r_node_idx, *code;
     PRP_HD int32_t id_of(int32_t r) const { return r < nl ? jl0 + 1 + r : short_id0 + (r - nl); }
 };
 
 // emits the segment records of one row from its per-tier counts; returns the number of entries that move to segments
 template <typename CNT>
-PRP_HD int32_t emit_segments(const CNT* cnt, int tlo, int T, int kmin, int32_t r, uint32_t* mask_out, int32_t* nrec, unsigned long long* rec_key,
+PRP_HD int32_t emit_segments(const CNT* cnt, int tlo, int T, int thi, int kmin, int kcold, int32_t r, uint32_t* mask_out, int32_t* nrec, unsigned long long* rec_key,
                              int32_t* rec_j, int32_t rec_cap, int32_t* err) {
     uint32_t mask = 0;
     int32_t tot = 0;
     int ns = 0;
     for (int t = tlo; t <= T; t++)
         if ((int32_t)cnt[t] >= (t == 0 ? 1 : kmin)) { mask |= 1u << t; tot += (int32_t)cnt[t]; ns++; }
+    // a row that is split anyway hands its cold entries to the cold stream (any CTA takes its tasks)
+    if (thi > T && ns > 0 && (int32_t)cnt[thi] >= kcold) { mask |= 1u << thi; tot += (int32_t)cnt[thi]; ns++; }
     *mask_out = mask;
     if (ns) {
         int32_t base = atomic_add_i32(nrec, ns);
         if (base + ns > rec_cap) { *err = 2; return tot; }
         int j = 1;
-        for (int t = tlo; t <= T; t++)
+        for (int t = tlo; t <= thi; t++)
             if (mask >> t & 1u) { rec_key[base] = seg_key(t, (int32_t)cnt[t], r); rec_j[base] = j++; base++; }
     }
     return tot;
@@ -294,13 +299,14 @@ struct CountShortF {   // item i: short row r = nl + i
         if (len == 0 ? e_lo != 0 : (rb + len - 1 < e_lo || rb + len - 1 >= e_hi)) return;
         if (c.tlo > c.T || len < (c.tlo == 0 ? 1 : c.kmin)) { segmask[r] = 0; home_len[r] = len; return; }
         uint16_t cnt[MAX_TIERS + 1];
-        for (int t = 0; t <= c.T; t++) cnt[t] = 0;
+        for (int t = 0; t <= c.thi; t++) cnt[t] = 0;
         for (int32_t k = 0; k < len; k++) {
             const int32_t cd = c.code[c.r_node_idx[rb + k]];
             if (cd < 0) cnt[(-cd) / HT]++;
+            else if (c.thi > c.T && cd >= HT) cnt[c.thi]++;
         }
         uint32_t mask;
-        const int32_t tot = emit_segments(cnt, c.tlo, c.T, c.kmin, r, &mask, nrec, rec_key, rec_j, rec_cap, err);
+        const int32_t tot = emit_segments(cnt, c.tlo, c.T, c.thi, c.kmin, c.kcold, r, &mask, nrec, rec_key, rec_j, rec_cap, err);
         segmask[r] = mask;
         home_len[r] = len - tot;
     }
@@ -335,12 +341,13 @@ struct PieceCountF {   // per-tier counts of one piece -> G[t * nps + p]
         const int32_t k0 = ((int32_t)p - piece_first[j]) * PIECE, k1 = std::min(len, k0 + PIECE);
         if (rb + k1 - 1 < e_lo || rb + k1 - 1 >= e_hi) return;
         uint16_t cnt[MAX_TIERS + 1];
-        for (int t = 0; t <= c.T; t++) cnt[t] = 0;
+        for (int t = 0; t <= c.thi; t++) cnt[t] = 0;
         for (int32_t k = k0; k < k1; k++) {
             const int32_t cd = c.code[c.r_node_idx[rb + k]];
             if (cd < 0) cnt[(-cd) / HT]++;
+            else if (c.thi > c.T && cd >= HT) cnt[c.thi]++;
         }
-        for (int t = c.tlo; t <= c.T; t++) G[(size_t)t * nps + p] = cnt[t];
+        for (int t = c.tlo; t <= c.thi; t++) G[(size_t)t * nps + p] = cnt[t];
     }
 };
 struct LongRowF {      // G scanned (exclusive): totals of long row j -> segments
@@ -356,9 +363,9 @@ struct LongRowF {      // G scanned (exclusive): totals of long row j -> segment
         const int32_t p0 = piece_first[j], p1 = piece_first[j + 1];
         int32_t cnt[MAX_TIERS + 1];
         cnt[0] = 0;
-        for (int t = c.tlo; t <= c.T; t++) cnt[t] = G[(size_t)t * nps + p1] - G[(size_t)t * nps + p0];
+        for (int t = 0; t <= c.thi; t++) cnt[t] = t >= c.tlo ? G[(size_t)t * nps + p1] - G[(size_t)t * nps + p0] : 0;
         uint32_t mask = 0;
-        const int32_t tot = c.tlo <= c.T ? emit_segments(cnt, c.tlo, c.T, c.kmin, (int32_t)j, &mask, nrec, rec_key, rec_j, rec_cap, err) : 0;
+        const int32_t tot = c.tlo <= c.T ? emit_segments(cnt, c.tlo, c.T, c.thi, c.kmin, c.kcold, (int32_t)j, &mask, nrec, rec_key, rec_j, rec_cap, err) : 0;
         segmask[j] = mask;
         home_len[j] = len - tot;
     }
@@ -484,6 +491,8 @@ struct FillCtx {
     const int32_t *pslot, *seg_ebase, *seg_estride, *new_of_old, *eoff;
     int32_t* E;
 };
+// class of an entry with code cd: its tier (code < 0), the cold class (no slot, and the cold stream exists), or -1 = stays home
+PRP_HD int entry_class(const RowCtx& c, int32_t cd) { return cd < 0 ? (-cd) / HT : ((c.thi > c.T && cd >= HT) ? c.thi : -1); }
 PRP_HD int32_t home_value(const FillCtx& f, int32_t cd, int32_t src) { return cd < 0 ? HT + f.new_of_old[src] : cd; }
 
 struct FillShortF {    // item i: short row r = nl + i; its home entries go to column-major slice slots, original order kept
@@ -505,12 +514,12 @@ struct FillShortF {    // item i: short row r = nl + i; its home entries go to c
         }
         SegCursor cur;
         int j = 1;
-        for (int t = 0; t <= c.T; t++)
+        for (int t = 0; t <= c.thi; t++)
             if (mask >> t & 1u) { const int32_t s = f.pslot[r] + j++; cur.pos[t] = f.seg_ebase[s]; cur.stride[t] = f.seg_estride[s]; }
         for (int32_t k = 0; k < len; k++) {
             const int32_t src = c.r_node_idx[rb + k], cd = c.code[src];
-            const int t = cd < 0 ? (-cd) / HT : -1;
-            if (t >= 0 && (mask >> t & 1u)) { f.E[cur.pos[t]] = (-cd) - t * HT; cur.pos[t] += cur.stride[t]; }
+            const int t = entry_class(c, cd);
+            if (t >= 0 && (mask >> t & 1u)) { f.E[cur.pos[t]] = cd < 0 ? (-cd) - t * HT : cd; cur.pos[t] += cur.stride[t]; }
             else { f.E[h] = home_value(f, cd, src); h += 32; }
         }
     }
@@ -529,7 +538,7 @@ struct FillPieceF {    // one piece of a long row: the scanned piece table says 
         SegCursor cur;
         int32_t moved = 0;
         int jj = 1;
-        for (int t = 0; t <= c.T; t++)
+        for (int t = 0; t <= c.thi; t++)
             if (mask >> t & 1u) {
                 const int32_t s = f.pslot[j] + jj++;
                 const int32_t before = G[(size_t)t * nps + p] - G[(size_t)t * nps + p0];
@@ -540,8 +549,8 @@ struct FillPieceF {    // one piece of a long row: the scanned piece table says 
         int32_t h = f.eoff[j] + (k0 - moved);
         for (int32_t k = k0; k < k1; k++) {
             const int32_t src = c.r_node_idx[rb + k], cd = c.code[src];
-            const int t = cd < 0 ? (-cd) / HT : -1;
-            if (t >= 0 && (mask >> t & 1u)) { f.E[cur.pos[t]] = (-cd) - t * HT; cur.pos[t] += cur.stride[t]; }
+            const int t = entry_class(c, cd);
+            if (t >= 0 && (mask >> t & 1u)) { f.E[cur.pos[t]] = cd < 0 ? (-cd) - t * HT : cd; cur.pos[t] += cur.stride[t]; }
             else f.E[h++] = home_value(f, cd, src);
         }
     }
@@ -689,7 +698,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     int32_t h3[4] = {0, 0, 0, 0};
     std::vector<int32_t> cutsL((size_t)world + 1), cutsS((size_t)world + 1), cutsZ((size_t)world + 1);
     std::vector<long long> h_tier_out(MAX_TIERS + 2, 0);
-    int32_t tlo = 1, g_n_slices = 0, nl = 0, ns = 0, nrows = 0, short_id0 = 0, nps = 0, rec_cap = 0, nseg = 0, X = 0, herr = 0;
+    int32_t tlo = 1, thi = 0, g_n_slices = 0, nl = 0, ns = 0, nrows = 0, short_id0 = 0, nps = 0, rec_cap = 0, nseg = 0, X = 0, herr = 0;
     uint32_t* segmask = nullptr;
     int32_t *home_len = nullptr, *nrec = nullptr, *rec_j = nullptr, *rec_j2 = nullptr, *np = nullptr, *piece_row = nullptr, *G = nullptr;
     unsigned long long *rec_key = nullptr, *rec_key2 = nullptr;
@@ -720,7 +729,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     // warm tiers: as many as asked for and as there are sources to fill them
     {
         int T = cfg.tiers;
-        if (T > MAX_TIERS) T = MAX_TIERS;
+        if (T > MAX_TIERS - 1) T = MAX_TIERS - 1;            // class T + 1 may be the cold stream
         if ((int64_t)m < cfg.tier_min_edges) T = 0;
         const int full = (P.n_src + HT_REAL - 1) / HT_REAL;      // tiers needed to give every source a slot
         if (T > full - 1) T = full - 1 > 0 ? full - 1 : 0;
@@ -728,6 +737,8 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
         P.split = (T >= 1 && cfg.split) ? 1 : 0;
     }
     tlo = P.split ? 0 : 1;
+    thi = (!P.split && P.T >= 1 && cfg.cold_stream) ? P.T + 1 : P.T;
+    P.thi = thi;
     be.pfor(n, HotF{so_ids, outdeg, hotslot_old, (P.T + 1) * HT_REAL});
     be.pfor((int64_t)(P.T + 1) * 64, TierSumF{so_ids, outdeg, (P.T + 1) * HT_REAL, n, tier_out});
     PRP_TRY(be.alloc((void**)&P.idslot, 4 * (size_t)P.NH));
@@ -776,14 +787,14 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     nrows = nl + 32 * ns;
     short_id0 = P.g_n_long + 1 + 32 * P.s0;
     if (nrows >= (1 << 27)) { P.error = "pagerank plan: more than 2^27 rows in one shard"; rc = -1; goto done; }
-    rc_ = RowCtx{n, nl, P.jl0, short_id0, tlo, P.T, cfg.kmin, P.old_of_new, in.r_begin, in.r_node_idx, code};
+    rc_ = RowCtx{n, nl, P.jl0, short_id0, tlo, P.T, thi, cfg.kmin, cfg.kcold, P.old_of_new, in.r_begin, in.r_node_idx, code};
 
     // ---- 3. pass 1 over the shard's reverse edges: (row, tier) counts -> segments, home lengths
     PRP_TRY(tmp.get(&segmask, (size_t)nrows + 1)); PRP_TRY(tmp.get(&home_len, (size_t)nrows + 32)); PRP_TRY(tmp.get(&nrec, 1));
     PRP_TRY(be.zero(nrec, 4)); PRP_TRY(be.zero(home_len, 4 * ((size_t)nrows + 32)));
     {
         // a row has at most one record per tier, and a record stands for >= 1 (tier 0) / >= kmin entries
-        const int64_t cap = tlo <= P.T ? std::min<int64_t>((int64_t)(P.T + 1 - tlo) * nrows, (int64_t)m / (tlo == 0 ? 1 : cfg.kmin) + 1) + 1 : 1;
+        const int64_t cap = tlo <= P.T ? std::min<int64_t>((int64_t)(thi + 1 - tlo) * nrows, (int64_t)m / (tlo == 0 ? 1 : cfg.kmin) + 1) + 1 : 1;
         if (cap > 0x7fffff00LL) { P.error = "pagerank plan: too many segment records"; rc = -1; goto done; }
         rec_cap = (int32_t)cap;
     }
@@ -791,11 +802,11 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     PRP_TRY(tmp.get(&rec_j, (size_t)rec_cap)); PRP_TRY(tmp.get(&rec_j2, (size_t)rec_cap));
     nps = (int32_t)std::min<int64_t>((int64_t)m / PIECE + nl + 2, 0x7fffff00LL);
     PRP_TRY(tmp.get(&np, (size_t)nl + 1)); PRP_TRY(tmp.get(&piece_row, (size_t)nps));
-    PRP_TRY(tmp.get(&G, (size_t)(P.T + 1) * nps));
+    PRP_TRY(tmp.get(&G, (size_t)(thi + 1) * nps));
     be.pfor((int64_t)nl + 1, PieceNumF{rc_, np});
     PRP_TRY(be.scan_i32(np, (size_t)nl + 1));                               // np = piece_first from here on
     be.pfor(nps, PieceRowF{np, nl, piece_row});
-    if (tlo <= P.T) PRP_TRY(be.zero(G, 4 * (size_t)(P.T + 1) * nps));
+    if (tlo <= P.T) PRP_TRY(be.zero(G, 4 * (size_t)(thi + 1) * nps));
     {
         // the reverse edges may still be arriving over PCIe (gmc_pagerank_host_csr): count chunk by chunk behind the copies
         const int nch = be.edge_chunks();
@@ -811,7 +822,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
             if (e_hi > e_lo) e_lo = e_hi;
         }
     }
-    if (tlo <= P.T) PRP_TRY(be.scan_i32(G, (size_t)(P.T + 1) * nps));
+    if (tlo <= P.T) PRP_TRY(be.scan_i32(G, (size_t)(thi + 1) * nps));
     be.pfor(nl, LongRowF{rc_, np, G, nps, segmask, home_len, nrec, rec_j, err, rec_key, rec_cap});
     PRP_TRY(be.d2h(&nseg, nrec, 4));
     PRP_TRY(be.d2h(&herr, err, 4));
@@ -822,7 +833,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     PRP_TRY(tmp.get(&tier_q, MAX_TIERS + 3)); PRP_TRY(tmp.get(&tier_mid, MAX_TIERS + 3));
     PRP_TRY(be.zero(tier_q, 4 * (MAX_TIERS + 3))); PRP_TRY(be.zero(tier_mid, 4 * (MAX_TIERS + 3)));
     if (nseg > 0) PRP_TRY(be.sort_u64(rec_key, rec_key2, rec_j, rec_j2, nseg, 64));
-    be.pfor(P.T + 2, TierBoundF{rec_key2, nseg, P.T, tier_q, tier_mid});
+    be.pfor(thi + 2, TierBoundF{rec_key2, nseg, thi, tier_q, tier_mid});
     PRP_TRY(tmp.get(&nparts, (size_t)nrows + 1)); PRP_TRY(tmp.get(&issplit, (size_t)nrows + 1));
     be.pfor((int64_t)nrows + 1, PartsF{segmask, nrows, nparts, issplit});
     PRP_TRY(be.scan_i32(nparts, (size_t)nrows + 1));                        // nparts = pslot from here on
@@ -857,7 +868,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
         // eoff indices: home long [0, nl], home slices [nl, nl + ns], tier t long [nl+ns+tq[t], nl+ns+tm[t]], sliced from there to tq[t+1]
         h_idx.clear();
         h_idx.push_back(0); h_idx.push_back(nl); h_idx.push_back(nl + ns);
-        for (int t = 0; t <= P.T; t++) { h_idx.push_back(nl + ns + h_tq[t]); h_idx.push_back(nl + ns + h_tm[t]); h_idx.push_back(nl + ns + h_tq[t + 1]); }      // stream t + 1
+        for (int t = 0; t <= thi; t++) { h_idx.push_back(nl + ns + h_tq[t]); h_idx.push_back(nl + ns + h_tm[t]); h_idx.push_back(nl + ns + h_tq[t + 1]); }      // stream t + 1
         h_idx.push_back(X);
         h_val.assign(h_idx.size(), 0);
         PRP_TRY(tmp.get(&gidx, h_idx.size())); PRP_TRY(tmp.get(&gout, h_idx.size()));
@@ -867,7 +878,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
         P.EN = h_val.back();
         if (P.EN < 0) { P.error = "pagerank plan: entry array exceeds int32 offsets"; rc = -1; goto done; }
         int32_t sb = 0, lto = 0, sto = 0;
-        for (int s = 0; s <= P.T + 1; s++) {
+        for (int s = 0; s <= thi + 1; s++) {
             Stream& st = S[s];
             int32_t i_long, i_mid, i_end, v_long, v_mid, v_end;
             if (s == 0) { i_long = 0; i_mid = nl; i_end = nl + ns; v_long = h_val[0]; v_mid = h_val[1]; v_end = h_val[2]; }
@@ -898,14 +909,14 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
         P.n_sbeg = sb; P.n_ltslots = lto; P.n_stslots = sto;
         PRP_TRY(be.alloc((void**)&P.sbeg, 4 * (size_t)sb)); PRP_TRY(tmp.get(&scost, (size_t)sb));
         PRP_TRY(be.alloc((void**)&P.ltask_row, 4 * (size_t)lto)); PRP_TRY(be.alloc((void**)&P.stask_slice, 4 * (size_t)sto));
-        for (int s = 0; s <= P.T + 1; s++) {
+        for (int s = 0; s <= thi + 1; s++) {
             Stream& st = S[s];
             const int32_t i_end = s == 0 ? nl + ns : h_idx[3 * s + 2];
             be.pfor((int64_t)st.n_slices + 1, SbegF{P.eoff, st.i_mid, s == 0 ? 1 : 32, st.n_slices, i_end, P.sbeg + st.sbeg_off});
             be.pfor((int64_t)st.n_slices + 1, SliceCostF{P.sbeg + st.sbeg_off, st.n_slices, P.slice_ovh, scost + st.sbeg_off});
         }
         PRP_TRY(be.scan_i32(scost, (size_t)sb));
-        for (int s = 0; s <= P.T + 1; s++) {
+        for (int s = 0; s <= thi + 1; s++) {
             Stream& st = S[s];
             be.pfor((int64_t)st.n_ltasks + 1, LtaskF{P.eoff + st.lbeg_off, st.n_long, st.n_ltasks, P.lt, st.e_long, P.ltask_row + st.lt_off});
             be.pfor((int64_t)st.n_stasks + 1, StaskF{scost + st.sbeg_off, st.n_slices, st.n_stasks, P.st_cost, st.n_big, s == 0 ? cfg.tail_shift : 0, P.stask_slice + st.st_off});
@@ -927,10 +938,10 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     {
         Stream* S = P.streams;
         int64_t seg_total = 0;
-        for (int s = 1; s <= P.T + 1; s++) {
+        for (int s = 1; s <= thi + 1; s++) {
             const int64_t slots = (int64_t)h_val[3 * s + 2] - h_val[3 * s];
             S[s].entries = (int32_t)std::min<int64_t>(slots, 0x7fffffff);
-            seg_total += slots;
+            if (s == thi + 1 && thi > P.T) P.cold_stream_entries = slots; else seg_total += slots;
         }
         P.seg_entries = seg_total;
         const double frac = world > 1 ? (double)(nl + ns * 32) / (double)(P.n_pos > 0 ? P.n_pos : 1) : 1.0;

@@ -32,7 +32,7 @@ class PlanInfo(C.Structure):
     _fields_ = [(k, C.c_int32) for k in ("n_long", "hot_n", "n_slices", "long_entries", "total_entries", "n_long_tasks",
                                          "n_short_tasks", "grid", "threads", "smem_bytes", "n_pos", "n_src", "tiers", "segments",
                                          "split_rows", "part_slots", "tier_ctas", "home_entries")] + \
-               [(k, C.c_int64) for k in ("hot0_entries", "cold_entries", "segment_entries")]
+               [(k, C.c_int64) for k in ("hot0_entries", "cold_entries", "segment_entries", "cold_stream_entries")]
 
 
 ARR = dict(begin=0, node_idx=1, r_begin=2, r_node_idx=3, e_rev2idx=4, e_idx2idx=5)

@@ -147,6 +147,7 @@ typedef struct {
     int64_t hot0_entries;   /* gathers of the home stream served by tier 0 (shared memory) */
     int64_t cold_entries;   /* gathers of the home stream that go to L2 */
     int64_t segment_entries;/* entry slots of the tier streams (shared-memory gathers) */
+    int64_t cold_stream_entries; /* entry slots of the cold stream (L2 gathers of split rows, taken by any CTA) */
 } gmc_pagerank_plan_info_t;
 int gmc_pagerank_plan_info(gmc_graph* g, gmc_pagerank_plan_info_t* out);
 

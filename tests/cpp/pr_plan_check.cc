@@ -103,6 +103,8 @@ int main(int argc, char** argv) {
     prp::Config cfg;
     cfg.tiers = tiers; cfg.kmin = kmin; cfg.tier_min_edges = 0;
     cfg.split = getenv("PRP_SPLIT") ? atoi(getenv("PRP_SPLIT")) : 1;
+    cfg.cold_stream = getenv("PRP_COLD") ? atoi(getenv("PRP_COLD")) : 1;
+    cfg.kcold = 2;
     cfg.row_cost = world > 2 ? 2 * (world - 2) : 0;
     if (const char* big = getenv("PRP_BIGTASKS")) if (atoi(big)) { cfg.lt = 8192; cfg.st_cost = 4096; cfg.slice_ovh = 136; }
     std::vector<prp::Plan> plans((size_t)world);
@@ -130,8 +132,8 @@ int main(int argc, char** argv) {
         const prp::Plan& P = plans[r];
         slot_row.assign((size_t)P.n_parts + 1, -1);
         for (int32_t k = 0; k < P.K; k++) for (int32_t s = P.pbeg[k]; s < P.pbeg[k + 1]; s++) slot_row[s] = P.prow[k];
-        auto decode = [&](int s, int32_t x) -> int32_t { return s == 0 ? (x < HT ? P.idslot[x] : x - HT) : P.idslot[(s - 1) * HT + x]; };
-        for (int s = 0; s <= P.T + 1; s++) {
+        auto decode = [&](int s, int32_t x) -> int32_t { return (s == 0 || (s == P.thi + 1 && P.thi > P.T)) ? (x < HT ? P.idslot[x] : x - HT) : P.idslot[(s - 1) * HT + x]; };
+        for (int s = 0; s <= P.thi + 1; s++) {
             const prp::Stream& st = P.streams[s];
             if (st.e_long & 3) { printf("FAIL: stream %d long section not 16-byte aligned\n", s); bad++; }
             for (int32_t j = 0; j < st.n_long; j++) {
@@ -207,9 +209,9 @@ int main(int argc, char** argv) {
                 if (of & prp::OD_HOT) hout[P.hotslot[id]] = c;
             };
             auto home_finish = [&](int32_t id, double S) { if ((uint32_t)P.od_flags[id] & prp::OD_SPLIT) part[P.home_slot[id]] = S; else finish(id, S); };
-            for (int s = 0; s <= P.T + 1; s++) {
+            for (int s = 0; s <= P.thi + 1; s++) {
                 const prp::Stream& st = P.streams[s];
-                auto val = [&](int32_t x) -> double { return s == 0 ? (x < HT ? hin[x] : cin[x - HT]) : hin[(s - 1) * HT + x]; };
+                auto val = [&](int32_t x) -> double { return (s == 0 || (s == P.thi + 1 && P.thi > P.T)) ? (x < HT ? hin[x] : cin[x - HT]) : hin[(s - 1) * HT + x]; };
                 for (int32_t j = 0; j < st.n_long; j++) {
                     double S = 0.0;
                     for (int32_t x = P.eoff[st.lbeg_off + j]; x < P.eoff[st.lbeg_off + j + 1]; x++) S += val(P.E[x]);
