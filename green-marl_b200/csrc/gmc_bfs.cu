@@ -472,7 +472,10 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     const float thr = (float)n * 0.05f;   // RRD_THRESHOLD, gm_bfs_template.h:359 (float arithmetic as in the reference)
     const unsigned fin_grid = (unsigned)div_up(w->words, BFS_THREADS);
     const unsigned exp_grid = (unsigned)sm_count() * 8;
-    bool device_driven = world == 1 && getenv("GMC_BFS_HOST_LOOP") == nullptr;
+    // Measured on the LJ-shaped graph (gpurun r2e): device-driven 0.43 ms per traversal, host-driven 0.37 ms -- five launches per
+    // level, two or three of them leaving at once (~3 us each), and the levels enqueued past the end of the traversal cost more
+    // than the host round trip they replace.  So the host-driven loop stays the default; GMC_BFS_DEVICE_LOOP=1 selects this one.
+    bool device_driven = world == 1 && getenv("GMC_BFS_DEVICE_LOOP") != nullptr && getenv("GMC_BFS_HOST_LOOP") == nullptr;
     if (device_driven) {
         // Single GPU: the kernels of several levels are enqueued back to back, the state machine runs on the device
         // (BfsCtl); the host only looks at the `done` word the last bfs_finish of a batch publishes.

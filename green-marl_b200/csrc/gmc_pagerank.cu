@@ -30,6 +30,7 @@
 #include <mutex>
 #include <vector>
 #include <stdlib.h>
+#include <time.h>
 
 using namespace gmc;
 using prp::HT;
@@ -719,6 +720,18 @@ struct CudaBackend {
         return cudaMemcpyAsync(d, s, b, cudaMemcpyHostToDevice, st) == cudaSuccess ? 0 : fail("copy to device");
     }
     int sync() { return cudaStreamSynchronize(st) == cudaSuccess ? 0 : fail("synchronize"); }
+    // GMC_PR_PLAN_TIMING=1: wall-clock time of every step of the builder (with a stream sync: the steps no longer overlap)
+    double t_last = -1.0;
+    void mark(const char* what) {
+        static const bool on = getenv("GMC_PR_PLAN_TIMING") != nullptr;
+        if (!on) return;
+        cudaStreamSynchronize(st);
+        struct timespec ts;
+        clock_gettime(CLOCK_MONOTONIC, &ts);
+        const double now = ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
+        if (t_last >= 0) fprintf(stderr, "pagerank plan: %-40s %8.3f ms\n", what, now - t_last);
+        t_last = now;
+    }
     // copy-in still in flight (gmc_pagerank_host_csr): the offsets arrive first, the edges in chunks
     int begin_offsets_ready() {
         if (g->pending && cudaStreamWaitEvent(st, g->pending->small, 0) != cudaSuccess) return fail("wait for offsets");
@@ -841,6 +854,7 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
         cfg.grid = sm_count();
         cfg.row_cost = shard_row_cost(world);
         CudaBackend be{st, g, std::string()};
+        be.mark("start");
         prp::Input in;
         in.n = n; in.m = m; in.begin = g->begin; in.r_begin = g->r_begin; in.r_node_idx = g->r_node_idx; in.world = world; in.rank = rank;
         rc = prp::build(be, in, cfg, L);

@@ -71,7 +71,7 @@ struct Config {
     int grid = 148;                    // CTAs of the sweep
     int row_cost = 0;                  // shard cuts: entries one row epilogue weighs (grows with the world size)
     double tier_scale = 1.25;          // multiplier on the CTAs given to the tier streams
-    int cold_stream = 1;               // MIXED mode with warm tiers: the cold entries of split rows get their own stream (class T + 1)
+    int cold_stream = 0;               // MIXED mode with warm tiers: the cold entries of split rows get their own stream (class T + 1)
     int kcold = 4;                     // ... when the row has at least this many of them
     int split = 0;                     // 1: SPLIT mode (tier 0 as a segment stream, home = cold entries only); see the header
     double r_smem = 2.4, r_miss = 0.75;   // gathers per clock and SM: shared memory / L2 (sched model)
@@ -284,6 +284,28 @@ PRP_HD int32_t emit_segments(const CNT* cnt, int tlo, int T, int thi, int kmin, 
     return tot;
 }
 
+// Walks the entries [a, b) of a reverse-CSR row in order, f(src, code[src]).  The sources and their codes are fetched eight at a
+// time so that a thread has 8 + 8 independent loads in flight instead of a chain of two dependent loads per entry: the plan
+// passes are latency chains of up to 512 entries per thread.
+template <class F>
+PRP_HD void walk_entries(const int32_t* __restrict__ idx, const int32_t* __restrict__ code, int32_t a, int32_t b, F&& f) {
+    for (int32_t k = a; k < b; k += 8) {
+        int32_t sr[8], cd[8];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int i = 0; i < 8; i++) sr[i] = k + i < b ? idx[k + i] : -1;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int i = 0; i < 8; i++) cd[i] = sr[i] >= 0 ? code[sr[i]] : 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int i = 0; i < 8; i++) if (sr[i] >= 0) f(sr[i], cd[i]);
+    }
+}
+
 struct CountShortF {   // item i: short row r = nl + i
     RowCtx c;
     uint32_t* segmask;
@@ -300,11 +322,11 @@ struct CountShortF {   // item i: short row r = nl + i
         if (c.tlo > c.T || len < (c.tlo == 0 ? 1 : c.kmin)) { segmask[r] = 0; home_len[r] = len; return; }
         uint16_t cnt[MAX_TIERS + 1];
         for (int t = 0; t <= c.thi; t++) cnt[t] = 0;
-        for (int32_t k = 0; k < len; k++) {
-            const int32_t cd = c.code[c.r_node_idx[rb + k]];
+        const RowCtx& cc = c;
+        walk_entries(c.r_node_idx, c.code, rb, rb + len, [&](int32_t, int32_t cd) {
             if (cd < 0) cnt[(-cd) / HT]++;
-            else if (c.thi > c.T && cd >= HT) cnt[c.thi]++;
-        }
+            else if (cc.thi > cc.T && cd >= HT) cnt[cc.thi]++;
+        });
         uint32_t mask;
         const int32_t tot = emit_segments(cnt, c.tlo, c.T, c.thi, c.kmin, c.kcold, r, &mask, nrec, rec_key, rec_j, rec_cap, err);
         segmask[r] = mask;
@@ -342,11 +364,11 @@ struct PieceCountF {   // per-tier counts of one piece -> G[t * nps + p]
         if (rb + k1 - 1 < e_lo || rb + k1 - 1 >= e_hi) return;
         uint16_t cnt[MAX_TIERS + 1];
         for (int t = 0; t <= c.thi; t++) cnt[t] = 0;
-        for (int32_t k = k0; k < k1; k++) {
-            const int32_t cd = c.code[c.r_node_idx[rb + k]];
+        const RowCtx& cc = c;
+        walk_entries(c.r_node_idx, c.code, rb + k0, rb + k1, [&](int32_t, int32_t cd) {
             if (cd < 0) cnt[(-cd) / HT]++;
-            else if (c.thi > c.T && cd >= HT) cnt[c.thi]++;
-        }
+            else if (cc.thi > cc.T && cd >= HT) cnt[cc.thi]++;
+        });
         for (int t = c.tlo; t <= c.thi; t++) G[(size_t)t * nps + p] = cnt[t];
     }
 };
@@ -506,22 +528,20 @@ struct FillShortF {    // item i: short row r = nl + i; its home entries go to c
         const uint32_t mask = f.segmask[r];
         int32_t h = f.eoff[c.nl + (i >> 5)] + (int32_t)(i & 31);
         if (!mask) {
-            for (int32_t k = 0; k < len; k++, h += 32) {
-                const int32_t src = c.r_node_idx[rb + k];
-                f.E[h] = home_value(f, c.code[src], src);
-            }
+            const FillCtx& f0 = f;
+            walk_entries(c.r_node_idx, c.code, rb, rb + len, [&](int32_t src, int32_t cd) { f0.E[h] = home_value(f0, cd, src); h += 32; });
             return;
         }
         SegCursor cur;
         int j = 1;
         for (int t = 0; t <= c.thi; t++)
             if (mask >> t & 1u) { const int32_t s = f.pslot[r] + j++; cur.pos[t] = f.seg_ebase[s]; cur.stride[t] = f.seg_estride[s]; }
-        for (int32_t k = 0; k < len; k++) {
-            const int32_t src = c.r_node_idx[rb + k], cd = c.code[src];
-            const int t = entry_class(c, cd);
-            if (t >= 0 && (mask >> t & 1u)) { f.E[cur.pos[t]] = cd < 0 ? (-cd) - t * HT : cd; cur.pos[t] += cur.stride[t]; }
-            else { f.E[h] = home_value(f, cd, src); h += 32; }
-        }
+        const FillCtx& ff = f;
+        walk_entries(c.r_node_idx, c.code, rb, rb + len, [&](int32_t src, int32_t cd) {
+            const int t = entry_class(ff.c, cd);
+            if (t >= 0 && (mask >> t & 1u)) { ff.E[cur.pos[t]] = cd < 0 ? (-cd) - t * HT : cd; cur.pos[t] += cur.stride[t]; }
+            else { ff.E[h] = home_value(ff, cd, src); h += 32; }
+        });
     }
 };
 struct FillPieceF {    // one piece of a long row: the scanned piece table says where the piece starts in every destination
@@ -547,12 +567,12 @@ struct FillPieceF {    // one piece of a long row: the scanned piece table says 
                 moved += before;
             }
         int32_t h = f.eoff[j] + (k0 - moved);
-        for (int32_t k = k0; k < k1; k++) {
-            const int32_t src = c.r_node_idx[rb + k], cd = c.code[src];
-            const int t = entry_class(c, cd);
-            if (t >= 0 && (mask >> t & 1u)) { f.E[cur.pos[t]] = cd < 0 ? (-cd) - t * HT : cd; cur.pos[t] += cur.stride[t]; }
-            else f.E[h++] = home_value(f, cd, src);
-        }
+        const FillCtx& ff = f;
+        walk_entries(c.r_node_idx, c.code, rb + k0, rb + k1, [&](int32_t src, int32_t cd) {
+            const int t = entry_class(ff.c, cd);
+            if (t >= 0 && (mask >> t & 1u)) { ff.E[cur.pos[t]] = cd < 0 ? (-cd) - t * HT : cd; cur.pos[t] += cur.stride[t]; }
+            else ff.E[h++] = home_value(ff, cd, src);
+        });
     }
 };
 struct GatherF {       // out[i] = a[idx[i]]: a handful of offsets the host needs
@@ -746,6 +766,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     be.pfor(n, RelabelF{sr_ids, P.new_of_old, P.old_of_new});
     be.pfor(n, ByIdF{P.old_of_new, outdeg, hotslot_old, P.od_flags, P.hotslot, P.idslot, code, P.split});
 
+    be.mark("1 degrees, orders, hot slots, ids");
     // ---- 2. task sizes, the shard's rows
     P.lt = cfg.lt; P.st_cost = cfg.st_cost; P.slice_ovh = cfg.slice_ovh;
     for (P.lt_shift = 0; (1 << P.lt_shift) < P.lt; P.lt_shift++) {}
@@ -789,6 +810,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     if (nrows >= (1 << 27)) { P.error = "pagerank plan: more than 2^27 rows in one shard"; rc = -1; goto done; }
     rc_ = RowCtx{n, nl, P.jl0, short_id0, tlo, P.T, thi, cfg.kmin, cfg.kcold, P.old_of_new, in.r_begin, in.r_node_idx, code};
 
+    be.mark("2 shard cuts");
     // ---- 3. pass 1 over the shard's reverse edges: (row, tier) counts -> segments, home lengths
     PRP_TRY(tmp.get(&segmask, (size_t)nrows + 1)); PRP_TRY(tmp.get(&home_len, (size_t)nrows + 32)); PRP_TRY(tmp.get(&nrec, 1));
     PRP_TRY(be.zero(nrec, 4)); PRP_TRY(be.zero(home_len, 4 * ((size_t)nrows + 32)));
@@ -829,6 +851,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     if (herr) { P.error = "pagerank plan: segment record buffer overflow"; rc = -1; goto done; }
     P.n_seg = nseg;
 
+    be.mark("3 pass 1 (counts, segments)");
     // ---- 4. segments sorted by (tier, length descending, row); split rows and their part slots
     PRP_TRY(tmp.get(&tier_q, MAX_TIERS + 3)); PRP_TRY(tmp.get(&tier_mid, MAX_TIERS + 3));
     PRP_TRY(be.zero(tier_q, 4 * (MAX_TIERS + 3))); PRP_TRY(be.zero(tier_mid, 4 * (MAX_TIERS + 3)));
@@ -847,6 +870,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     PRP_TRY(be.alloc((void**)&P.pbeg, 4 * ((size_t)P.K + 1))); PRP_TRY(be.alloc((void**)&P.prow, 4 * ((size_t)P.K + 1)));
     be.pfor((int64_t)nrows + 1, SplitF{rc_, segmask, nparts, issplit, nrows, P.pbeg, P.prow, P.home_slot, P.od_flags});
 
+    be.mark("4 segment sort, split rows");
     // ---- 5. entry offsets of everything: [home long rows | home slices | sorted segments] + a trailing 0, one scan
     X = nl + ns + nseg;
     P.n_eoff = X + 1;
@@ -861,6 +885,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     PRP_TRY(tmp.get(&seg_ebase, (size_t)P.n_parts + 1)); PRP_TRY(tmp.get(&seg_estride, (size_t)P.n_parts + 1));
     be.pfor(nseg, SegDestF{rec_key2, rec_j2, tier_mid, nparts, P.eoff + nl + ns, P.seg_slot, seg_ebase, seg_estride});
 
+    be.mark("5 entry offsets, segment destinations");
     // ---- 6. stream table (host) -- needs the entry offsets at the stream boundaries
     {
         Stream* S = P.streams;
@@ -925,6 +950,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
         PRP_TRY(be.d2h(h_tier_out.data(), tier_out, 8 * (MAX_TIERS + 2)));
     }
 
+    be.mark("6 stream table, tasks");
     // ---- 7. pass 2: the entries
     PRP_TRY(be.alloc((void**)&P.E, 4 * ((size_t)P.EN + 8)));
     PRP_TRY(be.zero(P.E, 4 * ((size_t)P.EN + 8)));
@@ -952,6 +978,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
         P.cold_entries = P.split ? home_slots : (home_slots > P.hot0_entries ? home_slots - P.hot0_entries : 0);
     }
 
+    be.mark("7 pass 2 (entries)");
     // ---- 8. diff_parts layout and the CTA schedule
     P.dp_short = P.streams[0].n_ltasks;
     P.dp_zero = P.dp_short + P.streams[0].n_stasks;
@@ -963,6 +990,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     PRP_TRY(be.alloc((void**)&P.streams_dev, sizeof(Stream) * (MAX_TIERS + 2)));
     PRP_TRY(be.h2d(P.streams_dev, P.streams, sizeof(Stream) * (MAX_TIERS + 2)));
     PRP_TRY(be.sync());
+    be.mark("8 schedule, end");
 done:
     if (rc != 0 && P.error.empty()) P.error = be.last_error();
     return rc;

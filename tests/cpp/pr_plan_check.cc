@@ -19,6 +19,7 @@ struct CpuBackend {
     int d2h(void* d, const void* s, size_t b) { memcpy(d, s, b); return 0; }
     int h2d(void* d, const void* s, size_t b) { memcpy(d, s, b); return 0; }
     int sync() { return 0; }
+    void mark(const char*) {}
     int begin_offsets_ready() { return 0; }
     int edges_ready() { return 0; }
     int n_chunks = 1, m_edges = 0;      // the check also runs the chunked pass 1 (edges arriving in pieces)

@@ -342,6 +342,7 @@ def test_pagerank_tiered_streams(gm, oracle, g_rmat, tiers, kmin, big, split, mo
     monkeypatch.setenv("GMC_PR_KMIN", str(kmin))
     monkeypatch.setenv("GMC_PR_BIGTASKS", big)
     monkeypatch.setenv("GMC_PR_SPLIT", split)
+    monkeypatch.setenv("GMC_PR_COLD_STREAM", "1" if kmin == 2 else "0")       # one case with the cold stream of the split rows
     dg = dev_graph(gm, g_rmat)
     pi = dg.pagerank_plan_info()
     assert pi["tiers"] >= 3 and pi["segments"] > 0 and pi["split_rows"] > 0 and pi["part_slots"] == pi["segments"] + pi["split_rows"]
@@ -372,14 +373,12 @@ def test_pagerank_tiered_emulated_shards(gm, oracle, g_rmat, monkeypatch):
 
 
 def test_bfs_host_loop_and_deep_graph(gm, oracle, g_rmat, monkeypatch):
-    """single-GPU traversals are device-driven (state machine in bfs_finish, kernels of several levels enqueued at once); the
-    host-driven loop (multi-GPU runs, GMC_BFS_HOST_LOOP=1, graphs deeper than the device trace) must give the same levels and
-    trace.  A path graph of 3000 vertices has 3000 levels: more than the device trace holds -> falls back to the host loop."""
+    """the device-driven traversal (GMC_BFS_DEVICE_LOOP=1: state machine in bfs_finish, kernels of several levels enqueued at
+    once) and the host-driven loop (default; multi-GPU runs; graphs deeper than the device trace) give the same levels and trace.  A path graph of 3000 vertices has 3000 levels: more than the device trace holds -> falls back to the host loop."""
     root = graphs.first_root_with_edges(g_rmat)
+    lev2, _, trace2, cnt2 = dev_graph(gm, g_rmat).bfs_levels(root)               # host-driven (default)
+    monkeypatch.setenv("GMC_BFS_DEVICE_LOOP", "1")
     lev, _, trace, cnt = dev_graph(gm, g_rmat).bfs_levels(root)
-    monkeypatch.setenv("GMC_BFS_HOST_LOOP", "1")
-    lev2, _, trace2, cnt2 = dev_graph(gm, g_rmat).bfs_levels(root)
-    monkeypatch.delenv("GMC_BFS_HOST_LOOP")
     assert np.array_equal(lev, lev2) and list(trace) == list(trace2) and list(cnt) == list(cnt2)
     n = 3000
     begin = np.minimum(np.arange(n + 1), n - 1).astype(np.int32)          # v -> v + 1
