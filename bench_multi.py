@@ -239,6 +239,39 @@ def run_multi(args, n, m, workload):
                "pinned": pin_ok,
                "breakdown_ms_max_over_ranks": {k: round(float(np.mean(v)), 2) for k, v in parts.items()}, "note": "each rank copies its 1/world slice of the CSR host->device, the slices are allgathered over NVLink, every rank plans its shard; all inside the timed region"}
 
+    # ---- the same e2e step through the DEVICE GROUP (gmc_group_*, what GM_CUDA_DEVICES=N selects for the reference's unchanged
+    # drivers): ONE process (rank 0 here; the other ranks of the launcher idle) drives all N GPUs -- every device copies 1/N of the
+    # host CSR over its own PCIe link, peers through plain pointers, each device copies its slice of rank[] back
+    group_e2e = None
+    if e2e is not None and not os.environ.get("GMC_BENCH_NO_GROUP"):
+        dist.barrier()
+        if rank == 0:
+            try:
+                sharded_result = rank_host.copy()
+                grp = lib.group(world)
+                gtimes = []
+                for k in range(1 + e2e_steps):
+                    t0 = time.perf_counter()
+                    grp.upload(pinned["begin"], None, pinned["r_begin"], pinned["r_node_idx"])
+                    t1 = time.perf_counter()
+                    _, ginfo = grp.pagerank(1e-30, 0.85, iters, out=rank_host)
+                    t2 = time.perf_counter()
+                    if k > 0:
+                        gtimes.append(((t2 - t0) * 1e3, (t1 - t0) * 1e3, (t2 - t1) * 1e3))
+                gms = float(np.mean([t[0] for t in gtimes]))
+                group_e2e = {"value": round(m * iters / gms / 1e6, 3), "unit": "GTEPS", "ms_per_step": round(gms, 3), "steps": e2e_steps,
+                             "copy_in_ms": round(float(np.mean([t[1] for t in gtimes])), 2),
+                             "plan_sweeps_copy_out_ms": round(float(np.mean([t[2] for t in gtimes])), 2),
+                             "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(rank_host.nbytes), "devices": grp.size(),
+                             "exchange_path": grp.exchange_path(), "iterations": int(ginfo.iterations),
+                             "max_abs_vs_torchrun_ranks": float(np.abs(rank_host - sharded_result).max()),
+                             "what": "gmc_group_graph_upload + gmc_group_pagerank from ONE process over all devices (host CSR in, host rank[] out)"}
+                grp.close()
+                del sharded_result
+            except Exception as ex:
+                group_e2e = {"error": str(ex)[:300]}
+        dist.barrier()
+
     if rank == 0:
         line = {
             "metric": "pagerank_gteps", "value": round(value, 3), "unit": "GTEPS", "n_gpus": world, "steps": args.steps,
@@ -250,7 +283,7 @@ def run_multi(args, n, m, workload):
                        "l2": "inputs larger than L2 (index stream %d MB per rank per sweep); no explicit flush" % (4 * m // world // 2**20),
                        "parallelism": f"{world} ranks x 1 GPU, destination-range shards, contributions exchanged per sweep (" + g.pagerank_exchange_path() + ")"},
             "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": None, "bfs": bfs,
-            "parity": parity, "single_gpu_same_graph": single,
+            "parity": parity, "single_gpu_same_graph": single, "e2e_device_group": group_e2e,
             "nccl_version": comm.nccl_version(),
         }
         import __main__ as _main           # bench.py, run as a script: its emit() owns the real stdout

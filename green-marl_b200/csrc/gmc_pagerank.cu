@@ -843,6 +843,11 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
         cfg.cold_stream = env_int("GMC_PR_COLD_STREAM", cfg.cold_stream);
         cfg.kcold = env_int("GMC_PR_KCOLD", cfg.kcold);
         if (cfg.kmin < 1) cfg.kmin = 1;
+        // One-shot call on host arrays (gmc_pagerank_host_csr): the plan serves max_iter sweeps and is thrown away.  The tier
+        // streams need a second pass over the edges after the last byte of the copy-in has landed (+2.1 ms on the LJ-shaped
+        // graph) and save 0.02 ms per sweep, so they pay from ~100 sweeps on; below that the plan without tiers is built,
+        // whose entries are written chunk by chunk behind the PCIe copy.  Resident graphs keep their plan: always tiered.
+        if (g->pending && !getenv("GMC_PR_TIERS") && g->pr_iters_hint > 0 && g->pr_iters_hint < 100) cfg.tiers = 0;
         if (const char* v = getenv("GMC_PR_TIER_MIN_EDGES")) cfg.tier_min_edges = atoll(v);
         if (const char* v = getenv("GMC_PR_TIER_SCALE")) cfg.tier_scale = atof(v);
         if (const char* v = getenv("GMC_PR_RATES")) sscanf(v, "%lf,%lf", &cfg.r_smem, &cfg.r_miss);
@@ -1286,6 +1291,7 @@ int gmc_pagerank_host_csr(int32_t num_nodes, int32_t num_edges, const int32_t* b
         if (!ok) { fail("copy-in"); break; }
         g->has_reverse = true;
         g->pending = &pu;
+        g->pr_iters_hint = max_iter > 0 ? max_iter : 1;
         rc = gmc_pagerank_dev(g, e, d, max_iter, tmp, info, nullptr);       // plan (waits on the events) + sweeps
         g->pending = nullptr;
         if (rc == GMC_OK) rc = gmc_d2h(rank_host, tmp, sizeof(double) * (size_t)num_nodes, nullptr);

@@ -333,6 +333,17 @@ struct CountShortF {   // item i: short row r = nl + i
         home_len[r] = len - tot;
     }
 };
+struct HomeLenDegF {   // no tier streams: every entry stays home, nothing needs the edges
+    RowCtx c;
+    int32_t nrows;
+    uint32_t* segmask;
+    int32_t* home_len;
+    PRP_HD void operator()(int64_t r) const {
+        const int32_t id = c.id_of((int32_t)r);
+        segmask[r] = 0;
+        home_len[r] = id <= c.n ? c.r_begin[c.old_of_new[id] + 1] - c.r_begin[c.old_of_new[id]] : 0;
+    }
+};
 struct PieceNumF {     // pieces of long row j (+ a trailing 0 for the scan)
     RowCtx c;
     int32_t* np;
@@ -520,11 +531,13 @@ PRP_HD int32_t home_value(const FillCtx& f, int32_t cd, int32_t src) { return cd
 struct FillShortF {    // item i: short row r = nl + i; its home entries go to column-major slice slots, original order kept
     FillCtx f;
     int32_t ns;
+    int32_t e_lo, e_hi;    // rows whose last edge lies in [e_lo, e_hi) (plans without tiers are filled behind the copy-in)
     PRP_HD void operator()(int64_t i) const {
         const RowCtx& c = f.c;
         const int32_t r = c.nl + (int32_t)i, id = c.short_id0 + (int32_t)i;
         if (id > c.n) return;
         const int32_t v = c.old_of_new[id], rb = c.r_begin[v], len = c.r_begin[v + 1] - rb;
+        if (len == 0 || rb + len - 1 < e_lo || rb + len - 1 >= e_hi) return;
         const uint32_t mask = f.segmask[r];
         int32_t h = f.eoff[c.nl + (i >> 5)] + (int32_t)(i & 31);
         if (!mask) {
@@ -548,12 +561,14 @@ struct FillPieceF {    // one piece of a long row: the scanned piece table says 
     FillCtx f;
     const int32_t *piece_first, *piece_row, *G;
     int32_t nps;
+    int32_t e_lo, e_hi;    // pieces whose last edge lies in [e_lo, e_hi)
     PRP_HD void operator()(int64_t p) const {
         const RowCtx& c = f.c;
         if (p >= piece_first[c.nl]) return;
         const int32_t j = piece_row[p], v = c.old_of_new[c.jl0 + 1 + j], rb = c.r_begin[v], len = c.r_begin[v + 1] - rb;
         const int32_t p0 = piece_first[j];
         const int32_t k0 = ((int32_t)p - p0) * PIECE, k1 = std::min(len, k0 + PIECE);
+        if (rb + k1 - 1 < e_lo || rb + k1 - 1 >= e_hi) return;
         const uint32_t mask = f.segmask[j];
         SegCursor cur;
         int32_t moved = 0;
@@ -829,7 +844,8 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     PRP_TRY(be.scan_i32(np, (size_t)nl + 1));                               // np = piece_first from here on
     be.pfor(nps, PieceRowF{np, nl, piece_row});
     if (tlo <= P.T) PRP_TRY(be.zero(G, 4 * (size_t)(thi + 1) * nps));
-    {
+    if (tlo > P.T) be.pfor(nrows, HomeLenDegF{rc_, nrows, segmask, home_len});        // no tiers: the layout follows from the degrees
+    else {
         // the reverse edges may still be arriving over PCIe (gmc_pagerank_host_csr): count chunk by chunk behind the copies
         const int nch = be.edge_chunks();
         int32_t e_lo = 0;
@@ -845,7 +861,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
         }
     }
     if (tlo <= P.T) PRP_TRY(be.scan_i32(G, (size_t)(thi + 1) * nps));
-    be.pfor(nl, LongRowF{rc_, np, G, nps, segmask, home_len, nrec, rec_j, err, rec_key, rec_cap});
+    if (tlo <= P.T) be.pfor(nl, LongRowF{rc_, np, G, nps, segmask, home_len, nrec, rec_j, err, rec_key, rec_cap});
     PRP_TRY(be.d2h(&nseg, nrec, 4));
     PRP_TRY(be.d2h(&herr, err, 4));
     if (herr) { P.error = "pagerank plan: segment record buffer overflow"; rc = -1; goto done; }
@@ -956,8 +972,24 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     PRP_TRY(be.zero(P.E, 4 * ((size_t)P.EN + 8)));
     {
         FillCtx f{rc_, segmask, nparts, seg_ebase, seg_estride, P.new_of_old, P.eoff, P.E};
-        be.pfor((int64_t)32 * ns, FillShortF{f, ns});
-        be.pfor(nps, FillPieceF{f, np, piece_row, G, nps});
+        if (tlo > P.T) {
+            // no tier streams: nothing above needed the edges, so the entries are written chunk by chunk behind their copy-in
+            const int nch = be.edge_chunks();
+            int32_t e_lo = 0;
+            for (int ch = 0; ch < nch; ch++) {
+                int32_t e_hi = m;
+                PRP_TRY(be.edge_chunk_ready(ch, &e_hi));
+                if (ch == nch - 1) e_hi = m;
+                if (e_hi > e_lo) {
+                    be.pfor((int64_t)32 * ns, FillShortF{f, ns, e_lo, e_hi});
+                    be.pfor(nps, FillPieceF{f, np, piece_row, G, nps, e_lo, e_hi});
+                    e_lo = e_hi;
+                }
+            }
+        } else {
+            be.pfor((int64_t)32 * ns, FillShortF{f, ns, 0, 0x7fffffff});
+            be.pfor(nps, FillPieceF{f, np, piece_row, G, nps, 0, 0x7fffffff});
+        }
     }
     // real entries per tier stream = sum of its segment lengths: long part from the offsets is padded, so walk the keys on the host
     // only for small plans; otherwise estimate from the padded slots (<= 3 % off)
