@@ -464,7 +464,10 @@ def run_single(args, n, m):
            "h2d_gbs": round(h2d / float(np.mean(parts["h2d_ms"])) / 1e6, 1)}
     if os.environ.get("GMC_BENCH_DEBUG"):
         sys.stderr.write("e2e parts: %r\n" % ({k: [round(x, 1) for x in v] for k, v in parts.items()},))
-    assert np.array_equal(rank_host, rank_gpu), "e2e result differs from the resident-graph result"
+    # the one-shot call builds the plan without tier streams (it serves 20 sweeps once: DESIGN.md 6.1), the resident graph has
+    # them: same values to the last bits of the summation order, far inside the 1e-9 tolerance
+    e2e["max_abs_vs_resident_result"] = float(np.abs(rank_host - rank_gpu).max())
+    assert e2e["max_abs_vs_resident_result"] <= 1e-12, "e2e result differs from the resident-graph result"
 
     # ---- BFS (configs[2]) on the same graph: hop_dist over 16 roots + the gm_bfs_template traversal ------
     deg = np.diff(host["begin"])

@@ -659,6 +659,21 @@ __global__ void k_init(SweepArgs A, double* __restrict__ contrib0, double* __res
     contrib0[id] = c;
     if (of & OD_HOT) hot0[A.hotslot[id]] = c;
 }
+// EXPERIMENT (GMC_PR_FAKE_BANKS, results invalid): rewrites the bank residue of the shared-memory entries so that every LDS.64 of
+// a warp is conflict-free -- the upper bound of what a bank-aware entry order inside segments could buy.  ell = 0: row-major
+// section (lane = (p / 4) % 32), ell = 1: sliced section (lane = p % 32, column = p / 32)
+__global__ void k_fake_banks(int32_t* __restrict__ E, int32_t e0, int32_t e1, int ell, int only_below) {
+    const int32_t p = e0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= e1) return;
+    const int32_t x = E[p];
+    if (x <= 0 || x >= only_below) return;
+    const int32_t q = p - e0;
+    const int res = ell ? ((q & 31) + (q >> 5)) & 15 : (q >> 2) & 15;
+    int32_t y = (x & ~15) | res;
+    if (y <= 0) y = 16 | res;
+    if (y >= HT) y -= 16;
+    E[p] = y;
+}
 // hotpack from the contribution vector (NCCL exchange path: the peers' contributions arrive by allgather, not by remote stores)
 __global__ void k_hot_refresh(const int32_t* __restrict__ idslot, int32_t nh, const double* __restrict__ contrib, double* __restrict__ hot) {
     int32_t s = blockIdx.x * blockDim.x + threadIdx.x;
@@ -865,6 +880,21 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
         rc = prp::build(be, in, cfg, L);
         if (rc != 0) { set_error("%s", L.error.empty() ? "pagerank plan: failed" : L.error.c_str()); if (rc > 0) rc = GMC_ERR_CUDA; goto fail; }
         if (cudaGetLastError() != cudaSuccess) { rc = GMC_ERR_CUDA; set_error("pagerank plan: a plan kernel failed to launch"); goto fail; }
+    }
+    if (const char* fb = getenv("GMC_PR_FAKE_BANKS")) {     // experiment: 1 = tier streams, 2 = + the tier-0 entries of the home stream
+        const int mode = atoi(fb);
+        for (int s2 = mode >= 2 ? 0 : 2; s2 <= L.thi + 1; s2++) {
+            if (s2 == 1 && !L.split) continue;
+            const Stream& stx = L.streams[s2];
+            std::vector<int32_t> hb(2);
+            if (stx.EL > 0) k_fake_banks<<<div_up(stx.EL, 256), 256, 0, st>>>(L.E, stx.e_long, stx.e_long + stx.EL, 0, HT);
+            if (stx.n_slices > 0) {
+                int32_t b0 = 0, b1 = 0;
+                cudaMemcpy(&b0, L.sbeg + stx.sbeg_off, 4, cudaMemcpyDeviceToHost);
+                cudaMemcpy(&b1, L.sbeg + stx.sbeg_off + stx.n_slices, 4, cudaMemcpyDeviceToHost);
+                if (b1 > b0) k_fake_banks<<<div_up(b1 - b0, 256), 256, 0, st>>>(L.E, b0, b1, 1, HT);
+            }
+        }
     }
     // cut-row arrays of the long sections, diff partials, part slots
     {
