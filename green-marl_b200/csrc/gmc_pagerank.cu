@@ -386,7 +386,10 @@ __device__ __forceinline__ void short_task(const SweepArgs& A, const Stream& st,
     int L = (__shfl_sync(FULL, sb, 1) - base) >> 5;
     int32_t w[8];
 #pragma unroll
-    for (int k = 0; k < 8; k++) w[k] = (k < L) ? __ldcs(A.E + base + lane + k * 32) : 0;
+    {
+        const int32_t* __restrict__ pe = A.E + base + lane;       // one pointer, constant offsets: 2 instructions per load
+        for (int k = 0; k < 8; k++) w[k] = (k < L) ? __ldcs(pe + k * 32) : 0;
+    }
     double S = 0.0, old = 0.0;
     uint32_t of = 0;          // home: od_flags of the lane's row; tier: part slot + 1 of the lane's segment (0: dead lane)
     while (q < ns) {
@@ -410,7 +413,14 @@ __device__ __forceinline__ void short_task(const SweepArgs& A, const Stream& st,
         }
         int32_t wn[8];
 #pragma unroll
-        for (int k = 0; k < 8; k++) wn[k] = (nj + k < nL) ? __ldcs(A.E + nbase + lane + (nj + k) * 32) : 0;
+        {
+            // the 8 index loads of the next chunk: one pointer and one remaining-column count, so that each load is a
+            // predicate + LDG with an immediate offset (the per-load address arithmetic was 25 % of the kernel's instructions)
+            const int32_t* __restrict__ pe = A.E + nbase + lane + nj * 32;
+            const int rem = nL - nj;
+#pragma unroll
+            for (int k = 0; k < 8; k++) wn[k] = (k < rem) ? __ldcs(pe + k * 32) : 0;
+        }
         double v[8];
 #pragma unroll
         for (int k = 0; k < 8; k++) v[k] = gather<SMEM>(hot, cin_m, w[k]);
@@ -1184,10 +1194,18 @@ int gmc_pagerank_sharded_dev(gmc_graph* g, gmc_comm* comm, double e, double d, i
     GMC_REQUIRE(g->N > 0, GMC_ERR_ARG, "gmc_pagerank_dev: empty graph");
     cudaStream_t st = as_stream(stream);
     const int world = comm ? comm->world : 1, rank = comm ? comm->rank : 0;
+    static const bool timing = getenv("GMC_PR_CALL_TIMING") != nullptr;       // phases of the call, wall clock, to stderr
+    auto now_ms = []() { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; };
+    const double t0 = timing ? now_ms() : 0.0;
     GMC_TRY(graph_plan(g, world, rank, st));
+    const double t1 = timing ? now_ms() : 0.0;
     gmc_pr_plan* p = g->pr;
     GMC_TRY(plan_map_peers(p, comm, st));
-    return run_pagerank(g, &p, 1, world > 1 ? comm : nullptr, e, d, max_iter, rank_dev, info, st);
+    const double t2 = timing ? now_ms() : 0.0;
+    const int rc = run_pagerank(g, &p, 1, world > 1 ? comm : nullptr, e, d, max_iter, rank_dev, info, st);
+    if (timing) fprintf(stderr, "pagerank call (rank %d of %d): plan %.2f ms (block %s), peer mapping %.2f ms, loop + result %.2f ms\n", rank, world,
+                        t1 - t0, p->block_cached ? "reused" : "new", t2 - t1, now_ms() - t2);
+    return rc;
 }
 
 int gmc_pagerank_dev(gmc_graph* g, double e, double d, int32_t max_iter, double* rank_dev, gmc_pagerank_info* info, void* stream) {
