@@ -57,6 +57,7 @@ def run_multi(args, n, m, workload):
     lib.init(local)
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    cpu_group = dist.new_group(backend="gloo")      # host-side barriers: ranks that wait must not spin a kernel on their GPU
     comm = bootstrap_comm(lib, dist, torch, rank, world)
     iters = args.iters
 
@@ -188,7 +189,8 @@ def run_multi(args, n, m, workload):
                   "first_call_s": round(plan_s, 2)}
         del one_dev
     del sharded_rank, bfs_dist_sharded
-    dist.barrier()
+    torch.cuda.synchronize()
+    dist.barrier(group=cpu_group)            # rank 0 alone was busy: the others wait on the host
 
     bfs = {"metric": "bfs_gteps", "value": round(sum(bfs_edges) / sum(bfs_ms) / 1e6, 3), "unit": "GTEPS", "roots": len(roots),
            "ms_per_traversal": round(float(np.mean(bfs_ms)), 4), "edges_per_traversal": int(np.mean(bfs_edges)),
@@ -244,7 +246,8 @@ def run_multi(args, n, m, workload):
     # host CSR over its own PCIe link, peers through plain pointers, each device copies its slice of rank[] back
     group_e2e = None
     if e2e is not None and not os.environ.get("GMC_BENCH_NO_GROUP"):
-        dist.barrier()
+        torch.cuda.synchronize()
+        dist.barrier(group=cpu_group)        # gloo: the idle ranks wait on the host while rank 0's process uses every GPU
         if rank == 0:
             try:
                 sharded_result = rank_host.copy()
@@ -270,7 +273,7 @@ def run_multi(args, n, m, workload):
                 del sharded_result
             except Exception as ex:
                 group_e2e = {"error": str(ex)[:300]}
-        dist.barrier()
+        dist.barrier(group=cpu_group)
 
     if rank == 0:
         line = {
@@ -281,7 +284,7 @@ def run_multi(args, n, m, workload):
                        "graph": "device R-MAT generator seed 1997 a=.57 b=.19 c=.19 permuted (counter-based RNG), identical on every rank",
                        "generate_s": round(gen_s, 2), "first_calls_s": round(warm_s, 2),
                        "l2": "inputs larger than L2 (index stream %d MB per rank per sweep); no explicit flush" % (4 * m // world // 2**20),
-                       "parallelism": f"{world} ranks x 1 GPU, destination-range shards, contributions exchanged per sweep (" + g.pagerank_exchange_path() + ")"},
+                       "parallelism": f"{world} ranks x 1 GPU, destination-range shards, contributions exchanged per sweep (" + exchange_path + ")"},
             "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": None, "bfs": bfs,
             "parity": parity, "single_gpu_same_graph": single, "e2e_device_group": group_e2e,
             "nccl_version": comm.nccl_version(),

@@ -89,7 +89,7 @@ struct gmc_graph {
     // copy-in still in flight (gmc_pagerank_host_csr): begin/r_begin are complete once `small` has fired, r_node_idx[0, end[k])
     // once chunk[k] has; the PageRank plan builder waits on them on its own stream, chunk by chunk (no host sync)
     struct gmc_pending_upload* pending = nullptr;
-    int32_t pr_iters_hint = 0;      // one-shot calls (gmc_pagerank_host_csr): max_iter of the call the plan is built for
+    int32_t pr_iters_hint = 0;      // max_iter of the call the next PageRank plan is built for (0: unknown / build the full plan)
     // lazily built per-algorithm state (invalidated when the CSR changes)
     gmc_pr_plan* pr = nullptr;      // PageRank plan: relabelled entry array, tasks, state buffers (gmc_pagerank.cu)
     gmc_bfs_ws* bfs = nullptr;

@@ -63,8 +63,8 @@ constexpr int SCHED_W = 4;             // tier streams a CTA may stage one after
 constexpr uint32_t OD_SPLIT = 0x80000000u, OD_HOT = 0x40000000u, OD_MASK = 0x3fffffffu;   // od_flags[id]
 
 struct Config {
-    int tiers = 16;                    // warm tiers wanted (0: the single hot block of round 1)
-    int kmin = 4;                      // entries from which a (row, tier) group becomes a segment
+    int tiers = 12;                    // warm tiers wanted (0: the single hot block of round 1)
+    int kmin = 6;                      // entries from which a (row, tier) group becomes a segment
     int64_t tier_min_edges = 4 << 20;  // smaller graphs keep T = 0 (every short row stays bit-identical to the CPU order)
     int lt = 2048, st_cost = 2048, slice_ovh = 68;     // task sizes (entries per long task, cost units per short task)
     int tail_big16 = 14, tail_shift = 2;               // home short tasks: 14/16 of the cost in full tasks, the rest in quarter ones

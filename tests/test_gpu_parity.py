@@ -350,6 +350,7 @@ def test_pagerank_tiered_streams(gm, oracle, g_rmat, tiers, kmin, big, split, mo
     monkeypatch.setenv("GMC_PR_KMIN", str(kmin))
     monkeypatch.setenv("GMC_PR_BIGTASKS", big)
     monkeypatch.setenv("GMC_PR_SPLIT", split)
+    monkeypatch.setenv("GMC_PR_NO_LITE", "1")          # every plan of this test with its tier streams, the first call's too
     monkeypatch.setenv("GMC_PR_COLD_STREAM", "1" if kmin == 2 else "0")       # one case with the cold stream of the split rows
     dg = dev_graph(gm, g_rmat)
     pi = dg.pagerank_plan_info()
