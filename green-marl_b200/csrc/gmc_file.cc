@@ -53,6 +53,17 @@ int gmc_file_read(const char* path, int32_t* begin, int32_t* node_idx) {
     if (rc == GMC_OK && m > 0 && (!node_idx || fread(node_idx, 4, (size_t)m, f) != (size_t)m)) { set_error("%s: error reading edge-end array", path); rc = GMC_ERR_IO; }
     fclose(f);
     if (rc == GMC_OK && !flipped) { swap_words(begin, (size_t)n + 1); if (m) swap_words(node_idx, (size_t)m); }
+    // a truncated or corrupt file must be an error here, not an out-of-bounds access in a kernel: offsets start at 0, never
+    // decrease, end at M; every neighbour id is a vertex
+    if (rc == GMC_OK) {
+        long bad = 0;
+        if (begin[0] != 0 || begin[n] != m) bad = 1;
+#pragma omp parallel for reduction(+ : bad) schedule(static)
+        for (int64_t v = 0; v < n; v++) bad += begin[v + 1] < begin[v];
+#pragma omp parallel for reduction(+ : bad) schedule(static)
+        for (int64_t e2 = 0; e2 < m; e2++) bad += (node_idx[e2] < 0) | (node_idx[e2] >= n);
+        if (bad) { set_error("%s: not a valid CSR (offsets must start at 0, be non-decreasing and end at %d; neighbour ids must be below %d)", path, m, n); rc = GMC_ERR_IO; }
+    }
     return rc;
 }
 

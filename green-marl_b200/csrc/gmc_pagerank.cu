@@ -631,7 +631,9 @@ __global__ void __launch_bounds__(PR_THREADS, 1) pr_sweep(const SweepArgs A) {
     if (!A.fused) return;
     // ---- every task of the sweep is done once all CTAs have passed this grid barrier (cooperative launch: they are all
     // resident); then the split rows.  bar counts arrivals of all launches of the call: this launch ends at bar_target.
-    __threadfence();
+    // (sharded: the epilogues' stores into the peers must be performed system-wide before this CTA counts as arrived -- the
+    // last CTA publishes the sweep's sequence number to the peers on the strength of these arrivals)
+    if (A.npeers > 0) __threadfence_system(); else __threadfence();
     __syncthreads();
     if (tid == 0) {
         atomicAdd(&A.ctrl->bar, 1u);

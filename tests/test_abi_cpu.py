@@ -75,3 +75,24 @@ def test_binary_file_io_through_abi(oracle, tmp_path):
     open(str(tmp_path / "bad.bin"), "wb").write(b"\x00" * 64)
     with pytest.raises(load_package().GmcError):
         lib.file_read(str(tmp_path / "bad.bin"))
+
+
+def test_binary_file_rejects_corrupt_csr(oracle, tmp_path):
+    """a file whose offsets decrease, do not end at M, or whose neighbour ids leave [0, N) is an I/O error, not a kernel fault"""
+    import graphs
+    from gmb200_loader import load_package
+    pkg = load_package()
+    lib = pkg.GmCuda()
+    g = graphs.rmat(oracle, 3000, 40000, seed=3)
+    for what in ("decreasing", "bad_end", "bad_id"):
+        b, i = g["begin"].copy(), g["node_idx"].copy()
+        if what == "decreasing":
+            b[100], b[101] = b[101] + 5, b[100]
+        elif what == "bad_end":
+            b[-1] -= 1
+        else:
+            i[1234] = len(b) + 7
+        p = str(tmp_path / (what + ".bin"))
+        lib.file_write(p, b, i)
+        with pytest.raises(pkg.GmcError):
+            lib.file_read(p)
