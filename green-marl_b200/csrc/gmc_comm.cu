@@ -148,10 +148,14 @@ int gmc_comm_ipc_open_all(gmc_comm* c, void* local_base, void** peer_bases, cuda
         for (int r = 0; r < c->world; r++) peer_bases[r] = (void*)(uintptr_t)all_p[(size_t)r];
         return GMC_OK;
     }
+    // No rank may leave before the collectives below (the others would hang in them): a local failure is carried as ok = 0
+    // through the handle exchange and decided by all ranks together in the agreement allreduce
+    int ok = 1;
     cudaIpcMemHandle_t mine;
+    memset(&mine, 0, sizeof(mine));
     if (cudaIpcGetMemHandle(&mine, local_base) != cudaSuccess) {
         set_error("cudaIpcGetMemHandle: %s", cudaGetErrorString(cudaGetLastError()));
-        return GMC_ERR_STATE;
+        ok = 0;
     }
     std::vector<cudaIpcMemHandle_t> all((size_t)c->world);
     char* stage = nullptr;
@@ -163,7 +167,6 @@ int gmc_comm_ipc_open_all(gmc_comm* c, void* local_base, void** peer_bases, cuda
                          cudaStreamSynchronize(st) != cudaSuccess)) rc = GMC_ERR_CUDA;
     cudaFree(stage);
     if (rc != GMC_OK) { set_error("gmc_comm_ipc_open_all: handle exchange failed"); return rc; }
-    int ok = 1;
     for (int r = 0; r < c->world; r++) {
         peer_bases[r] = nullptr;
         if (r == c->rank) { peer_bases[r] = local_base; continue; }
@@ -186,6 +189,13 @@ int gmc_comm_ipc_open_all(gmc_comm* c, void* local_base, void** peer_bases, cuda
             if (r != c->rank && peer_bases[r]) { cudaIpcCloseMemHandle(peer_bases[r]); peer_bases[r] = nullptr; }
     }
     return rc;
+}
+
+int gmc_comm_stream_barrier(gmc_comm* c, cudaStream_t st) {
+    if (!c || c->world == 1) return GMC_OK;
+    if (!c->scratch) GMC_TRY(gmc_malloc((void**)&c->scratch, 64));
+    GMC_NCCL(g_api.AllReduce(c->scratch, c->scratch, 1, ncclFloat64, ncclSum, c->nccl, st));
+    return GMC_OK;
 }
 
 void gmc_comm_ipc_close_all(int world, int rank, void** peer_bases, bool local) {

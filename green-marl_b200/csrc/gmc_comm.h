@@ -19,4 +19,6 @@ int gmc_comm_allreduce_sum_i64(gmc_comm* c, const long long* send, long long* re
 int gmc_comm_allgather_segments(gmc_comm* c, void* buf, size_t elem_bytes, const int64_t* seg_off, const int64_t* seg_len,
                                 int nseg, cudaStream_t st);
 int gmc_comm_ipc_open_all(gmc_comm* c, void* local_base, void** peer_bases, cudaStream_t st);
+// device-side barrier on `st` (a 1-element allreduce), no host synchronisation
+int gmc_comm_stream_barrier(gmc_comm* c, cudaStream_t st);
 void gmc_comm_ipc_close_all(int world, int rank, void** peer_bases, bool local);

@@ -1139,6 +1139,9 @@ static int run_pagerank(gmc_graph* g, gmc_pr_plan* const* plans, int nplans, gmc
     const bool sharded = world > 1;
     GMC_CUDA(cudaMemsetAsync(p0->ctrl, 0, sizeof(gmc_pr_ctrl), st));
     p0->bar_arrivals = 0;
+    // peer-memory exchange: the ranks enter the loop together (device-side barrier), so that the flag timeout of the sweeps
+    // bounds waits inside the loop only -- not the skew between the ranks' host threads before a repeat call on a kept plan
+    if (sharded && comm && p0->p2p) GMC_TRY(gmc_comm_stream_barrier(comm, st));
     cudaEvent_t ev0, ev1;
     GMC_CUDA(cudaEventCreate(&ev0));
     GMC_CUDA(cudaEventCreate(&ev1));
