@@ -61,7 +61,12 @@ struct gmc_bfs_ws {
     uint32_t* visited = nullptr;      // [wp]
     uint32_t* frontier_bm = nullptr;  // [wp] bitmap of the current level
     uint32_t* cand = nullptr;         // [wp] candidates of the next level (top-down) / next level (bottom-up)
-    uint32_t* allcand = nullptr;      // [world*wp] gathered candidate bitmaps (sharded top-down)
+    uint32_t* allcand = nullptr;      // [world*wp] gathered candidate bitmaps (sharded top-down without peer mapping)
+    // sharded runs: cand is the first of TWO buffers (level parity) in one exportable allocation, mapped by the peers, so that
+    // a top-down level can OR its candidates straight into the OWNER's slice over NVLink (owner-directed exchange)
+    bool peer_tried = false, peer_ok = false, peer_local = false;
+    void* peer_base[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    int rank = 0;
     int32_t* queue[2] = {nullptr, nullptr};   // owned vertices of the current / next level
     int32_t* blk_off = nullptr;       // [N] CTA-relative exclusive degree offsets of the queue entries
     int32_t* blk_total = nullptr;     // [ceil(N/256)]
@@ -82,6 +87,7 @@ struct gmc_bfs_ws {
 void gmc_bfs_ws_free(gmc_graph* g) {
     gmc_bfs_ws* w = g->bfs;
     if (!w) return;
+    if (w->peer_ok) gmc_comm_ipc_close_all(w->world, w->rank, w->peer_base, w->peer_local);
     cudaFree(w->visited); cudaFree(w->frontier_bm); cudaFree(w->cand); cudaFree(w->allcand);
     cudaFree(w->queue[0]); cudaFree(w->queue[1]); cudaFree(w->blk_off); cudaFree(w->blk_total); cudaFree(w->chunks);
     cudaFree(w->counters); cudaFree(w->level); cudaFree(w->edge_sum); cudaFree(w->ctl);
@@ -95,12 +101,13 @@ namespace {
 template <typename L>
 __global__ void bfs_init(L* __restrict__ level, int32_t n, L invalid, int32_t root, uint32_t* __restrict__ visited,
                          uint32_t* __restrict__ frontier, uint32_t* __restrict__ cand, int32_t wp,
-                         int32_t* __restrict__ queue, int root_owned, int32_t* __restrict__ counters) {
+                         int32_t* __restrict__ queue, int root_owned, int32_t* __restrict__ counters, int two_cand = 0) {
     int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) level[i] = (i == root) ? (L)0 : invalid;
     if (i < wp) {
         const uint32_t b = (i == (root >> 5)) ? (1u << (root & 31)) : 0u;
         visited[i] = b; frontier[i] = b; cand[i] = 0u;
+        if (two_cand) cand[wp + i] = 0u;
     }
     if (i == 0) { if (root_owned) queue[0] = root; counters[0] = 0; counters[1] = 0; counters[2] = 0; counters[3] = 0; }
 }
@@ -158,13 +165,30 @@ __device__ __forceinline__ int window_search(int32_t e, int32_t pos) {
     return k;
 }
 
+// Owner-directed exchange of the sharded top-down levels: base[r] = rank r's candidate buffer of this level (peer memory).
+// A candidate is ORed into the local buffer -- which doubles as the "already sent" filter -- and, when another rank owns
+// its word, into that rank's buffer over NVLink: at most one remote atomic per (rank, vertex) and level.
+struct PeerCand {
+    uint32_t* base[8];
+    int32_t wpr, world, rank;
+};
+__device__ __forceinline__ void mark_candidate(uint32_t* __restrict__ cand, const PeerCand& pc, int32_t uw, uint32_t bit) {
+    if (cand[uw] & bit) return;
+    atomicOr(&cand[uw], bit);
+    if (pc.world > 1) {
+        const int o = uw / pc.wpr;
+        if (o != pc.rank) atomicOr_system(pc.base[o] + uw, bit);       // performed at the owner's L2, system scope
+    }
+}
+
 // ---- top-down, step 2: one warp per chunk of TD_CHUNK edge slots ---------------------------------------------
 template <bool BATCHED>
 __global__ void __launch_bounds__(BFS_THREADS)
 td_expand(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_idx, const int32_t* __restrict__ queue, int32_t qcount,
           const int32_t* __restrict__ blk_off, const int32_t* __restrict__ blk_total, const int2* __restrict__ chunks,
           const int32_t* __restrict__ nchunks_p, const uint32_t* __restrict__ visited, uint32_t* __restrict__ cand,
-          const uint8_t* __restrict__ edge_mask, const int32_t* __restrict__ queue_alt = nullptr, const BfsCtl* __restrict__ ctl = nullptr) {
+          const uint8_t* __restrict__ edge_mask, const int32_t* __restrict__ queue_alt = nullptr, const BfsCtl* __restrict__ ctl = nullptr,
+          const PeerCand pc = PeerCand()) {
     const int lane = threadIdx.x & 31;
     if (ctl) {     // device-driven traversal: both forms are enqueued, the one that fits the frontier runs
         if (ctl->done || ctl_bottom_up(ctl->state)) return;
@@ -215,7 +239,7 @@ td_expand(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_id
                         const uint32_t bit = 1u << (u & 31);
                         const int32_t uw = u >> 5;
                         // navigator (check_navigator, gm_bfs_template.h:488-492,596-598): filtered edges are not followed
-                        if (!(visited[uw] & bit) && (!edge_mask || edge_mask[eidx]) && !(cand[uw] & bit)) atomicOr(&cand[uw], bit);
+                        if (!(visited[uw] & bit) && (!edge_mask || edge_mask[eidx])) mark_candidate(cand, pc, uw, bit);
                         todo = false;
                     }
                     if (__any_sync(FULLMASK, todo)) { r0 += 32; load_window(r0); }     // slots beyond the 32-row window
@@ -250,7 +274,7 @@ td_expand(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_id
             if (u[j] < 0) continue;
             const uint32_t bit = 1u << (u[j] & 31);
             const int32_t uw = u[j] >> 5;
-            if (!(vis[j] & bit) && (!edge_mask || edge_mask[eidx[j]]) && !(cand[uw] & bit)) atomicOr(&cand[uw], bit);
+            if (!(vis[j] & bit) && (!edge_mask || edge_mask[eidx[j]])) mark_candidate(cand, pc, uw, bit);
         }
         }
     }
@@ -418,7 +442,7 @@ int ensure_ws(gmc_graph* g, int world) {
     w->chunk_cap = (size_t)g->M / TD_CHUNK + nn / BFS_THREADS + 2;
     int rc = gmc_malloc((void**)&w->visited, wb);
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->frontier_bm, wb);
-    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->cand, wb);
+    if (rc == GMC_OK) rc = world > 1 ? gmc_malloc_ipc((void**)&w->cand, 2 * wb) : gmc_malloc((void**)&w->cand, wb);
     if (rc == GMC_OK && world > 1) rc = gmc_malloc((void**)&w->allcand, wb * (size_t)world);
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->queue[0], sizeof(int32_t) * nn);
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->queue[1], sizeof(int32_t) * nn);
@@ -461,11 +485,26 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     GMC_CUDA(cudaEventCreate(&ev0));
     GMC_CUDA(cudaEventCreate(&ev1));
     int launches = 0, bottom_up = 0;
+    // sharded: map the peers' candidate buffers once per workspace (collective: every rank is here on its first traversal);
+    // not mappable (or GMC_BFS_NO_PEER=1): the levels fall back to allgathering `world` full bitmaps
+    if (world > 1 && !w->peer_tried) {
+        w->peer_tried = true;
+        w->rank = rank;
+        if (!getenv("GMC_BFS_NO_PEER")) {
+            void* bases[8];
+            const int prc = world <= 8 ? gmc_comm_ipc_open_all(comm, w->cand, bases, st) : GMC_ERR_STATE;
+            if (prc == GMC_OK) { for (int r = 0; r < world; r++) w->peer_base[r] = bases[r]; w->peer_ok = true; w->peer_local = comm->local; }
+            else if (prc != GMC_ERR_STATE) return prc;
+        }
+    }
+    const bool peer = world > 1 && w->peer_ok;
     GMC_CUDA(cudaEventRecord(ev0, st));
     int qi = 0;     // queue[qi] = current level
     bfs_init<L><<<div_up(max(n, w->wp), 256), 256, 0, st>>>(level, n, invalid, root, w->visited, w->frontier_bm, w->cand, w->wp,
-                                                              w->queue[0], root_owned ? 1 : 0, w->counters);
+                                                              w->queue[0], root_owned ? 1 : 0, w->counters, world > 1 ? 1 : 0);
     launches++;
+    // nobody sends candidates into a buffer its owner has not cleared yet
+    if (peer) GMC_TRY(gmc_comm_stream_barrier(comm, st));
 
     int state = ST_SMALL;
     int32_t curr_level = 0, curr_count = 1, own_count = root_owned ? 1 : 0;
@@ -536,32 +575,44 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
         GMC_REQUIRE(sizeof(L) == 4 || curr_level + 1 <= 32767, GMC_ERR_STATE, "bfs: more levels than level_t can hold");
         const L nl = (L)(curr_level + 1);
         int use_all = 0;
+        // sharded: the candidate buffer alternates with the level (a rank one level ahead sends into the other buffer)
+        uint32_t* const cand_l = w->cand + (world > 1 ? (size_t)(curr_level & 1) * w->wp : 0);
+        PeerCand pc = PeerCand();
+        if (peer) {
+            for (int r = 0; r < world; r++) pc.base[r] = (uint32_t*)w->peer_base[r] + (size_t)(curr_level & 1) * w->wp;
+            pc.wpr = w->wpr; pc.world = world; pc.rank = rank;
+        }
         if (state == ST_RRD || state == ST_RR2Q) {
             if (own_hi > own_lo) {
                 bu_scan<<<div_up((own_hi - own_lo) * 32, BFS_THREADS), BFS_THREADS, 0, st>>>(rev_begin, rev_idx, n, own_lo, own_hi,
-                                                                                            w->frontier_bm, w->visited, w->cand);
+                                                                                            w->frontier_bm, w->visited, cand_l);
                 launches++;
             }
             bottom_up++;
-            if (world > 1) GMC_TRY(gmc_comm_allgather(comm, w->cand + (size_t)rank * w->wpr, w->cand, sizeof(uint32_t) * (size_t)w->wpr, st));
+            if (world > 1) GMC_TRY(gmc_comm_allgather(comm, cand_l + (size_t)rank * w->wpr, cand_l, sizeof(uint32_t) * (size_t)w->wpr, st));
         } else {
             if (own_count > 0) {
                 td_prepare<<<div_up(own_count, BFS_THREADS), BFS_THREADS, 0, st>>>(fwd_begin, w->queue[qi], own_count, w->blk_off,
                                                                                   w->blk_total, w->chunks, w->counters + 2);
                 if (own_count <= TD_BATCHED_MAX_FRONTIER)
                     td_expand<true><<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[qi], own_count, w->blk_off, w->blk_total,
-                                                                      w->chunks, w->counters + 2, w->visited, w->cand, edge_mask);
+                                                                      w->chunks, w->counters + 2, w->visited, cand_l, edge_mask, nullptr, nullptr, pc);
                 else
                     td_expand<false><<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[qi], own_count, w->blk_off, w->blk_total,
-                                                                       w->chunks, w->counters + 2, w->visited, w->cand, edge_mask);
+                                                                       w->chunks, w->counters + 2, w->visited, cand_l, edge_mask, nullptr, nullptr, pc);
                 launches += 2;
             }
-            if (world > 1) {
-                GMC_TRY(gmc_comm_allgather(comm, w->cand, w->allcand, sizeof(uint32_t) * (size_t)w->wp, st));
+            if (peer) {
+                // every rank's candidates have been ORed into their owners' slices once all expansions are complete (barrier);
+                // then the owned slices are allgathered in place: N/8 bytes per level in total instead of `world` full bitmaps
+                GMC_TRY(gmc_comm_stream_barrier(comm, st));
+                GMC_TRY(gmc_comm_allgather(comm, cand_l + (size_t)rank * w->wpr, cand_l, sizeof(uint32_t) * (size_t)w->wpr, st));
+            } else if (world > 1) {
+                GMC_TRY(gmc_comm_allgather(comm, cand_l, w->allcand, sizeof(uint32_t) * (size_t)w->wp, st));
                 use_all = 1;
             }
         }
-        bfs_finish<L><<<fin_grid, BFS_THREADS, 0, st>>>(w->words, w->wp, world, use_all, w->cand, w->allcand, w->visited, w->frontier_bm,
+        bfs_finish<L><<<fin_grid, BFS_THREADS, 0, st>>>(w->words, w->wp, world, use_all, cand_l, w->allcand, w->visited, w->frontier_bm,
                                                         nl, level, own_lo, own_hi, w->queue[qi ^ 1], w->counters, w->h_counters, ++w->seq);
         launches++;
         GMC_CUDA(cudaGetLastError());

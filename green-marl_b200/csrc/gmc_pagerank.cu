@@ -57,7 +57,9 @@ constexpr int64_t BIG_TASK_ENTRIES = 24000000;   // per-shard entries from which
 // into every peer (world-1 NVLink stores per row), so the weight grows with the world size (profiles/r1p_shard_row_cost.txt)
 static inline int shard_row_cost(int world) {
     if (const char* c = getenv("GMC_PR_ROWCOST")) return atoi(c);      // experiments
-    return world > 2 ? 2 * (world - 2) : 0;
+    // round 2 (tiered sweep, 8 ranks, TW-shaped; profiles/r2r_shard_row_cost_8gpu.txt): weight 12 -> 1605 GTEPS (sweep 0.68 .. 0.82 ms over
+    // the ranks), 20 -> 1715 (0.63 .. 0.76), 30 -> 1639 (0.59 .. 0.80)
+    return world > 2 ? (5 * world) / 2 : 0;
 }
 constexpr unsigned FULL = 0xffffffffu;
 constexpr int MAX_STREAMS = prp::MAX_TIERS + 2;      // home + tiers 0..31
