@@ -490,7 +490,10 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     if (world > 1 && !w->peer_tried) {
         w->peer_tried = true;
         w->rank = rank;
-        if (!getenv("GMC_BFS_NO_PEER")) {
+        // Measured on the TW-shaped graph (profiles/r2t_bfs_exchange_8gpu.txt): owner-directed 1.81 ms per traversal on 8 GPUs
+        // (2.99 ms on 2) against 1.52 ms (2.30 ms) for the allgather of full bitmaps -- the barrier per top-down level (an NCCL
+        // allreduce) and the remote atomics cost more than the 36 MB per level they save.  So it is opt-in: GMC_BFS_PEER=1.
+        if (getenv("GMC_BFS_PEER") && !getenv("GMC_BFS_NO_PEER")) {
             void* bases[8];
             const int prc = world <= 8 ? gmc_comm_ipc_open_all(comm, w->cand, bases, st) : GMC_ERR_STATE;
             if (prc == GMC_OK) { for (int r = 0; r < world; r++) w->peer_base[r] = bases[r]; w->peer_ok = true; w->peer_local = comm->local; }

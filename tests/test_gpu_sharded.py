@@ -64,12 +64,17 @@ def test_more_shards_than_rows(gm, oracle):
     assert np.array_equal(got, want)
 
 
-def test_two_rank_nccl_run(gm):
-    """real multi-process run: PageRank + hop_dist + bfs levels on 2 GPUs equal the 1-GPU results"""
+@pytest.mark.parametrize("bfs_peer", ["0", "1"])
+def test_two_rank_nccl_run(gm, bfs_peer):
+    """real multi-process run: PageRank + hop_dist + bfs levels on 2 GPUs equal the 1-GPU results; bfs_peer = 1: the
+    owner-directed exchange of the top-down levels (GMC_BFS_PEER, remote atomics into the owner's candidate slice)"""
     if gm.device_count() < 2:
         pytest.skip("box has one GPU: the 2-rank NCCL run needs two")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
-           "--master-port", "29541", os.path.join(ROOT, "tests", "multi_gpu_worker.py")]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+           "--master-port", "2954" + bfs_peer, os.path.join(ROOT, "tests", "multi_gpu_worker.py")]
+    env = dict(os.environ)
+    if bfs_peer == "1":
+        env["GMC_BFS_PEER"] = "1"
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "multi_gpu_worker ok" in r.stdout
