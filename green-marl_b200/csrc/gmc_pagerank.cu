@@ -206,12 +206,15 @@ __device__ __forceinline__ double butterfly(double v) {
 template <bool SMEM>
 __device__ __forceinline__ double gather(const double* hot, const double* cin_m, int32_t w) {
     if (SMEM) return hot[w];
+    // (tried in round 2: two predicated loads into one register through inline PTX instead of this branch -- 0.159 -> 0.230 ms
+    // per sweep, profiles/r2x_predicated_gather.txt: warps whose lanes are all hot or all cold skip the other load here)
     return (w < HT) ? hot[w] : __ldcg(cin_m + w);
 }
 
 // new contribution of vertex id: local copy + one copy per peer (fire-and-forget NVLink stores, coalesced across lanes)
 __device__ __forceinline__ void put_contrib(const SweepArgs& A, int32_t id, double c) {
     A.contrib_out[id] = c;
+    if (A.npeers == 0) return;                  // (uniform: one branch instead of seven predicates on a single GPU)
 #pragma unroll
     for (int p = 0; p < MAX_PEERS; p++)
         if (p < A.npeers) A.peer_out[p][id] = c;
@@ -219,6 +222,7 @@ __device__ __forceinline__ void put_contrib(const SweepArgs& A, int32_t id, doub
 __device__ __forceinline__ void put_hot(const SweepArgs& A, int32_t id, double c) {
     const int32_t slot = __ldg(A.hotslot + id);
     A.hot_out[slot] = c;
+    if (A.npeers == 0) return;
 #pragma unroll
     for (int p = 0; p < MAX_PEERS; p++)
         if (p < A.npeers) A.peer_hot[p][slot] = c;
@@ -689,6 +693,10 @@ __global__ void k_fake_banks(int32_t* __restrict__ E, int32_t e0, int32_t e1, in
     if (y >= HT) y -= 16;
     E[p] = y;
 }
+__global__ void k_fake_allhot(int32_t* __restrict__ E, int32_t e0, int32_t e1) {
+    const int32_t p = e0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < e1 && E[p] >= HT) E[p] = 1 + (int32_t)(((uint32_t)E[p] * 2654435761u) % 16000u);
+}
 // hotpack from the contribution vector (NCCL exchange path: the peers' contributions arrive by allgather, not by remote stores)
 __global__ void k_hot_refresh(const int32_t* __restrict__ idslot, int32_t nh, const double* __restrict__ contrib, double* __restrict__ hot) {
     int32_t s = blockIdx.x * blockDim.x + threadIdx.x;
@@ -871,6 +879,7 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
         cfg.kmin = env_int("GMC_PR_KMIN", cfg.kmin);
         cfg.split = env_int("GMC_PR_SPLIT", cfg.split);
         cfg.cold_stream = env_int("GMC_PR_COLD_STREAM", cfg.cold_stream);
+        cfg.hot_first = env_int("GMC_PR_HOT_FIRST", cfg.hot_first);
         cfg.kcold = env_int("GMC_PR_KCOLD", cfg.kcold);
         if (cfg.kmin < 1) cfg.kmin = 1;
         // The FIRST pagerank() call on a graph may be its only one (the reference's drivers: load, one call, exit; every
@@ -899,6 +908,13 @@ int build_plan(gmc_graph* g, int world, int rank, const gmc_pr_plan* state_of, g
         rc = prp::build(be, in, cfg, L);
         if (rc != 0) { set_error("%s", L.error.empty() ? "pagerank plan: failed" : L.error.c_str()); if (rc > 0) rc = GMC_ERR_CUDA; goto fail; }
         if (cudaGetLastError() != cudaSuccess) { rc = GMC_ERR_CUDA; set_error("pagerank plan: a plan kernel failed to launch"); goto fail; }
+    }
+    if (getenv("GMC_PR_FAKE_ALLHOT")) {       // experiment (results invalid): every L2 gather of the home stream becomes a tier-0 slot
+        const Stream& stx = L.streams[0];
+        int32_t b1 = 0;
+        cudaMemcpy(&b1, L.sbeg + stx.sbeg_off + stx.n_slices, 4, cudaMemcpyDeviceToHost);
+        const int32_t e1 = stx.n_slices > 0 ? b1 : stx.e_long + stx.EL;
+        if (e1 > stx.e_long) k_fake_allhot<<<div_up(e1 - stx.e_long, 256), 256, 0, st>>>(L.E, stx.e_long, e1);
     }
     if (const char* fb = getenv("GMC_PR_FAKE_BANKS")) {     // experiment: 1 = tier streams, 2 = + the tier-0 entries of the home stream
         const int mode = atoi(fb);

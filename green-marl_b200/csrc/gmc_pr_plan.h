@@ -71,6 +71,7 @@ struct Config {
     int grid = 148;                    // CTAs of the sweep
     int row_cost = 0;                  // shard cuts: entries one row epilogue weighs (grows with the world size)
     double tier_scale = 1.25;          // multiplier on the CTAs given to the tier streams
+    int hot_first = 1;                 // MIXED mode with warm tiers: tier-0 entries first inside a home row (uniform warps)
     int cold_stream = 0;               // MIXED mode with warm tiers: the cold entries of split rows get their own stream (class T + 1)
     int kcold = 4;                     // ... when the row has at least this many of them
     int split = 0;                     // 1: SPLIT mode (tier 0 as a segment stream, home = cold entries only); see the header
@@ -257,6 +258,7 @@ struct GlobalLenF {
 };
 
 struct RowCtx {        // the shard's rows: r in [0, nl) long rows (id = jl0 + 1 + r), r >= nl short rows (id = short_id0 + r - nl)
+    int32_t hot_first;     // MIXED mode with warm tiers: a home row holds its tier-0 entries first, then its L2 entries
     int32_t n, nl, jl0, short_id0, tlo, T, thi, kmin, kcold;   // thi = T, or T + 1 = the cold class when it has a stream       // tiers tlo..T have streams (tlo = 0 in SPLIT mode, 1 otherwise)
     const int32_t *old_of_new, *r_begin, *r_node_idx, *code;
     PRP_HD int32_t id_of(int32_t r) const { return r < nl ? jl0 + 1 + r : short_id0 + (r - nl); }
@@ -309,38 +311,43 @@ PRP_HD void walk_entries(const int32_t* __restrict__ idx, const int32_t* __restr
 struct CountShortF {   // item i: short row r = nl + i
     RowCtx c;
     uint32_t* segmask;
-    int32_t *home_len, *nrec, *rec_j, *err;
+    int32_t *home_len, *home_hot, *nrec, *rec_j, *err;
     unsigned long long* rec_key;
     int32_t rec_cap;
     int32_t e_lo, e_hi;    // this pass handles the rows whose LAST edge lies in [e_lo, e_hi) (copy-in still in flight: the edges
                            // arrive in chunks); rows without edges go with e_lo == 0
     PRP_HD void operator()(int64_t i) const {
         const int32_t r = c.nl + (int32_t)i, id = c.short_id0 + (int32_t)i;
-        if (id > c.n) { if (e_lo == 0) { segmask[r] = 0; home_len[r] = 0; } return; }
+        if (id > c.n) { if (e_lo == 0) { segmask[r] = 0; home_len[r] = 0; home_hot[r] = -1; } return; }
         const int32_t v = c.old_of_new[id], rb = c.r_begin[v], len = c.r_begin[v + 1] - rb;
         if (len == 0 ? e_lo != 0 : (rb + len - 1 < e_lo || rb + len - 1 >= e_hi)) return;
-        if (c.tlo > c.T || len < (c.tlo == 0 ? 1 : c.kmin)) { segmask[r] = 0; home_len[r] = len; return; }
+        // (rows too short for a segment are not walked: they keep their source order, home_hot = -1)
+        if (c.tlo > c.T || len < (c.tlo == 0 ? 1 : c.kmin)) { segmask[r] = 0; home_len[r] = len; home_hot[r] = -1; return; }
         uint16_t cnt[MAX_TIERS + 1];
         for (int t = 0; t <= c.thi; t++) cnt[t] = 0;
         const RowCtx& cc = c;
+        int32_t hot0 = 0;
         walk_entries(c.r_node_idx, c.code, rb, rb + len, [&](int32_t, int32_t cd) {
             if (cd < 0) cnt[(-cd) / HT]++;
+            else if (cd < HT) hot0++;
             else if (cc.thi > cc.T && cd >= HT) cnt[cc.thi]++;
         });
         uint32_t mask;
         const int32_t tot = emit_segments(cnt, c.tlo, c.T, c.thi, c.kmin, c.kcold, r, &mask, nrec, rec_key, rec_j, rec_cap, err);
         segmask[r] = mask;
         home_len[r] = len - tot;
+        home_hot[r] = c.hot_first ? hot0 : -1;
     }
 };
 struct HomeLenDegF {   // no tier streams: every entry stays home, nothing needs the edges
     RowCtx c;
     int32_t nrows;
     uint32_t* segmask;
-    int32_t* home_len;
+    int32_t *home_len, *home_hot;
     PRP_HD void operator()(int64_t r) const {
         const int32_t id = c.id_of((int32_t)r);
         segmask[r] = 0;
+        home_hot[r] = -1;
         home_len[r] = id <= c.n ? c.r_begin[c.old_of_new[id] + 1] - c.r_begin[c.old_of_new[id]] : 0;
     }
 };
@@ -376,11 +383,14 @@ struct PieceCountF {   // per-tier counts of one piece -> G[t * nps + p]
         uint16_t cnt[MAX_TIERS + 1];
         for (int t = 0; t <= c.thi; t++) cnt[t] = 0;
         const RowCtx& cc = c;
+        int32_t hot0 = 0;
         walk_entries(c.r_node_idx, c.code, rb + k0, rb + k1, [&](int32_t, int32_t cd) {
             if (cd < 0) cnt[(-cd) / HT]++;
+            else if (cd < HT) hot0++;
             else if (cc.thi > cc.T && cd >= HT) cnt[cc.thi]++;
         });
         for (int t = c.tlo; t <= c.thi; t++) G[(size_t)t * nps + p] = cnt[t];
+        if (c.hot_first) G[p] = hot0;                 // column 0 is free in MIXED mode: the tier-0 entries that stay home
     }
 };
 struct LongRowF {      // G scanned (exclusive): totals of long row j -> segments
@@ -388,7 +398,7 @@ struct LongRowF {      // G scanned (exclusive): totals of long row j -> segment
     const int32_t *piece_first, *G;
     int32_t nps;
     uint32_t* segmask;
-    int32_t *home_len, *nrec, *rec_j, *err;
+    int32_t *home_len, *home_hot, *nrec, *rec_j, *err;
     unsigned long long* rec_key;
     int32_t rec_cap;
     PRP_HD void operator()(int64_t j) const {
@@ -401,6 +411,7 @@ struct LongRowF {      // G scanned (exclusive): totals of long row j -> segment
         const int32_t tot = c.tlo <= c.T ? emit_segments(cnt, c.tlo, c.T, c.thi, c.kmin, c.kcold, (int32_t)j, &mask, nrec, rec_key, rec_j, rec_cap, err) : 0;
         segmask[j] = mask;
         home_len[j] = len - tot;
+        home_hot[j] = c.hot_first ? G[p1] - G[p0] : -1;
     }
 };
 struct TierBoundF {    // item t = 0..T+1: first sorted segment of tier t and first one of it that is not long
@@ -521,7 +532,7 @@ struct SegCursor {
 struct FillCtx {
     RowCtx c;
     const uint32_t* segmask;
-    const int32_t *pslot, *seg_ebase, *seg_estride, *new_of_old, *eoff;
+    const int32_t *pslot, *seg_ebase, *seg_estride, *new_of_old, *eoff, *home_hot;
     int32_t* E;
 };
 // class of an entry with code cd: its tier (code < 0), the cold class (no slot, and the cold stream exists), or -1 = stays home
@@ -542,7 +553,14 @@ struct FillShortF {    // item i: short row r = nl + i; its home entries go to c
         int32_t h = f.eoff[c.nl + (i >> 5)] + (int32_t)(i & 31);
         if (!mask) {
             const FillCtx& f0 = f;
-            walk_entries(c.r_node_idx, c.code, rb, rb + len, [&](int32_t src, int32_t cd) { f0.E[h] = home_value(f0, cd, src); h += 32; });
+            const int32_t nh0 = f.home_hot[r];
+            if (nh0 < 0) walk_entries(c.r_node_idx, c.code, rb, rb + len, [&](int32_t src, int32_t cd) { f0.E[h] = home_value(f0, cd, src); h += 32; });
+            else {              // tier-0 entries first, then the L2 ones (each group in source order)
+                int32_t hc0 = h + 32 * nh0;
+                walk_entries(c.r_node_idx, c.code, rb, rb + len, [&](int32_t src, int32_t cd) {
+                    if (cd > 0 && cd < HT) { f0.E[h] = cd; h += 32; } else { f0.E[hc0] = home_value(f0, cd, src); hc0 += 32; }
+                });
+            }
             return;
         }
         SegCursor cur;
@@ -550,10 +568,13 @@ struct FillShortF {    // item i: short row r = nl + i; its home entries go to c
         for (int t = 0; t <= c.thi; t++)
             if (mask >> t & 1u) { const int32_t s = f.pslot[r] + j++; cur.pos[t] = f.seg_ebase[s]; cur.stride[t] = f.seg_estride[s]; }
         const FillCtx& ff = f;
+        const int32_t nh = f.home_hot[r];
+        int32_t hc = nh >= 0 ? h + 32 * nh : h;          // first slot of the L2 entries when the row is hot-first
         walk_entries(c.r_node_idx, c.code, rb, rb + len, [&](int32_t src, int32_t cd) {
             const int t = entry_class(ff.c, cd);
             if (t >= 0 && (mask >> t & 1u)) { ff.E[cur.pos[t]] = cd < 0 ? (-cd) - t * HT : cd; cur.pos[t] += cur.stride[t]; }
-            else { ff.E[h] = home_value(ff, cd, src); h += 32; }
+            else if (nh < 0 || (cd > 0 && cd < HT)) { ff.E[h] = home_value(ff, cd, src); h += 32; }
+            else { ff.E[hc] = home_value(ff, cd, src); hc += 32; }
         });
     }
 };
@@ -581,12 +602,16 @@ struct FillPieceF {    // one piece of a long row: the scanned piece table says 
                 cur.pos[t] = f.seg_ebase[s] + before * cur.stride[t];
                 moved += before;
             }
-        int32_t h = f.eoff[j] + (k0 - moved);
+        const int32_t nh = f.home_hot[j];
+        const int32_t hot_before = nh >= 0 ? G[p] - G[p0] : 0;                 // column 0: tier-0 entries of the earlier pieces
+        int32_t h = nh >= 0 ? f.eoff[j] + hot_before : f.eoff[j] + (k0 - moved);
+        int32_t hc = nh >= 0 ? f.eoff[j] + nh + (k0 - moved - hot_before) : h;
         const FillCtx& ff = f;
         walk_entries(c.r_node_idx, c.code, rb + k0, rb + k1, [&](int32_t src, int32_t cd) {
             const int t = entry_class(ff.c, cd);
             if (t >= 0 && (mask >> t & 1u)) { ff.E[cur.pos[t]] = cd < 0 ? (-cd) - t * HT : cd; cur.pos[t] += cur.stride[t]; }
-            else ff.E[h++] = home_value(ff, cd, src);
+            else if (nh < 0 || (cd > 0 && cd < HT)) ff.E[h++] = home_value(ff, cd, src);
+            else ff.E[hc++] = home_value(ff, cd, src);
         });
     }
 };
@@ -735,7 +760,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     std::vector<long long> h_tier_out(MAX_TIERS + 2, 0);
     int32_t tlo = 1, thi = 0, g_n_slices = 0, nl = 0, ns = 0, nrows = 0, short_id0 = 0, nps = 0, rec_cap = 0, nseg = 0, X = 0, herr = 0;
     uint32_t* segmask = nullptr;
-    int32_t *home_len = nullptr, *nrec = nullptr, *rec_j = nullptr, *rec_j2 = nullptr, *np = nullptr, *piece_row = nullptr, *G = nullptr;
+    int32_t *home_len = nullptr, *home_hot = nullptr, *nrec = nullptr, *rec_j = nullptr, *rec_j2 = nullptr, *np = nullptr, *piece_row = nullptr, *G = nullptr;
     unsigned long long *rec_key = nullptr, *rec_key2 = nullptr;
     int32_t *tier_q = nullptr, *tier_mid = nullptr, *nparts = nullptr, *issplit = nullptr, *elen = nullptr, *seg_ebase = nullptr, *seg_estride = nullptr, *scost = nullptr;
     int32_t *gidx = nullptr, *gout = nullptr;
@@ -823,11 +848,11 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     nrows = nl + 32 * ns;
     short_id0 = P.g_n_long + 1 + 32 * P.s0;
     if (nrows >= (1 << 27)) { P.error = "pagerank plan: more than 2^27 rows in one shard"; rc = -1; goto done; }
-    rc_ = RowCtx{n, nl, P.jl0, short_id0, tlo, P.T, thi, cfg.kmin, cfg.kcold, P.old_of_new, in.r_begin, in.r_node_idx, code};
+    rc_ = RowCtx{(!P.split && P.T >= 1 && cfg.hot_first) ? 1 : 0, n, nl, P.jl0, short_id0, tlo, P.T, thi, cfg.kmin, cfg.kcold, P.old_of_new, in.r_begin, in.r_node_idx, code};
 
     be.mark("2 shard cuts");
     // ---- 3. pass 1 over the shard's reverse edges: (row, tier) counts -> segments, home lengths
-    PRP_TRY(tmp.get(&segmask, (size_t)nrows + 1)); PRP_TRY(tmp.get(&home_len, (size_t)nrows + 32)); PRP_TRY(tmp.get(&nrec, 1));
+    PRP_TRY(tmp.get(&segmask, (size_t)nrows + 1)); PRP_TRY(tmp.get(&home_len, (size_t)nrows + 32)); PRP_TRY(tmp.get(&home_hot, (size_t)nrows + 32)); PRP_TRY(tmp.get(&nrec, 1));
     PRP_TRY(be.zero(nrec, 4)); PRP_TRY(be.zero(home_len, 4 * ((size_t)nrows + 32)));
     {
         // a row has at most one record per tier, and a record stands for >= 1 (tier 0) / >= kmin entries
@@ -844,7 +869,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     PRP_TRY(be.scan_i32(np, (size_t)nl + 1));                               // np = piece_first from here on
     be.pfor(nps, PieceRowF{np, nl, piece_row});
     if (tlo <= P.T) PRP_TRY(be.zero(G, 4 * (size_t)(thi + 1) * nps));
-    if (tlo > P.T) be.pfor(nrows, HomeLenDegF{rc_, nrows, segmask, home_len});        // no tiers: the layout follows from the degrees
+    if (tlo > P.T) be.pfor(nrows, HomeLenDegF{rc_, nrows, segmask, home_len, home_hot});        // no tiers: the layout follows from the degrees
     else {
         // the reverse edges may still be arriving over PCIe (gmc_pagerank_host_csr): count chunk by chunk behind the copies
         const int nch = be.edge_chunks();
@@ -854,14 +879,14 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
             PRP_TRY(be.edge_chunk_ready(ch, &e_hi));
             if (ch == nch - 1) e_hi = m > 0 ? m : 1;
             if (e_hi > e_lo || ch == 0) {
-                be.pfor((int64_t)32 * ns, CountShortF{rc_, segmask, home_len, nrec, rec_j, err, rec_key, rec_cap, e_lo, e_hi > e_lo ? e_hi : e_lo + 1});
+                be.pfor((int64_t)32 * ns, CountShortF{rc_, segmask, home_len, home_hot, nrec, rec_j, err, rec_key, rec_cap, e_lo, e_hi > e_lo ? e_hi : e_lo + 1});
                 if (tlo <= P.T) be.pfor(nps, PieceCountF{rc_, np, piece_row, nps, G, e_lo, e_hi});
             }
             if (e_hi > e_lo) e_lo = e_hi;
         }
     }
     if (tlo <= P.T) PRP_TRY(be.scan_i32(G, (size_t)(thi + 1) * nps));
-    if (tlo <= P.T) be.pfor(nl, LongRowF{rc_, np, G, nps, segmask, home_len, nrec, rec_j, err, rec_key, rec_cap});
+    if (tlo <= P.T) be.pfor(nl, LongRowF{rc_, np, G, nps, segmask, home_len, home_hot, nrec, rec_j, err, rec_key, rec_cap});
     PRP_TRY(be.d2h(&nseg, nrec, 4));
     PRP_TRY(be.d2h(&herr, err, 4));
     if (herr) { P.error = "pagerank plan: segment record buffer overflow"; rc = -1; goto done; }
@@ -971,7 +996,7 @@ int build(B& be, const Input& in, const Config& cfg, Plan& P) {
     PRP_TRY(be.alloc((void**)&P.E, 4 * ((size_t)P.EN + 8)));
     PRP_TRY(be.zero(P.E, 4 * ((size_t)P.EN + 8)));
     {
-        FillCtx f{rc_, segmask, nparts, seg_ebase, seg_estride, P.new_of_old, P.eoff, P.E};
+        FillCtx f{rc_, segmask, nparts, seg_ebase, seg_estride, P.new_of_old, P.eoff, home_hot, P.E};
         if (tlo > P.T) {
             // no tier streams: nothing above needed the edges, so the entries are written chunk by chunk behind their copy-in
             const int nch = be.edge_chunks();

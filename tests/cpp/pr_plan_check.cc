@@ -140,7 +140,14 @@ int main(int argc, char** argv) {
             for (int32_t j = 0; j < st.n_long; j++) {
                 const int32_t id = s == 0 ? P.jl0 + 1 + j : slot_row[P.seg_slot[st.meta_off + j]];
                 if (id < 1 || id > n) { printf("FAIL: stream %d long row %d -> id %d\n", s, j, id); bad++; continue; }
-                for (int32_t x = P.eoff[st.lbeg_off + j]; x < P.eoff[st.lbeg_off + j + 1]; x++) { const int32_t w = decode(s, P.E[x]); if (w) got[id].push_back(w); }
+                bool seen_cold = false;       // MIXED mode with warm tiers: a home row holds its tier-0 entries first (hot_first)
+                for (int32_t x = P.eoff[st.lbeg_off + j]; x < P.eoff[st.lbeg_off + j + 1]; x++) {
+                    const int32_t w = decode(s, P.E[x]); if (w) got[id].push_back(w);
+                    if (s == 0 && !P.split && P.T >= 1 && P.E[x]) {
+                        if (P.E[x] >= HT) seen_cold = true;
+                        else if (seen_cold) { printf("FAIL: home long row %d: a tier-0 entry after an L2 entry\n", j); bad++; break; }
+                    }
+                }
             }
             for (int32_t q = 0; q < st.n_slices; q++) {
                 const int32_t b0 = P.sbeg[st.sbeg_off + q], L = (P.sbeg[st.sbeg_off + q + 1] - b0) >> 5;
