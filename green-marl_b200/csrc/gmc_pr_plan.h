@@ -71,7 +71,7 @@ struct Config {
     int grid = 148;                    // CTAs of the sweep
     int row_cost = 0;                  // shard cuts: entries one row epilogue weighs (grows with the world size)
     double tier_scale = 1.25;          // multiplier on the CTAs given to the tier streams
-    int hot_first = 1;                 // MIXED mode with warm tiers: tier-0 entries first inside a home row (uniform warps)
+    int hot_first = 0;                 // experiment (measured 1.7 % slower): tier-0 entries first inside a home row of a tiered plan
     int cold_stream = 0;               // MIXED mode with warm tiers: the cold entries of split rows get their own stream (class T + 1)
     int kcold = 4;                     // ... when the row has at least this many of them
     int split = 0;                     // 1: SPLIT mode (tier 0 as a segment stream, home = cold entries only); see the header
