@@ -153,6 +153,13 @@ def run_multi(args, n, m, workload):
     exchange_path = g.pagerank_exchange_path()
     parity = None
     single = None
+    traffic_tw = None          # dram bytes of one sweep of this graph on one GPU, from the committed ncu capture
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("tw_1gpu", {})
+        if tj.get("nodes") == n and tj.get("edges") == m:
+            traffic_tw = tj.get("dram_bytes_per_launch")
+    except Exception:
+        pass
     if rank == 0:
         t0 = time.perf_counter()
         one_dev = torch.empty(n, dtype=torch.float64, device="cuda")
@@ -186,6 +193,7 @@ def run_multi(args, n, m, workload):
         single = {"what": "same graph on one GPU of this job: the anchor of the strong-scaling curve", "pagerank_gteps": round(m * iters / one_ms / 1e6, 2),
                   "ms_per_step": round(one_ms, 3), "avg_sweep_ms": round(float(np.mean(one_sweeps)), 4),
                   "roofline_frac": round(a1 / float(np.mean(one_sweeps)) / 1e6 / peak, 4), "alg_bytes_per_launch": int(a1),
+                  "traffic": traffic_tw,
                   "bfs_gteps": round(sum(one_bfs_edges) / sum(one_bfs_ms) / 1e6, 2), "bfs_ms_per_traversal": round(float(np.mean(one_bfs_ms)), 4),
                   "first_call_s": round(plan_s, 2)}
         del one_dev

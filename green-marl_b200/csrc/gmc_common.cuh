@@ -84,6 +84,7 @@ struct gmc_graph {
     int32_t* e_rev2idx = nullptr;   // [M] optional
     int32_t* e_idx2idx = nullptr;   // [M] optional
     bool semi_sorted = false;
+    bool tc_rows_checked = false;   // triangle_counting has verified that the rows of both CSRs are ascending
     bool has_reverse = false;
     bool has_forward = true;        // false: node_idx was not copied in (pull-only graph: PageRank needs begin + the reverse CSR)
     // copy-in still in flight (gmc_pagerank_host_csr): begin/r_begin are complete once `small` has fired, r_node_idx[0, end[k])

@@ -15,6 +15,7 @@ void gmc_pr_plan_free(gmc_graph* g);   // gmc_pagerank.cu
 void gmc_bfs_ws_free(gmc_graph* g);    // gmc_bfs.cu
 
 void gmc_graph_invalidate_plans(gmc_graph* g) {
+    g->tc_rows_checked = false;
     gmc_pr_plan_free(g);
     gmc_bfs_ws_free(g);
 }

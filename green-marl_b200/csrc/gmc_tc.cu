@@ -163,6 +163,13 @@ __global__ void __launch_bounds__(TC_THREADS) tc_heavy(const int32_t* __restrict
 
 }  // namespace
 
+__global__ void k_rows_ascending(const int32_t* __restrict__ begin, const int32_t* __restrict__ idx, int32_t n, int32_t* __restrict__ bad) {
+    const int32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= n) return;
+    for (int32_t e = begin[v] + 1; e < begin[v + 1]; e++)
+        if (idx[e] < idx[e - 1]) { *bad = 1; return; }
+}
+
 extern "C" {
 
 // edge slots [e_lo, e_hi) of the forward CSR: the count is a plain sum over slots, so a multi-GPU job gives every rank a
@@ -178,6 +185,21 @@ int gmc_triangle_counting_range(gmc_graph* g, int64_t e_lo, int64_t e_hi, int64_
     if (kernel_ms) *kernel_ms = 0.f;
     if (e_hi == e_lo) return GMC_OK;
     cudaStream_t st = as_stream(stream);
+    // the intersections assume ascending rows in both CSRs; a graph filled through prepare_external_creation need not have them.
+    // Checked once per graph (one pass over the edges), not assumed: unsorted rows would silently give a wrong count.
+    if (!g->tc_rows_checked) {
+        int32_t* bad = nullptr;
+        GMC_TRY(gmc_malloc((void**)&bad, 4));
+        cudaMemsetAsync(bad, 0, 4, st);
+        k_rows_ascending<<<div_up(g->N, 256), 256, 0, st>>>(g->begin, g->node_idx, g->N, bad);
+        k_rows_ascending<<<div_up(g->N, 256), 256, 0, st>>>(g->r_begin, g->r_node_idx, g->N, bad);
+        int32_t hbad = 0;
+        cudaMemcpyAsync(&hbad, bad, 4, cudaMemcpyDeviceToHost, st);
+        cudaStreamSynchronize(st);
+        cudaFree(bad);
+        GMC_REQUIRE(!hbad, GMC_ERR_STATE, "triangle_counting: rows are not ascending (semi-sort the graph and rebuild the reverse CSR first)");
+        g->tc_rows_checked = true;
+    }
     const int32_t n = g->N, m = g->M;
     const int32_t n_hints = div_up(m, TC_TILE) + 1;
     int32_t* hints = nullptr;

@@ -92,3 +92,19 @@ def test_triangle_counting_needs_reverse(gm, oracle):
     dg = gm.graph_from_csr(g["begin"], g["node_idx"], semi_sort=False, make_reverse=False)
     with pytest.raises(Exception):
         dg.triangle_counting()
+
+
+@pytest.mark.gpu
+def test_triangle_counting_rejects_unsorted_rows(gm, oracle):
+    """a CSR filled through prepare_external_creation need not have ascending rows: the count would be silently wrong, so the
+    device entry point checks the rows once per graph and fails instead"""
+    from gmb200_loader import load_package
+    b, i = oracle.rmat(5000, 80000, 7, 0.57, 0.19, 0.19, True)          # generator output: rows NOT sorted
+    g = graphs.prepared(oracle, b, i)                                      # the sorted graph, for its reverse CSR
+    dg = gm.graph_from_csr(b, i, semi_sort=False, make_reverse=False)
+    dg.upload_reverse(g["r_begin"], g["r_node_idx"])
+    with pytest.raises(load_package().GmcError):
+        dg.triangle_counting()
+    dg.semi_sort()
+    got = dg.triangle_counting()
+    assert (got[0] if isinstance(got, tuple) else got) == oracle.triangle_counting(g["begin"], g["node_idx"])
