@@ -1,4 +1,4 @@
-// PageRank pull sweep (K1) with the updater (K2) and init (K3) fused away -- two launches per iteration (sweep + combine).
+// PageRank pull sweep (K1) with the updater (K2) and init (K3) fused away -- one cooperative launch per iteration.
 //
 // Reference loop being replaced (generated from apps/src/pagerank.gm:8-19, shape in SURVEY.md 3.1):
 //   foreach t: S = sum_{w in InNbrs(t), r_node_idx order} rank[w] / (double)outdeg(w)
@@ -20,9 +20,10 @@
 //               to arrive (atomic counter) adds them in task order.
 //   short task  sliced ELL, one lane per row, terms added strictly left to right in the original source order.
 // A finished row either runs its epilogue (rows without segments: bit-identical to the CPU order when short) or stores its
-// partial sum into the row's part slot; pr_combine adds the parts of every split row in slot order, runs their epilogues,
-// reduces the diff partials in a fixed order and advances the device-side loop control.  Nothing in the result depends on
-// which CTA ran what.
+// partial sum into the row's part slot; behind a grid barrier at the end of the launch the parts of every split row are added
+// in slot order and their epilogues run, the diff partials are reduced in a fixed order and the device-side loop control
+// advances (combine_rows; GMC_PR_TWO_KERNELS=1 runs it as a second kernel instead).  Nothing in the result depends on which
+// CTA ran what.  Measurements, the variants tried and why the sweep stops at 0.35 of HBM peak: DESIGN.md 4.1.
 #include "gmc_common.cuh"
 #include "gmc_comm.h"
 #include "gmc_pr_plan.h"

@@ -21,16 +21,19 @@
 //               ~1.25 sector operations, so it must replace at least ~2 cold gathers; tier 0: KMIN = 1).  Entry value = slot
 //               inside the tier.  Segments sorted by length: the long ones row-major in tasks, the others sliced ELL -- the
 //               same two task classes again.  No gather of a tier stream leaves the SM.
-//   two modes   SPLIT (graphs with warm tiers, T >= 1): home holds cold entries only, so a home task runs on ANY CTA
+//   two modes   SPLIT (Config::split, off by default): tier 0 is a segment stream too, home holds cold entries only, so a home task runs on ANY CTA
 //               whatever tier it has staged, and every SM keeps both of its gather paths busy at once: some warps on its
-//               tier's stream (shared memory), the others on home tasks (L2 sectors).  MIXED (small graphs, T = 0): tier-0
-//               entries stay inside the home rows (entry value = slot < HT), every CTA stages tier 0, no row is split and
-//               every short row is added in exactly the reference's order (bit-identical to the CPU result).
+//               tier's stream (shared memory), the others on home tasks (L2 sectors).  MIXED (default): tier-0 entries stay
+//               inside the home rows (entry value = slot < HT); home tasks run on CTAs that have tier 0 staged, the tier
+//               CTAs run their warm tiers first and join them.  With T = 0 (small graphs, short first calls) no row is split
+//               and every short row is added in exactly the reference's order (bit-identical to the CPU result).
 //   parts       a row with segments ("split row") owns 1 + nseg consecutive part slots: slot 0 for the home part, then one
 //               per segment in tier order.  Tasks store partial sums there; the combine kernel adds them in slot order and
 //               runs the row epilogue: deterministic whatever the CTA schedule, no atomics or fences in the sweep.
 // On the LJ-shaped R-MAT (tools/model_segments.py): T = 16, KMIN = 3 turns 24.5 M of the 39.8 M cold gathers into shared-memory
-// gathers at the price of 1.9 M part slots.
+// gathers at the price of 1.9 M part slots.  Measured: MIXED mode with T = 12, KMIN = 6 is the fastest and the
+// default (0.159 ms per sweep against 0.189 ms for T = 0); SPLIT mode, the cold stream (class T + 1) and hot_first are kept as
+// switches of Config -- each was built, checked here on the CPU and on the GPU, and measured slower.
 #pragma once
 #include <stdint.h>
 #include <stdlib.h>
