@@ -10,6 +10,9 @@ void hop_dist(gm_graph& G, int32_t* G_dist, node_t& root) {
 
     if (gmc_group* grp = G.group_mirror()) {      // GM_CUDA_DEVICES > 1: vertex-range shards over the device group
         shl__start_timer(10);
+        shl__print_array_conf("shl__G_begin", (size_t)G.num_nodes() + 1, sizeof(edge_t), 1, 1, 0);
+        shl__print_array_conf("shl__G_node_idx", (size_t)G.num_edges(), sizeof(node_t), 1, 1, 0);
+        shl__print_array_conf("shl__G_dist", (size_t)G.num_nodes(), sizeof(int32_t), 1, 0, 1);
         shl__end_timer("SHOAL_Copyin");
         gmc_bfs_info ginfo;
         shl__start();

@@ -19,6 +19,11 @@ void pagerank(gm_graph& G, double e, double d, int32_t max, double* G_pg_rank) {
         // its own PCIe link + NVLink allgather; the loop nest = sharded sweeps with the exchange fused into the epilogue;
         // copy-back = every device writes its slice of rank[] into G_pg_rank
         shl__start_timer(10);
+        // the arrays the generated procedure hands to Shoal (gm_cpp_gen.cc:685-775) and where they live in the group
+        shl__print_array_conf("shl__G_begin", (size_t)G.num_nodes() + 1, sizeof(edge_t), 1, 1, 0);
+        shl__print_array_conf("shl__G_r_begin", (size_t)G.num_nodes() + 1, sizeof(edge_t), 1, 1, 0);
+        shl__print_array_conf("shl__G_r_node_idx", (size_t)G.num_edges(), sizeof(node_t), 1, 1, 0);
+        shl__print_array_conf("shl__G_pg_rank", (size_t)G.num_nodes(), sizeof(double), 1, 0, 1);
         shl__end_timer("SHOAL_Copyin");
         gmc_pagerank_info ginfo;
         shl__start();

@@ -34,8 +34,21 @@ int shl__init(int nthreads, int partitioned) {
     g_device = dev;
     // Placement switch of the reference (shl__init(nthreads, partitioned); run.sh -p / -r) re-targeted: GM_CUDA_DEVICES=N
     // runs the generated procedures over N B200s of this box -- CSR replicated, rows partitioned (csrc/gmc_group.cu)
+    // The reference's own switches (scripts/run.sh:70-97,248-251 exports them; scripts/generate_settings.py:53-60 writes them
+    // into the Shoal settings): -r SHL_REPLICATION (replicate read-only arrays over the NUMA nodes), -p SHL_PARTITION (partition
+    // indexed arrays), -d SHL_DISTRIBUTION, -h SHL_HUGEPAGE.  Replication / partitioning over NUMA nodes = the device group over
+    // the GPUs of the box (CSR replicated, rows partitioned): either switch selects every visible device (1, 2, 4 or 8) unless
+    // GM_CUDA_DEVICES says otherwise; distribution and huge pages have no HBM equivalent and are reported as ignored.
+    const int s_rep = getenv("SHL_REPLICATION") ? atoi(getenv("SHL_REPLICATION")) : 0, s_part = getenv("SHL_PARTITION") ? atoi(getenv("SHL_PARTITION")) : 0;
+    const int s_dist = getenv("SHL_DISTRIBUTION") ? atoi(getenv("SHL_DISTRIBUTION")) : 0, s_huge = getenv("SHL_HUGEPAGE") ? atoi(getenv("SHL_HUGEPAGE")) : 0;
     int ndev = 1;
     if (const char* nd = getenv("GM_CUDA_DEVICES")) ndev = atoi(nd);
+    else if (s_rep || s_part) {       // (the second argument of shl__init is the SHL_STATIC build flag, common_main.h:95-99: not a placement switch)
+        int have = 1;
+        if (gmc_device_count(&have) == GMC_OK) for (ndev = 1; ndev * 2 <= have && ndev * 2 <= 8; ndev *= 2) {}
+    }
+    printf("SHOAL settings: replication=%d partition=%d distribution=%d hugepage=%d -> devices=%d%s\n", s_rep, s_part, s_dist, s_huge, ndev,
+           (s_dist || s_huge) ? " (distribution / hugepage: no HBM equivalent, ignored)" : "");
     if (ndev > 1 && !g_group) {
         if (gmc_group_create(&g_group, ndev, NULL) != GMC_OK) {
             fprintf(stderr, "shl__init: GM_CUDA_DEVICES=%d: %s\n", ndev, gmc_last_error());
@@ -69,6 +82,13 @@ double shl__end_timer(const char* label) { return shl__step_timer(label); }
 int shl__get_rep_id(void) { return g_device < 0 ? 0 : g_device; }
 struct gmc_group* shl__device_group(void) { return g_group; }
 void* shl__alloc_memory(size_t bytes) { return malloc(bytes); }
+
+// "Array[<name>]: elements= size= -- hugepage=[ ] -- used=[X] replication=[X] ..." : the array configuration line Shoal prints per
+// array and scripts/extract_result.py:171-190 (ArrayConfChecker) parses
+void shl__print_array_conf(const char* name, size_t elements, size_t elem_bytes, int used, int replicated, int partitioned) {
+    printf("Array[%20s]: elements=%10zu size=%12zu -- hugepage=[ ] -- used=[%c] replication=[%c] partition=[%c] hbm=[X]\n", name, elements,
+           elements * elem_bytes, used ? 'X' : ' ', replicated ? 'X' : ' ', partitioned ? 'X' : ' ');
+}
 
 // CRC-16/CCITT-FALSE (poly 0x1021, init 0xFFFF).  The polynomial libshoal's print_crc uses cannot be
 // recovered from the reference tree; only the "CRC <name> 0x%04x" line format is (extract_result.py:162).

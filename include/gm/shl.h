@@ -28,6 +28,7 @@ void* shl__alloc_memory(size_t bytes);
 // The reference chooses NUMA placement at the same point (common_main.h:95-99, scripts/run.sh -r / -p).
 struct gmc_group;
 struct gmc_group* shl__device_group(void);
+void shl__print_array_conf(const char* name, size_t elements, size_t elem_bytes, int used, int replicated, int partitioned);
 #ifdef __cplusplus
 }
 class Timer {

@@ -52,8 +52,7 @@ class shl_array {
 
   protected:
     void print_options() {
-        printf("Array[%20s]: elements=%10zu size=%12zu -- hugepage=[ ] -- used=[%c] replication=[ ] partition=[ ] hbm=[X]\n",
-               name, size, size * sizeof(T), is_used ? 'X' : ' ');
+        shl__print_array_conf(name, size, sizeof(T), is_used ? 1 : 0, 0, 0);
     }
     void die(const char* what) {
         fprintf(stderr, "shl_array[%s]::%s failed: %s\n", name, what, gmc_last_error());

@@ -85,3 +85,26 @@ def test_reference_drivers_on_a_device_group(gm, oracle, tmp_path, ndev):
     got = [int(x) for x in re.findall(r"dist\[\d\] = (-?\d+)", out)]
     assert got == [int(v) for v in dist[:10]]
     assert f"devices={ndev}" in out
+
+
+def test_shoal_placement_switches(gm, oracle, tmp_path):
+    """scripts/run.sh -r / -p export SHL_REPLICATION / SHL_PARTITION: shl__init maps them to the device group over every visible GPU
+    (one GPU: a no-op), prints the settings line and the Array[...] configuration lines scripts/extract_result.py parses"""
+    f = str(tmp_path / "c1.bin")
+    run("graph_gen", 65536, 1048576, f, 0)
+    have = gm.device_count()
+    ndev = 1
+    while ndev * 2 <= have and ndev * 2 <= 8:
+        ndev *= 2
+    out = run("pagerank", f, 4, "/dev/null", 20, 1e-30, 0.85, env={"SHL_REPLICATION": "1", "SHL_PARTITION": "1", "SHL_HUGEPAGE": "1"})
+    assert f"SHOAL settings: replication=1 partition=1 distribution=0 hugepage=1 -> devices={ndev}" in out
+    assert re.search(r"^Array\[\s*shl__G_pg_rank\]: elements=\s*65536 size=\s*524288 ", out, re.M)
+    b, i = oracle.uniform_random(65536, 1048576, 1997)
+    i = np.ascontiguousarray(i).copy()
+    oracle.semi_sort(b, i)
+    rb, ri = oracle.make_reverse(b, i)
+    rank, _, _ = oracle.pagerank(b, rb, ri, 1e-30, 0.85, 20)
+    got = [float(x) for x in re.findall(r"rank\[\d\] = ([0-9.]+)", out)]
+    assert got == [float("%0.9f" % v) for v in rank[:4]]
+    if ndev > 1:
+        assert "replication=[X]" in out and "partition=[X]" in out
