@@ -294,9 +294,17 @@ bu_scan(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_
     bool found = false;
     if (t < n && !((vis >> lane) & 1u)) {
         const int32_t b = r_begin[t], e = r_begin[t + 1];
-        for (int32_t nx = b; nx < e; nx++) {
-            const int32_t u = r_node_idx[nx];
-            if ((frontier_bm[u >> 5] >> (u & 31)) & 1u) { found = true; break; }
+        // four parents per step: their ids, then their frontier words, are independent loads (the one-at-a-time loop was a
+        // chain of two dependent loads per parent); any hit ends the scan as before
+        for (int32_t nx = b; nx < e && !found; nx += 4) {
+            int32_t u[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) u[k] = nx + k < e ? r_node_idx[nx + k] : -1;
+            uint32_t fw[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) fw[k] = u[k] >= 0 ? frontier_bm[u[k] >> 5] : 0u;
+#pragma unroll
+            for (int k = 0; k < 4; k++) found = found || (u[k] >= 0 && ((fw[k] >> (u[k] & 31)) & 1u));
         }
     }
     const uint32_t got = __ballot_sync(FULLMASK, found);
