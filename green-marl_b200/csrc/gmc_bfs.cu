@@ -119,10 +119,10 @@ __global__ void bfs_ctl_init(BfsCtl* ctl, float thr, int has_reverse, int rrd_di
 }
 
 // ---- top-down, step 1: degrees of the queued vertices -> CTA-relative offsets + chunk descriptors ----------
-__global__ void __launch_bounds__(BFS_THREADS)
-td_prepare(const int32_t* __restrict__ begin, const int32_t* __restrict__ queue, int32_t qcount, int32_t* __restrict__ blk_off,
+__device__ __forceinline__ void
+td_prepare_body(const int32_t* __restrict__ begin, const int32_t* __restrict__ queue, int32_t qcount, int32_t* __restrict__ blk_off,
            int32_t* __restrict__ blk_total, int2* __restrict__ chunks, int32_t* __restrict__ nchunks,
-           const int32_t* __restrict__ queue_alt = nullptr, const BfsCtl* __restrict__ ctl = nullptr) {
+           const int32_t* __restrict__ queue_alt, const BfsCtl* __restrict__ ctl) {
     __shared__ int32_t s_warp[BFS_THREADS / 32];
     __shared__ int32_t s_c0;
     if (ctl) {     // device-driven traversal: a top-down level? then the owned frontier is queue[qi], own_count long
@@ -183,12 +183,12 @@ __device__ __forceinline__ void mark_candidate(uint32_t* __restrict__ cand, cons
 
 // ---- top-down, step 2: one warp per chunk of TD_CHUNK edge slots ---------------------------------------------
 template <bool BATCHED>
-__global__ void __launch_bounds__(BFS_THREADS)
-td_expand(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_idx, const int32_t* __restrict__ queue, int32_t qcount,
+__device__ __forceinline__ void
+td_expand_body(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_idx, const int32_t* __restrict__ queue, int32_t qcount,
           const int32_t* __restrict__ blk_off, const int32_t* __restrict__ blk_total, const int2* __restrict__ chunks,
           const int32_t* __restrict__ nchunks_p, const uint32_t* __restrict__ visited, uint32_t* __restrict__ cand,
-          const uint8_t* __restrict__ edge_mask, const int32_t* __restrict__ queue_alt = nullptr, const BfsCtl* __restrict__ ctl = nullptr,
-          const PeerCand pc = PeerCand()) {
+          const uint8_t* __restrict__ edge_mask, const int32_t* __restrict__ queue_alt, const BfsCtl* __restrict__ ctl,
+          const PeerCand& pc) {
     const int lane = threadIdx.x & 31;
     if (ctl) {     // device-driven traversal: both forms are enqueued, the one that fits the frontier runs
         if (ctl->done || ctl_bottom_up(ctl->state)) return;
@@ -281,10 +281,10 @@ td_expand(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_id
 }
 
 // ---- bottom-up: warp w owns vertices [32w, 32w+32) = one word of the bitmaps ------------------------------------
-__global__ void __launch_bounds__(BFS_THREADS)
-bu_scan(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t w_lo, int32_t w_hi,
+__device__ __forceinline__ void
+bu_scan_body(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t w_lo, int32_t w_hi,
         const uint32_t* __restrict__ frontier_bm, const uint32_t* __restrict__ visited, uint32_t* __restrict__ cand,
-        const BfsCtl* __restrict__ ctl = nullptr) {
+        const BfsCtl* __restrict__ ctl) {
     const int lane = threadIdx.x & 31;
     if (ctl && (ctl->done || !ctl_bottom_up(ctl->state))) return;
     const int32_t wstep = (gridDim.x * BFS_THREADS) >> 5;
@@ -310,6 +310,50 @@ bu_scan(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_
     const uint32_t got = __ballot_sync(FULLMASK, found);
     if (lane == 0) cand[w] = got;
     }
+}
+
+// ---- the kernels: one per body for the host-driven loop, and two MERGED ones for the device-driven loop, where a level is
+// three launches whatever its direction (bfs_level_a: bottom-up scan OR top-down prepare; td_expand_any: either form of the
+// expansion, nothing in a bottom-up level; bfs_finish)
+__global__ void __launch_bounds__(BFS_THREADS)
+td_prepare(const int32_t* __restrict__ begin, const int32_t* __restrict__ queue, int32_t qcount, int32_t* __restrict__ blk_off,
+           int32_t* __restrict__ blk_total, int2* __restrict__ chunks, int32_t* __restrict__ nchunks) {
+    td_prepare_body(begin, queue, qcount, blk_off, blk_total, chunks, nchunks, nullptr, nullptr);
+}
+template <bool BATCHED>
+__global__ void __launch_bounds__(BFS_THREADS)
+td_expand(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_idx, const int32_t* __restrict__ queue, int32_t qcount,
+          const int32_t* __restrict__ blk_off, const int32_t* __restrict__ blk_total, const int2* __restrict__ chunks,
+          const int32_t* __restrict__ nchunks_p, const uint32_t* __restrict__ visited, uint32_t* __restrict__ cand,
+          const uint8_t* __restrict__ edge_mask, const PeerCand pc) {
+    td_expand_body<BATCHED>(begin, node_idx, queue, qcount, blk_off, blk_total, chunks, nchunks_p, visited, cand, edge_mask, nullptr, nullptr, pc);
+}
+__global__ void __launch_bounds__(BFS_THREADS)
+bu_scan(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t w_lo, int32_t w_hi,
+        const uint32_t* __restrict__ frontier_bm, const uint32_t* __restrict__ visited, uint32_t* __restrict__ cand) {
+    bu_scan_body(r_begin, r_node_idx, n, w_lo, w_hi, frontier_bm, visited, cand, nullptr);
+}
+__global__ void __launch_bounds__(BFS_THREADS)
+bfs_level_a(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t w_lo, int32_t w_hi,
+            const uint32_t* __restrict__ frontier_bm, const uint32_t* __restrict__ visited, uint32_t* __restrict__ cand,
+            const int32_t* __restrict__ begin, const int32_t* __restrict__ queue0, const int32_t* __restrict__ queue1,
+            int32_t* __restrict__ blk_off, int32_t* __restrict__ blk_total, int2* __restrict__ chunks, int32_t* __restrict__ nchunks,
+            const BfsCtl* __restrict__ ctl) {
+    if (ctl->done) return;
+    if (ctl_bottom_up(ctl->state)) { if (r_begin) bu_scan_body(r_begin, r_node_idx, n, w_lo, w_hi, frontier_bm, visited, cand, ctl); }
+    else td_prepare_body(begin, queue0, 0, blk_off, blk_total, chunks, nchunks, queue1, ctl);
+}
+__global__ void __launch_bounds__(BFS_THREADS)
+td_expand_any(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_idx, const int32_t* __restrict__ queue0,
+              const int32_t* __restrict__ queue1, const int32_t* __restrict__ blk_off, const int32_t* __restrict__ blk_total,
+              const int2* __restrict__ chunks, const int32_t* __restrict__ nchunks_p, const uint32_t* __restrict__ visited,
+              uint32_t* __restrict__ cand, const uint8_t* __restrict__ edge_mask, const BfsCtl* __restrict__ ctl) {
+    if (ctl->done || ctl_bottom_up(ctl->state)) return;
+    const PeerCand pc = PeerCand();
+    if (ctl->own_count <= TD_BATCHED_MAX_FRONTIER)
+        td_expand_body<true>(begin, node_idx, queue0, 0, blk_off, blk_total, chunks, nchunks_p, visited, cand, edge_mask, queue1, ctl, pc);
+    else
+        td_expand_body<false>(begin, node_idx, queue0, 0, blk_off, blk_total, chunks, nchunks_p, visited, cand, edge_mask, queue1, ctl, pc);
 }
 
 // ---- end of level: new = candidates & ~visited -> visited, frontier, level[], owned queue, count ------------------
@@ -537,15 +581,13 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
         bool done = false;
         for (int guard = 0; !done && guard < BFS_TRACE_CAP + 8; guard += batch, batch = 2) {
             for (int b = 0; b < batch; b++) {
-                if (has_reverse) { bu_scan<<<scan_grid, BFS_THREADS, 0, st>>>(rev_begin, rev_idx, n, own_lo, own_hi, w->frontier_bm, w->visited, w->cand, ctl); launches++; }
-                td_prepare<<<prep_grid, BFS_THREADS, 0, st>>>(fwd_begin, w->queue[0], 0, w->blk_off, w->blk_total, w->chunks, w->counters + 2, w->queue[1], ctl);
-                td_expand<true><<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[0], 0, w->blk_off, w->blk_total, w->chunks,
-                                                                  w->counters + 2, w->visited, w->cand, edge_mask, w->queue[1], ctl);
-                td_expand<false><<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[0], 0, w->blk_off, w->blk_total, w->chunks,
-                                                                   w->counters + 2, w->visited, w->cand, edge_mask, w->queue[1], ctl);
+                bfs_level_a<<<scan_grid, BFS_THREADS, 0, st>>>(has_reverse ? rev_begin : nullptr, rev_idx, n, own_lo, own_hi, w->frontier_bm, w->visited, w->cand,
+                                                               fwd_begin, w->queue[0], w->queue[1], w->blk_off, w->blk_total, w->chunks, w->counters + 2, ctl);
+                td_expand_any<<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[0], w->queue[1], w->blk_off, w->blk_total, w->chunks,
+                                                                w->counters + 2, w->visited, w->cand, edge_mask, ctl);
                 bfs_finish<L><<<fin_grid, BFS_THREADS, 0, st>>>(w->words, w->wp, 1, 0, w->cand, w->allcand, w->visited, w->frontier_bm, (L)0, level,
                                                                 own_lo, own_hi, w->queue[0], w->counters, w->h_counters, ++w->seq, w->queue[1], ctl);
-                launches += 4;
+                launches += 3;
             }
             GMC_CUDA(cudaGetLastError());
             volatile int32_t* h = w->h_counters;
@@ -607,10 +649,10 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
                                                                                   w->blk_total, w->chunks, w->counters + 2);
                 if (own_count <= TD_BATCHED_MAX_FRONTIER)
                     td_expand<true><<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[qi], own_count, w->blk_off, w->blk_total,
-                                                                      w->chunks, w->counters + 2, w->visited, cand_l, edge_mask, nullptr, nullptr, pc);
+                                                                      w->chunks, w->counters + 2, w->visited, cand_l, edge_mask, pc);
                 else
                     td_expand<false><<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[qi], own_count, w->blk_off, w->blk_total,
-                                                                       w->chunks, w->counters + 2, w->visited, cand_l, edge_mask, nullptr, nullptr, pc);
+                                                                       w->chunks, w->counters + 2, w->visited, cand_l, edge_mask, pc);
                 launches += 2;
             }
             if (peer) {
