@@ -172,12 +172,14 @@ struct PeerCand {
     uint32_t* base[8];
     int32_t wpr, world, rank;
 };
-__device__ __forceinline__ void mark_candidate(uint32_t* __restrict__ cand, const PeerCand& pc, int32_t uw, uint32_t bit) {
+// pc == nullptr: no owner-directed exchange.  (pc points at a __grid_constant__ kernel parameter: indexing a by-value copy of the
+// struct made every thread of the grid spill it to its stack -- 24 MB of local stores per launch, +8 us on every level)
+__device__ __forceinline__ void mark_candidate(uint32_t* __restrict__ cand, const PeerCand* __restrict__ pc, int32_t uw, uint32_t bit) {
     if (cand[uw] & bit) return;
     atomicOr(&cand[uw], bit);
-    if (pc.world > 1) {
-        const int o = uw / pc.wpr;
-        if (o != pc.rank) atomicOr_system(pc.base[o] + uw, bit);       // performed at the owner's L2, system scope
+    if (pc && pc->world > 1) {
+        const int o = uw / pc->wpr;
+        if (o != pc->rank) atomicOr_system(pc->base[o] + uw, bit);       // performed at the owner's L2, system scope
     }
 }
 
@@ -188,7 +190,7 @@ td_expand_body(const int32_t* __restrict__ begin, const int32_t* __restrict__ no
           const int32_t* __restrict__ blk_off, const int32_t* __restrict__ blk_total, const int2* __restrict__ chunks,
           const int32_t* __restrict__ nchunks_p, const uint32_t* __restrict__ visited, uint32_t* __restrict__ cand,
           const uint8_t* __restrict__ edge_mask, const int32_t* __restrict__ queue_alt, const BfsCtl* __restrict__ ctl,
-          const PeerCand& pc) {
+          const PeerCand* __restrict__ pc) {
     const int lane = threadIdx.x & 31;
     if (ctl) {     // device-driven traversal: both forms are enqueued, the one that fits the frontier runs
         if (ctl->done || ctl_bottom_up(ctl->state)) return;
@@ -325,8 +327,9 @@ __global__ void __launch_bounds__(BFS_THREADS)
 td_expand(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_idx, const int32_t* __restrict__ queue, int32_t qcount,
           const int32_t* __restrict__ blk_off, const int32_t* __restrict__ blk_total, const int2* __restrict__ chunks,
           const int32_t* __restrict__ nchunks_p, const uint32_t* __restrict__ visited, uint32_t* __restrict__ cand,
-          const uint8_t* __restrict__ edge_mask, const PeerCand pc) {
-    td_expand_body<BATCHED>(begin, node_idx, queue, qcount, blk_off, blk_total, chunks, nchunks_p, visited, cand, edge_mask, nullptr, nullptr, pc);
+          const uint8_t* __restrict__ edge_mask, const __grid_constant__ PeerCand pc) {
+    td_expand_body<BATCHED>(begin, node_idx, queue, qcount, blk_off, blk_total, chunks, nchunks_p, visited, cand, edge_mask, nullptr, nullptr,
+                            pc.world > 1 ? &pc : nullptr);
 }
 __global__ void __launch_bounds__(BFS_THREADS)
 bu_scan(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t w_lo, int32_t w_hi,
@@ -349,11 +352,10 @@ td_expand_any(const int32_t* __restrict__ begin, const int32_t* __restrict__ nod
               const int2* __restrict__ chunks, const int32_t* __restrict__ nchunks_p, const uint32_t* __restrict__ visited,
               uint32_t* __restrict__ cand, const uint8_t* __restrict__ edge_mask, const BfsCtl* __restrict__ ctl) {
     if (ctl->done || ctl_bottom_up(ctl->state)) return;
-    const PeerCand pc = PeerCand();
     if (ctl->own_count <= TD_BATCHED_MAX_FRONTIER)
-        td_expand_body<true>(begin, node_idx, queue0, 0, blk_off, blk_total, chunks, nchunks_p, visited, cand, edge_mask, queue1, ctl, pc);
+        td_expand_body<true>(begin, node_idx, queue0, 0, blk_off, blk_total, chunks, nchunks_p, visited, cand, edge_mask, queue1, ctl, nullptr);
     else
-        td_expand_body<false>(begin, node_idx, queue0, 0, blk_off, blk_total, chunks, nchunks_p, visited, cand, edge_mask, queue1, ctl, pc);
+        td_expand_body<false>(begin, node_idx, queue0, 0, blk_off, blk_total, chunks, nchunks_p, visited, cand, edge_mask, queue1, ctl, nullptr);
 }
 
 // ---- end of level: new = candidates & ~visited -> visited, frontier, level[], owned queue, count ------------------
@@ -647,8 +649,8 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             if (own_count > 0) {
                 td_prepare<<<div_up(own_count, BFS_THREADS), BFS_THREADS, 0, st>>>(fwd_begin, w->queue[qi], own_count, w->blk_off,
                                                                                   w->blk_total, w->chunks, w->counters + 2);
-                if (own_count <= TD_BATCHED_MAX_FRONTIER)
-                    td_expand<true><<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[qi], own_count, w->blk_off, w->blk_total,
+                if (own_count <= TD_BATCHED_MAX_FRONTIER)      // (small frontiers: one block per SM is plenty of warps for their chunks)
+                    td_expand<true><<<own_count <= 1024 ? (unsigned)sm_count() : exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[qi], own_count, w->blk_off, w->blk_total,
                                                                       w->chunks, w->counters + 2, w->visited, cand_l, edge_mask, pc);
                 else
                     td_expand<false><<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[qi], own_count, w->blk_off, w->blk_total,
