@@ -49,7 +49,28 @@ struct BfsCtl {
     int32_t has_reverse, rrd_direct, pad;
     int32_t trace_state[BFS_TRACE_CAP], trace_count[BFS_TRACE_CAP];
 };
-__device__ __forceinline__ bool ctl_bottom_up(int st) { return st == ST_RRD || st == ST_RR2Q; }
+__host__ __device__ __forceinline__ bool ctl_bottom_up(int st) { return st == ST_RRD || st == ST_RR2Q; }
+
+// get_next_state (gm_bfs_template.h:352-421): the state of the next level from the size of the frontier it found
+// (next_count > 0).  One definition for the host loop and the device-side control blocks.
+__host__ __device__ __forceinline__ int bfs_next_state(int state, int32_t next_count, int32_t curr_count, float thr, bool has_reverse,
+                                                       bool rrd_direct) {
+    switch (state) {
+        case ST_SMALL: return next_count >= 128 ? ST_QUE : ST_SMALL;
+        case ST_QUE:
+            if ((float)next_count >= thr) return rrd_direct ? ST_RRD : ST_RD;
+            if (next_count >= 1024 && next_count >= curr_count * 5) return ST_Q2R;
+            return ST_QUE;
+        case ST_Q2R: return (rrd_direct && (float)next_count >= thr) ? ST_RRD : ST_RD;
+        case ST_RD:
+            if (has_reverse && (float)next_count >= thr) return ST_RRD;
+            return next_count <= 2 * curr_count ? ST_R2Q : ST_RD;
+        case ST_R2Q: return ST_QUE;
+        case ST_RRD: return next_count <= 2 * curr_count ? ST_RR2Q : ST_RRD;
+        case ST_RR2Q: return ST_QUE;
+    }
+    return state;
+}
 
 struct gmc_bfs_ws {
     BfsCtl* ctl = nullptr;            // device
@@ -73,7 +94,8 @@ struct gmc_bfs_ws {
     int2* chunks = nullptr;           // [M/TD_CHUNK + N/256 + 2] (queue block, chunk-in-block)
     size_t chunk_cap = 0;
     int32_t* counters = nullptr;      // [8]: 0 = level count (global), 1 = owned queue count, 2 = nchunks
-    int32_t* h_counters = nullptr;    // pinned + mapped [8]: 0 = level count, 1 = owned count, 2 = sequence number of the level that wrote them
+    int32_t* h_counters = nullptr;    // pinned + mapped [BFS_HOST_WORDS]: 0 = level count, 1 = owned count, 2 = sequence number of the level that wrote
+                                      // them; bfs_small_levels: 0 = levels done, 1 = traversal ended, 2 = sequence number, 4.. = count found by each level
     int32_t seq = 0;
     void* level = nullptr;            // [N] int32 (also used as int16)
     unsigned long long* edge_sum = nullptr;
@@ -120,9 +142,8 @@ __global__ void bfs_ctl_init(BfsCtl* ctl, float thr, int has_reverse, int rrd_di
 
 // ---- top-down, step 1: degrees of the queued vertices -> CTA-relative offsets + chunk descriptors ----------
 __device__ __forceinline__ void
-td_prepare_body(const int32_t* __restrict__ begin, const int32_t* __restrict__ queue, int32_t qcount, int32_t* __restrict__ blk_off,
-           int32_t* __restrict__ blk_total, int2* __restrict__ chunks, int32_t* __restrict__ nchunks,
-           const int32_t* __restrict__ queue_alt, const BfsCtl* __restrict__ ctl) {
+td_prepare_body(const int32_t* __restrict__ begin, const int32_t* queue, int32_t qcount, int32_t* blk_off,
+           int32_t* blk_total, int2* chunks, int32_t* nchunks, const int32_t* queue_alt, const BfsCtl* ctl) {
     __shared__ int32_t s_warp[BFS_THREADS / 32];
     __shared__ int32_t s_c0;
     if (ctl) {     // device-driven traversal: a top-down level? then the owned frontier is queue[qi], own_count long
@@ -174,7 +195,7 @@ struct PeerCand {
 };
 // pc == nullptr: no owner-directed exchange.  (pc points at a __grid_constant__ kernel parameter: indexing a by-value copy of the
 // struct made every thread of the grid spill it to its stack -- 24 MB of local stores per launch, +8 us on every level)
-__device__ __forceinline__ void mark_candidate(uint32_t* __restrict__ cand, const PeerCand* __restrict__ pc, int32_t uw, uint32_t bit) {
+__device__ __forceinline__ void mark_candidate(uint32_t* cand, const PeerCand* __restrict__ pc, int32_t uw, uint32_t bit) {
     if (cand[uw] & bit) return;
     atomicOr(&cand[uw], bit);
     if (pc && pc->world > 1) {
@@ -186,10 +207,9 @@ __device__ __forceinline__ void mark_candidate(uint32_t* __restrict__ cand, cons
 // ---- top-down, step 2: one warp per chunk of TD_CHUNK edge slots ---------------------------------------------
 template <bool BATCHED>
 __device__ __forceinline__ void
-td_expand_body(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_idx, const int32_t* __restrict__ queue, int32_t qcount,
-          const int32_t* __restrict__ blk_off, const int32_t* __restrict__ blk_total, const int2* __restrict__ chunks,
-          const int32_t* __restrict__ nchunks_p, const uint32_t* __restrict__ visited, uint32_t* __restrict__ cand,
-          const uint8_t* __restrict__ edge_mask, const int32_t* __restrict__ queue_alt, const BfsCtl* __restrict__ ctl,
+td_expand_body(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_idx, const int32_t* queue, int32_t qcount,
+          const int32_t* blk_off, const int32_t* blk_total, const int2* chunks, const int32_t* nchunks_p, const uint32_t* visited,
+          uint32_t* cand, const uint8_t* __restrict__ edge_mask, const int32_t* queue_alt, const BfsCtl* ctl,
           const PeerCand* __restrict__ pc) {
     const int lane = threadIdx.x & 31;
     if (ctl) {     // device-driven traversal: both forms are enqueued, the one that fits the frontier runs
@@ -285,8 +305,7 @@ td_expand_body(const int32_t* __restrict__ begin, const int32_t* __restrict__ no
 // ---- bottom-up: warp w owns vertices [32w, 32w+32) = one word of the bitmaps ------------------------------------
 __device__ __forceinline__ void
 bu_scan_body(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t w_lo, int32_t w_hi,
-        const uint32_t* __restrict__ frontier_bm, const uint32_t* __restrict__ visited, uint32_t* __restrict__ cand,
-        const BfsCtl* __restrict__ ctl) {
+        const uint32_t* frontier_bm, const uint32_t* visited, uint32_t* cand, const BfsCtl* ctl) {
     const int lane = threadIdx.x & 31;
     if (ctl && (ctl->done || !ctl_bottom_up(ctl->state))) return;
     const int32_t wstep = (gridDim.x * BFS_THREADS) >> 5;
@@ -359,22 +378,13 @@ td_expand_any(const int32_t* __restrict__ begin, const int32_t* __restrict__ nod
 }
 
 // ---- end of level: new = candidates & ~visited -> visited, frontier, level[], owned queue, count ------------------
+// One warp, 32 consecutive bitmap words (lane = word w).
 template <typename L>
-__global__ void __launch_bounds__(BFS_THREADS)
-bfs_finish(int32_t words, int32_t wp, int world, int use_all, uint32_t* __restrict__ cand, const uint32_t* __restrict__ allcand,
-           uint32_t* __restrict__ visited, uint32_t* __restrict__ frontier, L next_level, L* __restrict__ level,
-           int32_t own_lo, int32_t own_hi, int32_t* __restrict__ next_queue, int32_t* __restrict__ counters,
-           volatile int32_t* __restrict__ host_out, int32_t seq, int32_t* __restrict__ queue_alt = nullptr, BfsCtl* ctl = nullptr) {
+__device__ __forceinline__ void
+finish_warp(int32_t w, int32_t words, int32_t wp, int world, int use_all, uint32_t* cand, const uint32_t* allcand, uint32_t* visited,
+            uint32_t* frontier, L next_level, L* __restrict__ level, int32_t own_lo, int32_t own_hi, int32_t* next_queue,
+            int32_t* counters) {
     const int lane = threadIdx.x & 31;
-    if (ctl) {     // device-driven traversal: level number and queue come from the control block
-        if (ctl->done) {      // the traversal ended earlier in this batch of launches: only tell the host
-            if (blockIdx.x == 0 && threadIdx.x == 0) { host_out[1] = 1; __threadfence_system(); host_out[2] = seq; }
-            return;
-        }
-        next_level = (L)(ctl->curr_level + 1);
-        if (!ctl->qi) next_queue = queue_alt;       // next = queue[qi ^ 1]; next_queue = queue[0], queue_alt = queue[1]
-    }
-    const int32_t w = blockIdx.x * BFS_THREADS + threadIdx.x;
     uint32_t nw = 0;
     if (w < words) {
         uint32_t c;
@@ -417,6 +427,44 @@ bfs_finish(int32_t words, int32_t wp, int world, int use_all, uint32_t* __restri
             if (own_s) next_queue[qb + __popc(bits & ((1u << lane) - 1u))] = v;
         }
     }
+}
+
+// get_next_state (gm_bfs_template.h:352-421) on the device, same arithmetic as the host loop of run_bfs: one thread, after
+// every count of the level has landed.  Returns `done`.
+__device__ __forceinline__ int ctl_advance(BfsCtl* ctl, int32_t next_count, int32_t own) {
+    const int done_in = next_count == 0;
+    const int next_state = done_in ? ctl->state
+                                   : bfs_next_state(ctl->state, next_count, ctl->curr_count, ctl->thr, ctl->has_reverse != 0, ctl->rrd_direct != 0);
+    int done = done_in;
+    if (!done) {
+        const int32_t k = ctl->n_trace;
+        if (k >= BFS_TRACE_CAP) { ctl->overflow = 1; done = 1; }
+        else {
+            ctl->trace_state[k] = next_state; ctl->trace_count[k] = next_count; ctl->n_trace = k + 1;
+            ctl->state = next_state; ctl->curr_count = next_count; ctl->own_count = own;
+            ctl->curr_level = ctl->curr_level + 1; ctl->qi = ctl->qi ^ 1;
+        }
+    }
+    ctl->done = done;
+    return done;
+}
+
+template <typename L>
+__global__ void __launch_bounds__(BFS_THREADS)
+bfs_finish(int32_t words, int32_t wp, int world, int use_all, uint32_t* __restrict__ cand, const uint32_t* __restrict__ allcand,
+           uint32_t* __restrict__ visited, uint32_t* __restrict__ frontier, L next_level, L* __restrict__ level,
+           int32_t own_lo, int32_t own_hi, int32_t* __restrict__ next_queue, int32_t* __restrict__ counters,
+           volatile int32_t* __restrict__ host_out, int32_t seq, int32_t* __restrict__ queue_alt = nullptr, BfsCtl* ctl = nullptr) {
+    if (ctl) {     // device-driven traversal: level number and queue come from the control block
+        if (ctl->done) {      // the traversal ended earlier in this batch of launches: only tell the host
+            if (blockIdx.x == 0 && threadIdx.x == 0) { host_out[1] = 1; __threadfence_system(); host_out[2] = seq; }
+            return;
+        }
+        next_level = (L)(ctl->curr_level + 1);
+        if (!ctl->qi) next_queue = queue_alt;       // next = queue[qi ^ 1]; next_queue = queue[0], queue_alt = queue[1]
+    }
+    finish_warp<L>(blockIdx.x * BFS_THREADS + threadIdx.x, words, wp, world, use_all, cand, allcand, visited, frontier, next_level, level,
+                   own_lo, own_hi, next_queue, counters);
     // the last block to finish publishes the two level counts straight into the host's (mapped, pinned) memory and
     // resets the device counters: the host polls the sequence number instead of a memcpy + memset + stream sync per level
     __shared__ int s_last;
@@ -432,43 +480,217 @@ bfs_finish(int32_t words, int32_t wp, int world, int use_all, uint32_t* __restri
         counters[0] = 0; counters[1] = 0; counters[2] = 0; counters[3] = 0;
         if (!ctl) { host_out[0] = next_count; host_out[1] = own; }
         else {
-            // get_next_state (gm_bfs_template.h:352-421), same arithmetic as the host loop of run_bfs
-            const int state = ctl->state;
-            const int32_t curr_count = ctl->curr_count;
-            const float thr = ctl->thr;
-            const bool has_reverse = ctl->has_reverse != 0, rrd_direct = ctl->rrd_direct != 0;
-            int next_state = state, done = next_count == 0;
-            switch (state) {
-                case ST_SMALL: if (next_count >= 128) next_state = ST_QUE; break;
-                case ST_QUE:
-                    if ((float)next_count >= thr) next_state = rrd_direct ? ST_RRD : ST_RD;
-                    else if (next_count >= 1024 && next_count >= curr_count * 5) next_state = ST_Q2R;
-                    break;
-                case ST_Q2R: next_state = (rrd_direct && (float)next_count >= thr) ? ST_RRD : ST_RD; break;
-                case ST_RD:
-                    if (has_reverse && (float)next_count >= thr) next_state = ST_RRD;
-                    else if (next_count <= 2 * curr_count) next_state = ST_R2Q;
-                    break;
-                case ST_R2Q: next_state = ST_QUE; break;
-                case ST_RRD: if (next_count <= 2 * curr_count) next_state = ST_RR2Q; break;
-                case ST_RR2Q: next_state = ST_QUE; break;
-            }
-            if (!done) {
-                const int32_t k = ctl->n_trace;
-                if (k >= BFS_TRACE_CAP) { ctl->overflow = 1; done = 1; }
-                else {
-                    ctl->trace_state[k] = next_state; ctl->trace_count[k] = next_count; ctl->n_trace = k + 1;
-                    ctl->state = next_state; ctl->curr_count = next_count; ctl->own_count = own;
-                    ctl->curr_level = ctl->curr_level + 1; ctl->qi = ctl->qi ^ 1;
-                }
-            }
-            ctl->done = done;
+            const int done = ctl_advance(ctl, next_count, own);
             __threadfence();
             host_out[0] = next_count; host_out[1] = done;
         }
         __threadfence_system();
         host_out[2] = seq;
     }
+}
+
+// ---- runs of SMALL top-down levels (single GPU): one CTA, no grid-wide step at all ----------------------------------------------
+// A level whose frontier has at most SMALL_Q vertices and SMALL_E out-edges is a latency chain, not a bandwidth problem: as
+// prepare / expand / finish launches it costs ~35 us of launch, drain and bitmap passes for a few thousand edges.  Here one CTA of
+// 1024 threads does the whole level between two __syncthreads: frontier degrees -> offsets in shared memory -> one edge slot per
+// thread and step (row by binary search in shared memory) -> atomicOr straight into `visited`; the thread that sets the bit owns the
+// discovery, writes level[u] and appends u to the next queue.  It keeps going, level after level (the reference's state machine
+// evaluated in place), until the frontier needs the grid (more vertices / edges than the limits), the next level is bottom-up, or
+// the traversal ends; the per-level counts go to the host's pinned block, which replays the state machine over them.
+// The candidate and frontier bitmaps are not used by these levels; the frontier bitmap is rebuilt from the queue when the level
+// that follows is bottom-up (only graphs of at most 20 x SMALL_E vertices can get there from a small level: RRD_THRESHOLD is N/20).
+constexpr int SMALL_THREADS = 1024, SMALL_Q = 4096, SMALL_E = 32768, SMALL_LEVELS = 56, SMALL_HDR = 4;
+constexpr int BFS_HOST_WORDS = SMALL_HDR + SMALL_LEVELS + 4;
+
+template <typename L>
+__global__ void __launch_bounds__(SMALL_THREADS, 1)
+bfs_small_levels(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_idx, const uint8_t* __restrict__ edge_mask,
+                 int32_t* queue0, int32_t* queue1, uint32_t* visited, uint32_t* frontier, int32_t words, L* level, int state,
+                 int32_t curr_level, int32_t curr_count, int32_t qi, float thr, int has_reverse, int rrd_direct, int max_levels,
+                 volatile int32_t* host_out, int32_t seq) {
+    __shared__ int32_t s_off[SMALL_Q + 1];
+    __shared__ int32_t s_beg[SMALL_Q];
+    __shared__ int32_t s_warp[SMALL_THREADS / 32];
+    __shared__ int32_t s_next;
+    constexpr int PER = SMALL_Q / SMALL_THREADS;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    int n_done = 0, ended = 0;
+    int32_t own = curr_count;
+    for (;;) {
+        const int32_t* q = qi ? queue1 : queue0;
+        int32_t* qn = qi ? queue0 : queue1;
+        // degrees of the frontier: thread t takes the PER consecutive entries t*PER ...
+        int32_t d[PER], b[PER], mine = 0;
+#pragma unroll
+        for (int k = 0; k < PER; k++) {
+            const int32_t i = tid * PER + k;
+            d[k] = 0; b[k] = 0;
+            if (i < own) { const int32_t v = q[i]; b[k] = begin[v]; d[k] = begin[v + 1] - b[k]; }
+            mine += d[k];
+        }
+        int32_t inc = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int32_t t = __shfl_up_sync(FULLMASK, inc, o); if (lane >= o) inc += t; }
+        if (lane == 31) s_warp[wid] = inc;
+        if (tid == 0) s_next = 0;
+        __syncthreads();
+        int32_t woff = 0, total = 0;
+#pragma unroll
+        for (int k = 0; k < SMALL_THREADS / 32; k++) { const int32_t t = s_warp[k]; if (k < wid) woff += t; total += t; }
+        if (total > SMALL_E) break;                 // (uniform) this level needs the grid
+        int32_t run = inc - mine + woff;
+#pragma unroll
+        for (int k = 0; k < PER; k++) {
+            const int32_t i = tid * PER + k;
+            if (i < own) { s_off[i] = run; s_beg[i] = b[k]; }
+            run += d[k];
+        }
+        if (tid == 0) s_off[own] = total;
+        __syncthreads();
+        const L nl = (L)(curr_level + 1);
+        // four edge slots of a thread per step: rows first (shared memory only), then the four neighbour ids, then the four probes
+        for (int32_t s0 = tid; s0 < total; s0 += 4 * SMALL_THREADS) {
+            int32_t eidx[4], u[4];
+            uint32_t vis[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int32_t sl = s0 + j * SMALL_THREADS;
+                eidx[j] = -1;
+                if (sl < total) {
+                    int32_t lo = 0, hi = own;            // last row with s_off[row] <= sl
+                    while (hi - lo > 1) { const int32_t mid = (lo + hi) >> 1; if (s_off[mid] <= sl) lo = mid; else hi = mid; }
+                    eidx[j] = s_beg[lo] + (sl - s_off[lo]);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) u[j] = eidx[j] >= 0 ? ld_stream(node_idx + eidx[j]) : -1;
+#pragma unroll
+            for (int j = 0; j < 4; j++) vis[j] = u[j] >= 0 ? visited[u[j] >> 5] : 0xffffffffu;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                if (u[j] < 0) continue;
+                const uint32_t bit = 1u << (u[j] & 31);
+                // navigator (check_navigator, gm_bfs_template.h:488-492,596-598): filtered edges are not followed
+                if ((vis[j] & bit) || (edge_mask && !edge_mask[eidx[j]])) continue;
+                const uint32_t old = atomicOr(&visited[u[j] >> 5], bit);
+                if (!(old & bit)) { level[u[j]] = nl; qn[atomicAdd(&s_next, 1)] = u[j]; }
+            }
+        }
+        __syncthreads();
+        const int32_t next_count = s_next;
+        if (tid == 0) host_out[SMALL_HDR + n_done] = next_count;
+        n_done++;
+        if (next_count == 0) { ended = 1; break; }
+        state = bfs_next_state(state, next_count, curr_count, thr, has_reverse != 0, rrd_direct != 0);
+        curr_count = next_count; own = next_count; curr_level++; qi ^= 1;
+        if (ctl_bottom_up(state)) {        // the scan of the next level probes the frontier bitmap: make it from the queue
+            for (int32_t w = tid; w < words; w += SMALL_THREADS) frontier[w] = 0u;
+            __syncthreads();
+            for (int32_t i = tid; i < own; i += SMALL_THREADS) { const int32_t v = qn[i]; atomicOr(&frontier[v >> 5], 1u << (v & 31)); }
+            break;
+        }
+        if (own > SMALL_Q || n_done >= max_levels) break;
+        __syncthreads();
+    }
+    __syncthreads();
+    if (tid == 0) {
+        host_out[0] = n_done; host_out[1] = ended;
+        __threadfence_system();
+        host_out[2] = seq;
+    }
+}
+
+// ---- one launch per traversal (single GPU): the levels are separated by grid barriers instead of launches ------------------------
+// counters[4] = arrivals of the current barrier, [5] = barrier generation, [6] = error (a barrier timed out).
+struct BfsPersist {
+    const int32_t *fwd_begin, *fwd_idx, *rev_begin, *rev_idx;
+    const uint8_t* edge_mask;
+    int32_t n, words;
+    uint32_t *visited, *frontier, *cand;
+    int32_t *queue0, *queue1, *blk_off, *blk_total;
+    int2* chunks;
+    int32_t* counters;
+    void* level;
+    BfsCtl* ctl;
+};
+constexpr unsigned BFS_BAR_SPINS = 1u << 26;       // x >= 40 ns: a barrier nobody completes fails the call after a few seconds instead of hanging
+
+// Every CTA arrives; the LAST one runs `last` (the level's bookkeeping) before it opens the barrier.  False: timed out / failed.
+template <typename F>
+__device__ __forceinline__ bool bfs_grid_sync(int32_t* counters, F&& last) {
+    __shared__ int s_ok;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        volatile int32_t* gen = counters + 5;
+        const int32_t g = *gen;
+        int ok = 1;
+        __threadfence();
+        if (atomicAdd(counters + 4, 1) == (int)gridDim.x - 1) {
+            __threadfence();
+            last();
+            counters[4] = 0;
+            __threadfence();
+            atomicAdd(counters + 5, 1);
+        } else {
+            unsigned spins = 0;
+            while (*gen == g) {
+                if (++spins > 256u) __nanosleep(40);
+                if (spins > BFS_BAR_SPINS || *(volatile int32_t*)(counters + 6)) { counters[6] = 1; ok = 0; break; }
+            }
+        }
+        __threadfence();
+        s_ok = ok;
+    }
+    __syncthreads();
+    return s_ok != 0;
+}
+
+template <typename L>
+__global__ void __launch_bounds__(BFS_THREADS, 6)
+bfs_persistent(const __grid_constant__ BfsPersist A) {
+    volatile BfsCtl* vc = A.ctl;
+    const int32_t nwarps = (gridDim.x * BFS_THREADS) >> 5, gwarp = (blockIdx.x * BFS_THREADS + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    auto nothing = [] {};
+    for (;;) {
+        // the control block was written by the last arrival of the previous barrier, before it opened
+        if (vc->done) break;
+        const int state = vc->state;
+        const int32_t own = vc->own_count, qi = vc->qi;
+        const L next_level = (L)(vc->curr_level + 1);
+        int32_t* const q = qi ? A.queue1 : A.queue0;
+        int32_t* const qn = qi ? A.queue0 : A.queue1;
+        if (ctl_bottom_up(state)) {
+            bu_scan_body(A.rev_begin, A.rev_idx, A.n, 0, A.words, A.frontier, A.visited, A.cand, nullptr);
+        } else {
+            td_prepare_body(A.fwd_begin, q, own, A.blk_off, A.blk_total, A.chunks, A.counters + 2, nullptr, nullptr);
+            if (!bfs_grid_sync(A.counters, nothing)) return;
+            if (own <= TD_BATCHED_MAX_FRONTIER)
+                td_expand_body<true>(A.fwd_begin, A.fwd_idx, q, own, A.blk_off, A.blk_total, A.chunks, A.counters + 2, A.visited, A.cand,
+                                     A.edge_mask, nullptr, nullptr, nullptr);
+            else
+                td_expand_body<false>(A.fwd_begin, A.fwd_idx, q, own, A.blk_off, A.blk_total, A.chunks, A.counters + 2, A.visited, A.cand,
+                                      A.edge_mask, nullptr, nullptr, nullptr);
+        }
+        if (!bfs_grid_sync(A.counters, nothing)) return;
+        for (int32_t w0 = gwarp * 32; w0 < A.words; w0 += nwarps * 32)
+            finish_warp<L>(w0 + lane, A.words, A.words, 1, 0, A.cand, nullptr, A.visited, A.frontier, next_level, (L*)A.level, 0, A.words, qn,
+                           A.counters);
+        int32_t* const counters = A.counters;
+        BfsCtl* const ctl = A.ctl;
+        if (!bfs_grid_sync(A.counters, [counters, ctl] {
+                const int32_t next_count = atomicAdd(&counters[0], 0), own_next = atomicAdd(&counters[1], 0);
+                counters[0] = 0; counters[1] = 0; counters[2] = 0;
+                ctl_advance(ctl, next_count, own_next);
+            })) return;
+    }
+}
+
+__global__ void bfs_persist_init(BfsCtl* ctl, float thr, int has_reverse, int rrd_direct, int32_t* counters) {
+    ctl->state = ST_SMALL; ctl->curr_level = 0; ctl->curr_count = 1; ctl->own_count = 1; ctl->qi = 0; ctl->done = 0;
+    ctl->n_trace = 1; ctl->overflow = 0; ctl->thr = thr; ctl->has_reverse = has_reverse; ctl->rrd_direct = rrd_direct;
+    ctl->trace_state[0] = ST_SMALL; ctl->trace_count[0] = 1;
+    counters[4] = 0; counters[5] = 0; counters[6] = 0;
 }
 
 template <typename L>
@@ -507,11 +729,26 @@ int ensure_ws(gmc_graph* g, int world) {
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->level, sizeof(int32_t) * nn);
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->edge_sum, sizeof(unsigned long long));
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->ctl, sizeof(BfsCtl));
-    if (rc == GMC_OK && cudaMallocHost((void**)&w->h_counters, sizeof(int32_t) * 8) != cudaSuccess) {
+    if (rc == GMC_OK && cudaMallocHost((void**)&w->h_counters, sizeof(int32_t) * BFS_HOST_WORDS) != cudaSuccess) {
         set_error("bfs: cudaMallocHost failed"); rc = GMC_ERR_NOMEM;
     }
-    if (rc == GMC_OK) memset(w->h_counters, 0, sizeof(int32_t) * 8);
+    if (rc == GMC_OK) memset(w->h_counters, 0, sizeof(int32_t) * BFS_HOST_WORDS);
     if (rc != GMC_OK) { gmc_bfs_ws_free(g); return rc; }
+    return GMC_OK;
+}
+
+// Wait until the kernel enqueued last has published its sequence number into the pinned block.
+int wait_host_seq(gmc_bfs_ws* w, cudaStream_t st) {
+    volatile int32_t* h = w->h_counters;
+    unsigned spins = 0;
+    while (h[2] != w->seq) {
+        if ((++spins & 0x3fffu) == 0) {            // a failed launch or a fault would never publish: ask the stream now and then
+            const cudaError_t q = cudaStreamQuery(st);
+            if (q != cudaErrorNotReady && q != cudaSuccess) { set_error("bfs: %s", cudaGetErrorString(q)); return GMC_ERR_CUDA; }
+            if (q == cudaSuccess && h[2] != w->seq) { set_error("bfs: level counts were not published"); return GMC_ERR_CUDA; }
+        }
+    }
+    __sync_synchronize();
     return GMC_OK;
 }
 
@@ -572,6 +809,59 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     // level, two or three of them leaving at once (~3 us each), and the levels enqueued past the end of the traversal cost more
     // than the host round trip they replace.  So the host-driven loop stays the default; GMC_BFS_DEVICE_LOOP=1 selects this one.
     bool device_driven = world == 1 && getenv("GMC_BFS_DEVICE_LOOP") != nullptr && getenv("GMC_BFS_HOST_LOOP") == nullptr;
+    // GMC_BFS_PERSISTENT=1: ONE cooperative launch per traversal (bfs_persistent), the levels separated by grid barriers instead of
+    // launches.  Measured SLOWER than the host-driven loop (gpurun r3g, LJ-shaped: 0.361 against 0.336 ms from root 3, 0.568 against
+    // 0.447 ms from the hub; 58 against 37 us for a one-level traversal): a software grid barrier (~3-4 us with the bookkeeping of the
+    // last arrival) is no cheaper than a kernel boundary on this part, and the static word striding of the bottom-up scan balances
+    // worse than 19 K CTAs handed out by the hardware.  Opt-in.
+    bool persistent = world == 1 && !device_driven && getenv("GMC_BFS_PERSISTENT") != nullptr && getenv("GMC_BFS_HOST_LOOP") == nullptr;
+    static thread_local int blocks_per_sm[2] = {0, 0};
+    if (persistent) {
+        int& bps = blocks_per_sm[sizeof(L) == 2];
+        if (!bps) {
+            int coop = 0, dev = 0;
+            GMC_CUDA(cudaGetDevice(&dev));
+            GMC_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+            int nb = 0;
+            if (coop) GMC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, bfs_persistent<L>, BFS_THREADS, 0));
+            bps = nb > 0 ? nb : -1;
+        }
+        if (bps < 0) persistent = false;
+    }
+    if (persistent) {
+        BfsCtl* ctl = w->ctl;
+        bfs_persist_init<<<1, 1, 0, st>>>(ctl, thr, has_reverse ? 1 : 0, rrd_direct ? 1 : 0, w->counters);
+        BfsPersist A;
+        A.fwd_begin = fwd_begin; A.fwd_idx = fwd_idx; A.rev_begin = rev_begin; A.rev_idx = rev_idx; A.edge_mask = edge_mask;
+        A.n = n; A.words = w->words; A.visited = w->visited; A.frontier = w->frontier_bm; A.cand = w->cand;
+        A.queue0 = w->queue[0]; A.queue1 = w->queue[1]; A.blk_off = w->blk_off; A.blk_total = w->blk_total; A.chunks = w->chunks;
+        A.counters = w->counters; A.level = level; A.ctl = ctl;
+        void* kargs[] = {&A};
+        const unsigned grid = (unsigned)(sm_count() * blocks_per_sm[sizeof(L) == 2]);
+        GMC_CUDA(cudaLaunchCooperativeKernel((const void*)bfs_persistent<L>, dim3(grid), dim3(BFS_THREADS), kargs, 0, st));
+        launches += 2;
+        GMC_CUDA(cudaEventRecord(ev1, st));
+        static thread_local BfsCtl hc;
+        static thread_local int32_t hcnt[8];
+        GMC_CUDA(cudaMemcpyAsync(&hc, ctl, sizeof(BfsCtl), cudaMemcpyDeviceToHost, st));
+        GMC_CUDA(cudaMemcpyAsync(hcnt, w->counters, sizeof(hcnt), cudaMemcpyDeviceToHost, st));
+        GMC_CUDA(cudaStreamSynchronize(st));
+        GMC_REQUIRE(hcnt[6] == 0 && hc.done, GMC_ERR_CUDA, "bfs: a grid barrier of the traversal kernel timed out");
+        if (hc.overflow) {       // more levels than the trace holds: the host-driven loop below starts over
+            persistent = false;
+            GMC_CUDA(cudaEventRecord(ev0, st));
+            bfs_init<L><<<div_up(max(n, w->wp), 256), 256, 0, st>>>(level, n, invalid, root, w->visited, w->frontier_bm, w->cand, w->wp,
+                                                                      w->queue[0], root_owned ? 1 : 0, w->counters);
+            launches++;
+        } else {
+            for (int k = 0; k < hc.n_trace; k++) {
+                w->state_trace.push_back(hc.trace_state[k]); w->level_count.push_back(hc.trace_count[k]);
+                if (hc.trace_state[k] == ST_RRD || hc.trace_state[k] == ST_RR2Q) bottom_up++;
+            }
+            curr_level = hc.n_trace - 1;
+            GMC_REQUIRE(sizeof(L) == 4 || curr_level + 1 <= 32767, GMC_ERR_STATE, "bfs: more levels than level_t can hold");
+        }
+    }
     if (device_driven) {
         // Single GPU: the kernels of several levels are enqueued back to back, the state machine runs on the device
         // (BfsCtl); the host only looks at the `done` word the last bfs_finish of a batch publishes.
@@ -624,7 +914,34 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             launches++; bottom_up = 0;
         }
     }
-    for (; !device_driven;) {
+    // runs of small top-down levels go to bfs_small_levels (one CTA, several levels per launch); GMC_BFS_NO_SMALL=1: never
+    const bool small_ok = world == 1 && getenv("GMC_BFS_NO_SMALL") == nullptr;
+    int32_t small_refused = -1;       // level whose frontier had more than SMALL_E edges: it takes the grid path
+    for (; !device_driven && !persistent;) {
+        if (small_ok && !ctl_bottom_up(state) && own_count > 0 && own_count <= SMALL_Q && small_refused != curr_level) {
+            int max_levels = SMALL_LEVELS;
+            if (sizeof(L) == 2) max_levels = min(max_levels, 32767 - curr_level);
+            GMC_REQUIRE(max_levels > 0, GMC_ERR_STATE, "bfs: more levels than level_t can hold");
+            bfs_small_levels<L><<<1, SMALL_THREADS, 0, st>>>(fwd_begin, fwd_idx, edge_mask, w->queue[0], w->queue[1], w->visited, w->frontier_bm,
+                                                             w->words, level, state, curr_level, curr_count, qi, thr, has_reverse ? 1 : 0,
+                                                             rrd_direct ? 1 : 0, max_levels, w->h_counters, ++w->seq);
+            launches++;
+            GMC_CUDA(cudaGetLastError());
+            GMC_TRY(wait_host_seq(w, st));
+            const int k = w->h_counters[0];
+            if (k == 0) small_refused = curr_level;
+            bool ended = false;
+            for (int j = 0; j < k && !ended; j++) {      // replay the state machine over the counts of the levels it ran
+                w->state_trace.push_back(state);
+                w->level_count.push_back(curr_count);
+                const int32_t next_count = w->h_counters[SMALL_HDR + j];
+                if (next_count == 0) { ended = true; break; }
+                state = bfs_next_state(state, next_count, curr_count, thr, has_reverse, rrd_direct);
+                curr_count = next_count; own_count = next_count; curr_level++; qi ^= 1;
+            }
+            if (ended) break;
+            continue;
+        }
         w->state_trace.push_back(state);
         w->level_count.push_back(curr_count);
         GMC_REQUIRE(sizeof(L) == 4 || curr_level + 1 <= 32767, GMC_ERR_STATE, "bfs: more levels than level_t can hold");
@@ -671,45 +988,19 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
                                                         nl, level, own_lo, own_hi, w->queue[qi ^ 1], w->counters, w->h_counters, ++w->seq);
         launches++;
         GMC_CUDA(cudaGetLastError());
-        {   // wait for the level's counts: poll the sequence number bfs_finish's last block writes into pinned memory
-            volatile int32_t* h = w->h_counters;
-            unsigned spins = 0;
-            while (h[2] != w->seq) {
-                if ((++spins & 0x3fffu) == 0) {            // a failed launch or a fault would never publish: ask the stream now and then
-                    const cudaError_t q = cudaStreamQuery(st);
-                    if (q != cudaErrorNotReady && q != cudaSuccess) { set_error("bfs: %s", cudaGetErrorString(q)); return GMC_ERR_CUDA; }
-                    if (q == cudaSuccess && h[2] != w->seq) { set_error("bfs: level counts were not published"); return GMC_ERR_CUDA; }
-                }
-            }
-            __sync_synchronize();
-        }
+        GMC_TRY(wait_host_seq(w, st));    // the level's counts: the sequence number bfs_finish's last block writes into pinned memory
         const int32_t next_count = w->h_counters[0];
         own_count = w->h_counters[1];
         qi ^= 1;
 
         // get_next_state (gm_bfs_template.h:352-421)
         if (next_count == 0) break;
-        int next_state = state;
-        switch (state) {
-            case ST_SMALL: if (next_count >= 128) next_state = ST_QUE; break;
-            case ST_QUE:
-                if ((float)next_count >= thr) next_state = rrd_direct ? ST_RRD : ST_RD;
-                else if (next_count >= 1024 && next_count >= curr_count * 5) next_state = ST_Q2R;
-                break;
-            case ST_Q2R: next_state = (rrd_direct && (float)next_count >= thr) ? ST_RRD : ST_RD; break;
-            case ST_RD:
-                if (has_reverse && (float)next_count >= thr) next_state = ST_RRD;
-                else if (next_count <= 2 * curr_count) next_state = ST_R2Q;
-                break;
-            case ST_R2Q: next_state = ST_QUE; break;
-            case ST_RRD: if (next_count <= 2 * curr_count) next_state = ST_RR2Q; break;
-            case ST_RR2Q: next_state = ST_QUE; break;
-        }
+        const int next_state = bfs_next_state(state, next_count, curr_count, thr, has_reverse, rrd_direct);
         curr_count = next_count;
         curr_level++;
         state = next_state;
     }
-    if (!device_driven) GMC_CUDA(cudaEventRecord(ev1, st));
+    if (!device_driven && !persistent) GMC_CUDA(cudaEventRecord(ev1, st));
     GMC_CUDA(cudaStreamSynchronize(st));
     w->valid = true;
     w->last_is_i16 = sizeof(L) == 2;

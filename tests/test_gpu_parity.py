@@ -400,6 +400,27 @@ def test_bfs_host_loop_and_deep_graph(gm, oracle, g_rmat, monkeypatch):
     assert np.array_equal(dist, want) and info.levels == 200
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["GMC_BFS_NO_SMALL", "GMC_BFS_PERSISTENT", "GMC_BFS_DEVICE_LOOP"])
+def test_bfs_loop_modes_agree(gm, oracle, g_rmat, monkeypatch, mode):
+    """the default traversal (runs of small top-down levels in one CTA, bfs_small_levels; the rest as prepare / expand / finish
+    launches) against the other ways to drive the same level kernels: no small-level kernel, one cooperative launch per
+    traversal, the device-side state machine.  Levels, state trace and level counts must be the oracle's in every mode, from a quiet root, from
+    the hub, and on graphs small enough that a small level is followed by a bottom-up one."""
+    deg = np.diff(g_rmat["begin"])
+    small = graphs.rmat(oracle, 600, 5000, seed=3)
+    sdeg = np.diff(small["begin"])
+    cases = [(g_rmat, graphs.first_root_with_edges(g_rmat)), (g_rmat, int(np.argmax(deg)))]
+    cases += [(small, int(r)) for r in np.nonzero(sdeg)[0][[0, 1, 2, 5, 11]]] + [(small, int(np.argmax(sdeg)))]
+    want = [oracle.bfs_levels(g["begin"], g["node_idx"], g["r_begin"], g["r_node_idx"], r) for g, r in cases]
+    for env in (None, mode):
+        if env: monkeypatch.setenv(env, "1")
+        for (g, r), (wlev, nl, wtrace, wcnt) in zip(cases, want):
+            lev, info, trace, cnt = dev_graph(gm, g).bfs_levels(r)
+            assert info.levels == nl and np.array_equal(lev, wlev), (env, r)
+            assert list(trace) == list(wtrace[:nl]) and list(cnt) == list(wcnt[:nl]), (env, r)
+
+
 def _ks(a, b):
     """Kolmogorov-Smirnov distance of two integer samples (max gap of their CDFs)"""
     hi = int(max(a.max(), b.max())) + 1
