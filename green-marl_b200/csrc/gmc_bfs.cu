@@ -80,7 +80,7 @@ struct gmc_bfs_ws {
     int32_t wpr = 0;                  // bitmap words owned per rank
     int32_t wp = 0;                   // padded bitmap length = wpr * world
     uint32_t* visited = nullptr;      // [wp]
-    uint32_t* frontier_bm = nullptr;  // [wp] bitmap of the current level
+    uint32_t* frontier_bm = nullptr;  // 2 x [wp]: bitmap of the current level and the one being made (host-driven loop: ping-pong)
     uint32_t* cand = nullptr;         // [wp] candidates of the next level (top-down) / next level (bottom-up)
     uint32_t* allcand = nullptr;      // [world*wp] gathered candidate bitmaps (sharded top-down without peer mapping)
     // sharded runs: cand is the first of TWO buffers (level parity) in one exportable allocation, mapped by the peers, so that
@@ -489,6 +489,78 @@ bfs_finish(int32_t words, int32_t wp, int world, int use_all, uint32_t* __restri
     }
 }
 
+// ---- bottom-up level in ONE launch (single GPU): scan + end-of-level work of the same word ------------------------------------
+// The warp that scans word w is the only one that reads visited[w], and what it finds IS the new part of the word, so it can
+// finish the word itself: visited |= got, level[] of the found lanes, next-frontier word (into the OTHER frontier buffer: the
+// current one is still being probed by every warp), queue entries.  One atomicAdd per CTA (8 words) hands out queue space -- per
+// warp it would be 150 K atomics on one address.  Saves the bitmap pass and the launch of bfs_finish on the 2-3 widest levels.
+template <typename L>
+__global__ void __launch_bounds__(BFS_THREADS)
+bu_scan_finish(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t words,
+               const uint32_t* __restrict__ frontier_cur, uint32_t* __restrict__ frontier_next, uint32_t* __restrict__ visited,
+               L next_level, L* __restrict__ level, int32_t* __restrict__ next_queue, int32_t* __restrict__ counters,
+               volatile int32_t* __restrict__ host_out, int32_t seq) {
+    __shared__ int32_t s_cnt[BFS_THREADS / 32];
+    __shared__ int32_t s_base;
+    __shared__ int s_last;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int32_t w = (blockIdx.x * BFS_THREADS + threadIdx.x) >> 5;
+    bool found = false;
+    uint32_t vis = 0xffffffffu;
+    const int32_t t = (w << 5) + lane;
+    if (w < words) {
+        vis = visited[w];
+        if (t < n && !((vis >> lane) & 1u)) {
+            const int32_t b = r_begin[t], e = r_begin[t + 1];
+            for (int32_t nx = b; nx < e && !found; nx += 4) {       // four parents per step, as in bu_scan_body
+                int32_t u[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++) u[k] = nx + k < e ? r_node_idx[nx + k] : -1;
+                uint32_t fw[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++) fw[k] = u[k] >= 0 ? frontier_cur[u[k] >> 5] : 0u;
+#pragma unroll
+                for (int k = 0; k < 4; k++) found = found || (u[k] >= 0 && ((fw[k] >> (u[k] & 31)) & 1u));
+            }
+        }
+    }
+    const uint32_t got = __ballot_sync(FULLMASK, found);
+    if (w < words && lane == 0) {
+        if (got) visited[w] = vis | got;
+        frontier_next[w] = got;
+    }
+    if (found) level[t] = next_level;
+    if (lane == 0) s_cnt[wid] = __popc(got);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int total = 0;
+#pragma unroll
+        for (int k = 0; k < BFS_THREADS / 32; k++) total += s_cnt[k];
+        s_base = total ? atomicAdd(&counters[1], total) : 0;
+    }
+    __syncthreads();
+    if (found) {
+        int32_t base = s_base;
+        for (int k = 0; k < wid; k++) base += s_cnt[k];
+        next_queue[base + __popc(got & ((1u << lane) - 1u))] = t;
+    }
+    // last CTA: publish the level's count (single GPU: all of it is owned) and reset the counters, as bfs_finish does
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_last = (atomicAdd(&counters[3], 1) == (int)gridDim.x - 1);
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x == 0) {
+        __threadfence();
+        const int32_t next_count = atomicAdd(&counters[1], 0);
+        counters[0] = 0; counters[1] = 0; counters[2] = 0; counters[3] = 0;
+        host_out[0] = next_count; host_out[1] = next_count;
+        __threadfence_system();
+        host_out[2] = seq;
+    }
+}
+
 // ---- runs of SMALL top-down levels (single GPU): one CTA, no grid-wide step at all ----------------------------------------------
 // A level whose frontier has at most SMALL_Q vertices and SMALL_E out-edges is a latency chain, not a bandwidth problem: as
 // prepare / expand / finish launches it costs ~35 us of launch, drain and bitmap passes for a few thousand edges.  Here one CTA of
@@ -717,7 +789,7 @@ int ensure_ws(gmc_graph* g, int world) {
     const size_t nn = (size_t)(g->N ? g->N : 1);
     w->chunk_cap = (size_t)g->M / TD_CHUNK + nn / BFS_THREADS + 2;
     int rc = gmc_malloc((void**)&w->visited, wb);
-    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->frontier_bm, wb);
+    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->frontier_bm, 2 * wb);      // current / next level (ping-pong)
     if (rc == GMC_OK) rc = world > 1 ? gmc_malloc_ipc((void**)&w->cand, 2 * wb) : gmc_malloc((void**)&w->cand, wb);
     if (rc == GMC_OK && world > 1) rc = gmc_malloc((void**)&w->allcand, wb * (size_t)world);
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->queue[0], sizeof(int32_t) * nn);
@@ -916,13 +988,19 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     }
     // runs of small top-down levels go to bfs_small_levels (one CTA, several levels per launch); GMC_BFS_NO_SMALL=1: never
     const bool small_ok = world == 1 && getenv("GMC_BFS_NO_SMALL") == nullptr;
+    // GMC_BFS_FUSED_BU=1: bottom-up levels in one launch (bu_scan_finish) on a single GPU.  Measured SLOWER than scan + finish as
+    // two launches (gpurun r3i, LJ-shaped, root 3: 0.324 against 0.281 ms; hub root 0.452 against 0.430): the block-wide queue
+    // allocation keeps the 8 warps of a CTA resident until its slowest row scan ends, which costs more than the bitmap pass and
+    // the launch it saves.  Opt-in.
+    const bool fused_bu = world == 1 && getenv("GMC_BFS_FUSED_BU") != nullptr;
+    uint32_t *fcur = w->frontier_bm, *fnext = w->frontier_bm + w->wp;      // every level writes fnext, then they swap
     int32_t small_refused = -1;       // level whose frontier had more than SMALL_E edges: it takes the grid path
     for (; !device_driven && !persistent;) {
         if (small_ok && !ctl_bottom_up(state) && own_count > 0 && own_count <= SMALL_Q && small_refused != curr_level) {
             int max_levels = SMALL_LEVELS;
             if (sizeof(L) == 2) max_levels = min(max_levels, 32767 - curr_level);
             GMC_REQUIRE(max_levels > 0, GMC_ERR_STATE, "bfs: more levels than level_t can hold");
-            bfs_small_levels<L><<<1, SMALL_THREADS, 0, st>>>(fwd_begin, fwd_idx, edge_mask, w->queue[0], w->queue[1], w->visited, w->frontier_bm,
+            bfs_small_levels<L><<<1, SMALL_THREADS, 0, st>>>(fwd_begin, fwd_idx, edge_mask, w->queue[0], w->queue[1], w->visited, fcur,
                                                              w->words, level, state, curr_level, curr_count, qi, thr, has_reverse ? 1 : 0,
                                                              rrd_direct ? 1 : 0, max_levels, w->h_counters, ++w->seq);
             launches++;
@@ -954,10 +1032,15 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             for (int r = 0; r < world; r++) pc.base[r] = (uint32_t*)w->peer_base[r] + (size_t)(curr_level & 1) * w->wp;
             pc.wpr = w->wpr; pc.world = world; pc.rank = rank;
         }
-        if (state == ST_RRD || state == ST_RR2Q) {
+        if ((state == ST_RRD || state == ST_RR2Q) && fused_bu) {
+            bu_scan_finish<L><<<div_up(w->words * 32, BFS_THREADS), BFS_THREADS, 0, st>>>(rev_begin, rev_idx, n, w->words, fcur, fnext, w->visited, nl,
+                                                                                         level, w->queue[qi ^ 1], w->counters, w->h_counters, ++w->seq);
+            launches++;
+            bottom_up++;
+        } else if (state == ST_RRD || state == ST_RR2Q) {
             if (own_hi > own_lo) {
                 bu_scan<<<div_up((own_hi - own_lo) * 32, BFS_THREADS), BFS_THREADS, 0, st>>>(rev_begin, rev_idx, n, own_lo, own_hi,
-                                                                                            w->frontier_bm, w->visited, cand_l);
+                                                                                            fcur, w->visited, cand_l);
                 launches++;
             }
             bottom_up++;
@@ -984,9 +1067,12 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
                 use_all = 1;
             }
         }
-        bfs_finish<L><<<fin_grid, BFS_THREADS, 0, st>>>(w->words, w->wp, world, use_all, cand_l, w->allcand, w->visited, w->frontier_bm,
-                                                        nl, level, own_lo, own_hi, w->queue[qi ^ 1], w->counters, w->h_counters, ++w->seq);
-        launches++;
+        if (!(fused_bu && ctl_bottom_up(state))) {
+            bfs_finish<L><<<fin_grid, BFS_THREADS, 0, st>>>(w->words, w->wp, world, use_all, cand_l, w->allcand, w->visited, fnext,
+                                                            nl, level, own_lo, own_hi, w->queue[qi ^ 1], w->counters, w->h_counters, ++w->seq);
+            launches++;
+        }
+        { uint32_t* t = fcur; fcur = fnext; fnext = t; }
         GMC_CUDA(cudaGetLastError());
         GMC_TRY(wait_host_seq(w, st));    // the level's counts: the sequence number bfs_finish's last block writes into pinned memory
         const int32_t next_count = w->h_counters[0];
