@@ -15,6 +15,7 @@
 // The count is an integer sum, so the result is exact and independent of the order of evaluation.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <mutex>
 #include "gmc_common.cuh"
 #include "gmc_comm.h"
 
@@ -266,3 +267,86 @@ int gmc_triangle_counting(gmc_graph* g, int64_t* count, float* kernel_ms) {
 }
 
 }  // extern "C"
+
+// ---- the same count for callers that must not allocate (no counterpart in the reference)
+// -- code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc.  The scratch of the three
+// kernels (row hints, counters, segment list of the heavy intersections, the "rows not ascending" flag) lives in ONE file-scope
+// device array of a fixed size, so every GPU that loads the library holds TC_NA_BYTES (about 0.9 MB) until exit, and graphs of
+// more than GMC_TC_NOALLOC_MAX_EDGES edge slots are refused.  All calls on a device share the array and it keeps the last call's
+// contents: every call clears the counters, the flag and the segment list first, and two calls that overlap on the GPU (two
+// streams, two host threads) RACE -- callers serialise them.
+constexpr int64_t TC_NA_MAX_EDGES = GMC_TC_NOALLOC_MAX_EDGES;
+constexpr unsigned TC_NA_SEG_CAP = 1u << 15;                   // 32 K segments (768 KB); heavy items beyond that are done in place
+constexpr size_t TC_NA_HDR = 256;                              // total[4] (u64) at 0, flag (i32) at 64
+constexpr size_t TC_NA_HINTS = ((size_t)(TC_NA_MAX_EDGES / TC_TILE + 2) * 4 + 255) / 256 * 256;
+constexpr size_t TC_NA_SEGS = sizeof(TcSeg) * (size_t)TC_NA_SEG_CAP;
+constexpr size_t TC_NA_BYTES = TC_NA_HDR + TC_NA_HINTS + TC_NA_SEGS;
+static __device__ __align__(256) unsigned char g_tc_na_scratch[TC_NA_BYTES];
+
+namespace {
+
+// count_dev = the count, or -1 when a row of either CSR was not ascending (the allocating entry point returns GMC_ERR_STATE there)
+__global__ void tc_na_publish(const unsigned long long* __restrict__ total, const int32_t* __restrict__ bad, int64_t* __restrict__ count_dev) {
+    *count_dev = *bad ? (int64_t)-1 : (int64_t)*total;
+}
+
+// In host code g_tc_na_scratch is only a stand-in for the symbol, not a device address: the address is asked for once per
+// device, with that device current, and cached.
+constexpr int TC_NA_MAX_DEVICES = 64;
+unsigned char* g_tc_na_ptr[TC_NA_MAX_DEVICES];
+std::mutex g_tc_na_mu;
+
+int tc_na_scratch(unsigned char** out) {
+    int dev = -1;
+    GMC_CUDA(cudaGetDevice(&dev));
+    GMC_REQUIRE(dev >= 0 && dev < TC_NA_MAX_DEVICES, GMC_ERR_STATE, "gmc_triangle_counting_noalloc: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lk(g_tc_na_mu);
+    if (!g_tc_na_ptr[dev]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_tc_na_scratch);
+        if (e != cudaSuccess || !p) {
+            set_error("gmc_triangle_counting_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            return GMC_ERR_CUDA;
+        }
+        g_tc_na_ptr[dev] = (unsigned char*)p;
+    }
+    *out = g_tc_na_ptr[dev];
+    return GMC_OK;
+}
+
+}  // namespace
+
+extern "C" int gmc_triangle_counting_noalloc(gmc_graph* g, int64_t* count_dev, void* stream) {
+    GMC_REQUIRE(g && count_dev, GMC_ERR_ARG, "gmc_triangle_counting_noalloc: NULL");
+    GMC_REQUIRE(g->has_forward, GMC_ERR_STATE, "triangle_counting: the forward CSR (node_idx) was not uploaded for this graph");
+    GMC_REQUIRE(g->has_reverse, GMC_ERR_STATE, "triangle_counting needs the reverse CSR: call gmc_graph_make_reverse first");
+    GMC_REQUIRE((int64_t)g->M <= TC_NA_MAX_EDGES, GMC_ERR_ARG,
+                "gmc_triangle_counting_noalloc: %d edge slots, the fixed scratch holds at most %lld (use gmc_triangle_counting)", g->M,
+                (long long)TC_NA_MAX_EDGES);
+    unsigned char* base = nullptr;
+    GMC_TRY(tc_na_scratch(&base));
+    cudaStream_t st = as_stream(stream);
+    unsigned long long* total = reinterpret_cast<unsigned long long*>(base);
+    int32_t* bad = reinterpret_cast<int32_t*>(base + 64);
+    int32_t* hints = reinterpret_cast<int32_t*>(base + TC_NA_HDR);
+    TcSeg* segs = reinterpret_cast<TcSeg*>(base + TC_NA_HDR + TC_NA_HINTS);
+    const int32_t n = g->N, m = g->M;
+    const int32_t n_hints = div_up(m, TC_TILE) + 1;
+    // the array holds whatever the last call left: counters, flag and segment list start at zero
+    GMC_CUDA(cudaMemsetAsync(base, 0, TC_NA_HDR, st));
+    GMC_CUDA(cudaMemsetAsync(segs, 0, TC_NA_SEGS, st));
+    if (m > 0) {
+        // no host-side state, no synchronisation: the ascending-rows check runs on every call and travels with the result
+        k_rows_ascending<<<div_up(n, 256), 256, 0, st>>>(g->begin, g->node_idx, n, bad);
+        k_rows_ascending<<<div_up(n, 256), 256, 0, st>>>(g->r_begin, g->r_node_idx, n, bad);
+        tc_row_hints<<<div_up(n_hints, 256), 256, 0, st>>>(g->begin, n, m, n_hints, hints);
+        tc_count<<<sm_count() * 8, TC_THREADS, 0, st>>>(g->begin, g->node_idx, g->r_begin, g->r_node_idx, hints, n, 0, m,
+                                                         reinterpret_cast<unsigned int*>(total + 1), total, segs,
+                                                         reinterpret_cast<unsigned int*>(total + 1) + 1, TC_NA_SEG_CAP);
+        tc_heavy<<<sm_count() * 8, TC_THREADS, 0, st>>>(g->node_idx, g->r_node_idx, segs, reinterpret_cast<unsigned int*>(total + 1) + 1,
+                                                         TC_NA_SEG_CAP, reinterpret_cast<unsigned int*>(total + 2), total);
+    }
+    tc_na_publish<<<1, 1, 0, st>>>(total, bad, count_dev);
+    GMC_CUDA(cudaGetLastError());
+    return GMC_OK;
+}

@@ -77,6 +77,7 @@ SIGNATURES = {
     "gmc_pagerank_plan_info": (C.c_int, [_vp, C.POINTER(PlanInfo)]),
     "gmc_triangle_counting": (C.c_int, [_vp, C.POINTER(C.c_int64), C.POINTER(C.c_float)]),
     "gmc_triangle_counting_range": (C.c_int, [_vp, C.c_int64, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_float), _vp]),
+    "gmc_triangle_counting_noalloc": (C.c_int, [_vp, _vp, _vp]),
     "gmc_triangle_counting_sharded": (C.c_int, [_vp, _vp, C.POINTER(C.c_int64), C.POINTER(C.c_float), _vp]),
     "gmc_comp_bc": (C.c_int, [_vp, _vp, _i32, _vp, C.POINTER(BcInfo)]),
     "gmc_comp_bc_adj": (C.c_int, [_vp, _vp, _i32, _vp, C.POINTER(BcInfo)]),
@@ -393,6 +394,11 @@ class Graph:
         else:
             self.lib.check(self.lib.L.gmc_triangle_counting_range(self.h, e_lo, e_hi, C.byref(cnt), C.byref(ms), None))
         return cnt.value, ms.value
+
+    def triangle_counting_noalloc(self, count_dev, stream=None):
+        """gmc_triangle_counting_noalloc: allocates nothing, does not synchronise; the count (or -1: rows not ascending) is
+        written into the caller's device int64 `count_dev` (an address from GmCuda.malloc) on `stream`"""
+        self.lib.check(self.lib.L.gmc_triangle_counting_noalloc(self.h, _vp(count_dev), _vp(stream) if stream else None))
 
     def comp_bc(self, seeds, adj=False):
         """comp_BC (bc.gm; adj=True: bc_adj.gm) over the given seeds in order: returns (BC float32[N], BcInfo)"""

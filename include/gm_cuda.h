@@ -214,6 +214,16 @@ int gmc_comp_bc_adj(gmc_graph* g, const int32_t* seeds, int32_t n_seeds, float* 
  * _range counts the edge slots [e_lo, e_hi) only: ranks of a multi-GPU job take slices and add their counts. */
 int gmc_triangle_counting(gmc_graph* g, int64_t* count, float* kernel_ms);
 int gmc_triangle_counting_range(gmc_graph* g, int64_t e_lo, int64_t e_hi, int64_t* count, float* kernel_ms, void* stream);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  The same count as gmc_triangle_counting, but the
+ * call allocates and frees nothing and does not synchronise: the kernels' scratch is a fixed file-scope device array (about
+ * 0.9 MB, held by every GPU that loads the library until exit), so graphs of more than GMC_TC_NOALLOC_MAX_EDGES edge slots are
+ * refused with GMC_ERR_ARG.  The graph (inputs) is the caller's resident gmc_graph; the output is ONE int64 in DEVICE memory
+ * the caller owns (count_dev), written on `stream`: the count, or -1 when a row of either CSR is not ascending (where
+ * gmc_triangle_counting returns GMC_ERR_STATE).  All calls on a device share the scratch array, which keeps the last call's
+ * contents (each call clears what must start at zero): calls that overlap on the GPU race -- serialise them. */
+#define GMC_TC_NOALLOC_MAX_EDGES (1 << 26)
+int gmc_triangle_counting_noalloc(gmc_graph* g, int64_t* count_dev, void* stream);
 
 /* --- multi-GPU: one process per GPU, destination-vertex ranges per rank.  Shoal's
  * replicate / partition placement (reference src/backend_cpp/gm_cpp_gen.cc:181-227: shl__malloc_array with
