@@ -488,7 +488,7 @@ def run_single(args, n, m):
            "edges_per_traversal": int(np.mean(bfs_edges)), "what": "hop_dist (direction-optimizing), device time",
            "gpu_launches": int(bfs_launches),
            "roofline": {"bound": "hbm", "achieved": round(a_bfs, 1), "peak": peak, "unit": "GB/s", "frac": round(a_bfs / peak, 4),
-                        "traffic": None, "peak_kind": peak_kind, "kernel": "whole traversal (td_prepare/td_expand/bu_scan/bfs_finish per level)",
+                        "traffic": None, "peak_kind": peak_kind, "kernel": "whole traversal (bfs_small_levels for runs of small levels; td_prepare/td_expand/bfs_finish, bu_scan_mark or bu_scan/bfs_finish per wide level)",
                         "alg_bytes_per_traversal": int(np.mean(bfs_abytes)),
                         "formula": "A_BFS = 4*M_r + N_r*(4+4) + 2*ceil(N/8)*L over the traversal's device time"}}
     # gm_bfs_template<short,...> traversal (bc / kosaraju's InBFS) on the first 4 roots

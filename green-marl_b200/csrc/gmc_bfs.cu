@@ -37,6 +37,7 @@ constexpr int BFS_THREADS = 256;
 constexpr int TD_CHUNK = 256;        // edge slots per warp chunk (8 per lane)
 constexpr int TD_BATCHED_MAX_FRONTIER = 8192;   // owned frontier vertices up to which td_expand batches a lane's 8 loads
 constexpr unsigned FULLMASK = 0xffffffffu;
+constexpr int BFS_SPREAD = 64;          // counters a bottom-up level spreads its per-warp counts over (bu_scan_mark)
 
 // Device-side traversal control (single-GPU runs): the reference's level-to-level state machine (get_next_state,
 // gm_bfs_template.h:352-421) is evaluated by the last block of bfs_finish, so the host enqueues the kernels of several
@@ -93,9 +94,10 @@ struct gmc_bfs_ws {
     int32_t* blk_total = nullptr;     // [ceil(N/256)]
     int2* chunks = nullptr;           // [M/TD_CHUNK + N/256 + 2] (queue block, chunk-in-block)
     size_t chunk_cap = 0;
+    int32_t* spread = nullptr;        // [BFS_SPREAD] per-warp counts of a bottom-up level (bu_scan_mark), summed by bfs_publish
     int32_t* counters = nullptr;      // [8]: 0 = level count (global), 1 = owned queue count, 2 = nchunks
     int32_t* h_counters = nullptr;    // pinned + mapped [BFS_HOST_WORDS]: 0 = level count, 1 = owned count, 2 = sequence number of the level that wrote
-                                      // them; bfs_small_levels: 0 = levels done, 1 = traversal ended, 2 = sequence number, 4.. = count found by each level
+                                      // them; bfs_small_levels: 0 = levels done, 1 = traversal ended, 2 = sequence number, 3 = the level after those is too big for it, 4.. = count found by each level
     int32_t seq = 0;
     void* level = nullptr;            // [N] int32 (also used as int16)
     unsigned long long* edge_sum = nullptr;
@@ -112,7 +114,7 @@ void gmc_bfs_ws_free(gmc_graph* g) {
     if (w->peer_ok) gmc_comm_ipc_close_all(w->world, w->rank, w->peer_base, w->peer_local);
     cudaFree(w->visited); cudaFree(w->frontier_bm); cudaFree(w->cand); cudaFree(w->allcand);
     cudaFree(w->queue[0]); cudaFree(w->queue[1]); cudaFree(w->blk_off); cudaFree(w->blk_total); cudaFree(w->chunks);
-    cudaFree(w->counters); cudaFree(w->level); cudaFree(w->edge_sum); cudaFree(w->ctl);
+    cudaFree(w->counters); cudaFree(w->spread); cudaFree(w->level); cudaFree(w->edge_sum); cudaFree(w->ctl);
     if (w->h_counters) cudaFreeHost(w->h_counters);
     delete w;
     g->bfs = nullptr;
@@ -120,18 +122,36 @@ void gmc_bfs_ws_free(gmc_graph* g) {
 
 namespace {
 
+// level[] = invalid (16-byte stores when the array allows it: 4.85 M one-element threads were 14 us of CTA launches), the bitmaps,
+// the counters.  seen != 0: `cand` is the SEEN bitmap of the host-driven single-GPU loop (visited | candidates) and starts as visited.
 template <typename L>
 __global__ void bfs_init(L* __restrict__ level, int32_t n, L invalid, int32_t root, uint32_t* __restrict__ visited,
                          uint32_t* __restrict__ frontier, uint32_t* __restrict__ cand, int32_t wp,
-                         int32_t* __restrict__ queue, int root_owned, int32_t* __restrict__ counters, int two_cand = 0) {
-    int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) level[i] = (i == root) ? (L)0 : invalid;
-    if (i < wp) {
+                         int32_t* __restrict__ queue, int root_owned, int32_t* __restrict__ counters, int two_cand = 0, int seen = 0,
+                         int32_t* __restrict__ spread = nullptr) {
+    constexpr int PER = 16 / (int)sizeof(L);
+    const int32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nthr = gridDim.x * blockDim.x;
+    int32_t done = 0;
+    if ((reinterpret_cast<uintptr_t>(level) & 15) == 0) {
+        union { int4 v; L e[PER]; } fill;
+#pragma unroll
+        for (int k = 0; k < PER; k++) fill.e[k] = invalid;
+        const int32_t nvec = n / PER;
+        for (int32_t i = tid; i < nvec; i += nthr) {
+            auto x = fill;
+            if (root >= i * PER && root < (i + 1) * PER) x.e[root - i * PER] = (L)0;
+            reinterpret_cast<int4*>(level)[i] = x.v;
+        }
+        done = nvec * PER;
+    }
+    for (int32_t i = done + tid; i < n; i += nthr) level[i] = (i == root) ? (L)0 : invalid;
+    for (int32_t i = tid; i < wp; i += nthr) {
         const uint32_t b = (i == (root >> 5)) ? (1u << (root & 31)) : 0u;
-        visited[i] = b; frontier[i] = b; cand[i] = 0u;
+        visited[i] = b; frontier[i] = b; cand[i] = seen ? b : 0u;
         if (two_cand) cand[wp + i] = 0u;
     }
-    if (i == 0) { if (root_owned) queue[0] = root; counters[0] = 0; counters[1] = 0; counters[2] = 0; counters[3] = 0; }
+    if (spread && tid < BFS_SPREAD) spread[tid] = 0;
+    if (tid == 0) { if (root_owned) queue[0] = root; counters[0] = 0; counters[1] = 0; counters[2] = 0; counters[3] = 0; }
 }
 
 __global__ void bfs_ctl_init(BfsCtl* ctl, float thr, int has_reverse, int rrd_direct) {
@@ -329,7 +349,8 @@ bu_scan_body(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_
         }
     }
     const uint32_t got = __ballot_sync(FULLMASK, found);
-    if (lane == 0) cand[w] = got;
+    // vis | got: bfs_finish takes cand & ~visited, and where cand is the SEEN bitmap the word has to be visited | candidates
+    if (lane == 0) cand[w] = vis | got;
     }
 }
 
@@ -349,6 +370,14 @@ td_expand(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_id
           const uint8_t* __restrict__ edge_mask, const __grid_constant__ PeerCand pc) {
     td_expand_body<BATCHED>(begin, node_idx, queue, qcount, blk_off, blk_total, chunks, nchunks_p, visited, cand, edge_mask, nullptr, nullptr,
                             pc.world > 1 ? &pc : nullptr);
+}
+// seen mode: ONE bitmap (visited | candidates) is probed and marked; it changes under the kernel, so no __restrict__ / read-only loads
+template <bool BATCHED>
+__global__ void __launch_bounds__(BFS_THREADS)
+td_expand_seen(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_idx, const int32_t* __restrict__ queue, int32_t qcount,
+               const int32_t* __restrict__ blk_off, const int32_t* __restrict__ blk_total, const int2* __restrict__ chunks,
+               const int32_t* __restrict__ nchunks_p, uint32_t* seen, const uint8_t* __restrict__ edge_mask) {
+    td_expand_body<BATCHED>(begin, node_idx, queue, qcount, blk_off, blk_total, chunks, nchunks_p, seen, seen, edge_mask, nullptr, nullptr, nullptr);
 }
 __global__ void __launch_bounds__(BFS_THREADS)
 bu_scan(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t w_lo, int32_t w_hi,
@@ -383,7 +412,7 @@ template <typename L>
 __device__ __forceinline__ void
 finish_warp(int32_t w, int32_t words, int32_t wp, int world, int use_all, uint32_t* cand, const uint32_t* allcand, uint32_t* visited,
             uint32_t* frontier, L next_level, L* __restrict__ level, int32_t own_lo, int32_t own_hi, int32_t* next_queue,
-            int32_t* counters) {
+            int32_t* counters, int keep_cand = 0) {
     const int lane = threadIdx.x & 31;
     uint32_t nw = 0;
     if (w < words) {
@@ -392,7 +421,7 @@ finish_warp(int32_t w, int32_t words, int32_t wp, int world, int use_all, uint32
             c = 0;
             for (int r = 0; r < world; r++) c |= allcand[(size_t)r * wp + w];
         } else c = cand[w];
-        cand[w] = 0u;
+        if (!keep_cand) cand[w] = 0u;          // (keep_cand: cand is the SEEN bitmap, visited | candidates = the new visited)
         const uint32_t vis = visited[w];
         nw = c & ~vis;
         if (nw) visited[w] = vis | nw;
@@ -454,7 +483,8 @@ __global__ void __launch_bounds__(BFS_THREADS)
 bfs_finish(int32_t words, int32_t wp, int world, int use_all, uint32_t* __restrict__ cand, const uint32_t* __restrict__ allcand,
            uint32_t* __restrict__ visited, uint32_t* __restrict__ frontier, L next_level, L* __restrict__ level,
            int32_t own_lo, int32_t own_hi, int32_t* __restrict__ next_queue, int32_t* __restrict__ counters,
-           volatile int32_t* __restrict__ host_out, int32_t seq, int32_t* __restrict__ queue_alt = nullptr, BfsCtl* ctl = nullptr) {
+           volatile int32_t* __restrict__ host_out, int32_t seq, int32_t* __restrict__ queue_alt = nullptr, BfsCtl* ctl = nullptr,
+           int keep_cand = 0) {
     if (ctl) {     // device-driven traversal: level number and queue come from the control block
         if (ctl->done) {      // the traversal ended earlier in this batch of launches: only tell the host
             if (blockIdx.x == 0 && threadIdx.x == 0) { host_out[1] = 1; __threadfence_system(); host_out[2] = seq; }
@@ -464,7 +494,7 @@ bfs_finish(int32_t words, int32_t wp, int world, int use_all, uint32_t* __restri
         if (!ctl->qi) next_queue = queue_alt;       // next = queue[qi ^ 1]; next_queue = queue[0], queue_alt = queue[1]
     }
     finish_warp<L>(blockIdx.x * BFS_THREADS + threadIdx.x, words, wp, world, use_all, cand, allcand, visited, frontier, next_level, level,
-                   own_lo, own_hi, next_queue, counters);
+                   own_lo, own_hi, next_queue, counters, keep_cand);
     // the last block to finish publishes the two level counts straight into the host's (mapped, pinned) memory and
     // resets the device counters: the host polls the sequence number instead of a memcpy + memset + stream sync per level
     __shared__ int s_last;
@@ -561,6 +591,69 @@ bu_scan_finish(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ 
     }
 }
 
+// ---- bottom-up level whose successor is bottom-up too (state RRD: the next state is RRD or RR2Q) ---------------------------------
+// No top-down level reads its result, so no queue is needed, and then the scanning warp can finish its word alone: visited |= got,
+// next-frontier word (the OTHER frontier buffer: this level's is being probed), level[] of the found lanes, seen word.  The level's
+// count goes into BFS_SPREAD counters (a warp adds to counter w mod BFS_SPREAD: no block-wide step, a finished warp leaves) and a
+// one-warp kernel adds them up for the host: scan + publish instead of scan + a bfs_finish pass over three bitmaps.
+template <typename L>
+__global__ void __launch_bounds__(BFS_THREADS)
+bu_scan_mark(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t words,
+             const uint32_t* __restrict__ frontier_cur, uint32_t* __restrict__ frontier_next, uint32_t* __restrict__ visited,
+             uint32_t* __restrict__ seen, L next_level, L* __restrict__ level, int32_t* __restrict__ spread) {
+    // the CTA's count: shared-memory atomics, flushed by whichever warp finishes last (no barrier after the scan: a finished warp
+    // leaves).  A global atomic per warp -- 150 K of them on 64 neighbouring counters -- ran at the L2's one-per-clock rate for a
+    // cache line and cost 30 us per level (gpurun r3l).
+    __shared__ int s_cnt, s_arrived;
+    if (threadIdx.x == 0) { s_cnt = 0; s_arrived = 0; }
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int32_t w = (blockIdx.x * BFS_THREADS + threadIdx.x) >> 5;
+    const uint32_t vis = w < words ? visited[w] : 0xffffffffu;
+    const int32_t t = (w << 5) + lane;
+    bool found = false;
+    if (t < n && !((vis >> lane) & 1u)) {
+        const int32_t b = r_begin[t], e = r_begin[t + 1];
+        for (int32_t nx = b; nx < e && !found; nx += 4) {       // four parents per step, as in bu_scan_body
+            int32_t u[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) u[k] = nx + k < e ? r_node_idx[nx + k] : -1;
+            uint32_t fw[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) fw[k] = u[k] >= 0 ? frontier_cur[u[k] >> 5] : 0u;
+#pragma unroll
+            for (int k = 0; k < 4; k++) found = found || (u[k] >= 0 && ((fw[k] >> (u[k] & 31)) & 1u));
+        }
+    }
+    const uint32_t got = __ballot_sync(FULLMASK, found);
+    if (found) level[t] = next_level;
+    if (lane == 0) {
+        if (w < words) frontier_next[w] = got;
+        if (got) {
+            visited[w] = vis | got;
+            if (seen) seen[w] = vis | got;
+            atomicAdd_block(&s_cnt, __popc(got));
+        }
+        __threadfence_block();
+        if (atomicAdd_block(&s_arrived, 1) == BFS_THREADS / 32 - 1) {
+            const int c = atomicAdd_block(&s_cnt, 0);
+            if (c) atomicAdd(&spread[blockIdx.x & (BFS_SPREAD - 1)], c);
+        }
+    }
+}
+
+// the count of a bu_scan_mark level -> the host's pinned block (same slots as bfs_finish writes); the spread counters start over
+__global__ void bfs_publish(int32_t* __restrict__ spread, volatile int32_t* __restrict__ host_out, int32_t seq) {
+    int v = 0;
+    for (int i = threadIdx.x; i < BFS_SPREAD; i += 32) { v += spread[i]; spread[i] = 0; }
+    v = warp_sum(v);
+    if (threadIdx.x == 0) {
+        host_out[0] = v; host_out[1] = v;
+        __threadfence_system();
+        host_out[2] = seq;
+    }
+}
+
 // ---- runs of SMALL top-down levels (single GPU): one CTA, no grid-wide step at all ----------------------------------------------
 // A level whose frontier has at most SMALL_Q vertices and SMALL_E out-edges is a latency chain, not a bandwidth problem: as
 // prepare / expand / finish launches it costs ~35 us of launch, drain and bitmap passes for a few thousand edges.  Here one CTA of
@@ -577,7 +670,7 @@ constexpr int BFS_HOST_WORDS = SMALL_HDR + SMALL_LEVELS + 4;
 template <typename L>
 __global__ void __launch_bounds__(SMALL_THREADS, 1)
 bfs_small_levels(const int32_t* __restrict__ begin, const int32_t* __restrict__ node_idx, const uint8_t* __restrict__ edge_mask,
-                 int32_t* queue0, int32_t* queue1, uint32_t* visited, uint32_t* frontier, int32_t words, L* level, int state,
+                 int32_t* queue0, int32_t* queue1, uint32_t* visited, uint32_t* seen, uint32_t* frontier, int32_t words, L* level, int state,
                  int32_t curr_level, int32_t curr_count, int32_t qi, float thr, int has_reverse, int rrd_direct, int max_levels,
                  volatile int32_t* host_out, int32_t seq) {
     __shared__ int32_t s_off[SMALL_Q + 1];
@@ -586,7 +679,7 @@ bfs_small_levels(const int32_t* __restrict__ begin, const int32_t* __restrict__ 
     __shared__ int32_t s_next;
     constexpr int PER = SMALL_Q / SMALL_THREADS;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    int n_done = 0, ended = 0;
+    int n_done = 0, ended = 0, refused = 0;
     int32_t own = curr_count;
     for (;;) {
         const int32_t* q = qi ? queue1 : queue0;
@@ -609,7 +702,7 @@ bfs_small_levels(const int32_t* __restrict__ begin, const int32_t* __restrict__ 
         int32_t woff = 0, total = 0;
 #pragma unroll
         for (int k = 0; k < SMALL_THREADS / 32; k++) { const int32_t t = s_warp[k]; if (k < wid) woff += t; total += t; }
-        if (total > SMALL_E) break;                 // (uniform) this level needs the grid
+        if (total > SMALL_E) { refused = 1; break; }       // (uniform) this level needs the grid
         int32_t run = inc - mine + woff;
 #pragma unroll
         for (int k = 0; k < PER; k++) {
@@ -645,7 +738,10 @@ bfs_small_levels(const int32_t* __restrict__ begin, const int32_t* __restrict__ 
                 // navigator (check_navigator, gm_bfs_template.h:488-492,596-598): filtered edges are not followed
                 if ((vis[j] & bit) || (edge_mask && !edge_mask[eidx[j]])) continue;
                 const uint32_t old = atomicOr(&visited[u[j] >> 5], bit);
-                if (!(old & bit)) { level[u[j]] = nl; qn[atomicAdd(&s_next, 1)] = u[j]; }
+                if (!(old & bit)) {
+                    level[u[j]] = nl; qn[atomicAdd(&s_next, 1)] = u[j];
+                    if (seen) atomicOr(&seen[u[j] >> 5], bit);          // seen = visited | candidates stays equal to visited
+                }
             }
         }
         __syncthreads();
@@ -666,7 +762,7 @@ bfs_small_levels(const int32_t* __restrict__ begin, const int32_t* __restrict__ 
     }
     __syncthreads();
     if (tid == 0) {
-        host_out[0] = n_done; host_out[1] = ended;
+        host_out[0] = n_done; host_out[1] = ended; host_out[3] = refused;
         __threadfence_system();
         host_out[2] = seq;
     }
@@ -798,6 +894,7 @@ int ensure_ws(gmc_graph* g, int world) {
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->blk_total, sizeof(int32_t) * (nn / BFS_THREADS + 1));
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->chunks, sizeof(int2) * w->chunk_cap);
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->counters, sizeof(int32_t) * 8);
+    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->spread, sizeof(int32_t) * BFS_SPREAD);
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->level, sizeof(int32_t) * nn);
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->edge_sum, sizeof(unsigned long long));
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->ctl, sizeof(BfsCtl));
@@ -865,9 +962,16 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     }
     const bool peer = world > 1 && w->peer_ok;
     GMC_CUDA(cudaEventRecord(ev0, st));
+    const unsigned init_grid = (unsigned)min(div_up(max(n / (16 / (int)sizeof(L)), w->wp), 256), sm_count() * 16);
+    // Host-driven loop on a single GPU: `cand` is kept as the SEEN bitmap = visited | candidates of the level being expanded, so
+    // td_expand probes ONE bitmap per edge instead of visited and then cand (the hub root's 105 K-vertex top-down level: 68.8 M L2
+    // sectors in 221 us, profiles/r3k_bfs_launches_hub.md -- one random sector per probe); bfs_finish takes new = seen & ~visited
+    // and leaves seen = the new visited.  GMC_BFS_NO_SEEN=1: separate bitmaps, cleared every level (what the sharded paths use).
+    const bool seen_mode = world == 1 && getenv("GMC_BFS_NO_SEEN") == nullptr && getenv("GMC_BFS_DEVICE_LOOP") == nullptr &&
+                           getenv("GMC_BFS_PERSISTENT") == nullptr && getenv("GMC_BFS_FUSED_BU") == nullptr;
     int qi = 0;     // queue[qi] = current level
-    bfs_init<L><<<div_up(max(n, w->wp), 256), 256, 0, st>>>(level, n, invalid, root, w->visited, w->frontier_bm, w->cand, w->wp,
-                                                              w->queue[0], root_owned ? 1 : 0, w->counters, world > 1 ? 1 : 0);
+    bfs_init<L><<<init_grid, 256, 0, st>>>(level, n, invalid, root, w->visited, w->frontier_bm, w->cand, w->wp,
+                                           w->queue[0], root_owned ? 1 : 0, w->counters, world > 1 ? 1 : 0, seen_mode ? 1 : 0, w->spread);
     launches++;
     // nobody sends candidates into a buffer its owner has not cleared yet
     if (peer) GMC_TRY(gmc_comm_stream_barrier(comm, st));
@@ -922,8 +1026,8 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
         if (hc.overflow) {       // more levels than the trace holds: the host-driven loop below starts over
             persistent = false;
             GMC_CUDA(cudaEventRecord(ev0, st));
-            bfs_init<L><<<div_up(max(n, w->wp), 256), 256, 0, st>>>(level, n, invalid, root, w->visited, w->frontier_bm, w->cand, w->wp,
-                                                                      w->queue[0], root_owned ? 1 : 0, w->counters);
+            bfs_init<L><<<init_grid, 256, 0, st>>>(level, n, invalid, root, w->visited, w->frontier_bm, w->cand, w->wp,
+                                                   w->queue[0], root_owned ? 1 : 0, w->counters, 0, 0, w->spread);
             launches++;
         } else {
             for (int k = 0; k < hc.n_trace; k++) {
@@ -981,8 +1085,8 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
         }
         if (!device_driven) {       // start over on the host-driven path
             GMC_CUDA(cudaEventRecord(ev0, st));
-            bfs_init<L><<<div_up(max(n, w->wp), 256), 256, 0, st>>>(level, n, invalid, root, w->visited, w->frontier_bm, w->cand, w->wp,
-                                                                      w->queue[0], root_owned ? 1 : 0, w->counters);
+            bfs_init<L><<<init_grid, 256, 0, st>>>(level, n, invalid, root, w->visited, w->frontier_bm, w->cand, w->wp,
+                                                   w->queue[0], root_owned ? 1 : 0, w->counters, 0, 0, w->spread);
             launches++; bottom_up = 0;
         }
     }
@@ -993,6 +1097,8 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     // allocation keeps the 8 warps of a CTA resident until its slowest row scan ends, which costs more than the bitmap pass and
     // the launch it saves.  Opt-in.
     const bool fused_bu = world == 1 && getenv("GMC_BFS_FUSED_BU") != nullptr;
+    // RRD levels (the next level is bottom-up again: no queue needed) as scan-and-mark + a one-warp publish; GMC_BFS_NO_BU_MARK=1: scan + finish
+    const bool bu_mark = world == 1 && !fused_bu && getenv("GMC_BFS_NO_BU_MARK") == nullptr;
     uint32_t *fcur = w->frontier_bm, *fnext = w->frontier_bm + w->wp;      // every level writes fnext, then they swap
     int32_t small_refused = -1;       // level whose frontier had more than SMALL_E edges: it takes the grid path
     for (; !device_driven && !persistent;) {
@@ -1000,14 +1106,14 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             int max_levels = SMALL_LEVELS;
             if (sizeof(L) == 2) max_levels = min(max_levels, 32767 - curr_level);
             GMC_REQUIRE(max_levels > 0, GMC_ERR_STATE, "bfs: more levels than level_t can hold");
-            bfs_small_levels<L><<<1, SMALL_THREADS, 0, st>>>(fwd_begin, fwd_idx, edge_mask, w->queue[0], w->queue[1], w->visited, fcur,
-                                                             w->words, level, state, curr_level, curr_count, qi, thr, has_reverse ? 1 : 0,
+            bfs_small_levels<L><<<1, SMALL_THREADS, 0, st>>>(fwd_begin, fwd_idx, edge_mask, w->queue[0], w->queue[1], w->visited,
+                                                             seen_mode ? w->cand : nullptr, fcur, w->words, level, state, curr_level, curr_count, qi, thr, has_reverse ? 1 : 0,
                                                              rrd_direct ? 1 : 0, max_levels, w->h_counters, ++w->seq);
             launches++;
             GMC_CUDA(cudaGetLastError());
             GMC_TRY(wait_host_seq(w, st));
             const int k = w->h_counters[0];
-            if (k == 0) small_refused = curr_level;
+            const bool refused = w->h_counters[3] != 0;
             bool ended = false;
             for (int j = 0; j < k && !ended; j++) {      // replay the state machine over the counts of the levels it ran
                 w->state_trace.push_back(state);
@@ -1018,6 +1124,7 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
                 curr_count = next_count; own_count = next_count; curr_level++; qi ^= 1;
             }
             if (ended) break;
+            if (refused || k == 0) small_refused = curr_level;     // the level it stopped at has too many edges for one CTA
             continue;
         }
         w->state_trace.push_back(state);
@@ -1032,11 +1139,20 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             for (int r = 0; r < world; r++) pc.base[r] = (uint32_t*)w->peer_base[r] + (size_t)(curr_level & 1) * w->wp;
             pc.wpr = w->wpr; pc.world = world; pc.rank = rank;
         }
-        if ((state == ST_RRD || state == ST_RR2Q) && fused_bu) {
+        bool published = false;       // the level's counts are already on their way to the host (no bfs_finish)
+        if (state == ST_RRD && bu_mark) {
+            bu_scan_mark<L><<<div_up(w->words * 32, BFS_THREADS), BFS_THREADS, 0, st>>>(rev_begin, rev_idx, n, w->words, fcur, fnext, w->visited,
+                                                                                       seen_mode ? w->cand : nullptr, nl, level, w->spread);
+            bfs_publish<<<1, 32, 0, st>>>(w->spread, w->h_counters, ++w->seq);
+            launches += 2;
+            bottom_up++;
+            published = true;
+        } else if ((state == ST_RRD || state == ST_RR2Q) && fused_bu) {
             bu_scan_finish<L><<<div_up(w->words * 32, BFS_THREADS), BFS_THREADS, 0, st>>>(rev_begin, rev_idx, n, w->words, fcur, fnext, w->visited, nl,
                                                                                          level, w->queue[qi ^ 1], w->counters, w->h_counters, ++w->seq);
             launches++;
             bottom_up++;
+            published = true;
         } else if (state == ST_RRD || state == ST_RR2Q) {
             if (own_hi > own_lo) {
                 bu_scan<<<div_up((own_hi - own_lo) * 32, BFS_THREADS), BFS_THREADS, 0, st>>>(rev_begin, rev_idx, n, own_lo, own_hi,
@@ -1049,8 +1165,16 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             if (own_count > 0) {
                 td_prepare<<<div_up(own_count, BFS_THREADS), BFS_THREADS, 0, st>>>(fwd_begin, w->queue[qi], own_count, w->blk_off,
                                                                                   w->blk_total, w->chunks, w->counters + 2);
-                if (own_count <= TD_BATCHED_MAX_FRONTIER)      // (small frontiers: one block per SM is plenty of warps for their chunks)
-                    td_expand<true><<<own_count <= 1024 ? (unsigned)sm_count() : exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[qi], own_count, w->blk_off, w->blk_total,
+                // (full grid whatever the frontier size: the levels of few vertices AND few edges went to bfs_small_levels, and a
+                // 500-vertex frontier of hubs has 10^6 edges -- on one block per SM that level took 43 us instead of 22)
+                if (seen_mode && own_count <= TD_BATCHED_MAX_FRONTIER)
+                    td_expand_seen<true><<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[qi], own_count, w->blk_off, w->blk_total,
+                                                                           w->chunks, w->counters + 2, w->cand, edge_mask);
+                else if (seen_mode)
+                    td_expand_seen<false><<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[qi], own_count, w->blk_off, w->blk_total,
+                                                                            w->chunks, w->counters + 2, w->cand, edge_mask);
+                else if (own_count <= TD_BATCHED_MAX_FRONTIER)
+                    td_expand<true><<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[qi], own_count, w->blk_off, w->blk_total,
                                                                       w->chunks, w->counters + 2, w->visited, cand_l, edge_mask, pc);
                 else
                     td_expand<false><<<exp_grid, BFS_THREADS, 0, st>>>(fwd_begin, fwd_idx, w->queue[qi], own_count, w->blk_off, w->blk_total,
@@ -1067,9 +1191,10 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
                 use_all = 1;
             }
         }
-        if (!(fused_bu && ctl_bottom_up(state))) {
+        if (!published) {
             bfs_finish<L><<<fin_grid, BFS_THREADS, 0, st>>>(w->words, w->wp, world, use_all, cand_l, w->allcand, w->visited, fnext,
-                                                            nl, level, own_lo, own_hi, w->queue[qi ^ 1], w->counters, w->h_counters, ++w->seq);
+                                                            nl, level, own_lo, own_hi, w->queue[qi ^ 1], w->counters, w->h_counters, ++w->seq,
+                                                            nullptr, nullptr, seen_mode ? 1 : 0);
             launches++;
         }
         { uint32_t* t = fcur; fcur = fnext; fnext = t; }

@@ -401,7 +401,7 @@ def test_bfs_host_loop_and_deep_graph(gm, oracle, g_rmat, monkeypatch):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("mode", ["GMC_BFS_NO_SMALL", "GMC_BFS_FUSED_BU", "GMC_BFS_PERSISTENT", "GMC_BFS_DEVICE_LOOP"])
+@pytest.mark.parametrize("mode", ["GMC_BFS_NO_SMALL", "GMC_BFS_NO_SEEN", "GMC_BFS_NO_BU_MARK", "GMC_BFS_FUSED_BU", "GMC_BFS_PERSISTENT", "GMC_BFS_DEVICE_LOOP"])
 def test_bfs_loop_modes_agree(gm, oracle, g_rmat, monkeypatch, mode):
     """the default traversal (runs of small top-down levels in one CTA, bfs_small_levels; the rest as prepare / expand / finish
     launches) against the other ways to drive the same level kernels: no small-level kernel, one cooperative launch per
