@@ -489,9 +489,19 @@ __device__ __forceinline__ void combine_rows(const SweepArgs& A, double* s_red, 
     double diff = 0.0;
     for (int32_t k = blockIdx.x * NT + tid; k < A.K; k += gridDim.x * NT) {
         const int32_t p0 = __ldg(A.pbeg + k), p1 = __ldg(A.pbeg + k + 1), id = __ldg(A.prow + k);
-        double S = 0.0;
-        for (int32_t p = p0; p < p1; p++) S += __ldcg(A.parts + p);        // home part, then the segments in tier order
-        diff += finish_row(A, id, (uint32_t)__ldcs(A.od_flags + id), __ldcs(A.rank_in + id), S);
+        // the row's flags and old rank are fetched beside its parts, the parts four at a time (independent loads; added in slot
+        // order as before): a thread has 1-2 rows here, so this phase is a latency chain, not a bandwidth problem
+        const uint32_t of = (uint32_t)__ldcs(A.od_flags + id);
+        const double old = __ldcs(A.rank_in + id);
+        double S = 0.0;                                                     // home part, then the segments in tier order
+        for (int32_t p = p0; p < p1; p += 4) {
+            double v[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) v[j] = p + j < p1 ? __ldcg(A.parts + p + j) : 0.0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) if (p + j < p1) S += v[j];
+        }
+        diff += finish_row(A, id, of, old, S);
     }
     diff = butterfly(diff);
     if (lane == 0) s_red[warp] = diff;
@@ -1055,11 +1065,42 @@ int launch_init(const gmc_pr_plan* p, cudaStream_t st) {
 int launch_sweep(gmc_pr_plan* state, const gmc_pr_plan* p, SweepArgs A, cudaStream_t st) {
     static const bool pdl = getenv("GMC_PR_NO_PDL") == nullptr;
     static int coop_pdl_ok = 1;              // cleared when the driver refuses the two attributes together
-    cudaLaunchAttribute at[2];
+    cudaLaunchAttribute at[3];
     at[0].id = cudaLaunchAttributeCooperative;
     at[0].val.cooperative = 1;
     at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[1].val.programmaticStreamSerializationAllowed = 1;
+    // GMC_PR_L2_WINDOW_MB=W (experiment): the first W MB of the contribution vector this sweep gathers from (the ids of the
+    // largest in-degree, which on a power-law graph are the most gathered sources) are read with the persisting L2 property, so
+    // that the cold gathers of a vector larger than L2 (TW-shaped: 333 MB) do not evict them.  The two buffers alternate, so the
+    // set-aside is sized for both windows.
+    static const int l2_window_mb = env_int("GMC_PR_L2_WINDOW_MB", 0);
+    int n_extra = 0;
+    if (l2_window_mb > 0) {
+        static thread_local int set_aside_dev = -1;
+        int dev = 0;
+        GMC_CUDA(cudaGetDevice(&dev));
+        if (set_aside_dev != dev) {
+            int max_persist = 0;
+            GMC_CUDA(cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, dev));
+            const size_t want = std::min<size_t>((size_t)max_persist, 2 * ((size_t)l2_window_mb << 20));
+            GMC_CUDA(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want));
+            if (getenv("GMC_PR_L2_WINDOW_VERBOSE")) fprintf(stderr, "pr_sweep: persisting L2 set-aside %zu of max %d bytes\n", want, max_persist);
+            set_aside_dev = dev;
+        }
+        int max_win = 0;
+        GMC_CUDA(cudaDeviceGetAttribute(&max_win, cudaDevAttrMaxAccessPolicyWindowSize, dev));
+        size_t bytes = std::min<size_t>((size_t)l2_window_mb << 20, 8 * ((size_t)p->N + 2));
+        bytes = std::min<size_t>(bytes, (size_t)max_win);
+        static const double hit = getenv("GMC_PR_L2_WINDOW_HIT") ? atof(getenv("GMC_PR_L2_WINDOW_HIT")) : 1.0;
+        at[2].id = cudaLaunchAttributeAccessPolicyWindow;
+        at[2].val.accessPolicyWindow.base_ptr = const_cast<double*>(A.contrib_in);
+        at[2].val.accessPolicyWindow.num_bytes = bytes;
+        at[2].val.accessPolicyWindow.hitRatio = (float)hit;
+        at[2].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        at[2].val.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+        n_extra = 1;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)p->grid);
     cfg.blockDim = dim3(PR_THREADS);
@@ -1070,12 +1111,15 @@ int launch_sweep(gmc_pr_plan* state, const gmc_pr_plan* p, SweepArgs A, cudaStre
         A.bar_target = state->bar_arrivals;
         A.n_cb = p->grid;
         cfg.attrs = at;
-        cfg.numAttrs = (pdl && coop_pdl_ok) ? 2 : 1;
+        const bool two = pdl && coop_pdl_ok;
+        if (!two && n_extra) at[1] = at[2];
+        cfg.numAttrs = (two ? 2 : 1) + n_extra;
         cudaError_t e = cudaLaunchKernelEx(&cfg, pr_sweep, A);
-        if (e != cudaSuccess && cfg.numAttrs == 2) {       // cooperative + programmatic serialization not accepted: cooperative only
+        if (e != cudaSuccess && two) {       // cooperative + programmatic serialization not accepted: cooperative only
             cudaGetLastError();
             coop_pdl_ok = 0;
-            cfg.numAttrs = 1;
+            if (n_extra) at[1] = at[2];
+            cfg.numAttrs = 1 + n_extra;
             e = cudaLaunchKernelEx(&cfg, pr_sweep, A);
         }
         GMC_CUDA(e);
