@@ -163,7 +163,8 @@ __global__ void bfs_ctl_init(BfsCtl* ctl, float thr, int has_reverse, int rrd_di
 // ---- top-down, step 1: degrees of the queued vertices -> CTA-relative offsets + chunk descriptors ----------
 __device__ __forceinline__ void
 td_prepare_body(const int32_t* __restrict__ begin, const int32_t* queue, int32_t qcount, int32_t* blk_off,
-           int32_t* blk_total, int2* chunks, int32_t* nchunks, const int32_t* queue_alt, const BfsCtl* ctl) {
+           int32_t* blk_total, int2* chunks, int32_t* nchunks, const int32_t* queue_alt, const BfsCtl* ctl,
+           int32_t v_lo = 0, int32_t v_hi = INT_MAX) {
     __shared__ int32_t s_warp[BFS_THREADS / 32];
     __shared__ int32_t s_c0;
     if (ctl) {     // device-driven traversal: a top-down level? then the owned frontier is queue[qi], own_count long
@@ -176,7 +177,9 @@ td_prepare_body(const int32_t* __restrict__ begin, const int32_t* queue, int32_t
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int32_t qi = qblk * BFS_THREADS + tid;
     int32_t deg = 0;
-    if (qi < qcount) { const int32_t v = queue[qi]; deg = begin[v + 1] - begin[v]; }
+    // (sharded runs whose queue holds the WHOLE frontier -- the levels before were run redundantly by every rank -- expand only
+    // the vertices in [v_lo, v_hi): the others count as rows without edges)
+    if (qi < qcount) { const int32_t v = queue[qi]; if (v >= v_lo && v < v_hi) deg = begin[v + 1] - begin[v]; }
     int32_t inc = deg;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) { const int32_t t = __shfl_up_sync(FULLMASK, inc, o); if (lane >= o) inc += t; }
@@ -359,8 +362,24 @@ bu_scan_body(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_
 // expansion, nothing in a bottom-up level; bfs_finish)
 __global__ void __launch_bounds__(BFS_THREADS)
 td_prepare(const int32_t* __restrict__ begin, const int32_t* __restrict__ queue, int32_t qcount, int32_t* __restrict__ blk_off,
-           int32_t* __restrict__ blk_total, int2* __restrict__ chunks, int32_t* __restrict__ nchunks) {
-    td_prepare_body(begin, queue, qcount, blk_off, blk_total, chunks, nchunks, nullptr, nullptr);
+           int32_t* __restrict__ blk_total, int2* __restrict__ chunks, int32_t* __restrict__ nchunks, int32_t v_lo, int32_t v_hi) {
+    td_prepare_body(begin, queue, qcount, blk_off, blk_total, chunks, nchunks, nullptr, nullptr, v_lo, v_hi);
+}
+// the whole frontier as a queue, from the (replicated) frontier bitmap: sharded runs going back to levels that every rank runs
+// redundantly (bfs_small_levels).  At most SMALL_Q bits are set; their order in the queue does not matter.  *count starts at 0.
+__global__ void __launch_bounds__(BFS_THREADS)
+queue_from_bitmap(const uint32_t* __restrict__ frontier, int32_t words, int32_t* __restrict__ queue, int32_t* __restrict__ count, int32_t cap) {
+    for (int32_t w = blockIdx.x * BFS_THREADS + threadIdx.x; w < words; w += gridDim.x * BFS_THREADS) {
+        uint32_t b = frontier[w];
+        if (!b) continue;
+        int32_t at = atomicAdd(count, __popc(b));
+        while (b) {
+            const int k = __ffs(b) - 1;
+            b &= b - 1;
+            if (at < cap) queue[at] = (w << 5) + k;
+            at++;
+        }
+    }
 }
 template <bool BATCHED>
 __global__ void __launch_bounds__(BFS_THREADS)
@@ -970,8 +989,14 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     const bool seen_mode = world == 1 && getenv("GMC_BFS_NO_SEEN") == nullptr && getenv("GMC_BFS_DEVICE_LOOP") == nullptr &&
                            getenv("GMC_BFS_PERSISTENT") == nullptr && getenv("GMC_BFS_FUSED_BU") == nullptr;
     int qi = 0;     // queue[qi] = current level
+    // Sharded runs: the CSR, the bitmaps and level[] are replicated, so a level whose frontier is small is run by EVERY rank in
+    // full (bfs_small_levels, the single-GPU kernel) instead of expanding 1/world of it and allgathering `world` full bitmaps: no
+    // exchange at all for the first and the last levels of a traversal.  queue_full: queue[qi] holds the whole frontier (identical
+    // sets on every rank), not the owned part.  GMC_BFS_NO_SMALL_SHARDED=1: round-1 behaviour.
+    const bool small_sharded = world > 1 && getenv("GMC_BFS_NO_SMALL") == nullptr && getenv("GMC_BFS_NO_SMALL_SHARDED") == nullptr;
+    bool queue_full = small_sharded;
     bfs_init<L><<<init_grid, 256, 0, st>>>(level, n, invalid, root, w->visited, w->frontier_bm, w->cand, w->wp,
-                                           w->queue[0], root_owned ? 1 : 0, w->counters, world > 1 ? 1 : 0, seen_mode ? 1 : 0, w->spread);
+                                           w->queue[0], (root_owned || small_sharded) ? 1 : 0, w->counters, world > 1 ? 1 : 0, seen_mode ? 1 : 0, w->spread);
     launches++;
     // nobody sends candidates into a buffer its owner has not cleared yet
     if (peer) GMC_TRY(gmc_comm_stream_barrier(comm, st));
@@ -1091,7 +1116,7 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
         }
     }
     // runs of small top-down levels go to bfs_small_levels (one CTA, several levels per launch); GMC_BFS_NO_SMALL=1: never
-    const bool small_ok = world == 1 && getenv("GMC_BFS_NO_SMALL") == nullptr;
+    const bool small_ok = (world == 1 && getenv("GMC_BFS_NO_SMALL") == nullptr) || small_sharded;
     // GMC_BFS_FUSED_BU=1: bottom-up levels in one launch (bu_scan_finish) on a single GPU.  Measured SLOWER than scan + finish as
     // two launches (gpurun r3i, LJ-shaped, root 3: 0.324 against 0.281 ms; hub root 0.452 against 0.430): the block-wide queue
     // allocation keeps the 8 warps of a CTA resident until its slowest row scan ends, which costs more than the bitmap pass and
@@ -1102,7 +1127,15 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     uint32_t *fcur = w->frontier_bm, *fnext = w->frontier_bm + w->wp;      // every level writes fnext, then they swap
     int32_t small_refused = -1;       // level whose frontier had more than SMALL_E edges: it takes the grid path
     for (; !device_driven && !persistent;) {
-        if (small_ok && !ctl_bottom_up(state) && own_count > 0 && own_count <= SMALL_Q && small_refused != curr_level) {
+        if (small_ok && !ctl_bottom_up(state) && (world > 1 ? curr_count : own_count) > 0 && (world > 1 ? curr_count : own_count) <= SMALL_Q &&
+            small_refused != curr_level) {
+            if (world > 1 && !queue_full) {        // back from sharded levels: the whole frontier from the replicated bitmap
+                GMC_CUDA(cudaMemsetAsync(w->counters + 3, 0, sizeof(int32_t), st));
+                queue_from_bitmap<<<(unsigned)min(div_up(w->words, BFS_THREADS), sm_count() * 8), BFS_THREADS, 0, st>>>(fcur, w->words, w->queue[qi],
+                                                                                                                       w->counters + 3, SMALL_Q);
+                launches++;
+                queue_full = true;
+            }
             int max_levels = SMALL_LEVELS;
             if (sizeof(L) == 2) max_levels = min(max_levels, 32767 - curr_level);
             GMC_REQUIRE(max_levels > 0, GMC_ERR_STATE, "bfs: more levels than level_t can hold");
@@ -1162,9 +1195,13 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             bottom_up++;
             if (world > 1) GMC_TRY(gmc_comm_allgather(comm, cand_l + (size_t)rank * w->wpr, cand_l, sizeof(uint32_t) * (size_t)w->wpr, st));
         } else {
+            // queue_full (sharded, after levels every rank ran in full): the queue holds the whole frontier, td_prepare lets only the
+            // owned vertices count
+            if (queue_full) own_count = curr_count;
+            const int32_t v_lo = queue_full ? own_lo * 32 : 0, v_hi = queue_full ? (int32_t)min((long long)own_hi * 32, (long long)INT_MAX) : INT_MAX;
             if (own_count > 0) {
                 td_prepare<<<div_up(own_count, BFS_THREADS), BFS_THREADS, 0, st>>>(fwd_begin, w->queue[qi], own_count, w->blk_off,
-                                                                                  w->blk_total, w->chunks, w->counters + 2);
+                                                                                  w->blk_total, w->chunks, w->counters + 2, v_lo, v_hi);
                 // (full grid whatever the frontier size: the levels of few vertices AND few edges went to bfs_small_levels, and a
                 // 500-vertex frontier of hubs has 10^6 edges -- on one block per SM that level took 43 us instead of 22)
                 if (seen_mode && own_count <= TD_BATCHED_MAX_FRONTIER)
@@ -1198,6 +1235,7 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             launches++;
         }
         { uint32_t* t = fcur; fcur = fnext; fnext = t; }
+        if (world > 1) queue_full = false;         // bfs_finish queued the owned part of the new frontier
         GMC_CUDA(cudaGetLastError());
         GMC_TRY(wait_host_seq(w, st));    // the level's counts: the sequence number bfs_finish's last block writes into pinned memory
         const int32_t next_count = w->h_counters[0];
