@@ -28,11 +28,15 @@
 #include "gmc_common.cuh"
 #include "gmc_comm.h"
 #include <limits.h>
+#include <chrono>
 #include <vector>
 
 using namespace gmc;
 
 enum { ST_SMALL = 0, ST_QUE = 1, ST_Q2R = 2, ST_RD = 3, ST_R2Q = 4, ST_RRD = 5, ST_RR2Q = 6 };
+// words [BFS_MF_WORD, BFS_MF_WORD + 2) of the pinned host block: out-edges of the frontier a level leaves (64 bits), for the
+// direction policy of hop_dist (see run_bfs)
+constexpr int BFS_MF_WORD = 60;
 constexpr int BFS_THREADS = 256;
 constexpr int TD_CHUNK = 256;        // edge slots per warp chunk (8 per lane)
 constexpr int TD_BATCHED_MAX_FRONTIER = 8192;   // owned frontier vertices up to which td_expand batches a lane's 8 loads
@@ -128,7 +132,7 @@ template <typename L>
 __global__ void bfs_init(L* __restrict__ level, int32_t n, L invalid, int32_t root, uint32_t* __restrict__ visited,
                          uint32_t* __restrict__ frontier, uint32_t* __restrict__ cand, int32_t wp,
                          int32_t* __restrict__ queue, int root_owned, int32_t* __restrict__ counters, int two_cand = 0, int seen = 0,
-                         int32_t* __restrict__ spread = nullptr) {
+                         int32_t* __restrict__ spread = nullptr, unsigned long long* __restrict__ mf = nullptr) {
     constexpr int PER = 16 / (int)sizeof(L);
     const int32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nthr = gridDim.x * blockDim.x;
     int32_t done = 0;
@@ -151,7 +155,7 @@ __global__ void bfs_init(L* __restrict__ level, int32_t n, L invalid, int32_t ro
         if (two_cand) cand[wp + i] = 0u;
     }
     if (spread && tid < BFS_SPREAD) spread[tid] = 0;
-    if (tid == 0) { if (root_owned) queue[0] = root; counters[0] = 0; counters[1] = 0; counters[2] = 0; counters[3] = 0; }
+    if (tid == 0) { if (root_owned) queue[0] = root; counters[0] = 0; counters[1] = 0; counters[2] = 0; counters[3] = 0; if (mf) *mf = 0ull; }
 }
 
 __global__ void bfs_ctl_init(BfsCtl* ctl, float thr, int has_reverse, int rrd_direct) {
@@ -365,6 +369,15 @@ td_prepare(const int32_t* __restrict__ begin, const int32_t* __restrict__ queue,
            int32_t* __restrict__ blk_total, int2* __restrict__ chunks, int32_t* __restrict__ nchunks, int32_t v_lo, int32_t v_hi) {
     td_prepare_body(begin, queue, qcount, blk_off, blk_total, chunks, nchunks, nullptr, nullptr, v_lo, v_hi);
 }
+// own[i] |= OR over the other ranks r of slices[r * wpr + i]: the owner's end of the all-to-all exchange of a top-down level
+__global__ void __launch_bounds__(BFS_THREADS)
+or_slices(const uint32_t* __restrict__ slices, int world, int rank, int32_t wpr, uint32_t* __restrict__ own) {
+    for (int32_t i = blockIdx.x * BFS_THREADS + threadIdx.x; i < wpr; i += gridDim.x * BFS_THREADS) {
+        uint32_t v = own[i];
+        for (int r = 0; r < world; r++) if (r != rank) v |= slices[(size_t)r * wpr + i];
+        own[i] = v;
+    }
+}
 // the whole frontier as a queue, from the (replicated) frontier bitmap: sharded runs going back to levels that every rank runs
 // redundantly (bfs_small_levels).  At most SMALL_Q bits are set; their order in the queue does not matter.  *count starts at 0.
 __global__ void __launch_bounds__(BFS_THREADS)
@@ -431,9 +444,10 @@ template <typename L>
 __device__ __forceinline__ void
 finish_warp(int32_t w, int32_t words, int32_t wp, int world, int use_all, uint32_t* cand, const uint32_t* allcand, uint32_t* visited,
             uint32_t* frontier, L next_level, L* __restrict__ level, int32_t own_lo, int32_t own_hi, int32_t* next_queue,
-            int32_t* counters, int keep_cand = 0) {
+            int32_t* counters, int keep_cand = 0, const int32_t* __restrict__ deg_begin = nullptr, unsigned long long* mf = nullptr) {
     const int lane = threadIdx.x & 31;
     uint32_t nw = 0;
+    unsigned long long dsum = 0;       // deg_begin != null: out-edges of the new frontier vertices this lane stored
     if (w < words) {
         uint32_t c;
         if (use_all) {
@@ -473,7 +487,13 @@ finish_warp(int32_t w, int32_t words, int32_t wp, int world, int use_all, uint32
         if ((bits >> lane) & 1u) {
             level[v] = next_level;
             if (own_s) next_queue[qb + __popc(bits & ((1u << lane) - 1u))] = v;
+            if (deg_begin) dsum += (unsigned long long)(deg_begin[v + 1] - deg_begin[v]);
         }
+    }
+    if (deg_begin) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) dsum += __shfl_xor_sync(FULLMASK, dsum, o);
+        if (lane == 0 && dsum) atomicAdd(mf, dsum);
     }
 }
 
@@ -503,7 +523,7 @@ bfs_finish(int32_t words, int32_t wp, int world, int use_all, uint32_t* __restri
            uint32_t* __restrict__ visited, uint32_t* __restrict__ frontier, L next_level, L* __restrict__ level,
            int32_t own_lo, int32_t own_hi, int32_t* __restrict__ next_queue, int32_t* __restrict__ counters,
            volatile int32_t* __restrict__ host_out, int32_t seq, int32_t* __restrict__ queue_alt = nullptr, BfsCtl* ctl = nullptr,
-           int keep_cand = 0) {
+           int keep_cand = 0, const int32_t* __restrict__ deg_begin = nullptr, unsigned long long* mf = nullptr) {
     if (ctl) {     // device-driven traversal: level number and queue come from the control block
         if (ctl->done) {      // the traversal ended earlier in this batch of launches: only tell the host
             if (blockIdx.x == 0 && threadIdx.x == 0) { host_out[1] = 1; __threadfence_system(); host_out[2] = seq; }
@@ -513,7 +533,7 @@ bfs_finish(int32_t words, int32_t wp, int world, int use_all, uint32_t* __restri
         if (!ctl->qi) next_queue = queue_alt;       // next = queue[qi ^ 1]; next_queue = queue[0], queue_alt = queue[1]
     }
     finish_warp<L>(blockIdx.x * BFS_THREADS + threadIdx.x, words, wp, world, use_all, cand, allcand, visited, frontier, next_level, level,
-                   own_lo, own_hi, next_queue, counters, keep_cand);
+                   own_lo, own_hi, next_queue, counters, keep_cand, deg_begin, mf);
     // the last block to finish publishes the two level counts straight into the host's (mapped, pinned) memory and
     // resets the device counters: the host polls the sequence number instead of a memcpy + memset + stream sync per level
     __shared__ int s_last;
@@ -527,6 +547,11 @@ bfs_finish(int32_t words, int32_t wp, int world, int use_all, uint32_t* __restri
         __threadfence();
         const int32_t next_count = atomicAdd(&counters[0], 0), own = atomicAdd(&counters[1], 0);
         counters[0] = 0; counters[1] = 0; counters[2] = 0; counters[3] = 0;
+        if (mf) {
+            const unsigned long long e = atomicAdd(mf, 0ull);
+            *mf = 0ull;
+            host_out[BFS_MF_WORD] = (int32_t)(uint32_t)e; host_out[BFS_MF_WORD + 1] = (int32_t)(uint32_t)(e >> 32);
+        }
         if (!ctl) { host_out[0] = next_count; host_out[1] = own; }
         else {
             const int done = ctl_advance(ctl, next_count, own);
@@ -780,10 +805,34 @@ bfs_small_levels(const int32_t* __restrict__ begin, const int32_t* __restrict__ 
         __syncthreads();
     }
     __syncthreads();
+    // out-edges of the frontier the kernel leaves to the grid (queue[qi], `own` entries): the host's direction policy wants them
+    __shared__ unsigned long long s_mf;
+    if (tid == 0) s_mf = 0ull;
+    __syncthreads();
+    if (!ended) {
+        const int32_t* q = qi ? queue1 : queue0;
+        unsigned long long mine = 0;
+        for (int32_t i = tid; i < own; i += SMALL_THREADS) { const int32_t v = q[i]; mine += (unsigned long long)(begin[v + 1] - begin[v]); }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mine += __shfl_xor_sync(FULLMASK, mine, o);
+        if (lane == 0 && mine) atomicAdd(&s_mf, mine);
+    }
+    __syncthreads();
     if (tid == 0) {
         host_out[0] = n_done; host_out[1] = ended; host_out[3] = refused;
+        host_out[BFS_MF_WORD] = (int32_t)(uint32_t)s_mf; host_out[BFS_MF_WORD + 1] = (int32_t)(uint32_t)(s_mf >> 32);
         __threadfence_system();
         host_out[2] = seq;
+    }
+}
+static_assert(BFS_MF_WORD == SMALL_HDR + SMALL_LEVELS && BFS_MF_WORD + 2 <= BFS_HOST_WORDS, "layout of the pinned host block");
+
+// frontier bitmap from a (whole-frontier) queue; the bitmap was cleared before
+__global__ void __launch_bounds__(BFS_THREADS)
+bitmap_from_queue(const int32_t* __restrict__ queue, int32_t count, uint32_t* __restrict__ frontier) {
+    for (int32_t i = blockIdx.x * BFS_THREADS + threadIdx.x; i < count; i += gridDim.x * BFS_THREADS) {
+        const int32_t v = queue[i];
+        atomicOr(&frontier[v >> 5], 1u << (v & 31));
     }
 }
 
@@ -915,7 +964,7 @@ int ensure_ws(gmc_graph* g, int world) {
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->counters, sizeof(int32_t) * 8);
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->spread, sizeof(int32_t) * BFS_SPREAD);
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->level, sizeof(int32_t) * nn);
-    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->edge_sum, sizeof(unsigned long long));
+    if (rc == GMC_OK) rc = gmc_malloc((void**)&w->edge_sum, 2 * sizeof(unsigned long long));     // [1] = out-edges of the new frontier (bfs_finish)
     if (rc == GMC_OK) rc = gmc_malloc((void**)&w->ctl, sizeof(BfsCtl));
     if (rc == GMC_OK && cudaMallocHost((void**)&w->h_counters, sizeof(int32_t) * BFS_HOST_WORDS) != cudaSuccess) {
         set_error("bfs: cudaMallocHost failed"); rc = GMC_ERR_NOMEM;
@@ -944,7 +993,7 @@ int wait_host_seq(gmc_bfs_ws* w, cudaStream_t st) {
 template <typename L>
 int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_t* fwd_idx, const int32_t* rev_begin,
             const int32_t* rev_idx, int32_t root, L invalid, L* level_out_dev, gmc_bfs_info* info, cudaStream_t st,
-            const uint8_t* edge_mask = nullptr, bool save_child = false) {
+            const uint8_t* edge_mask = nullptr, bool save_child = false, bool free_policy = false) {
     GMC_REQUIRE(root >= 0 && root < g->N, GMC_ERR_ARG, "bfs: root %d out of range [0,%d)", root, g->N);
     GMC_REQUIRE(g->has_forward, GMC_ERR_STATE, "bfs: the forward CSR (node_idx) was not uploaded for this graph");
     const int world = comm ? comm->world : 1, rank = comm ? comm->rank : 0;
@@ -995,15 +1044,42 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     // sets on every rank), not the owned part.  GMC_BFS_NO_SMALL_SHARDED=1: round-1 behaviour.
     const bool small_sharded = world > 1 && getenv("GMC_BFS_NO_SMALL") == nullptr && getenv("GMC_BFS_NO_SMALL_SHARDED") == nullptr;
     bool queue_full = small_sharded;
+    // GMC_BFS_A2A=1 (experiment): exchange of the sharded top-down levels that stay as all-to-all of the candidate slices + OR at
+    // the owner + allgather of the owned slices instead of allgathering `world` whole bitmaps.  Measured on 4 GPUs, TW-shaped
+    // (profiles/r3o): 1.424 against 1.406 ms per traversal -- two collectives and a kernel cost what the smaller transfer saves.
+    const bool a2a = world > 1 && (getenv("GMC_BFS_A2A") ? atoi(getenv("GMC_BFS_A2A")) != 0 : false);
     bfs_init<L><<<init_grid, 256, 0, st>>>(level, n, invalid, root, w->visited, w->frontier_bm, w->cand, w->wp,
-                                           w->queue[0], (root_owned || small_sharded) ? 1 : 0, w->counters, world > 1 ? 1 : 0, seen_mode ? 1 : 0, w->spread);
+                                           w->queue[0], (root_owned || small_sharded) ? 1 : 0, w->counters, world > 1 ? 1 : 0, seen_mode ? 1 : 0, w->spread,
+                                           w->edge_sum + 1);
     launches++;
     // nobody sends candidates into a buffer its owner has not cleared yet
     if (peer) GMC_TRY(gmc_comm_stream_barrier(comm, st));
 
     int state = ST_SMALL;
     int32_t curr_level = 0, curr_count = 1, own_count = root_owned ? 1 : 0;
-    const float thr = (float)n * 0.05f;   // RRD_THRESHOLD, gm_bfs_template.h:359 (float arithmetic as in the reference)
+    // Direction policy.  gm_bfs_template traversals (levels + state trace are compared with the reference) switch on the
+    // reference's rule: bottom-up once a level finds >= 5 % of the vertices (RRD_THRESHOLD).  hop_dist is not a template instance in
+    // the reference (hop_dist.gm is a frontier-filtered sweep), only its distances are defined, so it is free to switch on EDGES
+    // (Beamer et al., direction-optimizing BFS): bottom-up as soon as the out-edges of the new frontier, m_f, exceed 1/alpha of the
+    // edges not yet explored, while the frontier grows.  On the TW-shaped graph the reference's rule runs the widest level top-down
+    // (e.g. 318 K frontier vertices, > 10^8 out-edges, 16 M vertices found: 1.17 ms of a 1.8 ms traversal on 4 GPUs); leaving
+    // bottom-up follows the reference's rule (RRD -> RR2Q -> QUE) either way.  GMC_BFS_REF_POLICY=1: the reference's rule everywhere.
+    const bool beamer = free_policy && has_reverse && getenv("GMC_BFS_REF_POLICY") == nullptr && getenv("GMC_BFS_DEVICE_LOOP") == nullptr &&
+                        getenv("GMC_BFS_PERSISTENT") == nullptr && getenv("GMC_BFS_FUSED_BU") == nullptr;
+    const double alpha = getenv("GMC_BFS_ALPHA") ? atof(getenv("GMC_BFS_ALPHA")) : 14.0;
+    double explored = 0.0;                // out-edges of the frontiers so far (as far as the levels reported them)
+    // RRD_THRESHOLD, gm_bfs_template.h:359 (float arithmetic as in the reference); beamer: the vertex-count rule never fires
+    const float thr = beamer ? 3.0e38f : (float)n * 0.05f;
+    const int32_t* const deg_begin = beamer ? fwd_begin : nullptr;
+    unsigned long long* const mf_dev = beamer ? w->edge_sum + 1 : nullptr;
+    // next state of a level that would run top-down: bottom-up instead when the frontier's out-edges say so
+    auto policy = [&](int next_state, int32_t next_count, int32_t prev_count) {
+        if (!beamer || ctl_bottom_up(next_state)) return next_state;
+        const double mf = (double)(((unsigned long long)(uint32_t)w->h_counters[BFS_MF_WORD + 1] << 32) | (uint32_t)w->h_counters[BFS_MF_WORD]);
+        explored += mf;
+        const double mu = (double)g->M - explored;
+        return (next_count > prev_count && mf * alpha > mu) ? (int)ST_RRD : next_state;
+    };
     const unsigned fin_grid = (unsigned)div_up(w->words, BFS_THREADS);
     const unsigned exp_grid = (unsigned)sm_count() * 8;
     // Measured on the LJ-shaped graph (gpurun r2e): device-driven 0.43 ms per traversal, host-driven 0.37 ms -- five launches per
@@ -1126,6 +1202,16 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     const bool bu_mark = world == 1 && !fused_bu && getenv("GMC_BFS_NO_BU_MARK") == nullptr;
     uint32_t *fcur = w->frontier_bm, *fnext = w->frontier_bm + w->wp;      // every level writes fnext, then they swap
     int32_t small_refused = -1;       // level whose frontier had more than SMALL_E edges: it takes the grid path
+    // GMC_BFS_LEVEL_TIMING=1 (profiling aid): host wall time of every level of the host-driven loop on stderr (rank 0)
+    const bool lvl_timing = getenv("GMC_BFS_LEVEL_TIMING") != nullptr && rank == 0;
+    auto lvl_t0 = std::chrono::steady_clock::now();
+    auto lvl_report = [&](const char* what, int st_, int32_t lvl, int32_t cnt) {
+        if (!lvl_timing) return;
+        const auto t1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "bfs level %d state %d count %d: %s %.1f us\n", lvl, st_, cnt, what, std::chrono::duration<double, std::micro>(t1 - lvl_t0).count());
+        lvl_t0 = t1;
+    };
+    if (lvl_timing) { cudaStreamSynchronize(st); lvl_report("init", state, 0, 1); }
     for (; !device_driven && !persistent;) {
         if (small_ok && !ctl_bottom_up(state) && (world > 1 ? curr_count : own_count) > 0 && (world > 1 ? curr_count : own_count) <= SMALL_Q &&
             small_refused != curr_level) {
@@ -1147,6 +1233,7 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             GMC_TRY(wait_host_seq(w, st));
             const int k = w->h_counters[0];
             const bool refused = w->h_counters[3] != 0;
+            lvl_report(refused ? "small levels (stopped: too many edges)" : "small levels", state, curr_level, curr_count);
             bool ended = false;
             for (int j = 0; j < k && !ended; j++) {      // replay the state machine over the counts of the levels it ran
                 w->state_trace.push_back(state);
@@ -1158,6 +1245,16 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             }
             if (ended) break;
             if (refused || k == 0) small_refused = curr_level;     // the level it stopped at has too many edges for one CTA
+            if (beamer && !ctl_bottom_up(state)) {
+                // (prev_count 0: a level the small kernel hands over has more edges than it takes -- count it as growing)
+                const int ns = policy(state, curr_count, 0);
+                if (ctl_bottom_up(ns)) {        // the scan probes the frontier bitmap, which the small levels do not keep
+                    GMC_CUDA(cudaMemsetAsync(fcur, 0, sizeof(uint32_t) * (size_t)w->wp, st));
+                    bitmap_from_queue<<<(unsigned)min(div_up(curr_count, BFS_THREADS), sm_count() * 8), BFS_THREADS, 0, st>>>(w->queue[qi], curr_count, fcur);
+                    launches++;
+                    state = ns;
+                }
+            }
             continue;
         }
         w->state_trace.push_back(state);
@@ -1223,6 +1320,15 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
                 // then the owned slices are allgathered in place: N/8 bytes per level in total instead of `world` full bitmaps
                 GMC_TRY(gmc_comm_stream_barrier(comm, st));
                 GMC_TRY(gmc_comm_allgather(comm, cand_l + (size_t)rank * w->wpr, cand_l, sizeof(uint32_t) * (size_t)w->wpr, st));
+            } else if (world > 1 && a2a) {
+                // slice o of every rank's candidates to its owner o (all-to-all), the owner ORs the `world` slices, the owned
+                // slices are allgathered in place like a bottom-up level: a rank receives 2 (world - 1) / world bitmaps
+                // instead of world - 1 whole ones
+                GMC_TRY(gmc_comm_alltoall(comm, cand_l, w->allcand, sizeof(uint32_t) * (size_t)w->wpr, st));
+                or_slices<<<(unsigned)min(div_up(w->wpr, BFS_THREADS), sm_count() * 8), BFS_THREADS, 0, st>>>(w->allcand, world, rank, w->wpr,
+                                                                                                           cand_l + (size_t)rank * w->wpr);
+                launches++;
+                GMC_TRY(gmc_comm_allgather(comm, cand_l + (size_t)rank * w->wpr, cand_l, sizeof(uint32_t) * (size_t)w->wpr, st));
             } else if (world > 1) {
                 GMC_TRY(gmc_comm_allgather(comm, cand_l, w->allcand, sizeof(uint32_t) * (size_t)w->wp, st));
                 use_all = 1;
@@ -1231,7 +1337,7 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
         if (!published) {
             bfs_finish<L><<<fin_grid, BFS_THREADS, 0, st>>>(w->words, w->wp, world, use_all, cand_l, w->allcand, w->visited, fnext,
                                                             nl, level, own_lo, own_hi, w->queue[qi ^ 1], w->counters, w->h_counters, ++w->seq,
-                                                            nullptr, nullptr, seen_mode ? 1 : 0);
+                                                            nullptr, nullptr, seen_mode ? 1 : 0, deg_begin, mf_dev);
             launches++;
         }
         { uint32_t* t = fcur; fcur = fnext; fnext = t; }
@@ -1241,10 +1347,12 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
         const int32_t next_count = w->h_counters[0];
         own_count = w->h_counters[1];
         qi ^= 1;
+        lvl_report(ctl_bottom_up(state) ? "bottom-up" : "top-down", state, curr_level, curr_count);
 
         // get_next_state (gm_bfs_template.h:352-421)
         if (next_count == 0) break;
-        const int next_state = bfs_next_state(state, next_count, curr_count, thr, has_reverse, rrd_direct);
+        int next_state = bfs_next_state(state, next_count, curr_count, thr, has_reverse, rrd_direct);
+        if (!published) next_state = policy(next_state, next_count, curr_count);       // (published: no bfs_finish, no edge count)
         curr_count = next_count;
         curr_level++;
         state = next_state;
@@ -1297,7 +1405,8 @@ int gmc_hop_dist_sharded_dev(gmc_graph* g, gmc_comm* comm, int32_t root, int32_t
     GMC_REQUIRE(g && dist_dev, GMC_ERR_ARG, "gmc_hop_dist_dev: NULL");
     GMC_REQUIRE(g->N > 0, GMC_ERR_ARG, "gmc_hop_dist_dev: empty graph");
     return run_bfs<int32_t>(g, comm, g->begin, g->node_idx, g->has_reverse ? g->r_begin : nullptr,
-                            g->has_reverse ? g->r_node_idx : nullptr, root, INT_MAX, dist_dev, info, as_stream(stream));
+                            g->has_reverse ? g->r_node_idx : nullptr, root, INT_MAX, dist_dev, info, as_stream(stream), nullptr, false,
+                            /*free_policy (hop_dist.gm defines distances, not a traversal order)*/ true);
 }
 
 int gmc_hop_dist_dev(gmc_graph* g, int32_t root, int32_t* dist_dev, gmc_bfs_info* info, void* stream) {

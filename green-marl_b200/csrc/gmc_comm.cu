@@ -27,6 +27,8 @@ struct NcclApi {
     ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*GroupStart)() = nullptr;
     ncclResult_t (*GroupEnd)() = nullptr;
     ncclResult_t (*GetVersion)(int*) = nullptr;
@@ -56,6 +58,8 @@ int load_nccl() {
     BIND(AllGather, "ncclAllGather");
     BIND(AllReduce, "ncclAllReduce");
     BIND(Broadcast, "ncclBroadcast");
+    BIND(Send, "ncclSend");
+    BIND(Recv, "ncclRecv");
     BIND(GroupStart, "ncclGroupStart");
     BIND(GroupEnd, "ncclGroupEnd");
     BIND(GetVersion, "ncclGetVersion");
@@ -100,6 +104,25 @@ int gmc_comm_allreduce_sum_i64(gmc_comm* c, const long long* send, long long* re
         return GMC_OK;
     }
     GMC_NCCL(g_api.AllReduce(send, recv, count, ncclInt64, ncclSum, c->nccl, st));
+    return GMC_OK;
+}
+
+// slice r of `send` (bytes_per_rank each) goes to rank r, which stores the slice it gets from rank q at recv + q * bytes_per_rank;
+// the own slice is not moved (recv's own slot is left untouched).  One grouped launch of 2 * (world - 1) point-to-point transfers.
+int gmc_comm_alltoall(gmc_comm* c, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st) {
+    if (!c || c->world == 1) return GMC_OK;
+    GMC_NCCL(g_api.GroupStart());
+    for (int r = 0; r < c->world; r++) {
+        if (r == c->rank) continue;
+        ncclResult_t res = g_api.Send((const char*)send + (size_t)r * bytes_per_rank, bytes_per_rank, ncclUint8, r, c->nccl, st);
+        if (res == ncclSuccess) res = g_api.Recv((char*)recv + (size_t)r * bytes_per_rank, bytes_per_rank, ncclUint8, r, c->nccl, st);
+        if (res != ncclSuccess) {
+            g_api.GroupEnd();
+            set_error("ncclSend/ncclRecv: %s", g_api.GetErrorString(res));
+            return GMC_ERR_CUDA;
+        }
+    }
+    GMC_NCCL(g_api.GroupEnd());
     return GMC_OK;
 }
 

@@ -14,6 +14,7 @@ struct gmc_comm {
 };
 
 int gmc_comm_allgather(gmc_comm* c, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st);
+int gmc_comm_alltoall(gmc_comm* c, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t st);
 int gmc_comm_allreduce_sum_f64(gmc_comm* c, const double* send, double* recv, size_t count, cudaStream_t st);
 int gmc_comm_allreduce_sum_i64(gmc_comm* c, const long long* send, long long* recv, size_t count, cudaStream_t st);
 int gmc_comm_allgather_segments(gmc_comm* c, void* buf, size_t elem_bytes, const int64_t* seg_off, const int64_t* seg_len,

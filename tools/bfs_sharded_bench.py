@@ -25,9 +25,12 @@ want = {}
 for r in roots:
     want[r], _ = g.hop_dist(r)
 res = {}
-for mode in ("sharded_all_levels", "small_levels_redundant"):
+for mode in ("sharded_all_levels", "small_redundant_allgather", "small_redundant_alltoall"):
+    # sharded_all_levels = round-1 form; the other two run the small levels in full on every rank and differ in the exchange of
+    # the top-down levels that stay sharded: allgather of `world` whole bitmaps / all-to-all of slices + OR + allgather of slices
     if mode == "sharded_all_levels": os.environ["GMC_BFS_NO_SMALL_SHARDED"] = "1"
     else: os.environ.pop("GMC_BFS_NO_SMALL_SHARDED", None)
+    os.environ["GMC_BFS_A2A"] = "1" if mode == "small_redundant_alltoall" else "0"
     ms, edges, bad, launches, levels = [], [], 0, [], []
     for r in roots:
         g.hop_dist_sharded_dev(comm, d_dev.data_ptr(), r)
@@ -41,7 +44,7 @@ for mode in ("sharded_all_levels", "small_levels_redundant"):
         bad += int(not (np.array_equal(lev, lev1) and list(tr) == list(tr1) and list(cnt) == list(cnt1)))
     res[mode] = (ms, edges, bad, launches, levels)
     if rank == 0:
-        print(f"{mode:24s} world {world} n {n} m {m}: {np.mean(ms):.4f} ms per traversal, {sum(edges) / sum(ms) / 1e6:.1f} GTEPS, "
+        print(f"{mode:26s} world {world} n {n} m {m}: {np.mean(ms):.4f} ms per traversal, {sum(edges) / sum(ms) / 1e6:.1f} GTEPS, "
               f"mismatching {bad}, launches {launches}, levels {levels}, ms {[round(x, 3) for x in ms]}", flush=True)
 t = torch.tensor([res[k][2] for k in res], dtype=torch.float64); dist.all_reduce(t)
 assert float(t.sum().item()) == 0, "sharded BFS differs from the single-GPU traversal"
