@@ -99,7 +99,7 @@ struct gmc_bfs_ws {
     int2* chunks = nullptr;           // [M/TD_CHUNK + N/256 + 2] (queue block, chunk-in-block)
     size_t chunk_cap = 0;
     int32_t* spread = nullptr;        // [BFS_SPREAD] per-warp counts of a bottom-up level (bu_scan_mark), summed by bfs_publish
-    int32_t* counters = nullptr;      // [8]: 0 = level count (global), 1 = owned queue count, 2 = nchunks
+    int32_t* counters = nullptr;      // [8]: 0 = level count (global), 1 = owned queue count, 2 = nchunks, 3 = blocks of bfs_finish that are done, 4-6 = bfs_persistent, 7 = queue_from_bitmap
     int32_t* h_counters = nullptr;    // pinned + mapped [BFS_HOST_WORDS]: 0 = level count, 1 = owned count, 2 = sequence number of the level that wrote
                                       // them; bfs_small_levels: 0 = levels done, 1 = traversal ended, 2 = sequence number, 3 = the level after those is too big for it, 4.. = count found by each level
     int32_t seq = 0;
@@ -1070,15 +1070,23 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     double explored = 0.0;                // out-edges of the frontiers so far (as far as the levels reported them)
     // RRD_THRESHOLD, gm_bfs_template.h:359 (float arithmetic as in the reference); beamer: the vertex-count rule never fires
     const float thr = beamer ? 3.0e38f : (float)n * 0.05f;
-    const int32_t* const deg_begin = beamer ? fwd_begin : nullptr;
-    unsigned long long* const mf_dev = beamer ? w->edge_sum + 1 : nullptr;
+    const int32_t* const deg_begin = fwd_begin;           // every level that leaves a frontier reports its out-edges
+    unsigned long long* const mf_dev = w->edge_sum + 1;
+    // Sharded runs: a top-down level whose frontier has at most red_max out-edges is expanded IN FULL by every rank (the CSR and
+    // the bitmaps are replicated): no exchange, where expanding 1/world of it costs an allgather of `world` whole bitmaps
+    // (TW-shaped, 4 GPUs: 150-180 us for a 51-vertex level that one GPU does in 105 us).  GMC_BFS_RED_EDGES=0: never.
+    const double red_max = getenv("GMC_BFS_RED_EDGES") ? atof(getenv("GMC_BFS_RED_EDGES")) : (double)(1 << 21);
+    double last_mf = 0.0;                 // out-edges of the current frontier ...
+    bool mf_known = false;                // ... when the level that left it reported them
     // next state of a level that would run top-down: bottom-up instead when the frontier's out-edges say so
     auto policy = [&](int next_state, int32_t next_count, int32_t prev_count) {
-        if (!beamer || ctl_bottom_up(next_state)) return next_state;
-        const double mf = (double)(((unsigned long long)(uint32_t)w->h_counters[BFS_MF_WORD + 1] << 32) | (uint32_t)w->h_counters[BFS_MF_WORD]);
-        explored += mf;
+        mf_known = false;
+        if (ctl_bottom_up(next_state)) return next_state;
+        last_mf = (double)(((unsigned long long)(uint32_t)w->h_counters[BFS_MF_WORD + 1] << 32) | (uint32_t)w->h_counters[BFS_MF_WORD]);
+        mf_known = true;
+        explored += last_mf;
         const double mu = (double)g->M - explored;
-        return (next_count > prev_count && mf * alpha > mu) ? (int)ST_RRD : next_state;
+        return (beamer && next_count > prev_count && last_mf * alpha > mu) ? (int)ST_RRD : next_state;
     };
     const unsigned fin_grid = (unsigned)div_up(w->words, BFS_THREADS);
     const unsigned exp_grid = (unsigned)sm_count() * 8;
@@ -1216,9 +1224,9 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
         if (small_ok && !ctl_bottom_up(state) && (world > 1 ? curr_count : own_count) > 0 && (world > 1 ? curr_count : own_count) <= SMALL_Q &&
             small_refused != curr_level) {
             if (world > 1 && !queue_full) {        // back from sharded levels: the whole frontier from the replicated bitmap
-                GMC_CUDA(cudaMemsetAsync(w->counters + 3, 0, sizeof(int32_t), st));
+                GMC_CUDA(cudaMemsetAsync(w->counters + 7, 0, sizeof(int32_t), st));        // ([7]: a word no level kernel uses)
                 queue_from_bitmap<<<(unsigned)min(div_up(w->words, BFS_THREADS), sm_count() * 8), BFS_THREADS, 0, st>>>(fcur, w->words, w->queue[qi],
-                                                                                                                       w->counters + 3, SMALL_Q);
+                                                                                                                       w->counters + 7, SMALL_Q);
                 launches++;
                 queue_full = true;
             }
@@ -1245,7 +1253,7 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             }
             if (ended) break;
             if (refused || k == 0) small_refused = curr_level;     // the level it stopped at has too many edges for one CTA
-            if (beamer && !ctl_bottom_up(state)) {
+            if (!ctl_bottom_up(state)) {
                 // (prev_count 0: a level the small kernel hands over has more edges than it takes -- count it as growing)
                 const int ns = policy(state, curr_count, 0);
                 if (ctl_bottom_up(ns)) {        // the scan probes the frontier bitmap, which the small levels do not keep
@@ -1270,6 +1278,7 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             pc.wpr = w->wpr; pc.world = world; pc.rank = rank;
         }
         bool published = false;       // the level's counts are already on their way to the host (no bfs_finish)
+        bool redundant = false;       // sharded: this (top-down) level is expanded in full by every rank
         if (state == ST_RRD && bu_mark) {
             bu_scan_mark<L><<<div_up(w->words * 32, BFS_THREADS), BFS_THREADS, 0, st>>>(rev_begin, rev_idx, n, w->words, fcur, fnext, w->visited,
                                                                                        seen_mode ? w->cand : nullptr, nl, level, w->spread);
@@ -1292,10 +1301,19 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             bottom_up++;
             if (world > 1) GMC_TRY(gmc_comm_allgather(comm, cand_l + (size_t)rank * w->wpr, cand_l, sizeof(uint32_t) * (size_t)w->wpr, st));
         } else {
-            // queue_full (sharded, after levels every rank ran in full): the queue holds the whole frontier, td_prepare lets only the
-            // owned vertices count
+            redundant = world > 1 && !peer && mf_known && last_mf <= red_max && red_max > 0.0;
+            if (redundant && !queue_full) {        // the whole frontier from the replicated bitmap
+                GMC_CUDA(cudaMemsetAsync(w->counters + 7, 0, sizeof(int32_t), st));
+                queue_from_bitmap<<<(unsigned)min(div_up(w->words, BFS_THREADS), sm_count() * 8), BFS_THREADS, 0, st>>>(fcur, w->words, w->queue[qi],
+                                                                                                                       w->counters + 7, n);
+                launches++;
+                queue_full = true;
+            }
+            // queue_full (sharded, after levels every rank ran in full): the queue holds the whole frontier; unless this level is run
+            // in full as well, td_prepare lets only the owned vertices count
             if (queue_full) own_count = curr_count;
-            const int32_t v_lo = queue_full ? own_lo * 32 : 0, v_hi = queue_full ? (int32_t)min((long long)own_hi * 32, (long long)INT_MAX) : INT_MAX;
+            const bool filter = queue_full && !redundant;
+            const int32_t v_lo = filter ? own_lo * 32 : 0, v_hi = filter ? (int32_t)min((long long)own_hi * 32, (long long)INT_MAX) : INT_MAX;
             if (own_count > 0) {
                 td_prepare<<<div_up(own_count, BFS_THREADS), BFS_THREADS, 0, st>>>(fwd_begin, w->queue[qi], own_count, w->blk_off,
                                                                                   w->blk_total, w->chunks, w->counters + 2, v_lo, v_hi);
@@ -1315,7 +1333,9 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
                                                                        w->chunks, w->counters + 2, w->visited, cand_l, edge_mask, pc);
                 launches += 2;
             }
-            if (peer) {
+            if (redundant) {
+                // nothing to exchange: every rank found every candidate
+            } else if (peer) {
                 // every rank's candidates have been ORed into their owners' slices once all expansions are complete (barrier);
                 // then the owned slices are allgathered in place: N/8 bytes per level in total instead of `world` full bitmaps
                 GMC_TRY(gmc_comm_stream_barrier(comm, st));
@@ -1335,13 +1355,14 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             }
         }
         if (!published) {
+            // (a level every rank ran in full queues the whole new frontier: the levels after it are usually small as well)
             bfs_finish<L><<<fin_grid, BFS_THREADS, 0, st>>>(w->words, w->wp, world, use_all, cand_l, w->allcand, w->visited, fnext,
-                                                            nl, level, own_lo, own_hi, w->queue[qi ^ 1], w->counters, w->h_counters, ++w->seq,
-                                                            nullptr, nullptr, seen_mode ? 1 : 0, deg_begin, mf_dev);
+                                                            nl, level, redundant ? 0 : own_lo, redundant ? w->words : own_hi, w->queue[qi ^ 1], w->counters,
+                                                            w->h_counters, ++w->seq, nullptr, nullptr, seen_mode ? 1 : 0, deg_begin, mf_dev);
             launches++;
         }
         { uint32_t* t = fcur; fcur = fnext; fnext = t; }
-        if (world > 1) queue_full = false;         // bfs_finish queued the owned part of the new frontier
+        if (world > 1) queue_full = redundant;     // bfs_finish queued the owned part of the new frontier (all of it after a level run in full)
         GMC_CUDA(cudaGetLastError());
         GMC_TRY(wait_host_seq(w, st));    // the level's counts: the sequence number bfs_finish's last block writes into pinned memory
         const int32_t next_count = w->h_counters[0];
@@ -1353,6 +1374,7 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
         if (next_count == 0) break;
         int next_state = bfs_next_state(state, next_count, curr_count, thr, has_reverse, rrd_direct);
         if (!published) next_state = policy(next_state, next_count, curr_count);       // (published: no bfs_finish, no edge count)
+        else mf_known = false;
         curr_count = next_count;
         curr_level++;
         state = next_state;
