@@ -34,6 +34,27 @@ def from_edges(oracle, n, edges):
     return prepared(oracle, begin, idx)
 
 
+def two_blobs(begin, node_idx, path_len=40):
+    """CSR of: the given graph (blob A) | a directed path of `path_len` vertices | a copy of the graph (blob B); the
+    largest-out-degree vertex of A feeds the path, the end of the path feeds the largest-out-degree vertex of B.  A
+    traversal from inside A grows, shrinks to ONE vertex for `path_len` levels, then grows again: every transition
+    between the small-level, the grid and the bottom-up forms of a BFS level happens twice."""
+    begin = np.asarray(begin, np.int64); node_idx = np.asarray(node_idx, np.int64)
+    n, m = len(begin) - 1, len(node_idx)
+    deg = np.diff(begin)
+    hub = int(deg.argmax())
+    src = np.repeat(np.arange(n, dtype=np.int64), deg)
+    p0, b0 = n, n + path_len
+    s = np.concatenate([src, [hub], np.arange(p0, p0 + path_len - 1), [p0 + path_len - 1], src + b0])
+    d = np.concatenate([node_idx, [p0], np.arange(p0 + 1, p0 + path_len), [b0 + hub], node_idx + b0])
+    order = np.lexsort((d, s))
+    s, d = s[order], d[order]
+    nn = 2 * n + path_len
+    nb = np.zeros(nn + 1, np.int64)
+    np.add.at(nb, s + 1, 1)
+    return np.cumsum(nb).astype(np.int32), d.astype(np.int32), hub
+
+
 def first_root_with_edges(g):
     deg = np.diff(g["begin"])
     nz = np.nonzero(deg)[0]

@@ -9,6 +9,7 @@ import torch.distributed as dist
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
 from gmb200_loader import load_package  # noqa: E402
 
 
@@ -53,6 +54,21 @@ def main():
         lev, li, trace, cnt = g.bfs_levels_sharded(comm, root)
         lev1, li1, trace1, cnt1 = g.bfs_levels(root)
         assert np.array_equal(lev, lev1) and list(trace) == list(trace1) and list(cnt) == list(cnt1)
+    # two copies of the graph joined by a 40-vertex path: the traversal shrinks to one vertex and grows again, so the sharded
+    # loop goes small levels (run in full by every rank) -> sharded levels -> small -> sharded -> small
+    import graphs
+    b2, i2, hub = graphs.two_blobs(g.array("begin"), g.array("node_idx"))
+    g3 = lib.graph_from_csr(b2, i2, semi_sort=True, make_reverse=True)
+    for root in (hub, len(b2) - 2):
+        d_dev = torch.empty(len(b2) - 1, dtype=torch.int32, device="cuda")
+        bi = g3.hop_dist_sharded_dev(comm, d_dev.data_ptr(), root)
+        d_one, bi1 = g3.hop_dist(root)
+        assert np.array_equal(d_dev.cpu().numpy(), d_one) and bi.levels == bi1.levels, f"rank {rank}: two-blob hop_dist differs (root {root})"
+        lev, li, trace, cnt = g3.bfs_levels_sharded(comm, root)
+        lev1, li1, trace1, cnt1 = g3.bfs_levels(root)
+        assert np.array_equal(lev, lev1) and list(trace) == list(trace1) and list(cnt) == list(cnt1), f"rank {rank}: two-blob levels differ"
+    comm.barrier()
+    g3.close()
     # triangle counting: slot ranges per rank + one allreduce == the single-GPU count, on every rank
     t_all, _ = g.triangle_counting_sharded(comm)
     t_one, _ = g.triangle_counting()

@@ -220,6 +220,24 @@ def test_bfs_no_reverse_top_down_only(gm, oracle, g_c1):
     assert info.bottom_up_levels == 0
 
 
+def test_bfs_two_blobs_and_a_path(gm, oracle):
+    """grow -> shrink to one vertex for 40 levels -> grow again: small levels, grid levels and bottom-up levels follow each
+    other in every order; hop_dist (edge-based direction policy) and gm_bfs_template levels (reference policy + trace)"""
+    base = graphs.rmat(oracle, 60000, 900000)
+    b, i, hub = graphs.two_blobs(base["begin"], base["node_idx"])
+    g = graphs.prepared(oracle, b, i)
+    dg = dev_graph(gm, g)
+    for root in (hub, graphs.first_root_with_edges(g), g["N"] - 1):
+        dist, info = dg.hop_dist(root)
+        want, _ = oracle.hop_dist(g["begin"], g["node_idx"], root)
+        assert np.array_equal(dist, want), root
+        lev, linfo, trace, cnt = dg.bfs_levels(root)
+        wlev, nl, wtrace, wcnt = oracle.bfs_levels(g["begin"], g["node_idx"], g["r_begin"], g["r_node_idx"], root)
+        assert np.array_equal(lev, wlev) and list(trace) == list(wtrace) and list(cnt) == list(wcnt), root
+    dist, info = dg.hop_dist(hub)
+    assert info.levels > 45 and info.bottom_up_levels >= 2       # both blobs reached, each through bottom-up levels
+
+
 def test_micro_graphs(gm, oracle):
     """hand-checkable cases: path, star, 2-cycle + dangling vertex, isolated vertex, self loop, multi-edge"""
     cases = {
