@@ -1355,10 +1355,14 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             }
         }
         if (!published) {
-            // (a level every rank ran in full queues the whole new frontier: the levels after it are usually small as well)
+            // (a level every rank ran in full queues the whole new frontier: the levels after it are usually small as well; the level
+            // after an RRD level is bottom-up whatever it finds -- RRD or RR2Q -- so it needs neither a queue nor the edge count)
+            const bool no_queue = state == ST_RRD;
+            const int32_t q_lo = no_queue ? 0 : (redundant ? 0 : own_lo), q_hi = no_queue ? 0 : (redundant ? w->words : own_hi);
             bfs_finish<L><<<fin_grid, BFS_THREADS, 0, st>>>(w->words, w->wp, world, use_all, cand_l, w->allcand, w->visited, fnext,
-                                                            nl, level, redundant ? 0 : own_lo, redundant ? w->words : own_hi, w->queue[qi ^ 1], w->counters,
-                                                            w->h_counters, ++w->seq, nullptr, nullptr, seen_mode ? 1 : 0, deg_begin, mf_dev);
+                                                            nl, level, q_lo, q_hi, w->queue[qi ^ 1], w->counters,
+                                                            w->h_counters, ++w->seq, nullptr, nullptr, seen_mode ? 1 : 0, no_queue ? nullptr : deg_begin,
+                                                            no_queue ? nullptr : mf_dev);
             launches++;
         }
         { uint32_t* t = fcur; fcur = fnext; fnext = t; }
