@@ -98,6 +98,9 @@ struct gmc_bfs_ws {
     int32_t* blk_total = nullptr;     // [ceil(N/256)]
     int2* chunks = nullptr;           // [M/TD_CHUNK + N/256 + 2] (queue block, chunk-in-block)
     size_t chunk_cap = 0;
+    int32_t* best_parent = nullptr;   // [N] bottom-up shortcut: the in-neighbour of largest out-degree (-1: no in-edges), see bp_rows
+    const int32_t* bp_key = nullptr;  // the reverse row array it was built from (NULL: not built)
+    int32_t* bp_list = nullptr;       // [1 + BP_LIST_CAP] rows too long for a warp
     int32_t* spread = nullptr;        // [BFS_SPREAD] per-warp counts of a bottom-up level (bu_scan_mark), summed by bfs_publish
     int32_t* counters = nullptr;      // [8]: 0 = level count (global), 1 = owned queue count, 2 = nchunks, 3 = blocks of bfs_finish that are done, 4-6 = bfs_persistent, 7 = queue_from_bitmap
     int32_t* h_counters = nullptr;    // pinned + mapped [BFS_HOST_WORDS]: 0 = level count, 1 = owned count, 2 = sequence number of the level that wrote
@@ -118,6 +121,7 @@ void gmc_bfs_ws_free(gmc_graph* g) {
     if (w->peer_ok) gmc_comm_ipc_close_all(w->world, w->rank, w->peer_base, w->peer_local);
     cudaFree(w->visited); cudaFree(w->frontier_bm); cudaFree(w->cand); cudaFree(w->allcand);
     cudaFree(w->queue[0]); cudaFree(w->queue[1]); cudaFree(w->blk_off); cudaFree(w->blk_total); cudaFree(w->chunks);
+    cudaFree(w->best_parent); cudaFree(w->bp_list);
     cudaFree(w->counters); cudaFree(w->spread); cudaFree(w->level); cudaFree(w->edge_sum); cudaFree(w->ctl);
     if (w->h_counters) cudaFreeHost(w->h_counters);
     delete w;
@@ -332,7 +336,7 @@ td_expand_body(const int32_t* __restrict__ begin, const int32_t* __restrict__ no
 // ---- bottom-up: warp w owns vertices [32w, 32w+32) = one word of the bitmaps ------------------------------------
 __device__ __forceinline__ void
 bu_scan_body(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t w_lo, int32_t w_hi,
-        const uint32_t* frontier_bm, const uint32_t* visited, uint32_t* cand, const BfsCtl* ctl) {
+        const uint32_t* frontier_bm, const uint32_t* visited, uint32_t* cand, const BfsCtl* ctl, const int32_t* __restrict__ best_parent = nullptr) {
     const int lane = threadIdx.x & 31;
     if (ctl && (ctl->done || !ctl_bottom_up(ctl->state))) return;
     const int32_t wstep = (gridDim.x * BFS_THREADS) >> 5;
@@ -341,7 +345,10 @@ bu_scan_body(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_
     const int32_t t = (w << 5) + lane;
     bool found = false;
     if (t < n && !((vis >> lane) & 1u)) {
-        const int32_t b = r_begin[t], e = r_begin[t + 1];
+        // best parent first (bp_rows): one coalesced load instead of the row, and rows without in-edges end here
+        const int32_t bp = best_parent ? best_parent[t] : -2;
+        if (bp >= 0) found = (frontier_bm[bp >> 5] >> (bp & 31)) & 1u;
+        const int32_t b = (found || bp == -1) ? 0 : r_begin[t], e = (found || bp == -1) ? 0 : r_begin[t + 1];
         // four parents per step: their ids, then their frontier words, are independent loads (the one-at-a-time loop was a
         // chain of two dependent loads per parent); any hit ends the scan as before
         for (int32_t nx = b; nx < e && !found; nx += 4) {
@@ -413,8 +420,9 @@ td_expand_seen(const int32_t* __restrict__ begin, const int32_t* __restrict__ no
 }
 __global__ void __launch_bounds__(BFS_THREADS)
 bu_scan(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t w_lo, int32_t w_hi,
-        const uint32_t* __restrict__ frontier_bm, const uint32_t* __restrict__ visited, uint32_t* __restrict__ cand) {
-    bu_scan_body(r_begin, r_node_idx, n, w_lo, w_hi, frontier_bm, visited, cand, nullptr);
+        const uint32_t* __restrict__ frontier_bm, const uint32_t* __restrict__ visited, uint32_t* __restrict__ cand,
+        const int32_t* __restrict__ best_parent) {
+    bu_scan_body(r_begin, r_node_idx, n, w_lo, w_hi, frontier_bm, visited, cand, nullptr, best_parent);
 }
 __global__ void __launch_bounds__(BFS_THREADS)
 bfs_level_a(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t w_lo, int32_t w_hi,
@@ -444,7 +452,8 @@ template <typename L>
 __device__ __forceinline__ void
 finish_warp(int32_t w, int32_t words, int32_t wp, int world, int use_all, uint32_t* cand, const uint32_t* allcand, uint32_t* visited,
             uint32_t* frontier, L next_level, L* __restrict__ level, int32_t own_lo, int32_t own_hi, int32_t* next_queue,
-            int32_t* counters, int keep_cand = 0, const int32_t* __restrict__ deg_begin = nullptr, unsigned long long* mf = nullptr) {
+            int32_t* counters, int keep_cand = 0, const int32_t* __restrict__ deg_begin = nullptr, unsigned long long* mf = nullptr,
+            int32_t n_vertices = 0) {
     const int lane = threadIdx.x & 31;
     uint32_t nw = 0;
     unsigned long long dsum = 0;       // deg_begin != null: out-edges of the new frontier vertices this lane stored
@@ -474,6 +483,19 @@ finish_warp(int32_t w, int32_t words, int32_t wp, int world, int use_all, uint32
         if (own_tot) base = atomicAdd(&counters[1], own_tot);
     }
     base = __shfl_sync(FULLMASK, base, 0) + pre - own;
+    int32_t db[33];
+    if (deg_begin && nw) {
+        const int32_t v0 = w << 5;
+        if (v0 + 32 <= n_vertices && (reinterpret_cast<uintptr_t>(deg_begin) & 15) == 0) {
+            const int4* __restrict__ p4 = reinterpret_cast<const int4*>(deg_begin + v0);
+#pragma unroll
+            for (int k = 0; k < 8; k++) { const int4 x = __ldg(p4 + k); db[4 * k] = x.x; db[4 * k + 1] = x.y; db[4 * k + 2] = x.z; db[4 * k + 3] = x.w; }
+            db[32] = __ldg(deg_begin + v0 + 32);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 33; k++) db[k] = __ldg(deg_begin + min(v0 + k, n_vertices));       // (the last word: vertices >= n have no edges)
+        }
+    }
     // the warp goes through its non-empty words together: lane b takes bit b of the word, so the level[] and queue
     // stores of one word are one coalesced 128-byte store each (a lane per word wrote 32 scattered elements in turn)
     unsigned has = __ballot_sync(FULLMASK, nw != 0u);
@@ -487,10 +509,16 @@ finish_warp(int32_t w, int32_t words, int32_t wp, int world, int use_all, uint32
         if ((bits >> lane) & 1u) {
             level[v] = next_level;
             if (own_s) next_queue[qb + __popc(bits & ((1u << lane) - 1u))] = v;
-            if (deg_begin) dsum += (unsigned long long)(deg_begin[v + 1] - deg_begin[v]);
         }
     }
     if (deg_begin) {
+        // out-edges of the lane's own word: begin[32 w .. 32 w + 32] was requested before the loop above (33 independent loads, 128
+        // contiguous bytes per lane), so the loop hid their latency.  (Two dependent loads per set bit inside the loop made it a
+        // chain of L2 round trips: +15 us on the 405 K-vertex level of the LJ-shaped graph.)
+        if (nw) {
+#pragma unroll
+            for (int k = 0; k < 32; k++) if ((nw >> k) & 1u) dsum += (unsigned long long)(db[k + 1] - db[k]);
+        }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) dsum += __shfl_xor_sync(FULLMASK, dsum, o);
         if (lane == 0 && dsum) atomicAdd(mf, dsum);
@@ -523,7 +551,7 @@ bfs_finish(int32_t words, int32_t wp, int world, int use_all, uint32_t* __restri
            uint32_t* __restrict__ visited, uint32_t* __restrict__ frontier, L next_level, L* __restrict__ level,
            int32_t own_lo, int32_t own_hi, int32_t* __restrict__ next_queue, int32_t* __restrict__ counters,
            volatile int32_t* __restrict__ host_out, int32_t seq, int32_t* __restrict__ queue_alt = nullptr, BfsCtl* ctl = nullptr,
-           int keep_cand = 0, const int32_t* __restrict__ deg_begin = nullptr, unsigned long long* mf = nullptr) {
+           int keep_cand = 0, const int32_t* __restrict__ deg_begin = nullptr, unsigned long long* mf = nullptr, int32_t n_vertices = 0) {
     if (ctl) {     // device-driven traversal: level number and queue come from the control block
         if (ctl->done) {      // the traversal ended earlier in this batch of launches: only tell the host
             if (blockIdx.x == 0 && threadIdx.x == 0) { host_out[1] = 1; __threadfence_system(); host_out[2] = seq; }
@@ -533,7 +561,7 @@ bfs_finish(int32_t words, int32_t wp, int world, int use_all, uint32_t* __restri
         if (!ctl->qi) next_queue = queue_alt;       // next = queue[qi ^ 1]; next_queue = queue[0], queue_alt = queue[1]
     }
     finish_warp<L>(blockIdx.x * BFS_THREADS + threadIdx.x, words, wp, world, use_all, cand, allcand, visited, frontier, next_level, level,
-                   own_lo, own_hi, next_queue, counters, keep_cand, deg_begin, mf);
+                   own_lo, own_hi, next_queue, counters, keep_cand, deg_begin, mf, n_vertices);
     // the last block to finish publishes the two level counts straight into the host's (mapped, pinned) memory and
     // resets the device counters: the host polls the sequence number instead of a memcpy + memset + stream sync per level
     __shared__ int s_last;
@@ -644,7 +672,8 @@ template <typename L>
 __global__ void __launch_bounds__(BFS_THREADS)
 bu_scan_mark(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n, int32_t words,
              const uint32_t* __restrict__ frontier_cur, uint32_t* __restrict__ frontier_next, uint32_t* __restrict__ visited,
-             uint32_t* __restrict__ seen, L next_level, L* __restrict__ level, int32_t* __restrict__ spread) {
+             uint32_t* __restrict__ seen, L next_level, L* __restrict__ level, int32_t* __restrict__ spread,
+             const int32_t* __restrict__ best_parent) {
     // the CTA's count: shared-memory atomics, flushed by whichever warp finishes last (no barrier after the scan: a finished warp
     // leaves).  A global atomic per warp -- 150 K of them on 64 neighbouring counters -- ran at the L2's one-per-clock rate for a
     // cache line and cost 30 us per level (gpurun r3l).
@@ -657,7 +686,9 @@ bu_scan_mark(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_
     const int32_t t = (w << 5) + lane;
     bool found = false;
     if (t < n && !((vis >> lane) & 1u)) {
-        const int32_t b = r_begin[t], e = r_begin[t + 1];
+        const int32_t bp = best_parent ? best_parent[t] : -2;           // best parent first, as in bu_scan_body
+        if (bp >= 0) found = (frontier_cur[bp >> 5] >> (bp & 31)) & 1u;
+        const int32_t b = (found || bp == -1) ? 0 : r_begin[t], e = (found || bp == -1) ? 0 : r_begin[t + 1];
         for (int32_t nx = b; nx < e && !found; nx += 4) {       // four parents per step, as in bu_scan_body
             int32_t u[4];
 #pragma unroll
@@ -682,6 +713,82 @@ bu_scan_mark(const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_
         if (atomicAdd_block(&s_arrived, 1) == BFS_THREADS / 32 - 1) {
             const int c = atomicAdd_block(&s_cnt, 0);
             if (c) atomicAdd(&spread[blockIdx.x & (BFS_SPREAD - 1)], c);
+        }
+    }
+}
+
+// ---- best parent of every vertex: the in-neighbour with the most out-edges (ties: the first in the row), -1 without in-edges ------
+// A bottom-up level asks "is ANY in-neighbour in the frontier"; on a power-law graph the in-neighbour of largest out-degree is the
+// likeliest one at every level, so the scan probes it first -- one coalesced load per vertex instead of r_begin + a sector of the
+// row -- and walks the row only when that fails.  Built once per graph (one pass over the reverse rows), kept in the workspace.
+constexpr int BP_LIST_CAP = 4096, BP_WARP_MAX = 32768;
+__device__ __forceinline__ unsigned long long bp_key_of(const int32_t* __restrict__ begin, int32_t src, int32_t pos) {
+    return ((unsigned long long)(uint32_t)(begin[src + 1] - begin[src]) << 32) | (unsigned long long)(0xffffffffu - (uint32_t)pos);
+}
+__global__ void __launch_bounds__(BFS_THREADS)
+bp_rows(const int32_t* __restrict__ begin, const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx, int32_t n,
+        int32_t* __restrict__ best_parent, int32_t* __restrict__ list) {
+    const int lane = threadIdx.x & 31;
+    const int32_t nwarps = (gridDim.x * BFS_THREADS) >> 5;
+    for (int32_t w = (blockIdx.x * BFS_THREADS + threadIdx.x) >> 5; w * 32 < n; w += nwarps) {
+        const int32_t t = w * 32 + lane;
+        int32_t b = 0, d = 0;
+        if (t < n) { b = r_begin[t]; d = r_begin[t + 1] - b; }
+        if (t < n && d <= 32) {          // short row: its lane alone
+            unsigned long long best = 0ull;
+            for (int32_t k = 0; k < d; k++) { const unsigned long long key = bp_key_of(begin, r_node_idx[b + k], k); best = key > best ? key : best; }
+            best_parent[t] = d ? r_node_idx[b + (int32_t)(0xffffffffu - (uint32_t)best)] : -1;
+        }
+        unsigned longs = __ballot_sync(FULLMASK, t < n && d > 32);
+        while (longs) {                  // long rows: the warp together, four entries per lane and step
+            const int src = __ffs(longs) - 1;
+            longs &= longs - 1;
+            const int32_t rb = __shfl_sync(FULLMASK, b, src), rd = __shfl_sync(FULLMASK, d, src), row = w * 32 + src;
+            if (rd > BP_WARP_MAX) {      // a hub: one CTA per row (bp_huge), unless the list is full
+                int32_t at = 0;
+                if (lane == 0) { at = atomicAdd(list, 1); if (at < BP_LIST_CAP) list[1 + at] = row; }
+                if (__shfl_sync(FULLMASK, at, 0) < BP_LIST_CAP) continue;
+            }
+            unsigned long long best = 0ull;
+            for (int32_t k0 = 0; k0 < rd; k0 += 128) {
+                int32_t sv[4];
+#pragma unroll
+                for (int j = 0; j < 4; j++) { const int32_t k = k0 + j * 32 + lane; sv[j] = k < rd ? r_node_idx[rb + k] : -1; }
+#pragma unroll
+                for (int j = 0; j < 4; j++) if (sv[j] >= 0) { const unsigned long long key = bp_key_of(begin, sv[j], k0 + j * 32 + lane); best = key > best ? key : best; }
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) { const unsigned long long x = __shfl_xor_sync(FULLMASK, best, o); best = x > best ? x : best; }
+            if (lane == 0) best_parent[row] = r_node_idx[rb + (int32_t)(0xffffffffu - (uint32_t)best)];
+        }
+    }
+}
+__global__ void __launch_bounds__(1024)
+bp_huge(const int32_t* __restrict__ begin, const int32_t* __restrict__ r_begin, const int32_t* __restrict__ r_node_idx,
+        int32_t* __restrict__ best_parent, const int32_t* __restrict__ list) {
+    __shared__ unsigned long long s_best[32];
+    const int32_t cnt = min(list[0], BP_LIST_CAP);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (int32_t i = blockIdx.x; i < cnt; i += gridDim.x) {
+        const int32_t row = list[1 + i], rb = r_begin[row], rd = r_begin[row + 1] - rb;
+        unsigned long long best = 0ull;
+        for (int32_t k0 = 0; k0 < rd; k0 += 4096) {
+            int32_t sv[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) { const int32_t k = k0 + j * 1024 + (int32_t)threadIdx.x; sv[j] = k < rd ? r_node_idx[rb + k] : -1; }
+#pragma unroll
+            for (int j = 0; j < 4; j++) if (sv[j] >= 0) { const unsigned long long key = bp_key_of(begin, sv[j], k0 + j * 1024 + (int32_t)threadIdx.x); best = key > best ? key : best; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { const unsigned long long x = __shfl_xor_sync(FULLMASK, best, o); best = x > best ? x : best; }
+        __syncthreads();
+        if (lane == 0) s_best[wid] = best;
+        __syncthreads();
+        if (wid == 0) {
+            best = s_best[lane];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) { const unsigned long long x = __shfl_xor_sync(FULLMASK, best, o); best = x > best ? x : best; }
+            if (lane == 0) best_parent[row] = r_node_idx[rb + (int32_t)(0xffffffffu - (uint32_t)best)];
         }
     }
 }
@@ -974,6 +1081,19 @@ int ensure_ws(gmc_graph* g, int world) {
     return GMC_OK;
 }
 
+// best_parent of the (forward, reverse) pair a traversal runs over; built on first use, rebuilt when another pair is asked for
+int ensure_best_parent(gmc_bfs_ws* w, int32_t n, const int32_t* fwd_begin, const int32_t* rev_begin, const int32_t* rev_idx, cudaStream_t st) {
+    if (w->bp_key == rev_begin && w->best_parent) return GMC_OK;
+    if (!w->best_parent) GMC_TRY(gmc_malloc((void**)&w->best_parent, sizeof(int32_t) * (size_t)(n ? n : 1)));
+    if (!w->bp_list) GMC_TRY(gmc_malloc((void**)&w->bp_list, sizeof(int32_t) * (1 + BP_LIST_CAP)));
+    GMC_CUDA(cudaMemsetAsync(w->bp_list, 0, sizeof(int32_t), st));
+    bp_rows<<<(unsigned)min(div_up(n, BFS_THREADS), sm_count() * 32), BFS_THREADS, 0, st>>>(fwd_begin, rev_begin, rev_idx, n, w->best_parent, w->bp_list);
+    bp_huge<<<(unsigned)sm_count(), 1024, 0, st>>>(fwd_begin, rev_begin, rev_idx, w->best_parent, w->bp_list);
+    GMC_CUDA(cudaGetLastError());
+    w->bp_key = rev_begin;
+    return GMC_OK;
+}
+
 // Wait until the kernel enqueued last has published its sequence number into the pinned block.
 int wait_host_seq(gmc_bfs_ws* w, cudaStream_t st) {
     volatile int32_t* h = w->h_counters;
@@ -1070,7 +1190,7 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     double explored = 0.0;                // out-edges of the frontiers so far (as far as the levels reported them)
     // RRD_THRESHOLD, gm_bfs_template.h:359 (float arithmetic as in the reference); beamer: the vertex-count rule never fires
     const float thr = beamer ? 3.0e38f : (float)n * 0.05f;
-    const int32_t* const deg_begin = fwd_begin;           // every level that leaves a frontier reports its out-edges
+    const int32_t* const deg_begin = (beamer || world > 1) ? fwd_begin : nullptr;     // the levels report the out-edges of the frontier they leave
     unsigned long long* const mf_dev = w->edge_sum + 1;
     // Sharded runs: a top-down level whose frontier has at most red_max out-edges is expanded IN FULL by every rank (the CSR and
     // the bitmaps are replicated): no exchange, where expanding 1/world of it costs an allgather of `world` whole bitmaps
@@ -1211,6 +1331,10 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     uint32_t *fcur = w->frontier_bm, *fnext = w->frontier_bm + w->wp;      // every level writes fnext, then they swap
     int32_t small_refused = -1;       // level whose frontier had more than SMALL_E edges: it takes the grid path
     // GMC_BFS_LEVEL_TIMING=1 (profiling aid): host wall time of every level of the host-driven loop on stderr (rank 0)
+    // bottom-up scans probe the in-neighbour of largest out-degree first (bp_rows; built at the graph's first bottom-up level,
+    // GMC_BFS_NO_BEST_PARENT=1: never)
+    const bool bp_on = has_reverse && getenv("GMC_BFS_NO_BEST_PARENT") == nullptr;
+    const int32_t* best_parent = nullptr;
     const bool lvl_timing = getenv("GMC_BFS_LEVEL_TIMING") != nullptr && rank == 0;
     auto lvl_t0 = std::chrono::steady_clock::now();
     auto lvl_report = [&](const char* what, int st_, int32_t lvl, int32_t cnt) {
@@ -1279,9 +1403,13 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
         }
         bool published = false;       // the level's counts are already on their way to the host (no bfs_finish)
         bool redundant = false;       // sharded: this (top-down) level is expanded in full by every rank
+        if (ctl_bottom_up(state) && bp_on && !best_parent) {
+            GMC_TRY(ensure_best_parent(w, n, fwd_begin, rev_begin, rev_idx, st));
+            best_parent = w->best_parent;
+        }
         if (state == ST_RRD && bu_mark) {
             bu_scan_mark<L><<<div_up(w->words * 32, BFS_THREADS), BFS_THREADS, 0, st>>>(rev_begin, rev_idx, n, w->words, fcur, fnext, w->visited,
-                                                                                       seen_mode ? w->cand : nullptr, nl, level, w->spread);
+                                                                                       seen_mode ? w->cand : nullptr, nl, level, w->spread, best_parent);
             bfs_publish<<<1, 32, 0, st>>>(w->spread, w->h_counters, ++w->seq);
             launches += 2;
             bottom_up++;
@@ -1295,7 +1423,7 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
         } else if (state == ST_RRD || state == ST_RR2Q) {
             if (own_hi > own_lo) {
                 bu_scan<<<div_up((own_hi - own_lo) * 32, BFS_THREADS), BFS_THREADS, 0, st>>>(rev_begin, rev_idx, n, own_lo, own_hi,
-                                                                                            fcur, w->visited, cand_l);
+                                                                                            fcur, w->visited, cand_l, best_parent);
                 launches++;
             }
             bottom_up++;
@@ -1362,7 +1490,7 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
             bfs_finish<L><<<fin_grid, BFS_THREADS, 0, st>>>(w->words, w->wp, world, use_all, cand_l, w->allcand, w->visited, fnext,
                                                             nl, level, q_lo, q_hi, w->queue[qi ^ 1], w->counters,
                                                             w->h_counters, ++w->seq, nullptr, nullptr, seen_mode ? 1 : 0, no_queue ? nullptr : deg_begin,
-                                                            no_queue ? nullptr : mf_dev);
+                                                            no_queue ? nullptr : mf_dev, n);
             launches++;
         }
         { uint32_t* t = fcur; fcur = fnext; fnext = t; }
