@@ -5,6 +5,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 #include <omp.h>
 #include "shl.h"
 #include "shl_arrays.hpp"
@@ -23,6 +24,35 @@ static double ms_since(const struct timeval& t0) {
 
 extern "C" {
 
+// `global = {` / `dma = {` blocks of `name = value,` lines, `--` comments (scripts/generate_settings.py:53-75)
+int shl__load_settings(const char* path, shl_settings* out) {
+    if (!out) return -1;
+    *out = shl_settings{0, 0, 0, 0, 0, 4096, 1, 0, 0};        // the generator's defaults (generate_settings.py:53-62)
+    FILE* f = path ? fopen(path, "r") : NULL;
+    if (!f) return -1;
+    char line[512], block[64] = "";
+    while (fgets(line, sizeof line, f)) {
+        if (char* c = strstr(line, "--")) *c = 0;
+        char name[64];
+        long value = 0;
+        if (sscanf(line, " %63[A-Za-z_0-9] = {", name) == 1 && strchr(line, '{')) { snprintf(block, sizeof block, "%s", name); continue; }
+        if (strchr(line, '}')) { block[0] = 0; continue; }
+        if (sscanf(line, " %63[A-Za-z_0-9] = %li", name, &value) != 2) continue;
+        if (!strcmp(block, "global")) {
+            if (!strcmp(name, "distribution")) out->distribution = (int)value;
+            else if (!strcmp(name, "replication")) out->replication = (int)value;
+            else if (!strcmp(name, "partitioning")) out->partitioning = (int)value;
+            else if (!strcmp(name, "hugepage")) out->hugepage = (int)value;
+            else if (!strcmp(name, "trim")) out->trim = (int)value;
+            else if (!strcmp(name, "stride")) out->stride = (int)value;
+            else if (!strcmp(name, "crc")) out->crc = (int)value;
+            else if (!strcmp(name, "static")) out->static_schedule = (int)value;
+        } else if (!strcmp(block, "dma") && !strcmp(name, "enable")) out->dma_enable = (int)value;
+    }
+    fclose(f);
+    return 0;
+}
+
 int shl__init(int nthreads, int partitioned) {
     const char* env = getenv("SHL_DEVICE");
     if (!env) env = getenv("GM_CUDA_DEVICE");
@@ -39,8 +69,20 @@ int shl__init(int nthreads, int partitioned) {
     // indexed arrays), -d SHL_DISTRIBUTION, -h SHL_HUGEPAGE.  Replication / partitioning over NUMA nodes = the device group over
     // the GPUs of the box (CSR replicated, rows partitioned): either switch selects every visible device (1, 2, 4 or 8) unless
     // GM_CUDA_DEVICES says otherwise; distribution and huge pages have no HBM equivalent and are reported as ignored.
-    const int s_rep = getenv("SHL_REPLICATION") ? atoi(getenv("SHL_REPLICATION")) : 0, s_part = getenv("SHL_PARTITION") ? atoi(getenv("SHL_PARTITION")) : 0;
-    const int s_dist = getenv("SHL_DISTRIBUTION") ? atoi(getenv("SHL_DISTRIBUTION")) : 0, s_huge = getenv("SHL_HUGEPAGE") ? atoi(getenv("SHL_HUGEPAGE")) : 0;
+    // The settings file run.sh generates beside them (shl__settings.lua) gives the defaults, the environment wins.
+    shl_settings file_set;
+    const char* spath = getenv("SHL_SETTINGS");
+    const bool have_file = shl__load_settings(spath ? spath : "shl__settings.lua", &file_set) == 0;
+    if (spath && !have_file) fprintf(stderr, "shl__init: cannot read the settings file %s (SHL_SETTINGS): using the environment only\n", spath);
+    const int s_rep = getenv("SHL_REPLICATION") ? atoi(getenv("SHL_REPLICATION")) : file_set.replication;
+    const int s_part = getenv("SHL_PARTITION") ? atoi(getenv("SHL_PARTITION")) : file_set.partitioning;
+    const int s_dist = getenv("SHL_DISTRIBUTION") ? atoi(getenv("SHL_DISTRIBUTION")) : file_set.distribution;
+    const int s_huge = getenv("SHL_HUGEPAGE") ? atoi(getenv("SHL_HUGEPAGE")) : file_set.hugepage;
+    if (have_file)
+        printf("SHOAL settings file %s: distribution=%d replication=%d partitioning=%d hugepage=%d trim=%d stride=%d crc=%d static=%d dma=%d "
+               "(trim / stride / static / dma: NUMA and OpenMP knobs without an HBM equivalent, ignored)\n", spath ? spath : "shl__settings.lua",
+               file_set.distribution, file_set.replication, file_set.partitioning, file_set.hugepage, file_set.trim, file_set.stride, file_set.crc,
+               file_set.static_schedule, file_set.dma_enable);
     int ndev = 1;
     if (const char* nd = getenv("GM_CUDA_DEVICES")) ndev = atoi(nd);
     else if (s_rep || s_part) {       // (the second argument of shl__init is the SHL_STATIC build flag, common_main.h:95-99: not a placement switch)

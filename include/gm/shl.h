@@ -29,6 +29,14 @@ void* shl__alloc_memory(size_t bytes);
 struct gmc_group;
 struct gmc_group* shl__device_group(void);
 void shl__print_array_conf(const char* name, size_t elements, size_t elem_bytes, int used, int replicated, int partitioned);
+// The Shoal settings file scripts/generate_settings.py:53-75 writes (scripts/run.sh:256-267: shl__settings.lua): a `global = { ... }`
+// block of `name = value,` lines (distribution, replication, partitioning, hugepage, trim, stride, crc, static) and a `dma = { enable = .. }`
+// block.  shl__init reads the file named by SHL_SETTINGS (or ./shl__settings.lua when present); the SHL_* environment variables
+// run.sh exports win over it.  Returns 0, or -1 when the file cannot be read; fields a file does not name keep their defaults.
+typedef struct shl_settings {
+    int distribution, replication, partitioning, hugepage, trim, stride, crc, static_schedule, dma_enable;
+} shl_settings;
+int shl__load_settings(const char* path, shl_settings* out);
 #ifdef __cplusplus
 }
 class Timer {

@@ -96,3 +96,26 @@ def test_binary_file_rejects_corrupt_csr(oracle, tmp_path):
         lib.file_write(p, b, i)
         with pytest.raises(pkg.GmcError):
             lib.file_read(p)
+
+
+def test_shoal_settings_file(tmp_path):
+    """shl__load_settings reads the file scripts/generate_settings.py:53-75 writes (same text, produced here as run.sh:264-267
+    would with -R 1 -P 1 -H 0 -T 1 -S 1 -W 4096 -A 0 -C 1); names it does not know and the dma_device blocks are skipped"""
+    from gmb200_loader import load_package
+    lib = ctypes.CDLL(load_package().lib_path())
+
+    class Settings(ctypes.Structure):
+        _fields_ = [(k, ctypes.c_int) for k in ("distribution", "replication", "partitioning", "hugepage", "trim", "stride", "crc",
+                                                "static_schedule", "dma_enable")]
+    lib.shl__load_settings.argtypes = [ctypes.c_char_p, ctypes.POINTER(Settings)]
+    text = ("-- global configuration\nglobal = {\n    distribution = 0,\n    replication = 1,\n    partitioning = 1,\n    hugepage = 0,\n"
+            "    trim = 1,\n    stride = 4096,\n    crc = 1,\n    static = 1\n}\n-- dma configuration\ndma = {\n    enable = 1,\n    vendor = 32902,\n"
+            "    device = 3616,\n    device_count = 2\n}\ndma_device_0 = {\n    count=8, \n    bus=0, \n    dev=4, \n    fun=0\n}\n")
+    path = tmp_path / "shl__settings.lua"
+    path.write_text(text)
+    s = Settings()
+    assert lib.shl__load_settings(str(path).encode(), ctypes.byref(s)) == 0
+    assert (s.distribution, s.replication, s.partitioning, s.hugepage, s.trim, s.stride, s.crc, s.static_schedule, s.dma_enable) == \
+        (0, 1, 1, 0, 1, 4096, 1, 1, 1)
+    assert lib.shl__load_settings(str(tmp_path / "missing.lua").encode(), ctypes.byref(s)) == -1
+    assert (s.replication, s.stride, s.crc) == (0, 4096, 1)          # the generator's defaults
