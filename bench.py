@@ -485,7 +485,7 @@ def run_single(args, n, m):
     a_bfs = float(np.sum(bfs_abytes)) / float(np.sum(bfs_ms)) / 1e6
     bfs = {"metric": "bfs_gteps", "value": round(sum(bfs_edges) / sum(bfs_ms) / 1e6, 3), "unit": "GTEPS",
            "roots": len(roots), "ms_per_traversal": round(float(np.mean(bfs_ms)), 4),
-           "edges_per_traversal": int(np.mean(bfs_edges)), "what": "hop_dist (direction-optimizing), device time",
+           "edges_per_traversal": int(np.mean(bfs_edges)), "what": "hop_dist (direction-optimizing: bottom-up when the frontier's out-edges exceed 1/14 of the unexplored edges), device time",
            "gpu_launches": int(bfs_launches),
            "roofline": {"bound": "hbm", "achieved": round(a_bfs, 1), "peak": peak, "unit": "GB/s", "frac": round(a_bfs / peak, 4),
                         "traffic": None, "peak_kind": peak_kind, "kernel": "whole traversal (bfs_small_levels for runs of small levels; td_prepare/td_expand/bfs_finish, bu_scan_mark or bu_scan/bfs_finish per wide level)",

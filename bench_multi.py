@@ -203,7 +203,7 @@ def run_multi(args, n, m, workload):
 
     bfs = {"metric": "bfs_gteps", "value": round(sum(bfs_edges) / sum(bfs_ms) / 1e6, 3), "unit": "GTEPS", "roots": len(roots),
            "ms_per_traversal": round(float(np.mean(bfs_ms)), 4), "edges_per_traversal": int(np.mean(bfs_edges)),
-           "levels": bfs_levels, "what": "sharded hop_dist (direction-optimizing, bitmap allgather per level), device time, max over ranks"}
+           "levels": bfs_levels, "what": "sharded hop_dist (direction chosen from the frontier's out-edges; small / medium levels run in full by every rank, the others sharded with a bitmap exchange per level), device time, max over ranks"}
 
     # ---- e2e: host buffers through the C ABI on every rank (CSR + reverse CSR H2D, plan, sweeps + exchange,
     # rank[] D2H), wall clock between barriers, max over ranks ---------------------------------------------

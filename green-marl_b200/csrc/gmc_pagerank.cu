@@ -45,7 +45,6 @@ using prp::Stream;
 #define GMC_PR_THREADS 1024
 #endif
 constexpr int PR_THREADS = GMC_PR_THREADS;    // one CTA per SM, 32 independent warps
-constexpr int PR_WARPS = PR_THREADS / 32;
 constexpr int CB_THREADS = 1024;              // pr_combine: one thread per split row
 constexpr int ZT = prp::ZT;                   // ids per zero-in-degree task
 // task sizes: shards with many entries run 4x / 2x larger tasks: the start and the end of a task (metadata chain, row
@@ -393,9 +392,9 @@ __device__ __forceinline__ void short_task(const SweepArgs& A, const Stream& st,
     int32_t base = __shfl_sync(FULL, sb, 0);
     int L = (__shfl_sync(FULL, sb, 1) - base) >> 5;
     int32_t w[8];
-#pragma unroll
     {
         const int32_t* __restrict__ pe = A.E + base + lane;       // one pointer, constant offsets: 2 instructions per load
+#pragma unroll
         for (int k = 0; k < 8; k++) w[k] = (k < L) ? __ldcs(pe + k * 32) : 0;
     }
     double S = 0.0, old = 0.0;
@@ -420,7 +419,6 @@ __device__ __forceinline__ void short_task(const SweepArgs& A, const Stream& st,
             nL = nq < ns ? (__shfl_sync(FULL, sb, nq + 1 <= ns ? nq + 1 : 0) - nbase) >> 5 : 0;
         }
         int32_t wn[8];
-#pragma unroll
         {
             // the 8 index loads of the next chunk: one pointer and one remaining-column count, so that each load is a
             // predicate + LDG with an immediate offset (the per-load address arithmetic was 25 % of the kernel's instructions)
