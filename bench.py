@@ -483,12 +483,20 @@ def run_single(args, n, m):
         bfs_abytes.append(4 * bi.edges_traversed + bi.reached * 8 + 2 * ((n + 7) // 8) * bi.levels)
         bfs_dists[r] = dist_dev.cpu().numpy()
     a_bfs = float(np.sum(bfs_abytes)) / float(np.sum(bfs_ms)) / 1e6
+    bfs_traffic, bfs_traffic_what = None, None       # dram bytes of one traversal (the first root), from the committed ncu launch list
+    try:
+        tb = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get("bfs_lj_root3", {})
+        if tb.get("nodes") == n and tb.get("edges") == m and tb.get("root") == roots[0]:
+            bfs_traffic, bfs_traffic_what = tb.get("dram_bytes_per_traversal"), "one traversal from root %d (%s); A_BFS of that root: %d" % (
+                roots[0], tb.get("source"), int(bfs_abytes[0]))
+    except Exception:
+        pass
     bfs = {"metric": "bfs_gteps", "value": round(sum(bfs_edges) / sum(bfs_ms) / 1e6, 3), "unit": "GTEPS",
            "roots": len(roots), "ms_per_traversal": round(float(np.mean(bfs_ms)), 4),
            "edges_per_traversal": int(np.mean(bfs_edges)), "what": "hop_dist (direction-optimizing: bottom-up when the frontier's out-edges exceed 1/14 of the unexplored edges), device time",
            "gpu_launches": int(bfs_launches),
            "roofline": {"bound": "hbm", "achieved": round(a_bfs, 1), "peak": peak, "unit": "GB/s", "frac": round(a_bfs / peak, 4),
-                        "traffic": None, "peak_kind": peak_kind, "kernel": "whole traversal (bfs_small_levels for runs of small levels; td_prepare/td_expand/bfs_finish, bu_scan_mark or bu_scan/bfs_finish per wide level)",
+                        "traffic": bfs_traffic, "traffic_what": bfs_traffic_what, "peak_kind": peak_kind, "kernel": "whole traversal (bfs_small_levels for runs of small levels; td_prepare/td_expand/bfs_finish, bu_scan_mark or bu_scan/bfs_finish per wide level)",
                         "alg_bytes_per_traversal": int(np.mean(bfs_abytes)),
                         "formula": "A_BFS = 4*M_r + N_r*(4+4) + 2*ceil(N/8)*L over the traversal's device time"}}
     # gm_bfs_template<short,...> traversal (bc / kosaraju's InBFS) on the first 4 roots
