@@ -79,7 +79,10 @@ class gm_bfs_template {
             }
         }
 
-        // traversal on the device
+        // traversal on the device.  The device entry point returns 16-bit levels whatever level_t is: the generator only
+        // instantiates level_t = short (src/backend_cpp/gm_cpp_gen_bfs.cc:90); a wider level_t gets the same values widened, and
+        // a traversal deeper than 32767 levels fails with an error (gmc_bfs_levels) instead of wrapping as the reference's short would.
+        static_assert(sizeof(level_t) >= sizeof(int16_t), "gm_bfs_template: level_t narrower than the device's 16-bit levels");
         std::vector<int16_t> lev16(n > 0 ? n : 1);
         std::vector<int32_t> trace(LEVEL_CAP), counts(LEVEL_CAP);
         gmc_bfs_info info;
