@@ -1195,7 +1195,10 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     // Sharded runs: a top-down level whose frontier has at most red_max out-edges is expanded IN FULL by every rank (the CSR and
     // the bitmaps are replicated): no exchange, where expanding 1/world of it costs an allgather of `world` whole bitmaps
     // (TW-shaped, 4 GPUs: 150-180 us for a 51-vertex level that one GPU does in 105 us).  GMC_BFS_RED_EDGES=0: never.
-    const double red_max = getenv("GMC_BFS_RED_EDGES") ? atof(getenv("GMC_BFS_RED_EDGES")) : (double)(1 << 21);
+    // The limit grows with the world size (2 M out-edges per rank, at most 16 M): what a sharded level saves is (1 - 1/world) of the
+    // one-GPU time, what it costs is the exchange of `world` bitmaps -- on 8 GPUs a 133 K-vertex level near the end of a traversal took
+    // 162 us sharded against 55 us on one GPU (profiles/r3r_bfs_levels_8gpu.txt).
+    const double red_max = getenv("GMC_BFS_RED_EDGES") ? atof(getenv("GMC_BFS_RED_EDGES")) : (double)(1 << 21) * (double)min(world, 8);
     double last_mf = 0.0;                 // out-edges of the current frontier ...
     bool mf_known = false;                // ... when the level that left it reported them
     // next state of a level that would run top-down: bottom-up instead when the frontier's out-edges say so
