@@ -113,6 +113,7 @@ struct gmc_bfs_ws {
     bool last_is_i16 = false;
     bool valid = false;
     int last_launches = 0;
+    int traversals = 0;               // traversals completed on this workspace (best_parent is built for graphs that are reused)
 };
 
 void gmc_bfs_ws_free(gmc_graph* g) {
@@ -1334,9 +1335,12 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     uint32_t *fcur = w->frontier_bm, *fnext = w->frontier_bm + w->wp;      // every level writes fnext, then they swap
     int32_t small_refused = -1;       // level whose frontier had more than SMALL_E edges: it takes the grid path
     // GMC_BFS_LEVEL_TIMING=1 (profiling aid): host wall time of every level of the host-driven loop on stderr (rank 0)
-    // bottom-up scans probe the in-neighbour of largest out-degree first (bp_rows; built at the graph's first bottom-up level,
-    // GMC_BFS_NO_BEST_PARENT=1: never)
-    const bool bp_on = has_reverse && getenv("GMC_BFS_NO_BEST_PARENT") == nullptr;
+    // bottom-up scans probe the in-neighbour of largest out-degree first (bp_rows).  The table costs one pass over all reverse
+    // edges with a random out-degree lookup each -- more than a traversal -- so it is built for graphs that are REUSED: at the first
+    // bottom-up level of the third traversal on (a one-shot driver such as bin/hop_dist never pays for it; bc / bc_random, many
+    // roots, the bench do).  GMC_BFS_NO_BEST_PARENT=1: never; GMC_BFS_BEST_PARENT_NOW=1: from the first traversal.
+    const bool bp_on = has_reverse && getenv("GMC_BFS_NO_BEST_PARENT") == nullptr &&
+                       (w->traversals >= 2 || (w->best_parent && w->bp_key == rev_begin) || getenv("GMC_BFS_BEST_PARENT_NOW") != nullptr);
     const int32_t* best_parent = nullptr;
     const bool lvl_timing = getenv("GMC_BFS_LEVEL_TIMING") != nullptr && rank == 0;
     auto lvl_t0 = std::chrono::steady_clock::now();
@@ -1517,6 +1521,7 @@ int run_bfs(gmc_graph* g, gmc_comm* comm, const int32_t* fwd_begin, const int32_
     if (!device_driven && !persistent) GMC_CUDA(cudaEventRecord(ev1, st));
     GMC_CUDA(cudaStreamSynchronize(st));
     w->valid = true;
+    w->traversals++;
     w->last_is_i16 = sizeof(L) == 2;
     w->last_launches = launches;
     if (info) {

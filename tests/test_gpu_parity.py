@@ -238,6 +238,23 @@ def test_bfs_two_blobs_and_a_path(gm, oracle):
     assert info.levels > 45 and info.bottom_up_levels >= 2       # both blobs reached, each through bottom-up levels
 
 
+def test_bfs_best_parent_and_reference_policy(gm, oracle, g_rmat, monkeypatch):
+    """bottom-up scans with the best-parent table from the first traversal on (normally built for reused graphs only), and
+    hop_dist under the reference's direction rule: same distances"""
+    root = int(np.diff(g_rmat["begin"]).argmax())
+    want, _ = oracle.hop_dist(g_rmat["begin"], g_rmat["node_idx"], root)
+    monkeypatch.setenv("GMC_BFS_BEST_PARENT_NOW", "1")
+    dg = dev_graph(gm, g_rmat)
+    dist, info = dg.hop_dist(root)
+    assert np.array_equal(dist, want) and info.bottom_up_levels >= 1
+    monkeypatch.delenv("GMC_BFS_BEST_PARENT_NOW")
+    monkeypatch.setenv("GMC_BFS_REF_POLICY", "1")
+    dist2, info2 = dev_graph(gm, g_rmat).hop_dist(root)
+    assert np.array_equal(dist2, want)
+    _, _, wtrace, _ = oracle.bfs_levels(g_rmat["begin"], g_rmat["node_idx"], g_rmat["r_begin"], g_rmat["r_node_idx"], root)
+    assert info2.bottom_up_levels == sum(1 for s in wtrace if s in (5, 6))      # the reference's rule: the template's switches
+
+
 def test_micro_graphs(gm, oracle):
     """hand-checkable cases: path, star, 2-cycle + dangling vertex, isolated vertex, self loop, multi-edge"""
     cases = {
